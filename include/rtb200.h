@@ -1,0 +1,200 @@
+/* rtb200.h -- C ABI of librtb200.so, the B200-native (sm_100a CUDA) render path that
+ * replaces the reference's GLSL compute-shader dispatch.
+ *
+ * What it replaces (file:line relative to Rodyll/Ray-Tracing-GPU, Projet-INF8702/):
+ *   - CNuanceurCalculProg (NuanceurCalculProg.h:73-132): create / compile / activate one
+ *     compute program                                   -> rtb200_create / rtb200_destroy
+ *   - the two std140 UBO uploads of CScene::LancerRayons (Scene.cpp:704-783 "General",
+ *     Scene.cpp:799-1269 "SceneData": glBufferData + glBindBufferBase)
+ *                                                        -> rtb200_set_scene (+ rtb200_frame)
+ *   - glBindImageTexture + glDispatchCompute(W/16,H/16,1) + glMemoryBarrier
+ *     (Scene.cpp:697-698, 1307-1310) and the kernel rayTracing.glsl:128-509
+ *                                                        -> rtb200_render
+ * The plug-in point stays where the reference has it: the `if (CVar::g_ComputerShadersON)`
+ * branch of CScene::LancerRayons() (Scene.cpp:692).  The results are those of the
+ * reference's C++ CPU renderer (Scene.cpp:1535-1563, 1705-1861), with the reflection /
+ * refraction block of Scene.cpp:1779-1823 enabled and bounded by max_bounces.
+ *
+ * Conventions
+ *   - plain C, plain pointers and sizes; every entry point returns an int status
+ *     (0 = RTB200_OK, negative = RTB200_E_*); nothing exits, nothing throws.
+ *   - the caller owns every host array it passes; the library copies during the call and
+ *     keeps no host pointer.  The context owns all device memory, streams, events and the
+ *     NCCL communicator.
+ *   - a context is bound to ONE GPU and is not thread-safe (one caller thread), like the
+ *     GL context it replaces.  Multi-GPU = one context per GPU (one process or thread per
+ *     GPU) joined with rtb200_comm_init; image row-bands are sharded across the ranks and
+ *     the framebuffer is gathered to rank 0 with NCCL inside rtb200_render.
+ *   - all geometry is FINAL: ISurface::Pretraitement (Triangle.cpp:108, Plan.cpp:101,
+ *     Quadrique.cpp:110) has already been applied by the host scene classes.
+ *   - images: row 0 is the BOTTOM scanline (Scene.cpp:1556: index (x + y*W)), float RGB is
+ *     unclamped, RGBA8 is floor(clamp(c,0,1)*255+0.5) with A = 255 and NaN -> 0.
+ *   - there is NO CPU fallback: without a usable CUDA device every compute entry point
+ *     fails with RTB200_E_CUDA.
+ */
+#ifndef RTB200_H
+#define RTB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTB200_ABI_VERSION 1
+
+enum {
+    RTB200_OK            =  0,
+    RTB200_E_ARG         = -1,   /* bad argument / inconsistent sizes                        */
+    RTB200_E_CUDA        = -2,   /* CUDA runtime error (text: rtb200_last_error)             */
+    RTB200_E_NCCL        = -3,   /* NCCL error or NCCL library not loadable                   */
+    RTB200_E_OOM         = -4,   /* device or pinned-host allocation failed                   */
+    RTB200_E_CAPACITY    = -5,   /* secondary-ray queues overflowed even at the smallest chunk */
+    RTB200_E_STATE       = -6    /* call order (e.g. render before set_scene, bvh not built)  */
+};
+
+/* rtb200_frame.flags */
+enum {
+    RTB200_F_USE_BVH      = 1u << 0,  /* triangles through the GPU-built LBVH (rtb200_build_bvh)        */
+    RTB200_F_NO_SECONDARY = 1u << 1,  /* as-shipped reference: no reflection / refraction rays           */
+    RTB200_F_EXACT_FP     = 1u << 2,  /* no FMA contraction: same rounding sequence as the CPU reference  */
+    RTB200_F_FORCE_STREAM = 1u << 3,  /* always use the tiled (streamed) brute-force kernels              */
+    RTB200_F_FORCE_RESIDENT = 1u << 4 /* always use the scene-resident fused kernel (fails if too large)  */
+};
+
+/* Material block of ISurface (ISurface.h:24-41; defaults ISurface.cpp:15-25). 10 floats. */
+typedef struct rtb200_material {
+    float color[3];      /* m_Couleur (already /255 when it came from a scene file)          */
+    float ambient;       /* m_CoeffAmbient   (0.2)                                           */
+    float diffuse;       /* m_CoeffDiffus    (0.8)                                           */
+    float specular;      /* m_CoeffSpeculaire                                                */
+    float shininess;     /* m_CoeffShininess                                                 */
+    float reflect;       /* m_CoeffReflexion                                                 */
+    float refract;       /* m_CoeffRefraction                                                */
+    float ior;           /* m_IndiceDeRefraction                                             */
+} rtb200_material;
+
+/* CLumiere (Lumiere.h:19-48). 7 floats. */
+typedef struct rtb200_light {
+    float position[3];
+    float color[3];
+    float intensity;
+} rtb200_light;
+
+/* Scene = what the "SceneData" UBO carried (rayTracing.glsl:97-107), without its caps of
+ * 10 per type, as structure-of-arrays.  *_order[i] is the insertion index of the primitive
+ * in CScene::m_Surfaces (Scene.cpp:107): ties in distance go to the lowest order, exactly as
+ * the linear scan of Scene.cpp:1710-1715 resolves them.  Orders must be a permutation of
+ * 0..T+Q+P-1 and increasing within each array. */
+typedef struct rtb200_scene {
+    int32_t n_triangles, n_quadrics, n_planes, n_lights, n_materials;
+    const float*   tri_points;     /* [T][3][3]  m_Pts after Pretraitement (Triangle.h:20)           */
+    const float*   tri_normal;     /* [T][3]     m_Normale (Triangle.cpp:199-204)                    */
+    const int32_t* tri_material;   /* [T]                                                             */
+    const int32_t* tri_order;      /* [T]                                                             */
+    const float*   quad_coef;      /* [Q][10]    A B C | mixed yz xz xy | linear x y z | K  (Quadrique.h:20-29) */
+    const int32_t* quad_material;  /* [Q] */
+    const int32_t* quad_order;     /* [Q] */
+    const float*   plane_coef;     /* [P][4]     normal xyz, constant (Plan.h:11-12)                 */
+    const int32_t* plane_material; /* [P] */
+    const int32_t* plane_order;    /* [P] */
+    const rtb200_material* materials; /* [M] */
+    const rtb200_light*    lights;    /* [L] */
+} rtb200_scene;
+
+/* Frame = what the "General" UBO carried (rayTracing.glsl:79-91) plus the CScene knobs the
+ * CPU renderer reads (Scene.cpp:68-70, 162, 180, 197, 214). */
+typedef struct rtb200_frame {
+    int32_t  width, height;        /* pixels; no multiple-of-16 / power-of-two restriction           */
+    int32_t  spp_grid;             /* k: k*k regular sub-pixel grid, sample (i,j) of pixel (X,Y) is   */
+                                   /* the reference's primary ray at (k*X+i, k*Y+j) of a kW x kH      */
+                                   /* image; pixel = mean of the k*k float RGB results.  1 = reference */
+    int32_t  max_bounces;          /* m_NbRebondsMax (reference default 20)                           */
+    float    min_energy;           /* m_EnergieMinRayon (0.01)                                        */
+    float    scene_ior;            /* m_IndiceRefractionScene (1.0)                                   */
+    float    background[3];        /* m_CouleurArrierePlan                                            */
+    float    cam_pos[3];           /* m_Camera.Position                                               */
+    float    cam_u[3], cam_v[3], cam_n[3]; /* rows 0,1,2 of m_Camera.Orientation (Scene.cpp:656-659)  */
+    float    half_w, half_h;       /* Scene.cpp:676-677                                               */
+    uint32_t flags;                /* RTB200_F_*                                                      */
+    int32_t  band_rows;            /* multi-GPU: height of the interleaved row bands (0 = default 16) */
+} rtb200_frame;
+
+/* Device-side measurements of the last rtb200_render on THIS rank. */
+typedef struct rtb200_stats {
+    double   ms_render;            /* CUDA-event time, first kernel .. last kernel of the frame       */
+    double   ms_gather;            /* NCCL gather + de-interleave (0 without a communicator)          */
+    double   ms_h2d, ms_d2h;       /* copies done inside the call (0 when none were requested)        */
+    uint64_t rays_primary, rays_shadow, rays_reflect, rays_refract;
+    uint64_t tests_triangle, tests_quadric, tests_plane;   /* ray-primitive tests entered             */
+    uint64_t bvh_nodes_visited;
+    uint64_t nan_pixels;           /* NaN channels quantised to 0                                     */
+    uint32_t kernel_launches;      /* kernels launched by the call                                    */
+    uint32_t depth_levels;         /* wavefront levels that held at least one ray                     */
+    uint32_t path;                 /* 0 = scene-resident fused kernels, 1 = streamed tiled kernels, 2 = LBVH */
+    uint32_t chunks;               /* image chunks the frame was split into                           */
+    double   ms_trace_nearest, ms_trace_shadow, ms_shade;  /* streamed path: per-stage totals         */
+} rtb200_stats;
+
+typedef struct rtb200_ctx rtb200_ctx;
+
+/* --- lifetime --------------------------------------------------------------------------- */
+int  rtb200_abi_version(void);
+/* Creates a context on CUDA device `device_id` (the replacement for constructing
+ * CNuanceurCalculProg + compilerEtLier, NuanceurCalculProg.cpp:57,280). */
+int  rtb200_create(int device_id, rtb200_ctx** out);
+void rtb200_destroy(rtb200_ctx* ctx);
+const char* rtb200_error_string(int status);
+/* Text of the last CUDA/NCCL failure seen by this context ("" if none). */
+const char* rtb200_last_error(const rtb200_ctx* ctx);
+
+/* --- scene -------------------------------------------------------------------------------- */
+/* Validates, packs to the device layout and uploads (one pinned staging buffer, one async copy). */
+int  rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* scene);
+/* Optional: GPU-built LBVH over the triangles of the current scene (Morton codes, radix sort,
+ * Karras hierarchy, bottom-up refit).  Planes and quadrics stay in the brute-force side list. */
+int  rtb200_build_bvh(rtb200_ctx* ctx);
+
+/* --- render ------------------------------------------------------------------------------- */
+/* Renders one frame.  out_rgb_f32 (W*H*3 floats) and out_rgba8 (W*H*4 bytes) are HOST
+ * pointers, either may be NULL (nothing is copied back for a NULL pointer; the frame stays
+ * on the device and can be fetched later with rtb200_read_frame).  With a communicator the
+ * frame is sharded over the ranks in interleaved row bands and gathered on rank 0; the
+ * output pointers are ignored on the other ranks.  Synchronous: returns when the frame is
+ * complete (and copied, if requested). */
+int  rtb200_render(rtb200_ctx* ctx, const rtb200_frame* frame,
+                   float* out_rgb_f32, uint8_t* out_rgba8, rtb200_stats* stats);
+int  rtb200_read_frame(rtb200_ctx* ctx, float* out_rgb_f32, uint8_t* out_rgba8);
+
+/* Ray-level entry points used by the parity tests (the per-ray oracle of SURVEY.md 8c has
+ * the same shape): n rays in, nearest hit (insertion order index or -1, distance, normal)
+ * or shadow-filter RGB out.  Host pointers.  `flags` accepts RTB200_F_USE_BVH / EXACT_FP /
+ * FORCE_*. */
+int  rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* origin3, const float* dir3,
+                          uint32_t flags, int32_t* out_order, float* out_t, float* out_normal3);
+int  rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* point3, const float* light3,
+                         uint32_t flags, float* out_filter3);
+
+/* --- multi-GPU ---------------------------------------------------------------------------- */
+#define RTB200_UNIQUE_ID_BYTES 128
+/* Rank 0 obtains an id, distributes the bytes by any means (torch.distributed, a file, MPI),
+ * then every rank calls rtb200_comm_init with the same id. */
+int  rtb200_comm_unique_id(uint8_t id[RTB200_UNIQUE_ID_BYTES]);
+int  rtb200_comm_init(rtb200_ctx* ctx, int rank, int n_ranks, const uint8_t id[RTB200_UNIQUE_ID_BYTES]);
+
+/* --- helpers ------------------------------------------------------------------------------ */
+/* Page-locked host memory for the caller's scene / frame buffers (so that the copies inside
+ * rtb200_set_scene / rtb200_render are true async DMA). */
+int  rtb200_host_alloc(size_t bytes, void** out);
+void rtb200_host_free(void* p);
+/* FP32 FMA peak of the context's GPU measured with a register-resident FFMA chain on every SM
+ * (the denominator of the roofline fraction).  Returns TFLOP/s and the SM clock it saw. */
+int  rtb200_measure_fp32_peak(rtb200_ctx* ctx, double* tflops, double* sm_mhz);
+/* Device properties the benchmark reports. */
+int  rtb200_device_info(rtb200_ctx* ctx, int* sm_count, int* l2_bytes, char* name, int name_len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB200_H */
