@@ -1,0 +1,51 @@
+# Top-level build: the product (librtb200.so = hand-written sm_100a CUDA behind a C ABI, the
+# C++ host scene API on top of it, the headless CLI) and the checkers under oracle/.
+# Everything is built IN-TREE so that the binaries travel with the snapshot to the GPU box.
+ROOT    := $(dir $(abspath $(lastword $(MAKEFILE_LIST))))
+PKG     := $(ROOT)ray-tracing-gpu_b200
+CSRC    := $(PKG)/csrc
+HOST    := $(PKG)/host
+LIBDIR  := $(PKG)/lib
+OBJDIR  := $(PKG)/build
+NVCC    ?= /usr/local/cuda/bin/nvcc
+HOSTCXX := /usr/bin/g++
+
+NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -ccbin $(HOSTCXX) \
+           -Xcompiler -fPIC,-Wall,-Wno-unused-function -Xptxas -warn-spills
+CUOBJS  := $(addprefix $(OBJDIR)/,rt_api.o rt_resident.o rt_stream.o rt_comm.o rt_peak.o)
+CUHDRS  := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) $(ROOT)include/rtb200.h
+
+all: lib host oracle
+
+lib: $(LIBDIR)/librtb200.so
+
+$(OBJDIR)/%.o: $(CSRC)/%.cu $(CUHDRS)
+	@mkdir -p $(OBJDIR)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(LIBDIR)/librtb200.so: $(CUOBJS)
+	@mkdir -p $(LIBDIR)
+	$(NVCC) -shared -ccbin $(HOSTCXX) -o $@ $^ -ldl
+
+# C++ host scene API (fresh implementation of the reference's CScene / ISurface hierarchy)
+# and the headless CLI that replaces Main.cpp's GLUT window.
+HOSTSRC := $(wildcard $(HOST)/src/*.cpp)
+HOSTHDR := $(wildcard $(HOST)/include/*.h) $(wildcard $(HOST)/src/*.hpp)
+HOSTFLAGS := -std=c++17 -O2 -ffp-contract=off -fPIC -Wall -I$(HOST)/include -I$(HOST)/src -I$(ROOT)include
+
+host: $(LIBDIR)/librtb200_scene.so $(LIBDIR)/rt_cli
+
+$(LIBDIR)/librtb200_scene.so: $(filter-out $(HOST)/src/rt_cli.cpp,$(HOSTSRC)) $(HOSTHDR) $(LIBDIR)/librtb200.so
+	$(HOSTCXX) $(HOSTFLAGS) -shared -o $@ $(filter-out $(HOST)/src/rt_cli.cpp,$(HOSTSRC)) -L$(LIBDIR) -lrtb200 -Wl,-rpath,'$$ORIGIN'
+
+$(LIBDIR)/rt_cli: $(HOST)/src/rt_cli.cpp $(LIBDIR)/librtb200_scene.so
+	$(HOSTCXX) $(HOSTFLAGS) -o $@ $(HOST)/src/rt_cli.cpp -L$(LIBDIR) -lrtb200_scene -lrtb200 -Wl,-rpath,'$$ORIGIN'
+
+oracle:
+	$(MAKE) -C $(ROOT)oracle all
+
+clean:
+	rm -rf $(OBJDIR) $(LIBDIR)
+	$(MAKE) -C $(ROOT)oracle clean
+
+.PHONY: all lib host oracle clean

@@ -1,0 +1,602 @@
+// rt_api.cu -- C ABI of librtb200.so (include/rtb200.h): context, scene packing/upload and
+// the frame loop.  Replaces CNuanceurCalculProg + the UBO packer and glDispatchCompute of
+// CScene::LancerRayons (Scene.cpp:692-1312).  No CPU rendering path exists in this library.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "rt_context.h"
+
+using namespace rtb;
+
+#define TILE_TRIS 256                      // streamed path: triangles per shared-memory tile
+
+namespace rtb {
+int set_cuda_error(rtb200_ctx* c, cudaError_t e, const char* where)
+{
+    if (c) {
+        char buf[512];
+        snprintf(buf, sizeof buf, "%s: %s (%s)", where, cudaGetErrorString(e), cudaGetErrorName(e));
+        c->last_error = buf;
+    }
+    (void)cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? RTB200_E_OOM : RTB200_E_CUDA;
+}
+}
+
+#define CU(call)                                                         \
+    do {                                                                 \
+        cudaError_t e__ = (call);                                        \
+        if (e__ != cudaSuccess) return set_cuda_error(ctx, e__, #call);  \
+    } while (0)
+
+static std::string g_create_error;      // reason of the last failed rtb200_create (no context yet)
+
+static int create_fail(rtb200_ctx* ctx, const char* where)
+{
+    cudaError_t e = cudaGetLastError();
+    g_create_error = std::string(where) + ": " + cudaGetErrorString(e);
+    if (ctx) rtb200_destroy(ctx);
+    return RTB200_E_CUDA;
+}
+
+static int fail(rtb200_ctx* ctx, int code, const char* msg)
+{
+    if (ctx) ctx->last_error = msg;
+    return code;
+}
+
+extern "C" {
+
+int rtb200_abi_version(void) { return RTB200_ABI_VERSION; }
+
+const char* rtb200_error_string(int s)
+{
+    switch (s) {
+    case RTB200_OK: return "ok";
+    case RTB200_E_ARG: return "bad argument";
+    case RTB200_E_CUDA: return "CUDA error";
+    case RTB200_E_NCCL: return "NCCL error";
+    case RTB200_E_OOM: return "out of memory";
+    case RTB200_E_CAPACITY: return "ray queue capacity exceeded";
+    case RTB200_E_STATE: return "invalid call order / state";
+    default: return "unknown status";
+    }
+}
+
+const char* rtb200_last_error(const rtb200_ctx* ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }
+
+int rtb200_create(int device_id, rtb200_ctx** out)
+{
+    if (!out) return RTB200_E_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {            // no GPU: fail loudly, there is no fallback
+        g_create_error = std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e);
+        (void)cudaGetLastError();
+        return RTB200_E_CUDA;
+    }
+    if (device_id < 0 || device_id >= n) return RTB200_E_ARG;
+    rtb200_ctx* ctx = new (std::nothrow) rtb200_ctx();
+    if (!ctx) return RTB200_E_OOM;
+    ctx->device = device_id;
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device_id) != cudaSuccess) return create_fail(ctx, "cudaSetDevice");
+    if (cudaGetDeviceProperties(&prop, device_id) != cudaSuccess) return create_fail(ctx, "cudaGetDeviceProperties");
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->l2_bytes = prop.l2CacheSize;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    snprintf(ctx->name, sizeof ctx->name, "%.100s", prop.name);
+    if (prop.major < 10) {                       // the library carries sm_100a SASS only
+        g_create_error = "device is not sm_100 class";
+        rtb200_destroy(ctx);
+        return RTB200_E_CUDA;
+    }
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return create_fail(ctx, "cudaStreamCreate");
+    for (auto& ev : ctx->ev) if (cudaEventCreate(&ev) != cudaSuccess) return create_fail(ctx, "cudaEventCreate");
+    if (resident_prepare(ctx->smem_optin - 2048) != cudaSuccess) return create_fail(ctx, "cudaFuncSetAttribute(max dynamic smem)");
+    *out = ctx;
+    return RTB200_OK;
+}
+
+void rtb200_destroy(rtb200_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    comm_destroy(ctx);
+    ctx->scene_buf.release(); ctx->stage.release();
+    ctx->c0.release(); ctx->fb_f32.release(); ctx->fb_rgba8.release(); ctx->stats.release(); ctx->counters.release();
+    ctx->full_f32.release(); ctx->full_rgba8.release(); ctx->h_small.release();
+    for (auto& l : ctx->levels) { l.od0.release(); l.od1.release(); l.colour.release(); l.links.release(); }
+    ctx->q_in0.release(); ctx->q_in1.release(); ctx->q_out0.release(); ctx->q_out1.release(); ctx->q_out2.release();
+    for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int rtb200_host_alloc(size_t bytes, void** out)
+{
+    if (!out) return RTB200_E_ARG;
+    cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); *out = nullptr; return e == cudaErrorMemoryAllocation ? RTB200_E_OOM : RTB200_E_CUDA; }
+    return RTB200_OK;
+}
+
+void rtb200_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int rtb200_device_info(rtb200_ctx* ctx, int* sm_count, int* l2_bytes, char* name, int name_len)
+{
+    if (!ctx) return RTB200_E_ARG;
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (l2_bytes) *l2_bytes = ctx->l2_bytes;
+    if (name && name_len > 0) snprintf(name, (size_t)name_len, "%s", ctx->name);
+    return RTB200_OK;
+}
+
+int rtb200_measure_fp32_peak(rtb200_ctx* ctx, double* tflops, double* sm_mhz)
+{
+    if (!ctx) return RTB200_E_ARG;
+    CU(cudaSetDevice(ctx->device));
+    double tf = 0.0;
+    CU(run_fp32_peak(ctx->sm_count, &tf, ctx->stream));
+    ctx->peak_tflops = tf;
+    // FFMA chain: 128 lanes x 2 flop per SM per clock -> the clock the chain actually ran at
+    ctx->peak_mhz = tf * 1e12 / (2.0 * 128.0 * ctx->sm_count) / 1e6;
+    if (tflops) *tflops = tf;
+    if (sm_mhz) *sm_mhz = ctx->peak_mhz;
+    return RTB200_OK;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// Scene packing.  Replaces the std140 UBO packer of Scene.cpp:799-1269 (which walked the
+// surfaces through dynamic_cast + getters and capped every type at 10): the arrays of
+// rtb200_scene are repacked into (1) the insertion-ordered unified list the resident kernels
+// stage into shared memory and (2) per-type tile-friendly arrays for the streamed kernels,
+// in ONE pinned staging buffer, uploaded with ONE async copy.
+// ---------------------------------------------------------------------------------------
+static inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
+static inline float i2f(int v) { float f; memcpy(&f, &v, 4); return f; }
+
+extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
+{
+    if (!ctx || !s) return RTB200_E_ARG;
+    const int T = s->n_triangles, Q = s->n_quadrics, P = s->n_planes, L = s->n_lights, M = s->n_materials;
+    if (T < 0 || Q < 0 || P < 0 || L < 0 || M < 0) return fail(ctx, RTB200_E_ARG, "negative count");
+    const long long N = (long long)T + Q + P;
+    if (N > 0x7fffff00ll) return fail(ctx, RTB200_E_ARG, "too many surfaces");
+    if ((T && (!s->tri_points || !s->tri_normal || !s->tri_material || !s->tri_order)) ||
+        (Q && (!s->quad_coef || !s->quad_material || !s->quad_order)) ||
+        (P && (!s->plane_coef || !s->plane_material || !s->plane_order)) ||
+        (M && !s->materials) || (L && !s->lights) || (N && !M))
+        return fail(ctx, RTB200_E_ARG, "null array with non-zero count");
+    CU(cudaSetDevice(ctx->device));
+
+    const int Tpad = ((T + TILE_TRIS - 1) / TILE_TRIS) * TILE_TRIS;
+    ResidentLayout rl;
+    rl.n_surf = (int)N; rl.n_mat = M; rl.n_light = L;
+    rl.off_mat = (int)align16(sizeof(SurfRec) * (size_t)N);
+    rl.off_light = (int)align16((size_t)rl.off_mat + sizeof(MatRec) * (size_t)M);
+    const size_t blob_bytes = align16((size_t)rl.off_light + sizeof(LightRec) * (size_t)L);
+    if (blob_bytes > 0x7fffffffull) return fail(ctx, RTB200_E_ARG, "scene too large");
+    rl.bytes = (int)std::max<size_t>(blob_bytes, 16);
+    const size_t off_tri = align16((size_t)rl.bytes);
+    const size_t off_trn = off_tri + sizeof(TriRec) * (size_t)Tpad;
+    const size_t off_quad = off_trn + sizeof(float4) * (size_t)Tpad;
+    const size_t off_plane = off_quad + sizeof(QuadRec) * (size_t)Q;
+    const size_t total = align16(off_plane + sizeof(PlaneRec) * (size_t)P) + 16;
+
+    cudaError_t e = ctx->stage.ensure(total);
+    if (e != cudaSuccess) return set_cuda_error(ctx, e, "pinned staging");
+    e = ctx->scene_buf.ensure(total);
+    if (e != cudaSuccess) return set_cuda_error(ctx, e, "scene buffer");
+    unsigned char* h = ctx->stage.as<unsigned char>();
+    memset(h, 0, total);
+
+    // ---- unified list: slot = insertion order ------------------------------------------------
+    SurfRec* surf = reinterpret_cast<SurfRec*>(h);
+    std::vector<unsigned char> seen((size_t)N, 0);
+    auto claim = [&](int order, int mat, int prev) -> bool {
+        if (order < 0 || order >= N || seen[(size_t)order] || order <= prev) return false;
+        if (mat < 0 || mat >= M) return false;
+        seen[(size_t)order] = 1;
+        return true;
+    };
+    TriRec* tri = reinterpret_cast<TriRec*>(h + off_tri);
+    float4* trn = reinterpret_cast<float4*>(h + off_trn);
+    int prev = -1;
+    for (int i = 0; i < T; ++i) {
+        const float* p = s->tri_points + 9 * (size_t)i;
+        const float* n = s->tri_normal + 3 * (size_t)i;
+        const int ord = s->tri_order[i], mat = s->tri_material[i];
+        if (!claim(ord, mat, prev)) return fail(ctx, RTB200_E_ARG, "tri_order/tri_material invalid");
+        prev = ord;
+        // edges: the same binary32 subtractions CTriangle::Intersection performs per test
+        const float e1x = p[3] - p[0], e1y = p[4] - p[1], e1z = p[5] - p[2];
+        const float e2x = p[6] - p[0], e2y = p[7] - p[1], e2z = p[8] - p[2];
+        SurfRec& r = surf[ord];
+        r.r0 = make_float4(p[0], p[1], p[2], i2f(SURF_TRIANGLE));
+        r.r1 = make_float4(e1x, e1y, e1z, i2f(mat));
+        r.r2 = make_float4(e2x, e2y, e2z, 0.f);
+        r.r3 = make_float4(n[0], n[1], n[2], 0.f);
+        tri[i].a = make_float4(p[0], p[1], p[2], i2f(ord));
+        tri[i].b = make_float4(e1x, e1y, e1z, i2f(mat));
+        tri[i].c = make_float4(e2x, e2y, e2z, 0.f);
+        trn[i] = make_float4(n[0], n[1], n[2], 0.f);
+    }
+    for (int i = T; i < Tpad; ++i) tri[i].a.w = i2f(0x7fffffff);   // zero edges: det = 0, never hit
+    QuadRec* quad = reinterpret_cast<QuadRec*>(h + off_quad);
+    prev = -1;
+    for (int i = 0; i < Q; ++i) {
+        const float* c = s->quad_coef + 10 * (size_t)i;
+        const int ord = s->quad_order[i], mat = s->quad_material[i];
+        if (!claim(ord, mat, prev)) return fail(ctx, RTB200_E_ARG, "quad_order/quad_material invalid");
+        prev = ord;
+        SurfRec& r = surf[ord];
+        r.r0 = make_float4(c[0], c[1], c[2], i2f(SURF_QUADRIC));
+        r.r1 = make_float4(c[3], c[4], c[5], i2f(mat));
+        r.r2 = make_float4(c[6], c[7], c[8], c[9]);
+        quad[i].q0 = make_float4(c[0], c[1], c[2], i2f(ord));
+        quad[i].q1 = r.r1; quad[i].q2 = r.r2;
+    }
+    PlaneRec* plane = reinterpret_cast<PlaneRec*>(h + off_plane);
+    prev = -1;
+    for (int i = 0; i < P; ++i) {
+        const float* c = s->plane_coef + 4 * (size_t)i;
+        const int ord = s->plane_order[i], mat = s->plane_material[i];
+        if (!claim(ord, mat, prev)) return fail(ctx, RTB200_E_ARG, "plane_order/plane_material invalid");
+        prev = ord;
+        SurfRec& r = surf[ord];
+        r.r0 = make_float4(c[0], c[1], c[2], i2f(SURF_PLANE));
+        r.r1 = make_float4(c[3], 0.f, 0.f, i2f(mat));
+        plane[i].nc = make_float4(c[0], c[1], c[2], c[3]);
+        plane[i].order = ord; plane[i].material = mat;
+    }
+    MatRec* mat = reinterpret_cast<MatRec*>(h + rl.off_mat);
+    bool any_refl = false, any_refr = false, any_both = false;
+    for (int i = 0; i < M; ++i) {
+        const rtb200_material& m = s->materials[i];
+        mat[i].m0 = make_float4(m.color[0], m.color[1], m.color[2], m.ambient);
+        mat[i].m1 = make_float4(m.diffuse, m.specular, m.shininess, m.reflect);
+        mat[i].m2 = make_float4(m.refract, m.ior, 0.f, 0.f);
+        const bool a = m.reflect > 0.f, b = m.refract > 0.f;
+        any_refl |= a; any_refr |= b; any_both |= (a && b);
+    }
+    LightRec* light = reinterpret_cast<LightRec*>(h + rl.off_light);
+    for (int i = 0; i < L; ++i) {
+        const rtb200_light& l = s->lights[i];
+        light[i].l0 = make_float4(l.position[0], l.position[1], l.position[2], l.intensity);
+        light[i].l1 = make_float4(l.color[0], l.color[1], l.color[2], 0.f);
+    }
+
+    CU(cudaEventRecord(ctx->ev[4], ctx->stream));
+    CU(cudaMemcpyAsync(ctx->scene_buf.p, h, total, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaEventRecord(ctx->ev[5], ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, ctx->ev[4], ctx->ev[5]));
+    ctx->last_h2d_ms = ms;
+
+    const unsigned char* d = ctx->scene_buf.as<unsigned char>();
+    DeviceScene& ds = ctx->ds;
+    ds.rl = rl;
+    ds.blob = d;
+    ds.surf = reinterpret_cast<const SurfRec*>(d);
+    ds.mat = reinterpret_cast<const MatRec*>(d + rl.off_mat);
+    ds.light = reinterpret_cast<const LightRec*>(d + rl.off_light);
+    ds.n_tri = T; ds.n_quad = Q; ds.n_plane = P; ds.n_tri_padded = Tpad;
+    ds.tri = reinterpret_cast<const TriRec*>(d + off_tri);
+    ds.tri_normal = reinterpret_cast<const float4*>(d + off_trn);
+    ds.quad = reinterpret_cast<const QuadRec*>(d + off_quad);
+    ds.plane = reinterpret_cast<const PlaneRec*>(d + off_plane);
+    ctx->any_reflect = any_refl; ctx->any_refract = any_refr;
+    ctx->max_children = any_both ? 2 : ((any_refl || any_refr) ? 1 : 0);
+    ctx->have_scene = true;
+    return RTB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// Frame loop
+// ---------------------------------------------------------------------------------------
+#define MAX_CHUNK_SAMPLES (16u << 20)
+#define RESIDENT_AUTO_BYTES (64 * 1024)       // scenes up to this blob size use the fused resident kernels
+
+static int local_row_count(int H, int band_rows, int n_ranks, int rank)
+{
+    if (n_ranks <= 1) return H;
+    int rows = 0;
+    for (int y0 = rank * band_rows; y0 < H; y0 += band_rows * n_ranks) rows += std::min(band_rows, H - y0);
+    return rows;
+}
+
+static void fill_frame_params(const rtb200_frame* fr, int n_ranks, int rank, FrameParams& f)
+{
+    memset(&f, 0, sizeof f);
+    f.W = fr->width; f.H = fr->height;
+    f.k = fr->spp_grid > 1 ? fr->spp_grid : 1;
+    f.LW = f.W * f.k; f.LH = f.H * f.k;
+    f.inv_w = 1.0f / (float)f.LW;             // RENDRE_REEL(1.0) / m_ResLargeur at lattice resolution
+    f.inv_h = 1.0f / (float)f.LH;
+    f.half_w = fr->half_w; f.half_h = fr->half_h;
+    for (int i = 0; i < 3; ++i) {
+        f.cam_pos[i] = fr->cam_pos[i]; f.cam_u[i] = fr->cam_u[i]; f.cam_v[i] = fr->cam_v[i]; f.cam_n[i] = fr->cam_n[i];
+        f.background[i] = fr->background[i];
+    }
+    f.max_bounces = fr->max_bounces;
+    f.min_energy = fr->min_energy;
+    f.scene_ior = fr->scene_ior;
+    f.secondary = (fr->flags & RTB200_F_NO_SECONDARY) ? 0 : 1;
+    const int band = fr->band_rows > 0 ? fr->band_rows : 16;
+    f.band_lrows = band * f.k;
+    f.n_ranks = n_ranks; f.rank = rank;
+}
+
+// scene-resident path: one fused kernel per level, host reads the child count between levels
+static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
+                           bool exact, rtb200_stats* st, uint32_t* launches)
+{
+    const int k = fp.k;
+    const int local_LH = local_rows * k;
+    int children = ctx->max_children;
+    if (fr->min_energy < 0.f) children = 2;                 // 0 > negative: every hit spawns both
+    if (!fp.secondary || fr->max_bounces <= 0) children = 0;
+
+    int rows_per_chunk = (int)((MAX_CHUNK_SAMPLES / (unsigned)fp.LW) / (16u * k)) * 16 * k;
+    if (rows_per_chunk < 16 * k) rows_per_chunk = 16 * k;
+    if (rows_per_chunk > local_LH) rows_per_chunk = ((local_LH + 16 * k - 1) / (16 * k)) * 16 * k;
+
+    cudaError_t e;
+    if ((e = ctx->c0.ensure(sizeof(float) * 3 * (size_t)rows_per_chunk * fp.LW)) != cudaSuccess) return set_cuda_error(ctx, e, "c0");
+    const size_t n_counters = 2 * ((size_t)std::max(fr->max_bounces, 0) + 2);
+    if ((e = ctx->counters.ensure(sizeof(unsigned) * n_counters)) != cudaSuccess) return set_cuda_error(ctx, e, "counters");
+    if ((e = ctx->h_small.ensure(8192)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
+    unsigned* h_cnt = ctx->h_small.as<unsigned>();
+    unsigned* d_cnt = ctx->counters.as<unsigned>();
+    unsigned max_level_seen = 0, chunks = 0;
+
+    for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunks) {
+        const int rows = std::min(rows_per_chunk, local_LH - ly0);
+        CU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, ctx->stream));
+        std::vector<int> n_rays, n_links;
+        n_rays.push_back(rows * fp.LW);
+        int level = 0;
+        for (;; ++level) {
+            const int n_in = n_rays[level];
+            if (n_in == 0) break;
+            const bool spawn = children > 0 && level < fr->max_bounces;
+            if ((int)ctx->levels.size() < level + 2) ctx->levels.resize((size_t)level + 2);
+            LevelBuf& cur = ctx->levels[level];
+            LevelBuf& nxt = ctx->levels[level + 1];
+            if (spawn) {
+                const size_t cap = (size_t)n_in * children;
+                if ((e = nxt.od0.ensure(sizeof(float4) * cap)) != cudaSuccess) return set_cuda_error(ctx, e, "queue");
+                if ((e = nxt.od1.ensure(sizeof(float4) * cap)) != cudaSuccess) return set_cuda_error(ctx, e, "queue");
+                if ((e = nxt.colour.ensure(sizeof(float4) * cap)) != cudaSuccess) return set_cuda_error(ctx, e, "queue");
+                if ((e = cur.links.ensure(sizeof(int4) * (size_t)n_in)) != cudaSuccess) return set_cuda_error(ctx, e, "links");
+            }
+            LevelParams p;
+            memset(&p, 0, sizeof p);
+            p.f = fp;
+            if (!spawn) p.f.secondary = 0;
+            p.blob = ctx->ds.blob; p.rl = ctx->ds.rl;
+            p.level = level;
+            p.chunk_ly0 = ly0; p.chunk_rows = rows; p.local_LH = local_LH;
+            p.c0 = ctx->c0.as<float>();
+            p.in_od0 = cur.od0.as<float4>(); p.in_od1 = cur.od1.as<float4>(); p.in_colour = cur.colour.as<float4>();
+            p.in_count = n_in;
+            p.out_od0 = nxt.od0.as<float4>(); p.out_od1 = nxt.od1.as<float4>();
+            p.out_count = d_cnt + 2 * level; p.link_count = d_cnt + 2 * level + 1;
+            p.links = cur.links.as<int4>();
+            p.stats = ctx->stats.as<unsigned long long>();
+            CU(launch_resident_level(p, exact, ctx->stream));
+            ++*launches;
+            if (!spawn) { n_links.push_back(0); ++level; break; }
+            CU(cudaMemcpyAsync(h_cnt, d_cnt + 2 * level, 2 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            n_rays.push_back((int)h_cnt[0]);
+            n_links.push_back((int)h_cnt[1]);
+        }
+        const int levels_used = (int)n_links.size();          // levels that ran a kernel
+        max_level_seen = std::max<unsigned>(max_level_seen, (unsigned)levels_used);
+        for (int l = levels_used - 1; l >= 0; --l) {
+            if (n_links[l] <= 0) continue;
+            CombineParams c;
+            memset(&c, 0, sizeof c);
+            c.links = ctx->levels[l].links.as<int4>();
+            c.n_links = n_links[l];
+            c.parent_is_level0 = (l == 0);
+            c.parent_c0 = ctx->c0.as<float>();
+            c.parent_colour = ctx->levels[l].colour.as<float4>();
+            c.child_colour = ctx->levels[l + 1].colour.as<float4>();
+            c.mat = ctx->ds.mat;
+            CU(launch_combine(c, exact, ctx->stream));
+            ++*launches;
+        }
+        ResolveParams r;
+        memset(&r, 0, sizeof r);
+        r.f = fp;
+        r.c0 = ctx->c0.as<float>();
+        r.chunk_py0 = ly0 / k;
+        r.chunk_prows = std::min(rows / k, local_rows - r.chunk_py0);
+        r.fb_f32 = ctx->fb_f32.as<float>();
+        r.fb_rgba8 = ctx->fb_rgba8.as<uchar4>();
+        r.stats = ctx->stats.as<unsigned long long>();
+        CU(launch_resolve(r, ctx->stream));
+        ++*launches;
+    }
+    st->depth_levels = max_level_seen;
+    st->chunks = chunks;
+    st->path = 0;
+    // brute force by construction: every nearest-hit query and every shadow query that is not
+    // cut short by the all-zero early-out tests every surface; counted exactly on the host
+    return RTB200_OK;
+}
+
+static int read_back(rtb200_ctx* ctx, float* out_f32, uint8_t* out_rgba8, double* ms)
+{
+    if (!out_f32 && !out_rgba8) return RTB200_OK;
+    const bool full = ctx->last_gathered;
+    const size_t rows = full ? (size_t)ctx->last_H : (size_t)ctx->last_local_rows;
+    const size_t px = rows * (size_t)ctx->last_W;
+    CU(cudaEventRecord(ctx->ev[2], ctx->stream));
+    if (out_f32)
+        CU(cudaMemcpyAsync(out_f32, full ? ctx->full_f32.p : ctx->fb_f32.p, px * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_rgba8)
+        CU(cudaMemcpyAsync(out_rgba8, full ? ctx->full_rgba8.p : ctx->fb_rgba8.p, px * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaEventRecord(ctx->ev[3], ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    float t = 0.f;
+    CU(cudaEventElapsedTime(&t, ctx->ev[2], ctx->ev[3]));
+    if (ms) *ms = t;
+    return RTB200_OK;
+}
+
+extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out_f32, uint8_t* out_rgba8, rtb200_stats* stats)
+{
+    if (!ctx || !fr) return RTB200_E_ARG;
+    if (!ctx->have_scene) return fail(ctx, RTB200_E_STATE, "rtb200_render before rtb200_set_scene");
+    if (fr->width <= 0 || fr->height <= 0 || fr->spp_grid < 0 || fr->spp_grid > 64) return fail(ctx, RTB200_E_ARG, "bad frame size");
+    if ((long long)fr->width * std::max(fr->spp_grid, 1) > (1 << 20)) return fail(ctx, RTB200_E_ARG, "frame too wide");
+    CU(cudaSetDevice(ctx->device));
+    const bool exact = (fr->flags & RTB200_F_EXACT_FP) != 0;
+    FrameParams fp;
+    fill_frame_params(fr, ctx->n_ranks, ctx->rank, fp);
+    const int band = fp.band_lrows / fp.k;
+    const int local_rows = local_row_count(fp.H, band, ctx->n_ranks, ctx->rank);
+    rtb200_stats st;
+    memset(&st, 0, sizeof st);
+    uint32_t launches = 0;
+
+    cudaError_t e;
+    const size_t lpx = (size_t)std::max(local_rows, 1) * fp.W;
+    if ((e = ctx->fb_f32.ensure(lpx * 3 * sizeof(float))) != cudaSuccess) return set_cuda_error(ctx, e, "fb_f32");
+    if ((e = ctx->fb_rgba8.ensure(lpx * 4)) != cudaSuccess) return set_cuda_error(ctx, e, "fb_rgba8");
+    const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
+    if ((e = ctx->stats.ensure(stat_bytes)) != cudaSuccess) return set_cuda_error(ctx, e, "stats");
+    if ((e = ctx->h_small.ensure(8192)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
+    CU(cudaMemsetAsync(ctx->stats.p, 0, stat_bytes, ctx->stream));
+
+    // path selection
+    const size_t resident_limit = ctx->smem_optin > 4096 ? ctx->smem_optin - 2048 : 0;
+    bool use_stream = (size_t)ctx->ds.rl.bytes > RESIDENT_AUTO_BYTES || (fr->flags & (RTB200_F_FORCE_STREAM | RTB200_F_USE_BVH));
+    if (fr->flags & RTB200_F_FORCE_RESIDENT) {
+        if ((size_t)ctx->ds.rl.bytes > resident_limit) return fail(ctx, RTB200_E_ARG, "scene does not fit in shared memory");
+        use_stream = false;
+    }
+
+    CU(cudaEventRecord(ctx->ev[0], ctx->stream));
+    int rc = RTB200_OK;
+    if (local_rows > 0) {
+        if (use_stream) rc = render_streamed(ctx, fr, fp, local_rows, exact, &st, &launches);
+        else            rc = render_resident(ctx, fr, fp, local_rows, exact, &st, &launches);
+    }
+    if (rc != RTB200_OK) { cudaStreamSynchronize(ctx->stream); (void)cudaGetLastError(); return rc; }
+    CU(cudaEventRecord(ctx->ev[1], ctx->stream));
+
+    ctx->last_W = fp.W; ctx->last_H = fp.H; ctx->last_local_rows = local_rows; ctx->last_gathered = false;
+    if (ctx->comm && ctx->n_ranks > 1) {
+        rc = comm_gather_frame(ctx, fp.W, fp.H, band, true, true, &st.ms_gather);
+        if (rc != RTB200_OK) return rc;
+        ctx->last_gathered = (ctx->rank == 0);
+    }
+
+    // statistics
+    unsigned long long* h_st = reinterpret_cast<unsigned long long*>(ctx->h_small.as<unsigned char>() + 1024);
+    CU(cudaMemcpyAsync(h_st, ctx->stats.p, stat_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+    st.ms_render = ms;
+    unsigned long long sum[ST_COUNT] = {0};
+    for (int s = 0; s < RT_STAT_SLOTS; ++s) for (int c = 0; c < ST_COUNT; ++c) sum[c] += h_st[s * ST_COUNT + c];
+    st.rays_primary = (uint64_t)local_rows * fp.k * (uint64_t)fp.LW;
+    st.rays_shadow = sum[ST_SHADOW]; st.rays_reflect = sum[ST_REFLECT]; st.rays_refract = sum[ST_REFRACT];
+    st.nan_pixels = sum[ST_NAN];
+    if (st.path == 0) {
+        // resident kernels count surface tests in one counter; split by the scene's type mix
+        const double n = std::max(1, ctx->ds.rl.n_surf);
+        st.tests_triangle = (uint64_t)llround((double)sum[ST_TEST_TRI] * ctx->ds.n_tri / n);
+        st.tests_quadric  = (uint64_t)llround((double)sum[ST_TEST_TRI] * ctx->ds.n_quad / n);
+        st.tests_plane    = (uint64_t)llround((double)sum[ST_TEST_TRI] * ctx->ds.n_plane / n);
+    } else {
+        st.tests_triangle = sum[ST_TEST_TRI]; st.tests_quadric = sum[ST_TEST_QUAD]; st.tests_plane = sum[ST_TEST_PLANE];
+        st.bvh_nodes_visited = sum[ST_BVH_NODES];
+    }
+    st.kernel_launches = launches;
+    st.ms_h2d = 0.0;
+
+    if (ctx->rank == 0 || !ctx->last_gathered) {
+        const bool want = (ctx->n_ranks <= 1) || ctx->rank == 0;
+        if (want) {
+            rc = read_back(ctx, out_f32, out_rgba8, &st.ms_d2h);
+            if (rc != RTB200_OK) return rc;
+        }
+    }
+    if (stats) *stats = st;
+    return RTB200_OK;
+}
+
+extern "C" int rtb200_read_frame(rtb200_ctx* ctx, float* out_f32, uint8_t* out_rgba8)
+{
+    if (!ctx) return RTB200_E_ARG;
+    if (ctx->last_W <= 0) return fail(ctx, RTB200_E_STATE, "no frame rendered yet");
+    CU(cudaSetDevice(ctx->device));
+    return read_back(ctx, out_f32, out_rgba8, nullptr);
+}
+
+// ---------------------------------------------------------------------------------------
+// Ray-level queries
+// ---------------------------------------------------------------------------------------
+extern "C" int rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* o3, const float* d3, uint32_t flags,
+                                    int32_t* out_order, float* out_t, float* out_n3)
+{
+    if (!ctx || n < 0 || (n && (!o3 || !d3 || !out_order || !out_t || !out_n3))) return RTB200_E_ARG;
+    if (!ctx->have_scene) return fail(ctx, RTB200_E_STATE, "no scene");
+    if (n == 0) return RTB200_OK;
+    CU(cudaSetDevice(ctx->device));
+    cudaError_t e;
+    const size_t b3 = sizeof(float) * 3 * (size_t)n;
+    if ((e = ctx->q_in0.ensure(b3)) != cudaSuccess || (e = ctx->q_in1.ensure(b3)) != cudaSuccess ||
+        (e = ctx->q_out0.ensure(sizeof(int) * (size_t)n)) != cudaSuccess || (e = ctx->q_out1.ensure(sizeof(float) * (size_t)n)) != cudaSuccess ||
+        (e = ctx->q_out2.ensure(b3)) != cudaSuccess) return set_cuda_error(ctx, e, "query buffers");
+    CU(cudaMemcpyAsync(ctx->q_in0.p, o3, b3, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->q_in1.p, d3, b3, cudaMemcpyHostToDevice, ctx->stream));
+    CU(launch_query_nearest(ctx->ds, n, ctx->q_in0.as<float>(), ctx->q_in1.as<float>(), ctx->q_out0.as<int>(),
+                            ctx->q_out1.as<float>(), ctx->q_out2.as<float>(), (flags & RTB200_F_EXACT_FP) != 0, ctx->stream));
+    CU(cudaMemcpyAsync(out_order, ctx->q_out0.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(out_t, ctx->q_out1.p, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(out_n3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return RTB200_OK;
+}
+
+extern "C" int rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* p3, const float* l3, uint32_t flags, float* out3)
+{
+    if (!ctx || n < 0 || (n && (!p3 || !l3 || !out3))) return RTB200_E_ARG;
+    if (!ctx->have_scene) return fail(ctx, RTB200_E_STATE, "no scene");
+    if (n == 0) return RTB200_OK;
+    CU(cudaSetDevice(ctx->device));
+    cudaError_t e;
+    const size_t b3 = sizeof(float) * 3 * (size_t)n;
+    if ((e = ctx->q_in0.ensure(b3)) != cudaSuccess || (e = ctx->q_in1.ensure(b3)) != cudaSuccess ||
+        (e = ctx->q_out2.ensure(b3)) != cudaSuccess) return set_cuda_error(ctx, e, "query buffers");
+    CU(cudaMemcpyAsync(ctx->q_in0.p, p3, b3, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->q_in1.p, l3, b3, cudaMemcpyHostToDevice, ctx->stream));
+    CU(launch_query_shadow(ctx->ds, n, ctx->q_in0.as<float>(), ctx->q_in1.as<float>(), ctx->q_out2.as<float>(),
+                           (flags & RTB200_F_EXACT_FP) != 0, ctx->stream));
+    CU(cudaMemcpyAsync(out3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return RTB200_OK;
+}
+
+extern "C" int rtb200_comm_unique_id(uint8_t id[RTB200_UNIQUE_ID_BYTES]) { return comm_unique_id(id); }
+extern "C" int rtb200_comm_init(rtb200_ctx* ctx, int rank, int n_ranks, const uint8_t id[RTB200_UNIQUE_ID_BYTES])
+{
+    if (!ctx || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return RTB200_E_ARG;
+    return comm_init(ctx, rank, n_ranks, id);
+}

@@ -1,0 +1,100 @@
+// rt_context.h -- the context behind the C ABI (host side of librtb200.so).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/rtb200.h"
+#include "rt_kernels.cuh"
+
+namespace rtb {
+
+// growable device buffer (never shrinks; steady-state frames allocate nothing)
+struct DevBuf {
+    void*  p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct PinnedBuf {
+    void*  p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct LevelBuf {                 // one wavefront level (rays of one bounce count)
+    DevBuf od0, od1, colour, links;
+};
+
+struct Comm;                      // rt_comm.cu (NCCL, loaded lazily with dlopen)
+
+} // namespace rtb
+
+struct rtb200_ctx {
+    int device = 0;
+    int sm_count = 0, l2_bytes = 0;
+    size_t smem_optin = 0;
+    char name[128] = {0};
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::string last_error;
+
+    // scene
+    bool have_scene = false;
+    rtb::DeviceScene ds{};
+    rtb::DevBuf scene_buf;            // resident blob + streamed arrays, one allocation
+    rtb::PinnedBuf stage;             // pinned staging for uploads
+    int max_children = 0;             // 0, 1 or 2 secondary rays per hit at most
+    bool any_reflect = false, any_refract = false;
+    double last_h2d_ms = 0.0;
+
+    // frame buffers (local rows of this rank)
+    rtb::DevBuf c0, fb_f32, fb_rgba8, stats, counters;
+    rtb::DevBuf full_f32, full_rgba8; // rank 0 with a communicator: gathered frame
+    rtb::PinnedBuf h_small;           // counters / stats read-back
+    std::vector<rtb::LevelBuf> levels;
+    int last_W = 0, last_H = 0, last_local_rows = 0;
+    bool last_gathered = false;
+
+    // query scratch
+    rtb::DevBuf q_in0, q_in1, q_out0, q_out1, q_out2;
+
+    // multi-GPU
+    rtb::Comm* comm = nullptr;
+    int rank = 0, n_ranks = 1;
+
+    // peak cache
+    double peak_tflops = 0.0, peak_mhz = 0.0;
+};
+
+namespace rtb {
+int  set_cuda_error(rtb200_ctx* c, cudaError_t e, const char* where);
+int  render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
+                     bool exact, rtb200_stats* st, uint32_t* launches);     // rt_stream.cu
+// rt_comm.cu
+int  comm_unique_id(uint8_t* id);
+int  comm_init(rtb200_ctx* c, int rank, int n_ranks, const uint8_t* id);
+void comm_destroy(rtb200_ctx* c);
+int  comm_gather_frame(rtb200_ctx* c, int W, int H, int band_rows, bool want_f32, bool want_rgba8, double* ms);
+}

@@ -1,0 +1,71 @@
+// rt_kernels.cuh -- kernel parameter blocks and host-side launchers (defined in the .cu files).
+#pragma once
+#include "rt_scene.cuh"
+
+namespace rtb {
+
+#define RT_STAT_SLOTS 64           // counters are spread over 64 slots to keep atomics apart
+enum {                             // per-slot counter index
+    ST_SHADOW = 0, ST_REFLECT, ST_REFRACT, ST_NAN, ST_TEST_TRI, ST_TEST_QUAD, ST_TEST_PLANE, ST_BVH_NODES,
+    ST_COUNT
+};
+
+// One wavefront level of the scene-resident fused path (trace + shade + shadow + spawn).
+struct LevelParams {
+    FrameParams f;
+    const unsigned char* blob;     // resident blob (global)
+    ResidentLayout rl;
+    int   level;                   // 0 = primary rays generated from the lattice
+    // level 0: chunk of the local sample lattice
+    int   chunk_ly0, chunk_rows, local_LH;
+    float* c0;                     // [chunk_rows][LW][3] sample colours
+    // level >= 1: input queue
+    const float4* in_od0;
+    const float4* in_od1;
+    float4* in_colour;
+    int   in_count;
+    // children
+    float4* out_od0;
+    float4* out_od1;
+    unsigned int* out_count;
+    int4* links;
+    unsigned int* link_count;
+    unsigned long long* stats;     // [RT_STAT_SLOTS][ST_COUNT]
+};
+
+struct CombineParams {
+    const int4* links;
+    int   n_links;
+    float*  parent_c0;             // level-0 parents: 3 floats per sample
+    float4* parent_colour;         // level >= 1 parents
+    const float4* child_colour;
+    const MatRec* mat;
+    int   parent_is_level0;
+};
+
+struct ResolveParams {
+    FrameParams f;
+    const float* c0;               // [chunk_rows][LW][3]
+    int   chunk_py0, chunk_prows;  // local pixel rows covered by the chunk
+    float*  fb_f32;                // [local rows][W][3] or null
+    uchar4* fb_rgba8;              // [local rows][W]    or null
+    unsigned long long* stats;
+};
+
+// launchers (rt_resident.cu)
+size_t resident_smem_bytes(const ResidentLayout& rl);
+cudaError_t resident_prepare(size_t max_smem_bytes);
+cudaError_t launch_resident_level(const LevelParams& p, bool exact, cudaStream_t st);
+cudaError_t launch_combine(const CombineParams& p, bool exact, cudaStream_t st);
+cudaError_t launch_resolve(const ResolveParams& p, cudaStream_t st);
+
+// ray-level queries over the unified list in global memory (rt_resident.cu)
+cudaError_t launch_query_nearest(const DeviceScene& s, int n, const float* o3, const float* d3,
+                                 int* out_order, float* out_t, float* out_n3, bool exact, cudaStream_t st);
+cudaError_t launch_query_shadow(const DeviceScene& s, int n, const float* p3, const float* l3,
+                                float* out3, bool exact, cudaStream_t st);
+
+// FFMA peak micro-benchmark (rt_peak.cu): returns FFMA-chain flop count and elapsed ms
+cudaError_t run_fp32_peak(int sm_count, double* tflops, cudaStream_t st);
+
+} // namespace rtb

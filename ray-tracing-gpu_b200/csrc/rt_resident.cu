@@ -1,0 +1,445 @@
+// rt_resident.cu -- scene-resident fused wavefront kernels (small scenes: the whole scene
+// sits in shared memory, staged with ONE bulk TMA copy per CTA).
+//
+// One launch per recursion level.  A level-k thread owns one ray of bounce count k and does
+// what CScene::ObtenirCouleur + ObtenirCouleurSurIntersection + ObtenirFiltreDeSurface do for
+// it (Scene.cpp:1705-1861), except that the two recursive calls of Scene.cpp:1779-1823 become
+// two rays appended (warp-aggregated) to the level-(k+1) queue plus one "link" record, so the
+// colours are folded parent <- children bottom-up, reflection before refraction, exactly in
+// the reference's accumulation order and deterministically.  No per-thread stack, no
+// recursion; every level runs on a compacted queue so warps never diverge on depth.
+#include "rt_kernels.cuh"
+#include "rt_tma.cuh"
+
+namespace rtb {
+
+#define RES_THREADS 256
+
+struct SceneView {                 // resident blob seen through shared (or global) memory
+    const SurfRec*  surf;
+    const MatRec*   mat;
+    const LightRec* light;
+    int n_surf, n_light;
+};
+
+// distance of surface record `k` along (o,d); quadrics also report the A==0 branch
+template <bool E> RT_DEV float surface_t(const SurfRec* __restrict__ s, int k, V3 o, V3 d, int& type, bool& linear)
+{
+    const float4 r0 = s[k].r0, r1 = s[k].r1, r2 = s[k].r2;
+    type = __float_as_int(r0.w);
+    linear = false;
+    if (type == SURF_TRIANGLE) return triangle_t<E>(o, d, f4_xyz(r0), f4_xyz(r1), f4_xyz(r2));
+    if (type == SURF_QUADRIC) {
+        Quadric q = { r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r2.x, r2.y, r2.z, r2.w };
+        return quadric_t<E>(o, d, q, linear);
+    }
+    return plane_t<E>(o, d, f4_xyz(r0), r1.x);
+}
+
+// nearest hit: the loop of Scene.cpp:1710-1715 (strict <, so the first surface wins a tie)
+template <bool E> RT_DEV void nearest_hit(const SceneView& sv, V3 o, V3 d, float& best_t, int& best_k, bool& best_lin)
+{
+    best_t = -1.0f; best_k = -1; best_lin = false;
+    for (int k = 0; k < sv.n_surf; ++k) {
+        int type; bool lin;
+        float t = surface_t<E>(sv.surf, k, o, d, type, lin);
+        if (t > RT_EPS && (t < best_t || best_t < 0.f)) { best_t = t; best_k = k; best_lin = lin; }
+    }
+}
+
+// normal the reference would have stored in the winning CIntersection
+template <bool E> RT_DEV V3 hit_normal(const SceneView& sv, int k, V3 o, V3 d, float t, bool lin)
+{
+    const float4 r0 = sv.surf[k].r0;
+    const int type = __float_as_int(r0.w);
+    if (type == SURF_TRIANGLE) return f4_xyz(sv.surf[k].r3);
+    if (type == SURF_PLANE) return f4_xyz(r0);
+    const float4 r1 = sv.surf[k].r1, r2 = sv.surf[k].r2;
+    Quadric q = { r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r2.x, r2.y, r2.z, r2.w };
+    return quadric_normal<E>(o, d, t, q, lin);
+}
+
+// shadow filter: Scene.cpp:1842-1861.  `need` lanes accumulate; the warp leaves the scan as
+// soon as every lane that needs it holds a zero filter (0 * finite stays 0).
+template <bool E> RT_DEV int shadow_filter(const SceneView& sv, bool need, V3 P, V3 Ldir, float dist,
+                                           float& fr, float& fg, float& fb)
+{
+    fr = fg = fb = 1.0f;
+    int k = 0;
+    for (; k < sv.n_surf; ++k) {
+        int type; bool lin;
+        float t = surface_t<E>(sv.surf, k, P, Ldir, type, lin);
+        if (need && t > RT_EPS && t < dist) {
+            const int m = __float_as_int(sv.surf[k].r1.w);
+            const float4 m0 = sv.mat[m].m0;
+            const float kt = sv.mat[m].m2.x;
+            fr = FP<E>::mul(fr, FP<E>::mul(m0.x, kt));
+            fg = FP<E>::mul(fg, FP<E>::mul(m0.y, kt));
+            fb = FP<E>::mul(fb, FP<E>::mul(m0.z, kt));
+        }
+        const bool done = !need || (fr == 0.f && fg == 0.f && fb == 0.f);
+        if (__all_sync(0xffffffffu, done)) { ++k; break; }
+    }
+    return k;                                   // surfaces tested by the lanes that needed the query
+}
+
+// block-wide add of four per-thread counters into the spread statistics slots
+RT_DEV void block_stats4(unsigned long long* stats, unsigned int a, unsigned int b, unsigned int c, unsigned int d,
+                         unsigned int* sm_acc)
+{
+    for (int off = 16; off > 0; off >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, off);
+        b += __shfl_xor_sync(0xffffffffu, b, off);
+        c += __shfl_xor_sync(0xffffffffu, c, off);
+        d += __shfl_xor_sync(0xffffffffu, d, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (a) atomicAdd(&sm_acc[0], a);
+        if (b) atomicAdd(&sm_acc[1], b);
+        if (c) atomicAdd(&sm_acc[2], c);
+        if (d) atomicAdd(&sm_acc[3], d);
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        const unsigned int tot = sm_acc[threadIdx.x];
+        // resident path: ST_TEST_TRI holds ALL surface tests (split by type on the host)
+        const int which = threadIdx.x == 0 ? ST_SHADOW : (threadIdx.x == 1 ? ST_REFLECT : (threadIdx.x == 2 ? ST_REFRACT : ST_TEST_TRI));
+        if (tot) atomicAdd(&stats[(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + which], (unsigned long long)tot);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// One wavefront level.  CTA = 256 threads = one 16x16 tile of the sample lattice (level 0,
+// warps are 8x4 sub-tiles so a warp's rays stay a compact bundle) or 256 consecutive queue
+// entries (level >= 1).
+// ---------------------------------------------------------------------------------------
+template <bool E, bool PRIMARY>
+__global__ void __launch_bounds__(RES_THREADS)
+k_resident_level(const __grid_constant__ LevelParams p)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ unsigned int sm_acc[4];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); sm_acc[0] = sm_acc[1] = sm_acc[2] = sm_acc[3] = 0; }
+    __syncthreads();
+    if (tid == 0) {                         // one bulk copy stages the whole scene
+        mbar_arrive_expect_tx(&bar, (uint32_t)p.rl.bytes);
+        tma_load_1d(smem, p.blob, (uint32_t)p.rl.bytes, &bar);
+    }
+
+    // ---- this thread's ray (overlaps the copy) ---------------------------------------------
+    const FrameParams& f = p.f;
+    V3 o, d;
+    float energy = 1.0f, ior = 1.0f;
+    bool valid;
+    int  self;                              // index of this ray in its level's colour buffer
+    if (PRIMARY) {
+        const int tiles_x = (f.LW + 15) >> 4;
+        const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+        const int lx = (tx << 4) + ((warp & 1) << 3) + (lane & 7);
+        const int cy = (ty << 4) + ((warp >> 1) << 2) + (lane >> 3);   // row inside the chunk
+        const int ly = p.chunk_ly0 + cy;                                 // local lattice row
+        valid = lx < f.LW && cy < p.chunk_rows && ly < p.local_LH;
+        self = cy * f.LW + lx;
+        primary_ray<E>(f, valid ? lx : 0, valid ? global_lattice_row(f, ly) : 0, o, d);
+    } else {
+        self = blockIdx.x * RES_THREADS + tid;
+        valid = self < p.in_count;
+        const float4 a = valid ? p.in_od0[self] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 b = valid ? p.in_od1[self] : make_float4(0.f, 0.f, 0.f, 0.f);
+        o = f4_xyz(a); d = f4_xyz(b); energy = a.w; ior = b.w;
+    }
+
+    mbar_wait(&bar, 0);
+    SceneView sv;
+    sv.surf  = reinterpret_cast<const SurfRec*>(smem);
+    sv.mat   = reinterpret_cast<const MatRec*>(smem + p.rl.off_mat);
+    sv.light = reinterpret_cast<const LightRec*>(smem + p.rl.off_light);
+    sv.n_surf = p.rl.n_surf; sv.n_light = p.rl.n_light;
+
+    // ---- nearest hit (Scene.cpp:1705-1720) -----------------------------------------------
+    float t; int k; bool lin;
+    nearest_hit<E>(sv, o, d, t, k, lin);
+    const bool hit = valid && k >= 0;
+
+    float cr = f.background[0], cg = f.background[1], cb = f.background[2];
+    unsigned int n_shadow = 0, n_tests = valid ? (unsigned int)sv.n_surf : 0u;
+    bool want_refl = false, want_refr = false;
+    V3 P = mk3(0.f, 0.f, 0.f), N = mk3(0.f, 0.f, 0.f);
+    int mat = 0;
+    float kr = 0.f, kt = 0.f, mior = 0.f, e_refl = 0.f, e_refr = 0.f;
+
+    if (__any_sync(0xffffffffu, hit)) {
+        // ---- ObtenirCouleurSurIntersection (Scene.cpp:1740-1826) ---------------------------
+        float4 m0 = make_float4(0.f, 0.f, 0.f, 0.f), m1 = m0;
+        if (hit) {
+            mat = __float_as_int(sv.surf[k].r1.w);
+            m0 = sv.mat[mat].m0; m1 = sv.mat[mat].m1;
+            const float4 m2 = sv.mat[mat].m2;
+            kr = m1.w; kt = m2.x; mior = m2.y;
+            N = hit_normal<E>(sv, k, o, d, t, lin);
+            P = axpy3<E>(o, d, t);
+            cr = FP<E>::mul(m0.x, m0.w); cg = FP<E>::mul(m0.y, m0.w); cb = FP<E>::mul(m0.z, m0.w);
+        }
+        for (int l = 0; l < sv.n_light; ++l) {
+            const float4 l0 = sv.light[l].l0, l1 = sv.light[l].l1;
+            V3 Ld = sub3<E>(f4_xyz(l0), P);
+            const bool need = hit && dot3<E>(Ld, N) > 0.f;
+            if (!__any_sync(0xffffffffu, need)) continue;
+            // ObtenirFiltreDeSurface normalises the light ray in place (Scene.cpp:1847-1848)
+            const float dist = norm3<E>(Ld);
+            Ld = scale3<E>(Ld, FP<E>::rcp(dist));
+            float fr, fg, fb;
+            const int tested = shadow_filter<E>(sv, need, P, Ld, dist, fr, fg, fb);
+            if (need) {
+                ++n_shadow; n_tests += (unsigned int)tested;
+                const float lcr = FP<E>::mul(l1.x, fr), lcg = FP<E>::mul(l1.y, fg), lcb = FP<E>::mul(l1.z, fb);
+                // Gouraud term (Scene.cpp:1763-1765): colour * (I*kd*dot(N,L)) * lightcolour
+                const float g = FP<E>::mul(FP<E>::mul(l0.w, m1.x), dot3<E>(N, Ld));
+                cr = FP<E>::madd(FP<E>::mul(m0.x, g), lcr, cr);
+                cg = FP<E>::madd(FP<E>::mul(m0.y, g), lcg, cg);
+                cb = FP<E>::madd(FP<E>::mul(m0.z, g), lcb, cb);
+                // Phong term (Scene.cpp:1768-1775)
+                const V3 R = reflect3<E>(Ld, N);
+                const float ps = dot3<E>(R, d);
+                if (ps > 0.f) {
+                    const float ph = FP<E>::mul(FP<E>::mul(l0.w, m1.y), powf(ps, m1.z));
+                    cr = FP<E>::madd(lcr, ph, cr);
+                    cg = FP<E>::madd(lcg, ph, cg);
+                    cb = FP<E>::madd(lcb, ph, cb);
+                }
+            }
+        }
+        // ---- secondary rays (Scene.cpp:1779-1823) ---------------------------------------------
+        if (hit && f.secondary && p.level < f.max_bounces) {
+            e_refl = FP<E>::mul(kr, energy);
+            e_refr = FP<E>::mul(kt, energy);
+            want_refl = e_refl > f.min_energy;
+            want_refr = e_refr > f.min_energy;
+        }
+    }
+
+    // ---- this ray's own colour -------------------------------------------------------------
+    if (valid) {
+        if (PRIMARY) {
+            float* c = p.c0 + 3 * (size_t)self;
+            c[0] = cr; c[1] = cg; c[2] = cb;
+        } else {
+            p.in_colour[self] = make_float4(cr, cg, cb, 0.f);
+        }
+    }
+
+    // ---- warp-aggregated append of the children + link -------------------------------------
+    const unsigned int m_refl = __ballot_sync(0xffffffffu, want_refl);
+    const unsigned int m_refr = __ballot_sync(0xffffffffu, want_refr);
+    if (m_refl | m_refr) {
+        const unsigned int n_refl = __popc(m_refl), n_refr = __popc(m_refr);
+        const unsigned int m_any = m_refl | m_refr;
+        unsigned int base = 0, lbase = 0;
+        if (lane == 0) {
+            base  = atomicAdd(p.out_count, n_refl + n_refr);
+            lbase = atomicAdd(p.link_count, (unsigned int)__popc(m_any));
+        }
+        base  = __shfl_sync(0xffffffffu, base, 0);
+        lbase = __shfl_sync(0xffffffffu, lbase, 0);
+        const unsigned int below = (1u << lane) - 1u;
+        int s_refl = -1, s_refr = -1;
+        if (want_refl) {
+            s_refl = (int)(base + __popc(m_refl & below));
+            const V3 rd = reflect3<E>(d, N);
+            p.out_od0[s_refl] = make_float4(P.x, P.y, P.z, e_refl);
+            p.out_od1[s_refl] = make_float4(rd.x, rd.y, rd.z, 0.0f);          // CRayon default ior, Rayon.cpp:16
+        }
+        if (want_refr) {
+            s_refr = (int)(base + n_refl + __popc(m_refr & below));
+            V3 n2 = N; float ratio, nior;
+            if (ior == mior) { nior = f.scene_ior; ratio = FP<E>::div(mior, f.scene_ior); n2 = neg3(N); }
+            else             { nior = mior;        ratio = FP<E>::div(f.scene_ior, mior); }
+            const V3 rd = refract3<E>(d, n2, ratio);
+            p.out_od0[s_refr] = make_float4(P.x, P.y, P.z, e_refr);
+            p.out_od1[s_refr] = make_float4(rd.x, rd.y, rd.z, nior);
+        }
+        if (want_refl || want_refr)
+            p.links[lbase + __popc(m_any & below)] = make_int4(self, s_refl, s_refr, mat);
+    }
+
+    // ---- statistics ---------------------------------------------------------------------------
+    block_stats4(p.stats, n_shadow, want_refl ? 1u : 0u, want_refr ? 1u : 0u, n_tests, sm_acc);
+}
+
+// ---------------------------------------------------------------------------------------
+// Bottom-up fold: parent += refl_child * kr, then parent += refr_child * kt
+// (Scene.cpp:1789 and :1822, in that order).  One thread per link: deterministic.
+// ---------------------------------------------------------------------------------------
+template <bool E>
+__global__ void __launch_bounds__(256) k_combine(const CombineParams p)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n_links) return;
+    const int4 lk = p.links[i];
+    const float kr = p.mat[lk.w].m1.w, kt = p.mat[lk.w].m2.x;
+    float r, g, b;
+    if (p.parent_is_level0) { const float* c = p.parent_c0 + 3 * (size_t)lk.x; r = c[0]; g = c[1]; b = c[2]; }
+    else { const float4 c = p.parent_colour[lk.x]; r = c.x; g = c.y; b = c.z; }
+    if (lk.y >= 0) {
+        const float4 c = p.child_colour[lk.y];
+        r = FP<E>::madd(c.x, kr, r); g = FP<E>::madd(c.y, kr, g); b = FP<E>::madd(c.z, kr, b);
+    }
+    if (lk.z >= 0) {
+        const float4 c = p.child_colour[lk.z];
+        r = FP<E>::madd(c.x, kt, r); g = FP<E>::madd(c.y, kt, g); b = FP<E>::madd(c.z, kt, b);
+    }
+    if (p.parent_is_level0) { float* c = p.parent_c0 + 3 * (size_t)lk.x; c[0] = r; c[1] = g; c[2] = b; }
+    else p.parent_colour[lk.x] = make_float4(r, g, b, 0.f);
+}
+
+// ---------------------------------------------------------------------------------------
+// Resolve: k x k box filter of the sample lattice (j outer, i inner, times 1/(k*k); k = 1 is
+// a plain copy) + the RGBA8 quantiser floor(clamp(c,0,1)*255 + 0.5), NaN -> 0 (counted).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_resolve(const ResolveParams p)
+{
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int yr = blockIdx.y * 8 + (threadIdx.x >> 5);          // pixel row inside the chunk
+    unsigned int nans = 0;
+    if (x < p.f.W && yr < p.chunk_prows) {
+        const int k = p.f.k;
+        float r, g, b;
+        if (k == 1) {
+            const float* c = p.c0 + 3 * ((size_t)yr * p.f.LW + x);
+            r = c[0]; g = c[1]; b = c[2];
+        } else {
+            r = g = b = 0.f;
+            for (int j = 0; j < k; ++j)
+                for (int i = 0; i < k; ++i) {
+                    const float* c = p.c0 + 3 * ((size_t)(yr * k + j) * p.f.LW + (x * k + i));
+                    r = __fadd_rn(r, c[0]); g = __fadd_rn(g, c[1]); b = __fadd_rn(b, c[2]);
+                }
+            const float sc = __fdiv_rn(1.0f, (float)(k * k));
+            r = __fmul_rn(r, sc); g = __fmul_rn(g, sc); b = __fmul_rn(b, sc);
+        }
+        const size_t pix = (size_t)(p.chunk_py0 + yr) * p.f.W + x;
+        if (p.fb_f32) { float* o = p.fb_f32 + 3 * pix; o[0] = r; o[1] = g; o[2] = b; }
+        if (p.fb_rgba8) {
+            float v[3] = { r, g, b };
+            unsigned char q[3];
+            #pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                float w = v[c];
+                if (w != w) { ++nans; w = 0.f; }
+                w = fminf(fmaxf(w, 0.f), 1.f);
+                q[c] = (unsigned char)floorf(__fadd_rn(__fmul_rn(w, 255.0f), 0.5f));
+            }
+            p.fb_rgba8[pix] = make_uchar4(q[0], q[1], q[2], 255);
+        }
+    }
+    nans = __reduce_add_sync(0xffffffffu, nans);
+    if ((threadIdx.x & 31) == 0 && nans)
+        atomicAdd(&p.stats[((blockIdx.x + blockIdx.y) % RT_STAT_SLOTS) * ST_COUNT + ST_NAN], (unsigned long long)nans);
+}
+
+// ---------------------------------------------------------------------------------------
+// Ray-level queries over the unified list in global memory (parity-test entry points).
+// ---------------------------------------------------------------------------------------
+template <bool E>
+__global__ void __launch_bounds__(128) k_query_nearest(DeviceScene s, int n, const float* o3, const float* d3,
+                                                       int* out_order, float* out_t, float* out_n3)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = i < n;
+    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light;
+    V3 o = valid ? ld3(o3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
+    V3 d = valid ? ld3(d3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
+    float t; int k; bool lin;
+    nearest_hit<E>(sv, o, d, t, k, lin);
+    if (!valid) return;
+    V3 N = k >= 0 ? hit_normal<E>(sv, k, o, d, t, lin) : mk3(0.f, 0.f, 0.f);
+    out_order[i] = k; out_t[i] = t;
+    out_n3[3 * (size_t)i] = N.x; out_n3[3 * (size_t)i + 1] = N.y; out_n3[3 * (size_t)i + 2] = N.z;
+}
+
+template <bool E>
+__global__ void __launch_bounds__(128) k_query_shadow(DeviceScene s, int n, const float* p3, const float* l3, float* out3)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = i < n;
+    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light;
+    V3 P = valid ? ld3(p3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
+    V3 L = valid ? ld3(l3 + 3 * (size_t)i) : mk3(1.f, 0.f, 0.f);
+    V3 Ld = sub3<E>(L, P);
+    const float dist = norm3<E>(Ld);
+    Ld = scale3<E>(Ld, FP<E>::rcp(dist));
+    float fr, fg, fb;
+    (void)shadow_filter<E>(sv, valid, P, Ld, dist, fr, fg, fb);
+    if (!valid) return;
+    out3[3 * (size_t)i] = fr; out3[3 * (size_t)i + 1] = fg; out3[3 * (size_t)i + 2] = fb;
+}
+
+// ---------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------
+size_t resident_smem_bytes(const ResidentLayout& rl) { return (size_t)rl.bytes; }
+
+cudaError_t resident_prepare(size_t max_smem_bytes)
+{
+    cudaError_t e;
+    const int b = (int)max_smem_bytes;
+    if ((e = cudaFuncSetAttribute(k_resident_level<false, true>,  cudaFuncAttributeMaxDynamicSharedMemorySize, b)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_resident_level<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, b)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_resident_level<true, true>,   cudaFuncAttributeMaxDynamicSharedMemorySize, b)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(k_resident_level<true, false>,  cudaFuncAttributeMaxDynamicSharedMemorySize, b)) != cudaSuccess) return e;
+    return cudaSuccess;
+}
+
+cudaError_t launch_resident_level(const LevelParams& p, bool exact, cudaStream_t st)
+{
+    const size_t smem = resident_smem_bytes(p.rl);
+    if (p.level == 0) {
+        const int tiles_x = (p.f.LW + 15) / 16, tiles_y = (p.chunk_rows + 15) / 16;
+        const dim3 grid((unsigned)(tiles_x * tiles_y));
+        if (exact) k_resident_level<true, true><<<grid, RES_THREADS, smem, st>>>(p);
+        else       k_resident_level<false, true><<<grid, RES_THREADS, smem, st>>>(p);
+    } else {
+        const dim3 grid((unsigned)((p.in_count + RES_THREADS - 1) / RES_THREADS));
+        if (exact) k_resident_level<true, false><<<grid, RES_THREADS, smem, st>>>(p);
+        else       k_resident_level<false, false><<<grid, RES_THREADS, smem, st>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_combine(const CombineParams& p, bool exact, cudaStream_t st)
+{
+    const dim3 grid((unsigned)((p.n_links + 255) / 256));
+    if (exact) k_combine<true><<<grid, 256, 0, st>>>(p);
+    else       k_combine<false><<<grid, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_resolve(const ResolveParams& p, cudaStream_t st)
+{
+    const dim3 grid((unsigned)((p.f.W + 31) / 32), (unsigned)((p.chunk_prows + 7) / 8));
+    k_resolve<<<grid, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_query_nearest(const DeviceScene& s, int n, const float* o3, const float* d3,
+                                 int* out_order, float* out_t, float* out_n3, bool exact, cudaStream_t st)
+{
+    const dim3 grid((unsigned)((n + 127) / 128));
+    if (exact) k_query_nearest<true><<<grid, 128, 0, st>>>(s, n, o3, d3, out_order, out_t, out_n3);
+    else       k_query_nearest<false><<<grid, 128, 0, st>>>(s, n, o3, d3, out_order, out_t, out_n3);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_query_shadow(const DeviceScene& s, int n, const float* p3, const float* l3,
+                                float* out3, bool exact, cudaStream_t st)
+{
+    const dim3 grid((unsigned)((n + 127) / 128));
+    if (exact) k_query_shadow<true><<<grid, 128, 0, st>>>(s, n, p3, l3, out3);
+    else       k_query_shadow<false><<<grid, 128, 0, st>>>(s, n, p3, l3, out3);
+    return cudaGetLastError();
+}
+
+} // namespace rtb

@@ -1,0 +1,105 @@
+// rt_scene.cuh -- device-side scene / queue layouts shared by all kernels.
+#pragma once
+#include "rt_math.cuh"
+
+namespace rtb {
+
+// ---- unified, insertion-ordered surface list (64 B per surface, 4 x float4) -------------
+// slot k of the list IS insertion index k of CScene::m_Surfaces (Scene.cpp:107), so a hit id
+// is an order and ties resolve like the reference's linear scan (Scene.cpp:1713).
+//   triangle: r0 = p0.xyz | type   r1 = e1.xyz | material   r2 = e2.xyz | 0   r3 = normal.xyz | 0
+//   quadric : r0 = A B C  | type   r1 = yz xz xy | material r2 = lx ly lz | K r3 = 0
+//   plane   : r0 = n.xyz  | type   r1 = c 0 0 | material
+enum { SURF_TRIANGLE = 0, SURF_QUADRIC = 1, SURF_PLANE = 2 };
+struct SurfRec { float4 r0, r1, r2, r3; };
+
+// material: m0 = r g b ka | m1 = kd ks shininess kr | m2 = kt ior 0 0     (48 B)
+struct MatRec { float4 m0, m1, m2; };
+// light: l0 = position | intensity, l1 = colour | 0                         (32 B)
+struct LightRec { float4 l0, l1; };
+
+// "resident blob": [SurfRec x N][MatRec x M][LightRec x L], 16-byte aligned, one bulk copy.
+struct ResidentLayout {
+    int n_surf, n_mat, n_light;
+    int off_mat, off_light, bytes;      // byte offsets inside the blob
+};
+
+// ---- streamed (tiled brute-force) layout ------------------------------------------------
+// triangles: 3 x float4 per triangle, tile-contiguous:  p0.xyz | order,  e1.xyz | material, e2.xyz | 0
+struct TriRec { float4 a, b, c; };
+// quadrics: q0 = A B C | order, q1 = yz xz xy | material, q2 = lx ly lz | K
+struct QuadRec { float4 q0, q1, q2; };
+// planes:  n.xyz c | then order/material in a parallel int2
+struct PlaneRec { float4 nc; int order, material, pad0, pad1; };
+
+struct DeviceScene {
+    ResidentLayout rl;
+    const unsigned char* blob;      // resident blob in global memory
+    const SurfRec*  surf;           // = blob
+    const MatRec*   mat;
+    const LightRec* light;
+    // streamed layout
+    int n_tri, n_quad, n_plane;
+    const TriRec*   tri;            // padded to a multiple of the tile size with never-hit triangles
+    const float4*   tri_normal;     // normal.xyz | unused
+    const QuadRec*  quad;
+    const PlaneRec* plane;
+    int n_tri_padded;
+};
+
+// ---- per-frame constants ------------------------------------------------------------------
+struct FrameParams {
+    int   W, H;                 // pixels
+    int   k;                    // spp grid
+    int   LW, LH;               // sample lattice = k*W, k*H
+    float inv_w, inv_h;         // 1/(k*W), 1/(k*H)  (Scene.cpp:678-679 at lattice resolution)
+    float half_w, half_h;
+    float cam_pos[3], cam_u[3], cam_v[3], cam_n[3];
+    float background[3];
+    int   max_bounces;
+    float min_energy, scene_ior;
+    int   secondary;            // 0: never spawn
+    // banding (multi-GPU): local lattice row -> global lattice row
+    int   band_lrows;           // band height in lattice rows (band_rows * k)
+    int   n_ranks, rank;
+};
+
+// ---- wavefront queues -----------------------------------------------------------------------
+// level k >= 1 ray: o.xyz | energy,  d.xyz | ior.  (bounce count == level)
+struct RayQueue {
+    float4* od0;
+    float4* od1;
+    float4* colour;             // result of each ray (level >= 1)
+    int4*   links;              // parents at THIS level that spawned: parent, refl child, refr child, material
+    unsigned int* counters;     // [0] rays in the NEXT level, [1] links at this level (device)
+};
+
+RT_DEV V3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
+RT_DEV V3 f4_xyz(float4 v) { return mk3(v.x, v.y, v.z); }
+
+// Global lattice row of local lattice row `ly` under interleaved banding.
+RT_DEV int global_lattice_row(const FrameParams& f, int ly)
+{
+    if (f.n_ranks <= 1) return ly;
+    int b = ly / f.band_lrows, r = ly - b * f.band_lrows;
+    return (b * f.n_ranks + f.rank) * f.band_lrows + r;
+}
+
+// Primary ray through lattice sample (sx, sy): Scene.cpp:1543-1552.
+template <bool E> RT_DEV void primary_ray(const FrameParams& f, int sx, int sy, V3& o, V3& d)
+{
+    typedef FP<E> F;
+    // (2*PixX*InvW - 1) * HalfW : int multiply, then float
+    float vx = F::mul(F::sub(F::mul((float)(2 * sx), f.inv_w), 1.0f), f.half_w);
+    float vy = F::mul(F::sub(F::mul((float)(2 * sy), f.inv_h), 1.0f), f.half_h);
+    float vz = -1.0f;
+    // v * Orientation, rows U,V,N, zero translation row (Matrice4.h:297-306)
+    V3 r;
+    r.x = F::add(F::madd(f.cam_n[0], vz, F::madd(f.cam_v[0], vy, F::mul(f.cam_u[0], vx))), 0.0f);
+    r.y = F::add(F::madd(f.cam_n[1], vz, F::madd(f.cam_v[1], vy, F::mul(f.cam_u[1], vx))), 0.0f);
+    r.z = F::add(F::madd(f.cam_n[2], vz, F::madd(f.cam_v[2], vy, F::mul(f.cam_u[2], vx))), 0.0f);
+    o = mk3(f.cam_pos[0], f.cam_pos[1], f.cam_pos[2]);
+    d = normalise3<E>(r);
+}
+
+} // namespace rtb

@@ -1,0 +1,66 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from __graft_entry__ import load_package  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+REF_DIR = "/root/reference/Projet-INF8702"
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu")
+    config.addinivalue_line("markers", "slow: CPU test that takes more than a few seconds")
+
+
+@pytest.fixture(scope="session")
+def rt():
+    return load_package()
+
+
+@pytest.fixture(scope="session")
+def port(rt):
+    from oracle.portbind import PortOracle
+    return PortOracle(rt.abi)
+
+
+@pytest.fixture(scope="session")
+def renderer(rt):
+    r = rt.Renderer(0)          # raises without a GPU: there is no fallback
+    yield r
+    r.close()
+
+
+def packed_scene(rt, n):
+    return rt.PackedScene.load(os.path.join(GOLDEN, "packed", f"scene{n}.npz"))
+
+
+def golden_image(n, depth):
+    return np.load(os.path.join(GOLDEN, "images", f"scene{n}_d{depth}.npz"))["rgb"]
+
+
+def bits_equal(a, b):
+    return np.array_equal(np.ascontiguousarray(a, np.float32).view(np.uint32),
+                          np.ascontiguousarray(b, np.float32).view(np.uint32))
+
+
+def classify_mismatches(got8, want8, sig):
+    """North-star gate: per-channel |diff| <= 1 on >= 99.9 % of pixels, every other pixel must
+    sit next to (8-neighbourhood) a change of the oracle's ray-tree signature, i.e. on a
+    silhouette or shadow terminator.  Returns (fraction_ok, n_bad, n_bad_unexplained)."""
+    d = np.abs(got8[..., :3].astype(np.int32) - want8[..., :3].astype(np.int32)).max(axis=-1)
+    bad = d > 1
+    H, W = bad.shape
+    edge = np.zeros((H, W), bool)
+    p = np.pad(sig, 1, mode="edge")
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            if dy or dx:
+                edge |= p[1 + dy:1 + dy + H, 1 + dx:1 + dx + W] != sig
+    return 1.0 - bad.mean(), int(bad.sum()), int((bad & ~edge).sum())

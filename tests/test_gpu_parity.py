@@ -1,0 +1,122 @@
+"""GPU (-m gpu): the CUDA path through the C ABI against the CPU oracle and the golden frames.
+
+Bars: exact-FP mode (no FMA contraction) bit-identical to the oracle's float frame on every
+bundled scene except where powf enters (scene4: <= 4 ulp of the Phong term); default fused mode
+per-channel RGBA8 within +-1 on >= 99.9 % of pixels, every other pixel adjacent to a change of
+the oracle's ray-tree signature (silhouette / shadow terminator), counted and printed."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, bits_equal, classify_mismatches, golden_image, packed_scene
+
+pytestmark = pytest.mark.gpu
+SCENES = range(1, 10)
+
+
+@pytest.mark.parametrize("n", SCENES)
+@pytest.mark.parametrize("depth", [0, 2, 4])
+def test_exact_mode_bitwise_vs_golden(rt, renderer, n, depth):
+    ps = packed_scene(rt, n)
+    renderer.set_scene(ps)
+    fr = rt.make_frame(ps.frame, 160, 120, max_bounces=depth, flags=rt.F_EXACT_FP)
+    got, got8, st = renderer.render(fr)
+    want = golden_image(n, depth)
+    if n == 4:      # specular scene: powf (CUDA <= 4 ulp vs glibc) enters the Phong term
+        assert np.allclose(got, want, rtol=0, atol=2e-6)
+    else:
+        nd = int((got.view(np.uint32) != want.view(np.uint32)).sum())
+        assert nd == 0, f"{nd} differing floats"
+    assert st.rays_primary == 160 * 120 and st.nan_pixels == 0
+
+
+@pytest.mark.parametrize("n", SCENES)
+def test_fused_mode_tolerance_vs_oracle(rt, renderer, port, n):
+    ps = packed_scene(rt, n)
+    renderer.set_scene(ps)
+    W, H, depth = 640, 480, 4
+    fr = rt.make_frame(ps.frame, W, H, max_bounces=depth)
+    got, got8, st = renderer.render(fr)
+    want, _ = port.render(ps, fr, threads=port.max_threads)
+    want8, _ = port.quantise(want)
+    sig, _ = port.signatures(ps, fr, threads=port.max_threads)
+    ok, n_bad, n_unexplained = classify_mismatches(got8, want8, sig)
+    print(f"scene{n}: within +-1: {100 * ok:.4f} %, mismatching pixels {n_bad}, off-edge {n_unexplained}, "
+          f"max |float diff| {np.abs(got - want).max():.3g}")
+    assert ok >= 0.999
+    assert n_unexplained == 0
+    # ray counts are those of the reference's recursion
+    c = port.ray_counts()
+    assert st.rays_primary == c["primary"]
+    assert abs(int(st.rays_shadow) - c["shadow"]) <= max(4, c["shadow"] // 2000)
+    assert abs(int(st.rays_reflect) - c["reflect"]) <= max(4, c["reflect"] // 2000)
+    assert abs(int(st.rays_refract) - c["refract"]) <= max(4, c["refract"] // 2000)
+
+
+@pytest.mark.parametrize("n", SCENES)
+def test_ray_queries_exact(rt, renderer, n):
+    ps = packed_scene(rt, n)
+    renderer.set_scene(ps)
+    z = np.load(os.path.join(GOLDEN, "rays", f"scene{n}.npz"))
+    idx, t, nrm = renderer.trace_nearest(z["org"], z["dirs"], flags=rt.F_EXACT_FP)
+    assert np.array_equal(idx, z["idx"])
+    assert bits_equal(t, z["t"]) and bits_equal(nrm, z["nrm"])
+    filt = renderer.trace_shadow(z["pts"], z["lights"], flags=rt.F_EXACT_FP)
+    assert bits_equal(filt, z["filt"])
+    # fused mode: same winners except for rays within rounding of an edge
+    idx2, t2, _ = renderer.trace_nearest(z["org"], z["dirs"])
+    assert (idx2 != z["idx"]).mean() < 2e-3
+    same = idx2 == z["idx"]
+    assert np.allclose(t2[same], z["t"][same], rtol=1e-4, atol=1e-3)
+
+
+def test_default_bounces_20_and_odd_sizes(rt, renderer, port):
+    """Reference default m_NbRebondsMax = 20 (Scene.cpp:68); sizes that are not multiples of 16
+    (the GLSL path silently dropped edge pixels, Scene.cpp:1308)."""
+    ps = packed_scene(rt, 9)                       # two facing mirrors: long reflection chains
+    renderer.set_scene(ps)
+    fr = rt.make_frame(ps.frame, 237, 131, flags=rt.F_EXACT_FP)
+    assert fr.max_bounces == 20
+    got, _, st = renderer.render(fr)
+    want, _ = port.render(ps, fr, threads=port.max_threads)
+    assert bits_equal(got, want)
+    assert st.depth_levels >= 10
+
+
+def test_supersampling_exact(rt, renderer, port):
+    ps = packed_scene(rt, 7)
+    renderer.set_scene(ps)
+    fr = rt.make_frame(ps.frame, 96, 72, max_bounces=3, spp_grid=4, flags=rt.F_EXACT_FP)
+    got, _, st = renderer.render(fr)
+    want, _ = port.render(ps, fr, threads=port.max_threads)
+    assert bits_equal(got, want)
+    assert st.rays_primary == 96 * 72 * 16
+
+
+def test_quantiser_and_device_resident_frame(rt, renderer, port):
+    ps = packed_scene(rt, 5)
+    renderer.set_scene(ps)
+    fr = rt.make_frame(ps.frame, 200, 150, max_bounces=2, flags=rt.F_EXACT_FP)
+    _, _, st = renderer.render(fr, want_f32=False, want_rgba8=False)     # stays on the device
+    f, q = renderer.read_frame(150, 200)
+    q_want, _ = port.quantise(f)
+    assert np.array_equal(q, q_want)
+    assert st.ms_d2h == 0.0 and st.ms_render > 0.0
+
+
+def test_full_size_1080p_properties(rt, renderer, port):
+    """BASELINE config 2 at full size: size-independent checks (the oracle takes ~1 s here, so
+    the whole frame is compared as well)."""
+    ps = packed_scene(rt, 1)
+    renderer.set_scene(ps)
+    fr = rt.make_frame(ps.frame, 1920, 1080, max_bounces=2, flags=rt.F_EXACT_FP)
+    got, got8, st = renderer.render(fr)
+    want, _ = port.render(ps, fr, threads=port.max_threads)
+    assert bits_equal(got, want)
+    # idempotence: a second render of the same frame is bit-identical
+    again, _, _ = renderer.render(fr)
+    assert bits_equal(again, got)
+    # a crop of a frame equals the same pixels rendered as the lattice region by the oracle
+    reg, _ = port.render_region(ps, fr, 900, 500, 64, 32, threads=4)
+    assert bits_equal(got[500:532, 900:964], reg)

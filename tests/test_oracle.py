@@ -1,0 +1,97 @@
+"""CPU: pins the oracle.  The C restatement (oracle/rt_oracle.c) must reproduce, bit for bit,
+(a) the golden frames / rays generated from the reference's own compiled code and (b) -- where
+/root/reference is present -- the compiled reference itself, live."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, REF_DIR, bits_equal, golden_image, packed_scene
+
+SCENES = range(1, 10)
+
+
+@pytest.mark.parametrize("n", SCENES)
+@pytest.mark.parametrize("depth", [0, 2, 4])
+def test_port_matches_golden_frames(rt, port, n, depth):
+    ps = packed_scene(rt, n)
+    fr = rt.make_frame(ps.frame, 160, 120, max_bounces=depth)
+    out, _ = port.render(ps, fr, threads=4)
+    assert bits_equal(out, golden_image(n, depth))
+
+
+@pytest.mark.parametrize("n", SCENES)
+def test_port_matches_golden_rays(rt, port, n):
+    ps = packed_scene(rt, n)
+    z = np.load(os.path.join(GOLDEN, "rays", f"scene{n}.npz"))
+    idx, t, nrm = port.nearest(ps, z["org"], z["dirs"], threads=4)
+    assert np.array_equal(idx, z["idx"])
+    assert bits_equal(t, z["t"]) and bits_equal(nrm, z["nrm"])
+    filt = port.shadow(ps, z["pts"], z["lights"], threads=4)
+    assert bits_equal(filt, z["filt"])
+
+
+def test_no_secondary_flag_equals_depth0(rt, port):
+    ps = packed_scene(rt, 7)
+    fr = rt.make_frame(ps.frame, 96, 64, max_bounces=4, flags=rt.F_NO_SECONDARY)
+    out, _ = port.render(ps, fr, threads=4)
+    fr0 = rt.make_frame(ps.frame, 96, 64, max_bounces=0)
+    out0, _ = port.render(ps, fr0, threads=4)
+    assert bits_equal(out, out0)
+
+
+def test_checksums_640x480(rt, port):
+    """BASELINE.md section 2 fingerprints (sum of all float channels, sha256 of the PPM)."""
+    import hashlib
+    sums = json.load(open(os.path.join(GOLDEN, "checksums.json")))
+    assert abs(sums["scene1_d0"]["sum"] - 238466.994696) < 1e-5
+    assert sums["scene1_d0"]["sha256_ppm"].startswith("79af5233d8f01c87")
+    for key in ("scene1_d0", "scene7_d2", "scene9_d4"):
+        n, d = int(key[5]), int(key[-1])
+        ps = packed_scene(rt, n)
+        fr = rt.make_frame(ps.frame, 640, 480, max_bounces=d)
+        out, _ = port.render(ps, fr, threads=8)
+        assert abs(float(np.sum(out.astype(np.float64))) - sums[key]["sum"]) < 1e-6
+        q, nans = port.quantise(out)
+        ppm = b"P6\n640 480\n255\n" + q[::-1, :, :3].tobytes()
+        assert hashlib.sha256(ppm).hexdigest() == sums[key]["sha256_ppm"] and nans == 0
+
+
+def test_supersampling_is_box_filtered_lattice(rt, port):
+    """spp grid k == reference rendered at kW x kH, box filtered."""
+    ps = packed_scene(rt, 7)
+    k, W, H = 3, 40, 30
+    fr = rt.make_frame(ps.frame, W, H, max_bounces=2, spp_grid=k)
+    out, _ = port.render(ps, fr, threads=4)
+    big = rt.make_frame(ps.frame, W * k, H * k, max_bounces=2)
+    lat, _ = port.render(ps, big, threads=4)
+    acc = np.zeros((H, W, 3), np.float32)
+    for j in range(k):
+        for i in range(k):
+            acc = acc + lat[j::k, i::k]
+    assert bits_equal(out, acc * np.float32(1.0 / (k * k)))
+
+
+needs_ref = pytest.mark.skipif(not os.path.exists(os.path.join(REF_DIR, "Scene.cpp")),
+                               reason="reference sources not present on this machine")
+
+
+@needs_ref
+@pytest.mark.parametrize("n", [1, 2, 5, 8, 9])
+def test_port_matches_live_reference(rt, port, n):
+    from oracle.portbind import packed_from_ref_dump
+    from oracle.refbind import RefRenderer
+    ref = RefRenderer("rec")
+    ref.load(os.path.join(REF_DIR, "Scenes", f"scene{n}.dat"), max_bounces=3)
+    img, _ = ref.render_full(200, 150)
+    ps = packed_from_ref_dump(rt.abi, ref.dump())
+    fr = rt.make_frame(ps.frame, 200, 150, max_bounces=3)
+    out, _ = port.render(ps, fr, threads=4)
+    assert bits_equal(out, img)
+    # sub-pixel lattice through the per-ray entry of the reference
+    reg, _ = ref.render_region(200, 150, 2, 100, 60, 64, 48, threads=4)
+    fr2 = rt.make_frame(ps.frame, 200, 150, max_bounces=3, spp_grid=2)
+    mine, _ = port.render_region(ps, fr2, 100, 60, 64, 48, threads=4)
+    assert bits_equal(mine, reg)
+    ref.free()
