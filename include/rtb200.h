@@ -29,6 +29,11 @@
  *     Quadrique.cpp:110) has already been applied by the host scene classes.
  *   - images: row 0 is the BOTTOM scanline (Scene.cpp:1556: index (x + y*W)), float RGB is
  *     unclamped, RGBA8 is floor(clamp(c,0,1)*255+0.5) with A = 255 and NaN -> 0.
+ *   - arithmetic: by default every value that is kept (hit distance, normal, colour) is
+ *     produced by the reference's own binary32 rounding sequence (one rounding per operation,
+ *     no contraction), so frames are bit-identical to the CPU renderer except where powf
+ *     enters (<= 4 ulp of the Phong term); fused multiply-adds are used only inside
+ *     conservative culling tests whose survivors are re-evaluated in the reference sequence.
  *   - there is NO CPU fallback: without a usable CUDA device every compute entry point
  *     fails with RTB200_E_CUDA.
  */
@@ -58,9 +63,13 @@ enum {
 enum {
     RTB200_F_USE_BVH      = 1u << 0,  /* triangles through the GPU-built LBVH (rtb200_build_bvh)        */
     RTB200_F_NO_SECONDARY = 1u << 1,  /* as-shipped reference: no reflection / refraction rays           */
-    RTB200_F_EXACT_FP     = 1u << 2,  /* no FMA contraction: same rounding sequence as the CPU reference  */
+    RTB200_F_EXACT_FP     = 1u << 2,  /* reference rounding sequence everywhere AND no conservative culling */
+                                      /* filters: every test is the reference's own arithmetic            */
     RTB200_F_FORCE_STREAM = 1u << 3,  /* always use the tiled (streamed) brute-force kernels              */
-    RTB200_F_FORCE_RESIDENT = 1u << 4 /* always use the scene-resident fused kernel (fails if too large)  */
+    RTB200_F_FORCE_RESIDENT = 1u << 4,/* always use the scene-resident fused kernel (fails if too large)  */
+    RTB200_F_FUSED_FP     = 1u << 5,  /* contract every a*b+c into one FMA (fastest; NOT the reference's   */
+                                      /* rounding: decisions on acne / edge pixels may flip) */
+    RTB200_F_GATHER_F32   = 1u << 6   /* multi-GPU: also gather the float RGB frame (default: RGBA8 only)   */
 };
 
 /* Material block of ISurface (ISurface.h:24-41; defaults ISurface.cpp:15-25). 10 floats. */
@@ -134,7 +143,8 @@ typedef struct rtb200_stats {
     uint32_t depth_levels;         /* wavefront levels that held at least one ray                     */
     uint32_t path;                 /* 0 = scene-resident fused kernels, 1 = streamed tiled kernels, 2 = LBVH */
     uint32_t chunks;               /* image chunks the frame was split into                           */
-    double   ms_trace_nearest, ms_trace_shadow, ms_shade;  /* streamed path: per-stage totals         */
+    double   ms_trace_nearest, ms_trace_shadow, ms_shade;  /* streamed path: per-stage totals; resident   */
+                                   /* path: ms_trace_nearest = the level-0 fused kernel (first chunk)     */
 } rtb200_stats;
 
 typedef struct rtb200_ctx rtb200_ctx;

@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 from . import abi
-from .abi import (F_EXACT_FP, F_FORCE_RESIDENT, F_FORCE_STREAM, F_NO_SECONDARY, F_USE_BVH,  # noqa: F401
+from .abi import (F_EXACT_FP, F_FORCE_RESIDENT, F_FORCE_STREAM, F_FUSED_FP, F_GATHER_F32, F_NO_SECONDARY, F_USE_BVH,  # noqa: F401
                   Frame, PackedScene, Stats, make_frame)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))

@@ -15,6 +15,8 @@ F_NO_SECONDARY = 1 << 1
 F_EXACT_FP = 1 << 2
 F_FORCE_STREAM = 1 << 3
 F_FORCE_RESIDENT = 1 << 4
+F_FUSED_FP = 1 << 5
+F_GATHER_F32 = 1 << 6
 
 _fp = C.POINTER(C.c_float)
 _ip = C.POINTER(C.c_int32)

@@ -393,7 +393,10 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
             p.out_count = d_cnt + 2 * level; p.link_count = d_cnt + 2 * level + 1;
             p.links = cur.links.as<int4>();
             p.stats = ctx->stats.as<unsigned long long>();
+            const bool timed = (level == 0 && ly0 == 0);       // dominant kernel, timed on its own stream
+            if (timed) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
             CU(launch_resident_level(p, exact, ctx->stream));
+            if (timed) CU(cudaEventRecord(ctx->ev[3], ctx->stream));
             ++*launches;
             if (!spawn) { n_links.push_back(0); ++level; break; }
             CU(cudaMemcpyAsync(h_cnt, d_cnt + 2 * level, 2 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
@@ -432,6 +435,7 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
     st->depth_levels = max_level_seen;
     st->chunks = chunks;
     st->path = 0;
+    st->ms_trace_nearest = -1.0;                               // filled by the caller after the final sync
     // brute force by construction: every nearest-hit query and every shadow query that is not
     // cut short by the all-zero early-out tests every surface; counted exactly on the host
     return RTB200_OK;
@@ -463,7 +467,7 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     if (fr->width <= 0 || fr->height <= 0 || fr->spp_grid < 0 || fr->spp_grid > 64) return fail(ctx, RTB200_E_ARG, "bad frame size");
     if ((long long)fr->width * std::max(fr->spp_grid, 1) > (1 << 20)) return fail(ctx, RTB200_E_ARG, "frame too wide");
     CU(cudaSetDevice(ctx->device));
-    const bool exact = (fr->flags & RTB200_F_EXACT_FP) != 0;
+    const bool exact = (fr->flags & RTB200_F_FUSED_FP) == 0;     // reference rounding unless fused is requested
     FrameParams fp;
     fill_frame_params(fr, ctx->n_ranks, ctx->rank, fp);
     const int band = fp.band_lrows / fp.k;
@@ -500,7 +504,9 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
 
     ctx->last_W = fp.W; ctx->last_H = fp.H; ctx->last_local_rows = local_rows; ctx->last_gathered = false;
     if (ctx->comm && ctx->n_ranks > 1) {
-        rc = comm_gather_frame(ctx, fp.W, fp.H, band, true, true, &st.ms_gather);
+        const bool gather_f32 = (fr->flags & RTB200_F_GATHER_F32) != 0;
+        if (ctx->rank == 0 && out_f32 && !gather_f32) return fail(ctx, RTB200_E_ARG, "float output on several GPUs needs RTB200_F_GATHER_F32");
+        rc = comm_gather_frame(ctx, fp.W, fp.H, band, gather_f32, true, &st.ms_gather);
         if (rc != RTB200_OK) return rc;
         ctx->last_gathered = (ctx->rank == 0);
     }
@@ -512,6 +518,11 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
     st.ms_render = ms;
+    if (st.ms_trace_nearest < 0.0) {                           // level-0 fused kernel of the first chunk
+        float k0 = 0.f;
+        CU(cudaEventElapsedTime(&k0, ctx->ev[2], ctx->ev[3]));
+        st.ms_trace_nearest = k0;
+    }
     unsigned long long sum[ST_COUNT] = {0};
     for (int s = 0; s < RT_STAT_SLOTS; ++s) for (int c = 0; c < ST_COUNT; ++c) sum[c] += h_st[s * ST_COUNT + c];
     st.rays_primary = (uint64_t)local_rows * fp.k * (uint64_t)fp.LW;
@@ -567,7 +578,7 @@ extern "C" int rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* o3, con
     CU(cudaMemcpyAsync(ctx->q_in0.p, o3, b3, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->q_in1.p, d3, b3, cudaMemcpyHostToDevice, ctx->stream));
     CU(launch_query_nearest(ctx->ds, n, ctx->q_in0.as<float>(), ctx->q_in1.as<float>(), ctx->q_out0.as<int>(),
-                            ctx->q_out1.as<float>(), ctx->q_out2.as<float>(), (flags & RTB200_F_EXACT_FP) != 0, ctx->stream));
+                            ctx->q_out1.as<float>(), ctx->q_out2.as<float>(), (flags & RTB200_F_FUSED_FP) == 0, ctx->stream));
     CU(cudaMemcpyAsync(out_order, ctx->q_out0.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(out_t, ctx->q_out1.p, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(out_n3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));
@@ -588,7 +599,7 @@ extern "C" int rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* p3, cons
     CU(cudaMemcpyAsync(ctx->q_in0.p, p3, b3, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->q_in1.p, l3, b3, cudaMemcpyHostToDevice, ctx->stream));
     CU(launch_query_shadow(ctx->ds, n, ctx->q_in0.as<float>(), ctx->q_in1.as<float>(), ctx->q_out2.as<float>(),
-                           (flags & RTB200_F_EXACT_FP) != 0, ctx->stream));
+                           (flags & RTB200_F_FUSED_FP) == 0, ctx->stream));
     CU(cudaMemcpyAsync(out3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return RTB200_OK;

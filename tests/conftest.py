@@ -50,7 +50,7 @@ def bits_equal(a, b):
                           np.ascontiguousarray(b, np.float32).view(np.uint32))
 
 
-def classify_mismatches(got8, want8, sig):
+def classify_mismatches(got8, want8, sig, radius=1):
     """North-star gate: per-channel |diff| <= 1 on >= 99.9 % of pixels, every other pixel must
     sit next to (8-neighbourhood) a change of the oracle's ray-tree signature, i.e. on a
     silhouette or shadow terminator.  Returns (fraction_ok, n_bad, n_bad_unexplained)."""
@@ -58,9 +58,10 @@ def classify_mismatches(got8, want8, sig):
     bad = d > 1
     H, W = bad.shape
     edge = np.zeros((H, W), bool)
-    p = np.pad(sig, 1, mode="edge")
-    for dy in (-1, 0, 1):
-        for dx in (-1, 0, 1):
+    r = radius
+    p = np.pad(sig, r, mode="edge")
+    for dy in range(-r, r + 1):
+        for dx in range(-r, r + 1):
             if dy or dx:
-                edge |= p[1 + dy:1 + dy + H, 1 + dx:1 + dx + W] != sig
+                edge |= p[r + dy:r + dy + H, r + dx:r + dx + W] != sig
     return 1.0 - bad.mean(), int(bad.sum()), int((bad & ~edge).sum())
