@@ -1,0 +1,391 @@
+// rtb_scene.cpp -- CScene, the scene-file parser, the SoA packer and the CUDA dispatch.
+#include "rtb_scene.hpp"
+
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+
+using namespace Scene;
+
+int CVar::g_FenetreID = 0;
+int CVar::g_LargeurFenetre = 512;
+int CVar::g_HauteurFenetre = 256;
+int CVar::g_LargeurViewport = 0;
+int CVar::g_HauteurViewport = 0;
+CScene* CVar::g_GestionnaireDeScene = nullptr;
+bool CVar::g_ComputerShadersON = true;
+static char g_chemin_nuanceur[] = "shaders/rayTracing.glsl";
+char* CVar::g_ComputeShaderPath = g_chemin_nuanceur;
+CNuanceurCalculProg* CVar::g_ComputeShader = nullptr;
+int CVar::g_Peripherique = 0;
+
+const REAL CScene::DIM_FILM_CAM = 0.024f;
+
+// ---- CStringUtils ---------------------------------------------------------------------------
+std::string CStringUtils::TrimRight(const std::string& s, const std::string& t) { std::string r = s; return r.erase(r.find_last_not_of(t) + 1); }
+std::string CStringUtils::TrimLeft(const std::string& s, const std::string& t) { std::string r = s; return r.erase(0, s.find_first_not_of(t)); }
+std::string CStringUtils::Trim(const std::string& s, const std::string& t) { return TrimLeft(TrimRight(s, t), t); }
+
+// ---- CNuanceurCalculProg ----------------------------------------------------------------------
+CNuanceurCalculProg::CNuanceurCalculProg() {}
+CNuanceurCalculProg::CNuanceurCalculProg(char*, bool compilerImmediatement)
+{
+    estVide_ = false;
+    if (compilerImmediatement) compilerEtLier();
+}
+CNuanceurCalculProg::~CNuanceurCalculProg() { if (ctx_) rtb200_destroy(ctx_); }
+
+void CNuanceurCalculProg::compilerEtLier()
+{
+    if (ctx_) return;
+    const int rc = rtb200_create(CVar::g_Peripherique, &ctx_);
+    if (rc != RTB200_OK) {
+        // the reference's convention: print and exit (NuanceurCalculProg.cpp:300, Scene.cpp:708)
+        std::cerr << "[ERREUR]: rtb200_create(" << CVar::g_Peripherique << ") : " << rtb200_error_string(rc) << " -- "
+                  << rtb200_last_error(nullptr) << " (no CPU fallback in this build)" << std::endl;
+        exit(EXIT_FAILURE);
+    }
+    estCompileEtLie_ = true;
+}
+void CNuanceurCalculProg::activer() { compilerEtLier(); }
+void CNuanceurCalculProg::uniform1(char*, int) {}
+void CNuanceurCalculProg::uniform1(char*, float) {}
+void CNuanceurCalculProg::enregistrerUniformFloat(const char*, const float&) {}
+void CNuanceurCalculProg::enregistrerUniformInteger(const char*, const int&) {}
+GLuint CNuanceurCalculProg::getProg() { return ctx_ ? 1u : 0u; }
+
+// ---- SceneEmballee ----------------------------------------------------------------------------
+rtb200_scene SceneEmballee::vue() const
+{
+    rtb200_scene s;
+    s.n_triangles = (int32_t)tri_order.size(); s.n_quadrics = (int32_t)quad_order.size(); s.n_planes = (int32_t)plane_order.size();
+    s.n_lights = (int32_t)lights.size(); s.n_materials = (int32_t)materials.size();
+    s.tri_points = tri_points.data(); s.tri_normal = tri_normal.data(); s.tri_material = tri_material.data(); s.tri_order = tri_order.data();
+    s.quad_coef = quad_coef.data(); s.quad_material = quad_material.data(); s.quad_order = quad_order.data();
+    s.plane_coef = plane_coef.data(); s.plane_material = plane_material.data(); s.plane_order = plane_order.data();
+    s.materials = materials.data(); s.lights = lights.data();
+    return s;
+}
+
+// ---- CScene: construction and setters ----------------------------------------------------------
+CScene::CScene()
+{
+    m_Camera.Position = CVecteur3::ZERO; m_Camera.PointVise = CVecteur3::ZERO; m_Camera.Up = CVecteur3::UNIT_Y;
+    m_Camera.Orientation = CMatrice4::IDENTITE;
+    m_Camera.Focale = RENDRE_REEL(50.0); m_Camera.Angle = 0;     // Scene.cpp:71-77
+}
+CScene::~CScene() { Liberer(); }
+
+void CScene::AjouterSurface(ISurface* const s) { m_Surfaces.push_back(s); }
+void CScene::AjouterLumiere(CLumiere* const l) { m_Lumieres.push_back(l); }
+void CScene::AjusterPositionCamera(const CVecteur3& p) { m_Camera.Position = p; }
+void CScene::AjusterPointViseCamera(const CVecteur3& p) { m_Camera.PointVise = p; }
+void CScene::AjusterVecteurUpCamera(const CVecteur3& u) { m_Camera.Up = u; }
+void CScene::AjusterResolution(const int w, const int h) { m_ResLargeur = w; m_ResHauteur = h; }
+void CScene::AjusterCouleurArrierePlan(const CCouleur& c) { m_CouleurArrierePlan = c; }
+void CScene::AjusterNbRebondsMax(const int n) { m_NbRebondsMax = n; }
+void CScene::AjusterEnergieMinimale(const REAL e) { m_EnergieMinRayon = e; }
+void CScene::AjusterIndiceRefraction(const REAL i) { m_IndiceRefractionScene = i; }
+GLuint CScene::ObtenirTextureGL() { return 0; }
+
+void CScene::Liberer()
+{
+    for (ISurface* s : m_Surfaces) delete s;
+    m_Surfaces.clear();
+    for (CLumiere* l : m_Lumieres) delete l;
+    m_Lumieres.clear();
+    delete[] m_InfoPixel;
+    m_InfoPixel = nullptr;
+    m_ImageRGBA8.clear();
+    m_Prepare = false;
+}
+
+// ---- scene file ---------------------------------------------------------------------------------
+// Same grammar and quirks as CScene::TraiterFichierDeScene (Scene.cpp:231-501): lines are NOT
+// trimmed (the reference discards Trim's result, :255), only a first-byte '*' is a comment,
+// keywords are found by substring search, values by sscanf, a header flushes the previous
+// object, unknown keys are ignored.  Hardening beyond the reference: lines of any length (the
+// reference loops forever on >= 80 bytes), a trailing CR is dropped, an unopenable file is
+// reported (and, like the reference, leaves an empty scene).
+void CScene::TraiterFichierDeScene(const char* fichier)
+{
+    std::ifstream in(fichier);
+    if (!in.is_open()) {
+        std::cerr << "[CScene::TraiterFichierDeScene()] : Incapable d'ouvrir " << fichier << "." << std::endl;
+        return;
+    }
+    auto has = [](const std::string& s, const char* key) { return s.find(key) != std::string::npos; };
+    EtatTraitementScene etat = TRAITEMENT_SCENE;
+    CLumiere* lumiere = nullptr;
+    ISurface* surface = nullptr;
+    char mot[256];
+    float v0 = 0, v1 = 0, v2 = 0;
+    int R = 0, G = 0, B = 0;
+    std::string ligne;
+    while (std::getline(in, ligne)) {
+        if (!ligne.empty() && ligne.back() == '\r') ligne.pop_back();
+        if (ligne.empty() || ligne[0] == '*') continue;
+        const char* txt = ligne.c_str();
+        EtatTraitementScene nouveau = etat;
+        bool entete = true;
+        if (has(ligne, "Lumiere:")) nouveau = TRAITEMENT_LUMIERE;
+        else if (has(ligne, "Poly:")) nouveau = TRAITEMENT_TRIANGLE;
+        else if (has(ligne, "Plane:")) nouveau = TRAITEMENT_PLAN;
+        else if (has(ligne, "Quad:")) nouveau = TRAITEMENT_QUADRIQUE;
+        else entete = false;
+
+        if (entete) {
+            if (etat != TRAITEMENT_SCENE) {
+                if (etat == TRAITEMENT_LUMIERE) AjouterLumiere(lumiere); else AjouterSurface(surface);
+                surface = nullptr; lumiere = nullptr;
+            }
+            etat = nouveau;
+            switch (etat) {
+            case TRAITEMENT_LUMIERE:   lumiere = new CLumiere(); break;
+            case TRAITEMENT_TRIANGLE:  surface = new CTriangle(); break;
+            case TRAITEMENT_PLAN:      surface = new CPlan(); break;
+            case TRAITEMENT_QUADRIQUE: surface = new CQuadrique(); break;
+            default: break;
+            }
+            continue;
+        }
+        if (surface) {                                  // material / transform keys of any surface
+            bool generique = true;
+            if (has(ligne, "color:")) { sscanf(txt, "%255s %i %i %i", mot, &R, &G, &B); surface->AjusterCouleur(CCouleur(R, G, B)); }
+            else if (has(ligne, "ambient:")) { sscanf(txt, "%255s %f", mot, &v0); surface->AjusterCoeffAmbiant(v0); }
+            else if (has(ligne, "diffus:")) { sscanf(txt, "%255s %f", mot, &v0); surface->AjusterCoeffDiffus(v0); }
+            else if (has(ligne, "specular:")) { sscanf(txt, "%255s %f %f", mot, &v0, &v1); surface->AjusterCoeffSpeculaire(v0); surface->AjusterCoeffBrillance(v1); }
+            else if (has(ligne, "reflect:")) { sscanf(txt, "%255s %f", mot, &v0); surface->AjusterCoeffReflexion(v0); }
+            else if (has(ligne, "refract:")) { sscanf(txt, "%255s %f %f", mot, &v0, &v1); surface->AjusterCoeffRefraction(v0); surface->AjusterIndiceRefraction(v1); }
+            else if (has(ligne, "rotate:")) {           // X then Y then Z, each post-multiplied (Scene.cpp:356-364)
+                sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2);
+                CMatrice4 t = surface->ObtenirTransformation();
+                t.RotationAutourDesX(Deg2Rad<REAL>(v0)); t.RotationAutourDesY(Deg2Rad<REAL>(v1)); t.RotationAutourDesZ(Deg2Rad<REAL>(v2));
+                surface->AjusterTransformation(t);
+            }
+            else if (has(ligne, "translate:")) {
+                sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2);
+                CMatrice4 t = surface->ObtenirTransformation(); t.Translation(v0, v1, v2); surface->AjusterTransformation(t);
+            }
+            else if (has(ligne, "scale:")) {
+                sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2);
+                CMatrice4 t = surface->ObtenirTransformation(); t.MiseAEchelle(v0, v1, v2); surface->AjusterTransformation(t);
+            }
+            else generique = false;
+            if (generique) continue;
+        }
+        switch (etat) {
+        case TRAITEMENT_SCENE:
+            if (has(ligne, "background:")) { sscanf(txt, "%255s %i %i %i", mot, &R, &G, &B); AjusterCouleurArrierePlan(CCouleur(R, G, B)); }
+            else if (has(ligne, "origin:")) { sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2); AjusterPositionCamera(CVecteur3(v0, v1, v2)); }
+            else if (has(ligne, "eye:")) { sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2); AjusterPointViseCamera(CVecteur3(v0, v1, v2)); }
+            else if (has(ligne, "up:")) { sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2); AjusterVecteurUpCamera(CVecteur3(v0, v1, v2)); }
+            break;
+        case TRAITEMENT_LUMIERE:
+            if (has(ligne, "position:")) { sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2); lumiere->SetPosition(CVecteur3(v0, v1, v2)); }
+            else if (has(ligne, "intens:")) { sscanf(txt, "%255s %f", mot, &v0); lumiere->SetIntensity(v0); }
+            else if (has(ligne, "color:")) { sscanf(txt, "%255s %i %i %i", mot, &R, &G, &B); lumiere->AjusterCouleur(CCouleur(R, G, B)); }
+            break;
+        case TRAITEMENT_TRIANGLE:
+            if (has(ligne, "point:")) {
+                int idx = 0;
+                sscanf(txt, "%255s %i %f %f %f", mot, &idx, &v0, &v1, &v2);
+                static_cast<CTriangle*>(surface)->AjusterPoint(idx, CVecteur3(v0, v1, v2));
+            }
+            break;
+        case TRAITEMENT_PLAN:
+            if (has(ligne, "v_linear:")) { sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2); static_cast<CPlan*>(surface)->AjusterNormale(CVecteur3(v0, v1, v2)); }
+            else if (has(ligne, "v_const:")) { sscanf(txt, "%255s %f", mot, &v0); static_cast<CPlan*>(surface)->AjusterConstante(v0); }
+            break;
+        case TRAITEMENT_QUADRIQUE:
+            if (has(ligne, "v_quad:")) { sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2); static_cast<CQuadrique*>(surface)->AjusterQuadratique(CVecteur3(v0, v1, v2)); }
+            else if (has(ligne, "v_mixte:")) { sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2); static_cast<CQuadrique*>(surface)->AjusterMixte(CVecteur3(v0, v1, v2)); }
+            else if (has(ligne, "v_linear:")) { sscanf(txt, "%255s %f %f %f", mot, &v0, &v1, &v2); static_cast<CQuadrique*>(surface)->AjusterLineaire(CVecteur3(v0, v1, v2)); }
+            else if (has(ligne, "v_const:")) { sscanf(txt, "%255s %f", mot, &v0); static_cast<CQuadrique*>(surface)->AjusterConstante(v0); }
+            break;
+        }
+    }
+    if (surface) AjouterSurface(surface);
+    if (lumiere) AjouterLumiere(lumiere);
+}
+
+// ---- camera and pre-processing ------------------------------------------------------------------
+// Scene.cpp:624-660: thin-lens field of view from the camera-to-target distance, then the
+// orthonormal basis U,V,N stored as the ROWS of the orientation matrix.
+void CScene::InitialiserCamera()
+{
+    const REAL d2 = CVecteur3::Distance(m_Camera.Position, m_Camera.PointVise);
+    const REAL y2 = (d2 / (m_Camera.Focale * RENDRE_REEL(0.001)) - 1) * DIM_FILM_CAM;
+    m_Camera.Angle = (360 * std::atan2(y2 * RENDRE_REEL(0.5), d2)) / RENDRE_REEL(PI);
+    const CVecteur3 N = CVecteur3::Normaliser(m_Camera.Position - m_Camera.PointVise);
+    const CVecteur3 V = CVecteur3::Normaliser(m_Camera.Up - N * CVecteur3::ProdScal(m_Camera.Up, N));
+    const CVecteur3 U = CVecteur3::ProdVect(V, N);
+    m_Camera.Orientation = CMatrice4(U.x, U.y, U.z, 0.0f, V.x, V.y, V.z, 0.0f, N.x, N.y, N.z, 0.0f, 0.0f, 0.0f, 0.0f, 1.0f);
+}
+
+void CScene::Initialiser()                               // Scene.cpp:140-147
+{
+    InitialiserCamera();
+    for (ISurface* s : m_Surfaces) s->Pretraitement();
+    delete[] m_InfoPixel;
+    m_InfoPixel = new float[(size_t)m_ResLargeur * m_ResHauteur * 3];
+}
+
+// The reference re-runs Pretraitement on every LancerRayons (transforms applied twice on a
+// second call, Scene.cpp:140-147 has no guard); here it runs once per loaded scene.
+void CScene::Preparer()
+{
+    if (m_Prepare) {                                     // resolution may have changed since the last frame
+        delete[] m_InfoPixel;
+        m_InfoPixel = new float[(size_t)m_ResLargeur * m_ResHauteur * 3];
+    } else {
+        Initialiser();
+        m_Prepare = true;
+    }
+    // ---- SoA packer: replaces the std140 UBO packer of Scene.cpp:799-1269 ------------------------
+    SceneEmballee& e = m_Emballee;
+    e = SceneEmballee();
+    int ordre = 0;
+    for (ISurface* s : m_Surfaces) {
+        rtb200_material m;
+        const CCouleur c = s->ObtenirCouleur();
+        m.color[0] = c.r; m.color[1] = c.g; m.color[2] = c.b;
+        m.ambient = s->ObtenirCoeffAmbiant(); m.diffuse = s->ObtenirCoeffDiffus();
+        m.specular = s->ObtenirCoeffSpeculaire(); m.shininess = s->ObtenirCoeffBrillance();
+        m.reflect = s->ObtenirCoeffReflexion(); m.refract = s->ObtenirCoeffRefraction(); m.ior = s->ObtenirIndiceRefraction();
+        const int mat = (int)e.materials.size();
+        e.materials.push_back(m);
+        if (const CTriangle* t = dynamic_cast<const CTriangle*>(s)) {
+            for (int k = 0; k < 3; ++k) { const CVecteur3 p = t->ObtenirPoint(k); e.tri_points.insert(e.tri_points.end(), { p.x, p.y, p.z }); }
+            const CVecteur3 n = t->ObtenirNormale();
+            e.tri_normal.insert(e.tri_normal.end(), { n.x, n.y, n.z });
+            e.tri_material.push_back(mat); e.tri_order.push_back(ordre);
+        } else if (const CQuadrique* q = dynamic_cast<const CQuadrique*>(s)) {
+            const CVecteur3 a = q->ObtenirQuadratique(), mx = q->ObtenirMixte(), l = q->ObtenirLineaire();
+            e.quad_coef.insert(e.quad_coef.end(), { a.x, a.y, a.z, mx.x, mx.y, mx.z, l.x, l.y, l.z, q->ObtenirConstante() });
+            e.quad_material.push_back(mat); e.quad_order.push_back(ordre);
+        } else if (const CPlan* p = dynamic_cast<const CPlan*>(s)) {
+            const CVecteur3 n = p->ObtenirNormale();
+            e.plane_coef.insert(e.plane_coef.end(), { n.x, n.y, n.z, p->ObtenirConstante() });
+            e.plane_material.push_back(mat); e.plane_order.push_back(ordre);
+        }
+        ++ordre;
+    }
+    for (const CLumiere* l : m_Lumieres) {
+        rtb200_light g;
+        const CVecteur3 p = l->GetPosition(); const CCouleur c = l->ObtenirCouleur();
+        g.position[0] = p.x; g.position[1] = p.y; g.position[2] = p.z;
+        g.color[0] = c.r; g.color[1] = c.g; g.color[2] = c.b; g.intensity = l->GetIntensity();
+        e.lights.push_back(g);
+    }
+    // ---- frame block: replaces the "General" UBO (Scene.cpp:704-783) and Scene.cpp:676-679 -------
+    rtb200_frame& f = e.cadre;
+    memset(&f, 0, sizeof f);
+    f.width = m_ResLargeur; f.height = m_ResHauteur; f.spp_grid = m_GrilleSpp;
+    f.max_bounces = m_NbRebondsMax; f.min_energy = m_EnergieMinRayon; f.scene_ior = m_IndiceRefractionScene;
+    f.background[0] = m_CouleurArrierePlan.r; f.background[1] = m_CouleurArrierePlan.g; f.background[2] = m_CouleurArrierePlan.b;
+    f.cam_pos[0] = m_Camera.Position.x; f.cam_pos[1] = m_Camera.Position.y; f.cam_pos[2] = m_Camera.Position.z;
+    for (int c = 0; c < 3; ++c) { f.cam_u[c] = m_Camera.Orientation.m[0][c]; f.cam_v[c] = m_Camera.Orientation.m[1][c]; f.cam_n[c] = m_Camera.Orientation.m[2][c]; }
+    f.half_h = std::tan(Deg2Rad<REAL>(m_Camera.Angle * RENDRE_REEL(0.5)));
+    f.half_w = (RENDRE_REEL(m_ResLargeur) / m_ResHauteur) * f.half_h;
+    f.flags = m_Drapeaux;
+}
+
+const SceneEmballee& CScene::ObtenirSceneEmballee()
+{
+    Preparer();
+    return m_Emballee;
+}
+
+// ---- render ---------------------------------------------------------------------------------------
+void CScene::LancerRayons()
+{
+    Preparer();
+    if (!CVar::g_ComputerShadersON) {
+        // The reference's C++ per-pixel loop (Scene.cpp:1535-1563) is deliberately NOT part of this
+        // build: the only renderer is the CUDA one.  Fail loudly, like every other fatal error here.
+        std::cerr << "[ERREUR]: CVar::g_ComputerShadersON == false: this build has no CPU renderer." << std::endl;
+        exit(EXIT_FAILURE);
+    }
+    if (!CVar::g_ComputeShader) CVar::g_ComputeShader = new CNuanceurCalculProg(CVar::g_ComputeShaderPath, true);
+    CVar::g_ComputeShader->activer();
+    rtb200_ctx* ctx = CVar::g_ComputeShader->contexte();
+    const rtb200_scene vue = m_Emballee.vue();
+    int rc = rtb200_set_scene(ctx, &vue);                // was: SceneData UBO glBufferData (Scene.cpp:1268)
+    if (rc == RTB200_OK && (m_Drapeaux & RTB200_F_USE_BVH)) rc = rtb200_build_bvh(ctx);
+    if (rc == RTB200_OK) {
+        m_ImageRGBA8.resize((size_t)m_ResLargeur * m_ResHauteur * 4);
+        rc = rtb200_render(ctx, &m_Emballee.cadre, m_InfoPixel, m_ImageRGBA8.data(), &m_Stats);   // was: glDispatchCompute (Scene.cpp:1308)
+    }
+    if (rc != RTB200_OK) {
+        std::cerr << "[ERREUR]: rendu CUDA : " << rtb200_error_string(rc) << " -- " << rtb200_last_error(ctx) << std::endl;
+        exit(EXIT_FAILURE);
+    }
+}
+
+bool CScene::EcrireImagePPM(const char* fichier) const
+{
+    if (m_ImageRGBA8.empty()) return false;
+    FILE* f = fopen(fichier, "wb");
+    if (!f) return false;
+    fprintf(f, "P6\n%d %d\n255\n", m_ResLargeur, m_ResHauteur);
+    std::vector<unsigned char> row((size_t)m_ResLargeur * 3);
+    for (int y = m_ResHauteur - 1; y >= 0; --y) {       // buffer row 0 is the bottom scanline
+        const unsigned char* src = m_ImageRGBA8.data() + (size_t)y * m_ResLargeur * 4;
+        for (int x = 0; x < m_ResLargeur; ++x) { row[3 * x] = src[4 * x]; row[3 * x + 1] = src[4 * x + 1]; row[3 * x + 2] = src[4 * x + 2]; }
+        fwrite(row.data(), 1, row.size(), f);
+    }
+    fclose(f);
+    return true;
+}
+
+// ---- C helpers for the Python test harness (ctypes) -------------------------------------------------
+extern "C" {
+
+int rtscene_load(const char* path, int max_bounces)
+{
+    CScene::LibererInstance();
+    CScene* s = CScene::ObtenirInstance();
+    CVar::g_GestionnaireDeScene = s;
+    std::ifstream probe(path);
+    if (!probe.is_open()) return -1;
+    probe.close();
+    s->TraiterFichierDeScene(path);
+    if (max_bounces >= 0) s->AjusterNbRebondsMax(max_bounces);
+    return (int)s->NbSurfaces();
+}
+
+// Packs the current scene for resolution W x H; returns pointers into the scene's own vectors.
+int rtscene_pack(int W, int H, rtb200_scene* out_scene, rtb200_frame* out_frame)
+{
+    CScene* s = CScene::ObtenirInstance();
+    s->AjusterResolution(W, H);
+    const SceneEmballee& e = s->ObtenirSceneEmballee();
+    *out_scene = e.vue();
+    *out_frame = e.cadre;
+    return 0;
+}
+
+// Full drop-in path: CScene::LancerRayons() -> CUDA.  Copies the float and RGBA8 frames out.
+int rtscene_render(int W, int H, int spp_grid, unsigned int flags, float* out_rgb, unsigned char* out_rgba8, rtb200_stats* st)
+{
+    CScene* s = CScene::ObtenirInstance();
+    s->AjusterResolution(W, H);
+    s->AjusterSurechantillonnage(spp_grid);
+    s->AjusterDrapeauxRendu(flags);
+    CVar::g_ComputerShadersON = true;
+    s->LancerRayons();
+    if (out_rgb) memcpy(out_rgb, s->ObtenirInfoPixel(), sizeof(float) * 3 * (size_t)W * H);
+    if (out_rgba8) memcpy(out_rgba8, s->ObtenirImageRGBA8(), (size_t)4 * W * H);
+    if (st) *st = s->ObtenirStatistiques();
+    return 0;
+}
+
+void rtscene_free(void)
+{
+    CScene::LibererInstance();
+    delete CVar::g_ComputeShader;
+    CVar::g_ComputeShader = nullptr;
+}
+
+} // extern "C"

@@ -1,0 +1,107 @@
+"""The fresh C++ host scene API (parser, camera, Pretraitement, SoA packer) against the
+reference: post-Pretraitement coefficients, materials, lights and camera basis of all nine
+bundled scenes must equal -- bit for bit -- what the reference's own classes produce
+(tests/golden/packed/*.npz, dumped through the reference's getters)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, REF_DIR, bits_equal, golden_image, packed_scene
+
+KEYS = ("tri_points", "tri_normal", "quad_coef", "plane_coef", "materials", "lights")
+IKEYS = ("tri_material", "tri_order", "quad_material", "quad_order", "plane_material", "plane_order")
+
+
+@pytest.fixture(scope="module")
+def host(rt):
+    from importlib import import_module
+    hb = import_module("rtb200.hostbind")
+    yield hb
+    hb.free()
+
+
+def _same_scene(ps, want, f, W, H):
+    for k in KEYS:
+        assert ps[k].shape == want[k].shape, k
+        assert bits_equal(ps[k], want[k]), k
+    for k in IKEYS:
+        assert np.array_equal(ps[k], want[k]), k
+    for k in ("cam_pos", "cam_u", "cam_v", "cam_n", "background"):
+        assert bits_equal(ps.frame[k], want.frame[k]), k
+    assert np.float32(ps.frame["half_h"]) == np.float32(want.frame["half_h"])
+    assert np.float32(f.half_w) == (np.float32(W) / np.float32(H)) * np.float32(want.frame["half_h"])
+    assert f.max_bounces == 20 and np.float32(f.min_energy) == np.float32(0.01) and f.scene_ior == 1.0
+
+
+@pytest.mark.parametrize("n", range(1, 10))
+def test_parser_and_pretraitement_match_reference(rt, host, n):
+    ps, f = host.load_and_pack(os.path.join(GOLDEN, "scenes", f"scene{n}.dat"), 160, 120)
+    _same_scene(ps, packed_scene(rt, n), f, 160, 120)
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(REF_DIR, "Scenes")), reason="reference not present")
+@pytest.mark.parametrize("n", range(1, 10))
+def test_original_scene_files_parse_identically(rt, host, n):
+    """The unstripped bundled files (comments, indented '* ---' lines, 'instance:' keys)."""
+    ps, f = host.load_and_pack(os.path.join(REF_DIR, "Scenes", f"scene{n}.dat"), 640, 480)
+    _same_scene(ps, packed_scene(rt, n), f, 640, 480)
+
+
+def test_parser_hardening(rt, host, tmp_path):
+    """CRLF line endings and lines longer than the reference's 80-byte buffer."""
+    src = open(os.path.join(GOLDEN, "scenes", "scene1.dat")).read()
+    long_comment = "* " + "x" * 200 + "\n"
+    p = tmp_path / "crlf.dat"
+    p.write_bytes((long_comment + src).replace("\n", "\r\n").encode())
+    ps, f = host.load_and_pack(str(p), 160, 120)
+    _same_scene(ps, packed_scene(rt, 1), f, 160, 120)
+    with pytest.raises(FileNotFoundError):
+        host.load_and_pack(str(tmp_path / "missing.dat"), 16, 16)
+
+
+def test_host_pack_feeds_oracle_to_golden_frame(rt, host, port):
+    """host classes -> packed scene -> C oracle == golden frame of the reference renderer."""
+    for n in (3, 9):
+        ps, _ = host.load_and_pack(os.path.join(GOLDEN, "scenes", f"scene{n}.dat"), 160, 120)
+        fr = rt.make_frame(ps.frame, 160, 120, max_bounces=4)
+        out, _ = port.render(ps, fr, threads=4)
+        assert bits_equal(out, golden_image(n, 4))
+
+
+def test_cli_fails_loudly_without_gpu(rt, host):
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("a GPU is present")
+    except ImportError:
+        pass
+    r = subprocess.run([host.CLI_PATH, os.path.join(GOLDEN, "scenes", "scene1.dat"), "-x", "64", "-y", "48"],
+                       capture_output=True, text=True)
+    assert r.returncode != 0 and "no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 7, 9])
+def test_dropin_lancer_rayons_on_gpu(rt, host, n):
+    """CScene::TraiterFichierDeScene + LancerRayons (the reference's call sequence, Main.cpp:87-181)
+    through CUDA == golden frame of the reference CPU renderer, bit for bit."""
+    host.lib().rtscene_load(os.fsencode(os.path.join(GOLDEN, "scenes", f"scene{n}.dat")), 4)
+    f, q, st = host.render_loaded(160, 120)
+    assert bits_equal(f, golden_image(n, 4))
+    assert st.rays_primary == 160 * 120 and q[..., 3].min() == 255
+
+
+@pytest.mark.gpu
+def test_cli_renders_ppm(rt, host, tmp_path):
+    out = tmp_path / "s7.ppm"
+    r = subprocess.run([host.CLI_PATH, os.path.join(GOLDEN, "scenes", "scene7.dat"), "-x", "160", "-y", "120",
+                        "--depth", "4", "--out", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    data = out.read_bytes()
+    assert data.startswith(b"P6\n160 120\n255\n")
+    img = np.frombuffer(data[len(b"P6\n160 120\n255\n"):], np.uint8).reshape(120, 160, 3)[::-1]
+    want = golden_image(7, 4)
+    q = np.floor(np.clip(want, 0, 1) * np.float32(255) + np.float32(0.5)).astype(np.uint8)
+    assert np.array_equal(img, q)
