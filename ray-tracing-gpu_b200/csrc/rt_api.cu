@@ -108,6 +108,7 @@ void rtb200_destroy(rtb200_ctx* ctx)
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     comm_destroy(ctx);
+    stream_release(ctx);
     ctx->scene_buf.release(); ctx->stage.release();
     ctx->c0.release(); ctx->fb_f32.release(); ctx->fb_rgba8.release(); ctx->stats.release(); ctx->counters.release();
     ctx->full_f32.release(); ctx->full_rgba8.release(); ctx->h_small.release();
@@ -526,7 +527,8 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     unsigned long long sum[ST_COUNT] = {0};
     for (int s = 0; s < RT_STAT_SLOTS; ++s) for (int c = 0; c < ST_COUNT; ++c) sum[c] += h_st[s * ST_COUNT + c];
     st.rays_primary = (uint64_t)local_rows * fp.k * (uint64_t)fp.LW;
-    st.rays_shadow = sum[ST_SHADOW]; st.rays_reflect = sum[ST_REFLECT]; st.rays_refract = sum[ST_REFRACT];
+    if (st.path == 0) st.rays_shadow = sum[ST_SHADOW];
+    st.rays_reflect = sum[ST_REFLECT]; st.rays_refract = sum[ST_REFRACT];
     st.nan_pixels = sum[ST_NAN];
     if (st.path == 0) {
         // resident kernels count surface tests in one counter; split by the scene's type mix
@@ -535,7 +537,9 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
         st.tests_quadric  = (uint64_t)llround((double)sum[ST_TEST_TRI] * ctx->ds.n_quad / n);
         st.tests_plane    = (uint64_t)llround((double)sum[ST_TEST_TRI] * ctx->ds.n_plane / n);
     } else {
-        st.tests_triangle = sum[ST_TEST_TRI]; st.tests_quadric = sum[ST_TEST_QUAD]; st.tests_plane = sum[ST_TEST_PLANE];
+        st.tests_triangle = sum[ST_TEST_TRI] + ctx->host_tests[0];
+        st.tests_quadric = sum[ST_TEST_QUAD] + ctx->host_tests[1];
+        st.tests_plane = sum[ST_TEST_PLANE] + ctx->host_tests[2];
         st.bvh_nodes_visited = sum[ST_BVH_NODES];
     }
     st.kernel_launches = launches;
@@ -577,6 +581,11 @@ extern "C" int rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* o3, con
         (e = ctx->q_out2.ensure(b3)) != cudaSuccess) return set_cuda_error(ctx, e, "query buffers");
     CU(cudaMemcpyAsync(ctx->q_in0.p, o3, b3, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->q_in1.p, d3, b3, cudaMemcpyHostToDevice, ctx->stream));
+    const bool q_stream = ((size_t)ctx->ds.rl.bytes > RESIDENT_AUTO_BYTES || (flags & RTB200_F_FORCE_STREAM)) && !(flags & RTB200_F_FORCE_RESIDENT);
+    if (q_stream) {
+        const int rc = stream_query_nearest(ctx, n, flags);
+        if (rc != RTB200_OK) return rc;
+    } else
     CU(launch_query_nearest(ctx->ds, n, ctx->q_in0.as<float>(), ctx->q_in1.as<float>(), ctx->q_out0.as<int>(),
                             ctx->q_out1.as<float>(), ctx->q_out2.as<float>(), (flags & RTB200_F_FUSED_FP) == 0, ctx->stream));
     CU(cudaMemcpyAsync(out_order, ctx->q_out0.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
@@ -598,6 +607,11 @@ extern "C" int rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* p3, cons
         (e = ctx->q_out2.ensure(b3)) != cudaSuccess) return set_cuda_error(ctx, e, "query buffers");
     CU(cudaMemcpyAsync(ctx->q_in0.p, p3, b3, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->q_in1.p, l3, b3, cudaMemcpyHostToDevice, ctx->stream));
+    const bool q_stream = ((size_t)ctx->ds.rl.bytes > RESIDENT_AUTO_BYTES || (flags & RTB200_F_FORCE_STREAM)) && !(flags & RTB200_F_FORCE_RESIDENT);
+    if (q_stream) {
+        const int rc = stream_query_shadow(ctx, n, flags);
+        if (rc != RTB200_OK) return rc;
+    } else
     CU(launch_query_shadow(ctx->ds, n, ctx->q_in0.as<float>(), ctx->q_in1.as<float>(), ctx->q_out2.as<float>(),
                            (flags & RTB200_F_FUSED_FP) == 0, ctx->stream));
     CU(cudaMemcpyAsync(out3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));

@@ -84,6 +84,10 @@ struct rtb200_ctx {
     rtb::Comm* comm = nullptr;
     int rank = 0, n_ranks = 1;
 
+    // streamed path scratch (rt_stream.cu) and host-side test counts of the last frame
+    void* stream_scratch = nullptr;
+    unsigned long long host_tests[3] = {0, 0, 0};
+
     // peak cache
     double peak_tflops = 0.0, peak_mhz = 0.0;
 };
@@ -92,6 +96,9 @@ namespace rtb {
 int  set_cuda_error(rtb200_ctx* c, cudaError_t e, const char* where);
 int  render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
                      bool exact, rtb200_stats* st, uint32_t* launches);     // rt_stream.cu
+void stream_release(rtb200_ctx* c);
+int  stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags);            // inputs q_in0/q_in1, outputs q_out0..2 (device)
+int  stream_query_shadow(rtb200_ctx* c, int n, uint32_t flags);
 // rt_comm.cu
 int  comm_unique_id(uint8_t* id);
 int  comm_init(rtb200_ctx* c, int rank, int n_ranks, const uint8_t* id);

@@ -1,13 +1,236 @@
-// rt_stream.cu -- streamed (tiled brute-force) path and LBVH entry points.
+// rt_stream.cu -- host side of the streamed (tiled brute-force) wavefront path.
+//
+// Per image chunk and per recursion level k:
+//   trace_nearest  every ray x every surface           -> (t, order)
+//   shade_a        hit point, normal, shadow queries, children (level k+1 queue), links
+//   trace_shadow   every shadow query x every surface  -> filter RGB
+//   shade_b        ambient + per-light diffuse/Phong * filter, in light order -> ray colour
+// then the same bottom-up fold (k_combine) and resolve (k_resolve) as the resident path.
+// The host reads three counters per level (children, links, shadow queries) to size the next
+// launches exactly; nothing else crosses the bus during a frame.
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
 #include "rt_context.h"
+#include "rt_stream.cuh"
+
+using namespace rtb;
+
+#define SCU(call)                                                       \
+    do {                                                                \
+        cudaError_t e__ = (call);                                       \
+        if (e__ != cudaSuccess) return set_cuda_error(c, e__, #call);   \
+    } while (0)
+
+#define STREAM_CHUNK_SAMPLES (8u << 20)
 
 namespace rtb {
-int render_streamed(rtb200_ctx* c, const rtb200_frame*, const FrameParams&, int, bool, rtb200_stats*, uint32_t*)
+
+struct StreamBufs {                // per-context scratch of the streamed path (lives in the ctx levels + these)
+    DevBuf hit, hitP, hitN, q_base, sq0, sq1, filter;
+};
+
+static StreamBufs* stream_bufs(rtb200_ctx* c)
 {
-    c->last_error = "streamed path not available in this build";
-    return RTB200_E_STATE;
+    if (!c->stream_scratch) c->stream_scratch = new StreamBufs();
+    return static_cast<StreamBufs*>(c->stream_scratch);
 }
+
+void stream_release(rtb200_ctx* c)
+{
+    if (!c->stream_scratch) return;
+    StreamBufs* b = static_cast<StreamBufs*>(c->stream_scratch);
+    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->filter.release();
+    delete b;
+    c->stream_scratch = nullptr;
 }
+
+int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
+                    bool exact, rtb200_stats* st, uint32_t* launches)
+{
+    StreamBufs* sb = stream_bufs(c);
+    const int mode = (fr->flags & RTB200_F_FUSED_FP) ? 2 : ((fr->flags & RTB200_F_EXACT_FP) ? 1 : 0);
+    const int k = fp.k;
+    const int local_LH = local_rows * k;
+    const int L = c->ds.rl.n_light;
+    int children = c->max_children;
+    if (fr->min_energy < 0.f) children = 2;
+    if (!fp.secondary || fr->max_bounces <= 0) children = 0;
+
+    int rows_per_chunk = (int)((STREAM_CHUNK_SAMPLES / (unsigned)fp.LW) / (32u * k)) * 32 * k;
+    if (rows_per_chunk < 32 * k) rows_per_chunk = 32 * k;
+    if (rows_per_chunk > local_LH) rows_per_chunk = ((local_LH + 32 * k - 1) / (32 * k)) * 32 * k;
+
+    cudaError_t e;
+    if ((e = c->c0.ensure(sizeof(float) * 3 * (size_t)rows_per_chunk * fp.LW)) != cudaSuccess) return set_cuda_error(c, e, "c0");
+    const size_t n_counters = 4 * ((size_t)std::max(fr->max_bounces, 0) + 2);
+    if ((e = c->counters.ensure(sizeof(unsigned) * n_counters)) != cudaSuccess) return set_cuda_error(c, e, "counters");
+    unsigned* h_cnt = c->h_small.as<unsigned>();
+    unsigned* d_cnt = c->counters.as<unsigned>();
+    unsigned max_level_seen = 0, chunks = 0;
+    unsigned long long rays_nearest = 0;
+    cudaEvent_t ev_a = c->ev[2], ev_b = c->ev[3];
+    double ms_nearest = 0.0, ms_shadow = 0.0;
+    bool timed_first = false;
+
+    for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunks) {
+        const int rows = std::min(rows_per_chunk, local_LH - ly0);
+        SCU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, c->stream));
+        std::vector<int> n_rays, n_links;
+        n_rays.push_back(rows * fp.LW);
+        int level = 0;
+        for (;; ++level) {
+            const int n_in = n_rays[level];
+            if (n_in == 0) break;
+            const bool spawn = children > 0 && level < fr->max_bounces;
+            if ((int)c->levels.size() < level + 2) c->levels.resize((size_t)level + 2);
+            LevelBuf& cur = c->levels[level];
+            LevelBuf& nxt = c->levels[level + 1];
+            const size_t n = (size_t)n_in;
+            if ((e = sb->hit.ensure(sizeof(float2) * n)) != cudaSuccess || (e = sb->hitP.ensure(sizeof(float4) * n)) != cudaSuccess ||
+                (e = sb->hitN.ensure(sizeof(float4) * n)) != cudaSuccess || (e = sb->q_base.ensure(sizeof(int) * n)) != cudaSuccess ||
+                (e = sb->sq0.ensure(sizeof(float4) * n * std::max(L, 1))) != cudaSuccess || (e = sb->sq1.ensure(sizeof(float4) * n * std::max(L, 1))) != cudaSuccess ||
+                (e = sb->filter.ensure(sizeof(float4) * n * std::max(L, 1))) != cudaSuccess)
+                return set_cuda_error(c, e, "stream scratch");
+            if (level > 0 && (e = cur.colour.ensure(sizeof(float4) * n)) != cudaSuccess) return set_cuda_error(c, e, "colour");
+            if (spawn) {
+                const size_t cap = n * children;
+                if ((e = nxt.od0.ensure(sizeof(float4) * cap)) != cudaSuccess || (e = nxt.od1.ensure(sizeof(float4) * cap)) != cudaSuccess ||
+                    (e = cur.links.ensure(sizeof(int4) * n)) != cudaSuccess)
+                    return set_cuda_error(c, e, "queue");
+            }
+            // ---- nearest hit -------------------------------------------------------------------
+            TraceParams tp;
+            memset(&tp, 0, sizeof tp);
+            tp.f = fp; tp.s = c->ds; tp.primary = (level == 0);
+            tp.chunk_ly0 = ly0; tp.chunk_rows = rows; tp.local_LH = local_LH;
+            tp.in_od0 = cur.od0.as<float4>(); tp.in_od1 = cur.od1.as<float4>();
+            tp.n_rays = n_in; tp.hit = sb->hit.as<float2>(); tp.mode = mode;
+            const bool timed = !timed_first && level == 0;
+            if (timed) SCU(cudaEventRecord(ev_a, c->stream));
+            SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
+            if (timed) { SCU(cudaEventRecord(ev_b, c->stream)); timed_first = true; }
+            ++*launches;
+            rays_nearest += (unsigned long long)n_in;
+            // ---- shade A ------------------------------------------------------------------------
+            ShadeAParams sa;
+            memset(&sa, 0, sizeof sa);
+            sa.f = fp; if (!spawn) sa.f.secondary = 0;
+            sa.s = c->ds; sa.level = level;
+            sa.chunk_ly0 = ly0; sa.chunk_rows = rows; sa.local_LH = local_LH;
+            sa.in_od0 = tp.in_od0; sa.in_od1 = tp.in_od1; sa.n_rays = n_in; sa.hit = tp.hit;
+            sa.hitP = sb->hitP.as<float4>(); sa.hitN = sb->hitN.as<float4>(); sa.q_base = sb->q_base.as<int>();
+            sa.sq0 = sb->sq0.as<float4>(); sa.sq1 = sb->sq1.as<float4>();
+            sa.out_od0 = nxt.od0.as<float4>(); sa.out_od1 = nxt.od1.as<float4>();
+            sa.out_count = d_cnt + 4 * level; sa.link_count = d_cnt + 4 * level + 1; sa.sq_count = d_cnt + 4 * level + 2;
+            sa.links = cur.links.as<int4>();
+            sa.stats = c->stats.as<unsigned long long>();
+            sa.exact = exact ? 1 : 0;
+            SCU(launch_shade_a(sa, c->stream));
+            ++*launches;
+            SCU(cudaMemcpyAsync(h_cnt, d_cnt + 4 * level, 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
+            SCU(cudaStreamSynchronize(c->stream));
+            const int n_children = (int)h_cnt[0], n_lk = (int)h_cnt[1], n_sq = (int)h_cnt[2];
+            st->rays_shadow += (uint64_t)n_sq;
+            // ---- shadow filters --------------------------------------------------------------
+            if (n_sq > 0) {
+                ShadowParams sp;
+                memset(&sp, 0, sizeof sp);
+                sp.s = c->ds; sp.sq0 = sa.sq0; sp.sq1 = sa.sq1; sp.n_queries = n_sq;
+                sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode;
+                SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+                ++*launches;
+            }
+            // ---- shade B -------------------------------------------------------------------------
+            ShadeBParams sbp;
+            memset(&sbp, 0, sizeof sbp);
+            sbp.f = fp; sbp.s = c->ds; sbp.level = level;
+            sbp.chunk_ly0 = ly0; sbp.chunk_rows = rows; sbp.local_LH = local_LH;
+            sbp.in_od1 = tp.in_od1; sbp.n_rays = n_in;
+            sbp.hitP = sa.hitP; sbp.hitN = sa.hitN; sbp.q_base = sa.q_base; sbp.filter = sb->filter.as<float4>();
+            sbp.c0 = c->c0.as<float>(); sbp.colour = cur.colour.as<float4>(); sbp.exact = exact ? 1 : 0;
+            SCU(launch_shade_b(sbp, c->stream));
+            ++*launches;
+            n_links.push_back(spawn ? n_lk : 0);
+            if (!spawn) { ++level; break; }
+            n_rays.push_back(n_children);
+        }
+        const int levels_used = (int)n_links.size();
+        max_level_seen = std::max<unsigned>(max_level_seen, (unsigned)levels_used);
+        for (int l = levels_used - 1; l >= 0; --l) {
+            if (n_links[l] <= 0) continue;
+            CombineParams cp;
+            memset(&cp, 0, sizeof cp);
+            cp.links = c->levels[l].links.as<int4>(); cp.n_links = n_links[l];
+            cp.parent_is_level0 = (l == 0);
+            cp.parent_c0 = c->c0.as<float>(); cp.parent_colour = c->levels[l].colour.as<float4>();
+            cp.child_colour = c->levels[l + 1].colour.as<float4>(); cp.mat = c->ds.mat;
+            SCU(launch_combine(cp, exact, c->stream));
+            ++*launches;
+        }
+        ResolveParams r;
+        memset(&r, 0, sizeof r);
+        r.f = fp; r.c0 = c->c0.as<float>();
+        r.chunk_py0 = ly0 / k; r.chunk_prows = std::min(rows / k, local_rows - r.chunk_py0);
+        r.fb_f32 = c->fb_f32.as<float>(); r.fb_rgba8 = c->fb_rgba8.as<uchar4>();
+        r.stats = c->stats.as<unsigned long long>();
+        SCU(launch_resolve(r, c->stream));
+        ++*launches;
+    }
+    (void)ms_nearest; (void)ms_shadow;
+    st->depth_levels = max_level_seen;
+    st->chunks = chunks;
+    st->path = 1;
+    st->ms_trace_nearest = -1.0;              // first level-0 nearest-hit launch, read after the final sync
+    // nearest-hit queries test every surface by construction (no early-out): exact host-side count;
+    // shadow queries are counted on the device (warps leave early once their filters are zero)
+    c->host_tests[0] = rays_nearest * (unsigned long long)c->ds.n_tri;
+    c->host_tests[1] = rays_nearest * (unsigned long long)c->ds.n_quad;
+    c->host_tests[2] = rays_nearest * (unsigned long long)c->ds.n_plane;
+    return RTB200_OK;
+}
+
+// rays in c->q_in0 (origins) / c->q_in1 (directions) -> c->q_out0 (order) / q_out1 (t) / q_out2 (normal)
+int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
+{
+    StreamBufs* sb = stream_bufs(c);
+    const int mode = (flags & RTB200_F_FUSED_FP) ? 2 : ((flags & RTB200_F_EXACT_FP) ? 1 : 0);
+    cudaError_t e;
+    if ((e = sb->sq0.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess || (e = sb->sq1.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess ||
+        (e = sb->hit.ensure(sizeof(float2) * (size_t)n)) != cudaSuccess) return set_cuda_error(c, e, "query scratch");
+    SCU(launch_query_pack_rays(n, c->q_in0.as<float>(), c->q_in1.as<float>(), sb->sq0.as<float4>(), sb->sq1.as<float4>(), c->stream));
+    TraceParams tp;
+    memset(&tp, 0, sizeof tp);
+    tp.s = c->ds; tp.primary = 0; tp.in_od0 = sb->sq0.as<float4>(); tp.in_od1 = sb->sq1.as<float4>();
+    tp.n_rays = n; tp.hit = sb->hit.as<float2>(); tp.mode = mode;
+    SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
+    SCU(launch_query_finish_nearest(c->ds, n, tp.in_od0, tp.in_od1, tp.hit, c->q_out0.as<int>(), c->q_out1.as<float>(),
+                                    c->q_out2.as<float>(), mode != 2, c->stream));
+    return RTB200_OK;
+}
+
+// points in c->q_in0 / light positions in c->q_in1 -> filters in c->q_out2
+int stream_query_shadow(rtb200_ctx* c, int n, uint32_t flags)
+{
+    StreamBufs* sb = stream_bufs(c);
+    const int mode = (flags & RTB200_F_FUSED_FP) ? 2 : ((flags & RTB200_F_EXACT_FP) ? 1 : 0);
+    cudaError_t e;
+    if ((e = sb->sq0.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess || (e = sb->sq1.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess ||
+        (e = sb->filter.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess) return set_cuda_error(c, e, "query scratch");
+    const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
+    if ((e = c->stats.ensure(stat_bytes)) != cudaSuccess) return set_cuda_error(c, e, "stats");
+    SCU(launch_query_pack_shadow(n, c->q_in0.as<float>(), c->q_in1.as<float>(), sb->sq0.as<float4>(), sb->sq1.as<float4>(), mode != 2, c->stream));
+    ShadowParams sp;
+    memset(&sp, 0, sizeof sp);
+    sp.s = c->ds; sp.sq0 = sb->sq0.as<float4>(); sp.sq1 = sb->sq1.as<float4>(); sp.n_queries = n;
+    sp.filter = sb->filter.as<float4>(); sp.stats = c->stats.as<unsigned long long>(); sp.mode = mode;
+    SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+    SCU(launch_query_unpack_filter(n, sp.filter, c->q_out2.as<float>(), c->stream));
+    return RTB200_OK;
+}
+
+} // namespace rtb
 
 extern "C" int rtb200_build_bvh(rtb200_ctx* ctx)
 {

@@ -1,0 +1,91 @@
+// rt_stream.cuh -- parameter blocks of the streamed (tiled brute-force) wavefront kernels.
+#pragma once
+#include "rt_kernels.cuh"
+
+namespace rtb {
+
+#define ST_THREADS   256           // threads per CTA
+#define ST_RPT       4             // rays per thread (ILP + amortised shared-memory reads)
+#define ST_BLOCK_RAYS (ST_THREADS * ST_RPT)
+#define ST_TILE      256           // triangles per shared-memory tile (12 KB)
+#define ST_STAGES    2
+#define ST_SIDE_MAX  16384         // bytes of quadric + plane records kept in shared memory
+
+// nearest hit of every ray of one wavefront level against ALL surfaces (tiled brute force)
+struct TraceParams {
+    FrameParams f;
+    DeviceScene s;
+    int   primary;                 // 1: rays generated from the sample lattice (level 0)
+    int   chunk_ly0, chunk_rows, local_LH;
+    const float4* in_od0;          // level >= 1 / query rays: o.xyz | energy
+    const float4* in_od1;          //                          d.xyz | ior
+    int   n_rays;
+    float2* hit;                   // t | order (int bits, -1 = miss), indexed like the rays
+    int   mode;                    // 0: FMA culling filter + reference-rounded survivors (default)
+                                   // 1: no filter, reference sequence for every test (EXACT_FP)
+                                   // 2: filter + fused survivors (FUSED_FP)
+};
+
+// shade-A: hit point, normal, shadow queries of the facing lights, children
+struct ShadeAParams {
+    FrameParams f;
+    DeviceScene s;
+    int   level;
+    int   chunk_ly0, chunk_rows, local_LH;
+    const float4* in_od0;
+    const float4* in_od1;
+    int   n_rays;
+    const float2* hit;
+    float4* hitP;                  // P.xyz | t
+    float4* hitN;                  // N.xyz | order (int bits, -1 = miss)
+    int*    q_base;                // first shadow query of the ray
+    float4* sq0;                   // P.xyz | dist
+    float4* sq1;                   // L.xyz (normalised) | 0
+    unsigned int* sq_count;
+    float4* out_od0;
+    float4* out_od1;
+    unsigned int* out_count;
+    int4*   links;
+    unsigned int* link_count;
+    unsigned long long* stats;
+    int   exact;                   // rounding of everything that is kept (1 unless FUSED_FP)
+};
+
+struct ShadowParams {
+    DeviceScene s;
+    const float4* sq0;
+    const float4* sq1;
+    int   n_queries;
+    float4* filter;                // r g b | 0 per query
+    unsigned long long* stats;
+    int   mode;
+};
+
+// shade-B: ambient + per-light diffuse/Phong with the shadow filters, in light order
+struct ShadeBParams {
+    FrameParams f;
+    DeviceScene s;
+    int   level;
+    int   chunk_ly0, chunk_rows, local_LH;
+    const float4* in_od1;          // ray directions (level >= 1)
+    int   n_rays;
+    const float4* hitP;
+    const float4* hitN;
+    const int*    q_base;
+    const float4* filter;
+    float*  c0;                    // level 0 colours (3 floats per sample)
+    float4* colour;                // level >= 1 colours
+    int   exact;
+};
+
+cudaError_t launch_trace_nearest(const TraceParams& p, int sm_count, cudaStream_t st);
+cudaError_t launch_shade_a(const ShadeAParams& p, cudaStream_t st);
+cudaError_t launch_trace_shadow(const ShadowParams& p, int sm_count, cudaStream_t st);
+cudaError_t launch_shade_b(const ShadeBParams& p, cudaStream_t st);
+cudaError_t launch_query_pack_rays(int n, const float* o3, const float* d3, float4* od0, float4* od1, cudaStream_t st);
+cudaError_t launch_query_finish_nearest(const DeviceScene& s, int n, const float4* od0, const float4* od1, const float2* hit,
+                                        int* out_order, float* out_t, float* out_n3, bool exact, cudaStream_t st);
+cudaError_t launch_query_pack_shadow(int n, const float* p3, const float* l3, float4* sq0, float4* sq1, bool exact, cudaStream_t st);
+cudaError_t launch_query_unpack_filter(int n, const float4* filter, float* out3, cudaStream_t st);
+
+} // namespace rtb

@@ -1,0 +1,674 @@
+// rt_trace.cu -- the brute-force intersection kernels of the streamed path (large scenes).
+//
+// Every ray of a wavefront level is tested against EVERY surface (this is the reference's
+// algorithm: Scene.cpp:1710-1715 and :1850-1858 are linear scans).  What makes it fast:
+//   * triangles stream through shared memory in 12 KB tiles (256 x 48 B: p0|order, e1|material,
+//     e2) fetched by 1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx), double
+//     buffered; every warp reads a triangle as three broadcast LDS.128;
+//   * a persistent CTA holds 1024 rays (256 threads x 4 rays in registers) so one staged
+//     triangle serves 4 rays per thread (ILP) and 1024 rays per CTA (arithmetic intensity
+//     ~ 1000 x 46 flop per 48 B: HBM/L2 are irrelevant, the FMA pipe is the roof);
+//   * per (ray, triangle) a two-phase CULLING FILTER in fused arithmetic: phase 1 computes
+//     det and u only (one MUFU.RCP, no division) and a warp vote skips the rest of the test
+//     when no lane of the warp can hit; phase 2 finishes v and t for the survivors of phase 1.
+//     The filter is conservative (margins far above the rounding differences); only rays that
+//     pass it run the reference's own rounding sequence (triangle_t<true>), so the accepted
+//     distances are bit-identical to the CPU renderer.
+//   * shadow queries leave at warp granularity once every ray of the warp holds a zero filter.
+#include "rt_stream.cuh"
+#include "rt_tma.cuh"
+
+namespace rtb {
+
+#define FULL_MASK 0xffffffffu
+// culling margins (see DESIGN.md "conservative filter"): relative 1e-3, far above the
+// ~1e-6 relative differences between fused and unfused evaluation
+#define CULL_DET   0.0099f         // |det| >= EPSILON, with 1 % slack
+#define CULL_UV    0.001f
+#define CULL_TREL  1.001f
+#define CULL_TABS  1.0e-3f
+
+RT_DEV float rcp_approx(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+struct TraceSmem {
+    TriRec tile[ST_STAGES][ST_TILE];                 // 24 KB
+    unsigned char side[ST_SIDE_MAX];                 // quadric + plane records (when they fit)
+    uint64_t full[ST_STAGES];
+};
+
+// Phase-2 of the filter + exact evaluation for one (ray, triangle); returns the reference
+// distance or -1.  `tmin`/`tmax` bound the distances that could still matter to the caller.
+template <int MODE>
+RT_DEV float triangle_survivor(V3 o, V3 d, V3 p0, V3 e1, V3 e2, float tmax)
+{
+    // fused re-evaluation of the whole test with margins
+    const V3 P = cross3<false>(d, e2);
+    const float det = dot3<false>(e1, P);
+    const float rd = rcp_approx(det);
+    const V3 S = sub3<false>(o, p0);
+    const float u = dot3<false>(S, P) * rd;
+    const V3 Q = cross3<false>(S, e1);
+    const float v = dot3<false>(d, Q) * rd;
+    const float t = dot3<false>(e2, Q) * rd;
+    if (!(v >= -CULL_UV && u + v <= 1.0f + CULL_UV && t > RT_EPS * 0.99f && t < tmax)) return -1.0f;
+    return MODE == 2 ? triangle_t<false>(o, d, p0, e1, e2) : triangle_t<true>(o, d, p0, e1, e2);
+}
+
+// ---------------------------------------------------------------------------------------
+// Nearest hit.  One CTA = 1024 rays.  PRIMARY: the rays are a 32x32 tile of the sample lattice
+// (warp = 16x8 pixels, thread = a 2x2 quad) generated on the fly; otherwise 1024 consecutive
+// queue entries.
+// ---------------------------------------------------------------------------------------
+template <int MODE, bool PRIMARY>
+__global__ void __launch_bounds__(ST_THREADS, 2)
+k_trace_nearest(const __grid_constant__ TraceParams p)
+{
+    __shared__ __align__(128) TraceSmem sm;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const DeviceScene& s = p.s;
+    const int n_tiles = s.n_tri_padded / ST_TILE;
+    const int side_bytes = (int)(sizeof(QuadRec) * s.n_quad + sizeof(PlaneRec) * s.n_plane);
+    const bool side_in_smem = side_bytes <= ST_SIDE_MAX;
+
+    if (tid == 0) {
+        for (int i = 0; i < ST_STAGES; ++i) mbar_init(&sm.full[i], 1);
+        mbar_fence_init();
+    }
+    if (side_in_smem) {                              // quadrics then planes, contiguous in the scene buffer
+        const float4* src = reinterpret_cast<const float4*>(s.quad);
+        float4* dst = reinterpret_cast<float4*>(sm.side);
+        for (int i = tid; i < side_bytes / 16; i += ST_THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    const QuadRec*  quads  = side_in_smem ? reinterpret_cast<const QuadRec*>(sm.side) : s.quad;
+    const PlaneRec* planes = side_in_smem ? reinterpret_cast<const PlaneRec*>(sm.side + sizeof(QuadRec) * s.n_quad) : s.plane;
+
+    const int tiles_x = (p.f.LW + 31) >> 5;
+    const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + 31) >> 5) : (p.n_rays + ST_BLOCK_RAYS - 1) / ST_BLOCK_RAYS;
+    uint32_t phase_bits = 0;                         // parity of each stage's barrier
+
+    for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+        // ---- this thread's 4 rays ------------------------------------------------------------
+        V3 o[ST_RPT], d[ST_RPT];
+        float best_t[ST_RPT], tlim[ST_RPT];
+        int best_id[ST_RPT], slot[ST_RPT];
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r) {
+            bool valid;
+            if (PRIMARY) {
+                const int tx = blk % tiles_x, ty = blk / tiles_x;
+                const int lx = (tx << 5) + ((warp & 1) << 4) + ((lane & 7) << 1) + (r & 1);
+                const int cy = (ty << 5) + ((warp >> 1) << 3) + ((lane >> 3) << 1) + (r >> 1);
+                const int ly = p.chunk_ly0 + cy;
+                valid = lx < p.f.LW && cy < p.chunk_rows && ly < p.local_LH;
+                slot[r] = valid ? cy * p.f.LW + lx : -1;
+                primary_ray<(MODE != 2)>(p.f, valid ? lx : 0, valid ? global_lattice_row(p.f, ly) : 0, o[r], d[r]);
+            } else {
+                const int i = blk * ST_BLOCK_RAYS + r * ST_THREADS + tid;
+                valid = i < p.n_rays;
+                slot[r] = valid ? i : -1;
+                const float4 a = valid ? p.in_od0[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 b = valid ? p.in_od1[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+                o[r] = f4_xyz(a); d[r] = f4_xyz(b);
+            }
+            if (!valid) d[r] = mk3(0.f, 0.f, 0.f);     // zero direction: det = 0, nothing can hit
+            best_t[r] = -1.0f; best_id[r] = -1; tlim[r] = 3.0e38f;
+        }
+
+        // ---- triangles: double-buffered TMA tiles ---------------------------------------------
+        if (tid == 0 && n_tiles > 0) {
+            mbar_arrive_expect_tx(&sm.full[0], (uint32_t)sizeof(TriRec) * ST_TILE);
+            tma_load_1d(sm.tile[0], s.tri, (uint32_t)sizeof(TriRec) * ST_TILE, &sm.full[0]);
+        }
+        for (int t = 0; t < n_tiles; ++t) {
+            const int st = t & (ST_STAGES - 1);
+            if (tid == 0 && t + 1 < n_tiles) {       // the other stage was released by the barrier below
+                const int nx = (t + 1) & (ST_STAGES - 1);
+                mbar_arrive_expect_tx(&sm.full[nx], (uint32_t)sizeof(TriRec) * ST_TILE);
+                tma_load_1d(sm.tile[nx], s.tri + (size_t)(t + 1) * ST_TILE, (uint32_t)sizeof(TriRec) * ST_TILE, &sm.full[nx]);
+            }
+            mbar_wait(&sm.full[st], (phase_bits >> st) & 1u);
+            phase_bits ^= (1u << st);
+            const TriRec* __restrict__ tile = sm.tile[st];
+
+            #pragma unroll 2
+            for (int j = 0; j < ST_TILE; ++j) {
+                const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
+                const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
+                if (MODE == 1) {                     // no filter: the reference sequence for every test
+                    #pragma unroll
+                    for (int r = 0; r < ST_RPT; ++r) {
+                        const float tt = triangle_t<true>(o[r], d[r], p0, e1, e2);
+                        if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f)) { best_t[r] = tt; best_id[r] = __float_as_int(ra.w); }
+                    }
+                } else {
+                    bool cand[ST_RPT];
+                    bool any = false;
+                    #pragma unroll
+                    for (int r = 0; r < ST_RPT; ++r) {       // phase 1: det and u, fused, no division
+                        const V3 P = cross3<false>(d[r], e2);
+                        const float det = dot3<false>(e1, P);
+                        const V3 S = sub3<false>(o[r], p0);
+                        const float u = dot3<false>(S, P) * rcp_approx(det);
+                        cand[r] = fabsf(det) >= CULL_DET && fabsf(u - 0.5f) <= 0.5f + CULL_UV;
+                        any |= cand[r];
+                    }
+                    if (__any_sync(FULL_MASK, any)) {
+                        #pragma unroll
+                        for (int r = 0; r < ST_RPT; ++r) {
+                            if (cand[r]) {
+                                const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, tlim[r]);
+                                if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f)) {
+                                    best_t[r] = tt; best_id[r] = __float_as_int(ra.w);
+                                    tlim[r] = fmaf(tt, CULL_TREL, CULL_TABS);
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+            __syncthreads();                         // everyone is done with this stage
+        }
+
+        // ---- quadrics and planes (reference sequence; ties go to the lower insertion order) ----
+        for (int q = 0; q < s.n_quad; ++q) {
+            const float4 q0 = quads[q].q0, q1 = quads[q].q1, q2 = quads[q].q2;
+            const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+            const int ord = __float_as_int(q0.w);
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) {
+                bool lin;
+                const float tt = MODE == 2 ? quadric_t<false>(o[r], d[r], Q, lin) : quadric_t<true>(o[r], d[r], Q, lin);
+                if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f || (tt == best_t[r] && ord < best_id[r]))) { best_t[r] = tt; best_id[r] = ord; }
+            }
+        }
+        for (int q = 0; q < s.n_plane; ++q) {
+            const float4 nc = planes[q].nc;
+            const int ord = planes[q].order;
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) {
+                const float tt = MODE == 2 ? plane_t<false>(o[r], d[r], f4_xyz(nc), nc.w) : plane_t<true>(o[r], d[r], f4_xyz(nc), nc.w);
+                if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f || (tt == best_t[r] && ord < best_id[r]))) { best_t[r] = tt; best_id[r] = ord; }
+            }
+        }
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r)
+            if (slot[r] >= 0) p.hit[slot[r]] = make_float2(best_t[r], __int_as_float(best_id[r]));
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Shadow filter (Scene.cpp:1842-1861): product of colour*kt over every surface hit strictly
+// between EPSILON and the light.  One CTA = 1024 consecutive shadow queries.
+// ---------------------------------------------------------------------------------------
+template <int MODE>
+RT_DEV void filter_mul(const MatRec* __restrict__ mat, int m, float& fr, float& fg, float& fb)
+{
+    const float4 m0 = mat[m].m0;
+    const float kt = mat[m].m2.x;
+    fr = __fmul_rn(fr, __fmul_rn(m0.x, kt));
+    fg = __fmul_rn(fg, __fmul_rn(m0.y, kt));
+    fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(ST_THREADS, 2)
+k_trace_shadow(const __grid_constant__ ShadowParams p)
+{
+    __shared__ __align__(128) TraceSmem sm;
+    const int tid = threadIdx.x;
+    const DeviceScene& s = p.s;
+    const int n_tiles = s.n_tri_padded / ST_TILE;
+    const int side_bytes = (int)(sizeof(QuadRec) * s.n_quad + sizeof(PlaneRec) * s.n_plane);
+    const bool side_in_smem = side_bytes <= ST_SIDE_MAX;
+
+    if (tid == 0) {
+        for (int i = 0; i < ST_STAGES; ++i) mbar_init(&sm.full[i], 1);
+        mbar_fence_init();
+    }
+    if (side_in_smem) {
+        const float4* src = reinterpret_cast<const float4*>(s.quad);
+        float4* dst = reinterpret_cast<float4*>(sm.side);
+        for (int i = tid; i < side_bytes / 16; i += ST_THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    const QuadRec*  quads  = side_in_smem ? reinterpret_cast<const QuadRec*>(sm.side) : s.quad;
+    const PlaneRec* planes = side_in_smem ? reinterpret_cast<const PlaneRec*>(sm.side + sizeof(QuadRec) * s.n_quad) : s.plane;
+
+    const int n_blocks = (p.n_queries + ST_BLOCK_RAYS - 1) / ST_BLOCK_RAYS;
+    uint32_t phase_bits = 0;
+    unsigned long long tests_tri = 0, tests_side_q = 0, tests_side_p = 0;
+
+    for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+        V3 o[ST_RPT], d[ST_RPT];
+        float dist[ST_RPT], tlim[ST_RPT], fr[ST_RPT], fg[ST_RPT], fb[ST_RPT];
+        int slot[ST_RPT];
+        int n_valid = 0;
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r) {
+            const int i = blk * ST_BLOCK_RAYS + r * ST_THREADS + tid;
+            const bool valid = i < p.n_queries;
+            slot[r] = valid ? i : -1;
+            n_valid += valid ? 1 : 0;
+            const float4 a = valid ? p.sq0[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 b = valid ? p.sq1[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+            o[r] = f4_xyz(a); d[r] = f4_xyz(b); dist[r] = a.w;
+            tlim[r] = fmaf(a.w, CULL_TREL, CULL_TABS);
+            fr[r] = fg[r] = fb[r] = 1.0f;
+            if (!valid) { fr[r] = fg[r] = fb[r] = 0.0f; }        // counts as finished
+        }
+        bool warp_done = false;
+
+        if (tid == 0 && n_tiles > 0) {
+            mbar_arrive_expect_tx(&sm.full[0], (uint32_t)sizeof(TriRec) * ST_TILE);
+            tma_load_1d(sm.tile[0], s.tri, (uint32_t)sizeof(TriRec) * ST_TILE, &sm.full[0]);
+        }
+        for (int t = 0; t < n_tiles; ++t) {
+            const int st = t & (ST_STAGES - 1);
+            if (tid == 0 && t + 1 < n_tiles) {
+                const int nx = (t + 1) & (ST_STAGES - 1);
+                mbar_arrive_expect_tx(&sm.full[nx], (uint32_t)sizeof(TriRec) * ST_TILE);
+                tma_load_1d(sm.tile[nx], s.tri + (size_t)(t + 1) * ST_TILE, (uint32_t)sizeof(TriRec) * ST_TILE, &sm.full[nx]);
+            }
+            mbar_wait(&sm.full[st], (phase_bits >> st) & 1u);
+            phase_bits ^= (1u << st);
+            const TriRec* __restrict__ tile = sm.tile[st];
+
+            if (!warp_done) {
+                const int real = min(ST_TILE, s.n_tri - t * ST_TILE);
+                tests_tri += (unsigned long long)n_valid * (unsigned long long)real;
+                #pragma unroll 2
+                for (int j = 0; j < ST_TILE; ++j) {
+                    const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
+                    const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
+                    if (MODE == 1) {
+                        #pragma unroll
+                        for (int r = 0; r < ST_RPT; ++r) {
+                            const float tt = triangle_t<true>(o[r], d[r], p0, e1, e2);
+                            if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(rb.w), fr[r], fg[r], fb[r]);
+                        }
+                    } else {
+                        bool cand[ST_RPT];
+                        bool any = false;
+                        #pragma unroll
+                        for (int r = 0; r < ST_RPT; ++r) {
+                            const V3 P = cross3<false>(d[r], e2);
+                            const float det = dot3<false>(e1, P);
+                            const V3 S = sub3<false>(o[r], p0);
+                            const float u = dot3<false>(S, P) * rcp_approx(det);
+                            cand[r] = fabsf(det) >= CULL_DET && fabsf(u - 0.5f) <= 0.5f + CULL_UV;
+                            any |= cand[r];
+                        }
+                        if (__any_sync(FULL_MASK, any)) {
+                            #pragma unroll
+                            for (int r = 0; r < ST_RPT; ++r) {
+                                if (cand[r] && slot[r] >= 0) {
+                                    const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, tlim[r]);
+                                    if (tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(rb.w), fr[r], fg[r], fb[r]);
+                                }
+                            }
+                        }
+                    }
+                }
+                bool done = true;
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) done = done && (fr[r] == 0.f && fg[r] == 0.f && fb[r] == 0.f);
+                warp_done = __all_sync(FULL_MASK, done);     // 0 * finite stays 0: the warp may stop testing
+            }
+            __syncthreads();
+        }
+
+        if (!warp_done) {
+            tests_side_q += (unsigned long long)n_valid * (unsigned long long)s.n_quad;
+            tests_side_p += (unsigned long long)n_valid * (unsigned long long)s.n_plane;
+            for (int q = 0; q < s.n_quad; ++q) {
+                const float4 q0 = quads[q].q0, q1 = quads[q].q1, q2 = quads[q].q2;
+                const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) {
+                    bool lin;
+                    const float tt = MODE == 2 ? quadric_t<false>(o[r], d[r], Q, lin) : quadric_t<true>(o[r], d[r], Q, lin);
+                    if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(q1.w), fr[r], fg[r], fb[r]);
+                }
+            }
+            for (int q = 0; q < s.n_plane; ++q) {
+                const float4 nc = planes[q].nc;
+                const int m = planes[q].material;
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) {
+                    const float tt = MODE == 2 ? plane_t<false>(o[r], d[r], f4_xyz(nc), nc.w) : plane_t<true>(o[r], d[r], f4_xyz(nc), nc.w);
+                    if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, m, fr[r], fg[r], fb[r]);
+                }
+            }
+        }
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r)
+            if (slot[r] >= 0) p.filter[slot[r]] = make_float4(fr[r], fg[r], fb[r], 0.f);
+    }
+
+    // ---- statistics: tests entered (per thread -> warp -> one atomic per warp) ----------------
+    for (int off = 16; off > 0; off >>= 1) {
+        tests_tri += __shfl_xor_sync(FULL_MASK, tests_tri, off);
+        tests_side_q += __shfl_xor_sync(FULL_MASK, tests_side_q, off);
+        tests_side_p += __shfl_xor_sync(FULL_MASK, tests_side_p, off);
+    }
+    if ((tid & 31) == 0) {
+        unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+        if (tests_tri) atomicAdd(&st[ST_TEST_TRI], tests_tri);
+        if (tests_side_q) atomicAdd(&st[ST_TEST_QUAD], tests_side_q);
+        if (tests_side_p) atomicAdd(&st[ST_TEST_PLANE], tests_side_p);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// shade-A: per ray -- hit point and normal (as CIntersection would carry them), one shadow
+// query per light facing the stored normal (Scene.cpp:1751-1759), reflected / refracted
+// children (Scene.cpp:1779-1823).  Queries of one ray are contiguous, in light order.
+// ---------------------------------------------------------------------------------------
+template <bool E>
+RT_DEV void level_ray(const FrameParams& f, int level, int chunk_ly0, int i, const float4* od0, const float4* od1,
+                      V3& o, V3& d, float& energy, float& ior)
+{
+    if (level == 0) {
+        const int x = i % f.LW, cy = i / f.LW;
+        primary_ray<E>(f, x, global_lattice_row(f, chunk_ly0 + cy), o, d);
+        energy = 1.0f; ior = 1.0f;
+    } else {
+        const float4 a = od0[i], b = od1[i];
+        o = f4_xyz(a); d = f4_xyz(b); energy = a.w; ior = b.w;
+    }
+}
+
+template <bool E>
+__global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAParams p)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const bool valid = i < p.n_rays;
+    const DeviceScene& s = p.s;
+    V3 o = mk3(0.f, 0.f, 0.f), d = o, P = o, N = o;
+    float energy = 0.f, ior = 0.f, t = -1.f;
+    int id = -1, mat = 0;
+    if (valid) {
+        level_ray<E>(p.f, p.level, p.chunk_ly0, i, p.in_od0, p.in_od1, o, d, energy, ior);
+        const float2 h = p.hit[i];
+        t = h.x; id = __float_as_int(h.y);
+    }
+    const bool hit = valid && id >= 0;
+    float kr = 0.f, kt = 0.f, mior = 0.f;
+    if (hit) {
+        const float4 r0 = s.surf[id].r0, r1 = s.surf[id].r1;
+        const int type = __float_as_int(r0.w);
+        mat = __float_as_int(r1.w);
+        if (type == SURF_TRIANGLE) N = f4_xyz(s.surf[id].r3);
+        else if (type == SURF_PLANE) N = f4_xyz(r0);
+        else {
+            const float4 r2 = s.surf[id].r2;
+            const Quadric Q = { r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r2.x, r2.y, r2.z, r2.w };
+            bool lin;
+            (void)quadric_t<E>(o, d, Q, lin);              // which branch produced t
+            N = quadric_normal<E>(o, d, t, Q, lin);
+        }
+        P = axpy3<E>(o, d, t);
+        const float4 m1 = s.mat[mat].m1, m2 = s.mat[mat].m2;
+        kr = m1.w; kt = m2.x; mior = m2.y;
+    }
+    // ---- shadow queries ---------------------------------------------------------------------
+    int n_face = 0;
+    if (hit)
+        for (int l = 0; l < s.rl.n_light; ++l) {
+            const V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
+            n_face += dot3<E>(Ld, N) > 0.f ? 1 : 0;
+        }
+    int incl = n_face;
+    for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(FULL_MASK, incl, off); if (lane >= off) incl += v; }
+    unsigned int base = 0;
+    const int total = __shfl_sync(FULL_MASK, incl, 31);
+    if (lane == 31 && total > 0) base = atomicAdd(p.sq_count, (unsigned int)total);
+    base = __shfl_sync(FULL_MASK, base, 31);
+    int q = (int)base + incl - n_face;
+    if (valid) {
+        p.q_base[i] = q;
+        p.hitP[i] = make_float4(P.x, P.y, P.z, t);
+        p.hitN[i] = make_float4(N.x, N.y, N.z, __int_as_float(id));
+    }
+    if (hit)
+        for (int l = 0; l < s.rl.n_light; ++l) {
+            V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
+            if (dot3<E>(Ld, N) > 0.f) {
+                const float dist = norm3<E>(Ld);             // Scene.cpp:1847-1848
+                Ld = scale3<E>(Ld, FP<E>::rcp(dist));
+                p.sq0[q] = make_float4(P.x, P.y, P.z, dist);
+                p.sq1[q] = make_float4(Ld.x, Ld.y, Ld.z, 0.f);
+                ++q;
+            }
+        }
+    // ---- children --------------------------------------------------------------------------------
+    bool want_refl = false, want_refr = false;
+    float e_refl = 0.f, e_refr = 0.f;
+    if (hit && p.f.secondary && p.level < p.f.max_bounces) {
+        e_refl = FP<E>::mul(kr, energy); e_refr = FP<E>::mul(kt, energy);
+        want_refl = e_refl > p.f.min_energy; want_refr = e_refr > p.f.min_energy;
+    }
+    const unsigned int m_refl = __ballot_sync(FULL_MASK, want_refl), m_refr = __ballot_sync(FULL_MASK, want_refr);
+    if (m_refl | m_refr) {
+        const unsigned int n_refl = __popc(m_refl), n_refr = __popc(m_refr), m_any = m_refl | m_refr;
+        unsigned int cbase = 0, lbase = 0;
+        if (lane == 0) {
+            cbase = atomicAdd(p.out_count, n_refl + n_refr);
+            lbase = atomicAdd(p.link_count, (unsigned int)__popc(m_any));
+            unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+            if (n_refl) atomicAdd(&st[ST_REFLECT], (unsigned long long)n_refl);
+            if (n_refr) atomicAdd(&st[ST_REFRACT], (unsigned long long)n_refr);
+        }
+        cbase = __shfl_sync(FULL_MASK, cbase, 0); lbase = __shfl_sync(FULL_MASK, lbase, 0);
+        const unsigned int below = (1u << lane) - 1u;
+        int s_refl = -1, s_refr = -1;
+        if (want_refl) {
+            s_refl = (int)(cbase + __popc(m_refl & below));
+            const V3 rd = reflect3<E>(d, N);
+            p.out_od0[s_refl] = make_float4(P.x, P.y, P.z, e_refl);
+            p.out_od1[s_refl] = make_float4(rd.x, rd.y, rd.z, 0.0f);
+        }
+        if (want_refr) {
+            s_refr = (int)(cbase + n_refl + __popc(m_refr & below));
+            V3 n2 = N; float ratio, nior;
+            if (ior == mior) { nior = p.f.scene_ior; ratio = FP<E>::div(mior, p.f.scene_ior); n2 = neg3(N); }
+            else             { nior = mior;          ratio = FP<E>::div(p.f.scene_ior, mior); }
+            const V3 rd = refract3<E>(d, n2, ratio);
+            p.out_od0[s_refr] = make_float4(P.x, P.y, P.z, e_refr);
+            p.out_od1[s_refr] = make_float4(rd.x, rd.y, rd.z, nior);
+        }
+        if (want_refl || want_refr) p.links[lbase + __popc(m_any & below)] = make_int4(i, s_refl, s_refr, mat);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// shade-B: the ray's own colour (Scene.cpp:1742-1776) with the shadow filters now known.
+// ---------------------------------------------------------------------------------------
+template <bool E>
+__global__ void __launch_bounds__(256) k_shade_b(const __grid_constant__ ShadeBParams p)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n_rays) return;
+    const DeviceScene& s = p.s;
+    const float4 hn = p.hitN[i];
+    const int id = __float_as_int(hn.w);
+    float cr = p.f.background[0], cg = p.f.background[1], cb = p.f.background[2];
+    if (id >= 0) {
+        const V3 N = f4_xyz(hn), P = f4_xyz(p.hitP[i]);
+        V3 d;
+        if (p.level == 0) { V3 o; primary_ray<E>(p.f, i % p.f.LW, global_lattice_row(p.f, p.chunk_ly0 + i / p.f.LW), o, d); }
+        else d = f4_xyz(p.in_od1[i]);
+        const int mat = __float_as_int(s.surf[id].r1.w);
+        const float4 m0 = s.mat[mat].m0, m1 = s.mat[mat].m1;
+        cr = FP<E>::mul(m0.x, m0.w); cg = FP<E>::mul(m0.y, m0.w); cb = FP<E>::mul(m0.z, m0.w);
+        int q = p.q_base[i];
+        for (int l = 0; l < s.rl.n_light; ++l) {
+            const float4 l0 = s.light[l].l0, l1 = s.light[l].l1;
+            V3 Ld = sub3<E>(f4_xyz(l0), P);
+            if (!(dot3<E>(Ld, N) > 0.f)) continue;
+            const float4 fl = p.filter[q++];
+            const float dist = norm3<E>(Ld);
+            Ld = scale3<E>(Ld, FP<E>::rcp(dist));
+            const float lcr = FP<E>::mul(l1.x, fl.x), lcg = FP<E>::mul(l1.y, fl.y), lcb = FP<E>::mul(l1.z, fl.z);
+            const float g = FP<E>::mul(FP<E>::mul(l0.w, m1.x), dot3<E>(N, Ld));
+            cr = FP<E>::madd(FP<E>::mul(m0.x, g), lcr, cr);
+            cg = FP<E>::madd(FP<E>::mul(m0.y, g), lcg, cg);
+            cb = FP<E>::madd(FP<E>::mul(m0.z, g), lcb, cb);
+            const V3 R = reflect3<E>(Ld, N);
+            const float ps = dot3<E>(R, d);
+            if (ps > 0.f) {
+                const float ph = FP<E>::mul(FP<E>::mul(l0.w, m1.y), powf(ps, m1.z));
+                cr = FP<E>::madd(lcr, ph, cr); cg = FP<E>::madd(lcg, ph, cg); cb = FP<E>::madd(lcb, ph, cb);
+            }
+        }
+    }
+    if (p.level == 0) { float* c = p.c0 + 3 * (size_t)i; c[0] = cr; c[1] = cg; c[2] = cb; }
+    else p.colour[i] = make_float4(cr, cg, cb, 0.f);
+}
+
+// ---------------------------------------------------------------------------------------
+// Ray-level query plumbing (rtb200_trace_nearest / rtb200_trace_shadow through the tiled kernels)
+// ---------------------------------------------------------------------------------------
+__global__ void k_query_pack_rays(int n, const float* o3, const float* d3, float4* od0, float4* od1)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    od0[i] = make_float4(o3[3 * i], o3[3 * i + 1], o3[3 * i + 2], 1.0f);
+    od1[i] = make_float4(d3[3 * i], d3[3 * i + 1], d3[3 * i + 2], 1.0f);
+}
+
+template <bool E>
+__global__ void k_query_finish_nearest(DeviceScene s, int n, const float4* od0, const float4* od1, const float2* hit,
+                                       int* out_order, float* out_t, float* out_n3)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float2 h = hit[i];
+    const int id = __float_as_int(h.y);
+    V3 N = mk3(0.f, 0.f, 0.f);
+    if (id >= 0) {
+        const V3 o = f4_xyz(od0[i]), d = f4_xyz(od1[i]);
+        const float4 r0 = s.surf[id].r0, r1 = s.surf[id].r1;
+        const int type = __float_as_int(r0.w);
+        if (type == SURF_TRIANGLE) N = f4_xyz(s.surf[id].r3);
+        else if (type == SURF_PLANE) N = f4_xyz(r0);
+        else {
+            const float4 r2 = s.surf[id].r2;
+            const Quadric Q = { r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r2.x, r2.y, r2.z, r2.w };
+            bool lin;
+            (void)quadric_t<E>(o, d, Q, lin);
+            N = quadric_normal<E>(o, d, h.x, Q, lin);
+        }
+    }
+    out_order[i] = id; out_t[i] = h.x;
+    out_n3[3 * i] = N.x; out_n3[3 * i + 1] = N.y; out_n3[3 * i + 2] = N.z;
+}
+
+template <bool E>
+__global__ void k_query_pack_shadow(int n, const float* p3, const float* l3, float4* sq0, float4* sq1)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 P = ld3(p3 + 3 * (size_t)i);
+    V3 Ld = sub3<E>(ld3(l3 + 3 * (size_t)i), P);
+    const float dist = norm3<E>(Ld);
+    Ld = scale3<E>(Ld, FP<E>::rcp(dist));
+    sq0[i] = make_float4(P.x, P.y, P.z, dist);
+    sq1[i] = make_float4(Ld.x, Ld.y, Ld.z, 0.f);
+}
+
+__global__ void k_query_unpack_filter(int n, const float4* filter, float* out3)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 f = filter[i];
+    out3[3 * i] = f.x; out3[3 * i + 1] = f.y; out3[3 * i + 2] = f.z;
+}
+
+cudaError_t launch_query_pack_rays(int n, const float* o3, const float* d3, float4* od0, float4* od1, cudaStream_t st)
+{
+    k_query_pack_rays<<<(n + 255) / 256, 256, 0, st>>>(n, o3, d3, od0, od1);
+    return cudaGetLastError();
+}
+cudaError_t launch_query_finish_nearest(const DeviceScene& s, int n, const float4* od0, const float4* od1, const float2* hit,
+                                        int* out_order, float* out_t, float* out_n3, bool exact, cudaStream_t st)
+{
+    if (exact) k_query_finish_nearest<true><<<(n + 255) / 256, 256, 0, st>>>(s, n, od0, od1, hit, out_order, out_t, out_n3);
+    else       k_query_finish_nearest<false><<<(n + 255) / 256, 256, 0, st>>>(s, n, od0, od1, hit, out_order, out_t, out_n3);
+    return cudaGetLastError();
+}
+cudaError_t launch_query_pack_shadow(int n, const float* p3, const float* l3, float4* sq0, float4* sq1, bool exact, cudaStream_t st)
+{
+    if (exact) k_query_pack_shadow<true><<<(n + 255) / 256, 256, 0, st>>>(n, p3, l3, sq0, sq1);
+    else       k_query_pack_shadow<false><<<(n + 255) / 256, 256, 0, st>>>(n, p3, l3, sq0, sq1);
+    return cudaGetLastError();
+}
+cudaError_t launch_query_unpack_filter(int n, const float4* filter, float* out3, cudaStream_t st)
+{
+    k_query_unpack_filter<<<(n + 255) / 256, 256, 0, st>>>(n, filter, out3);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------
+template <int MODE, bool PRIMARY>
+static cudaError_t launch_nearest_t(const TraceParams& p, int blocks, cudaStream_t st)
+{
+    k_trace_nearest<MODE, PRIMARY><<<blocks, ST_THREADS, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace_nearest(const TraceParams& p, int sm_count, cudaStream_t st)
+{
+    const int tiles_x = (p.f.LW + 31) / 32;
+    const int n_blocks = p.primary ? tiles_x * ((p.chunk_rows + 31) / 32) : (p.n_rays + ST_BLOCK_RAYS - 1) / ST_BLOCK_RAYS;
+    if (n_blocks <= 0) return cudaSuccess;
+    const int blocks = n_blocks < 2 * sm_count ? n_blocks : 2 * sm_count;      // persistent: 2 CTAs per SM
+    if (p.primary) {
+        if (p.mode == 1) return launch_nearest_t<1, true>(p, blocks, st);
+        if (p.mode == 2) return launch_nearest_t<2, true>(p, blocks, st);
+        return launch_nearest_t<0, true>(p, blocks, st);
+    }
+    if (p.mode == 1) return launch_nearest_t<1, false>(p, blocks, st);
+    if (p.mode == 2) return launch_nearest_t<2, false>(p, blocks, st);
+    return launch_nearest_t<0, false>(p, blocks, st);
+}
+
+cudaError_t launch_trace_shadow(const ShadowParams& p, int sm_count, cudaStream_t st)
+{
+    const int n_blocks = (p.n_queries + ST_BLOCK_RAYS - 1) / ST_BLOCK_RAYS;
+    if (n_blocks <= 0) return cudaSuccess;
+    const int blocks = n_blocks < 2 * sm_count ? n_blocks : 2 * sm_count;
+    if (p.mode == 1) k_trace_shadow<1><<<blocks, ST_THREADS, 0, st>>>(p);
+    else if (p.mode == 2) k_trace_shadow<2><<<blocks, ST_THREADS, 0, st>>>(p);
+    else k_trace_shadow<0><<<blocks, ST_THREADS, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shade_a(const ShadeAParams& p, cudaStream_t st)
+{
+    if (p.n_rays <= 0) return cudaSuccess;
+    const int blocks = (p.n_rays + 255) / 256;
+    if (p.exact) k_shade_a<true><<<blocks, 256, 0, st>>>(p);
+    else         k_shade_a<false><<<blocks, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shade_b(const ShadeBParams& p, cudaStream_t st)
+{
+    if (p.n_rays <= 0) return cudaSuccess;
+    const int blocks = (p.n_rays + 255) / 256;
+    if (p.exact) k_shade_b<true><<<blocks, 256, 0, st>>>(p);
+    else         k_shade_b<false><<<blocks, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+} // namespace rtb

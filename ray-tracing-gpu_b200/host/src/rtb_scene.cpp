@@ -381,6 +381,22 @@ int rtscene_render(int W, int H, int spp_grid, unsigned int flags, float* out_rg
     return 0;
 }
 
+// Camera block (basis, field of view) the host classes derive for a camera given through the
+// public setters -- used by the synthetic-scene generators so that every camera goes through
+// CScene::InitialiserCamera.
+int rtscene_camera(const float* pos, const float* look, const float* up, int W, int H, rtb200_frame* out)
+{
+    CScene::LibererInstance();
+    CScene* s = CScene::ObtenirInstance();
+    s->AjusterPositionCamera(CVecteur3(pos[0], pos[1], pos[2]));
+    s->AjusterPointViseCamera(CVecteur3(look[0], look[1], look[2]));
+    s->AjusterVecteurUpCamera(CVecteur3(up[0], up[1], up[2]));
+    s->AjusterResolution(W, H);
+    *out = s->ObtenirSceneEmballee().cadre;
+    CScene::LibererInstance();
+    return 0;
+}
+
 void rtscene_free(void)
 {
     CScene::LibererInstance();

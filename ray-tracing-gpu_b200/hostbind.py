@@ -23,6 +23,7 @@ def lib():
         L.rtscene_pack.argtypes = [C.c_int, C.c_int, C.POINTER(abi.Scene), C.POINTER(abi.Frame)]
         L.rtscene_render.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.POINTER(abi.Stats)]
         L.rtscene_free.restype = None
+        L.rtscene_camera.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(abi.Frame)]
         _lib = L
     return _lib
 
@@ -73,3 +74,15 @@ def render_loaded(W, H, spp_grid=1, flags=0):
 
 def free():
     lib().rtscene_free()
+
+
+def camera_frame(pos, look, up):
+    """Frame dict (basis U,V,N, half_h) from CScene::InitialiserCamera for the given camera."""
+    pos, look, up = (np.ascontiguousarray(v, np.float32) for v in (pos, look, up))
+    f = abi.Frame()
+    lib().rtscene_camera(pos.ctypes.data, look.ctypes.data, up.ctypes.data, 16, 16, C.byref(f))
+    return {"cam_pos": np.array(f.cam_pos[:], np.float32), "cam_u": np.array(f.cam_u[:], np.float32),
+            "cam_v": np.array(f.cam_v[:], np.float32), "cam_n": np.array(f.cam_n[:], np.float32),
+            "half_h": np.float32(f.half_h).item(), "background": np.zeros(3, np.float32),
+            "max_bounces": 20, "min_energy": np.float32(0.01).item(), "scene_ior": 1.0,
+            "camera_pos": pos, "camera_look": look, "camera_up": up}
