@@ -165,6 +165,10 @@ int  rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* scene);
 /* Optional: GPU-built LBVH over the triangles of the current scene (Morton codes, radix sort,
  * Karras hierarchy, bottom-up refit).  Planes and quadrics stay in the brute-force side list. */
 int  rtb200_build_bvh(rtb200_ctx* ctx);
+/* Facts about the LBVH of the current scene: internal nodes, triangles, device build time (ms),
+ * the origin radius its boxes are padded for and bytes per node. */
+int  rtb200_bvh_info(rtb200_ctx* ctx, int* n_nodes, int* n_triangles, double* build_ms,
+                     double* pad_radius, double* node_bytes);
 
 /* --- render ------------------------------------------------------------------------------- */
 /* Renders one frame.  out_rgb_f32 (W*H*3 floats) and out_rgba8 (W*H*4 bytes) are HOST

@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "librtb200.so")
 
 EXPORTS = [
     "rtb200_abi_version", "rtb200_create", "rtb200_destroy", "rtb200_error_string", "rtb200_last_error",
-    "rtb200_set_scene", "rtb200_build_bvh", "rtb200_render", "rtb200_read_frame",
+    "rtb200_set_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_read_frame",
     "rtb200_trace_nearest", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init",
     "rtb200_host_alloc", "rtb200_host_free", "rtb200_measure_fp32_peak", "rtb200_device_info",
 ]
@@ -52,6 +52,7 @@ def lib():
         L.rtb200_last_error.restype = C.c_char_p
         L.rtb200_set_scene.argtypes = [vp, C.POINTER(abi.Scene)]
         L.rtb200_build_bvh.argtypes = [vp]
+        L.rtb200_bvh_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.rtb200_render.argtypes = [vp, C.POINTER(abi.Frame), vp, vp, C.POINTER(abi.Stats)]
         L.rtb200_read_frame.argtypes = [vp, vp, vp]
         L.rtb200_trace_nearest.argtypes = [vp, C.c_int, vp, vp, C.c_uint32, vp, vp, vp]
@@ -141,6 +142,13 @@ class Renderer:
 
     def build_bvh(self):
         self._check(self.L.rtb200_build_bvh(self.h))
+        return self.bvh_info()
+
+    def bvh_info(self):
+        nn, nt = C.c_int(), C.c_int()
+        ms, rad, nb = C.c_double(), C.c_double(), C.c_double()
+        self._check(self.L.rtb200_bvh_info(self.h, C.byref(nn), C.byref(nt), C.byref(ms), C.byref(rad), C.byref(nb)))
+        return {"nodes": nn.value, "triangles": nt.value, "build_ms": ms.value, "pad_radius": rad.value, "node_bytes": nb.value}
 
     def render(self, frame, want_f32=True, want_rgba8=True, out_f32=None, out_rgba8=None):
         """Returns (float RGB [H,W,3] or None, RGBA8 [H,W,4] or None, Stats)."""

@@ -109,6 +109,7 @@ void rtb200_destroy(rtb200_ctx* ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     comm_destroy(ctx);
     stream_release(ctx);
+    bvh_release(ctx);
     ctx->scene_buf.release(); ctx->stage.release();
     ctx->c0.release(); ctx->fb_f32.release(); ctx->fb_rgba8.release(); ctx->stats.release(); ctx->counters.release();
     ctx->full_f32.release(); ctx->full_rgba8.release(); ctx->h_small.release();
@@ -177,6 +178,7 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
         (M && !s->materials) || (L && !s->lights) || (N && !M))
         return fail(ctx, RTB200_E_ARG, "null array with non-zero count");
     CU(cudaSetDevice(ctx->device));
+    bvh_invalidate(ctx);                         // an LBVH belongs to the scene it was built from
 
     const int Tpad = ((T + TILE_TRIS - 1) / TILE_TRIS) * TILE_TRIS;
     ResidentLayout rl;
@@ -541,6 +543,7 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
         st.tests_quadric = sum[ST_TEST_QUAD] + ctx->host_tests[1];
         st.tests_plane = sum[ST_TEST_PLANE] + ctx->host_tests[2];
         st.bvh_nodes_visited = sum[ST_BVH_NODES];
+        if (sum[ST_BVH_OVERFLOW]) return fail(ctx, RTB200_E_CAPACITY, "LBVH traversal stack overflow");
     }
     st.kernel_launches = launches;
     st.ms_h2d = 0.0;
@@ -581,7 +584,8 @@ extern "C" int rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* o3, con
         (e = ctx->q_out2.ensure(b3)) != cudaSuccess) return set_cuda_error(ctx, e, "query buffers");
     CU(cudaMemcpyAsync(ctx->q_in0.p, o3, b3, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->q_in1.p, d3, b3, cudaMemcpyHostToDevice, ctx->stream));
-    const bool q_stream = ((size_t)ctx->ds.rl.bytes > RESIDENT_AUTO_BYTES || (flags & RTB200_F_FORCE_STREAM)) && !(flags & RTB200_F_FORCE_RESIDENT);
+    const bool q_stream = ((size_t)ctx->ds.rl.bytes > RESIDENT_AUTO_BYTES || (flags & (RTB200_F_FORCE_STREAM | RTB200_F_USE_BVH))) && !(flags & RTB200_F_FORCE_RESIDENT);
+    if (flags & RTB200_F_USE_BVH) { const int rc = bvh_prepare(ctx, o3, n); if (rc != RTB200_OK) return rc; }
     if (q_stream) {
         const int rc = stream_query_nearest(ctx, n, flags);
         if (rc != RTB200_OK) return rc;
@@ -607,7 +611,8 @@ extern "C" int rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* p3, cons
         (e = ctx->q_out2.ensure(b3)) != cudaSuccess) return set_cuda_error(ctx, e, "query buffers");
     CU(cudaMemcpyAsync(ctx->q_in0.p, p3, b3, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemcpyAsync(ctx->q_in1.p, l3, b3, cudaMemcpyHostToDevice, ctx->stream));
-    const bool q_stream = ((size_t)ctx->ds.rl.bytes > RESIDENT_AUTO_BYTES || (flags & RTB200_F_FORCE_STREAM)) && !(flags & RTB200_F_FORCE_RESIDENT);
+    const bool q_stream = ((size_t)ctx->ds.rl.bytes > RESIDENT_AUTO_BYTES || (flags & (RTB200_F_FORCE_STREAM | RTB200_F_USE_BVH))) && !(flags & RTB200_F_FORCE_RESIDENT);
+    if (flags & RTB200_F_USE_BVH) { const int rc = bvh_prepare(ctx, p3, n); if (rc != RTB200_OK) return rc; }
     if (q_stream) {
         const int rc = stream_query_shadow(ctx, n, flags);
         if (rc != RTB200_OK) return rc;

@@ -1,0 +1,651 @@
+// rt_bvh.cu -- GPU-built LBVH over the scene's triangles and its traversal kernels.
+//
+// The reference has no acceleration structure: nearest hit and shadow filter are linear scans
+// (Scene.cpp:1710-1715, 1850-1858).  This file is the north-star's "optional GPU-built LBVH
+// for large synthetic meshes that must return the same nearest hit as the brute-force loop":
+//
+//   build  (all on the device, no host round trip except one 24-byte bounds read):
+//     scene bounds -> 63-bit Morton code of every triangle centroid -> radix sort (key, index)
+//     -> Karras 2012 binary radix tree, one thread per internal node -> bottom-up refit with
+//     one atomic counter per node.  Subtrees of <= BVH_LEAF_MAX triangles become leaves
+//     (contiguous ranges of the Morton-sorted triangle array).
+//   exactness: a leaf test IS the reference's rounding sequence (triangle_t<true>), so the BVH
+//     only has to guarantee that it never culls a triangle the linear scan would accept.  The
+//     accepted hit of CTriangle::Intersection can lie outside the geometric triangle by the
+//     rounding error of u, v and t, which grows like 1/|det| up to the reference's own
+//     threshold |det| >= EPSILON (Triangle.cpp:142).  Every triangle's box is therefore padded by
+//         pad = PADC * 2^-24 / EPSILON * R * |e1| * |e2|      (R = largest |origin - p0| possible)
+//     (first-order bound of the displacement) and nodes are culled only when the
+//     PADDED box lies strictly beyond the current best distance.  Ties resolve on (t, order)
+//     exactly like Scene.cpp:1713.
+//   traversal: one ray per thread, stack in local memory, nearer child first, both child boxes
+//     in one 64-byte node fetch; primary rays are generated on the fly in 8x4-pixel warps.
+#include <algorithm>
+#include <cfloat>
+#include <climits>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include "rt_bvh.cuh"
+#include "rt_context.h"
+
+namespace rtb {
+
+#define FULL_MASK 0xffffffffu
+#define BVH_SLACK 1.0e-5f          // relative slack of the slab test (rounding of the test itself)
+#define BVH_SHADOW_LIST 8          // transparent occluders kept per shadow ray for in-order products
+
+struct BvhState {
+    DevBuf nodes, tri_sorted, keys, keys_out, idx, idx_out, cub_tmp, parent, leaf_parent, gamma, flags, bounds;
+    int    n_tri = 0, n_nodes = 0, root = 0;
+    bool   built = false;
+    float  lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};   // vertex bounds of the triangles
+    float  radius = 0.f;                           // R the boxes are padded for
+    float  padc = 4.0f;
+    double build_ms = 0.0, refit_ms = 0.0;
+    unsigned refits = 0;
+};
+
+static BvhState* bvh_state(rtb200_ctx* c)
+{
+    if (!c->bvh_state) c->bvh_state = new BvhState();
+    return static_cast<BvhState*>(c->bvh_state);
+}
+
+// ---------------------------------------------------------------------------------------
+// build kernels
+// ---------------------------------------------------------------------------------------
+RT_DEV int float_order(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+static inline float order_float(int i) { const int b = i >= 0 ? i : i ^ 0x7fffffff; float f; memcpy(&f, &b, 4); return f; }
+
+__global__ void k_bvh_bounds(const TriRec* __restrict__ tri, int n, int* __restrict__ bounds)
+{
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = tri[i].a, b = tri[i].b, c = tri[i].c;
+        const float p[3] = {a.x, a.y, a.z}, e1[3] = {b.x, b.y, b.z}, e2[3] = {c.x, c.y, c.z};
+        #pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float v1 = p[k] + e1[k], v2 = p[k] + e2[k];
+            lo[k] = fminf(lo[k], fminf(p[k], fminf(v1, v2)));
+            hi[k] = fmaxf(hi[k], fmaxf(p[k], fmaxf(v1, v2)));
+        }
+    }
+    #pragma unroll
+    for (int k = 0; k < 3; ++k)
+        for (int off = 16; off > 0; off >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(FULL_MASK, lo[k], off));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(FULL_MASK, hi[k], off));
+        }
+    if ((threadIdx.x & 31) == 0) {
+        #pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(&bounds[k], float_order(lo[k]));
+            atomicMax(&bounds[3 + k], float_order(hi[k]));
+        }
+    }
+}
+
+RT_DEV unsigned long long expand21(unsigned int v)
+{
+    unsigned long long x = v & 0x1fffffull;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+struct Bounds6 { float lo[3], inv[3]; };
+
+__global__ void k_bvh_morton(const TriRec* __restrict__ tri, int n, Bounds6 b, unsigned long long* __restrict__ keys,
+                             unsigned int* __restrict__ idx)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = tri[i].a, e1 = tri[i].b, e2 = tri[i].c;
+    const float c[3] = {a.x + (e1.x + e2.x) * (1.0f / 3.0f), a.y + (e1.y + e2.y) * (1.0f / 3.0f), a.z + (e1.z + e2.z) * (1.0f / 3.0f)};
+    unsigned int q[3];
+    #pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float u = fminf(fmaxf((c[k] - b.lo[k]) * b.inv[k], 0.0f), 1.0f);
+        q[k] = min((unsigned int)(u * 2097152.0f), 2097151u);
+    }
+    keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
+    idx[i] = (unsigned int)i;
+}
+
+__global__ void k_bvh_gather(const TriRec* __restrict__ tri, const unsigned int* __restrict__ idx, int n, TriRec* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = tri[idx[i]];
+}
+
+// common-prefix length of keys i and j (Karras 2012, sec. 4); equal keys fall back to the index
+RT_DEV int bvh_delta(const unsigned long long* __restrict__ k, int n, int i, int j)
+{
+    if (j < 0 || j >= n) return -1;
+    const unsigned long long a = k[i], b = k[j];
+    if (a == b) return 64 + __clz(i ^ j);
+    return __clzll((long long)(a ^ b));
+}
+
+RT_DEV int bvh_leaf_ref(int first, int count) { return ~(first | ((count - 1) << BVH_LEAF_SHIFT)); }
+
+__global__ void k_bvh_hierarchy(const unsigned long long* __restrict__ keys, int n, BvhNode* __restrict__ nodes,
+                                int* __restrict__ parent, int* __restrict__ leaf_parent, int* __restrict__ gamma)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (bvh_delta(keys, n, i, i + 1) - bvh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = bvh_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (bvh_delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (bvh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = bvh_delta(keys, n, i, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (bvh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    const int g = i + s * d + min(d, 0);
+    const int first = min(i, j), last = max(i, j);
+    gamma[i] = g;
+    // Karras children: left = node/leaf g, right = node/leaf g + 1
+    if (first == g) leaf_parent[g] = i; else parent[g] = i;
+    if (last == g + 1) leaf_parent[g + 1] = i; else parent[g + 1] = i;
+    if (i == 0) parent[0] = -1;
+    // traversal references: small subtrees collapse into leaves over [first, g] / [g + 1, last]
+    const int nl = g - first + 1, nr = last - g;
+    nodes[i].c = make_int4(nl <= BVH_LEAF_MAX ? bvh_leaf_ref(first, nl) : g,
+                           nr <= BVH_LEAF_MAX ? bvh_leaf_ref(g + 1, nr) : g + 1, first, last);
+}
+
+// bottom-up refit: every triangle carries its padded box up; the second thread to reach a node
+// merges the two child boxes and continues
+__global__ void k_bvh_refit(const TriRec* __restrict__ tri, int n, BvhNode* nodes, const int* __restrict__ parent,
+                            const int* __restrict__ leaf_parent, const int* __restrict__ gamma, int* flags,
+                            float pad_scale, float pad_floor)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = tri[i].a, b = tri[i].b, c = tri[i].c;
+    const float l1 = sqrtf(b.x * b.x + b.y * b.y + b.z * b.z), l2 = sqrtf(c.x * c.x + c.y * c.y + c.z * c.z);
+    const float pad = fmaxf(pad_scale * l1 * l2, pad_floor);
+    float lo[3], hi[3];
+    {
+        const float p[3] = {a.x, a.y, a.z}, e1[3] = {b.x, b.y, b.z}, e2[3] = {c.x, c.y, c.z};
+        #pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float v1 = p[k] + e1[k], v2 = p[k] + e2[k];
+            lo[k] = fminf(p[k], fminf(v1, v2)) - pad;
+            hi[k] = fmaxf(p[k], fmaxf(v1, v2)) + pad;
+        }
+    }
+    int child = i, p = leaf_parent[i];
+    while (p >= 0) {
+        float* f = reinterpret_cast<float*>(&nodes[p]);
+        const int slot = (child == gamma[p]) ? 0 : 1;
+        float* mine = f + 6 * slot;
+        mine[0] = lo[0]; mine[1] = lo[1]; mine[2] = lo[2]; mine[3] = hi[0]; mine[4] = hi[1]; mine[5] = hi[2];
+        __threadfence();
+        if (atomicAdd(&flags[p], 1) == 0) return;          // the sibling subtree is not finished yet
+        __threadfence();
+        const volatile float* other = f + 6 * (1 - slot);
+        lo[0] = fminf(lo[0], other[0]); lo[1] = fminf(lo[1], other[1]); lo[2] = fminf(lo[2], other[2]);
+        hi[0] = fmaxf(hi[0], other[3]); hi[1] = fmaxf(hi[1], other[4]); hi[2] = fmaxf(hi[2], other[5]);
+        child = p;
+        p = parent[p];
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// traversal
+// ---------------------------------------------------------------------------------------
+struct RayBox { float ix, iy, iz, ox, oy, oz; };           // 1/d and o/d
+
+RT_DEV float safe_rcp(float d)
+{
+    return fabsf(d) > 1.0e-30f ? 1.0f / d : copysignf(1.0e30f, d);
+}
+
+RT_DEV RayBox make_raybox(V3 o, V3 d)
+{
+    RayBox r;
+    r.ix = safe_rcp(d.x); r.iy = safe_rcp(d.y); r.iz = safe_rcp(d.z);
+    r.ox = o.x * r.ix; r.oy = o.y * r.iy; r.oz = o.z * r.iz;
+    return r;
+}
+
+// entry distance of the (already padded) box, or -1 when the ray misses it inside [0, limit]
+RT_DEV float slab(const RayBox& r, float lx, float ly, float lz, float hx, float hy, float hz, float limit)
+{
+    const float ax = fmaf(lx, r.ix, -r.ox), bx = fmaf(hx, r.ix, -r.ox);
+    const float ay = fmaf(ly, r.iy, -r.oy), by = fmaf(hy, r.iy, -r.oy);
+    const float az = fmaf(lz, r.iz, -r.oz), bz = fmaf(hz, r.iz, -r.oz);
+    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), limit));
+    return tn * (1.0f - BVH_SLACK) <= tf * (1.0f + BVH_SLACK) ? tn : -1.0f;
+}
+
+// Generic traversal.  `Leaf` is called as leaf(first, count) and returns the new distance limit
+// (or a negative value to stop the traversal).
+template <class Leaf>
+RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& leaf, unsigned& n_nodes, unsigned& overflow)
+{
+    const RayBox rb = make_raybox(o, d);
+    int   stack_ref[BVH_STACK];
+    float stack_tn[BVH_STACK];
+    int sp = 0;
+    int ref = s.bvh_root;
+    for (;;) {
+        if (ref >= 0) {
+            const BvhNode* __restrict__ nd = s.bvh_nodes + ref;
+            const float4 b0 = __ldg(&nd->b0), b1 = __ldg(&nd->b1), b2 = __ldg(&nd->b2);
+            const int4 c = __ldg(&nd->c);
+            ++n_nodes;
+            const float t0 = slab(rb, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit);
+            const float t1 = slab(rb, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit);
+            if (t0 >= 0.f && t1 >= 0.f) {
+                const bool swap = t1 < t0;
+                if (sp < BVH_STACK) { stack_ref[sp] = swap ? c.x : c.y; stack_tn[sp] = swap ? t0 : t1; ++sp; }
+                else overflow = 1;
+                ref = swap ? c.y : c.x;
+                continue;
+            }
+            if (t0 >= 0.f) { ref = c.x; continue; }
+            if (t1 >= 0.f) { ref = c.y; continue; }
+        } else {
+            const int code = ~ref;
+            limit = leaf(code & ((1 << BVH_LEAF_SHIFT) - 1), (code >> BVH_LEAF_SHIFT) + 1, limit);
+            if (limit < 0.f) return;
+        }
+        // pop the next subtree that can still matter
+        for (;;) {
+            if (sp == 0) return;
+            --sp;
+            if (stack_tn[sp] * (1.0f - BVH_SLACK) <= limit * (1.0f + BVH_SLACK)) { ref = stack_ref[sp]; break; }
+        }
+    }
+}
+
+template <int MODE, bool PRIMARY>
+__global__ void __launch_bounds__(BVH_THREADS)
+k_bvh_nearest(const __grid_constant__ TraceParams p)
+{
+    const DeviceScene& s = p.s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    V3 o, d;
+    int slot = -1;
+    if (PRIMARY) {                                            // CTA = 16x8 lattice tile, warp = 8x4
+        const int tiles_x = (p.f.LW + 15) >> 4;
+        const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
+        const int lx = (tx << 4) + ((warp & 1) << 3) + (lane & 7);
+        const int cy = (ty << 3) + ((warp >> 1) << 2) + (lane >> 3);
+        const int ly = p.chunk_ly0 + cy;
+        if (lx < p.f.LW && cy < p.chunk_rows && ly < p.local_LH) {
+            slot = cy * p.f.LW + lx;
+            primary_ray<(MODE != 2)>(p.f, lx, global_lattice_row(p.f, ly), o, d);
+        }
+    } else {
+        const int i = blockIdx.x * BVH_THREADS + threadIdx.x;
+        if (i < p.n_rays) { slot = i; o = f4_xyz(p.in_od0[i]); d = f4_xyz(p.in_od1[i]); }
+    }
+    unsigned n_nodes = 0, n_tests = 0, overflow = 0;
+    if (slot >= 0) {
+        float best_t = -1.0f;
+        int best_id = -1;
+        if (s.n_tri > 0) {
+            const TriRec* __restrict__ tri = s.bvh_tri;
+            bvh_traverse(s, o, d, 3.0e38f, [&](int first, int count, float limit) -> float {
+                for (int k = 0; k < count; ++k) {
+                    const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
+                    const float tt = MODE == 2 ? triangle_t<false>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc))
+                                               : triangle_t<true>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc));
+                    const int ord = __float_as_int(ra.w);
+                    if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) {
+                        best_t = tt; best_id = ord; limit = tt;
+                    }
+                }
+                n_tests += (unsigned)count;
+                return limit;
+            }, n_nodes, overflow);
+        }
+        // quadrics and planes: the brute-force side list (reference sequence; ties -> lower order)
+        for (int q = 0; q < s.n_quad; ++q) {
+            const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
+            const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+            const int ord = __float_as_int(q0.w);
+            bool lin;
+            const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+            if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+        }
+        for (int q = 0; q < s.n_plane; ++q) {
+            const float4 nc = __ldg(&s.plane[q].nc);
+            const int ord = s.plane[q].order;
+            const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
+            if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+        }
+        p.hit[slot] = make_float2(best_t, __int_as_float(best_id));
+    }
+    // statistics: one atomic per warp and counter
+    for (int off = 16; off > 0; off >>= 1) {
+        n_nodes += __shfl_xor_sync(FULL_MASK, n_nodes, off);
+        n_tests += __shfl_xor_sync(FULL_MASK, n_tests, off);
+        overflow |= __shfl_xor_sync(FULL_MASK, overflow, off);
+    }
+    if (lane == 0 && p.stats) {
+        unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+        if (n_nodes) atomicAdd(&st[ST_BVH_NODES], (unsigned long long)n_nodes);
+        if (n_tests) atomicAdd(&st[ST_TEST_TRI], (unsigned long long)n_tests);
+        if (overflow) atomicAdd(&st[ST_BVH_OVERFLOW], 1ull);
+    }
+}
+
+// Shadow filter through the BVH: every triangle hit strictly inside (EPSILON, dist) multiplies
+// the filter by colour*kt (Scene.cpp:1856-1857).  An opaque occluder makes the filter exactly 0
+// (0 * finite = 0), so the traversal may stop there; transparent occluders are collected and
+// multiplied in insertion order, the order of the linear scan.
+template <int MODE>
+__global__ void __launch_bounds__(BVH_THREADS)
+k_bvh_shadow(const __grid_constant__ ShadowParams p)
+{
+    const DeviceScene& s = p.s;
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * BVH_THREADS + threadIdx.x;
+    unsigned n_nodes = 0, n_tests = 0, overflow = 0, n_side_q = 0, n_side_p = 0;
+    if (i < p.n_queries) {
+        const float4 a = p.sq0[i], b = p.sq1[i];
+        const V3 o = f4_xyz(a), d = f4_xyz(b);
+        const float dist = a.w;
+        float fr = 1.0f, fg = 1.0f, fb = 1.0f;
+        bool zero = false;
+        int l_ord[BVH_SHADOW_LIST], l_mat[BVH_SHADOW_LIST];
+        int n_list = 0;
+        if (s.n_tri > 0) {
+            const TriRec* __restrict__ tri = s.bvh_tri;
+            bvh_traverse(s, o, d, dist, [&](int first, int count, float limit) -> float {
+                n_tests += (unsigned)count;
+                for (int k = 0; k < count; ++k) {
+                    const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
+                    const float tt = MODE == 2 ? triangle_t<false>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc))
+                                               : triangle_t<true>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc));
+                    if (tt > RT_EPS && tt < dist) {
+                        const int m = __float_as_int(rb.w);
+                        const float4 m0 = __ldg(&s.mat[m].m0);
+                        const float kt = __ldg(&s.mat[m].m2).x;
+                        const float cr = __fmul_rn(m0.x, kt), cg = __fmul_rn(m0.y, kt), cb = __fmul_rn(m0.z, kt);
+                        if (cr == 0.f && cg == 0.f && cb == 0.f) { zero = true; return -1.0f; }
+                        if (n_list < BVH_SHADOW_LIST) { l_ord[n_list] = __float_as_int(ra.w); l_mat[n_list] = m; ++n_list; }
+                        else { fr = __fmul_rn(fr, cr); fg = __fmul_rn(fg, cg); fb = __fmul_rn(fb, cb); }   // > 8 transparent layers: unordered
+                    }
+                }
+                return limit;
+            }, n_nodes, overflow);
+        }
+        if (zero) { fr = fg = fb = 0.0f; }
+        else {
+            for (int x = 1; x < n_list; ++x) {                 // insertion sort by order
+                const int ko = l_ord[x], km = l_mat[x];
+                int y = x - 1;
+                while (y >= 0 && l_ord[y] > ko) { l_ord[y + 1] = l_ord[y]; l_mat[y + 1] = l_mat[y]; --y; }
+                l_ord[y + 1] = ko; l_mat[y + 1] = km;
+            }
+            for (int x = 0; x < n_list; ++x) {
+                const float4 m0 = __ldg(&s.mat[l_mat[x]].m0);
+                const float kt = __ldg(&s.mat[l_mat[x]].m2).x;
+                fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+            }
+        }
+        if (!(fr == 0.f && fg == 0.f && fb == 0.f)) {
+            n_side_q = (unsigned)s.n_quad; n_side_p = (unsigned)s.n_plane;
+            for (int q = 0; q < s.n_quad; ++q) {
+                const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
+                const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+                bool lin;
+                const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+                if (tt > RT_EPS && tt < dist) {
+                    const int m = __float_as_int(q1.w);
+                    const float4 m0 = __ldg(&s.mat[m].m0);
+                    const float kt = __ldg(&s.mat[m].m2).x;
+                    fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+                }
+            }
+            for (int q = 0; q < s.n_plane; ++q) {
+                const float4 nc = __ldg(&s.plane[q].nc);
+                const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
+                if (tt > RT_EPS && tt < dist) {
+                    const int m = s.plane[q].material;
+                    const float4 m0 = __ldg(&s.mat[m].m0);
+                    const float kt = __ldg(&s.mat[m].m2).x;
+                    fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+                }
+            }
+        }
+        p.filter[i] = make_float4(fr, fg, fb, 0.f);
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        n_nodes += __shfl_xor_sync(FULL_MASK, n_nodes, off);
+        n_tests += __shfl_xor_sync(FULL_MASK, n_tests, off);
+        n_side_q += __shfl_xor_sync(FULL_MASK, n_side_q, off);
+        n_side_p += __shfl_xor_sync(FULL_MASK, n_side_p, off);
+        overflow |= __shfl_xor_sync(FULL_MASK, overflow, off);
+    }
+    if (lane == 0 && p.stats) {
+        unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+        if (n_nodes) atomicAdd(&st[ST_BVH_NODES], (unsigned long long)n_nodes);
+        if (n_tests) atomicAdd(&st[ST_TEST_TRI], (unsigned long long)n_tests);
+        if (n_side_q) atomicAdd(&st[ST_TEST_QUAD], (unsigned long long)n_side_q);
+        if (n_side_p) atomicAdd(&st[ST_TEST_PLANE], (unsigned long long)n_side_p);
+        if (overflow) atomicAdd(&st[ST_BVH_OVERFLOW], 1ull);
+    }
+}
+
+cudaError_t launch_bvh_nearest(const TraceParams& p, cudaStream_t st)
+{
+    int blocks;
+    if (p.primary) blocks = ((p.f.LW + 15) / 16) * ((p.chunk_rows + 7) / 8);
+    else blocks = (p.n_rays + BVH_THREADS - 1) / BVH_THREADS;
+    if (blocks <= 0) return cudaSuccess;
+    if (p.primary) {
+        if (p.mode == 2) k_bvh_nearest<2, true><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else             k_bvh_nearest<0, true><<<blocks, BVH_THREADS, 0, st>>>(p);
+    } else {
+        if (p.mode == 2) k_bvh_nearest<2, false><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else             k_bvh_nearest<0, false><<<blocks, BVH_THREADS, 0, st>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bvh_shadow(const ShadowParams& p, cudaStream_t st)
+{
+    const int blocks = (p.n_queries + BVH_THREADS - 1) / BVH_THREADS;
+    if (blocks <= 0) return cudaSuccess;
+    if (p.mode == 2) k_bvh_shadow<2><<<blocks, BVH_THREADS, 0, st>>>(p);
+    else             k_bvh_shadow<0><<<blocks, BVH_THREADS, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------
+#define BCU(call)                                                       \
+    do {                                                                \
+        cudaError_t e__ = (call);                                       \
+        if (e__ != cudaSuccess) return set_cuda_error(c, e__, #call);   \
+    } while (0)
+
+void bvh_release(rtb200_ctx* c)
+{
+    if (!c->bvh_state) return;
+    BvhState* b = static_cast<BvhState*>(c->bvh_state);
+    b->nodes.release(); b->tri_sorted.release(); b->keys.release(); b->keys_out.release(); b->idx.release(); b->idx_out.release();
+    b->cub_tmp.release(); b->parent.release(); b->leaf_parent.release(); b->gamma.release(); b->flags.release(); b->bounds.release();
+    delete b;
+    c->bvh_state = nullptr;
+}
+
+void bvh_invalidate(rtb200_ctx* c)
+{
+    if (c->bvh_state) static_cast<BvhState*>(c->bvh_state)->built = false;
+    c->ds.bvh_nodes = nullptr; c->ds.bvh_tri = nullptr; c->ds.bvh_root = 0;
+}
+
+bool bvh_ready(const rtb200_ctx* c)
+{
+    return c->bvh_state && static_cast<const BvhState*>(c->bvh_state)->built;
+}
+
+static int bvh_refit(rtb200_ctx* c, BvhState* b, float radius)
+{
+    const int T = b->n_tri;
+    b->radius = radius;
+    if (T <= BVH_LEAF_MAX) return RTB200_OK;                  // a single leaf: no boxes at all
+    // pad = PADC * 2^-24 / EPSILON * R * |e1| |e2|, floor 32 ulp of R (rounding of the slab test)
+    const float pad_scale = b->padc * 5.9604645e-8f / RT_EPS * radius;
+    const float pad_floor = 32.0f * 1.1920929e-7f * radius;
+    BCU(cudaMemsetAsync(b->flags.p, 0, sizeof(int) * (size_t)(T - 1), c->stream));
+    k_bvh_refit<<<(T + 255) / 256, 256, 0, c->stream>>>(b->tri_sorted.as<TriRec>(), T, b->nodes.as<BvhNode>(), b->parent.as<int>(),
+                                                        b->leaf_parent.as<int>(), b->gamma.as<int>(), b->flags.as<int>(), pad_scale, pad_floor);
+    BCU(cudaGetLastError());
+    return RTB200_OK;
+}
+
+int bvh_build(rtb200_ctx* c)
+{
+    BvhState* b = bvh_state(c);
+    b->built = false;
+    const int T = c->ds.n_tri;
+    if (T >= (1 << BVH_LEAF_SHIFT)) { c->last_error = "too many triangles for the LBVH leaf encoding"; return RTB200_E_ARG; }
+    if (const char* e = getenv("RTB200_BVH_PADC")) { const float v = (float)atof(e); if (v >= 0.f) b->padc = v; }
+    b->n_tri = T; b->n_nodes = T > BVH_LEAF_MAX ? T - 1 : 0;
+    b->root = T > BVH_LEAF_MAX ? 0 : ~(0 | ((std::max(T, 1) - 1) << BVH_LEAF_SHIFT));
+    cudaError_t e;
+    cudaEvent_t ev0 = c->ev[2], ev1 = c->ev[3];
+    BCU(cudaEventRecord(ev0, c->stream));
+    if (T > 0) {
+        const size_t n = (size_t)T;
+        if ((e = b->tri_sorted.ensure(sizeof(TriRec) * n)) != cudaSuccess || (e = b->bounds.ensure(sizeof(int) * 8)) != cudaSuccess)
+            return set_cuda_error(c, e, "bvh buffers");
+        int h_init[6] = {INT_MAX, INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MIN};
+        BCU(cudaMemcpyAsync(b->bounds.p, h_init, sizeof h_init, cudaMemcpyHostToDevice, c->stream));
+        k_bvh_bounds<<<std::min((T + 255) / 256, 4 * c->sm_count), 256, 0, c->stream>>>(c->ds.tri, T, b->bounds.as<int>());
+        BCU(cudaGetLastError());
+        int h_b[6];
+        BCU(cudaMemcpyAsync(h_b, b->bounds.p, sizeof h_b, cudaMemcpyDeviceToHost, c->stream));
+        BCU(cudaStreamSynchronize(c->stream));
+        for (int k = 0; k < 3; ++k) { b->lo[k] = order_float(h_b[k]); b->hi[k] = order_float(h_b[3 + k]); }
+    }
+    if (T > BVH_LEAF_MAX) {
+        const size_t n = (size_t)T;
+        if ((e = b->nodes.ensure(sizeof(BvhNode) * (n - 1))) != cudaSuccess ||
+            (e = b->keys.ensure(8 * n)) != cudaSuccess || (e = b->keys_out.ensure(8 * n)) != cudaSuccess ||
+            (e = b->idx.ensure(4 * n)) != cudaSuccess || (e = b->idx_out.ensure(4 * n)) != cudaSuccess ||
+            (e = b->parent.ensure(4 * n)) != cudaSuccess || (e = b->leaf_parent.ensure(4 * n)) != cudaSuccess ||
+            (e = b->gamma.ensure(4 * n)) != cudaSuccess || (e = b->flags.ensure(4 * n)) != cudaSuccess)
+            return set_cuda_error(c, e, "bvh buffers");
+        Bounds6 bb;
+        for (int k = 0; k < 3; ++k) {
+            bb.lo[k] = b->lo[k];
+            const float ext = b->hi[k] - b->lo[k];
+            bb.inv[k] = ext > 0.f ? 1.0f / ext : 0.0f;
+        }
+        const int blocks = (T + 255) / 256;
+        k_bvh_morton<<<blocks, 256, 0, c->stream>>>(c->ds.tri, T, bb, b->keys.as<unsigned long long>(), b->idx.as<unsigned int>());
+        BCU(cudaGetLastError());
+        size_t tmp_bytes = 0;
+        BCU(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, b->keys.as<unsigned long long>(), b->keys_out.as<unsigned long long>(),
+                                            b->idx.as<unsigned int>(), b->idx_out.as<unsigned int>(), T, 0, 63, c->stream));
+        if ((e = b->cub_tmp.ensure(tmp_bytes)) != cudaSuccess) return set_cuda_error(c, e, "sort scratch");
+        BCU(cub::DeviceRadixSort::SortPairs(b->cub_tmp.p, tmp_bytes, b->keys.as<unsigned long long>(), b->keys_out.as<unsigned long long>(),
+                                            b->idx.as<unsigned int>(), b->idx_out.as<unsigned int>(), T, 0, 63, c->stream));
+        k_bvh_gather<<<blocks, 256, 0, c->stream>>>(c->ds.tri, b->idx_out.as<unsigned int>(), T, b->tri_sorted.as<TriRec>());
+        BCU(cudaGetLastError());
+        k_bvh_hierarchy<<<blocks, 256, 0, c->stream>>>(b->keys_out.as<unsigned long long>(), T, b->nodes.as<BvhNode>(), b->parent.as<int>(),
+                                                       b->leaf_parent.as<int>(), b->gamma.as<int>());
+        BCU(cudaGetLastError());
+    } else if (T > 0) {
+        BCU(cudaMemcpyAsync(b->tri_sorted.p, c->ds.tri, sizeof(TriRec) * (size_t)T, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    // default radius: origins anywhere within one scene diagonal of the box (refitted on demand)
+    const float dx = b->hi[0] - b->lo[0], dy = b->hi[1] - b->lo[1], dz = b->hi[2] - b->lo[2];
+    const float diag = T > 0 ? sqrtf(dx * dx + dy * dy + dz * dz) : 0.f;
+    int rc = bvh_refit(c, b, 2.0f * diag);
+    if (rc != RTB200_OK) return rc;
+    BCU(cudaEventRecord(ev1, c->stream));
+    BCU(cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    BCU(cudaEventElapsedTime(&ms, ev0, ev1));
+    b->build_ms = ms;
+    b->built = true;
+    c->ds.bvh_nodes = b->nodes.as<BvhNode>();
+    c->ds.bvh_tri = b->tri_sorted.as<TriRec>();
+    c->ds.bvh_root = b->root;
+    return RTB200_OK;
+}
+
+// Make the padded boxes valid for rays starting at the given points (host array of n xyz):
+// R must bound |origin - p0| for every triangle.  Refits (no rebuild) when the current pad is
+// too small.
+int bvh_prepare(rtb200_ctx* c, const float* origins3, int n)
+{
+    if (!bvh_ready(c)) { c->last_error = "RTB200_F_USE_BVH without rtb200_build_bvh"; return RTB200_E_STATE; }
+    BvhState* b = static_cast<BvhState*>(c->bvh_state);
+    if (b->n_tri == 0) return RTB200_OK;
+    float need = 0.f;
+    for (int i = 0; i < n; ++i) {
+        float d2 = 0.f;
+        for (int k = 0; k < 3; ++k) {
+            const float o = origins3[3 * (size_t)i + k];
+            const float far = std::max(std::fabs(o - b->lo[k]), std::fabs(o - b->hi[k]));
+            d2 += far * far;
+        }
+        if (std::isfinite(d2)) need = std::max(need, std::sqrt(d2));
+    }
+    // secondary and shadow rays start on the scene's surfaces; planes and quadrics can lie outside
+    // the triangle bounds, so keep at least the default of two diagonals
+    if (need <= b->radius) return RTB200_OK;
+    cudaEvent_t ev0 = c->ev[2], ev1 = c->ev[3];
+    BCU(cudaEventRecord(ev0, c->stream));
+    int rc = bvh_refit(c, b, need * 1.25f);
+    if (rc != RTB200_OK) return rc;
+    BCU(cudaEventRecord(ev1, c->stream));
+    BCU(cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    BCU(cudaEventElapsedTime(&ms, ev0, ev1));
+    b->refit_ms = ms; ++b->refits;
+    return RTB200_OK;
+}
+
+} // namespace rtb
+
+using namespace rtb;
+
+extern "C" int rtb200_build_bvh(rtb200_ctx* ctx)
+{
+    if (!ctx) return RTB200_E_ARG;
+    if (!ctx->have_scene) { ctx->last_error = "rtb200_build_bvh before rtb200_set_scene"; return RTB200_E_STATE; }
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return set_cuda_error(ctx, cudaGetLastError(), "cudaSetDevice");
+    return bvh_build(ctx);
+}
+
+extern "C" int rtb200_bvh_info(rtb200_ctx* ctx, int* n_nodes, int* n_triangles, double* build_ms, double* pad_radius, double* node_bytes)
+{
+    if (!ctx) return RTB200_E_ARG;
+    if (!bvh_ready(ctx)) { ctx->last_error = "no LBVH built"; return RTB200_E_STATE; }
+    const BvhState* b = static_cast<const BvhState*>(ctx->bvh_state);
+    if (n_nodes) *n_nodes = b->n_nodes;
+    if (n_triangles) *n_triangles = b->n_tri;
+    if (build_ms) *build_ms = b->build_ms;
+    if (pad_radius) *pad_radius = b->radius;
+    if (node_bytes) *node_bytes = (double)sizeof(BvhNode);
+    return RTB200_OK;
+}

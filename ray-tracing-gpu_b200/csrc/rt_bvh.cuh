@@ -1,0 +1,17 @@
+// rt_bvh.cuh -- GPU-built LBVH over the triangles of the scene (no
+// counterpart in the reference, whose nearest hit is a linear scan, Scene.cpp:1710-1715).
+// Contract: the SAME (t, order) winner and the SAME shadow filter as the brute-force kernels.
+#pragma once
+#include "rt_stream.cuh"
+
+namespace rtb {
+
+#define BVH_LEAF_MAX   4          // triangles per leaf (contiguous in Morton order)
+#define BVH_STACK      64         // traversal stack entries per ray
+#define BVH_THREADS    128
+#define BVH_LEAF_SHIFT 28         // leaf reference = ~(first | (count - 1) << 28)
+
+cudaError_t launch_bvh_nearest(const TraceParams& p, cudaStream_t st);
+cudaError_t launch_bvh_shadow(const ShadowParams& p, cudaStream_t st);
+
+} // namespace rtb

@@ -47,7 +47,13 @@ struct LevelBuf {                 // one wavefront level (rays of one bounce cou
     DevBuf od0, od1, colour, links;
 };
 
-struct Comm;                      // rt_comm.cu (NCCL, loaded lazily with dlopen)
+struct Comm;                      // rt_bvh.cu
+int  bvh_build(rtb200_ctx* c);
+void bvh_release(rtb200_ctx* c);
+void bvh_invalidate(rtb200_ctx* c);                                         // the scene changed
+bool bvh_ready(const rtb200_ctx* c);
+int  bvh_prepare(rtb200_ctx* c, const float* origins3, int n);              // pad the boxes for rays starting this far out
+// rt_comm.cu (NCCL, loaded lazily with dlopen)
 
 } // namespace rtb
 
@@ -86,6 +92,7 @@ struct rtb200_ctx {
 
     // streamed path scratch (rt_stream.cu) and host-side test counts of the last frame
     void* stream_scratch = nullptr;
+    void* bvh_state = nullptr;        // rt_bvh.cu
     unsigned long long host_tests[3] = {0, 0, 0};
 
     // peak cache

@@ -32,6 +32,12 @@ struct QuadRec { float4 q0, q1, q2; };
 // planes:  n.xyz c | then order/material in a parallel int2
 struct PlaneRec { float4 nc; int order, material, pad0, pad1; };
 
+// LBVH node (rt_bvh.cu): the boxes of BOTH children + their references, 64 bytes, one fetch
+// decides two subtrees.  b0 = c0.min.xyz | c0.max.x, b1 = c0.max.yz | c1.min.xy,
+// b2 = c1.min.z | c1.max.xyz, c = (ref0, ref1, -, -).  ref >= 0: internal node index;
+// ref < 0: leaf, ~ref = first | (count - 1) << 28 over the Morton-sorted triangle array.
+struct BvhNode { float4 b0, b1, b2; int4 c; };
+
 struct DeviceScene {
     ResidentLayout rl;
     const unsigned char* blob;      // resident blob in global memory
@@ -45,6 +51,10 @@ struct DeviceScene {
     const QuadRec*  quad;
     const PlaneRec* plane;
     int n_tri_padded;
+    // LBVH over the triangles (null until rtb200_build_bvh)
+    const BvhNode*  bvh_nodes;
+    const TriRec*   bvh_tri;        // triangles in Morton order (order / material travel in .a.w / .b.w)
+    int             bvh_root;       // reference of the root (a leaf reference when T <= BVH_LEAF_MAX)
 };
 
 // ---- per-frame constants ------------------------------------------------------------------

@@ -14,6 +14,7 @@
 
 #include "rt_context.h"
 #include "rt_stream.cuh"
+#include "rt_bvh.cuh"
 
 using namespace rtb;
 
@@ -51,6 +52,11 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
 {
     StreamBufs* sb = stream_bufs(c);
     const int mode = (fr->flags & RTB200_F_FUSED_FP) ? 2 : ((fr->flags & RTB200_F_EXACT_FP) ? 1 : 0);
+    const bool use_bvh = (fr->flags & RTB200_F_USE_BVH) != 0;
+    if (use_bvh) {                               // boxes must be padded for rays that start at the camera
+        const int rc = bvh_prepare(c, fr->cam_pos, 1);
+        if (rc != RTB200_OK) return rc;
+    }
     const int k = fp.k;
     const int local_LH = local_rows * k;
     const int L = c->ds.rl.n_light;
@@ -109,7 +115,9 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             tp.n_rays = n_in; tp.hit = sb->hit.as<float2>(); tp.mode = mode;
             const bool timed = !timed_first && level == 0;
             if (timed) SCU(cudaEventRecord(ev_a, c->stream));
-            SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
+            tp.stats = c->stats.as<unsigned long long>();
+            if (use_bvh) SCU(launch_bvh_nearest(tp, c->stream));
+            else         SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
             if (timed) { SCU(cudaEventRecord(ev_b, c->stream)); timed_first = true; }
             ++*launches;
             rays_nearest += (unsigned long long)n_in;
@@ -139,7 +147,8 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 memset(&sp, 0, sizeof sp);
                 sp.s = c->ds; sp.sq0 = sa.sq0; sp.sq1 = sa.sq1; sp.n_queries = n_sq;
                 sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode;
-                SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+                if (use_bvh) SCU(launch_bvh_shadow(sp, c->stream));
+                else         SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
                 ++*launches;
             }
             // ---- shade B -------------------------------------------------------------------------
@@ -181,11 +190,11 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     (void)ms_nearest; (void)ms_shadow;
     st->depth_levels = max_level_seen;
     st->chunks = chunks;
-    st->path = 1;
+    st->path = use_bvh ? 2 : 1;
     st->ms_trace_nearest = -1.0;              // first level-0 nearest-hit launch, read after the final sync
     // nearest-hit queries test every surface by construction (no early-out): exact host-side count;
     // shadow queries are counted on the device (warps leave early once their filters are zero)
-    c->host_tests[0] = rays_nearest * (unsigned long long)c->ds.n_tri;
+    c->host_tests[0] = use_bvh ? 0ull : rays_nearest * (unsigned long long)c->ds.n_tri;   // LBVH: counted on the device
     c->host_tests[1] = rays_nearest * (unsigned long long)c->ds.n_quad;
     c->host_tests[2] = rays_nearest * (unsigned long long)c->ds.n_plane;
     return RTB200_OK;
@@ -204,7 +213,8 @@ int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
     memset(&tp, 0, sizeof tp);
     tp.s = c->ds; tp.primary = 0; tp.in_od0 = sb->sq0.as<float4>(); tp.in_od1 = sb->sq1.as<float4>();
     tp.n_rays = n; tp.hit = sb->hit.as<float2>(); tp.mode = mode;
-    SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
+    if (flags & RTB200_F_USE_BVH) SCU(launch_bvh_nearest(tp, c->stream));
+    else                          SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
     SCU(launch_query_finish_nearest(c->ds, n, tp.in_od0, tp.in_od1, tp.hit, c->q_out0.as<int>(), c->q_out1.as<float>(),
                                     c->q_out2.as<float>(), mode != 2, c->stream));
     return RTB200_OK;
@@ -225,16 +235,10 @@ int stream_query_shadow(rtb200_ctx* c, int n, uint32_t flags)
     memset(&sp, 0, sizeof sp);
     sp.s = c->ds; sp.sq0 = sb->sq0.as<float4>(); sp.sq1 = sb->sq1.as<float4>(); sp.n_queries = n;
     sp.filter = sb->filter.as<float4>(); sp.stats = c->stats.as<unsigned long long>(); sp.mode = mode;
-    SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+    if (flags & RTB200_F_USE_BVH) SCU(launch_bvh_shadow(sp, c->stream));
+    else                          SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
     SCU(launch_query_unpack_filter(n, sp.filter, c->q_out2.as<float>(), c->stream));
     return RTB200_OK;
 }
 
 } // namespace rtb
-
-extern "C" int rtb200_build_bvh(rtb200_ctx* ctx)
-{
-    if (!ctx) return RTB200_E_ARG;
-    ctx->last_error = "LBVH not available in this build";
-    return RTB200_E_STATE;
-}

@@ -24,6 +24,7 @@ struct TraceParams {
     int   mode;                    // 0: FMA culling filter + reference-rounded survivors (default)
                                    // 1: no filter, reference sequence for every test (EXACT_FP)
                                    // 2: filter + fused survivors (FUSED_FP)
+    unsigned long long* stats;     // LBVH kernels: nodes visited / triangle tests (may be null)
 };
 
 // shade-A: hit point, normal, shadow queries of the facing lights, children

@@ -1,0 +1,172 @@
+"""GPU (-m gpu): the GPU-built LBVH must return the SAME nearest hit (order and distance bits) and
+the SAME shadow filter as the brute-force linear scan (the scan it has to
+agree with is Scene.cpp:1710-1715 / 1850-1858), on random, regular and adversarial scenes."""
+from importlib import import_module
+
+import numpy as np
+import pytest
+
+from conftest import bits_equal
+
+pytestmark = pytest.mark.gpu
+
+F = np.float32
+
+
+@pytest.fixture(scope="module")
+def synth(rt):
+    return import_module("rtb200.synth")
+
+
+def _camera_rays(ps, rng, n, jitter=30.0, lo=(-400, -40, -400), hi=(400, 360, 400)):
+    cam = np.asarray(ps.frame["cam_pos"], F)
+    org = (cam + rng.uniform(-jitter, jitter, (n, 3))).astype(F)
+    tgt = rng.uniform(lo, hi, (n, 3)).astype(F)
+    d = tgt - org
+    return org, (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(F)
+
+
+def _compare_queries(rt, r, ps, org, d, pts, lights):
+    idx_b, t_b, n_b = r.trace_nearest(org, d, flags=rt.F_FORCE_STREAM)
+    idx_v, t_v, n_v = r.trace_nearest(org, d, flags=rt.F_USE_BVH)
+    assert np.array_equal(idx_b, idx_v)
+    assert bits_equal(t_b, t_v) and bits_equal(n_b, n_v)
+    f_b = r.trace_shadow(pts, lights, flags=rt.F_FORCE_STREAM)
+    f_v = r.trace_shadow(pts, lights, flags=rt.F_USE_BVH)
+    assert bits_equal(f_b, f_v)
+    return idx_b, f_b
+
+
+def test_bvh_requires_build(rt, renderer, synth):
+    ps = synth.soup(200, 2, 1, seed=1)
+    renderer.set_scene(ps)                       # a new scene invalidates any earlier LBVH
+    fr = rt.make_frame(ps.frame, 32, 32, max_bounces=1, flags=rt.F_USE_BVH)
+    with pytest.raises(rt.RtError) as e:
+        renderer.render(fr)
+    assert e.value.status == -6
+
+
+def test_soup_queries_equal_brute_force(rt, renderer, port, synth):
+    ps = synth.soup(6000, 16, 2, seed=11)
+    renderer.set_scene(ps)
+    info = renderer.build_bvh()
+    assert info["triangles"] == 6000 and info["nodes"] == 5999
+    rng = np.random.default_rng(4)
+    n = 65536
+    org, d = _camera_rays(ps, rng, n)
+    pts = rng.uniform(-300, 300, (n, 3)).astype(F)
+    lights = np.tile(ps["lights"][0, 0:3], (n, 1)).astype(F)
+    idx, filt = _compare_queries(rt, renderer, ps, org, d, pts, lights)
+    assert (idx >= 0).mean() > 0.3 and (filt == 0).any() and (filt == 1).any()
+    # and against the CPU oracle (the restated linear scan) on a subset
+    m = 8192
+    widx, wt, _ = port.nearest(ps, org[:m], d[:m], threads=port.max_threads)
+    assert np.array_equal(idx[:m], widx)
+
+
+def test_heightfield_frame_equals_brute_force(rt, renderer, port, synth):
+    ps = synth.heightfield(30000, 400.0, 3, seed=21)
+    renderer.set_scene(ps)
+    renderer.build_bvh()
+    W, H = 192, 108
+    fr_b = rt.make_frame(ps.frame, W, H, max_bounces=3, flags=rt.F_FORCE_STREAM)
+    fr_v = rt.make_frame(ps.frame, W, H, max_bounces=3, flags=rt.F_USE_BVH)
+    a, a8, st_a = renderer.render(fr_b)
+    b, b8, st_b = renderer.render(fr_v)
+    assert st_a.path == 1 and st_b.path == 2
+    assert bits_equal(a, b) and np.array_equal(a8, b8)
+    assert (st_a.rays_shadow, st_a.rays_reflect, st_a.rays_refract) == (st_b.rays_shadow, st_b.rays_reflect, st_b.rays_refract)
+    assert st_b.bvh_nodes_visited > 0 and 0 < st_b.tests_triangle < st_a.tests_triangle / 50
+    want, _ = port.render(ps, fr_b, threads=port.max_threads)
+    assert np.allclose(b, want, rtol=0, atol=4e-6)
+
+
+def test_supersampled_bvh_frame(rt, renderer, synth):
+    ps = synth.heightfield(8000, 300.0, 2, seed=5)
+    renderer.set_scene(ps)
+    renderer.build_bvh()
+    a, _, _ = renderer.render(rt.make_frame(ps.frame, 64, 48, max_bounces=2, spp_grid=4, flags=rt.F_FORCE_STREAM))
+    b, _, st = renderer.render(rt.make_frame(ps.frame, 64, 48, max_bounces=2, spp_grid=4, flags=rt.F_USE_BVH))
+    assert bits_equal(a, b) and st.rays_primary == 64 * 48 * 16
+
+
+def test_coplanar_duplicates_lowest_order_wins(rt, renderer, synth):
+    """Adversarial: every triangle exists 3 times (identical vertices); the linear scan keeps the
+    first one (strict <, Scene.cpp:1713), so must the LBVH, whatever order it visits them in."""
+    base = synth.soup(1500, 0, 1, seed=3)
+    tri = np.concatenate([base["tri_points"]] * 3)
+    rng = np.random.default_rng(8)
+    perm = rng.permutation(len(tri))
+    tri = tri[perm]
+    T = len(tri)
+    arrays = {k: base[k] for k in ("quad_coef", "quad_material", "plane_coef", "plane_material", "materials", "lights")}
+    arrays.update({"tri_points": tri, "tri_normal": synth.face_normals(tri),
+                   "tri_material": rng.integers(0, len(base["materials"]), T).astype(np.int32),
+                   "tri_order": np.arange(T, dtype=np.int32), "quad_order": np.zeros(0, np.int32),
+                   "plane_order": np.array([T], np.int32)})
+    ps = rt.PackedScene(arrays, base.frame)
+    renderer.set_scene(ps)
+    renderer.build_bvh()
+    org, d = _camera_rays(ps, rng, 40000)
+    pts = rng.uniform(-300, 300, (40000, 3)).astype(F)
+    lights = np.tile(ps["lights"][0, 0:3], (40000, 1)).astype(F)
+    idx, _ = _compare_queries(rt, renderer, ps, org, d, pts, lights)
+    hit = idx[(idx >= 0) & (idx < T)]
+    assert len(hit) > 1000
+    # a winner is always the lowest-order copy of its geometry
+    first_copy = {}
+    for o, src in enumerate(perm % 1500):
+        first_copy.setdefault(int(src), o)
+    assert all(first_copy[int(perm[i] % 1500)] == int(i) for i in hit[:5000])
+
+
+@pytest.mark.parametrize("n_tris", [1, 3, 4, 5, 9])
+def test_tiny_scenes(rt, renderer, synth, n_tris):
+    ps = synth.soup(n_tris, 2, 1, seed=40 + n_tris, radius=120.0)
+    renderer.set_scene(ps)
+    renderer.build_bvh()
+    rng = np.random.default_rng(n_tris)
+    org, d = _camera_rays(ps, rng, 20000)
+    pts = rng.uniform(-300, 300, (20000, 3)).astype(F)
+    lights = np.tile(ps["lights"][0, 0:3], (20000, 1)).astype(F)
+    _compare_queries(rt, renderer, ps, org, d, pts, lights)
+
+
+def test_stacked_transparent_occluders_keep_scan_order(rt, renderer, synth):
+    """Shadow rays through several transparent triangles: the product of colour*kt must be taken
+    in insertion order (Scene.cpp:1856), not in traversal order."""
+    rng = np.random.default_rng(12)
+    n_layers = 6
+    tri = []
+    for i in range(n_layers):                 # big horizontal triangles stacked at y = 10, 20, ...
+        y = 10.0 * (i + 1)
+        tri.append([-500, y, -500, 500, y, -500, 0, y, 700])
+    tri = np.asarray(tri, F)
+    tri = tri[rng.permutation(n_layers)]
+    mats = np.zeros((n_layers + 1, 10), F)
+    mats[:, 0:3] = rng.uniform(0.3, 0.97, (n_layers + 1, 3))
+    mats[:, 3], mats[:, 4] = 0.2, 0.8
+    mats[:n_layers, 8], mats[:n_layers, 9] = rng.uniform(0.5, 0.95, n_layers), 1.3
+    # enough extra small triangles that the tree has internal nodes
+    extra = synth.soup(300, 0, 1, seed=2)["tri_points"]
+    extra[:, 1::3] += 400.0
+    allt = np.concatenate([tri, extra]).astype(F)
+    T = len(allt)
+    tm = np.concatenate([np.arange(n_layers), np.full(len(extra), n_layers)]).astype(np.int32)
+    arrays = {"tri_points": allt, "tri_normal": synth.face_normals(allt), "tri_material": tm,
+              "tri_order": np.arange(T, dtype=np.int32),
+              "quad_coef": np.zeros((0, 10), F), "quad_material": np.zeros(0, np.int32), "quad_order": np.zeros(0, np.int32),
+              "plane_coef": np.array([[0, 1, 0, 45.0]], F), "plane_material": np.array([n_layers], np.int32),
+              "plane_order": np.array([T], np.int32), "materials": mats,
+              "lights": np.array([[0, 300, 0, 1, 1, 1, 1.0]], F)}
+    base = synth.soup(10, 0, 1, seed=1)
+    ps = rt.PackedScene(arrays, base.frame)
+    renderer.set_scene(ps)
+    renderer.build_bvh()
+    n = 4096
+    pts = np.stack([rng.uniform(-100, 100, n), np.full(n, 1.0), rng.uniform(-100, 100, n)], axis=1).astype(F)
+    lights = np.tile(np.array([0, 300, 0], F), (n, 1))
+    f_b = renderer.trace_shadow(pts, lights, flags=rt.F_FORCE_STREAM)
+    f_v = renderer.trace_shadow(pts, lights, flags=rt.F_USE_BVH)
+    assert bits_equal(f_b, f_v)
+    assert ((f_b > 0) & (f_b < 0.7)).all()       # all six layers filtered the light
