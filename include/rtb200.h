@@ -143,8 +143,11 @@ typedef struct rtb200_stats {
     uint32_t depth_levels;         /* wavefront levels that held at least one ray                     */
     uint32_t path;                 /* 0 = scene-resident fused kernels, 1 = streamed tiled kernels, 2 = LBVH */
     uint32_t chunks;               /* image chunks the frame was split into                           */
-    double   ms_trace_nearest, ms_trace_shadow, ms_shade;  /* streamed path: per-stage totals; resident   */
-                                   /* path: ms_trace_nearest = the level-0 fused kernel (first chunk)     */
+    double   ms_trace_nearest, ms_trace_shadow, ms_shade;  /* streamed / LBVH path: per-stage device  */
+                                   /* totals over all levels and chunks (resident path: the fused kernels) */
+    double   ms_primary_kernel;    /* the level-0 nearest-hit (or fused resident) kernel of the first chunk */
+    uint64_t shadow_tests_triangle;/* part of tests_triangle entered by shadow-filter queries              */
+    uint64_t shadow_bvh_nodes;     /* part of bvh_nodes_visited entered by shadow-filter queries           */
 } rtb200_stats;
 
 typedef struct rtb200_ctx rtb200_ctx;
@@ -207,6 +210,10 @@ void rtb200_host_free(void* p);
 int  rtb200_measure_fp32_peak(rtb200_ctx* ctx, double* tflops, double* sm_mhz);
 /* Device properties the benchmark reports. */
 int  rtb200_device_info(rtb200_ctx* ctx, int* sm_count, int* l2_bytes, char* name, int name_len);
+/* Device-side stopwatch over SEVERAL calls (benchmarks time K frames as one region): records a
+ * CUDA event on the context's stream in slot 0..3; elapsed = slot b - slot a in milliseconds. */
+int  rtb200_timer_mark(rtb200_ctx* ctx, int slot);
+int  rtb200_timer_elapsed(rtb200_ctx* ctx, int slot_a, int slot_b, double* ms);
 
 #ifdef __cplusplus
 }

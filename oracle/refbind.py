@@ -81,6 +81,20 @@ class RefRenderer:
         ALREADY final -- transforms are identity) through the reference's public API, in
         insertion order."""
         T, Q, P = len(ps["tri_order"]), len(ps["quad_order"]), len(ps["plane_order"])
+        if T > 1000 and np.array_equal(ps["tri_order"], np.arange(T)):
+            # large synthetic meshes: the triangles come first in insertion order -> one bulk call
+            self.lib.ref_add_triangles(T, np.ascontiguousarray(ps["tri_points"], np.float32).reshape(-1),
+                                       np.ascontiguousarray(ps["materials"], np.float32).reshape(-1),
+                                       np.ascontiguousarray(ps["tri_material"], np.int32))
+            rest = {k: ps[k] for k in ("quad_order", "quad_coef", "quad_material", "plane_order", "plane_coef", "plane_material", "materials", "lights")}
+            rest.update({"tri_order": np.zeros(0, np.int32), "tri_points": np.zeros((0, 9), np.float32), "tri_material": np.zeros(0, np.int32)})
+            self._add_items(rest)
+            assert T + Q + P == self.lib.ref_num_surfaces()
+            return
+        self._add_items(ps)
+        assert T + Q + P == self.lib.ref_num_surfaces()
+
+    def _add_items(self, ps):
         items = [(int(o), 0, i) for i, o in enumerate(ps["tri_order"])]
         items += [(int(o), 1, i) for i, o in enumerate(ps["quad_order"])]
         items += [(int(o), 2, i) for i, o in enumerate(ps["plane_order"])]
@@ -99,7 +113,6 @@ class RefRenderer:
         lights = np.ascontiguousarray(ps["lights"], np.float32).reshape(-1, 7)
         for l in lights:
             self.lib.ref_add_light(np.ascontiguousarray(l[0:3]), np.ascontiguousarray(l[3:6]), float(l[6]))
-        assert T + Q + P == self.lib.ref_num_surfaces()
 
     # -- rendering ---------------------------------------------------------------------
     def render_full(self, W, H):

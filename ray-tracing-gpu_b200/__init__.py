@@ -23,6 +23,7 @@ EXPORTS = [
     "rtb200_set_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_read_frame",
     "rtb200_trace_nearest", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init",
     "rtb200_host_alloc", "rtb200_host_free", "rtb200_measure_fp32_peak", "rtb200_device_info",
+    "rtb200_timer_mark", "rtb200_timer_elapsed",
 ]
 
 _lib = None
@@ -64,6 +65,8 @@ def lib():
         L.rtb200_host_free.restype = None
         L.rtb200_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.rtb200_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_char_p, C.c_int]
+        L.rtb200_timer_mark.argtypes = [vp, C.c_int]
+        L.rtb200_timer_elapsed.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -134,6 +137,14 @@ class Renderer:
         tf, mhz = C.c_double(), C.c_double()
         self._check(self.L.rtb200_measure_fp32_peak(self.h, C.byref(tf), C.byref(mhz)))
         return tf.value, mhz.value
+
+    def timer_mark(self, slot):
+        self._check(self.L.rtb200_timer_mark(self.h, slot))
+
+    def timer_elapsed(self, a, b):
+        ms = C.c_double()
+        self._check(self.L.rtb200_timer_elapsed(self.h, a, b, C.byref(ms)))
+        return ms.value
 
     def set_scene(self, ps):
         self._scene = ps                       # keep the arrays alive during the call

@@ -97,6 +97,7 @@ int rtb200_create(int device_id, rtb200_ctx** out)
     }
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return create_fail(ctx, "cudaStreamCreate");
     for (auto& ev : ctx->ev) if (cudaEventCreate(&ev) != cudaSuccess) return create_fail(ctx, "cudaEventCreate");
+    for (auto& ev : ctx->timer) if (cudaEventCreate(&ev) != cudaSuccess) return create_fail(ctx, "cudaEventCreate");
     if (resident_prepare(ctx->smem_optin - 2048) != cudaSuccess) return create_fail(ctx, "cudaFuncSetAttribute(max dynamic smem)");
     *out = ctx;
     return RTB200_OK;
@@ -116,6 +117,7 @@ void rtb200_destroy(rtb200_ctx* ctx)
     for (auto& l : ctx->levels) { l.od0.release(); l.od1.release(); l.colour.release(); l.links.release(); }
     ctx->q_in0.release(); ctx->q_in1.release(); ctx->q_out0.release(); ctx->q_out1.release(); ctx->q_out2.release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->timer) if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -136,6 +138,25 @@ int rtb200_device_info(rtb200_ctx* ctx, int* sm_count, int* l2_bytes, char* name
     if (sm_count) *sm_count = ctx->sm_count;
     if (l2_bytes) *l2_bytes = ctx->l2_bytes;
     if (name && name_len > 0) snprintf(name, (size_t)name_len, "%s", ctx->name);
+    return RTB200_OK;
+}
+
+int rtb200_timer_mark(rtb200_ctx* ctx, int slot)
+{
+    if (!ctx || slot < 0 || slot >= 4) return RTB200_E_ARG;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventRecord(ctx->timer[slot], ctx->stream));
+    return RTB200_OK;
+}
+
+int rtb200_timer_elapsed(rtb200_ctx* ctx, int a, int b, double* ms)
+{
+    if (!ctx || !ms || a < 0 || a >= 4 || b < 0 || b >= 4) return RTB200_E_ARG;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventSynchronize(ctx->timer[b]));
+    float t = 0.f;
+    CU(cudaEventElapsedTime(&t, ctx->timer[a], ctx->timer[b]));
+    *ms = t;
     return RTB200_OK;
 }
 
@@ -438,7 +459,7 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
     st->depth_levels = max_level_seen;
     st->chunks = chunks;
     st->path = 0;
-    st->ms_trace_nearest = -1.0;                               // filled by the caller after the final sync
+    st->ms_primary_kernel = -1.0;                              // filled by the caller after the final sync
     // brute force by construction: every nearest-hit query and every shadow query that is not
     // cut short by the all-zero early-out tests every surface; counted exactly on the host
     return RTB200_OK;
@@ -521,10 +542,11 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
     st.ms_render = ms;
-    if (st.ms_trace_nearest < 0.0) {                           // level-0 fused kernel of the first chunk
+    if (st.ms_primary_kernel < 0.0) {                          // level-0 kernel of the first chunk
         float k0 = 0.f;
         CU(cudaEventElapsedTime(&k0, ctx->ev[2], ctx->ev[3]));
-        st.ms_trace_nearest = k0;
+        st.ms_primary_kernel = k0;
+        if (st.path == 0) st.ms_trace_nearest = k0;
     }
     unsigned long long sum[ST_COUNT] = {0};
     for (int s = 0; s < RT_STAT_SLOTS; ++s) for (int c = 0; c < ST_COUNT; ++c) sum[c] += h_st[s * ST_COUNT + c];
@@ -539,10 +561,12 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
         st.tests_quadric  = (uint64_t)llround((double)sum[ST_TEST_TRI] * ctx->ds.n_quad / n);
         st.tests_plane    = (uint64_t)llround((double)sum[ST_TEST_TRI] * ctx->ds.n_plane / n);
     } else {
-        st.tests_triangle = sum[ST_TEST_TRI] + ctx->host_tests[0];
+        st.shadow_tests_triangle = sum[ST_TEST_TRI_SHADOW];
+        st.shadow_bvh_nodes = sum[ST_BVH_NODES_SHADOW];
+        st.tests_triangle = sum[ST_TEST_TRI] + sum[ST_TEST_TRI_SHADOW] + ctx->host_tests[0];
         st.tests_quadric = sum[ST_TEST_QUAD] + ctx->host_tests[1];
         st.tests_plane = sum[ST_TEST_PLANE] + ctx->host_tests[2];
-        st.bvh_nodes_visited = sum[ST_BVH_NODES];
+        st.bvh_nodes_visited = sum[ST_BVH_NODES] + sum[ST_BVH_NODES_SHADOW];
         if (sum[ST_BVH_OVERFLOW]) return fail(ctx, RTB200_E_CAPACITY, "LBVH traversal stack overflow");
     }
     st.kernel_launches = launches;

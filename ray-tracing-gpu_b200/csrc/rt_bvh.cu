@@ -44,7 +44,7 @@ struct BvhState {
     bool   built = false;
     float  lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};   // vertex bounds of the triangles
     float  radius = 0.f;                           // R the boxes are padded for
-    float  padc = 4.0f;
+    float  padc = 1.0f;                            // PADC; RTB200_BVH_PADC overrides
     double build_ms = 0.0, refit_ms = 0.0;
     unsigned refits = 0;
 };
@@ -441,8 +441,8 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
     }
     if (lane == 0 && p.stats) {
         unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
-        if (n_nodes) atomicAdd(&st[ST_BVH_NODES], (unsigned long long)n_nodes);
-        if (n_tests) atomicAdd(&st[ST_TEST_TRI], (unsigned long long)n_tests);
+        if (n_nodes) atomicAdd(&st[ST_BVH_NODES_SHADOW], (unsigned long long)n_nodes);
+        if (n_tests) atomicAdd(&st[ST_TEST_TRI_SHADOW], (unsigned long long)n_tests);
         if (n_side_q) atomicAdd(&st[ST_TEST_QUAD], (unsigned long long)n_side_q);
         if (n_side_p) atomicAdd(&st[ST_TEST_PLANE], (unsigned long long)n_side_p);
         if (overflow) atomicAdd(&st[ST_BVH_OVERFLOW], 1ull);
@@ -575,10 +575,11 @@ int bvh_build(rtb200_ctx* c)
     } else if (T > 0) {
         BCU(cudaMemcpyAsync(b->tri_sorted.p, c->ds.tri, sizeof(TriRec) * (size_t)T, cudaMemcpyDeviceToDevice, c->stream));
     }
-    // default radius: origins anywhere within one scene diagonal of the box (refitted on demand)
+    // default radius: origins anywhere inside the triangles' bounds (secondary and shadow rays start
+    // on surfaces); a camera farther out triggers one refit (bvh_prepare)
     const float dx = b->hi[0] - b->lo[0], dy = b->hi[1] - b->lo[1], dz = b->hi[2] - b->lo[2];
     const float diag = T > 0 ? sqrtf(dx * dx + dy * dy + dz * dz) : 0.f;
-    int rc = bvh_refit(c, b, 2.0f * diag);
+    int rc = bvh_refit(c, b, diag);
     if (rc != RTB200_OK) return rc;
     BCU(cudaEventRecord(ev1, c->stream));
     BCU(cudaStreamSynchronize(c->stream));
@@ -610,12 +611,10 @@ int bvh_prepare(rtb200_ctx* c, const float* origins3, int n)
         }
         if (std::isfinite(d2)) need = std::max(need, std::sqrt(d2));
     }
-    // secondary and shadow rays start on the scene's surfaces; planes and quadrics can lie outside
-    // the triangle bounds, so keep at least the default of two diagonals
     if (need <= b->radius) return RTB200_OK;
     cudaEvent_t ev0 = c->ev[2], ev1 = c->ev[3];
     BCU(cudaEventRecord(ev0, c->stream));
-    int rc = bvh_refit(c, b, need * 1.25f);
+    int rc = bvh_refit(c, b, need * 1.1f);
     if (rc != RTB200_OK) return rc;
     BCU(cudaEventRecord(ev1, c->stream));
     BCU(cudaStreamSynchronize(c->stream));

@@ -64,6 +64,7 @@ struct rtb200_ctx {
     char name[128] = {0};
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t timer[4] = {nullptr, nullptr, nullptr, nullptr};   // rtb200_timer_mark
     std::string last_error;
 
     // scene

@@ -30,6 +30,7 @@ namespace rtb {
 
 struct StreamBufs {                // per-context scratch of the streamed path (lives in the ctx levels + these)
     DevBuf hit, hitP, hitN, q_base, sq0, sq1, filter;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // per-stage stopwatch
 };
 
 static StreamBufs* stream_bufs(rtb200_ctx* c)
@@ -43,6 +44,7 @@ void stream_release(rtb200_ctx* c)
     if (!c->stream_scratch) return;
     StreamBufs* b = static_cast<StreamBufs*>(c->stream_scratch);
     b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->filter.release();
+    for (auto& e : b->ev) if (e) cudaEventDestroy(e);
     delete b;
     c->stream_scratch = nullptr;
 }
@@ -77,8 +79,20 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     unsigned max_level_seen = 0, chunks = 0;
     unsigned long long rays_nearest = 0;
     cudaEvent_t ev_a = c->ev[2], ev_b = c->ev[3];
-    double ms_nearest = 0.0, ms_shadow = 0.0;
     bool timed_first = false;
+    // per-stage device time: E0 nearest E1 shade-A E2 | host reads the counters | E3 shadow E4 shade-B E5;
+    // the second triple is read after the NEXT synchronisation point
+    for (auto& ev : sb->ev) if (!ev) SCU(cudaEventCreate(&ev));
+    cudaEvent_t* E = sb->ev;
+    double ms_nearest = 0.0, ms_shadow = 0.0, ms_shade = 0.0;
+    bool pending_b = false;
+    auto flush_b = [&]() {
+        if (!pending_b) return;
+        float a = 0.f, b = 0.f;
+        if (cudaEventElapsedTime(&a, E[3], E[4]) == cudaSuccess) ms_shadow += a;
+        if (cudaEventElapsedTime(&b, E[4], E[5]) == cudaSuccess) ms_shade += b;
+        pending_b = false;
+    };
 
     for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunks) {
         const int rows = std::min(rows_per_chunk, local_LH - ly0);
@@ -115,9 +129,11 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             tp.n_rays = n_in; tp.hit = sb->hit.as<float2>(); tp.mode = mode;
             const bool timed = !timed_first && level == 0;
             if (timed) SCU(cudaEventRecord(ev_a, c->stream));
+            SCU(cudaEventRecord(E[0], c->stream));
             tp.stats = c->stats.as<unsigned long long>();
             if (use_bvh) SCU(launch_bvh_nearest(tp, c->stream));
             else         SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
+            SCU(cudaEventRecord(E[1], c->stream));
             if (timed) { SCU(cudaEventRecord(ev_b, c->stream)); timed_first = true; }
             ++*launches;
             rays_nearest += (unsigned long long)n_in;
@@ -136,12 +152,21 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             sa.stats = c->stats.as<unsigned long long>();
             sa.exact = exact ? 1 : 0;
             SCU(launch_shade_a(sa, c->stream));
+            SCU(cudaEventRecord(E[2], c->stream));
             ++*launches;
             SCU(cudaMemcpyAsync(h_cnt, d_cnt + 4 * level, 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
             SCU(cudaStreamSynchronize(c->stream));
+            flush_b();
+            {
+                float a = 0.f, b = 0.f;
+                SCU(cudaEventElapsedTime(&a, E[0], E[1]));
+                SCU(cudaEventElapsedTime(&b, E[1], E[2]));
+                ms_nearest += a; ms_shade += b;
+            }
             const int n_children = (int)h_cnt[0], n_lk = (int)h_cnt[1], n_sq = (int)h_cnt[2];
             st->rays_shadow += (uint64_t)n_sq;
             // ---- shadow filters --------------------------------------------------------------
+            SCU(cudaEventRecord(E[3], c->stream));
             if (n_sq > 0) {
                 ShadowParams sp;
                 memset(&sp, 0, sizeof sp);
@@ -151,6 +176,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 else         SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
                 ++*launches;
             }
+            SCU(cudaEventRecord(E[4], c->stream));
             // ---- shade B -------------------------------------------------------------------------
             ShadeBParams sbp;
             memset(&sbp, 0, sizeof sbp);
@@ -160,6 +186,8 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             sbp.hitP = sa.hitP; sbp.hitN = sa.hitN; sbp.q_base = sa.q_base; sbp.filter = sb->filter.as<float4>();
             sbp.c0 = c->c0.as<float>(); sbp.colour = cur.colour.as<float4>(); sbp.exact = exact ? 1 : 0;
             SCU(launch_shade_b(sbp, c->stream));
+            SCU(cudaEventRecord(E[5], c->stream));
+            pending_b = true;
             ++*launches;
             n_links.push_back(spawn ? n_lk : 0);
             if (!spawn) { ++level; break; }
@@ -187,11 +215,13 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
         SCU(launch_resolve(r, c->stream));
         ++*launches;
     }
-    (void)ms_nearest; (void)ms_shadow;
+    SCU(cudaStreamSynchronize(c->stream));
+    flush_b();
+    st->ms_trace_nearest = ms_nearest; st->ms_trace_shadow = ms_shadow; st->ms_shade = ms_shade;
     st->depth_levels = max_level_seen;
     st->chunks = chunks;
     st->path = use_bvh ? 2 : 1;
-    st->ms_trace_nearest = -1.0;              // first level-0 nearest-hit launch, read after the final sync
+    st->ms_primary_kernel = -1.0;             // first level-0 nearest-hit launch, read after the final sync
     // nearest-hit queries test every surface by construction (no early-out): exact host-side count;
     // shadow queries are counted on the device (warps leave early once their filters are zero)
     c->host_tests[0] = use_bvh ? 0ull : rays_nearest * (unsigned long long)c->ds.n_tri;   // LBVH: counted on the device

@@ -359,7 +359,7 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
     }
     if ((tid & 31) == 0) {
         unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
-        if (tests_tri) atomicAdd(&st[ST_TEST_TRI], tests_tri);
+        if (tests_tri) atomicAdd(&st[ST_TEST_TRI_SHADOW], tests_tri);
         if (tests_side_q) atomicAdd(&st[ST_TEST_QUAD], tests_side_q);
         if (tests_side_p) atomicAdd(&st[ST_TEST_PLANE], tests_side_p);
     }

@@ -69,6 +69,6 @@ for pc in padcs:
         frames.append({"ms": st.ms_render, "Mrays": st.rays / 1e6, "Mrays_per_s": st.rays / st.ms_render / 1e3,
                        "rays": [st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract], "levels": st.depth_levels, "chunks": st.chunks,
                        "launches": st.kernel_launches, "nodes_per_ray": st.bvh_nodes_visited / max(st.rays, 1), "tri_tests_per_ray": st.tests_triangle / max(st.rays, 1),
-                       "traversal_GBs": byts / st.ms_render / 1e6, "frac_of_hbm": byts / st.ms_render / 1e6 / hbm, "k_nearest_l0_ms": st.ms_trace_nearest})
+                       "traversal_GBs": byts / st.ms_render / 1e6, "frac_of_hbm": byts / st.ms_render / 1e6 / hbm, "k_nearest_l0_ms": st.ms_primary_kernel})
     out["frames"] = frames
     print(json.dumps(out), flush=True)

@@ -23,5 +23,5 @@ for i in range(a.frames):
     print(json.dumps({"frame": i, "ms": st.ms_render, "Mrays": st.rays / 1e6, "Mrays_per_s": st.rays / st.ms_render / 1e3,
                       "rays": [st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract], "levels": st.depth_levels,
                       "launches": st.kernel_launches, "TFLOPs_alg": flop / st.ms_render / 1e9, "frac_of_peak": flop / st.ms_render / 1e9 / peak,
-                      "k_nearest_l0_ms": st.ms_trace_nearest, "k_nearest_l0_TFLOPs": prim_flop / st.ms_trace_nearest / 1e9,
-                      "k_nearest_l0_frac": prim_flop / st.ms_trace_nearest / 1e9 / peak, "peak": peak}))
+                      "k_nearest_l0_ms": st.ms_primary_kernel, "k_nearest_l0_TFLOPs": prim_flop / st.ms_primary_kernel / 1e9,
+                      "k_nearest_l0_frac": prim_flop / st.ms_primary_kernel / 1e9 / peak, "peak": peak}))
