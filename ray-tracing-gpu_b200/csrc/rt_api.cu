@@ -98,6 +98,9 @@ int rtb200_create(int device_id, rtb200_ctx** out)
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return create_fail(ctx, "cudaStreamCreate");
     for (auto& ev : ctx->ev) if (cudaEventCreate(&ev) != cudaSuccess) return create_fail(ctx, "cudaEventCreate");
     for (auto& ev : ctx->timer) if (cudaEventCreate(&ev) != cudaSuccess) return create_fail(ctx, "cudaEventCreate");
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return create_fail(ctx, "cudaStreamCreate");
+    for (int i = 0; i < 4; ++i)
+        if (cudaEventCreateWithFlags(&ctx->copy_ev[i], i < 2 ? cudaEventDisableTiming : cudaEventDefault) != cudaSuccess) return create_fail(ctx, "cudaEventCreate");
     if (resident_prepare(ctx->smem_optin - 2048) != cudaSuccess) return create_fail(ctx, "cudaFuncSetAttribute(max dynamic smem)");
     *out = ctx;
     return RTB200_OK;
@@ -118,6 +121,8 @@ void rtb200_destroy(rtb200_ctx* ctx)
     ctx->q_in0.release(); ctx->q_in1.release(); ctx->q_out0.release(); ctx->q_out1.release(); ctx->q_out2.release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->timer) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->copy_ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -215,6 +220,8 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
     const size_t off_plane = off_quad + sizeof(QuadRec) * (size_t)Q;
     const size_t total = align16(off_plane + sizeof(PlaneRec) * (size_t)P) + 16;
 
+    // the previous upload may still be reading the staging buffer (uploads are asynchronous)
+    if (ctx->upload_pending) { CU(cudaEventSynchronize(ctx->ev[5])); ctx->upload_pending = false; }
     cudaError_t e = ctx->stage.ensure(total);
     if (e != cudaSuccess) return set_cuda_error(ctx, e, "pinned staging");
     e = ctx->scene_buf.ensure(total);
@@ -301,10 +308,8 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
     CU(cudaEventRecord(ctx->ev[4], ctx->stream));
     CU(cudaMemcpyAsync(ctx->scene_buf.p, h, total, cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaEventRecord(ctx->ev[5], ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
-    float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, ctx->ev[4], ctx->ev[5]));
-    ctx->last_h2d_ms = ms;
+    ctx->upload_pending = true;                 // stream-ordered: every later kernel sees the new scene; the
+                                                // caller's arrays were already copied into the staging buffer
 
     const unsigned char* d = ctx->scene_buf.as<unsigned char>();
     DeviceScene& ds = ctx->ds;
@@ -360,6 +365,27 @@ static void fill_frame_params(const rtb200_frame* fr, int n_ranks, int rank, Fra
     f.n_ranks = n_ranks; f.rank = rank;
 }
 
+// Overlapped read-back: called after the kernel that finished pixel rows [py0, py0 + prows) of the
+// local frame.  The copy stream waits for that kernel only, so the transfer of chunk i runs under
+// the rendering of chunk i + 1 (PCIe and the SMs work at the same time).
+namespace rtb {
+int chunk_copy_out(rtb200_ctx* ctx, int W, int py0, int prows)
+{
+    if ((!ctx->host_f32 && !ctx->host_rgba8) || prows <= 0) return RTB200_OK;
+    cudaEvent_t done = ctx->copy_ev[ctx->copy_chunks & 1];
+    CU(cudaEventRecord(done, ctx->stream));
+    CU(cudaStreamWaitEvent(ctx->copy_stream, done, 0));
+    if (ctx->copy_chunks == 0) CU(cudaEventRecord(ctx->copy_ev[2], ctx->copy_stream));
+    const size_t off = (size_t)py0 * W, n = (size_t)prows * W;
+    if (ctx->host_f32)
+        CU(cudaMemcpyAsync(ctx->host_f32 + 3 * off, ctx->fb_f32.as<float>() + 3 * off, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (ctx->host_rgba8)
+        CU(cudaMemcpyAsync(ctx->host_rgba8 + 4 * off, ctx->fb_rgba8.as<unsigned char>() + 4 * off, n * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    ++ctx->copy_chunks;
+    return RTB200_OK;
+}
+}
+
 // scene-resident path: one fused kernel per level, host reads the child count between levels
 static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
                            bool exact, rtb200_stats* st, uint32_t* launches)
@@ -373,6 +399,12 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
     int rows_per_chunk = (int)((MAX_CHUNK_SAMPLES / (unsigned)fp.LW) / (16u * k)) * 16 * k;
     if (rows_per_chunk < 16 * k) rows_per_chunk = 16 * k;
     if (rows_per_chunk > local_LH) rows_per_chunk = ((local_LH + 16 * k - 1) / (16 * k)) * 16 * k;
+    if (ctx->host_f32 || ctx->host_rgba8) {
+        // overlapped read-back: about 8 chunks per frame, never smaller than 64 pixel rows
+        int want = (((local_rows + 7) / 8 + 15) / 16) * 16;
+        if (want < 64) want = 64;
+        if (want * k < rows_per_chunk) rows_per_chunk = want * k;
+    }
 
     cudaError_t e;
     if ((e = ctx->c0.ensure(sizeof(float) * 3 * (size_t)rows_per_chunk * fp.LW)) != cudaSuccess) return set_cuda_error(ctx, e, "c0");
@@ -385,10 +417,11 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
 
     for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunks) {
         const int rows = std::min(rows_per_chunk, local_LH - ly0);
-        CU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, ctx->stream));
+        if (children > 0) CU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, ctx->stream));
         std::vector<int> n_rays, n_links;
         n_rays.push_back(rows * fp.LW);
         int level = 0;
+        bool resolved = false;
         for (;; ++level) {
             const int n_in = n_rays[level];
             if (n_in == 0) break;
@@ -417,9 +450,14 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
             p.out_count = d_cnt + 2 * level; p.link_count = d_cnt + 2 * level + 1;
             p.links = cur.links.as<int4>();
             p.stats = ctx->stats.as<unsigned long long>();
+            // no secondary rays and no supersampling: the level-0 kernel is the whole frame
+            const bool direct = (level == 0 && !spawn && k == 1);
+            p.direct = direct ? 1 : 0;
+            p.fb_f32 = ctx->out_f32_dev; p.fb_rgba8 = ctx->out_rgba8_dev;
             const bool timed = (level == 0 && ly0 == 0);       // dominant kernel, timed on its own stream
             if (timed) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
-            CU(launch_resident_level(p, exact, ctx->stream));
+            CU(launch_resident_level(p, exact, ctx->sm_count, ctx->stream));
+            if (direct) resolved = true;
             if (timed) CU(cudaEventRecord(ctx->ev[3], ctx->stream));
             ++*launches;
             if (!spawn) { n_links.push_back(0); ++level; break; }
@@ -444,17 +482,24 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
             CU(launch_combine(c, exact, ctx->stream));
             ++*launches;
         }
-        ResolveParams r;
-        memset(&r, 0, sizeof r);
-        r.f = fp;
-        r.c0 = ctx->c0.as<float>();
-        r.chunk_py0 = ly0 / k;
-        r.chunk_prows = std::min(rows / k, local_rows - r.chunk_py0);
-        r.fb_f32 = ctx->fb_f32.as<float>();
-        r.fb_rgba8 = ctx->fb_rgba8.as<uchar4>();
-        r.stats = ctx->stats.as<unsigned long long>();
-        CU(launch_resolve(r, ctx->stream));
-        ++*launches;
+        if (!resolved) {
+            ResolveParams r;
+            memset(&r, 0, sizeof r);
+            r.f = fp;
+            r.c0 = ctx->c0.as<float>();
+            r.chunk_py0 = ly0 / k;
+            r.chunk_prows = std::min(rows / k, local_rows - r.chunk_py0);
+            r.fb_f32 = ctx->out_f32_dev;
+            r.fb_rgba8 = ctx->out_rgba8_dev;
+            r.stats = ctx->stats.as<unsigned long long>();
+            CU(launch_resolve(r, ctx->stream));
+            ++*launches;
+        }
+        {
+            const int py0 = ly0 / k;
+            const int rc2 = chunk_copy_out(ctx, fp.W, py0, std::min(rows / k, local_rows - py0));
+            if (rc2 != RTB200_OK) return rc2;
+        }
     }
     st->depth_levels = max_level_seen;
     st->chunks = chunks;
@@ -507,7 +552,27 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
     if ((e = ctx->stats.ensure(stat_bytes)) != cudaSuccess) return set_cuda_error(ctx, e, "stats");
     if ((e = ctx->h_small.ensure(8192)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
-    CU(cudaMemsetAsync(ctx->stats.p, 0, stat_bytes, ctx->stream));
+    if (!ctx->stats_clean) CU(cudaMemsetAsync(ctx->stats.p, 0, stat_bytes, ctx->stream));
+    ctx->stats_clean = false;
+
+    // where the pixels go: the local band buffers, or -- several GPUs with peer access -- straight
+    // into rank 0's full frame over NVLink (the producing kernels do the "gather" themselves)
+    ctx->out_f32_dev = ctx->fb_f32.as<float>(); ctx->out_rgba8_dev = ctx->fb_rgba8.as<uchar4>();
+    const bool multi = ctx->comm && ctx->n_ranks > 1;
+    const bool gather_f32 = (fr->flags & RTB200_F_GATHER_F32) != 0;
+    bool peer = false;
+    if (multi) {
+        if (ctx->rank == 0 && out_f32 && !gather_f32) return fail(ctx, RTB200_E_ARG, "float output on several GPUs needs RTB200_F_GATHER_F32");
+        void *p8 = nullptr, *p32 = nullptr;
+        const int prc = comm_peer_frame(ctx, fp.W, fp.H, gather_f32, &p8, &p32);
+        if (prc != RTB200_OK) return prc;
+        if (p8) {
+            peer = true;
+            fp.fb_global = 1;
+            ctx->out_rgba8_dev = static_cast<uchar4*>(p8);
+            ctx->out_f32_dev = static_cast<float*>(p32);          // null unless the float frame is gathered too
+        }
+    }
 
     // path selection
     const size_t resident_limit = ctx->smem_optin > 4096 ? ctx->smem_optin - 2048 : 0;
@@ -517,20 +582,28 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
         use_stream = false;
     }
 
+    // one GPU and host pointers given: read finished row chunks back while the next ones render
+    const bool overlap = !multi && (out_f32 || out_rgba8) && (size_t)fp.W * fp.H >= (256u << 10);
+    ctx->host_f32 = overlap ? out_f32 : nullptr;
+    ctx->host_rgba8 = overlap ? out_rgba8 : nullptr;
+    ctx->copy_chunks = 0;
+
     CU(cudaEventRecord(ctx->ev[0], ctx->stream));
     int rc = RTB200_OK;
     if (local_rows > 0) {
         if (use_stream) rc = render_streamed(ctx, fr, fp, local_rows, exact, &st, &launches);
         else            rc = render_resident(ctx, fr, fp, local_rows, exact, &st, &launches);
     }
-    if (rc != RTB200_OK) { cudaStreamSynchronize(ctx->stream); (void)cudaGetLastError(); return rc; }
+    ctx->host_f32 = nullptr; ctx->host_rgba8 = nullptr;
+    if (rc != RTB200_OK) { cudaStreamSynchronize(ctx->stream); cudaStreamSynchronize(ctx->copy_stream); (void)cudaGetLastError(); return rc; }
     CU(cudaEventRecord(ctx->ev[1], ctx->stream));
+    const bool copied = overlap && ctx->copy_chunks > 0;
+    if (copied) CU(cudaEventRecord(ctx->copy_ev[3], ctx->copy_stream));
 
     ctx->last_W = fp.W; ctx->last_H = fp.H; ctx->last_local_rows = local_rows; ctx->last_gathered = false;
-    if (ctx->comm && ctx->n_ranks > 1) {
-        const bool gather_f32 = (fr->flags & RTB200_F_GATHER_F32) != 0;
-        if (ctx->rank == 0 && out_f32 && !gather_f32) return fail(ctx, RTB200_E_ARG, "float output on several GPUs needs RTB200_F_GATHER_F32");
-        rc = comm_gather_frame(ctx, fp.W, fp.H, band, gather_f32, true, &st.ms_gather);
+    if (multi) {
+        if (peer) rc = comm_peer_frame_done(ctx, &st.ms_gather);
+        else      rc = comm_gather_frame(ctx, fp.W, fp.H, band, gather_f32, true, &st.ms_gather);
         if (rc != RTB200_OK) return rc;
         ctx->last_gathered = (ctx->rank == 0);
     }
@@ -538,7 +611,9 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     // statistics
     unsigned long long* h_st = reinterpret_cast<unsigned long long*>(ctx->h_small.as<unsigned char>() + 1024);
     CU(cudaMemcpyAsync(h_st, ctx->stats.p, stat_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemsetAsync(ctx->stats.p, 0, stat_bytes, ctx->stream));     // for the NEXT frame, off its critical path
     CU(cudaStreamSynchronize(ctx->stream));
+    ctx->stats_clean = true;
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
     st.ms_render = ms;
@@ -570,9 +645,19 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
         if (sum[ST_BVH_OVERFLOW]) return fail(ctx, RTB200_E_CAPACITY, "LBVH traversal stack overflow");
     }
     st.kernel_launches = launches;
-    st.ms_h2d = 0.0;
+    if (ctx->upload_pending) {                   // the frame has completed, so has the upload before it
+        float h = 0.f;
+        if (cudaEventElapsedTime(&h, ctx->ev[4], ctx->ev[5]) == cudaSuccess) ctx->last_h2d_ms = h;
+        ctx->upload_pending = false;
+    }
+    st.ms_h2d = ctx->last_h2d_ms;
 
-    if (ctx->rank == 0 || !ctx->last_gathered) {
+    if (copied) {
+        CU(cudaStreamSynchronize(ctx->copy_stream));
+        float t = 0.f;
+        CU(cudaEventElapsedTime(&t, ctx->copy_ev[2], ctx->copy_ev[3]));
+        st.ms_d2h = t;                                          // mostly hidden under the rendering
+    } else if (ctx->rank == 0 || !ctx->last_gathered) {
         const bool want = (ctx->n_ranks <= 1) || ctx->rank == 0;
         if (want) {
             rc = read_back(ctx, out_f32, out_rgba8, &st.ms_d2h);

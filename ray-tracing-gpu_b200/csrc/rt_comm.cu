@@ -1,11 +1,18 @@
-// rt_comm.cu -- multi-GPU: one context per GPU, NCCL over NVLink.  The image is sharded in
-// interleaved row bands (rank = band mod n_ranks, balances sky / geometry / mirror cost), the
-// scene is replicated, and the only exchange is the framebuffer gather to rank 0:
-// grouped ncclSend/ncclRecv of each rank's compact band buffer + one de-interleave kernel.
+// rt_comm.cu -- multi-GPU: one context per GPU (one process per GPU), NVLink / NVSwitch.
+// The image is sharded in interleaved row bands (rank = band mod n_ranks, balances sky /
+// geometry / mirror cost), the scene is replicated, and the only exchange is the framebuffer
+// reaching rank 0.  Two ways:
+//   * peer frame (default where the GPUs have peer access): rank 0 exports its full-frame buffers
+//     with CUDA IPC, every other rank maps them, and the kernels that PRODUCE the pixels (the
+//     fused resident level kernel / k_resolve) store their rows straight into rank 0's memory over
+//     NVLink -- compute and "gather" are one kernel, no staging buffer, no de-interleave pass.  One
+//     tiny stream-ordered ncclAllReduce tells rank 0 that every rank's stores have landed.
+//   * fallback: grouped ncclSend/ncclRecv of each rank's compact band buffer + a de-interleave kernel.
 // NCCL is loaded lazily with dlopen so that single-GPU use has no NCCL dependency.
 #include <dlfcn.h>
 #include <nccl.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <algorithm>
 #include <vector>
@@ -21,6 +28,8 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -43,6 +52,8 @@ static NcclApi* nccl_api()
         LOAD(CommDestroy, "ncclCommDestroy");
         LOAD(Send, "ncclSend");
         LOAD(Recv, "ncclRecv");
+        LOAD(Broadcast, "ncclBroadcast");
+        LOAD(AllReduce, "ncclAllReduce");
         LOAD(GroupStart, "ncclGroupStart");
         LOAD(GroupEnd, "ncclGroupEnd");
         LOAD(GetErrorString, "ncclGetErrorString");
@@ -56,6 +67,13 @@ struct Comm {
     ncclComm_t comm = nullptr;
     DevBuf recv_f32, recv_rgba8;     // rank 0: compact buffers of ranks 1..n-1, concatenated
     cudaEvent_t e0 = nullptr, e1 = nullptr;
+    // peer frame: rank 0's full-frame buffers mapped into every rank (CUDA IPC over NVLink)
+    bool   p2p_tried = false, p2p = false;
+    void*  map_rgba8 = nullptr;      // ranks > 0: rank 0's full RGBA8 frame in this process
+    void*  map_f32 = nullptr;        //            rank 0's full float frame (only when requested)
+    size_t cap_rgba8 = 0, cap_f32 = 0;
+    DevBuf sync;                     // 2 ints: all-reduce in / out
+    DevBuf handles;                  // 2 IPC handles travelling through ncclBroadcast
 };
 
 static int nccl_fail(rtb200_ctx* c, ncclResult_t r, const char* where)
@@ -98,11 +116,21 @@ int comm_init(rtb200_ctx* c, int rank, int n_ranks, const uint8_t* id)
     return RTB200_OK;
 }
 
+static void peer_unmap(Comm* cm)
+{
+    if (cm->map_rgba8) { cudaIpcCloseMemHandle(cm->map_rgba8); cm->map_rgba8 = nullptr; }
+    if (cm->map_f32) { cudaIpcCloseMemHandle(cm->map_f32); cm->map_f32 = nullptr; }
+    (void)cudaGetLastError();
+}
+
 void comm_destroy(rtb200_ctx* c)
 {
     if (!c || !c->comm) return;
     NcclApi* a = nccl_api();
     Comm* cm = c->comm;
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    peer_unmap(cm);
+    cm->sync.release(); cm->handles.release();
     if (a && cm->comm) a->CommDestroy(cm->comm);
     cm->recv_f32.release(); cm->recv_rgba8.release();
     if (cm->e0) cudaEventDestroy(cm->e0);
@@ -189,6 +217,102 @@ int comm_gather_frame(rtb200_ctx* c, int W, int H, int band, bool want_f32, bool
     }
     cudaEventRecord(cm->e1, c->stream);
     if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return set_cuda_error(c, e, "gather sync");
+    float t = 0.f;
+    cudaEventElapsedTime(&t, cm->e0, cm->e1);
+    if (ms) *ms = t;
+    return RTB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// Peer frame
+// ---------------------------------------------------------------------------------------
+// min over ranks of `v` (stream-ordered, then waited for): agreement on success / failure
+static int all_min(rtb200_ctx* c, int v, int* out)
+{
+    NcclApi* a = nccl_api();
+    Comm* cm = c->comm;
+    cudaError_t e;
+    if ((e = cm->sync.ensure(2 * sizeof(int))) != cudaSuccess) return set_cuda_error(c, e, "sync buffer");
+    if ((e = cudaMemcpyAsync(cm->sync.p, &v, sizeof(int), cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) return set_cuda_error(c, e, "sync h2d");
+    ncclResult_t r = a->AllReduce(cm->sync.p, cm->sync.as<int>() + 1, 1, ncclInt, ncclMin, cm->comm, c->stream);
+    if (r != ncclSuccess) return nccl_fail(c, r, "ncclAllReduce");
+    int res = 0;
+    if ((e = cudaMemcpyAsync(&res, cm->sync.as<int>() + 1, sizeof(int), cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) return set_cuda_error(c, e, "sync d2h");
+    if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return set_cuda_error(c, e, "sync");
+    *out = res;
+    return RTB200_OK;
+}
+
+// Collective.  Makes rank 0's full-frame buffers (W x H RGBA8, plus float RGB when asked) visible
+// in every rank.  On return *rgba8 / *f32 are the pointers THIS rank's kernels must store to
+// (rank 0: its own buffers), or p2p is off for good and the caller uses the NCCL gather.
+int comm_peer_frame(rtb200_ctx* c, int W, int H, bool want_f32, void** rgba8, void** f32)
+{
+    NcclApi* a = nccl_api();
+    Comm* cm = c->comm;
+    *rgba8 = nullptr; *f32 = nullptr;
+    if (!a || !cm) return RTB200_E_STATE;
+    if (cm->p2p_tried && !cm->p2p) return RTB200_OK;
+    if (getenv("RTB200_NO_P2P")) { cm->p2p_tried = true; cm->p2p = false; return RTB200_OK; }
+    const size_t need8 = 4 * (size_t)W * H, need32 = want_f32 ? sizeof(float) * 3 * (size_t)W * H : 0;
+    const int me = c->rank;
+    int rc, agreed = 0;
+    if (!(cm->p2p && need8 <= cm->cap_rgba8 && need32 <= cm->cap_f32)) {
+        // (re)establish the mapping: peers let go of the old buffers before rank 0 reallocates them
+        cm->p2p_tried = true;
+        if (me != 0) peer_unmap(cm);
+        if ((rc = all_min(c, 1, &agreed)) != RTB200_OK) return rc;
+        cudaError_t e = cudaSuccess;
+        cudaIpcMemHandle_t h[2];
+        memset(h, 0, sizeof h);
+        int ok = 1;
+        if (me == 0) {
+            if ((e = c->full_rgba8.ensure(need8)) != cudaSuccess) ok = 0;
+            if (ok && want_f32 && (e = c->full_f32.ensure(need32)) != cudaSuccess) ok = 0;
+            if (ok && cudaIpcGetMemHandle(&h[0], c->full_rgba8.p) != cudaSuccess) ok = 0;
+            if (ok && want_f32 && cudaIpcGetMemHandle(&h[1], c->full_f32.p) != cudaSuccess) ok = 0;
+            (void)cudaGetLastError();
+        }
+        if ((e = cm->handles.ensure(sizeof h)) != cudaSuccess) return set_cuda_error(c, e, "handle buffer");
+        if (me == 0 && (e = cudaMemcpyAsync(cm->handles.p, h, sizeof h, cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) return set_cuda_error(c, e, "handle h2d");
+        ncclResult_t r = a->Broadcast(cm->handles.p, cm->handles.p, sizeof h, ncclUint8, 0, cm->comm, c->stream);
+        if (r != ncclSuccess) return nccl_fail(c, r, "ncclBroadcast");
+        if (me != 0) {
+            if ((e = cudaMemcpyAsync(h, cm->handles.p, sizeof h, cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) return set_cuda_error(c, e, "handle d2h");
+            if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return set_cuda_error(c, e, "handle sync");
+            if (cudaIpcOpenMemHandle(&cm->map_rgba8, h[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; cm->map_rgba8 = nullptr; }
+            if (ok && want_f32 && cudaIpcOpenMemHandle(&cm->map_f32, h[1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; cm->map_f32 = nullptr; }
+            (void)cudaGetLastError();
+        }
+        if ((rc = all_min(c, ok, &agreed)) != RTB200_OK) return rc;
+        if (!agreed) {                       // some rank cannot reach rank 0's memory: NCCL gather from now on
+            if (me != 0) peer_unmap(cm);
+            cm->p2p = false; cm->cap_rgba8 = cm->cap_f32 = 0;
+            return RTB200_OK;
+        }
+        cm->p2p = true;
+        cm->cap_rgba8 = need8;
+        cm->cap_f32 = need32;
+    }
+    *rgba8 = me == 0 ? c->full_rgba8.p : cm->map_rgba8;
+    *f32 = want_f32 ? (me == 0 ? c->full_f32.p : cm->map_f32) : nullptr;
+    return RTB200_OK;
+}
+
+// After the kernels that stored into rank 0's frame: one tiny all-reduce, ordered after them on
+// every rank's stream.  When it completes on rank 0, every rank's stores have landed.
+int comm_peer_frame_done(rtb200_ctx* c, double* ms)
+{
+    NcclApi* a = nccl_api();
+    Comm* cm = c->comm;
+    if (!a || !cm) return RTB200_E_STATE;
+    cudaError_t e;
+    if ((e = cm->sync.ensure(2 * sizeof(int))) != cudaSuccess) return set_cuda_error(c, e, "sync buffer");
+    cudaEventRecord(cm->e0, c->stream);
+    ncclResult_t r = a->AllReduce(cm->sync.p, cm->sync.as<int>() + 1, 1, ncclInt, ncclMin, cm->comm, c->stream);
+    if (r != ncclSuccess) return nccl_fail(c, r, "ncclAllReduce");
+    cudaEventRecord(cm->e1, c->stream);
+    if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return set_cuda_error(c, e, "peer frame sync");
     float t = 0.f;
     cudaEventElapsedTime(&t, cm->e0, cm->e1);
     if (ms) *ms = t;

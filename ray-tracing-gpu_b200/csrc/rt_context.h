@@ -75,12 +75,23 @@ struct rtb200_ctx {
     int max_children = 0;             // 0, 1 or 2 secondary rays per hit at most
     bool any_reflect = false, any_refract = false;
     double last_h2d_ms = 0.0;
+    bool upload_pending = false;      // an asynchronous scene upload may still be reading `stage`
 
     // frame buffers (local rows of this rank)
     rtb::DevBuf c0, fb_f32, fb_rgba8, stats, counters;
+    bool stats_clean = false;         // the device counters were zeroed at the end of the previous frame
     rtb::DevBuf full_f32, full_rgba8; // rank 0 with a communicator: gathered frame
     rtb::PinnedBuf h_small;           // counters / stats read-back
     std::vector<rtb::LevelBuf> levels;
+    float*  out_f32_dev = nullptr;    // where THIS frame's kernels store pixels: the local band buffers, or
+    uchar4* out_rgba8_dev = nullptr;  // rank 0's full frame (own or peer-mapped over NVLink, FrameParams::fb_global)
+    // overlapped read-back (one GPU, host output pointers given): finished row chunks travel to the
+    // host on a second stream while the next chunk renders
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t  copy_ev[4] = {nullptr, nullptr, nullptr, nullptr};   // 0/1: chunk done (alternating), 2/3: copy begin / end
+    float*   host_f32 = nullptr;      // non-null during a render that overlaps its read-back
+    uint8_t* host_rgba8 = nullptr;
+    int      copy_chunks = 0;         // chunks already handed to the copy stream in this frame
     int last_W = 0, last_H = 0, last_local_rows = 0;
     bool last_gathered = false;
 
@@ -102,6 +113,7 @@ struct rtb200_ctx {
 
 namespace rtb {
 int  set_cuda_error(rtb200_ctx* c, cudaError_t e, const char* where);
+int  chunk_copy_out(rtb200_ctx* c, int W, int py0, int prows);              // rt_api.cu: overlapped read-back of finished rows
 int  render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
                      bool exact, rtb200_stats* st, uint32_t* launches);     // rt_stream.cu
 void stream_release(rtb200_ctx* c);
@@ -112,4 +124,6 @@ int  comm_unique_id(uint8_t* id);
 int  comm_init(rtb200_ctx* c, int rank, int n_ranks, const uint8_t* id);
 void comm_destroy(rtb200_ctx* c);
 int  comm_gather_frame(rtb200_ctx* c, int W, int H, int band_rows, bool want_f32, bool want_rgba8, double* ms);
+int  comm_peer_frame(rtb200_ctx* c, int W, int H, bool want_f32, void** rgba8, void** f32);   // collective; null = use the gather
+int  comm_peer_frame_done(rtb200_ctx* c, double* ms);
 }

@@ -32,6 +32,10 @@ struct LevelParams {
     int4* links;
     unsigned int* link_count;
     unsigned long long* stats;     // [RT_STAT_SLOTS][ST_COUNT]
+    // direct resolve (level 0, spp 1, no secondary rays): the level kernel writes the frame itself
+    int     direct;
+    float*  fb_f32;                // [local rows][W][3]
+    uchar4* fb_rgba8;              // [local rows][W]
 };
 
 struct CombineParams {
@@ -56,7 +60,7 @@ struct ResolveParams {
 // launchers (rt_resident.cu)
 size_t resident_smem_bytes(const ResidentLayout& rl);
 cudaError_t resident_prepare(size_t max_smem_bytes);
-cudaError_t launch_resident_level(const LevelParams& p, bool exact, cudaStream_t st);
+cudaError_t launch_resident_level(const LevelParams& p, bool exact, int sm_count, cudaStream_t st);
 cudaError_t launch_combine(const CombineParams& p, bool exact, cudaStream_t st);
 cudaError_t launch_resolve(const ResolveParams& p, cudaStream_t st);
 

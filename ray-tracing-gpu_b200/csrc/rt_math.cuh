@@ -25,7 +25,7 @@ struct FP {
     static RT_DEV float add(float a, float b) { return __fadd_rn(a, b); }
     static RT_DEV float sub(float a, float b) { return __fsub_rn(a, b); }
     static RT_DEV float div(float a, float b) { return __fdiv_rn(a, b); }
-    static RT_DEV float rcp(float a) { return __fdiv_rn(1.0f, a); }
+    static RT_DEV float rcp(float a) { return __frcp_rn(a); }      // correctly rounded 1/a == the reference's 1.0f / a
     static RT_DEV float sqrt(float a) { return __fsqrt_rn(a); }
     // a*b + c
     static RT_DEV float madd(float a, float b, float c)
@@ -149,6 +149,15 @@ template <bool E> RT_DEV float quadric_t(V3 o, V3 d, const Quadric& q, bool& lin
     float C = F::add(F::add(F::add(c1, c2), c3), q.K);
 
     if (A != 0.0f) {
+        // Division-free miss test.  delta = fl(fl(ka*ka) - kb) with ka = fl(-B/A), kb = fl(C/A) has the
+        // sign of (B^2/A^2)(1+e1)^2(1+e3) - (C/A)(1+e2), |e| <= 2^-24; it is <= 0 (the reference returns
+        // "no intersection", Quadrique.cpp:205) whenever B^2 (1 + 2^-18) < A*C, evaluated here with two
+        // rounded products (relative slack 61 ulp >> the 5 ulp needed; the 1e-30 floor keeps both
+        // products out of the subnormal range).  Saves two IEEE divisions per missed quadric.
+        {
+            const float ac = __fmul_rn(A, C);
+            if (ac > 1.0e-30f && __fmul_rn(__fmul_rn(B, B), 1.00000381f) < ac) return -1.0f;
+        }
         float ka = F::div(-B, A);
         float kb = F::div(C, A);
         float delta = F::mmsub(ka, ka, kb, 1.0f);   // ka*ka - kb  (kb*1 is exact)

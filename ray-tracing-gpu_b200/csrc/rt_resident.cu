@@ -8,6 +8,8 @@
 // colours are folded parent <- children bottom-up, reflection before refraction, exactly in
 // the reference's accumulation order and deterministically.  No per-thread stack, no
 // recursion; every level runs on a compacted queue so warps never diverge on depth.
+#include <algorithm>
+
 #include "rt_kernels.cuh"
 #include "rt_tma.cuh"
 
@@ -83,35 +85,49 @@ template <bool E> RT_DEV int shadow_filter(const SceneView& sv, bool need, V3 P,
     return k;                                   // surfaces tested by the lanes that needed the query
 }
 
-// block-wide add of four per-thread counters into the spread statistics slots
-RT_DEV void block_stats4(unsigned long long* stats, unsigned int a, unsigned int b, unsigned int c, unsigned int d,
-                         unsigned int* sm_acc)
+// warp-wide add of the per-thread counters into the spread statistics slots (once per CTA:
+// the CTAs are persistent, the counters live in registers across tiles)
+RT_DEV void warp_stats(unsigned long long* stats, unsigned int n_shadow, unsigned int n_refl, unsigned int n_refr,
+                       unsigned int n_tests, unsigned int n_nan)
 {
-    for (int off = 16; off > 0; off >>= 1) {
-        a += __shfl_xor_sync(0xffffffffu, a, off);
-        b += __shfl_xor_sync(0xffffffffu, b, off);
-        c += __shfl_xor_sync(0xffffffffu, c, off);
-        d += __shfl_xor_sync(0xffffffffu, d, off);
-    }
+    n_shadow = __reduce_add_sync(0xffffffffu, n_shadow);
+    n_refl   = __reduce_add_sync(0xffffffffu, n_refl);
+    n_refr   = __reduce_add_sync(0xffffffffu, n_refr);
+    n_tests  = __reduce_add_sync(0xffffffffu, n_tests);
+    n_nan    = __reduce_add_sync(0xffffffffu, n_nan);
     if ((threadIdx.x & 31) == 0) {
-        if (a) atomicAdd(&sm_acc[0], a);
-        if (b) atomicAdd(&sm_acc[1], b);
-        if (c) atomicAdd(&sm_acc[2], c);
-        if (d) atomicAdd(&sm_acc[3], d);
-    }
-    __syncthreads();
-    if (threadIdx.x < 4) {
-        const unsigned int tot = sm_acc[threadIdx.x];
+        unsigned long long* st = stats + (size_t)((blockIdx.x * 8 + (threadIdx.x >> 5)) % RT_STAT_SLOTS) * ST_COUNT;
         // resident path: ST_TEST_TRI holds ALL surface tests (split by type on the host)
-        const int which = threadIdx.x == 0 ? ST_SHADOW : (threadIdx.x == 1 ? ST_REFLECT : (threadIdx.x == 2 ? ST_REFRACT : ST_TEST_TRI));
-        if (tot) atomicAdd(&stats[(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + which], (unsigned long long)tot);
+        if (n_shadow) atomicAdd(&st[ST_SHADOW], (unsigned long long)n_shadow);
+        if (n_refl)   atomicAdd(&st[ST_REFLECT], (unsigned long long)n_refl);
+        if (n_refr)   atomicAdd(&st[ST_REFRACT], (unsigned long long)n_refr);
+        if (n_tests)  atomicAdd(&st[ST_TEST_TRI], (unsigned long long)n_tests);
+        if (n_nan)    atomicAdd(&st[ST_NAN], (unsigned long long)n_nan);
     }
 }
 
+// the RGBA8 quantiser floor(clamp(c,0,1)*255 + 0.5), NaN -> 0 (counted)
+RT_DEV uchar4 quantise_rgba8(float r, float g, float b, unsigned int& nans)
+{
+    float v[3] = { r, g, b };
+    unsigned char q[3];
+    #pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float w = v[c];
+        if (w != w) { ++nans; w = 0.f; }
+        w = fminf(fmaxf(w, 0.f), 1.f);
+        q[c] = (unsigned char)floorf(__fadd_rn(__fmul_rn(w, 255.0f), 0.5f));
+    }
+    return make_uchar4(q[0], q[1], q[2], 255);
+}
+
 // ---------------------------------------------------------------------------------------
-// One wavefront level.  CTA = 256 threads = one 16x16 tile of the sample lattice (level 0,
-// warps are 8x4 sub-tiles so a warp's rays stay a compact bundle) or 256 consecutive queue
-// entries (level >= 1).
+// One wavefront level.  PERSISTENT CTAs (a few per SM): the scene is staged into shared memory
+// ONCE per CTA by one bulk TMA copy, then the CTA walks 16x16 tiles of the sample lattice
+// (level 0, warps are 8x4 sub-tiles so a warp's rays stay a compact bundle) or blocks of 256
+// consecutive queue entries (level >= 1).  When the frame spawns no secondary rays and is not
+// supersampled (p.direct), the level-0 kernel also resolves: it writes the float RGB and the
+// RGBA8 framebuffers itself and the frame is ONE kernel.
 // ---------------------------------------------------------------------------------------
 template <bool E, bool PRIMARY>
 __global__ void __launch_bounds__(RES_THREADS)
@@ -119,45 +135,48 @@ k_resident_level(const __grid_constant__ LevelParams p)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ __align__(8) uint64_t bar;
-    __shared__ unsigned int sm_acc[4];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); sm_acc[0] = sm_acc[1] = sm_acc[2] = sm_acc[3] = 0; }
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
     __syncthreads();
     if (tid == 0) {                         // one bulk copy stages the whole scene
         mbar_arrive_expect_tx(&bar, (uint32_t)p.rl.bytes);
         tma_load_1d(smem, p.blob, (uint32_t)p.rl.bytes, &bar);
     }
-
-    // ---- this thread's ray (overlaps the copy) ---------------------------------------------
     const FrameParams& f = p.f;
-    V3 o, d;
-    float energy = 1.0f, ior = 1.0f;
-    bool valid;
-    int  self;                              // index of this ray in its level's colour buffer
-    if (PRIMARY) {
-        const int tiles_x = (f.LW + 15) >> 4;
-        const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
-        const int lx = (tx << 4) + ((warp & 1) << 3) + (lane & 7);
-        const int cy = (ty << 4) + ((warp >> 1) << 2) + (lane >> 3);   // row inside the chunk
-        const int ly = p.chunk_ly0 + cy;                                 // local lattice row
-        valid = lx < f.LW && cy < p.chunk_rows && ly < p.local_LH;
-        self = cy * f.LW + lx;
-        primary_ray<E>(f, valid ? lx : 0, valid ? global_lattice_row(f, ly) : 0, o, d);
-    } else {
-        self = blockIdx.x * RES_THREADS + tid;
-        valid = self < p.in_count;
-        const float4 a = valid ? p.in_od0[self] : make_float4(0.f, 0.f, 0.f, 0.f);
-        const float4 b = valid ? p.in_od1[self] : make_float4(0.f, 0.f, 0.f, 0.f);
-        o = f4_xyz(a); d = f4_xyz(b); energy = a.w; ior = b.w;
-    }
-
+    const int tiles_x = (f.LW + 15) >> 4;
+    const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + 15) >> 4) : (p.in_count + RES_THREADS - 1) / RES_THREADS;
     mbar_wait(&bar, 0);
     SceneView sv;
     sv.surf  = reinterpret_cast<const SurfRec*>(smem);
     sv.mat   = reinterpret_cast<const MatRec*>(smem + p.rl.off_mat);
     sv.light = reinterpret_cast<const LightRec*>(smem + p.rl.off_light);
     sv.n_surf = p.rl.n_surf; sv.n_light = p.rl.n_light;
+    unsigned int n_shadow = 0, n_tests = 0, n_refl_st = 0, n_refr_st = 0, n_nan = 0;
+
+    for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+    // ---- this thread's ray ------------------------------------------------------------------
+    V3 o, d;
+    float energy = 1.0f, ior = 1.0f;
+    bool valid;
+    int  self;                              // index of this ray in its level's colour buffer
+    int  pix_x = 0, pix_y = 0;
+    if (PRIMARY) {
+        const int tx = blk % tiles_x, ty = blk / tiles_x;
+        const int lx = (tx << 4) + ((warp & 1) << 3) + (lane & 7);
+        const int cy = (ty << 4) + ((warp >> 1) << 2) + (lane >> 3);   // row inside the chunk
+        const int ly = p.chunk_ly0 + cy;                                 // local lattice row
+        valid = lx < f.LW && cy < p.chunk_rows && ly < p.local_LH;
+        self = cy * f.LW + lx;
+        pix_x = lx; pix_y = ly;
+        primary_ray<E>(f, valid ? lx : 0, valid ? global_lattice_row(f, ly) : 0, o, d);
+    } else {
+        self = blk * RES_THREADS + tid;
+        valid = self < p.in_count;
+        const float4 a = valid ? p.in_od0[self] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 b = valid ? p.in_od1[self] : make_float4(0.f, 0.f, 0.f, 0.f);
+        o = f4_xyz(a); d = f4_xyz(b); energy = a.w; ior = b.w;
+    }
 
     // ---- nearest hit (Scene.cpp:1705-1720) -----------------------------------------------
     float t; int k; bool lin;
@@ -165,7 +184,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
     const bool hit = valid && k >= 0;
 
     float cr = f.background[0], cg = f.background[1], cb = f.background[2];
-    unsigned int n_shadow = 0, n_tests = valid ? (unsigned int)sv.n_surf : 0u;
+    n_tests += valid ? (unsigned int)sv.n_surf : 0u;
     bool want_refl = false, want_refr = false;
     V3 P = mk3(0.f, 0.f, 0.f), N = mk3(0.f, 0.f, 0.f);
     int mat = 0;
@@ -183,6 +202,9 @@ k_resident_level(const __grid_constant__ LevelParams p)
             P = axpy3<E>(o, d, t);
             cr = FP<E>::mul(m0.x, m0.w); cg = FP<E>::mul(m0.y, m0.w); cb = FP<E>::mul(m0.z, m0.w);
         }
+        // ks == 0 with a sane shininess: the Phong term is (I*0)*pow(ps, n) = 0 for every finite
+        // pow, and adding lcr*0 = 0 leaves the (non-negative) colour unchanged -> no powf needed
+        const bool no_phong = m1.y == 0.f && m1.z >= 0.f && m1.z <= 1.0e4f;
         for (int l = 0; l < sv.n_light; ++l) {
             const float4 l0 = sv.light[l].l0, l1 = sv.light[l].l1;
             V3 Ld = sub3<E>(f4_xyz(l0), P);
@@ -202,13 +224,15 @@ k_resident_level(const __grid_constant__ LevelParams p)
                 cg = FP<E>::madd(FP<E>::mul(m0.y, g), lcg, cg);
                 cb = FP<E>::madd(FP<E>::mul(m0.z, g), lcb, cb);
                 // Phong term (Scene.cpp:1768-1775)
-                const V3 R = reflect3<E>(Ld, N);
-                const float ps = dot3<E>(R, d);
-                if (ps > 0.f) {
-                    const float ph = FP<E>::mul(FP<E>::mul(l0.w, m1.y), powf(ps, m1.z));
-                    cr = FP<E>::madd(lcr, ph, cr);
-                    cg = FP<E>::madd(lcg, ph, cg);
-                    cb = FP<E>::madd(lcb, ph, cb);
+                if (!no_phong || !(lcr == lcr && lcg == lcg && lcb == lcb && fabsf(lcr) <= 3.0e38f && fabsf(lcg) <= 3.0e38f && fabsf(lcb) <= 3.0e38f)) {
+                    const V3 R = reflect3<E>(Ld, N);
+                    const float ps = dot3<E>(R, d);
+                    if (ps > 0.f) {
+                        const float ph = FP<E>::mul(FP<E>::mul(l0.w, m1.y), powf(ps, m1.z));
+                        cr = FP<E>::madd(lcr, ph, cr);
+                        cg = FP<E>::madd(lcg, ph, cg);
+                        cb = FP<E>::madd(lcb, ph, cb);
+                    }
                 }
             }
         }
@@ -224,8 +248,14 @@ k_resident_level(const __grid_constant__ LevelParams p)
     // ---- this ray's own colour -------------------------------------------------------------
     if (valid) {
         if (PRIMARY) {
-            float* c = p.c0 + 3 * (size_t)self;
-            c[0] = cr; c[1] = cg; c[2] = cb;
+            if (p.direct) {                                   // k == 1, no children: resolve here
+                const size_t pix = (size_t)framebuffer_row(f, pix_y) * f.W + pix_x;
+                if (p.fb_f32) { float* c = p.fb_f32 + 3 * pix; c[0] = cr; c[1] = cg; c[2] = cb; }
+                if (p.fb_rgba8) p.fb_rgba8[pix] = quantise_rgba8(cr, cg, cb, n_nan);
+            } else {
+                float* c = p.c0 + 3 * (size_t)self;
+                c[0] = cr; c[1] = cg; c[2] = cb;
+            }
         } else {
             p.in_colour[self] = make_float4(cr, cg, cb, 0.f);
         }
@@ -251,6 +281,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
             const V3 rd = reflect3<E>(d, N);
             p.out_od0[s_refl] = make_float4(P.x, P.y, P.z, e_refl);
             p.out_od1[s_refl] = make_float4(rd.x, rd.y, rd.z, 0.0f);          // CRayon default ior, Rayon.cpp:16
+            ++n_refl_st;
         }
         if (want_refr) {
             s_refr = (int)(base + n_refl + __popc(m_refr & below));
@@ -260,13 +291,15 @@ k_resident_level(const __grid_constant__ LevelParams p)
             const V3 rd = refract3<E>(d, n2, ratio);
             p.out_od0[s_refr] = make_float4(P.x, P.y, P.z, e_refr);
             p.out_od1[s_refr] = make_float4(rd.x, rd.y, rd.z, nior);
+            ++n_refr_st;
         }
         if (want_refl || want_refr)
             p.links[lbase + __popc(m_any & below)] = make_int4(self, s_refl, s_refr, mat);
     }
+    }   // tiles of this CTA
 
     // ---- statistics ---------------------------------------------------------------------------
-    block_stats4(p.stats, n_shadow, want_refl ? 1u : 0u, want_refr ? 1u : 0u, n_tests, sm_acc);
+    warp_stats(p.stats, n_shadow, n_refl_st, n_refr_st, n_tests, n_nan);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -320,20 +353,9 @@ __global__ void __launch_bounds__(256) k_resolve(const ResolveParams p)
             const float sc = __fdiv_rn(1.0f, (float)(k * k));
             r = __fmul_rn(r, sc); g = __fmul_rn(g, sc); b = __fmul_rn(b, sc);
         }
-        const size_t pix = (size_t)(p.chunk_py0 + yr) * p.f.W + x;
+        const size_t pix = (size_t)framebuffer_row(p.f, p.chunk_py0 + yr) * p.f.W + x;
         if (p.fb_f32) { float* o = p.fb_f32 + 3 * pix; o[0] = r; o[1] = g; o[2] = b; }
-        if (p.fb_rgba8) {
-            float v[3] = { r, g, b };
-            unsigned char q[3];
-            #pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                float w = v[c];
-                if (w != w) { ++nans; w = 0.f; }
-                w = fminf(fmaxf(w, 0.f), 1.f);
-                q[c] = (unsigned char)floorf(__fadd_rn(__fmul_rn(w, 255.0f), 0.5f));
-            }
-            p.fb_rgba8[pix] = make_uchar4(q[0], q[1], q[2], 255);
-        }
+        if (p.fb_rgba8) p.fb_rgba8[pix] = quantise_rgba8(r, g, b, nans);
     }
     nans = __reduce_add_sync(0xffffffffu, nans);
     if ((threadIdx.x & 31) == 0 && nans)
@@ -393,16 +415,24 @@ cudaError_t resident_prepare(size_t max_smem_bytes)
     return cudaSuccess;
 }
 
-cudaError_t launch_resident_level(const LevelParams& p, bool exact, cudaStream_t st)
+static int g_resident_ctas_per_sm = 0;          // occupancy of the level kernel (queried once)
+
+cudaError_t launch_resident_level(const LevelParams& p, bool exact, int sm_count, cudaStream_t st)
 {
     const size_t smem = resident_smem_bytes(p.rl);
+    if (g_resident_ctas_per_sm <= 0) {
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_resident_level<true, true>, RES_THREADS, smem) != cudaSuccess || n <= 0) n = 2;
+        g_resident_ctas_per_sm = n;
+    }
+    const int max_ctas = g_resident_ctas_per_sm * sm_count;
     if (p.level == 0) {
         const int tiles_x = (p.f.LW + 15) / 16, tiles_y = (p.chunk_rows + 15) / 16;
-        const dim3 grid((unsigned)(tiles_x * tiles_y));
+        const dim3 grid((unsigned)std::min(tiles_x * tiles_y, max_ctas));
         if (exact) k_resident_level<true, true><<<grid, RES_THREADS, smem, st>>>(p);
         else       k_resident_level<false, true><<<grid, RES_THREADS, smem, st>>>(p);
     } else {
-        const dim3 grid((unsigned)((p.in_count + RES_THREADS - 1) / RES_THREADS));
+        const dim3 grid((unsigned)std::min((p.in_count + RES_THREADS - 1) / RES_THREADS, max_ctas));
         if (exact) k_resident_level<true, false><<<grid, RES_THREADS, smem, st>>>(p);
         else       k_resident_level<false, false><<<grid, RES_THREADS, smem, st>>>(p);
     }

@@ -72,6 +72,8 @@ struct FrameParams {
     // banding (multi-GPU): local lattice row -> global lattice row
     int   band_lrows;           // band height in lattice rows (band_rows * k)
     int   n_ranks, rank;
+    int   fb_global;            // 1: the framebuffers are FULL frames (rank 0's, possibly peer-mapped over
+                                //    NVLink) and pixel rows are addressed globally; 0: compact local rows
 };
 
 // ---- wavefront queues -----------------------------------------------------------------------
@@ -93,6 +95,15 @@ RT_DEV int global_lattice_row(const FrameParams& f, int ly)
     if (f.n_ranks <= 1) return ly;
     int b = ly / f.band_lrows, r = ly - b * f.band_lrows;
     return (b * f.n_ranks + f.rank) * f.band_lrows + r;
+}
+
+// Row of the framebuffer a LOCAL pixel row is stored at (see FrameParams::fb_global).
+RT_DEV int framebuffer_row(const FrameParams& f, int local_row)
+{
+    if (!f.fb_global || f.n_ranks <= 1) return local_row;
+    const int band = f.band_lrows / f.k;
+    const int b = local_row / band, r = local_row - b * band;
+    return (b * f.n_ranks + f.rank) * band + r;
 }
 
 // Primary ray through lattice sample (sx, sy): Scene.cpp:1543-1552.

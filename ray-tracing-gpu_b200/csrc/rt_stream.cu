@@ -210,10 +210,14 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
         memset(&r, 0, sizeof r);
         r.f = fp; r.c0 = c->c0.as<float>();
         r.chunk_py0 = ly0 / k; r.chunk_prows = std::min(rows / k, local_rows - r.chunk_py0);
-        r.fb_f32 = c->fb_f32.as<float>(); r.fb_rgba8 = c->fb_rgba8.as<uchar4>();
+        r.fb_f32 = c->out_f32_dev; r.fb_rgba8 = c->out_rgba8_dev;
         r.stats = c->stats.as<unsigned long long>();
         SCU(launch_resolve(r, c->stream));
         ++*launches;
+        {
+            const int rc2 = chunk_copy_out(c, fp.W, r.chunk_py0, r.chunk_prows);
+            if (rc2 != RTB200_OK) return rc2;
+        }
     }
     SCU(cudaStreamSynchronize(c->stream));
     flush_b();
@@ -260,6 +264,7 @@ int stream_query_shadow(rtb200_ctx* c, int n, uint32_t flags)
         (e = sb->filter.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess) return set_cuda_error(c, e, "query scratch");
     const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
     if ((e = c->stats.ensure(stat_bytes)) != cudaSuccess) return set_cuda_error(c, e, "stats");
+    c->stats_clean = false;                      // the query kernels add to the frame counters
     SCU(launch_query_pack_shadow(n, c->q_in0.as<float>(), c->q_in1.as<float>(), sb->sq0.as<float4>(), sb->sq1.as<float4>(), mode != 2, c->stream));
     ShadowParams sp;
     memset(&sp, 0, sizeof sp);
