@@ -200,6 +200,12 @@ int  rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* point3, const floa
 int  rtb200_comm_unique_id(uint8_t id[RTB200_UNIQUE_ID_BYTES]);
 int  rtb200_comm_init(rtb200_ctx* ctx, int rank, int n_ranks, const uint8_t id[RTB200_UNIQUE_ID_BYTES]);
 
+/* The band layout rtb200_render uses with a communicator (pure host arithmetic, callable without a
+ * GPU): rank `rank` renders *n_local rows and stores them compactly; out_global_rows[i] (capacity
+ * >= *n_local, may be NULL) is the image row of its local row i.  band_rows 0 = default 16. */
+int  rtb200_band_map(int height, int band_rows, int n_ranks, int rank,
+                     int32_t* out_global_rows, int capacity, int* n_local);
+
 /* --- helpers ------------------------------------------------------------------------------ */
 /* Page-locked host memory for the caller's scene / frame buffers (so that the copies inside
  * rtb200_set_scene / rtb200_render are true async DMA). */

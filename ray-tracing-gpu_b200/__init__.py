@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "librtb200.so")
 EXPORTS = [
     "rtb200_abi_version", "rtb200_create", "rtb200_destroy", "rtb200_error_string", "rtb200_last_error",
     "rtb200_set_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_read_frame",
-    "rtb200_trace_nearest", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init",
+    "rtb200_trace_nearest", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init", "rtb200_band_map",
     "rtb200_host_alloc", "rtb200_host_free", "rtb200_measure_fp32_peak", "rtb200_device_info",
     "rtb200_timer_mark", "rtb200_timer_elapsed",
 ]
@@ -65,10 +65,25 @@ def lib():
         L.rtb200_host_free.restype = None
         L.rtb200_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.rtb200_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_char_p, C.c_int]
+        L.rtb200_band_map.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.POINTER(C.c_int)]
         L.rtb200_timer_mark.argtypes = [vp, C.c_int]
         L.rtb200_timer_elapsed.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_double)]
         _lib = L
     return _lib
+
+
+def band_map(height, band_rows, n_ranks, rank):
+    """Image rows rendered by `rank` (global row of each of its local rows) -- rtb200_band_map."""
+    L = lib()
+    n = C.c_int()
+    rc = L.rtb200_band_map(height, band_rows, n_ranks, rank, None, 0, C.byref(n))
+    if rc != 0:
+        raise RtError(rc, "rtb200_band_map")
+    rows = np.empty(n.value, np.int32)
+    rc = L.rtb200_band_map(height, band_rows, n_ranks, rank, rows.ctypes.data, len(rows), C.byref(n))
+    if rc != 0:
+        raise RtError(rc, "rtb200_band_map")
+    return rows
 
 
 def pinned_empty(shape, dtype):

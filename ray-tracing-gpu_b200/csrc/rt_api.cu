@@ -733,6 +733,19 @@ extern "C" int rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* p3, cons
     return RTB200_OK;
 }
 
+// Pure host arithmetic (no GPU needed): which rows of an H-row image rank `rank` of `n_ranks` renders.
+extern "C" int rtb200_band_map(int height, int band_rows, int n_ranks, int rank, int32_t* out_global_rows, int capacity, int* n_local)
+{
+    if (height < 0 || n_ranks < 1 || rank < 0 || rank >= n_ranks || !n_local) return RTB200_E_ARG;
+    const int band = band_rows > 0 ? band_rows : 16;
+    const int rows = local_row_count(height, band, n_ranks, rank);
+    *n_local = rows;
+    if (!out_global_rows) return RTB200_OK;
+    if (capacity < rows) return RTB200_E_ARG;
+    for (int i = 0; i < rows; ++i) out_global_rows[i] = band_global_row(band, n_ranks, rank, i);
+    return RTB200_OK;
+}
+
 extern "C" int rtb200_comm_unique_id(uint8_t id[RTB200_UNIQUE_ID_BYTES]) { return comm_unique_id(id); }
 extern "C" int rtb200_comm_init(rtb200_ctx* ctx, int rank, int n_ranks, const uint8_t id[RTB200_UNIQUE_ID_BYTES])
 {

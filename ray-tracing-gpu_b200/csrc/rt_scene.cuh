@@ -89,21 +89,27 @@ struct RayQueue {
 RT_DEV V3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
 RT_DEV V3 f4_xyz(float4 v) { return mk3(v.x, v.y, v.z); }
 
+// Interleaved banding (multi-GPU): rank r owns bands r, r + n, r + 2n, ... of `band` rows each and
+// stores them compactly.  Global row of local row `local` -- the ONE formula used by the kernels,
+// the host-side gather and rtb200_band_map.
+__host__ __device__ inline int band_global_row(int band, int n_ranks, int rank, int local)
+{
+    if (n_ranks <= 1) return local;
+    const int b = local / band, r = local - b * band;
+    return (b * n_ranks + rank) * band + r;
+}
+
 // Global lattice row of local lattice row `ly` under interleaved banding.
 RT_DEV int global_lattice_row(const FrameParams& f, int ly)
 {
-    if (f.n_ranks <= 1) return ly;
-    int b = ly / f.band_lrows, r = ly - b * f.band_lrows;
-    return (b * f.n_ranks + f.rank) * f.band_lrows + r;
+    return band_global_row(f.band_lrows, f.n_ranks, f.rank, ly);
 }
 
 // Row of the framebuffer a LOCAL pixel row is stored at (see FrameParams::fb_global).
 RT_DEV int framebuffer_row(const FrameParams& f, int local_row)
 {
-    if (!f.fb_global || f.n_ranks <= 1) return local_row;
-    const int band = f.band_lrows / f.k;
-    const int b = local_row / band, r = local_row - b * band;
-    return (b * f.n_ranks + f.rank) * band + r;
+    if (!f.fb_global) return local_row;
+    return band_global_row(f.band_lrows / f.k, f.n_ranks, f.rank, local_row);
 }
 
 // Primary ray through lattice sample (sx, sy): Scene.cpp:1543-1552.
