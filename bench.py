@@ -258,9 +258,16 @@ def run_gpu(args):
     r.timer_mark(1)
     loop_ms = r.timer_elapsed(0, 1) / steps                 # K frames as ONE device-timed region
     barrier()
-    # keep the GPU under load long enough for the clock sampler to see it
-    t_end = time.time() + 1.0
-    while time.time() < t_end:
+    # keep the GPU under load long enough for the clock sampler to see it.  Every frame contains a
+    # collective at N > 1, so all ranks must run the SAME number of extra frames: it is derived from
+    # the max-over-ranks frame time, not from each rank's own clock.
+    frame_ms = loop_ms
+    if dist is not None:
+        import torch
+        tmax = torch.tensor([loop_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        frame_ms = float(tmax[0])
+    for _ in range(int(min(max(1000.0 / max(frame_ms, 1e-3), 1), 20000))):
         r.render(fr, want_f32=False, want_rgba8=False)
     barrier()
     clocks = sampler.stop()

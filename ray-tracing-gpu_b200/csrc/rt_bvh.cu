@@ -31,6 +31,7 @@
 
 #include "rt_bvh.cuh"
 #include "rt_context.h"
+#include "rt_cull.cuh"
 
 namespace rtb {
 
@@ -233,11 +234,33 @@ RT_DEV float slab(const RayBox& r, float lx, float ly, float lz, float hx, float
     const float az = fmaf(lz, r.iz, -r.oz), bz = fmaf(hz, r.iz, -r.oz);
     const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), limit));
-    return tn * (1.0f - BVH_SLACK) <= tf * (1.0f + BVH_SLACK) ? tn : -1.0f;
+    return tn <= tf * (1.0f + 2.0f * BVH_SLACK) ? tn : -1.0f;
 }
 
-// Generic traversal.  `Leaf` is called as leaf(first, count) and returns the new distance limit
-// (or a negative value to stop the traversal).
+// One triangle of a leaf.  MODE 0 / 2: the conservative fused filter of rt_cull.cuh in ONE pass
+// (det, u, v, t with margins), survivors re-evaluated in the reference's rounding sequence (MODE 0)
+// or fused (MODE 2); MODE 1 (RTB200_F_EXACT_FP): the reference sequence for every test.
+template <int MODE>
+RT_DEV float triangle_leaf(V3 o, V3 d, V3 p0, V3 e1, V3 e2, float tmax)
+{
+    if (MODE == 1) return triangle_t<true>(o, d, p0, e1, e2);
+    const V3 P = cross3<false>(d, e2);
+    const float det = dot3<false>(e1, P);
+    if (!(fabsf(det) >= CULL_DET)) return -1.0f;
+    const float rd = rcp_approx(det);
+    const V3 S = sub3<false>(o, p0);
+    const float u = dot3<false>(S, P) * rd;
+    if (!(fabsf(u - 0.5f) <= 0.5f + CULL_UV)) return -1.0f;
+    const V3 Q = cross3<false>(S, e1);
+    const float v = dot3<false>(d, Q) * rd;
+    const float t = dot3<false>(e2, Q) * rd;
+    if (!(v >= -CULL_UV && u + v <= 1.0f + CULL_UV && t > RT_EPS * 0.99f && t < tmax)) return -1.0f;
+    return MODE == 2 ? triangle_t<false>(o, d, p0, e1, e2) : triangle_t<true>(o, d, p0, e1, e2);
+}
+
+// Generic "while-while" traversal: the inner loop walks internal nodes only, so the lanes of a
+// warp leave it together and run the leaf code converged.  `Leaf` is called as
+// leaf(first, count, limit) and returns the new distance limit (negative = stop the traversal).
 template <class Leaf>
 RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& leaf, unsigned& n_nodes, unsigned& overflow)
 {
@@ -246,8 +269,17 @@ RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& l
     float stack_tn[BVH_STACK];
     int sp = 0;
     int ref = s.bvh_root;
-    for (;;) {
-        if (ref >= 0) {
+    bool alive = true;
+    // pop the next subtree that can still matter
+    auto pop = [&]() {
+        for (;;) {
+            if (sp == 0) { alive = false; ref = -1; return; }
+            --sp;
+            if (stack_tn[sp] <= limit * (1.0f + 2.0f * BVH_SLACK)) { ref = stack_ref[sp]; return; }
+        }
+    };
+    while (alive) {
+        while (ref >= 0) {                                   // ---- internal nodes
             const BvhNode* __restrict__ nd = s.bvh_nodes + ref;
             const float4 b0 = __ldg(&nd->b0), b1 = __ldg(&nd->b1), b2 = __ldg(&nd->b2);
             const int4 c = __ldg(&nd->c);
@@ -259,21 +291,15 @@ RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& l
                 if (sp < BVH_STACK) { stack_ref[sp] = swap ? c.x : c.y; stack_tn[sp] = swap ? t0 : t1; ++sp; }
                 else overflow = 1;
                 ref = swap ? c.y : c.x;
-                continue;
-            }
-            if (t0 >= 0.f) { ref = c.x; continue; }
-            if (t1 >= 0.f) { ref = c.y; continue; }
-        } else {
-            const int code = ~ref;
-            limit = leaf(code & ((1 << BVH_LEAF_SHIFT) - 1), (code >> BVH_LEAF_SHIFT) + 1, limit);
-            if (limit < 0.f) return;
+            } else if (t0 >= 0.f) ref = c.x;
+            else if (t1 >= 0.f) ref = c.y;
+            else { pop(); if (!alive) break; }
         }
-        // pop the next subtree that can still matter
-        for (;;) {
-            if (sp == 0) return;
-            --sp;
-            if (stack_tn[sp] * (1.0f - BVH_SLACK) <= limit * (1.0f + BVH_SLACK)) { ref = stack_ref[sp]; break; }
-        }
+        if (!alive) break;
+        const int code = ~ref;                               // ---- leaf
+        limit = leaf(code & ((1 << BVH_LEAF_SHIFT) - 1), (code >> BVH_LEAF_SHIFT) + 1, limit);
+        if (limit < 0.f) return;
+        pop();
     }
 }
 
@@ -308,8 +334,8 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
             bvh_traverse(s, o, d, 3.0e38f, [&](int first, int count, float limit) -> float {
                 for (int k = 0; k < count; ++k) {
                     const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
-                    const float tt = MODE == 2 ? triangle_t<false>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc))
-                                               : triangle_t<true>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc));
+                    const float tt = triangle_leaf<MODE>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc),
+                                                         best_t < 0.f ? 3.0e38f : fmaf(best_t, CULL_TREL, CULL_TABS));
                     const int ord = __float_as_int(ra.w);
                     if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) {
                         best_t = tt; best_id = ord; limit = tt;
@@ -366,6 +392,7 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
         const float4 a = p.sq0[i], b = p.sq1[i];
         const V3 o = f4_xyz(a), d = f4_xyz(b);
         const float dist = a.w;
+        const float tlim = fmaf(dist, CULL_TREL, CULL_TABS);
         float fr = 1.0f, fg = 1.0f, fb = 1.0f;
         bool zero = false;
         int l_ord[BVH_SHADOW_LIST], l_mat[BVH_SHADOW_LIST];
@@ -376,8 +403,7 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
                 n_tests += (unsigned)count;
                 for (int k = 0; k < count; ++k) {
                     const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
-                    const float tt = MODE == 2 ? triangle_t<false>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc))
-                                               : triangle_t<true>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc));
+                    const float tt = triangle_leaf<MODE>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc), tlim);
                     if (tt > RT_EPS && tt < dist) {
                         const int m = __float_as_int(rb.w);
                         const float4 m0 = __ldg(&s.mat[m].m0);
@@ -456,11 +482,13 @@ cudaError_t launch_bvh_nearest(const TraceParams& p, cudaStream_t st)
     else blocks = (p.n_rays + BVH_THREADS - 1) / BVH_THREADS;
     if (blocks <= 0) return cudaSuccess;
     if (p.primary) {
-        if (p.mode == 2) k_bvh_nearest<2, true><<<blocks, BVH_THREADS, 0, st>>>(p);
-        else             k_bvh_nearest<0, true><<<blocks, BVH_THREADS, 0, st>>>(p);
+        if (p.mode == 2)      k_bvh_nearest<2, true><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else if (p.mode == 1) k_bvh_nearest<1, true><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else                  k_bvh_nearest<0, true><<<blocks, BVH_THREADS, 0, st>>>(p);
     } else {
-        if (p.mode == 2) k_bvh_nearest<2, false><<<blocks, BVH_THREADS, 0, st>>>(p);
-        else             k_bvh_nearest<0, false><<<blocks, BVH_THREADS, 0, st>>>(p);
+        if (p.mode == 2)      k_bvh_nearest<2, false><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else if (p.mode == 1) k_bvh_nearest<1, false><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else                  k_bvh_nearest<0, false><<<blocks, BVH_THREADS, 0, st>>>(p);
     }
     return cudaGetLastError();
 }
@@ -469,8 +497,9 @@ cudaError_t launch_bvh_shadow(const ShadowParams& p, cudaStream_t st)
 {
     const int blocks = (p.n_queries + BVH_THREADS - 1) / BVH_THREADS;
     if (blocks <= 0) return cudaSuccess;
-    if (p.mode == 2) k_bvh_shadow<2><<<blocks, BVH_THREADS, 0, st>>>(p);
-    else             k_bvh_shadow<0><<<blocks, BVH_THREADS, 0, st>>>(p);
+    if (p.mode == 2)      k_bvh_shadow<2><<<blocks, BVH_THREADS, 0, st>>>(p);
+    else if (p.mode == 1) k_bvh_shadow<1><<<blocks, BVH_THREADS, 0, st>>>(p);
+    else                  k_bvh_shadow<0><<<blocks, BVH_THREADS, 0, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -16,48 +16,18 @@
 //     distances are bit-identical to the CPU renderer.
 //   * shadow queries leave at warp granularity once every ray of the warp holds a zero filter.
 #include "rt_stream.cuh"
+#include "rt_cull.cuh"
 #include "rt_tma.cuh"
 
 namespace rtb {
 
 #define FULL_MASK 0xffffffffu
-// culling margins (see DESIGN.md "conservative filter"): relative 1e-3, far above the
-// ~1e-6 relative differences between fused and unfused evaluation
-#define CULL_DET   0.0099f         // |det| >= EPSILON, with 1 % slack
-#define CULL_UV    0.001f
-#define CULL_TREL  1.001f
-#define CULL_TABS  1.0e-3f
-
-RT_DEV float rcp_approx(float x)
-{
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
 
 struct TraceSmem {
     TriRec tile[ST_STAGES][ST_TILE];                 // 24 KB
     unsigned char side[ST_SIDE_MAX];                 // quadric + plane records (when they fit)
     uint64_t full[ST_STAGES];
 };
-
-// Phase-2 of the filter + exact evaluation for one (ray, triangle); returns the reference
-// distance or -1.  `tmin`/`tmax` bound the distances that could still matter to the caller.
-template <int MODE>
-RT_DEV float triangle_survivor(V3 o, V3 d, V3 p0, V3 e1, V3 e2, float tmax)
-{
-    // fused re-evaluation of the whole test with margins
-    const V3 P = cross3<false>(d, e2);
-    const float det = dot3<false>(e1, P);
-    const float rd = rcp_approx(det);
-    const V3 S = sub3<false>(o, p0);
-    const float u = dot3<false>(S, P) * rd;
-    const V3 Q = cross3<false>(S, e1);
-    const float v = dot3<false>(d, Q) * rd;
-    const float t = dot3<false>(e2, Q) * rd;
-    if (!(v >= -CULL_UV && u + v <= 1.0f + CULL_UV && t > RT_EPS * 0.99f && t < tmax)) return -1.0f;
-    return MODE == 2 ? triangle_t<false>(o, d, p0, e1, e2) : triangle_t<true>(o, d, p0, e1, e2);
-}
 
 // ---------------------------------------------------------------------------------------
 // Nearest hit.  One CTA = 1024 rays.  PRIMARY: the rays are a 32x32 tile of the sample lattice

@@ -1,7 +1,7 @@
 // rt_cli.cpp -- headless command line of the renderer: the reference's `exe scene.dat -x W -y H`
 // (Main.cpp:51-124) without GLUT/GLEW: the frame goes to a PPM file instead of a window.
 //   rt_cli scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--fused] [--exact] [--bvh]
-//          [--frames n] [--out image.ppm]
+//          [--frames n] [--out image.ppm] [--obj mesh.obj]
 // Unlike Main.cpp:79 there is no power-of-two / multiple-of-16 restriction on W and H.
 #include <chrono>
 #include <cstdio>
@@ -17,12 +17,13 @@ using namespace Scene;
 int main(int argc, char** argv)
 {
     if (argc < 2) {
-        std::cerr << "usage: " << argv[0] << " scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--fused] [--exact] [--bvh] [--frames n] [--out f.ppm]" << std::endl;
+        std::cerr << "usage: " << argv[0] << " scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--fused] [--exact] [--bvh] [--frames n] [--out f.ppm] [--obj mesh.obj]" << std::endl;
         return EXIT_FAILURE;
     }
     int W = CVar::g_LargeurFenetre, H = CVar::g_HauteurFenetre, depth = -1, spp = 1, frames = 1;
     unsigned int flags = 0;
     const char* out = nullptr;
+    const char* obj = nullptr;
     for (int i = 2; i < argc; ++i) {
         auto next = [&](const char* what) -> const char* {
             if (i + 1 >= argc) { std::cerr << "[ERREUR]: " << what << " needs a value" << std::endl; exit(EXIT_FAILURE); }
@@ -35,6 +36,7 @@ int main(int argc, char** argv)
         else if (!strcmp(argv[i], "--device")) CVar::g_Peripherique = atoi(next("--device"));
         else if (!strcmp(argv[i], "--frames")) frames = atoi(next("--frames"));
         else if (!strcmp(argv[i], "--out")) out = next("--out");
+        else if (!strcmp(argv[i], "--obj")) obj = next("--obj");
         else if (!strcmp(argv[i], "--fused")) flags |= RTB200_F_FUSED_FP;
         else if (!strcmp(argv[i], "--exact")) flags |= RTB200_F_EXACT_FP;
         else if (!strcmp(argv[i], "--bvh")) flags |= RTB200_F_USE_BVH;
@@ -47,6 +49,14 @@ int main(int argc, char** argv)
     scene->AjusterResolution(W, H);
     std::cout << "[ETAT]: Traitement du fichier de scene " << argv[1] << std::endl;
     scene->TraiterFichierDeScene(argv[1]);
+    if (obj) {                                             // triangle mesh appended to the scene file's surfaces
+        CTriangle modele;
+        modele.AjusterCouleur(CCouleur(0.8f, 0.8f, 0.8f));
+        const int n = scene->ChargerMaillageOBJ(obj, modele);
+        if (n < 0) { std::cerr << "[ERREUR]: cannot read " << obj << std::endl; return EXIT_FAILURE; }
+        std::cout << "[ETAT]: " << n << " triangles charges de " << obj << std::endl;
+        if (n > 64) flags |= RTB200_F_USE_BVH;             // meshes go through the LBVH
+    }
     if (scene->NbSurfaces() == 0) { std::cerr << "[ERREUR]: empty scene (file missing or without surfaces)" << std::endl; return EXIT_FAILURE; }
     if (depth >= 0) scene->AjusterNbRebondsMax(depth);
     scene->AjusterSurechantillonnage(spp);

@@ -88,6 +88,46 @@ void CScene::AjusterEnergieMinimale(const REAL e) { m_EnergieMinRayon = e; }
 void CScene::AjusterIndiceRefraction(const REAL i) { m_IndiceRefractionScene = i; }
 GLuint CScene::ObtenirTextureGL() { return 0; }
 
+int CScene::ChargerMaillageOBJ(const char* fichier, const CTriangle& modele)
+{
+    std::ifstream in(fichier);
+    if (!in.is_open()) return -1;
+    std::vector<CVecteur3> sommets;
+    std::string ligne;
+    int ajoutes = 0;
+    while (std::getline(in, ligne)) {
+        if (ligne.size() < 2) continue;
+        if (ligne[0] == 'v' && (ligne[1] == ' ' || ligne[1] == '\t')) {
+            float x = 0.f, y = 0.f, z = 0.f;
+            if (sscanf(ligne.c_str() + 1, "%f %f %f", &x, &y, &z) == 3) sommets.push_back(CVecteur3(x, y, z));
+        } else if (ligne[0] == 'f' && (ligne[1] == ' ' || ligne[1] == '\t')) {
+            std::vector<int> idx;                              // "f a b c ..." with a, a/t, a//n or a/t/n
+            const char* p = ligne.c_str() + 1;
+            while (*p) {
+                while (*p == ' ' || *p == '\t') ++p;
+                if (!*p || *p == '\r' || *p == '#') break;
+                char* fin = nullptr;
+                long v = strtol(p, &fin, 10);
+                if (fin == p) break;
+                const long n = (long)sommets.size();
+                if (v < 0) v = n + v + 1;                      // relative index
+                if (v < 1 || v > n) { idx.clear(); break; }   // dangling reference: drop the face
+                idx.push_back((int)v - 1);
+                p = fin;
+                while (*p && *p != ' ' && *p != '\t') ++p;      // skip /t/n
+            }
+            for (size_t k = 2; k < idx.size(); ++k) {          // fan triangulation
+                CTriangle* t = modele.Copier();
+                t->AjusterPoints(sommets[idx[0]], sommets[idx[k - 1]], sommets[idx[k]]);
+                AjouterSurface(t);
+                ++ajoutes;
+            }
+        }
+    }
+    m_Prepare = false;
+    return ajoutes;
+}
+
 void CScene::Liberer()
 {
     for (ISurface* s : m_Surfaces) delete s;
@@ -353,6 +393,21 @@ int rtscene_load(const char* path, int max_bounces)
     s->TraiterFichierDeScene(path);
     if (max_bounces >= 0) s->AjusterNbRebondsMax(max_bounces);
     return (int)s->NbSurfaces();
+}
+
+// Appends an OBJ mesh to the current scene: colour r g b, reflection coefficient, uniform scale and a
+// translation (applied through the prototype's transformation, i.e. by CTriangle::Pretraitement).
+int rtscene_add_obj(const char* path, const float* rgb, float reflect, float scale, const float* translate)
+{
+    CScene* s = CScene::ObtenirInstance();
+    CTriangle modele;
+    modele.AjusterCouleur(CCouleur(rgb[0], rgb[1], rgb[2]));
+    modele.AjusterCoeffReflexion(reflect);
+    CMatrice4 m(CMatrice4::IDENTITE);                    // scale then translate, post-multiplied like the parser
+    m.MiseAEchelle(scale, scale, scale);
+    m.Translation(translate[0], translate[1], translate[2]);
+    modele.AjusterTransformation(m);
+    return s->ChargerMaillageOBJ(path, modele);
 }
 
 // Packs the current scene for resolution W x H; returns pointers into the scene's own vectors.

@@ -91,6 +91,11 @@ public:
 
     // ---- additions of the headless B200 build -----------------------------------------------
     void AjusterSurechantillonnage(const int grille) { m_GrilleSpp = grille; }       // k x k samples per pixel
+    // Triangle-mesh loader (the roadmap remark of Main.cpp:13-16): every face of a Wavefront OBJ file
+    // (v / f records, polygons fan-triangulated, negative indices allowed) becomes one CTriangle that
+    // copies material AND transformation from `modele`, appended in file order through AjouterSurface.
+    // Returns the number of triangles added, -1 when the file cannot be read.
+    int  ChargerMaillageOBJ(const char* fichier, const CTriangle& modele);
     void AjusterDrapeauxRendu(const unsigned int drapeaux) { m_Drapeaux = drapeaux; } // RTB200_F_*
     const float* ObtenirInfoPixel() const { return m_InfoPixel; }                     // W*H*3 floats, row 0 = bottom
     const unsigned char* ObtenirImageRGBA8() const { return m_ImageRGBA8.data(); }    // W*H*4 bytes

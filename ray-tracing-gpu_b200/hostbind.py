@@ -22,6 +22,7 @@ def lib():
         L.rtscene_load.argtypes = [C.c_char_p, C.c_int]
         L.rtscene_pack.argtypes = [C.c_int, C.c_int, C.POINTER(abi.Scene), C.POINTER(abi.Frame)]
         L.rtscene_render.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.POINTER(abi.Stats)]
+        L.rtscene_add_obj.argtypes = [C.c_char_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p]
         L.rtscene_free.restype = None
         L.rtscene_camera.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(abi.Frame)]
         _lib = L
@@ -70,6 +71,16 @@ def render_loaded(W, H, spp_grid=1, flags=0):
     st = abi.Stats()
     L.rtscene_render(W, H, spp_grid, flags, f.ctypes.data, q.ctypes.data, C.byref(st))
     return f, q, st
+
+
+def add_obj(path, rgb=(0.8, 0.8, 0.8), reflect=0.0, scale=1.0, translate=(0.0, 0.0, 0.0)):
+    """CScene::ChargerMaillageOBJ on the currently loaded scene; returns the triangles added."""
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    tr = np.ascontiguousarray(translate, np.float32)
+    n = lib().rtscene_add_obj(os.fsencode(path), rgb.ctypes.data, float(reflect), float(scale), tr.ctypes.data)
+    if n < 0:
+        raise FileNotFoundError(path)
+    return n
 
 
 def free():

@@ -105,3 +105,68 @@ def test_cli_renders_ppm(rt, host, tmp_path):
     want = golden_image(7, 4)
     q = np.floor(np.clip(want, 0, 1) * np.float32(255) + np.float32(0.5)).astype(np.uint8)
     assert np.array_equal(img, q)
+
+
+def _write_obj(path, nq=12, size=60.0, y0=5.0):
+    """A bumpy nq x nq quad grid (two conventions of face records, one 4-gon per quad)."""
+    xs = np.linspace(-size, size, nq + 1)
+    lines = ["# test mesh"]
+    for j in range(nq + 1):
+        for i in range(nq + 1):
+            lines.append(f"v {xs[i]:.4f} {y0 + 6.0 * np.sin(0.7 * i) * np.cos(0.9 * j):.4f} {xs[j]:.4f}")
+    for j in range(nq):
+        for i in range(nq):
+            a = j * (nq + 1) + i + 1
+            b, c, d = a + 1, a + nq + 2, a + nq + 1
+            if (i + j) % 2:
+                lines.append(f"f {a}/1/1 {d}/2/1 {c}/3/1 {b}/4/1")        # quad, v/vt/vn form
+            else:
+                lines.append(f"f {a - (nq + 1) ** 2 - 1} {d}//7 {c} {b}")   # relative index, v//vn form
+    path.write_text("\n".join(lines) + "\n")
+    return 2 * nq * nq
+
+
+def test_obj_loader_appends_triangles_in_file_order(rt, host, tmp_path):
+    """CScene::ChargerMaillageOBJ: fan-triangulated faces appended through AjouterSurface after the
+    scene file's own surfaces, transformed by the prototype's matrix in Pretraitement."""
+    obj = tmp_path / "grid.obj"
+    n_tri = _write_obj(obj)
+    scene = os.path.join(GOLDEN, "scenes", "scene1.dat")
+    base, _ = host.load_and_pack(scene, 64, 48)
+    host.lib().rtscene_load(os.fsencode(scene), 2)
+    assert host.add_obj(str(obj), rgb=(0.9, 0.2, 0.1), reflect=0.3, scale=2.0, translate=(10.0, 0.0, -5.0)) == n_tri
+    import ctypes as C
+    s, f = rt.abi.Scene(), rt.abi.Frame()
+    host.lib().rtscene_pack(64, 48, C.byref(s), C.byref(f))
+    T0 = len(base["tri_order"])
+    assert s.n_triangles == T0 + n_tri and s.n_quadrics == len(base["quad_order"])
+    pts = np.ctypeslib.as_array(s.tri_points, shape=(s.n_triangles * 9,)).reshape(-1, 3, 3)
+    order = np.ctypeslib.as_array(s.tri_order, shape=(s.n_triangles,))
+    n_base = T0 + len(base["quad_order"]) + len(base["plane_order"])
+    assert list(order[T0:]) == list(range(n_base, n_base + n_tri))      # appended after every scene-file surface
+    # first face: quad (v1, v14, v15, v2) fanned -> (v1, v14, v15), scaled by 2 then translated
+    xs = np.linspace(-60.0, 60.0, 13)
+    v1 = np.array([xs[0], 5.0, xs[0]], np.float32) * np.float32(2.0) + np.array([10.0, 0.0, -5.0], np.float32)
+    assert np.allclose(pts[T0, 0], v1, atol=1e-3)
+    with pytest.raises(FileNotFoundError):
+        host.add_obj(str(tmp_path / "missing.obj"))
+
+
+@pytest.mark.gpu
+def test_obj_mesh_renders_through_lbvh_like_the_oracle(rt, host, port, tmp_path):
+    """scene file + OBJ mesh -> CScene::LancerRayons with RTB200_F_USE_BVH == the oracle's frame."""
+    obj = tmp_path / "grid.obj"
+    _write_obj(obj, nq=24)
+    scene = os.path.join(GOLDEN, "scenes", "scene7.dat")
+    host.lib().rtscene_load(os.fsencode(scene), 3)
+    host.add_obj(str(obj), rgb=(0.2, 0.7, 0.9), reflect=0.4, scale=1.5, translate=(0.0, -20.0, -60.0))
+    f, q, st = host.render_loaded(200, 150, flags=rt.F_USE_BVH)
+    assert st.path == 2 and st.bvh_nodes_visited > 0
+    # the same scene through the packer into the CPU oracle
+    import ctypes as C
+    s, fr = rt.abi.Scene(), rt.abi.Frame()
+    host.lib().rtscene_pack(200, 150, C.byref(s), C.byref(fr))
+    want = np.empty((150, 200, 3), np.float32)
+    port.lib.rto_render(C.byref(s), C.byref(fr), want, port.max_threads)
+    assert np.allclose(f, want, rtol=0, atol=4e-6)
+    assert (np.abs(f - want) > 0).mean() < 0.01
