@@ -191,6 +191,30 @@ int rtb200_measure_fp32_peak(rtb200_ctx* ctx, double* tflops, double* sm_mhz)
 static inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
 static inline float i2f(int v) { float f; memcpy(&f, &v, 4); return f; }
 
+// Centred form of a quadric for the warp-vote culling test of the resident kernels
+// (rt_resident.cu: quadric_miss):  sum_i q_i (x_i - c_i)^2 = rhs  with every q_i >= 0 (not all zero),
+// no mixed terms, no linear term along an axis with q_i == 0 and rhs > 0 -- spheres, ellipsoids and
+// axis-aligned cylinders.  Returns (c, rhs); rhs = -1 means "not of that form" (cones, paraboloids,
+// hyperboloids, rotated quadrics, degenerate cases): never culled.
+static float4 quadric_bounding_sphere(const float* q)
+{
+    const float4 none = make_float4(0.f, 0.f, 0.f, -1.0f);
+    for (int i = 0; i < 10; ++i) if (!std::isfinite(q[i])) return none;
+    if (q[3] != 0.f || q[4] != 0.f || q[5] != 0.f) return none;
+    double c[3] = {0, 0, 0}, rhs = -(double)q[9];
+    bool any = false;
+    for (int i = 0; i < 3; ++i) {
+        const double a = q[i], l = q[6 + i];
+        if (a < 0) return none;
+        if (a == 0) { if (l != 0) return none; continue; }
+        any = true;
+        c[i] = -l / (2.0 * a);
+        rhs += a * c[i] * c[i];
+    }
+    if (!any || !(rhs > 0) || !std::isfinite(rhs) || rhs > 1e30) return none;
+    return make_float4((float)c[0], (float)c[1], (float)c[2], (float)rhs);
+}
+
 extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
 {
     if (!ctx || !s) return RTB200_E_ARG;
@@ -272,6 +296,7 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
         r.r0 = make_float4(c[0], c[1], c[2], i2f(SURF_QUADRIC));
         r.r1 = make_float4(c[3], c[4], c[5], i2f(mat));
         r.r2 = make_float4(c[6], c[7], c[8], c[9]);
+        r.r3 = quadric_bounding_sphere(c);
         quad[i].q0 = make_float4(c[0], c[1], c[2], i2f(ord));
         quad[i].q1 = r.r1; quad[i].q2 = r.r2;
     }
@@ -453,6 +478,7 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
             // no secondary rays and no supersampling: the level-0 kernel is the whole frame
             const bool direct = (level == 0 && !spawn && k == 1);
             p.direct = direct ? 1 : 0;
+            p.cull = (fr->flags & RTB200_F_EXACT_FP) ? 0 : 1;
             p.fb_f32 = ctx->out_f32_dev; p.fb_rgba8 = ctx->out_rgba8_dev;
             const bool timed = (level == 0 && ly0 == 0);       // dominant kernel, timed on its own stream
             if (timed) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
@@ -700,7 +726,8 @@ extern "C" int rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* o3, con
         if (rc != RTB200_OK) return rc;
     } else
     CU(launch_query_nearest(ctx->ds, n, ctx->q_in0.as<float>(), ctx->q_in1.as<float>(), ctx->q_out0.as<int>(),
-                            ctx->q_out1.as<float>(), ctx->q_out2.as<float>(), (flags & RTB200_F_FUSED_FP) == 0, ctx->stream));
+                            ctx->q_out1.as<float>(), ctx->q_out2.as<float>(), (flags & RTB200_F_FUSED_FP) == 0,
+                            (flags & RTB200_F_EXACT_FP) == 0, ctx->stream));
     CU(cudaMemcpyAsync(out_order, ctx->q_out0.p, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(out_t, ctx->q_out1.p, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(out_n3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));
@@ -727,7 +754,7 @@ extern "C" int rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* p3, cons
         if (rc != RTB200_OK) return rc;
     } else
     CU(launch_query_shadow(ctx->ds, n, ctx->q_in0.as<float>(), ctx->q_in1.as<float>(), ctx->q_out2.as<float>(),
-                           (flags & RTB200_F_FUSED_FP) == 0, ctx->stream));
+                           (flags & RTB200_F_FUSED_FP) == 0, (flags & RTB200_F_EXACT_FP) == 0, ctx->stream));
     CU(cudaMemcpyAsync(out3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return RTB200_OK;

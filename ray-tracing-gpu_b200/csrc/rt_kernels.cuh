@@ -33,6 +33,7 @@ struct LevelParams {
     unsigned int* link_count;
     unsigned long long* stats;     // [RT_STAT_SLOTS][ST_COUNT]
     // direct resolve (level 0, spp 1, no secondary rays): the level kernel writes the frame itself
+    int     cull;                  // warp-vote culling of bounded quadrics / triangles (0 with RTB200_F_EXACT_FP)
     int     direct;
     float*  fb_f32;                // [local rows][W][3]
     uchar4* fb_rgba8;              // [local rows][W]
@@ -66,9 +67,9 @@ cudaError_t launch_resolve(const ResolveParams& p, cudaStream_t st);
 
 // ray-level queries over the unified list in global memory (rt_resident.cu)
 cudaError_t launch_query_nearest(const DeviceScene& s, int n, const float* o3, const float* d3,
-                                 int* out_order, float* out_t, float* out_n3, bool exact, cudaStream_t st);
+                                 int* out_order, float* out_t, float* out_n3, bool exact, bool cull, cudaStream_t st);
 cudaError_t launch_query_shadow(const DeviceScene& s, int n, const float* p3, const float* l3,
-                                float* out3, bool exact, cudaStream_t st);
+                                float* out3, bool exact, bool cull, cudaStream_t st);
 
 // FFMA peak micro-benchmark (rt_peak.cu): returns FFMA-chain flop count and elapsed ms
 cudaError_t run_fp32_peak(int sm_count, double* tflops, cudaStream_t st);

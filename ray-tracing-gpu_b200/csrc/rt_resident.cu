@@ -11,27 +11,68 @@
 #include <algorithm>
 
 #include "rt_kernels.cuh"
+#include "rt_cull.cuh"
 #include "rt_tma.cuh"
 
 namespace rtb {
 
 #define RES_THREADS 256
+#ifndef RES_MIN_CTAS
+#define RES_MIN_CTAS 3            // 4 (<= 64 registers) was measured slower: spills, 86.0 vs 83.4 us on config 2
+#endif
 
 struct SceneView {                 // resident blob seen through shared (or global) memory
     const SurfRec*  surf;
     const MatRec*   mat;
     const LightRec* light;
     int n_surf, n_light;
+    bool cull;                     // warp-vote culling allowed (off with RTB200_F_EXACT_FP)
 };
 
+// Conservative "this ray cannot hit the quadric" test for quadrics rtb200_set_scene could write in
+// centred form  sum_i q_i (x_i - c_i)^2 = rhs  with q_i >= 0, rhs > 0 (spheres, ellipsoids, axis-aligned
+// cylinders): r3 = (c, rhs).  In that metric the ray passes the centre at squared distance
+// dist2 = e - b^2 / a  (a = q.d.d, b = q.oc.d, e = q.oc.oc) and misses iff dist2 > rhs.  The reference
+// decides on the sign of delta = ka^2 - kb (Quadrique.cpp:199) evaluated in UN-centred coordinates,
+// whose rounding error in these units is below ~12 * 2^-24 * M, M = sum q_i (o_i^2 + c_i^2); the warp
+// only culls beyond rhs * 1.05 + 2e-5 * M (> 25 x that bound), or when the inflated quadric lies
+// entirely behind the origin.  a > 1e-20 keeps clear of the reference's A == 0 branch
+// (Quadrique.cpp:241), which is an unconditional "hit".
+RT_DEV bool quadric_miss(V3 o, V3 d, float4 r0, float K, float4 r3)
+{
+    const V3 q = mk3(r0.x, r0.y, r0.z);
+    const V3 oc = mk3(r3.x - o.x, r3.y - o.y, r3.z - o.z);
+    const V3 qd = mk3(q.x * d.x, q.y * d.y, q.z * d.z);
+    const V3 qo = mk3(q.x * oc.x, q.y * oc.y, q.z * oc.z);
+    const float a = dot3<false>(qd, d);
+    const float b = dot3<false>(qo, d);
+    const float e = dot3<false>(qo, oc);
+    const float M = fmaf(q.x * o.x, o.x, fmaf(q.y * o.y, o.y, fmaf(q.z * o.z, o.z, r3.w + K)));   // sum q c^2 = rhs + K
+    const float lim = fmaf(r3.w, 1.05f, 2.0e-5f * M);
+    return a > 1.0e-20f && (fmaf(a, e, -b * b) > a * lim || (b < 0.f && e > lim));
+}
+
 // distance of surface record `k` along (o,d); quadrics also report the A==0 branch
-template <bool E> RT_DEV float surface_t(const SurfRec* __restrict__ s, int k, V3 o, V3 d, int& type, bool& linear)
+//
+// Culling with warp votes (k, hence the type, is uniform over the warp): a centred-form quadric
+// no ACTIVE lane's ray can touch (quadric_miss), or a triangle no active lane passes the fused
+// det/u filter of rt_cull.cuh for, is skipped by the whole warp -- the reference sequence below
+// only runs where its result can be a hit, so every value that is kept is still the reference's.
+template <bool E> RT_DEV float surface_t(const SurfRec* __restrict__ s, int k, V3 o, V3 d, bool active, bool cull,
+                                         int& type, bool& linear)
 {
     const float4 r0 = s[k].r0, r1 = s[k].r1, r2 = s[k].r2;
     type = __float_as_int(r0.w);
     linear = false;
-    if (type == SURF_TRIANGLE) return triangle_t<E>(o, d, f4_xyz(r0), f4_xyz(r1), f4_xyz(r2));
+    if (type == SURF_TRIANGLE) {
+        if (cull && !__any_sync(0xffffffffu, active && triangle_candidate(o, d, f4_xyz(r0), f4_xyz(r1), f4_xyz(r2)))) return -1.0f;
+        return triangle_t<E>(o, d, f4_xyz(r0), f4_xyz(r1), f4_xyz(r2));
+    }
     if (type == SURF_QUADRIC) {
+        if (cull) {
+            const float4 r3 = s[k].r3;                 // centred form (c, rhs); rhs <= 0: not cullable
+            if (r3.w > 0.f && !__any_sync(0xffffffffu, active && !quadric_miss(o, d, r0, r2.w, r3))) return -1.0f;
+        }
         Quadric q = { r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r2.x, r2.y, r2.z, r2.w };
         return quadric_t<E>(o, d, q, linear);
     }
@@ -39,12 +80,12 @@ template <bool E> RT_DEV float surface_t(const SurfRec* __restrict__ s, int k, V
 }
 
 // nearest hit: the loop of Scene.cpp:1710-1715 (strict <, so the first surface wins a tie)
-template <bool E> RT_DEV void nearest_hit(const SceneView& sv, V3 o, V3 d, float& best_t, int& best_k, bool& best_lin)
+template <bool E> RT_DEV void nearest_hit(const SceneView& sv, bool active, V3 o, V3 d, float& best_t, int& best_k, bool& best_lin)
 {
     best_t = -1.0f; best_k = -1; best_lin = false;
     for (int k = 0; k < sv.n_surf; ++k) {
         int type; bool lin;
-        float t = surface_t<E>(sv.surf, k, o, d, type, lin);
+        float t = surface_t<E>(sv.surf, k, o, d, active, sv.cull, type, lin);
         if (t > RT_EPS && (t < best_t || best_t < 0.f)) { best_t = t; best_k = k; best_lin = lin; }
     }
 }
@@ -70,7 +111,7 @@ template <bool E> RT_DEV int shadow_filter(const SceneView& sv, bool need, V3 P,
     int k = 0;
     for (; k < sv.n_surf; ++k) {
         int type; bool lin;
-        float t = surface_t<E>(sv.surf, k, P, Ldir, type, lin);
+        float t = surface_t<E>(sv.surf, k, P, Ldir, need, sv.cull, type, lin);
         if (need && t > RT_EPS && t < dist) {
             const int m = __float_as_int(sv.surf[k].r1.w);
             const float4 m0 = sv.mat[m].m0;
@@ -130,7 +171,7 @@ RT_DEV uchar4 quantise_rgba8(float r, float g, float b, unsigned int& nans)
 // RGBA8 framebuffers itself and the frame is ONE kernel.
 // ---------------------------------------------------------------------------------------
 template <bool E, bool PRIMARY>
-__global__ void __launch_bounds__(RES_THREADS)
+__global__ void __launch_bounds__(RES_THREADS, RES_MIN_CTAS)
 k_resident_level(const __grid_constant__ LevelParams p)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -151,7 +192,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
     sv.surf  = reinterpret_cast<const SurfRec*>(smem);
     sv.mat   = reinterpret_cast<const MatRec*>(smem + p.rl.off_mat);
     sv.light = reinterpret_cast<const LightRec*>(smem + p.rl.off_light);
-    sv.n_surf = p.rl.n_surf; sv.n_light = p.rl.n_light;
+    sv.n_surf = p.rl.n_surf; sv.n_light = p.rl.n_light; sv.cull = p.cull != 0;
     unsigned int n_shadow = 0, n_tests = 0, n_refl_st = 0, n_refr_st = 0, n_nan = 0;
 
     for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
@@ -180,7 +221,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
 
     // ---- nearest hit (Scene.cpp:1705-1720) -----------------------------------------------
     float t; int k; bool lin;
-    nearest_hit<E>(sv, o, d, t, k, lin);
+    nearest_hit<E>(sv, valid, o, d, t, k, lin);
     const bool hit = valid && k >= 0;
 
     float cr = f.background[0], cg = f.background[1], cb = f.background[2];
@@ -367,15 +408,15 @@ __global__ void __launch_bounds__(256) k_resolve(const ResolveParams p)
 // ---------------------------------------------------------------------------------------
 template <bool E>
 __global__ void __launch_bounds__(128) k_query_nearest(DeviceScene s, int n, const float* o3, const float* d3,
-                                                       int* out_order, float* out_t, float* out_n3)
+                                                       int* out_order, float* out_t, float* out_n3, bool cull)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = i < n;
-    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light;
+    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light; sv.cull = cull;
     V3 o = valid ? ld3(o3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
     V3 d = valid ? ld3(d3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
     float t; int k; bool lin;
-    nearest_hit<E>(sv, o, d, t, k, lin);
+    nearest_hit<E>(sv, valid, o, d, t, k, lin);
     if (!valid) return;
     V3 N = k >= 0 ? hit_normal<E>(sv, k, o, d, t, lin) : mk3(0.f, 0.f, 0.f);
     out_order[i] = k; out_t[i] = t;
@@ -383,11 +424,11 @@ __global__ void __launch_bounds__(128) k_query_nearest(DeviceScene s, int n, con
 }
 
 template <bool E>
-__global__ void __launch_bounds__(128) k_query_shadow(DeviceScene s, int n, const float* p3, const float* l3, float* out3)
+__global__ void __launch_bounds__(128) k_query_shadow(DeviceScene s, int n, const float* p3, const float* l3, float* out3, bool cull)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = i < n;
-    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light;
+    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light; sv.cull = cull;
     V3 P = valid ? ld3(p3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
     V3 L = valid ? ld3(l3 + 3 * (size_t)i) : mk3(1.f, 0.f, 0.f);
     V3 Ld = sub3<E>(L, P);
@@ -455,20 +496,20 @@ cudaError_t launch_resolve(const ResolveParams& p, cudaStream_t st)
 }
 
 cudaError_t launch_query_nearest(const DeviceScene& s, int n, const float* o3, const float* d3,
-                                 int* out_order, float* out_t, float* out_n3, bool exact, cudaStream_t st)
+                                 int* out_order, float* out_t, float* out_n3, bool exact, bool cull, cudaStream_t st)
 {
     const dim3 grid((unsigned)((n + 127) / 128));
-    if (exact) k_query_nearest<true><<<grid, 128, 0, st>>>(s, n, o3, d3, out_order, out_t, out_n3);
-    else       k_query_nearest<false><<<grid, 128, 0, st>>>(s, n, o3, d3, out_order, out_t, out_n3);
+    if (exact) k_query_nearest<true><<<grid, 128, 0, st>>>(s, n, o3, d3, out_order, out_t, out_n3, cull);
+    else       k_query_nearest<false><<<grid, 128, 0, st>>>(s, n, o3, d3, out_order, out_t, out_n3, cull);
     return cudaGetLastError();
 }
 
 cudaError_t launch_query_shadow(const DeviceScene& s, int n, const float* p3, const float* l3,
-                                float* out3, bool exact, cudaStream_t st)
+                                float* out3, bool exact, bool cull, cudaStream_t st)
 {
     const dim3 grid((unsigned)((n + 127) / 128));
-    if (exact) k_query_shadow<true><<<grid, 128, 0, st>>>(s, n, p3, l3, out3);
-    else       k_query_shadow<false><<<grid, 128, 0, st>>>(s, n, p3, l3, out3);
+    if (exact) k_query_shadow<true><<<grid, 128, 0, st>>>(s, n, p3, l3, out3, cull);
+    else       k_query_shadow<false><<<grid, 128, 0, st>>>(s, n, p3, l3, out3, cull);
     return cudaGetLastError();
 }
 

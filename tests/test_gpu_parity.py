@@ -126,3 +126,43 @@ def test_full_size_1080p_properties(rt, renderer, port):
     # a crop of a frame equals the same pixels rendered as the lattice region by the oracle
     reg, _ = port.render_region(ps, fr, 900, 500, 64, 32, threads=4)
     assert bits_equal(got[500:532, 900:964], reg)
+
+
+def test_warp_vote_culling_changes_no_bit(rt, renderer, port):
+    """Resident kernels: culling by bounding-sphere / fused-filter warp votes (default) against the
+    same kernels with every test evaluated (RTB200_F_EXACT_FP) and against the oracle: 400 small
+    ellipsoids + 300 triangles seen from far away, so that most rays graze many bounding spheres."""
+    from importlib import import_module
+    synth = import_module("rtb200.synth")
+    ps = synth.soup(300, 400, 3, seed=31, radius=25.0)
+    renderer.set_scene(ps)
+    W, H = 320, 200
+    a, _, sa = renderer.render(rt.make_frame(ps.frame, W, H, max_bounces=3, flags=rt.F_FORCE_RESIDENT))
+    b, _, sb = renderer.render(rt.make_frame(ps.frame, W, H, max_bounces=3, flags=rt.F_FORCE_RESIDENT | rt.F_EXACT_FP))
+    assert sa.path == 0 and sb.path == 0
+    assert bits_equal(a, b)
+    assert (sa.rays_shadow, sa.rays_reflect, sa.rays_refract) == (sb.rays_shadow, sb.rays_reflect, sb.rays_refract)
+    want, _ = port.render(ps, rt.make_frame(ps.frame, W, H, max_bounces=3), threads=port.max_threads)
+    assert np.allclose(a, want, rtol=0, atol=4e-6)
+    # near-tangent rays: aim at the silhouettes of the bounding spheres
+    rng = np.random.default_rng(5)
+    q = ps["quad_coef"]
+    ctr = -q[:, 6:9] / (2 * q[:, 0:3])
+    rad = np.sqrt((q[:, 0:3] * ctr * ctr).sum(1, keepdims=True) - q[:, 9:10]) / np.sqrt(q[:, 0:3])   # semi-axes
+    n = 40000
+    pick = rng.integers(0, len(q), n)
+    off = rng.normal(size=(n, 3)); off /= np.linalg.norm(off, axis=1, keepdims=True)
+    tgt = ctr[pick] + off * rad[pick] * rng.uniform(0.9, 1.1, (n, 1))
+    org = (np.asarray(ps.frame["cam_pos"], np.float32) + rng.uniform(-20, 20, (n, 3))).astype(np.float32)
+    d = tgt - org
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    i0, t0, n0 = renderer.trace_nearest(org, d, flags=rt.F_FORCE_RESIDENT)
+    i1, t1, n1 = renderer.trace_nearest(org, d, flags=rt.F_FORCE_RESIDENT | rt.F_EXACT_FP)
+    assert np.array_equal(i0, i1) and bits_equal(t0, t1) and bits_equal(n0, n1)
+    wi, wt, _ = port.nearest(ps, org, d, threads=port.max_threads)
+    assert np.array_equal(i0, wi) and bits_equal(t0, wt)
+    lights = np.tile(ps["lights"][0, 0:3], (n, 1)).astype(np.float32)
+    pts = (tgt + rng.normal(size=(n, 3)) * 30).astype(np.float32)
+    f0 = renderer.trace_shadow(pts, lights, flags=rt.F_FORCE_RESIDENT)
+    f1 = renderer.trace_shadow(pts, lights, flags=rt.F_FORCE_RESIDENT | rt.F_EXACT_FP)
+    assert bits_equal(f0, f1)
