@@ -17,8 +17,10 @@ WEAKLY (image height x N), c5 STRONGLY (the config fixes the image).
 
 One "step" = one frame.  The timed region is K frames bracketed by a barrier and a device
 synchronisation on both sides, timed with CUDA events on the library's own stream
-(rtb200_timer_mark), max over ranks.  `value` = rays of the whole job / that time, scene resident
-in HBM.  `e2e` = the same through the C ABI with HOST buffers: every step uploads the packed scene
+(rtb200_timer_mark), max over ranks; the K frames are submitted as one camera path through
+rtb200_render_sequence (pipelined where the path allows it -- config 2 --, frame by frame
+otherwise; `ms_per_frame_synchronous_calls` is the same loop through K synchronous rtb200_render
+calls).  `value` = rays of the whole job / that time, scene resident in HBM.  `e2e` = the same through the C ABI with HOST buffers: every step uploads the packed scene
 from host memory (rtb200_set_scene, plus rtb200_build_bvh for the LBVH workloads) and reads the
 RGBA8 frame back into pinned host memory.  A ray = one nearest-hit query or one shadow-filter
 query.  `--impl reference` times the reference's own CPU renderer instead.
@@ -248,15 +250,26 @@ def run_gpu(args):
     dev_ms, prim_ms, launches = [], [], 0
     stage = np.zeros(3)
     st = None
-    r.timer_mark(0)
+    # frame-by-frame through the synchronous call (per-kernel device times for the roofline) ...
+    r.timer_mark(2)
     for _ in range(steps):
         _, _, st = r.render(fr, want_f32=False, want_rgba8=False)
         dev_ms.append(st.ms_render + st.ms_gather)
         prim_ms.append(st.ms_primary_kernel)
         stage += (st.ms_trace_nearest, st.ms_trace_shadow, st.ms_shade)
         launches += st.kernel_launches
+    r.timer_mark(3)
+    sync_loop_ms = r.timer_elapsed(2, 3) / steps
+    barrier()
+    # ... and the K timed steps as ONE submission (rtb200_render_sequence: the frames of a camera
+    # path enqueued back to back where the path allows it, else the same frame-by-frame loop)
+    r.render_sequence([fr] * min(steps, 3), want_stats=False)
+    barrier()
+    r.timer_mark(0)
+    _, seq_stats = r.render_sequence([fr] * steps)
     r.timer_mark(1)
     loop_ms = r.timer_elapsed(0, 1) / steps                 # K frames as ONE device-timed region
+    assert all(s.rays_primary == st.rays_primary and s.rays_shadow == st.rays_shadow for s in seq_stats)
     barrier()
     # keep the GPU under load long enough for the clock sampler to see it.  Every frame contains a
     # collective at N > 1, so all ranks must run the SAME number of extra frames: it is derived from
@@ -267,8 +280,9 @@ def run_gpu(args):
         tmax = torch.tensor([loop_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         frame_ms = float(tmax[0])
-    for _ in range(int(min(max(1000.0 / max(frame_ms, 1e-3), 1), 20000))):
-        r.render(fr, want_f32=False, want_rgba8=False)
+    n_load = int(min(max(1000.0 / max(frame_ms, 1e-3), 1), 20000))
+    for i in range(0, n_load, 256):
+        r.render_sequence([fr] * min(256, n_load - i), want_stats=False)
     barrier()
     clocks = sampler.stop()
     rays_local = float(st.rays)
@@ -352,6 +366,7 @@ def run_gpu(args):
                    "parallelism": f"interleaved 16-row image bands x{world}, scene replicated, NCCL gather to rank 0",
                    "arithmetic": "reference rounding sequence (bit-exact mode)"},
         "rays_per_frame": rays_total, "ms_per_frame": ms_max, "device_ms_per_frame": dev_max,
+        "ms_per_frame_synchronous_calls": sync_loop_ms,
         "stage_ms_per_frame": {"trace_nearest": stage[0] / steps, "trace_shadow": stage[1] / steps, "shade": stage[2] / steps},
         "rays": {"primary": st.rays_primary, "shadow": st.rays_shadow, "reflect": st.rays_reflect, "refract": st.rays_refract, "rank": 0},
         "e2e": {"value": rays_total / (e2e_max * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": e2e_max,

@@ -183,6 +183,18 @@ int  rtb200_bvh_info(rtb200_ctx* ctx, int* n_nodes, int* n_triangles, double* bu
 int  rtb200_render(rtb200_ctx* ctx, const rtb200_frame* frame,
                    float* out_rgb_f32, uint8_t* out_rgba8, rtb200_stats* stats);
 int  rtb200_read_frame(rtb200_ctx* ctx, float* out_rgb_f32, uint8_t* out_rgba8);
+/* A camera path as ONE pipelined submission (the reference renders a single frame per process,
+ * Main.cpp:181; repeated frames with the scene resident are SURVEY.md 8f rank 2).  All frames share
+ * width, height, spp_grid, flags and band_rows.  out_rgba8 (HOST, n_frames * W*H*4 bytes, frame i at
+ * offset i * W*H*4) and stats ([n_frames]) may be NULL.  Frames whose level-0 kernel is the whole
+ * frame (scene-resident path, no secondary rays, spp_grid 1) are enqueued back to back with no host
+ * round trip between them, read back on a second stream while the next frame renders, and -- with a
+ * communicator and peer access -- signalled with one asynchronous all-reduce per frame; any other
+ * sequence is rendered frame by frame through rtb200_render (identical results).  With several
+ * ranks out_rgba8 must be NULL for the pipelined form; the last frame stays on rank 0
+ * (rtb200_read_frame).  Per-frame ms_render of a pipelined sequence = sequence time / n_frames. */
+int  rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frames, int n_frames,
+                            uint8_t* out_rgba8, rtb200_stats* stats);
 
 /* Ray-level entry points used by the parity tests (the per-ray oracle of SURVEY.md 8c has
  * the same shape): n rays in, nearest hit (insertion order index or -1, distance, normal)

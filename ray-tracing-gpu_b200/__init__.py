@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "librtb200.so")
 
 EXPORTS = [
     "rtb200_abi_version", "rtb200_create", "rtb200_destroy", "rtb200_error_string", "rtb200_last_error",
-    "rtb200_set_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_read_frame",
+    "rtb200_set_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_render_sequence", "rtb200_read_frame",
     "rtb200_trace_nearest", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init", "rtb200_band_map",
     "rtb200_host_alloc", "rtb200_host_free", "rtb200_measure_fp32_peak", "rtb200_device_info",
     "rtb200_timer_mark", "rtb200_timer_elapsed",
@@ -56,6 +56,7 @@ def lib():
         L.rtb200_bvh_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.rtb200_render.argtypes = [vp, C.POINTER(abi.Frame), vp, vp, C.POINTER(abi.Stats)]
         L.rtb200_read_frame.argtypes = [vp, vp, vp]
+        L.rtb200_render_sequence.argtypes = [vp, vp, C.c_int, vp, vp]
         L.rtb200_trace_nearest.argtypes = [vp, C.c_int, vp, vp, C.c_uint32, vp, vp, vp]
         L.rtb200_trace_shadow.argtypes = [vp, C.c_int, vp, vp, C.c_uint32, vp]
         L.rtb200_comm_unique_id.argtypes = [vp]
@@ -189,10 +190,20 @@ class Renderer:
         self._check(self.L.rtb200_render(self.h, C.byref(frame), pf, p8, C.byref(st)))
         return (out_f32 if want_f32 else None), (out_rgba8 if want_rgba8 else None), st
 
-    def read_frame(self, H, W):
-        f = np.empty((H, W, 3), np.float32)
+    def render_sequence(self, frames, out_rgba8=None, want_stats=True):
+        """frames: list of abi.Frame (same size / flags).  out_rgba8: None or a uint8 array
+        [n, H, W, 4] (pinned for true overlap).  Returns (out_rgba8, list of Stats)."""
+        n = len(frames)
+        arr = (abi.Frame * n)(*frames)
+        sts = (abi.Stats * n)() if want_stats else None
+        p8 = out_rgba8.ctypes.data if out_rgba8 is not None else None
+        self._check(self.L.rtb200_render_sequence(self.h, C.byref(arr), n, p8, C.byref(sts) if want_stats else None))
+        return out_rgba8, (list(sts) if want_stats else None)
+
+    def read_frame(self, H, W, want_f32=True):
+        f = np.empty((H, W, 3), np.float32) if want_f32 else None
         q = np.empty((H, W, 4), np.uint8)
-        self._check(self.L.rtb200_read_frame(self.h, f.ctypes.data, q.ctypes.data))
+        self._check(self.L.rtb200_read_frame(self.h, f.ctypes.data if want_f32 else None, q.ctypes.data))
         return f, q
 
     def trace_nearest(self, org, dirs, flags=0):

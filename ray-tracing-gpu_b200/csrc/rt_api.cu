@@ -117,6 +117,7 @@ void rtb200_destroy(rtb200_ctx* ctx)
     ctx->scene_buf.release(); ctx->stage.release();
     ctx->c0.release(); ctx->fb_f32.release(); ctx->fb_rgba8.release(); ctx->stats.release(); ctx->counters.release();
     ctx->full_f32.release(); ctx->full_rgba8.release(); ctx->h_small.release();
+    ctx->seq_fb[0].release(); ctx->seq_fb[1].release(); ctx->seq_stats.release(); ctx->seq_host.release();
     for (auto& l : ctx->levels) { l.od0.release(); l.od1.release(); l.colour.release(); l.links.release(); }
     ctx->q_in0.release(); ctx->q_in1.release(); ctx->q_out0.release(); ctx->q_out1.release(); ctx->q_out2.release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -360,7 +361,8 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
 #define MAX_CHUNK_SAMPLES (16u << 20)
 #define RESIDENT_AUTO_BYTES (64 * 1024)       // scenes up to this blob size use the fused resident kernels
 
-static int local_row_count(int H, int band_rows, int n_ranks, int rank)
+namespace rtb {
+int local_row_count(int H, int band_rows, int n_ranks, int rank)
 {
     if (n_ranks <= 1) return H;
     int rows = 0;
@@ -368,7 +370,7 @@ static int local_row_count(int H, int band_rows, int n_ranks, int rank)
     return rows;
 }
 
-static void fill_frame_params(const rtb200_frame* fr, int n_ranks, int rank, FrameParams& f)
+void fill_frame_params(const rtb200_frame* fr, int n_ranks, int rank, FrameParams& f)
 {
     memset(&f, 0, sizeof f);
     f.W = fr->width; f.H = fr->height;
@@ -389,6 +391,7 @@ static void fill_frame_params(const rtb200_frame* fr, int n_ranks, int rank, Fra
     f.band_lrows = band * f.k;
     f.n_ranks = n_ranks; f.rank = rank;
 }
+} // namespace rtb
 
 // Overlapped read-back: called after the kernel that finished pixel rows [py0, py0 + prows) of the
 // local frame.  The copy stream waits for that kernel only, so the transfer of chunk i runs under

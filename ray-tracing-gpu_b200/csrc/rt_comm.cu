@@ -301,18 +301,20 @@ int comm_peer_frame(rtb200_ctx* c, int W, int H, bool want_f32, void** rgba8, vo
 
 // After the kernels that stored into rank 0's frame: one tiny all-reduce, ordered after them on
 // every rank's stream.  When it completes on rank 0, every rank's stores have landed.
-int comm_peer_frame_done(rtb200_ctx* c, double* ms)
+int comm_peer_frame_done(rtb200_ctx* c, double* ms, bool wait, cudaStream_t on)
 {
+    cudaStream_t s = on ? on : c->stream;
     NcclApi* a = nccl_api();
     Comm* cm = c->comm;
     if (!a || !cm) return RTB200_E_STATE;
     cudaError_t e;
     if ((e = cm->sync.ensure(2 * sizeof(int))) != cudaSuccess) return set_cuda_error(c, e, "sync buffer");
-    cudaEventRecord(cm->e0, c->stream);
-    ncclResult_t r = a->AllReduce(cm->sync.p, cm->sync.as<int>() + 1, 1, ncclInt, ncclMin, cm->comm, c->stream);
+    if (wait) cudaEventRecord(cm->e0, s);
+    ncclResult_t r = a->AllReduce(cm->sync.p, cm->sync.as<int>() + 1, 1, ncclInt, ncclMin, cm->comm, s);
     if (r != ncclSuccess) return nccl_fail(c, r, "ncclAllReduce");
-    cudaEventRecord(cm->e1, c->stream);
-    if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return set_cuda_error(c, e, "peer frame sync");
+    if (!wait) return RTB200_OK;
+    cudaEventRecord(cm->e1, s);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return set_cuda_error(c, e, "peer frame sync");
     float t = 0.f;
     cudaEventElapsedTime(&t, cm->e0, cm->e1);
     if (ms) *ms = t;

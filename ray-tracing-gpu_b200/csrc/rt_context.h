@@ -92,6 +92,8 @@ struct rtb200_ctx {
     float*   host_f32 = nullptr;      // non-null during a render that overlaps its read-back
     uint8_t* host_rgba8 = nullptr;
     int      copy_chunks = 0;         // chunks already handed to the copy stream in this frame
+    rtb::DevBuf seq_fb[2], seq_stats;  // rtb200_render_sequence: double-buffered RGBA8 frames, per-frame counters
+    rtb::PinnedBuf seq_host;
     int last_W = 0, last_H = 0, last_local_rows = 0;
     bool last_gathered = false;
 
@@ -113,6 +115,8 @@ struct rtb200_ctx {
 
 namespace rtb {
 int  set_cuda_error(rtb200_ctx* c, cudaError_t e, const char* where);
+int  local_row_count(int H, int band_rows, int n_ranks, int rank);          // rt_api.cu
+void fill_frame_params(const rtb200_frame* fr, int n_ranks, int rank, FrameParams& f);
 int  chunk_copy_out(rtb200_ctx* c, int W, int py0, int prows);              // rt_api.cu: overlapped read-back of finished rows
 int  render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
                      bool exact, rtb200_stats* st, uint32_t* launches);     // rt_stream.cu
@@ -125,5 +129,5 @@ int  comm_init(rtb200_ctx* c, int rank, int n_ranks, const uint8_t* id);
 void comm_destroy(rtb200_ctx* c);
 int  comm_gather_frame(rtb200_ctx* c, int W, int H, int band_rows, bool want_f32, bool want_rgba8, double* ms);
 int  comm_peer_frame(rtb200_ctx* c, int W, int H, bool want_f32, void** rgba8, void** f32);   // collective; null = use the gather
-int  comm_peer_frame_done(rtb200_ctx* c, double* ms);
+int  comm_peer_frame_done(rtb200_ctx* c, double* ms, bool wait = true, cudaStream_t on = nullptr);    // wait = false: only enqueue the signal
 }

@@ -43,6 +43,26 @@ for name, ps, W, H, depth, k, flags, bvh in cases:
             bad += (not ok8) + (not okf)
             print(json.dumps({"case": name, "ranks": world, "gather_f32": gather_f32, "p2p": not bool(os.environ.get("RTB200_NO_P2P")),
                               "rgba8_equal": ok8, "f32_equal": okf, "ms_gather": st.ms_gather, "ms_render": st.ms_render}), flush=True)
+# a pipelined camera path (rtb200_render_sequence): the LAST frame left in rank 0's memory must equal
+# the frame one GPU renders alone for the last camera
+ps = rt.PackedScene.load(os.path.join(ROOT, "tests/golden/packed/scene1.npz"))
+r.set_scene(ps)
+W, H, n = 640, 363, 24
+frames = []
+for i in range(n):
+    fr = rt.make_frame(ps.frame, W, H, max_bounces=2)
+    fr.cam_pos[0] += 3.0 * i
+    frames.append(fr)
+_, sts = r.render_sequence(frames)
+dist.barrier()
+if rank == 0:
+    _, got = r.read_frame(H, W, want_f32=False)
+    solo.set_scene(ps)
+    _, want, _ = solo.render(frames[-1])
+    ok = bool(np.array_equal(got, want))
+    bad += not ok
+    print(json.dumps({"case": "scene1 sequence of 24 cameras (last frame)", "ranks": world, "rgba8_equal": ok,
+                      "ms_per_frame": sts[0].ms_render}), flush=True)
 flag = torch.tensor([bad], device="cuda"); dist.broadcast(flag, src=0)
 dist.destroy_process_group()
 sys.exit(1 if int(flag.item()) else 0)
