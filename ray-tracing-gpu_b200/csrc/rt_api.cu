@@ -389,6 +389,9 @@ void fill_frame_params(const rtb200_frame* fr, int n_ranks, int rank, FrameParam
     f.secondary = (fr->flags & RTB200_F_NO_SECONDARY) ? 0 : 1;
     const int band = fr->band_rows > 0 ? fr->band_rows : 16;
     f.band_lrows = band * f.k;
+    auto log2_exact = [](int v) { int s = 0; while ((1 << s) < v) ++s; return (1 << s) == v ? s : -1; };
+    f.band_lshift = log2_exact(f.band_lrows);
+    f.band_pshift = log2_exact(band);
     f.n_ranks = n_ranks; f.rank = rank;
 }
 } // namespace rtb
@@ -483,6 +486,11 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
             p.direct = direct ? 1 : 0;
             p.cull = (fr->flags & RTB200_F_EXACT_FP) ? 0 : 1;
             p.fb_f32 = ctx->out_f32_dev; p.fb_rgba8 = ctx->out_rgba8_dev;
+            if (direct && ctx->peer_cur && ly0 + rows_per_chunk >= local_LH) {
+                // the frame's last producing kernel carries the completion signal to rank 0 itself
+                const PeerFrame* pf = static_cast<const PeerFrame*>(ctx->peer_cur);
+                if (pf->flag) { p.peer_flag = pf->flag; p.peer_done = pf->done; p.peer_seq = pf->seq; ctx->peer_signalled = true; }
+            }
             const bool timed = (level == 0 && ly0 == 0);       // dominant kernel, timed on its own stream
             if (timed) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
             CU(launch_resident_level(p, exact, ctx->sm_count, ctx->stream));
@@ -547,9 +555,9 @@ static int read_back(rtb200_ctx* ctx, float* out_f32, uint8_t* out_rgba8, double
     const size_t px = rows * (size_t)ctx->last_W;
     CU(cudaEventRecord(ctx->ev[2], ctx->stream));
     if (out_f32)
-        CU(cudaMemcpyAsync(out_f32, full ? ctx->full_f32.p : ctx->fb_f32.p, px * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaMemcpyAsync(out_f32, full ? static_cast<void*>(ctx->full_f32.as<unsigned char>() + ctx->full_off32) : ctx->fb_f32.p, px * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     if (out_rgba8)
-        CU(cudaMemcpyAsync(out_rgba8, full ? ctx->full_rgba8.p : ctx->fb_rgba8.p, px * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaMemcpyAsync(out_rgba8, full ? static_cast<void*>(ctx->full_rgba8.as<unsigned char>() + ctx->full_off8) : ctx->fb_rgba8.p, px * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaEventRecord(ctx->ev[3], ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     float t = 0.f;
@@ -590,16 +598,19 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     const bool multi = ctx->comm && ctx->n_ranks > 1;
     const bool gather_f32 = (fr->flags & RTB200_F_GATHER_F32) != 0;
     bool peer = false;
+    PeerFrame pf;
+    ctx->peer_cur = nullptr; ctx->peer_signalled = false;
     if (multi) {
         if (ctx->rank == 0 && out_f32 && !gather_f32) return fail(ctx, RTB200_E_ARG, "float output on several GPUs needs RTB200_F_GATHER_F32");
-        void *p8 = nullptr, *p32 = nullptr;
-        const int prc = comm_peer_frame(ctx, fp.W, fp.H, gather_f32, &p8, &p32);
+        // rank 0 entering this frame has consumed the previous one: it tells the peers so (ack)
+        const int prc = comm_peer_begin(ctx, fp.W, fp.H, gather_f32, true, false, &pf, ctx->stream);
         if (prc != RTB200_OK) return prc;
-        if (p8) {
+        if (pf.rgba8) {
             peer = true;
             fp.fb_global = 1;
-            ctx->out_rgba8_dev = static_cast<uchar4*>(p8);
-            ctx->out_f32_dev = static_cast<float*>(p32);          // null unless the float frame is gathered too
+            ctx->out_rgba8_dev = static_cast<uchar4*>(pf.rgba8);
+            ctx->out_f32_dev = static_cast<float*>(pf.f32);       // null unless the float frame is gathered too
+            ctx->peer_cur = &pf;
         }
     }
 
@@ -624,6 +635,8 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
         else            rc = render_resident(ctx, fr, fp, local_rows, exact, &st, &launches);
     }
     ctx->host_f32 = nullptr; ctx->host_rgba8 = nullptr;
+    ctx->peer_cur = nullptr;
+    if (rc != RTB200_OK && peer && ctx->rank != 0 && !ctx->peer_signalled) comm_peer_signal(ctx, pf, ctx->stream);   // never leave rank 0 waiting
     if (rc != RTB200_OK) { cudaStreamSynchronize(ctx->stream); cudaStreamSynchronize(ctx->copy_stream); (void)cudaGetLastError(); return rc; }
     CU(cudaEventRecord(ctx->ev[1], ctx->stream));
     const bool copied = overlap && ctx->copy_chunks > 0;
@@ -631,8 +644,16 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
 
     ctx->last_W = fp.W; ctx->last_H = fp.H; ctx->last_local_rows = local_rows; ctx->last_gathered = false;
     if (multi) {
-        if (peer) rc = comm_peer_frame_done(ctx, &st.ms_gather);
-        else      rc = comm_gather_frame(ctx, fp.W, fp.H, band, gather_f32, true, &st.ms_gather);
+        if (peer) {
+            // ranks > 0: the completion word, unless the producing kernel wrote it itself;
+            // rank 0: the stream waits for every peer's word before anything reads the frame
+            if (ctx->rank != 0 && !ctx->peer_signalled) rc = comm_peer_signal(ctx, pf, ctx->stream);
+            if (rc == RTB200_OK && ctx->rank == 0) {
+                CU(cudaEventRecord(ctx->ev[6], ctx->stream));
+                rc = comm_peer_wait(ctx, pf, ctx->stream);
+                CU(cudaEventRecord(ctx->ev[7], ctx->stream));
+            }
+        } else rc = comm_gather_frame(ctx, fp.W, fp.H, band, gather_f32, true, &st.ms_gather);
         if (rc != RTB200_OK) return rc;
         ctx->last_gathered = (ctx->rank == 0);
     }
@@ -646,6 +667,11 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
     st.ms_render = ms;
+    if (peer && ctx->rank == 0) {
+        float w = 0.f;
+        CU(cudaEventElapsedTime(&w, ctx->ev[6], ctx->ev[7]));
+        st.ms_gather = w;                                       // how long rank 0 waited for the slowest peer
+    }
     if (st.ms_primary_kernel < 0.0) {                          // level-0 kernel of the first chunk
         float k0 = 0.f;
         CU(cudaEventElapsedTime(&k0, ctx->ev[2], ctx->ev[3]));

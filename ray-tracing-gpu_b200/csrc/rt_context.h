@@ -63,7 +63,7 @@ struct rtb200_ctx {
     size_t smem_optin = 0;
     char name[128] = {0};
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // 6/7: wait for the peers
     cudaEvent_t timer[4] = {nullptr, nullptr, nullptr, nullptr};   // rtb200_timer_mark
     std::string last_error;
 
@@ -80,7 +80,8 @@ struct rtb200_ctx {
     // frame buffers (local rows of this rank)
     rtb::DevBuf c0, fb_f32, fb_rgba8, stats, counters;
     bool stats_clean = false;         // the device counters were zeroed at the end of the previous frame
-    rtb::DevBuf full_f32, full_rgba8; // rank 0 with a communicator: gathered frame
+    rtb::DevBuf full_f32, full_rgba8; // rank 0 with a communicator: gathered frame (peer frame: two halves + flag words)
+    size_t full_off8 = 0, full_off32 = 0;   // byte offset of the LAST frame inside them
     rtb::PinnedBuf h_small;           // counters / stats read-back
     std::vector<rtb::LevelBuf> levels;
     float*  out_f32_dev = nullptr;    // where THIS frame's kernels store pixels: the local band buffers, or
@@ -103,6 +104,8 @@ struct rtb200_ctx {
     // multi-GPU
     rtb::Comm* comm = nullptr;
     int rank = 0, n_ranks = 1;
+    const void* peer_cur = nullptr;   // rtb::PeerFrame of the frame being rendered (null: none)
+    bool peer_signalled = false;      // a kernel of this frame carries the completion signal itself
 
     // streamed path scratch (rt_stream.cu) and host-side test counts of the last frame
     void* stream_scratch = nullptr;
@@ -128,6 +131,20 @@ int  comm_unique_id(uint8_t* id);
 int  comm_init(rtb200_ctx* c, int rank, int n_ranks, const uint8_t* id);
 void comm_destroy(rtb200_ctx* c);
 int  comm_gather_frame(rtb200_ctx* c, int W, int H, int band_rows, bool want_f32, bool want_rgba8, double* ms);
-int  comm_peer_frame(rtb200_ctx* c, int W, int H, bool want_f32, void** rgba8, void** f32);   // collective; null = use the gather
-int  comm_peer_frame_done(rtb200_ctx* c, double* ms, bool wait = true, cudaStream_t on = nullptr);    // wait = false: only enqueue the signal
+// peer frame: what one frame's kernels on THIS rank need (see rt_comm.cu)
+struct PeerFrame {
+    void* rgba8 = nullptr;            // this frame's half of rank 0's double-buffered full frame (null: use the NCCL gather)
+    void* f32 = nullptr;              // same for the float frame (null unless asked for)
+    unsigned int* flag = nullptr;     // ranks > 0: this rank's completion word in rank 0's memory
+    unsigned int* done = nullptr;     // ranks > 0: local CTA counter for the in-kernel signal
+    unsigned int  seq = 0;            // frame sequence number (same on every rank)
+    const unsigned int* ack = nullptr;   // ranks > 0, wait_in_kernel: local word that must reach ack_min before the first store
+    unsigned int  ack_min = 0;
+};
+// ack_previous (rank 0): tell the peers that the frame before this one is consumed.  wait_in_kernel (ranks > 0): the
+// caller's first kernel waits for the acknowledgement itself (LevelParams::peer_ack) instead of the stream.
+int  comm_peer_begin(rtb200_ctx* c, int W, int H, bool want_f32, bool ack_previous, bool wait_in_kernel, PeerFrame* pf, cudaStream_t s);
+int  comm_peer_signal(rtb200_ctx* c, const PeerFrame& pf, cudaStream_t s);   // ranks > 0, when no kernel signalled by itself
+int  comm_peer_wait(rtb200_ctx* c, const PeerFrame& pf, cudaStream_t s);     // rank 0: s waits for every peer's word
+int  comm_peer_ack(rtb200_ctx* c, unsigned int seq, cudaStream_t s);         // rank 0: frames <= seq are consumed
 }

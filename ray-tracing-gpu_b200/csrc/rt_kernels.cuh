@@ -37,6 +37,14 @@ struct LevelParams {
     int     direct;
     float*  fb_f32;                // [local rows][W][3]
     uchar4* fb_rgba8;              // [local rows][W]
+    // several GPUs, peer frame (rt_comm.cu): the kernel that stored this rank's rows into rank 0's
+    // memory also tells rank 0 so -- the last CTA to finish writes peer_seq to peer_flag over NVLink
+    unsigned int* peer_flag;       // null = no signal from this launch
+    unsigned int* peer_done;       // local CTA counter (zero between launches)
+    unsigned int  peer_seq;
+    // ... and may first have to wait until rank 0 has let go of the frame half it is about to overwrite
+    const unsigned int* peer_ack;  // null = nothing to wait for (or the stream already waited)
+    unsigned int  peer_ack_min;
 };
 
 struct CombineParams {

@@ -187,6 +187,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
     const FrameParams& f = p.f;
     const int tiles_x = (f.LW + 15) >> 4;
     const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + 15) >> 4) : (p.in_count + RES_THREADS - 1) / RES_THREADS;
+    if (p.peer_ack) peer_frame_wait_ack(p.peer_ack, p.peer_ack_min);      // several GPUs: the frame half is free
     mbar_wait(&bar, 0);
     SceneView sv;
     sv.surf  = reinterpret_cast<const SurfRec*>(smem);
@@ -341,6 +342,9 @@ k_resident_level(const __grid_constant__ LevelParams p)
 
     // ---- statistics ---------------------------------------------------------------------------
     warp_stats(p.stats, n_shadow, n_refl_st, n_refr_st, n_tests, n_nan);
+
+    // ---- several GPUs: completion signal to rank 0, from the kernel that made the pixels ------
+    if (p.peer_flag) peer_frame_signal(p.peer_done, p.peer_flag, p.peer_seq);
 }
 
 // ---------------------------------------------------------------------------------------

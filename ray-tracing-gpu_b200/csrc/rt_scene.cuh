@@ -71,6 +71,7 @@ struct FrameParams {
     int   secondary;            // 0: never spawn
     // banding (multi-GPU): local lattice row -> global lattice row
     int   band_lrows;           // band height in lattice rows (band_rows * k)
+    int   band_lshift, band_pshift;   // log2 of the band height in lattice / pixel rows, -1 if not a power of two
     int   n_ranks, rank;
     int   fb_global;            // 1: the framebuffers are FULL frames (rank 0's, possibly peer-mapped over
                                 //    NVLink) and pixel rows are addressed globally; 0: compact local rows
@@ -102,14 +103,62 @@ __host__ __device__ inline int band_global_row(int band, int n_ranks, int rank, 
 // Global lattice row of local lattice row `ly` under interleaved banding.
 RT_DEV int global_lattice_row(const FrameParams& f, int ly)
 {
+    if (f.n_ranks <= 1) return ly;
+    if (f.band_lshift >= 0) {                              // same formula, shifts instead of a division per sample
+        const int b = ly >> f.band_lshift;
+        return (((b * f.n_ranks + f.rank) << f.band_lshift)) + (ly - (b << f.band_lshift));
+    }
     return band_global_row(f.band_lrows, f.n_ranks, f.rank, ly);
 }
 
 // Row of the framebuffer a LOCAL pixel row is stored at (see FrameParams::fb_global).
 RT_DEV int framebuffer_row(const FrameParams& f, int local_row)
 {
-    if (!f.fb_global) return local_row;
+    if (!f.fb_global || f.n_ranks <= 1) return local_row;
+    if (f.band_pshift >= 0) {
+        const int b = local_row >> f.band_pshift;
+        return (((b * f.n_ranks + f.rank) << f.band_pshift)) + (local_row - (b << f.band_pshift));
+    }
     return band_global_row(f.band_lrows / f.k, f.n_ranks, f.rank, local_row);
+}
+
+// Peer frame (rt_comm.cu): called by EVERY CTA of the grid after its last framebuffer store.  The
+// stores went into rank 0's memory over NVLink; each CTA makes them visible system-wide and counts
+// itself done, and the last one to do so writes the frame's sequence number into this rank's word
+// of rank 0's flag array (release at system scope): rank 0's stream waits on that word.
+__device__ __forceinline__ void peer_frame_signal(unsigned int* done, unsigned int* flag, unsigned int seq)
+{
+    __syncthreads();                                        // every thread of the CTA has issued its stores
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        __threadfence_system();
+        const unsigned int n = gridDim.x * gridDim.y * gridDim.z;
+        if (atomicAdd(done, 1u) == n - 1u) {
+            *done = 0u;                                     // ready for the next launch (stream order)
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(flag), "r"(seq) : "memory");
+        }
+    }
+}
+
+// Peer frame: thread 0 of a CTA waits until rank 0's acknowledgement word (LOCAL memory, written by
+// rank 0 over NVLink) has reached `want` (cyclic compare).  Normally true on the first load.  Gives
+// up after 2 s of GPU time: a torn frame on a broken peer beats a hung GPU.  Followed by a barrier.
+__device__ __forceinline__ void peer_frame_wait_ack(const unsigned int* ack, unsigned int want)
+{
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        unsigned long long t0 = 0;
+        for (;;) {
+            unsigned int v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(ack) : "memory");
+            if ((int)(v - want) >= 0) break;
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 2000000000ull) break;
+            __nanosleep(200);
+        }
+    }
+    __syncthreads();
 }
 
 // Primary ray through lattice sample (sx, sy): Scene.cpp:1543-1552.

@@ -9,8 +9,10 @@
 //     sample per pixel) are enqueued back to back: kernel i+1 starts when kernel i ends;
 //   * with a host destination the RGBA8 frames alternate between two device buffers and travel to
 //     the host on the copy stream while the next frame renders (PCIe and the SMs overlap);
-//   * several GPUs (peer frame, rt_comm.cu): every rank enqueues kernel + completion all-reduce per
-//     frame without waiting on the host, so the collective's latency hides under the next kernel;
+//   * several GPUs (peer frame, rt_comm.cu): every rank enqueues its kernels without waiting on the
+//     host; each kernel stores into rank 0's frame half and signals by itself, rank 0's COPY stream
+//     waits for the peers' words, copies the frame out and acknowledges, so neither the signalling nor
+//     the read-back is on any rank's kernel-to-kernel path (peers run at most two frames ahead);
 //   * per-frame counters live in per-frame slots and come back in one copy at the end.
 // Anything else (secondary rays, supersampling, streamed / LBVH paths, NCCL-gather fallback) is
 // rendered frame by frame through rtb200_render -- same results, no pipelining.
@@ -67,12 +69,15 @@ extern "C" int rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frame
     const int band = fp0.band_lrows / fp0.k;
     const int local_rows = local_row_count(fp0.H, band, ctx->n_ranks, ctx->rank);
     if ((size_t)std::max(local_rows, 1) * fp0.LW > (16u << 20)) fast = false;       // frames that need chunking
-    if (multi && out_rgba8) fast = false;                     // rank 0 would have to hold the peers back per frame
-    void *peer8 = nullptr, *peer32 = nullptr;
+    // NOTE every condition above depends on replicated state only (out_rgba8 may differ between ranks
+    // and must not enter the decision): all ranks pipeline, or none does.
+    PeerFrame pf;
     if (fast && multi) {
-        const int prc = comm_peer_frame(ctx, fp0.W, fp0.H, false, &peer8, &peer32);   // collective, same decision on every rank
+        // first frame of the path; rank 0 has consumed whatever it rendered before (ack).  Collective
+        // only when the mapping must be (re)established -- the same decision on every rank.
+        const int prc = comm_peer_begin(ctx, fp0.W, fp0.H, false, true, local_rows > 0, &pf, ctx->stream);
         if (prc != RTB200_OK) return prc;
-        if (!peer8) fast = false;
+        if (!pf.rgba8) fast = false;
     }
     if (!fast) {
         for (int i = 0; i < n_frames; ++i) {
@@ -90,7 +95,7 @@ extern "C" int rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frame
     if ((e = ctx->seq_stats.ensure(stat_bytes * (size_t)n_frames)) != cudaSuccess) return set_cuda_error(ctx, e, "sequence counters");
     if ((e = ctx->seq_host.ensure(stat_bytes * (size_t)n_frames)) != cudaSuccess) return set_cuda_error(ctx, e, "sequence counters (host)");
     uchar4* target[2] = {nullptr, nullptr};
-    if (multi) target[0] = target[1] = static_cast<uchar4*>(peer8);
+    if (multi) { /* the frame halves of rank 0, chosen per frame by comm_peer_begin */ }
     else if (out_rgba8) {
         for (int b = 0; b < 2; ++b) {
             if ((e = ctx->seq_fb[b].ensure(lpx * 4)) != cudaSuccess) return set_cuda_error(ctx, e, "sequence frame buffer");
@@ -109,7 +114,12 @@ extern "C" int rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frame
     cudaEvent_t copied[2] = {ctx->ev[2], ctx->ev[3]};
     QCU(cudaEventRecord(ctx->ev[0], ctx->stream));
     for (int i = 0; i < n_frames; ++i) {
-        const int b = i & 1;
+        if (multi && i > 0) {
+            const int prc = comm_peer_begin(ctx, fp0.W, fp0.H, false, false, local_rows > 0, &pf, ctx->stream);
+            if (prc != RTB200_OK || !pf.rgba8) return prc != RTB200_OK ? prc : seq_fail(ctx, RTB200_E_STATE, "peer frame lost inside a sequence");
+        }
+        const int b = multi ? (int)(pf.seq & 1u) : (i & 1);
+        const bool consumer = out_rgba8 && (!multi || ctx->rank == 0);
         FrameParams fp;
         fill_frame_params(&frames[i], ctx->n_ranks, ctx->rank, fp);
         fp.secondary = 0;
@@ -124,35 +134,39 @@ extern "C" int rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frame
         p.direct = 1;
         p.cull = (frames[i].flags & RTB200_F_EXACT_FP) ? 0 : 1;
         p.fb_f32 = nullptr;                                   // a sequence delivers RGBA8 only
-        p.fb_rgba8 = target[b];
-        if (out_rgba8 && i >= 2) QCU(cudaStreamWaitEvent(ctx->stream, copied[b], 0));   // buffer b is free again
-        if (local_rows > 0) QCU(launch_resident_level(p, exact, ctx->sm_count, ctx->stream));
-        if (multi) {
-            // completion signal of frame i on the side stream: the next kernel does not wait for it
-            // (a consumer on rank 0 would; nothing in a sequence without host destination does)
-            QCU(cudaEventRecord(done[b], ctx->stream));
-            QCU(cudaStreamWaitEvent(ctx->copy_stream, done[b], 0));
-            const int rc = comm_peer_frame_done(ctx, nullptr, false, ctx->copy_stream);
-            if (rc != RTB200_OK) return rc;
+        p.fb_rgba8 = multi ? static_cast<uchar4*>(pf.rgba8) : target[b];
+        if (multi && pf.flag && local_rows > 0) {             // wait for the half, store, signal: all in the one kernel
+            p.peer_flag = pf.flag; p.peer_done = pf.done; p.peer_seq = pf.seq;
+            p.peer_ack = pf.ack; p.peer_ack_min = pf.ack_min;
         }
-        if (out_rgba8) {
+        if (consumer && i >= 2) QCU(cudaStreamWaitEvent(ctx->stream, copied[b], 0));   // buffer b is free again
+        if (local_rows > 0) QCU(launch_resident_level(p, exact, ctx->sm_count, ctx->stream));
+        else if (multi && pf.flag) { const int rc = comm_peer_signal(ctx, pf, ctx->stream); if (rc != RTB200_OK) return rc; }
+        if (consumer || (multi && ctx->rank == 0)) {
+            // side stream: (several GPUs: wait for the peers' words,) copy the frame out, acknowledge
             QCU(cudaEventRecord(done[b], ctx->stream));
             QCU(cudaStreamWaitEvent(ctx->copy_stream, done[b], 0));
-            QCU(cudaMemcpyAsync(out_rgba8 + (size_t)i * frame_bytes, target[b], frame_bytes, cudaMemcpyDeviceToHost, ctx->copy_stream));
-            QCU(cudaEventRecord(copied[b], ctx->copy_stream));
+            if (multi) { const int rc = comm_peer_wait(ctx, pf, ctx->copy_stream); if (rc != RTB200_OK) return rc; }
+            if (consumer) {
+                QCU(cudaMemcpyAsync(out_rgba8 + (size_t)i * frame_bytes, p.fb_rgba8, frame_bytes, cudaMemcpyDeviceToHost, ctx->copy_stream));
+                QCU(cudaEventRecord(copied[b], ctx->copy_stream));
+            }
+            // acknowledge = "the peers may overwrite this half"; a last frame that stays on the device for
+            // rtb200_read_frame is acknowledged by rank 0's next render call instead
+            if (multi && (consumer || i + 1 < n_frames)) { const int rc = comm_peer_ack(ctx, pf.seq, ctx->copy_stream); if (rc != RTB200_OK) return rc; }
         }
     }
     QCU(cudaEventRecord(ctx->ev[1], ctx->stream));
     QCU(cudaMemcpyAsync(ctx->seq_host.p, ctx->seq_stats.p, stat_bytes * (size_t)n_frames, cudaMemcpyDeviceToHost, ctx->stream));
     QCU(cudaStreamSynchronize(ctx->stream));
-    if (out_rgba8 || multi) QCU(cudaStreamSynchronize(ctx->copy_stream));
+    QCU(cudaStreamSynchronize(ctx->copy_stream));
     float total = 0.f;
     QCU(cudaEventElapsedTime(&total, ctx->ev[0], ctx->ev[1]));
 
     // ---- statistics -----------------------------------------------------------------------------------------
     ctx->last_W = fp0.W; ctx->last_H = fp0.H; ctx->last_local_rows = local_rows;
     ctx->last_gathered = multi && ctx->rank == 0;
-    if (!multi && out_rgba8) ctx->last_W = 0;                 // the frames went to the host; nothing to read back later
+    if (out_rgba8) ctx->last_W = 0;                           // the frames went to the host; nothing to read back later
     if (stats) {
         const unsigned long long* h = ctx->seq_host.as<unsigned long long>();
         const double n_surf = std::max(1, ctx->ds.rl.n_surf);

@@ -56,13 +56,33 @@ for i in range(n):
 _, sts = r.render_sequence(frames)
 dist.barrier()
 if rank == 0:
-    _, got = r.read_frame(H, W, want_f32=False)
     solo.set_scene(ps)
-    _, want, _ = solo.render(frames[-1])
-    ok = bool(np.array_equal(got, want))
+    want_all = [solo.render(fr, want_f32=False)[1].copy() for fr in frames]
+    _, got = r.read_frame(H, W, want_f32=False)
+    ok = bool(np.array_equal(got, want_all[-1]))
     bad += not ok
-    print(json.dumps({"case": "scene1 sequence of 24 cameras (last frame)", "ranks": world, "rgba8_equal": ok,
+    print(json.dumps({"case": "scene1 sequence of 24 cameras, frame left on rank 0", "ranks": world, "rgba8_equal": ok,
                       "ms_per_frame": sts[0].ms_render}), flush=True)
+# the same path with a host destination on rank 0 (every frame must arrive, untorn), twice in a row
+for rep in range(2):
+    out = rt.pinned_empty((n, H, W, 4), np.uint8) if rank == 0 else None
+    _, sts = r.render_sequence(frames, out_rgba8=out)
+    if rank == 0:
+        eq = [bool(np.array_equal(out[i], want_all[i])) for i in range(n)]
+        bad += not all(eq)
+        print(json.dumps({"case": "scene1 sequence of 24 cameras -> host", "ranks": world, "frames_equal": sum(eq), "of": n,
+                          "ms_per_frame": sts[0].ms_render}), flush=True)
+# synchronous calls with a moving camera and NO barrier between frames: a peer that runs ahead must
+# not overwrite the frame rank 0 is still reading (double-buffered halves + ack)
+got_all = []
+for fr in frames:
+    _, u8, _ = r.render(fr, want_f32=False, want_rgba8=rank == 0)
+    if rank == 0:
+        got_all.append(u8.copy())
+if rank == 0:
+    eq = [bool(np.array_equal(got_all[i], want_all[i])) for i in range(n)]
+    bad += not all(eq)
+    print(json.dumps({"case": "scene1 24 synchronous frames, moving camera, no barrier", "ranks": world, "frames_equal": sum(eq), "of": n}), flush=True)
 flag = torch.tensor([bad], device="cuda"); dist.broadcast(flag, src=0)
 dist.destroy_process_group()
 sys.exit(1 if int(flag.item()) else 0)
