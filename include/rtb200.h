@@ -148,6 +148,9 @@ typedef struct rtb200_stats {
     double   ms_primary_kernel;    /* the level-0 nearest-hit (or fused resident) kernel of the first chunk */
     uint64_t shadow_tests_triangle;/* part of tests_triangle entered by shadow-filter queries              */
     uint64_t shadow_bvh_nodes;     /* part of bvh_nodes_visited entered by shadow-filter queries           */
+    uint64_t level_loop_redone;    /* 1: the frame's levels were first enqueued without host round trips,   */
+                                   /* a guessed queue capacity proved too small and the frame was redone    */
+                                   /* with exact capacities (same pixels, slower)                           */
 } rtb200_stats;
 
 typedef struct rtb200_ctx rtb200_ctx;

@@ -117,7 +117,7 @@ void rtb200_destroy(rtb200_ctx* ctx)
     ctx->scene_buf.release(); ctx->stage.release();
     ctx->c0.release(); ctx->fb_f32.release(); ctx->fb_rgba8.release(); ctx->stats.release(); ctx->counters.release();
     ctx->full_f32.release(); ctx->full_rgba8.release(); ctx->h_small.release();
-    ctx->seq_fb[0].release(); ctx->seq_fb[1].release(); ctx->seq_stats.release(); ctx->seq_host.release();
+    ctx->seq_fb[0].release(); ctx->seq_fb[1].release(); ctx->seq_stats.release(); ctx->seq_host.release(); ctx->h_levels.release();
     for (auto& l : ctx->levels) { l.od0.release(); l.od1.release(); l.colour.release(); l.links.release(); }
     ctx->q_in0.release(); ctx->q_in1.release(); ctx->q_out0.release(); ctx->q_out1.release(); ctx->q_out2.release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -230,6 +230,7 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
         return fail(ctx, RTB200_E_ARG, "null array with non-zero count");
     CU(cudaSetDevice(ctx->device));
     bvh_invalidate(ctx);                         // an LBVH belongs to the scene it was built from
+    ++ctx->scene_serial;
 
     const int Tpad = ((T + TILE_TRIS - 1) / TILE_TRIS) * TILE_TRIS;
     ResidentLayout rl;
@@ -417,6 +418,155 @@ int chunk_copy_out(rtb200_ctx* ctx, int W, int py0, int prows)
 }
 }
 
+// scene-resident path with secondary rays, WITHOUT a host round trip per level.  The synchronous loop
+// below reads the child count back after every level kernel to size the next launch: on the reference's
+// own mirror / glass scenes (scene7-9: 20 bounces allowed, a few hundred rays left after the 8th) that is
+// 21 round trips of ~30 us around ~0.1 ms of work.  Here every level kernel reads its input count from
+// the counter the previous one wrote (LevelParams::in_count_dev), queues are sized by a guess -- what
+// the last frame of this shape needed plus half, or a halving sequence for a first frame -- and a kernel
+// that runs out of room raises a flag.  Levels, folds and the resolve of a chunk are enqueued in one go;
+// the host waits once per frame, and redoes the frame through the synchronous loop if the flag is up
+// (*overflowed).  Same kernels, same arithmetic, same frame.
+static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
+                                 bool exact, int children, int rows_per_chunk, rtb200_stats* st, uint32_t* launches,
+                                 bool* overflowed)
+{
+    const int k = fp.k, local_LH = local_rows * k, max_b = fr->max_bounces;
+    *overflowed = false;
+    rtb200_ctx::LevelGuess& g = ctx->level_guess;
+    const bool known = g.valid && g.scene_serial == ctx->scene_serial && g.W == fp.W && g.H == fp.H && g.k == k &&
+                       g.max_bounces == max_b && g.children == children && g.rows_per_chunk == rows_per_chunk &&
+                       g.local_rows == local_rows;
+    int last = max_b;                                       // deepest level that gets a kernel
+    if (known) {
+        int used = 0;
+        for (size_t l = 1; l < g.rays.size(); ++l) if (g.rays[l]) used = (int)l;
+        last = std::min(max_b, used + 1);
+    }
+    // queue capacities per level (entries)
+    const size_t chunk_samples = (size_t)std::min(rows_per_chunk, local_LH) * fp.LW;
+    std::vector<size_t> cap((size_t)last + 2, 0);
+    cap[0] = chunk_samples;
+    for (int l = 1; l <= last; ++l) {
+        const size_t worst = cap[(size_t)l - 1] * (size_t)children;
+        size_t want;
+        if (known && (size_t)l < g.rays.size()) want = (size_t)g.rays[(size_t)l] + g.rays[(size_t)l] / 2 + 8192;
+        else want = (l == 1) ? worst : std::max<size_t>(cap[(size_t)l - 1] / 2, 65536);
+        cap[(size_t)l] = std::max<size_t>(std::min(worst, want), 256);
+    }
+    cap[(size_t)last + 1] = 256;                            // a level that may not spawn still needs valid pointers
+
+    cudaError_t e;
+    if ((e = ctx->c0.ensure(sizeof(float) * 3 * (size_t)rows_per_chunk * fp.LW)) != cudaSuccess) return set_cuda_error(ctx, e, "c0");
+    const size_t n_counters = 2 * ((size_t)max_b + 2) + 1, ovf = n_counters - 1;
+    const int n_chunks = (local_LH + rows_per_chunk - 1) / rows_per_chunk;
+    if ((e = ctx->counters.ensure(sizeof(unsigned) * n_counters)) != cudaSuccess) return set_cuda_error(ctx, e, "counters");
+    if ((e = ctx->h_levels.ensure(sizeof(unsigned) * n_counters * (size_t)n_chunks)) != cudaSuccess) return set_cuda_error(ctx, e, "level counters (host)");
+    unsigned* d_cnt = ctx->counters.as<unsigned>();
+    unsigned* h_all = ctx->h_levels.as<unsigned>();
+    if ((int)ctx->levels.size() < last + 2) ctx->levels.resize((size_t)last + 2);
+    for (int l = 0; l <= last; ++l) {
+        LevelBuf& cur = ctx->levels[(size_t)l];
+        LevelBuf& nxt = ctx->levels[(size_t)l + 1];
+        if (l >= max_b) break;                              // the deepest allowed level never spawns
+        if ((e = nxt.od0.ensure(sizeof(float4) * cap[(size_t)l + 1])) != cudaSuccess) return set_cuda_error(ctx, e, "queue");
+        if ((e = nxt.od1.ensure(sizeof(float4) * cap[(size_t)l + 1])) != cudaSuccess) return set_cuda_error(ctx, e, "queue");
+        if ((e = nxt.colour.ensure(sizeof(float4) * cap[(size_t)l + 1])) != cudaSuccess) return set_cuda_error(ctx, e, "queue");
+        if ((e = cur.links.ensure(sizeof(int4) * cap[(size_t)l])) != cudaSuccess) return set_cuda_error(ctx, e, "links");
+    }
+
+    int chunk = 0;
+    for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunk) {
+        const int rows = std::min(rows_per_chunk, local_LH - ly0);
+        CU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, ctx->stream));
+        for (int level = 0; level <= last; ++level) {
+            const bool spawn = level < max_b;
+            LevelBuf& cur = ctx->levels[(size_t)level];
+            LevelBuf& nxt = ctx->levels[(size_t)level + 1];
+            LevelParams p;
+            memset(&p, 0, sizeof p);
+            p.f = fp;
+            if (!spawn) p.f.secondary = 0;
+            p.blob = ctx->ds.blob; p.rl = ctx->ds.rl;
+            p.level = level;
+            p.chunk_ly0 = ly0; p.chunk_rows = rows; p.local_LH = local_LH;
+            p.c0 = ctx->c0.as<float>();
+            p.in_od0 = cur.od0.as<float4>(); p.in_od1 = cur.od1.as<float4>(); p.in_colour = cur.colour.as<float4>();
+            if (level == 0) p.in_count = rows * fp.LW;
+            else { p.in_count_dev = d_cnt + 2 * (level - 1); p.in_cap = (int)cap[(size_t)level]; p.in_count = p.in_cap; }
+            p.out_od0 = nxt.od0.as<float4>(); p.out_od1 = nxt.od1.as<float4>();
+            p.out_count = d_cnt + 2 * level; p.link_count = d_cnt + 2 * level + 1;
+            p.links = cur.links.as<int4>();
+            if (spawn) {                                    // the last launched level may only REPORT that it wanted children
+                p.out_guarded = 1;
+                p.out_cap = (level == last) ? 0u : (unsigned)cap[(size_t)level + 1];
+                p.overflow = d_cnt + ovf;
+            }
+            p.stats = ctx->stats.as<unsigned long long>();
+            p.cull = (fr->flags & RTB200_F_EXACT_FP) ? 0 : 1;
+            p.fb_f32 = ctx->out_f32_dev; p.fb_rgba8 = ctx->out_rgba8_dev;
+            const bool timed = (level == 0 && ly0 == 0);
+            if (timed) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
+            CU(launch_resident_level(p, exact, ctx->sm_count, ctx->stream));
+            if (timed) CU(cudaEventRecord(ctx->ev[3], ctx->stream));
+            ++*launches;
+        }
+        for (int l = std::min(last, max_b - 1); l >= 0; --l) {          // bottom-up fold of the levels that spawned
+            if (l == last) continue;                                     // (a probe level has no children to fold)
+            CombineParams c;
+            memset(&c, 0, sizeof c);
+            c.links = ctx->levels[(size_t)l].links.as<int4>();
+            c.n_links = (l == 0) ? rows * fp.LW : (int)cap[(size_t)l];
+            c.n_links_dev = d_cnt + 2 * l + 1;
+            c.parent_is_level0 = (l == 0);
+            c.parent_c0 = ctx->c0.as<float>();
+            c.parent_colour = ctx->levels[(size_t)l].colour.as<float4>();
+            c.child_colour = ctx->levels[(size_t)l + 1].colour.as<float4>();
+            c.mat = ctx->ds.mat;
+            CU(launch_combine(c, exact, ctx->stream));
+            ++*launches;
+        }
+        ResolveParams r;
+        memset(&r, 0, sizeof r);
+        r.f = fp;
+        r.c0 = ctx->c0.as<float>();
+        r.chunk_py0 = ly0 / k;
+        r.chunk_prows = std::min(rows / k, local_rows - r.chunk_py0);
+        r.fb_f32 = ctx->out_f32_dev;
+        r.fb_rgba8 = ctx->out_rgba8_dev;
+        r.stats = ctx->stats.as<unsigned long long>();
+        CU(launch_resolve(r, ctx->stream));
+        ++*launches;
+        CU(cudaMemcpyAsync(h_all + (size_t)chunk * n_counters, d_cnt, sizeof(unsigned) * n_counters, cudaMemcpyDeviceToHost, ctx->stream));
+        const int rc2 = chunk_copy_out(ctx, fp.W, r.chunk_py0, r.chunk_prows);
+        if (rc2 != RTB200_OK) return rc2;
+    }
+    CU(cudaStreamSynchronize(ctx->stream));                 // the one wait of the frame
+
+    std::vector<unsigned> seen((size_t)max_b + 2, 0);
+    unsigned depth = 1;
+    for (int c = 0; c < n_chunks; ++c) {
+        const unsigned* h = h_all + (size_t)c * n_counters;
+        if (h[ovf]) *overflowed = true;
+        for (int l = 1; l <= last; ++l) {
+            const unsigned n = h[2 * (l - 1)];
+            if (n > cap[(size_t)l]) *overflowed = true;      // (cannot happen without the flag; belt and braces)
+            seen[(size_t)l] = std::max(seen[(size_t)l], n);
+            if (n) depth = std::max(depth, (unsigned)l + 1);
+        }
+    }
+    if (*overflowed) { g.valid = false; return RTB200_OK; }
+    g.valid = true; g.scene_serial = ctx->scene_serial;
+    g.W = fp.W; g.H = fp.H; g.k = k; g.max_bounces = max_b; g.children = children;
+    g.rows_per_chunk = rows_per_chunk; g.local_rows = local_rows;
+    g.rays = seen;
+    st->depth_levels = depth;
+    st->chunks = (uint32_t)n_chunks;
+    st->path = 0;
+    st->ms_primary_kernel = -1.0;
+    return RTB200_OK;
+}
+
 // scene-resident path: one fused kernel per level, host reads the child count between levels
 static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
                            bool exact, rtb200_stats* st, uint32_t* launches)
@@ -437,6 +587,19 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
         if (want * k < rows_per_chunk) rows_per_chunk = want * k;
     }
 
+    if (children > 0 && !getenv("RTB200_SYNC_LEVELS")) {
+        // secondary rays: all levels of a chunk enqueued at once, one wait per frame
+        bool overflowed = false;
+        const int arc = render_resident_async(ctx, fr, fp, local_rows, exact, children, rows_per_chunk, st, launches, &overflowed);
+        if (arc != RTB200_OK || !overflowed) return arc;
+        // a queue guess was too small: forget the attempt (counters, launches, copies) and take the exact route
+        CU(cudaMemsetAsync(ctx->stats.p, 0, sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT, ctx->stream));
+        *launches = 0;
+        if (ctx->copy_chunks) { CU(cudaStreamSynchronize(ctx->copy_stream)); ctx->copy_chunks = 0; }
+        ++ctx->level_fallbacks;
+        st->level_loop_redone = 1;
+    }
+
     cudaError_t e;
     if ((e = ctx->c0.ensure(sizeof(float) * 3 * (size_t)rows_per_chunk * fp.LW)) != cudaSuccess) return set_cuda_error(ctx, e, "c0");
     const size_t n_counters = 2 * ((size_t)std::max(fr->max_bounces, 0) + 2);
@@ -445,6 +608,7 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
     unsigned* h_cnt = ctx->h_small.as<unsigned>();
     unsigned* d_cnt = ctx->counters.as<unsigned>();
     unsigned max_level_seen = 0, chunks = 0;
+    std::vector<unsigned> seen_rays(1, 0);
 
     for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunks) {
         const int rows = std::min(rows_per_chunk, local_LH - ly0);
@@ -503,6 +667,10 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
             n_rays.push_back((int)h_cnt[0]);
             n_links.push_back((int)h_cnt[1]);
         }
+        for (size_t l = 1; l < n_rays.size(); ++l) {           // what this chunk needed: the next frame's guess
+            if (seen_rays.size() <= l) seen_rays.resize(l + 1, 0);
+            seen_rays[l] = std::max(seen_rays[l], (unsigned)n_rays[l]);
+        }
         const int levels_used = (int)n_links.size();          // levels that ran a kernel
         max_level_seen = std::max<unsigned>(max_level_seen, (unsigned)levels_used);
         for (int l = levels_used - 1; l >= 0; --l) {
@@ -537,6 +705,13 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
             const int rc2 = chunk_copy_out(ctx, fp.W, py0, std::min(rows / k, local_rows - py0));
             if (rc2 != RTB200_OK) return rc2;
         }
+    }
+    if (children > 0) {
+        rtb200_ctx::LevelGuess& g = ctx->level_guess;
+        g.valid = true; g.scene_serial = ctx->scene_serial;
+        g.W = fp.W; g.H = fp.H; g.k = k; g.max_bounces = fr->max_bounces; g.children = children;
+        g.rows_per_chunk = rows_per_chunk; g.local_rows = local_rows;
+        g.rays = seen_rays;
     }
     st->depth_levels = max_level_seen;
     st->chunks = chunks;

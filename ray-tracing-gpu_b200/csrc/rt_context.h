@@ -93,6 +93,17 @@ struct rtb200_ctx {
     float*   host_f32 = nullptr;      // non-null during a render that overlaps its read-back
     uint8_t* host_rgba8 = nullptr;
     int      copy_chunks = 0;         // chunks already handed to the copy stream in this frame
+    // level loop without host round trips (resident path with secondary rays): what the last frame
+    // of this shape needed per level, the guess the next one is sized by
+    struct LevelGuess {
+        bool valid = false;
+        unsigned long long scene_serial = 0;
+        int W = 0, H = 0, k = 0, max_bounces = 0, children = 0, rows_per_chunk = 0, local_rows = 0;
+        std::vector<unsigned> rays;   // [l] = most rays any chunk had at level l (l >= 1)
+    } level_guess;
+    unsigned long long scene_serial = 0;   // bumped by rtb200_set_scene
+    unsigned long long level_fallbacks = 0;   // frames redone through the synchronous level loop (a queue guess was too small)
+    rtb::PinnedBuf h_levels;               // per-chunk copies of the level counters
     rtb::DevBuf seq_fb[2], seq_stats;  // rtb200_render_sequence: double-buffered RGBA8 frames, per-frame counters
     rtb::PinnedBuf seq_host;
     int last_W = 0, last_H = 0, last_local_rows = 0;

@@ -37,6 +37,14 @@ struct LevelParams {
     int     direct;
     float*  fb_f32;                // [local rows][W][3]
     uchar4* fb_rgba8;              // [local rows][W]
+    // level loop without host round trips (rt_api.cu, render_resident_async): the number of input rays is
+    // read from the counter the previous level wrote, and appends are bounded by the capacity the host
+    // guessed -- a kernel that runs out of room raises *overflow and the host redoes the frame the slow way
+    const unsigned int* in_count_dev;   // null: in_count is exact
+    int   in_cap;                       // entries the input queue can hold
+    int   out_guarded;                  // 1: appends are checked against out_cap
+    unsigned int out_cap;
+    unsigned int* overflow;
     // several GPUs, peer frame (rt_comm.cu): the kernel that stored this rank's rows into rank 0's
     // memory also tells rank 0 so -- the last CTA to finish writes peer_seq to peer_flag over NVLink
     unsigned int* peer_flag;       // null = no signal from this launch
@@ -55,6 +63,7 @@ struct CombineParams {
     const float4* child_colour;
     const MatRec* mat;
     int   parent_is_level0;
+    const unsigned int* n_links_dev;    // non-null: the link count lives on the device (n_links = capacity)
 };
 
 struct ResolveParams {

@@ -177,6 +177,12 @@ k_resident_level(const __grid_constant__ LevelParams p)
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ __align__(8) uint64_t bar;
 
+    int in_count = p.in_count;
+    if (!PRIMARY && p.in_count_dev) {       // written by the level before this one, no host in between
+        const unsigned int n = *p.in_count_dev;
+        in_count = (int)(n < (unsigned int)p.in_cap ? n : (unsigned int)p.in_cap);
+        if ((int)blockIdx.x * RES_THREADS >= in_count) return;             // whole CTA, before any barrier
+    }
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
     __syncthreads();
@@ -186,7 +192,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
     }
     const FrameParams& f = p.f;
     const int tiles_x = (f.LW + 15) >> 4;
-    const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + 15) >> 4) : (p.in_count + RES_THREADS - 1) / RES_THREADS;
+    const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + 15) >> 4) : (in_count + RES_THREADS - 1) / RES_THREADS;
     if (p.peer_ack) peer_frame_wait_ack(p.peer_ack, p.peer_ack_min);      // several GPUs: the frame half is free
     mbar_wait(&bar, 0);
     SceneView sv;
@@ -214,7 +220,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
         primary_ray<E>(f, valid ? lx : 0, valid ? global_lattice_row(f, ly) : 0, o, d);
     } else {
         self = blk * RES_THREADS + tid;
-        valid = self < p.in_count;
+        valid = self < in_count;
         const float4 a = valid ? p.in_od0[self] : make_float4(0.f, 0.f, 0.f, 0.f);
         const float4 b = valid ? p.in_od1[self] : make_float4(0.f, 0.f, 0.f, 0.f);
         o = f4_xyz(a); d = f4_xyz(b); energy = a.w; ior = b.w;
@@ -318,14 +324,18 @@ k_resident_level(const __grid_constant__ LevelParams p)
         lbase = __shfl_sync(0xffffffffu, lbase, 0);
         const unsigned int below = (1u << lane) - 1u;
         int s_refl = -1, s_refr = -1;
-        if (want_refl) {
+        // guessed capacity exhausted: nothing is written, the link carries no children (so that the
+        // fold stays in bounds) and the host is told to redo the frame with exact capacities
+        const bool room = !p.out_guarded || base + n_refl + n_refr <= p.out_cap;
+        if (!room && lane == 0) *p.overflow = 1u;
+        if (room && want_refl) {
             s_refl = (int)(base + __popc(m_refl & below));
             const V3 rd = reflect3<E>(d, N);
             p.out_od0[s_refl] = make_float4(P.x, P.y, P.z, e_refl);
             p.out_od1[s_refl] = make_float4(rd.x, rd.y, rd.z, 0.0f);          // CRayon default ior, Rayon.cpp:16
             ++n_refl_st;
         }
-        if (want_refr) {
+        if (room && want_refr) {
             s_refr = (int)(base + n_refl + __popc(m_refr & below));
             V3 n2 = N; float ratio, nior;
             if (ior == mior) { nior = f.scene_ior; ratio = FP<E>::div(mior, f.scene_ior); n2 = neg3(N); }
@@ -354,8 +364,9 @@ k_resident_level(const __grid_constant__ LevelParams p)
 template <bool E>
 __global__ void __launch_bounds__(256) k_combine(const CombineParams p)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= p.n_links) return;
+    int n_links = p.n_links;
+    if (p.n_links_dev) { const unsigned int n = *p.n_links_dev; n_links = (int)(n < (unsigned int)p.n_links ? n : (unsigned int)p.n_links); }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_links; i += gridDim.x * blockDim.x) {
     const int4 lk = p.links[i];
     const float kr = p.mat[lk.w].m1.w, kt = p.mat[lk.w].m2.x;
     float r, g, b;
@@ -371,6 +382,7 @@ __global__ void __launch_bounds__(256) k_combine(const CombineParams p)
     }
     if (p.parent_is_level0) { float* c = p.parent_c0 + 3 * (size_t)lk.x; c[0] = r; c[1] = g; c[2] = b; }
     else p.parent_colour[lk.x] = make_float4(r, g, b, 0.f);
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -477,7 +489,8 @@ cudaError_t launch_resident_level(const LevelParams& p, bool exact, int sm_count
         if (exact) k_resident_level<true, true><<<grid, RES_THREADS, smem, st>>>(p);
         else       k_resident_level<false, true><<<grid, RES_THREADS, smem, st>>>(p);
     } else {
-        const dim3 grid((unsigned)std::min((p.in_count + RES_THREADS - 1) / RES_THREADS, max_ctas));
+        const int n_max = p.in_count_dev ? p.in_cap : p.in_count;
+        const dim3 grid((unsigned)std::min((n_max + RES_THREADS - 1) / RES_THREADS, max_ctas));
         if (exact) k_resident_level<true, false><<<grid, RES_THREADS, smem, st>>>(p);
         else       k_resident_level<false, false><<<grid, RES_THREADS, smem, st>>>(p);
     }
@@ -486,7 +499,9 @@ cudaError_t launch_resident_level(const LevelParams& p, bool exact, int sm_count
 
 cudaError_t launch_combine(const CombineParams& p, bool exact, cudaStream_t st)
 {
-    const dim3 grid((unsigned)((p.n_links + 255) / 256));
+    // device-side count: the grid covers the capacity up to 8 blocks per SM, threads stride beyond
+    const unsigned want = (unsigned)((p.n_links + 255) / 256);
+    const dim3 grid(p.n_links_dev ? std::min(want, 1184u) : want);
     if (exact) k_combine<true><<<grid, 256, 0, st>>>(p);
     else       k_combine<false><<<grid, 256, 0, st>>>(p);
     return cudaGetLastError();
