@@ -475,6 +475,9 @@ static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const 
         if ((e = cur.links.ensure(sizeof(int4) * cap[(size_t)l])) != cudaSuccess) return set_cuda_error(ctx, e, "links");
     }
 
+    // levels, folds and the resolve of a chunk form one chain of dependent launches: each kernel lets the
+    // next one start its prologue early and waits for its predecessor itself (RTB200_NO_PDL=1: plain launches)
+    const bool pdl = getenv("RTB200_NO_PDL") == nullptr;
     int chunk = 0;
     for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunk) {
         const int rows = std::min(rows_per_chunk, local_LH - ly0);
@@ -505,6 +508,7 @@ static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const 
             p.stats = ctx->stats.as<unsigned long long>();
             p.cull = (fr->flags & RTB200_F_EXACT_FP) ? 0 : 1;
             p.fb_f32 = ctx->out_f32_dev; p.fb_rgba8 = ctx->out_rgba8_dev;
+            p.pdl = pdl ? (level == 0 ? 1 : 2) : 0;            // the chain starts at the level-0 kernel
             const bool timed = (level == 0 && ly0 == 0);
             if (timed) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
             CU(launch_resident_level(p, exact, ctx->sm_count, ctx->stream));
@@ -523,6 +527,7 @@ static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const 
             c.parent_colour = ctx->levels[(size_t)l].colour.as<float4>();
             c.child_colour = ctx->levels[(size_t)l + 1].colour.as<float4>();
             c.mat = ctx->ds.mat;
+            c.pdl = pdl ? 2 : 0;
             CU(launch_combine(c, exact, ctx->stream));
             ++*launches;
         }
@@ -535,6 +540,7 @@ static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const 
         r.fb_f32 = ctx->out_f32_dev;
         r.fb_rgba8 = ctx->out_rgba8_dev;
         r.stats = ctx->stats.as<unsigned long long>();
+        r.pdl = pdl ? 2 : 0;
         CU(launch_resolve(r, ctx->stream));
         ++*launches;
         CU(cudaMemcpyAsync(h_all + (size_t)chunk * n_counters, d_cnt, sizeof(unsigned) * n_counters, cudaMemcpyDeviceToHost, ctx->stream));

@@ -45,6 +45,11 @@ struct LevelParams {
     int   out_guarded;                  // 1: appends are checked against out_cap
     unsigned int out_cap;
     unsigned int* overflow;
+    // programmatic dependent launch: 1 = this kernel is part of a chain enqueued in one go; it lets its
+    // successor start early (the successor's prologue overlaps this kernel's tail) and waits for its
+    // predecessor before touching anything the predecessor wrote.  2 = same, and the launch itself carries
+    // the attribute (every kernel of the chain but the first).
+    int   pdl;
     // several GPUs, peer frame (rt_comm.cu): the kernel that stored this rank's rows into rank 0's
     // memory also tells rank 0 so -- the last CTA to finish writes peer_seq to peer_flag over NVLink
     unsigned int* peer_flag;       // null = no signal from this launch
@@ -64,6 +69,7 @@ struct CombineParams {
     const MatRec* mat;
     int   parent_is_level0;
     const unsigned int* n_links_dev;    // non-null: the link count lives on the device (n_links = capacity)
+    int   pdl;                          // see LevelParams::pdl
 };
 
 struct ResolveParams {
@@ -73,6 +79,7 @@ struct ResolveParams {
     float*  fb_f32;                // [local rows][W][3] or null
     uchar4* fb_rgba8;              // [local rows][W]    or null
     unsigned long long* stats;
+    int   pdl;                     // see LevelParams::pdl
 };
 
 // launchers (rt_resident.cu)

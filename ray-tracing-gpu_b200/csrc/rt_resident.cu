@@ -9,6 +9,7 @@
 // the reference's accumulation order and deterministically.  No per-thread stack, no
 // recursion; every level runs on a compacted queue so warps never diverge on depth.
 #include <algorithm>
+#include <cstring>
 
 #include "rt_kernels.cuh"
 #include "rt_cull.cuh"
@@ -170,6 +171,10 @@ RT_DEV uchar4 quantise_rgba8(float r, float g, float b, unsigned int& nans)
 // supersampled (p.direct), the level-0 kernel also resolves: it writes the float RGB and the
 // RGBA8 framebuffers itself and the frame is ONE kernel.
 // ---------------------------------------------------------------------------------------
+// programmatic dependent launch (sm_90+): see LevelParams::pdl
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 template <bool E, bool PRIMARY>
 __global__ void __launch_bounds__(RES_THREADS, RES_MIN_CTAS)
 k_resident_level(const __grid_constant__ LevelParams p)
@@ -177,18 +182,23 @@ k_resident_level(const __grid_constant__ LevelParams p)
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ __align__(8) uint64_t bar;
 
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (p.pdl) pdl_launch_dependents();     // the next kernel of the chain may start its prologue now
+    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    __syncthreads();
+    if (tid == 0) {                         // one bulk copy stages the whole scene (never written by a kernel)
+        mbar_arrive_expect_tx(&bar, (uint32_t)p.rl.bytes);
+        tma_load_1d(smem, p.blob, (uint32_t)p.rl.bytes, &bar);
+    }
+    if (p.pdl) pdl_wait();                  // everything below may read what the previous kernel wrote
     int in_count = p.in_count;
     if (!PRIMARY && p.in_count_dev) {       // written by the level before this one, no host in between
         const unsigned int n = *p.in_count_dev;
         in_count = (int)(n < (unsigned int)p.in_cap ? n : (unsigned int)p.in_cap);
-        if ((int)blockIdx.x * RES_THREADS >= in_count) return;             // whole CTA, before any barrier
-    }
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
-    __syncthreads();
-    if (tid == 0) {                         // one bulk copy stages the whole scene
-        mbar_arrive_expect_tx(&bar, (uint32_t)p.rl.bytes);
-        tma_load_1d(smem, p.blob, (uint32_t)p.rl.bytes, &bar);
+        if ((int)blockIdx.x * RES_THREADS >= in_count) {                   // whole CTA: nothing to do
+            if (tid == 0) mbar_wait(&bar, 0);                              // (not before the bulk copy has landed)
+            return;
+        }
     }
     const FrameParams& f = p.f;
     const int tiles_x = (f.LW + 15) >> 4;
@@ -364,6 +374,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
 template <bool E>
 __global__ void __launch_bounds__(256) k_combine(const CombineParams p)
 {
+    if (p.pdl) { pdl_launch_dependents(); pdl_wait(); }
     int n_links = p.n_links;
     if (p.n_links_dev) { const unsigned int n = *p.n_links_dev; n_links = (int)(n < (unsigned int)p.n_links ? n : (unsigned int)p.n_links); }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_links; i += gridDim.x * blockDim.x) {
@@ -391,6 +402,7 @@ __global__ void __launch_bounds__(256) k_combine(const CombineParams p)
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_resolve(const ResolveParams p)
 {
+    if (p.pdl) { pdl_launch_dependents(); pdl_wait(); }
     const int x = blockIdx.x * 32 + (threadIdx.x & 31);
     const int yr = blockIdx.y * 8 + (threadIdx.x >> 5);          // pixel row inside the chunk
     unsigned int nans = 0;
@@ -474,6 +486,19 @@ cudaError_t resident_prepare(size_t max_smem_bytes)
 
 static int g_resident_ctas_per_sm = 0;          // occupancy of the level kernel (queried once)
 
+// plain launch, or (pdl) one that may start before the kernel ahead of it in the stream has finished
+template <class P>
+static cudaError_t launch_chain(void (*kernel)(P), dim3 grid, unsigned block, size_t smem, cudaStream_t st, bool pdl, const P& p)
+{
+    cudaLaunchConfig_t cfg = cudaLaunchConfig_t();
+    cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
 cudaError_t launch_resident_level(const LevelParams& p, bool exact, int sm_count, cudaStream_t st)
 {
     const size_t smem = resident_smem_bytes(p.rl);
@@ -483,18 +508,15 @@ cudaError_t launch_resident_level(const LevelParams& p, bool exact, int sm_count
         g_resident_ctas_per_sm = n;
     }
     const int max_ctas = g_resident_ctas_per_sm * sm_count;
+    const bool pdl = p.pdl == 2;
     if (p.level == 0) {
         const int tiles_x = (p.f.LW + 15) / 16, tiles_y = (p.chunk_rows + 15) / 16;
         const dim3 grid((unsigned)std::min(tiles_x * tiles_y, max_ctas));
-        if (exact) k_resident_level<true, true><<<grid, RES_THREADS, smem, st>>>(p);
-        else       k_resident_level<false, true><<<grid, RES_THREADS, smem, st>>>(p);
-    } else {
-        const int n_max = p.in_count_dev ? p.in_cap : p.in_count;
-        const dim3 grid((unsigned)std::min((n_max + RES_THREADS - 1) / RES_THREADS, max_ctas));
-        if (exact) k_resident_level<true, false><<<grid, RES_THREADS, smem, st>>>(p);
-        else       k_resident_level<false, false><<<grid, RES_THREADS, smem, st>>>(p);
+        return launch_chain(exact ? k_resident_level<true, true> : k_resident_level<false, true>, grid, RES_THREADS, smem, st, pdl, p);
     }
-    return cudaGetLastError();
+    const int n_max = p.in_count_dev ? p.in_cap : p.in_count;
+    const dim3 grid((unsigned)std::min((n_max + RES_THREADS - 1) / RES_THREADS, max_ctas));
+    return launch_chain(exact ? k_resident_level<true, false> : k_resident_level<false, false>, grid, RES_THREADS, smem, st, pdl, p);
 }
 
 cudaError_t launch_combine(const CombineParams& p, bool exact, cudaStream_t st)
@@ -502,16 +524,13 @@ cudaError_t launch_combine(const CombineParams& p, bool exact, cudaStream_t st)
     // device-side count: the grid covers the capacity up to 8 blocks per SM, threads stride beyond
     const unsigned want = (unsigned)((p.n_links + 255) / 256);
     const dim3 grid(p.n_links_dev ? std::min(want, 1184u) : want);
-    if (exact) k_combine<true><<<grid, 256, 0, st>>>(p);
-    else       k_combine<false><<<grid, 256, 0, st>>>(p);
-    return cudaGetLastError();
+    return launch_chain(exact ? k_combine<true> : k_combine<false>, grid, 256, 0, st, p.pdl == 2, p);
 }
 
 cudaError_t launch_resolve(const ResolveParams& p, cudaStream_t st)
 {
     const dim3 grid((unsigned)((p.f.W + 31) / 32), (unsigned)((p.chunk_prows + 7) / 8));
-    k_resolve<<<grid, 256, 0, st>>>(p);
-    return cudaGetLastError();
+    return launch_chain(k_resolve, grid, 256, 0, st, p.pdl == 2, p);
 }
 
 cudaError_t launch_query_nearest(const DeviceScene& s, int n, const float* o3, const float* d3,
