@@ -4,8 +4,11 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
+#include <thread>
+#include <vector>
 
 #include "rt_context.h"
 
@@ -114,7 +117,7 @@ void rtb200_destroy(rtb200_ctx* ctx)
     comm_destroy(ctx);
     stream_release(ctx);
     bvh_release(ctx);
-    ctx->scene_buf.release(); ctx->stage.release();
+    ctx->scene_buf.release(); ctx->stage.release(); ctx->raw_buf.release();
     ctx->c0.release(); ctx->fb_f32.release(); ctx->fb_rgba8.release(); ctx->stats.release(); ctx->counters.release();
     ctx->full_f32.release(); ctx->full_rgba8.release(); ctx->h_small.release();
     ctx->seq_fb[0].release(); ctx->seq_fb[1].release(); ctx->seq_stats.release(); ctx->seq_host.release(); ctx->h_levels.release();
@@ -216,6 +219,40 @@ static float4 quadric_bounding_sphere(const float* q)
     return make_float4((float)c[0], (float)c[1], (float)c[2], (float)rhs);
 }
 
+// The three order arrays must each be strictly increasing and together be a permutation of 0..N-1
+// (slot = insertion index of CScene::m_Surfaces); materials must exist.  O(N), no scratch memory.
+static const char* validate_orders(const rtb200_scene* s, long long N)
+{
+    const int T = s->n_triangles, Q = s->n_quadrics, P = s->n_planes, M = s->n_materials;
+    for (int i = 0; i < T; ++i) if (s->tri_material[i] < 0 || s->tri_material[i] >= M) return "tri_order/tri_material invalid";
+    for (int i = 0; i < Q; ++i) if (s->quad_material[i] < 0 || s->quad_material[i] >= M) return "quad_order/quad_material invalid";
+    for (int i = 0; i < P; ++i) if (s->plane_material[i] < 0 || s->plane_material[i] >= M) return "plane_order/plane_material invalid";
+    int it = 0, iq = 0, ip = 0;
+    for (long long k = 0; k < N; ++k) {                       // slot k must be the head of exactly one list
+        if (it < T && s->tri_order[it] == k) ++it;
+        else if (iq < Q && s->quad_order[iq] == k) ++iq;
+        else if (ip < P && s->plane_order[ip] == k) ++ip;
+        else return it < T || (iq >= Q && ip >= P) ? "tri_order/tri_material invalid" : (iq < Q ? "quad_order/quad_material invalid" : "plane_order/plane_material invalid");
+    }
+    return nullptr;
+}
+
+// memcpy of a large array into the pinned staging buffer on a few threads (one core moves ~10 GB/s)
+static void parallel_copy(void* dst, const void* src, size_t bytes)
+{
+    const size_t min_slice = 4u << 20;
+    int n = (int)std::min<size_t>(4, bytes / min_slice);
+    if (n <= 1) { memcpy(dst, src, bytes); return; }
+    const size_t slice = ((bytes / (size_t)n) + 63) & ~(size_t)63;
+    std::vector<std::thread> th;
+    for (int i = 1; i < n; ++i) {
+        const size_t off = slice * (size_t)i, len = std::min(slice, bytes - std::min(bytes, off));
+        if (len) th.emplace_back([=] { memcpy(static_cast<unsigned char*>(dst) + off, static_cast<const unsigned char*>(src) + off, len); });
+    }
+    memcpy(dst, src, std::min(slice, bytes));
+    for (auto& t : th) t.join();
+}
+
 extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
 {
     if (!ctx || !s) return RTB200_E_ARG;
@@ -248,10 +285,101 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
 
     // the previous upload may still be reading the staging buffer (uploads are asynchronous)
     if (ctx->upload_pending) { CU(cudaEventSynchronize(ctx->ev[5])); ctx->upload_pending = false; }
-    cudaError_t e = ctx->stage.ensure(total);
-    if (e != cudaSuccess) return set_cuda_error(ctx, e, "pinned staging");
-    e = ctx->scene_buf.ensure(total);
+    cudaError_t e = ctx->scene_buf.ensure(total);
     if (e != cudaSuccess) return set_cuda_error(ctx, e, "scene buffer");
+
+    // ---- large meshes: upload the raw arrays, pack on the device (rt_pack.cu) -----------------------
+    int pack_min = 2048;
+    if (const char* pm = getenv("RTB200_PACK_ON_DEVICE_MIN")) pack_min = atoi(pm);
+    if (T >= pack_min && T > 0) {
+        if (const char* why = validate_orders(s, N)) return fail(ctx, RTB200_E_ARG, why);
+        // staging: [materials + lights][quad + plane records][quad centred forms][raw triangle arrays]
+        const size_t ml_bytes = (size_t)rl.bytes - (size_t)rl.off_mat;
+        const size_t qp_bytes = sizeof(QuadRec) * (size_t)Q + sizeof(PlaneRec) * (size_t)P;
+        const size_t s_qp = align16(ml_bytes), s_raw = align16(s_qp + qp_bytes);
+        const size_t r_r3 = 0, r_pts = align16(sizeof(float4) * (size_t)Q), r_nrm = r_pts + align16(36 * (size_t)T),
+                     r_mat = r_nrm + align16(12 * (size_t)T), r_ord = r_mat + align16(4 * (size_t)T), raw_bytes = r_ord + align16(4 * (size_t)T);
+        if ((e = ctx->stage.ensure(s_raw + raw_bytes)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned staging");
+        if ((e = ctx->raw_buf.ensure(raw_bytes)) != cudaSuccess) return set_cuda_error(ctx, e, "raw scene buffer");
+        unsigned char* h = ctx->stage.as<unsigned char>();
+        memset(h, 0, s_raw + r_pts);
+        MatRec* mat = reinterpret_cast<MatRec*>(h);
+        LightRec* light = reinterpret_cast<LightRec*>(h + (rl.off_light - rl.off_mat));
+        bool any_refl = false, any_refr = false, any_both = false;
+        for (int i = 0; i < M; ++i) {
+            const rtb200_material& m = s->materials[i];
+            mat[i].m0 = make_float4(m.color[0], m.color[1], m.color[2], m.ambient);
+            mat[i].m1 = make_float4(m.diffuse, m.specular, m.shininess, m.reflect);
+            mat[i].m2 = make_float4(m.refract, m.ior, 0.f, 0.f);
+            const bool a = m.reflect > 0.f, b = m.refract > 0.f;
+            any_refl |= a; any_refr |= b; any_both |= (a && b);
+        }
+        for (int i = 0; i < L; ++i) {
+            const rtb200_light& l = s->lights[i];
+            light[i].l0 = make_float4(l.position[0], l.position[1], l.position[2], l.intensity);
+            light[i].l1 = make_float4(l.color[0], l.color[1], l.color[2], 0.f);
+        }
+        QuadRec* quad = reinterpret_cast<QuadRec*>(h + s_qp);
+        float4* qr3 = reinterpret_cast<float4*>(h + s_raw + r_r3);
+        for (int i = 0; i < Q; ++i) {
+            const float* c = s->quad_coef + 10 * (size_t)i;
+            quad[i].q0 = make_float4(c[0], c[1], c[2], i2f(s->quad_order[i]));
+            quad[i].q1 = make_float4(c[3], c[4], c[5], i2f(s->quad_material[i]));
+            quad[i].q2 = make_float4(c[6], c[7], c[8], c[9]);
+            qr3[i] = quadric_bounding_sphere(c);
+        }
+        PlaneRec* plane = reinterpret_cast<PlaneRec*>(h + s_qp + sizeof(QuadRec) * (size_t)Q);
+        for (int i = 0; i < P; ++i) {
+            const float* c = s->plane_coef + 4 * (size_t)i;
+            plane[i].nc = make_float4(c[0], c[1], c[2], c[3]);
+            plane[i].order = s->plane_order[i]; plane[i].material = s->plane_material[i];
+        }
+        parallel_copy(h + s_raw + r_pts, s->tri_points, 36 * (size_t)T);
+        parallel_copy(h + s_raw + r_nrm, s->tri_normal, 12 * (size_t)T);
+        parallel_copy(h + s_raw + r_mat, s->tri_material, 4 * (size_t)T);
+        parallel_copy(h + s_raw + r_ord, s->tri_order, 4 * (size_t)T);
+
+        unsigned char* d = ctx->scene_buf.as<unsigned char>();
+        unsigned char* draw = ctx->raw_buf.as<unsigned char>();
+        CU(cudaEventRecord(ctx->ev[4], ctx->stream));
+        CU(cudaMemcpyAsync(d + rl.off_mat, h, ml_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        if (qp_bytes) CU(cudaMemcpyAsync(d + off_quad, h + s_qp, qp_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(draw, h + s_raw, raw_bytes, cudaMemcpyHostToDevice, ctx->stream));
+        PackParams pp;
+        memset(&pp, 0, sizeof pp);
+        pp.T = T; pp.Tpad = Tpad; pp.Q = Q; pp.P = P;
+        pp.tri_points = reinterpret_cast<const float*>(draw + r_pts);
+        pp.tri_normal = reinterpret_cast<const float*>(draw + r_nrm);
+        pp.tri_material = reinterpret_cast<const int*>(draw + r_mat);
+        pp.tri_order = reinterpret_cast<const int*>(draw + r_ord);
+        pp.quad_r3 = reinterpret_cast<const float4*>(draw + r_r3);
+        pp.surf = reinterpret_cast<SurfRec*>(d);
+        pp.tri = reinterpret_cast<TriRec*>(d + off_tri);
+        pp.trn = reinterpret_cast<float4*>(d + off_trn);
+        pp.quad = reinterpret_cast<const QuadRec*>(d + off_quad);
+        pp.plane = reinterpret_cast<const PlaneRec*>(d + off_plane);
+        CU(launch_pack_scene(pp, ctx->stream));
+        CU(cudaEventRecord(ctx->ev[5], ctx->stream));
+        ctx->upload_pending = true;
+        DeviceScene& ds = ctx->ds;
+        ds.rl = rl;
+        ds.blob = d;
+        ds.surf = reinterpret_cast<const SurfRec*>(d);
+        ds.mat = reinterpret_cast<const MatRec*>(d + rl.off_mat);
+        ds.light = reinterpret_cast<const LightRec*>(d + rl.off_light);
+        ds.n_tri = T; ds.n_quad = Q; ds.n_plane = P; ds.n_tri_padded = Tpad;
+        ds.tri = reinterpret_cast<const TriRec*>(d + off_tri);
+        ds.tri_normal = reinterpret_cast<const float4*>(d + off_trn);
+        ds.quad = reinterpret_cast<const QuadRec*>(d + off_quad);
+        ds.plane = reinterpret_cast<const PlaneRec*>(d + off_plane);
+        ctx->any_reflect = any_refl; ctx->any_refract = any_refr;
+        ctx->max_children = any_both ? 2 : ((any_refl || any_refr) ? 1 : 0);
+        ctx->have_scene = true;
+        return RTB200_OK;
+    }
+
+    e = ctx->stage.ensure(total);
+    if (e != cudaSuccess) return set_cuda_error(ctx, e, "pinned staging");
     unsigned char* h = ctx->stage.as<unsigned char>();
     memset(h, 0, total);
 

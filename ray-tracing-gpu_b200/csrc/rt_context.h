@@ -72,6 +72,7 @@ struct rtb200_ctx {
     rtb::DeviceScene ds{};
     rtb::DevBuf scene_buf;            // resident blob + streamed arrays, one allocation
     rtb::PinnedBuf stage;             // pinned staging for uploads
+    rtb::DevBuf raw_buf;              // large scenes: the caller's raw arrays on the device, input of the pack kernel
     int max_children = 0;             // 0, 1 or 2 secondary rays per hit at most
     bool any_reflect = false, any_refract = false;
     double last_h2d_ms = 0.0;

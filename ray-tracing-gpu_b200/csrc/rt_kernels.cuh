@@ -82,6 +82,22 @@ struct ResolveParams {
     int   pdl;                     // see LevelParams::pdl
 };
 
+// scene packing on the device (rt_pack.cu): raw caller arrays -> unified list + tile arrays
+struct PackParams {
+    int T, Tpad, Q, P;
+    const float* tri_points;       // [T][9]   raw, as the caller passed them
+    const float* tri_normal;       // [T][3]
+    const int*   tri_material;     // [T]
+    const int*   tri_order;        // [T]
+    const float4* quad_r3;         // [Q] centred form for the culling votes (computed on the host in double)
+    SurfRec* surf;                 // out: unified list (every slot is written by exactly one thread)
+    TriRec*  tri;                  // out: [Tpad]
+    float4*  trn;                  // out: [Tpad]
+    const QuadRec*  quad;          // [Q] already in place (uploaded packed)
+    const PlaneRec* plane;         // [P] already in place
+};
+cudaError_t launch_pack_scene(const PackParams& p, cudaStream_t st);
+
 // launchers (rt_resident.cu)
 size_t resident_smem_bytes(const ResidentLayout& rl);
 cudaError_t resident_prepare(size_t max_smem_bytes);

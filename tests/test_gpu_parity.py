@@ -166,3 +166,69 @@ def test_warp_vote_culling_changes_no_bit(rt, renderer, port):
     f0 = renderer.trace_shadow(pts, lights, flags=rt.F_FORCE_RESIDENT)
     f1 = renderer.trace_shadow(pts, lights, flags=rt.F_FORCE_RESIDENT | rt.F_EXACT_FP)
     assert bits_equal(f0, f1)
+
+
+def _with_pack_min(value, fn):
+    os.environ["RTB200_PACK_ON_DEVICE_MIN"] = str(value)
+    try:
+        return fn()
+    finally:
+        del os.environ["RTB200_PACK_ON_DEVICE_MIN"]
+
+
+def test_device_packing_equals_host_packing(rt, renderer):
+    """Large meshes are packed by a kernel from the raw arrays (rt_pack.cu), small scenes by the host
+    loop: same device scene either way -- frames and ray queries bit-equal on the resident path
+    (unified list in shared memory), the streamed path (tile arrays) and the LBVH."""
+    from importlib import import_module
+    synth = import_module("rtb200.synth")
+    NEVER, ALWAYS = 1 << 30, 1
+    # resident kernels: bundled scene 2 (12 triangles + plane, 3 lights)
+    ps = packed_scene(rt, 2)
+    fr = rt.make_frame(ps.frame, 200, 120, max_bounces=3)
+    frames = []
+    for pack_min in (NEVER, ALWAYS):
+        _with_pack_min(pack_min, lambda: renderer.set_scene(ps))
+        frames.append(renderer.render(fr))
+    assert frames[0][2].path == 0
+    assert bits_equal(frames[0][0], frames[1][0]) and np.array_equal(frames[0][1], frames[1][1])
+    # streamed + LBVH: soup with quadrics and planes between the triangles (orders interleaved)
+    base = synth.soup(3000, 12, 2, seed=77)
+    rng = np.random.default_rng(5)
+    T, Q, P, _ = base.counts
+    slots = rng.permutation(T + Q + P)                      # insertion order: the three types interleaved
+    arrays = {k: base[k] for k in base.a}
+    arrays["tri_order"] = np.sort(slots[:T]).astype(np.int32)
+    arrays["quad_order"] = np.sort(slots[T:T + Q]).astype(np.int32)
+    arrays["plane_order"] = np.sort(slots[T + Q:]).astype(np.int32)
+    ps = rt.PackedScene(arrays, base.frame)
+    org = (np.asarray(ps.frame["cam_pos"], np.float32) + rng.uniform(-20, 20, (20000, 3))).astype(np.float32)
+    d = rng.normal(size=(20000, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    got = []
+    for pack_min in (NEVER, ALWAYS):
+        _with_pack_min(pack_min, lambda: renderer.set_scene(ps))
+        renderer.build_bvh()
+        a = renderer.render(rt.make_frame(ps.frame, 160, 90, max_bounces=2, flags=rt.F_FORCE_STREAM))
+        b = renderer.render(rt.make_frame(ps.frame, 160, 90, max_bounces=2, flags=rt.F_USE_BVH))
+        q = renderer.trace_nearest(org, d, flags=rt.F_FORCE_STREAM)
+        got.append((a, b, q))
+    for i in range(2):
+        assert bits_equal(got[0][i][0], got[1][i][0]) and np.array_equal(got[0][i][1], got[1][i][1])
+    assert np.array_equal(got[0][2][0], got[1][2][0]) and bits_equal(got[0][2][1], got[1][2][1]) and bits_equal(got[0][2][2], got[1][2][2])
+    assert bits_equal(got[0][0][0], got[0][1][0])           # and the LBVH frame equals the brute-force frame
+
+
+@pytest.mark.parametrize("pack_min", [1 << 30, 1])
+def test_invalid_orders_rejected(rt, renderer, pack_min):
+    from importlib import import_module
+    synth = import_module("rtb200.synth")
+    base = synth.soup(50, 2, 1, seed=3)
+    for key, bad in (("tri_order", lambda a: np.concatenate([a[:1], a[:-1]])),       # a duplicate, not increasing
+                     ("tri_material", lambda a: np.where(np.arange(len(a)) == 7, 10 ** 6, a)),
+                     ("plane_order", lambda a: a + 5)):                              # out of range / not a permutation
+        arrays = {k: base[k].copy() for k in base.a}
+        arrays[key] = bad(arrays[key]).astype(np.int32)
+        ps = rt.PackedScene(arrays, base.frame)
+        with pytest.raises(rt.RtError):
+            _with_pack_min(pack_min, lambda: renderer.set_scene(ps))
