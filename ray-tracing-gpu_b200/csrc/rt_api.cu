@@ -328,6 +328,7 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
             quad[i].q2 = make_float4(c[6], c[7], c[8], c[9]);
             qr3[i] = quadric_bounding_sphere(c);
         }
+        ctx->h_quad.assign(quad, quad + Q); ctx->h_quad_r3.assign(qr3, qr3 + Q);
         PlaneRec* plane = reinterpret_cast<PlaneRec*>(h + s_qp + sizeof(QuadRec) * (size_t)Q);
         for (int i = 0; i < P; ++i) {
             const float* c = s->plane_coef + 4 * (size_t)i;
@@ -430,6 +431,9 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
         quad[i].q0 = make_float4(c[0], c[1], c[2], i2f(ord));
         quad[i].q1 = r.r1; quad[i].q2 = r.r2;
     }
+    ctx->h_quad.assign(quad, quad + Q);
+    ctx->h_quad_r3.resize((size_t)Q);
+    for (int i = 0; i < Q; ++i) ctx->h_quad_r3[(size_t)i] = surf[s->quad_order[i]].r3;
     PlaneRec* plane = reinterpret_cast<PlaneRec*>(h + off_plane);
     prev = -1;
     for (int i = 0; i < P; ++i) {

@@ -20,12 +20,21 @@
 //     exactly like Scene.cpp:1713.
 //   traversal: one ray per thread, stack in local memory, nearer child first, both child boxes
 //     in one 64-byte node fetch; primary rays are generated on the fly in 8x4-pixel warps.
+//   bounded quadrics: a quadric rtb200_set_scene could write in centred form
+//     sum q_i (x_i - c_i)^2 = rhs with every q_i > 0 and no mixed terms (spheres, axis-aligned
+//     ellipsoids) is a primitive of the same tree; its box is the box of the INFLATED quadric
+//     sum q_i (x_i - c_i)^2 <= 1.05 rhs + 2e-5 M(R), the region outside of which the reference's
+//     float discriminant cannot come out positive (rt_resident.cu: quadric_miss, same margin, with
+//     M bounded for every origin within R).  Its leaf test is the reference's Quadrique.cpp:160
+//     sequence with the ten original coefficients.  Cylinders, cones, paraboloids, rotated quadrics
+//     and planes stay in the linear side list.
 #include <algorithm>
 #include <cfloat>
 #include <climits>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -41,7 +50,9 @@ namespace rtb {
 
 struct BvhState {
     DevBuf nodes, tri_sorted, keys, keys_out, idx, idx_out, cub_tmp, parent, leaf_parent, gamma, flags, bounds;
+    DevBuf tree_quad, side_quad;                   // bounded quadrics as tree records / the rest as QuadRec
     int    n_tri = 0, n_nodes = 0, root = 0;
+    int    n_prims = 0, n_tree_quad = 0, n_side_quad = 0;
     bool   built = false;
     float  lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};   // vertex bounds of the triangles
     float  radius = 0.f;                           // R the boxes are padded for
@@ -62,11 +73,45 @@ static BvhState* bvh_state(rtb200_ctx* c)
 RT_DEV int float_order(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
 static inline float order_float(int i) { const int b = i >= 0 ? i : i ^ 0x7fffffff; float f; memcpy(&f, &b, 4); return f; }
 
-__global__ void k_bvh_bounds(const TriRec* __restrict__ tri, int n, int* __restrict__ bounds)
+// primitive i of the build: a triangle of the scene array or a bounded quadric record
+RT_DEV TriRec bvh_prim(const TriRec* __restrict__ tri, int n_tri, const TriRec* __restrict__ tq, int i)
+{
+    return i < n_tri ? tri[i] : tq[i - n_tri];
+}
+RT_DEV bool rec_is_quadric(const float4& c) { return c.w != 0.0f; }
+
+// box of a bounded quadric record; R < 0: the quadric itself, R >= 0: inflated for ray origins within R
+RT_DEV void quadric_box(const float4& a, const float4& b, const float4& c, float R, float* lo, float* hi)
+{
+    const float q[3] = {a.x, a.y, a.z}, l[3] = {b.x, b.y, b.z};
+    float ctr[3], M = 0.f;
+    #pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        ctr[k] = -l[k] / (2.0f * q[k]);
+        const float far = fabsf(ctr[k]) + fmaxf(R, 0.f);
+        M += q[k] * (far * far + ctr[k] * ctr[k]);
+    }
+    const float lim = R < 0.f ? c.y : fmaf(c.y, 1.05f, 2.0e-5f * M);
+    #pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float h = sqrtf(lim / q[k]) * 1.00001f + 1.0e-6f * fabsf(ctr[k]);
+        lo[k] = ctr[k] - h; hi[k] = ctr[k] + h;
+    }
+}
+
+__global__ void k_bvh_bounds(const TriRec* __restrict__ tri, int n_tri, const TriRec* __restrict__ tq, int n, int* __restrict__ bounds)
 {
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 a = tri[i].a, b = tri[i].b, c = tri[i].c;
+        const TriRec r = bvh_prim(tri, n_tri, tq, i);
+        const float4 a = r.a, b = r.b, c = r.c;
+        if (rec_is_quadric(c)) {
+            float ql[3], qh[3];
+            quadric_box(a, b, c, -1.0f, ql, qh);
+            #pragma unroll
+            for (int k = 0; k < 3; ++k) { lo[k] = fminf(lo[k], ql[k]); hi[k] = fmaxf(hi[k], qh[k]); }
+            continue;
+        }
         const float p[3] = {a.x, a.y, a.z}, e1[3] = {b.x, b.y, b.z}, e2[3] = {c.x, c.y, c.z};
         #pragma unroll
         for (int k = 0; k < 3; ++k) {
@@ -103,13 +148,15 @@ RT_DEV unsigned long long expand21(unsigned int v)
 
 struct Bounds6 { float lo[3], inv[3]; };
 
-__global__ void k_bvh_morton(const TriRec* __restrict__ tri, int n, Bounds6 b, unsigned long long* __restrict__ keys,
-                             unsigned int* __restrict__ idx)
+__global__ void k_bvh_morton(const TriRec* __restrict__ tri, int n_tri, const TriRec* __restrict__ tq, int n, Bounds6 b,
+                             unsigned long long* __restrict__ keys, unsigned int* __restrict__ idx)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const float4 a = tri[i].a, e1 = tri[i].b, e2 = tri[i].c;
-    const float c[3] = {a.x + (e1.x + e2.x) * (1.0f / 3.0f), a.y + (e1.y + e2.y) * (1.0f / 3.0f), a.z + (e1.z + e2.z) * (1.0f / 3.0f)};
+    const TriRec r = bvh_prim(tri, n_tri, tq, i);
+    const float4 a = r.a, e1 = r.b, e2 = r.c;
+    float c[3] = {a.x + (e1.x + e2.x) * (1.0f / 3.0f), a.y + (e1.y + e2.y) * (1.0f / 3.0f), a.z + (e1.z + e2.z) * (1.0f / 3.0f)};
+    if (rec_is_quadric(e2)) { c[0] = -e1.x / (2.0f * a.x); c[1] = -e1.y / (2.0f * a.y); c[2] = -e1.z / (2.0f * a.z); }
     unsigned int q[3];
     #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -120,11 +167,12 @@ __global__ void k_bvh_morton(const TriRec* __restrict__ tri, int n, Bounds6 b, u
     idx[i] = (unsigned int)i;
 }
 
-__global__ void k_bvh_gather(const TriRec* __restrict__ tri, const unsigned int* __restrict__ idx, int n, TriRec* __restrict__ out)
+__global__ void k_bvh_gather(const TriRec* __restrict__ tri, int n_tri, const TriRec* __restrict__ tq,
+                             const unsigned int* __restrict__ idx, int n, TriRec* __restrict__ out)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i] = tri[idx[i]];
+    out[i] = bvh_prim(tri, n_tri, tq, (int)idx[i]);
 }
 
 // common-prefix length of keys i and j (Karras 2012, sec. 4); equal keys fall back to the index
@@ -174,7 +222,7 @@ __global__ void k_bvh_hierarchy(const unsigned long long* __restrict__ keys, int
 // merges the two child boxes and continues
 __global__ void k_bvh_refit(const TriRec* __restrict__ tri, int n, BvhNode* nodes, const int* __restrict__ parent,
                             const int* __restrict__ leaf_parent, const int* __restrict__ gamma, int* flags,
-                            float pad_scale, float pad_floor)
+                            float pad_scale, float pad_floor, float radius)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -182,7 +230,11 @@ __global__ void k_bvh_refit(const TriRec* __restrict__ tri, int n, BvhNode* node
     const float l1 = sqrtf(b.x * b.x + b.y * b.y + b.z * b.z), l2 = sqrtf(c.x * c.x + c.y * c.y + c.z * c.z);
     const float pad = fmaxf(pad_scale * l1 * l2, pad_floor);
     float lo[3], hi[3];
-    {
+    if (rec_is_quadric(c)) {
+        quadric_box(a, b, c, radius, lo, hi);
+        #pragma unroll
+        for (int k = 0; k < 3; ++k) { lo[k] -= pad_floor; hi[k] += pad_floor; }
+    } else {
         const float p[3] = {a.x, a.y, a.z}, e1[3] = {b.x, b.y, b.z}, e2[3] = {c.x, c.y, c.z};
         #pragma unroll
         for (int k = 0; k < 3; ++k) {
@@ -303,7 +355,7 @@ RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& l
     }
 }
 
-template <int MODE, bool PRIMARY>
+template <int MODE, bool PRIMARY, bool QUADS>    // QUADS: the tree holds bounded quadrics besides triangles
 __global__ void __launch_bounds__(BVH_THREADS)
 k_bvh_nearest(const __grid_constant__ TraceParams p)
 {
@@ -325,16 +377,23 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
         const int i = blockIdx.x * BVH_THREADS + threadIdx.x;
         if (i < p.n_rays) { slot = i; o = f4_xyz(p.in_od0[i]); d = f4_xyz(p.in_od1[i]); }
     }
-    unsigned n_nodes = 0, n_tests = 0, overflow = 0;
+    unsigned n_nodes = 0, n_tests = 0, n_qtests = 0, overflow = 0;
     if (slot >= 0) {
         float best_t = -1.0f;
         int best_id = -1;
-        if (s.n_tri > 0) {
+        if (s.bvh_n_prims > 0) {
             const TriRec* __restrict__ tri = s.bvh_tri;
             bvh_traverse(s, o, d, 3.0e38f, [&](int first, int count, float limit) -> float {
                 for (int k = 0; k < count; ++k) {
                     const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
-                    const float tt = triangle_leaf<MODE>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc),
+                    float tt;
+                    if (QUADS && rec_is_quadric(rc)) {      // bounded quadric: the reference sequence, original coefficients
+                        const Quadric Q = { ra.x, ra.y, ra.z, 0.f, 0.f, 0.f, rb.x, rb.y, rb.z, rc.x };
+                        bool lin;
+                        tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+                        ++n_qtests; --n_tests;
+                    } else
+                    tt = triangle_leaf<MODE>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc),
                                                          best_t < 0.f ? 3.0e38f : fmaf(best_t, CULL_TREL, CULL_TABS));
                     const int ord = __float_as_int(ra.w);
                     if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) {
@@ -345,9 +404,10 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
                 return limit;
             }, n_nodes, overflow);
         }
-        // quadrics and planes: the brute-force side list (reference sequence; ties -> lower order)
-        for (int q = 0; q < s.n_quad; ++q) {
-            const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
+        // quadrics outside the tree and planes: the brute-force side list (reference sequence; ties -> lower order)
+        n_qtests += (unsigned)s.bvh_n_quad;
+        for (int q = 0; q < s.bvh_n_quad; ++q) {
+            const float4 q0 = __ldg(&s.bvh_quad[q].q0), q1 = __ldg(&s.bvh_quad[q].q1), q2 = __ldg(&s.bvh_quad[q].q2);
             const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
             const int ord = __float_as_int(q0.w);
             bool lin;
@@ -366,12 +426,14 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
     for (int off = 16; off > 0; off >>= 1) {
         n_nodes += __shfl_xor_sync(FULL_MASK, n_nodes, off);
         n_tests += __shfl_xor_sync(FULL_MASK, n_tests, off);
+        n_qtests += __shfl_xor_sync(FULL_MASK, n_qtests, off);
         overflow |= __shfl_xor_sync(FULL_MASK, overflow, off);
     }
     if (lane == 0 && p.stats) {
         unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
         if (n_nodes) atomicAdd(&st[ST_BVH_NODES], (unsigned long long)n_nodes);
         if (n_tests) atomicAdd(&st[ST_TEST_TRI], (unsigned long long)n_tests);
+        if (n_qtests) atomicAdd(&st[ST_TEST_QUAD], (unsigned long long)n_qtests);
         if (overflow) atomicAdd(&st[ST_BVH_OVERFLOW], 1ull);
     }
 }
@@ -380,7 +442,7 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
 // the filter by colour*kt (Scene.cpp:1856-1857).  An opaque occluder makes the filter exactly 0
 // (0 * finite = 0), so the traversal may stop there; transparent occluders are collected and
 // multiplied in insertion order, the order of the linear scan.
-template <int MODE>
+template <int MODE, bool QUADS>
 __global__ void __launch_bounds__(BVH_THREADS)
 k_bvh_shadow(const __grid_constant__ ShadowParams p)
 {
@@ -397,13 +459,20 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
         bool zero = false;
         int l_ord[BVH_SHADOW_LIST], l_mat[BVH_SHADOW_LIST];
         int n_list = 0;
-        if (s.n_tri > 0) {
+        if (s.bvh_n_prims > 0) {
             const TriRec* __restrict__ tri = s.bvh_tri;
             bvh_traverse(s, o, d, dist, [&](int first, int count, float limit) -> float {
                 n_tests += (unsigned)count;
                 for (int k = 0; k < count; ++k) {
                     const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
-                    const float tt = triangle_leaf<MODE>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc), tlim);
+                    float tt;
+                    if (QUADS && rec_is_quadric(rc)) {
+                        const Quadric Q = { ra.x, ra.y, ra.z, 0.f, 0.f, 0.f, rb.x, rb.y, rb.z, rc.x };
+                        bool lin;
+                        tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+                        ++n_side_q; --n_tests;
+                    } else
+                    tt = triangle_leaf<MODE>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc), tlim);
                     if (tt > RT_EPS && tt < dist) {
                         const int m = __float_as_int(rb.w);
                         const float4 m0 = __ldg(&s.mat[m].m0);
@@ -432,9 +501,9 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
             }
         }
         if (!(fr == 0.f && fg == 0.f && fb == 0.f)) {
-            n_side_q = (unsigned)s.n_quad; n_side_p = (unsigned)s.n_plane;
-            for (int q = 0; q < s.n_quad; ++q) {
-                const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
+            n_side_q += (unsigned)s.bvh_n_quad; n_side_p = (unsigned)s.n_plane;
+            for (int q = 0; q < s.bvh_n_quad; ++q) {
+                const float4 q0 = __ldg(&s.bvh_quad[q].q0), q1 = __ldg(&s.bvh_quad[q].q1), q2 = __ldg(&s.bvh_quad[q].q2);
                 const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
                 bool lin;
                 const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
@@ -475,21 +544,28 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
     }
 }
 
+template <bool QUADS>
+static void launch_nearest_t(const TraceParams& p, int blocks, cudaStream_t st)
+{
+    if (p.primary) {
+        if (p.mode == 2)      k_bvh_nearest<2, true, QUADS><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else if (p.mode == 1) k_bvh_nearest<1, true, QUADS><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else                  k_bvh_nearest<0, true, QUADS><<<blocks, BVH_THREADS, 0, st>>>(p);
+    } else {
+        if (p.mode == 2)      k_bvh_nearest<2, false, QUADS><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else if (p.mode == 1) k_bvh_nearest<1, false, QUADS><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else                  k_bvh_nearest<0, false, QUADS><<<blocks, BVH_THREADS, 0, st>>>(p);
+    }
+}
+
 cudaError_t launch_bvh_nearest(const TraceParams& p, cudaStream_t st)
 {
     int blocks;
     if (p.primary) blocks = ((p.f.LW + 15) / 16) * ((p.chunk_rows + 7) / 8);
     else blocks = (p.n_rays + BVH_THREADS - 1) / BVH_THREADS;
     if (blocks <= 0) return cudaSuccess;
-    if (p.primary) {
-        if (p.mode == 2)      k_bvh_nearest<2, true><<<blocks, BVH_THREADS, 0, st>>>(p);
-        else if (p.mode == 1) k_bvh_nearest<1, true><<<blocks, BVH_THREADS, 0, st>>>(p);
-        else                  k_bvh_nearest<0, true><<<blocks, BVH_THREADS, 0, st>>>(p);
-    } else {
-        if (p.mode == 2)      k_bvh_nearest<2, false><<<blocks, BVH_THREADS, 0, st>>>(p);
-        else if (p.mode == 1) k_bvh_nearest<1, false><<<blocks, BVH_THREADS, 0, st>>>(p);
-        else                  k_bvh_nearest<0, false><<<blocks, BVH_THREADS, 0, st>>>(p);
-    }
+    if (p.s.bvh_n_prims > p.s.n_tri) launch_nearest_t<true>(p, blocks, st);     // triangle-only trees keep the lean leaf code
+    else                             launch_nearest_t<false>(p, blocks, st);
     return cudaGetLastError();
 }
 
@@ -497,9 +573,15 @@ cudaError_t launch_bvh_shadow(const ShadowParams& p, cudaStream_t st)
 {
     const int blocks = (p.n_queries + BVH_THREADS - 1) / BVH_THREADS;
     if (blocks <= 0) return cudaSuccess;
-    if (p.mode == 2)      k_bvh_shadow<2><<<blocks, BVH_THREADS, 0, st>>>(p);
-    else if (p.mode == 1) k_bvh_shadow<1><<<blocks, BVH_THREADS, 0, st>>>(p);
-    else                  k_bvh_shadow<0><<<blocks, BVH_THREADS, 0, st>>>(p);
+    if (p.s.bvh_n_prims > p.s.n_tri) {
+        if (p.mode == 2)      k_bvh_shadow<2, true><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else if (p.mode == 1) k_bvh_shadow<1, true><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else                  k_bvh_shadow<0, true><<<blocks, BVH_THREADS, 0, st>>>(p);
+    } else {
+        if (p.mode == 2)      k_bvh_shadow<2, false><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else if (p.mode == 1) k_bvh_shadow<1, false><<<blocks, BVH_THREADS, 0, st>>>(p);
+        else                  k_bvh_shadow<0, false><<<blocks, BVH_THREADS, 0, st>>>(p);
+    }
     return cudaGetLastError();
 }
 
@@ -517,7 +599,7 @@ void bvh_release(rtb200_ctx* c)
     if (!c->bvh_state) return;
     BvhState* b = static_cast<BvhState*>(c->bvh_state);
     b->nodes.release(); b->tri_sorted.release(); b->keys.release(); b->keys_out.release(); b->idx.release(); b->idx_out.release();
-    b->cub_tmp.release(); b->parent.release(); b->leaf_parent.release(); b->gamma.release(); b->flags.release(); b->bounds.release();
+    b->cub_tmp.release(); b->tree_quad.release(); b->side_quad.release(); b->parent.release(); b->leaf_parent.release(); b->gamma.release(); b->flags.release(); b->bounds.release();
     delete b;
     c->bvh_state = nullptr;
 }
@@ -526,6 +608,7 @@ void bvh_invalidate(rtb200_ctx* c)
 {
     if (c->bvh_state) static_cast<BvhState*>(c->bvh_state)->built = false;
     c->ds.bvh_nodes = nullptr; c->ds.bvh_tri = nullptr; c->ds.bvh_root = 0;
+    c->ds.bvh_n_prims = 0; c->ds.bvh_quad = nullptr; c->ds.bvh_n_quad = 0;
 }
 
 bool bvh_ready(const rtb200_ctx* c)
@@ -535,17 +618,32 @@ bool bvh_ready(const rtb200_ctx* c)
 
 static int bvh_refit(rtb200_ctx* c, BvhState* b, float radius)
 {
-    const int T = b->n_tri;
+    const int n = b->n_prims;
     b->radius = radius;
-    if (T <= BVH_LEAF_MAX) return RTB200_OK;                  // a single leaf: no boxes at all
+    if (n <= BVH_LEAF_MAX) return RTB200_OK;                  // a single leaf: no boxes at all
     // pad = PADC * 2^-24 / EPSILON * R * |e1| |e2|, floor 32 ulp of R (rounding of the slab test)
     const float pad_scale = b->padc * 5.9604645e-8f / RT_EPS * radius;
     const float pad_floor = 32.0f * 1.1920929e-7f * radius;
-    BCU(cudaMemsetAsync(b->flags.p, 0, sizeof(int) * (size_t)(T - 1), c->stream));
-    k_bvh_refit<<<(T + 255) / 256, 256, 0, c->stream>>>(b->tri_sorted.as<TriRec>(), T, b->nodes.as<BvhNode>(), b->parent.as<int>(),
-                                                        b->leaf_parent.as<int>(), b->gamma.as<int>(), b->flags.as<int>(), pad_scale, pad_floor);
+    BCU(cudaMemsetAsync(b->flags.p, 0, sizeof(int) * (size_t)(n - 1), c->stream));
+    k_bvh_refit<<<(n + 255) / 256, 256, 0, c->stream>>>(b->tri_sorted.as<TriRec>(), n, b->nodes.as<BvhNode>(), b->parent.as<int>(),
+                                                        b->leaf_parent.as<int>(), b->gamma.as<int>(), b->flags.as<int>(),
+                                                        pad_scale, pad_floor, radius);
     BCU(cudaGetLastError());
     return RTB200_OK;
+}
+
+// Which quadrics become primitives of the tree: centred form known (rtb200_set_scene: r3.w = rhs > 0, no mixed
+// terms), every quadratic coefficient positive (a cylinder has one zero: unbounded) and mixed terms that are +0
+// bit for bit (the leaf test passes literal zeros for them).
+static bool quadric_is_bounded(const QuadRec& q, const float4& r3)
+{
+    if (!(r3.w > 0.f) || !(q.q0.x > 0.f && q.q0.y > 0.f && q.q0.z > 0.f)) return false;
+    const float mixed[3] = {q.q1.x, q.q1.y, q.q1.z};
+    unsigned int bits[3];
+    memcpy(bits, mixed, sizeof bits);
+    if (bits[0] | bits[1] | bits[2]) return false;
+    const float ratio = std::max(q.q0.x, std::max(q.q0.y, q.q0.z)) / std::min(q.q0.x, std::min(q.q0.y, q.q0.z));
+    return std::isfinite(ratio) && ratio < 1.0e6f && std::isfinite(r3.w);
 }
 
 int bvh_build(rtb200_ctx* c)
@@ -553,33 +651,61 @@ int bvh_build(rtb200_ctx* c)
     BvhState* b = bvh_state(c);
     b->built = false;
     const int T = c->ds.n_tri;
-    if (T >= (1 << BVH_LEAF_SHIFT)) { c->last_error = "too many triangles for the LBVH leaf encoding"; return RTB200_E_ARG; }
     if (const char* e = getenv("RTB200_BVH_PADC")) { const float v = (float)atof(e); if (v >= 0.f) b->padc = v; }
-    b->n_tri = T; b->n_nodes = T > BVH_LEAF_MAX ? T - 1 : 0;
-    b->root = T > BVH_LEAF_MAX ? 0 : ~(0 | ((std::max(T, 1) - 1) << BVH_LEAF_SHIFT));
     cudaError_t e;
+
+    // ---- quadrics: bounded ones join the tree, the others stay in the linear side list -----------------------
+    std::vector<TriRec> tree_q;
+    std::vector<QuadRec> side_q;
+    const bool quads_in_tree = getenv("RTB200_BVH_NO_QUADRICS") == nullptr;
+    for (size_t i = 0; i < c->h_quad.size(); ++i) {
+        const QuadRec& q = c->h_quad[i];
+        const float4 r3 = i < c->h_quad_r3.size() ? c->h_quad_r3[i] : make_float4(0.f, 0.f, 0.f, -1.f);
+        if (quads_in_tree && quadric_is_bounded(q, r3)) {
+            TriRec r;
+            r.a = q.q0;                                                   // A B C | order
+            r.b = make_float4(q.q2.x, q.q2.y, q.q2.z, q.q1.w);            // lx ly lz | material
+            r.c = make_float4(q.q2.w, r3.w, 0.f, 1.0f);                   // K, rhs, -, tag
+            tree_q.push_back(r);
+        } else side_q.push_back(q);
+    }
+    const int Qb = (int)tree_q.size(), Qs = (int)side_q.size();
+    const long long n_ll = (long long)T + Qb;
+    if (n_ll >= (1ll << BVH_LEAF_SHIFT)) { c->last_error = "too many primitives for the LBVH leaf encoding"; return RTB200_E_ARG; }
+    const int n = (int)n_ll;
+    if ((e = b->tree_quad.ensure(sizeof(TriRec) * (size_t)std::max(Qb, 1))) != cudaSuccess ||
+        (e = b->side_quad.ensure(sizeof(QuadRec) * (size_t)std::max(Qs, 1))) != cudaSuccess) return set_cuda_error(c, e, "bvh quadric buffers");
+    // (pageable sources: the copies are staged before the calls return)
+    if (Qb) BCU(cudaMemcpyAsync(b->tree_quad.p, tree_q.data(), sizeof(TriRec) * (size_t)Qb, cudaMemcpyHostToDevice, c->stream));
+    if (Qs) BCU(cudaMemcpyAsync(b->side_quad.p, side_q.data(), sizeof(QuadRec) * (size_t)Qs, cudaMemcpyHostToDevice, c->stream));
+    const TriRec* tq = b->tree_quad.as<TriRec>();
+
+    b->n_tri = T; b->n_prims = n; b->n_tree_quad = Qb; b->n_side_quad = Qs;
+    b->n_nodes = n > BVH_LEAF_MAX ? n - 1 : 0;
+    b->root = n > BVH_LEAF_MAX ? 0 : ~(0 | ((std::max(n, 1) - 1) << BVH_LEAF_SHIFT));
     cudaEvent_t ev0 = c->ev[2], ev1 = c->ev[3];
     BCU(cudaEventRecord(ev0, c->stream));
-    if (T > 0) {
-        const size_t n = (size_t)T;
-        if ((e = b->tri_sorted.ensure(sizeof(TriRec) * n)) != cudaSuccess || (e = b->bounds.ensure(sizeof(int) * 8)) != cudaSuccess)
+    if (n > 0) {
+        if ((e = b->tri_sorted.ensure(sizeof(TriRec) * (size_t)n)) != cudaSuccess || (e = b->bounds.ensure(sizeof(int) * 8)) != cudaSuccess)
             return set_cuda_error(c, e, "bvh buffers");
         int h_init[6] = {INT_MAX, INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MIN};
         BCU(cudaMemcpyAsync(b->bounds.p, h_init, sizeof h_init, cudaMemcpyHostToDevice, c->stream));
-        k_bvh_bounds<<<std::min((T + 255) / 256, 4 * c->sm_count), 256, 0, c->stream>>>(c->ds.tri, T, b->bounds.as<int>());
+        k_bvh_bounds<<<std::min((n + 255) / 256, 4 * c->sm_count), 256, 0, c->stream>>>(c->ds.tri, T, tq, n, b->bounds.as<int>());
         BCU(cudaGetLastError());
         int h_b[6];
         BCU(cudaMemcpyAsync(h_b, b->bounds.p, sizeof h_b, cudaMemcpyDeviceToHost, c->stream));
         BCU(cudaStreamSynchronize(c->stream));
         for (int k = 0; k < 3; ++k) { b->lo[k] = order_float(h_b[k]); b->hi[k] = order_float(h_b[3 + k]); }
+    } else {
+        for (int k = 0; k < 3; ++k) b->lo[k] = b->hi[k] = 0.f;
     }
-    if (T > BVH_LEAF_MAX) {
-        const size_t n = (size_t)T;
-        if ((e = b->nodes.ensure(sizeof(BvhNode) * (n - 1))) != cudaSuccess ||
-            (e = b->keys.ensure(8 * n)) != cudaSuccess || (e = b->keys_out.ensure(8 * n)) != cudaSuccess ||
-            (e = b->idx.ensure(4 * n)) != cudaSuccess || (e = b->idx_out.ensure(4 * n)) != cudaSuccess ||
-            (e = b->parent.ensure(4 * n)) != cudaSuccess || (e = b->leaf_parent.ensure(4 * n)) != cudaSuccess ||
-            (e = b->gamma.ensure(4 * n)) != cudaSuccess || (e = b->flags.ensure(4 * n)) != cudaSuccess)
+    if (n > BVH_LEAF_MAX) {
+        const size_t nn = (size_t)n;
+        if ((e = b->nodes.ensure(sizeof(BvhNode) * (nn - 1))) != cudaSuccess ||
+            (e = b->keys.ensure(8 * nn)) != cudaSuccess || (e = b->keys_out.ensure(8 * nn)) != cudaSuccess ||
+            (e = b->idx.ensure(4 * nn)) != cudaSuccess || (e = b->idx_out.ensure(4 * nn)) != cudaSuccess ||
+            (e = b->parent.ensure(4 * nn)) != cudaSuccess || (e = b->leaf_parent.ensure(4 * nn)) != cudaSuccess ||
+            (e = b->gamma.ensure(4 * nn)) != cudaSuccess || (e = b->flags.ensure(4 * nn)) != cudaSuccess)
             return set_cuda_error(c, e, "bvh buffers");
         Bounds6 bb;
         for (int k = 0; k < 3; ++k) {
@@ -587,27 +713,28 @@ int bvh_build(rtb200_ctx* c)
             const float ext = b->hi[k] - b->lo[k];
             bb.inv[k] = ext > 0.f ? 1.0f / ext : 0.0f;
         }
-        const int blocks = (T + 255) / 256;
-        k_bvh_morton<<<blocks, 256, 0, c->stream>>>(c->ds.tri, T, bb, b->keys.as<unsigned long long>(), b->idx.as<unsigned int>());
+        const int blocks = (n + 255) / 256;
+        k_bvh_morton<<<blocks, 256, 0, c->stream>>>(c->ds.tri, T, tq, n, bb, b->keys.as<unsigned long long>(), b->idx.as<unsigned int>());
         BCU(cudaGetLastError());
         size_t tmp_bytes = 0;
         BCU(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, b->keys.as<unsigned long long>(), b->keys_out.as<unsigned long long>(),
-                                            b->idx.as<unsigned int>(), b->idx_out.as<unsigned int>(), T, 0, 63, c->stream));
+                                            b->idx.as<unsigned int>(), b->idx_out.as<unsigned int>(), n, 0, 63, c->stream));
         if ((e = b->cub_tmp.ensure(tmp_bytes)) != cudaSuccess) return set_cuda_error(c, e, "sort scratch");
         BCU(cub::DeviceRadixSort::SortPairs(b->cub_tmp.p, tmp_bytes, b->keys.as<unsigned long long>(), b->keys_out.as<unsigned long long>(),
-                                            b->idx.as<unsigned int>(), b->idx_out.as<unsigned int>(), T, 0, 63, c->stream));
-        k_bvh_gather<<<blocks, 256, 0, c->stream>>>(c->ds.tri, b->idx_out.as<unsigned int>(), T, b->tri_sorted.as<TriRec>());
+                                            b->idx.as<unsigned int>(), b->idx_out.as<unsigned int>(), n, 0, 63, c->stream));
+        k_bvh_gather<<<blocks, 256, 0, c->stream>>>(c->ds.tri, T, tq, b->idx_out.as<unsigned int>(), n, b->tri_sorted.as<TriRec>());
         BCU(cudaGetLastError());
-        k_bvh_hierarchy<<<blocks, 256, 0, c->stream>>>(b->keys_out.as<unsigned long long>(), T, b->nodes.as<BvhNode>(), b->parent.as<int>(),
+        k_bvh_hierarchy<<<blocks, 256, 0, c->stream>>>(b->keys_out.as<unsigned long long>(), n, b->nodes.as<BvhNode>(), b->parent.as<int>(),
                                                        b->leaf_parent.as<int>(), b->gamma.as<int>());
         BCU(cudaGetLastError());
-    } else if (T > 0) {
-        BCU(cudaMemcpyAsync(b->tri_sorted.p, c->ds.tri, sizeof(TriRec) * (size_t)T, cudaMemcpyDeviceToDevice, c->stream));
+    } else if (n > 0) {
+        if (T) BCU(cudaMemcpyAsync(b->tri_sorted.p, c->ds.tri, sizeof(TriRec) * (size_t)T, cudaMemcpyDeviceToDevice, c->stream));
+        if (Qb) BCU(cudaMemcpyAsync(b->tri_sorted.as<TriRec>() + T, tq, sizeof(TriRec) * (size_t)Qb, cudaMemcpyDeviceToDevice, c->stream));
     }
-    // default radius: origins anywhere inside the triangles' bounds (secondary and shadow rays start
+    // default radius: origins anywhere inside the primitives' bounds (secondary and shadow rays start
     // on surfaces); a camera farther out triggers one refit (bvh_prepare)
     const float dx = b->hi[0] - b->lo[0], dy = b->hi[1] - b->lo[1], dz = b->hi[2] - b->lo[2];
-    const float diag = T > 0 ? sqrtf(dx * dx + dy * dy + dz * dz) : 0.f;
+    const float diag = n > 0 ? sqrtf(dx * dx + dy * dy + dz * dz) : 0.f;
     int rc = bvh_refit(c, b, diag);
     if (rc != RTB200_OK) return rc;
     BCU(cudaEventRecord(ev1, c->stream));
@@ -619,6 +746,9 @@ int bvh_build(rtb200_ctx* c)
     c->ds.bvh_nodes = b->nodes.as<BvhNode>();
     c->ds.bvh_tri = b->tri_sorted.as<TriRec>();
     c->ds.bvh_root = b->root;
+    c->ds.bvh_n_prims = n;
+    c->ds.bvh_quad = b->side_quad.as<QuadRec>();
+    c->ds.bvh_n_quad = Qs;
     return RTB200_OK;
 }
 
@@ -629,7 +759,7 @@ int bvh_prepare(rtb200_ctx* c, const float* origins3, int n)
 {
     if (!bvh_ready(c)) { c->last_error = "RTB200_F_USE_BVH without rtb200_build_bvh"; return RTB200_E_STATE; }
     BvhState* b = static_cast<BvhState*>(c->bvh_state);
-    if (b->n_tri == 0) return RTB200_OK;
+    if (b->n_prims == 0) return RTB200_OK;
     float need = 0.f;
     for (int i = 0; i < n; ++i) {
         float d2 = 0.f;

@@ -73,6 +73,8 @@ struct rtb200_ctx {
     rtb::DevBuf scene_buf;            // resident blob + streamed arrays, one allocation
     rtb::PinnedBuf stage;             // pinned staging for uploads
     rtb::DevBuf raw_buf;              // large scenes: the caller's raw arrays on the device, input of the pack kernel
+    std::vector<rtb::QuadRec> h_quad; // host copy of the quadrics and their centred forms (rt_bvh.cu decides which
+    std::vector<float4> h_quad_r3;    // of them are bounded and go into the tree)
     int max_children = 0;             // 0, 1 or 2 secondary rays per hit at most
     bool any_reflect = false, any_refract = false;
     double last_h2d_ms = 0.0;

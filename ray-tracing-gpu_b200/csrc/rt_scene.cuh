@@ -53,8 +53,12 @@ struct DeviceScene {
     int n_tri_padded;
     // LBVH over the triangles (null until rtb200_build_bvh)
     const BvhNode*  bvh_nodes;
-    const TriRec*   bvh_tri;        // triangles in Morton order (order / material travel in .a.w / .b.w)
-    int             bvh_root;       // reference of the root (a leaf reference when T <= BVH_LEAF_MAX)
+    const TriRec*   bvh_tri;        // primitives in Morton order: triangles (order / material in .a.w / .b.w, .c.w = 0)
+                                    // and bounded quadrics (A B C | order, lx ly lz | material, K rhs 0 | 1.0f)
+    int             bvh_root;       // reference of the root (a leaf reference when there are <= BVH_LEAF_MAX primitives)
+    int             bvh_n_prims;    // triangles + bounded quadrics in the tree
+    const QuadRec*  bvh_quad;       // quadrics the LBVH kernels still scan linearly (unbounded / rotated ones)
+    int             bvh_n_quad;
 };
 
 // ---- per-frame constants ------------------------------------------------------------------

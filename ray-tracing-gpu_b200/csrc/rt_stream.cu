@@ -229,7 +229,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     // nearest-hit queries test every surface by construction (no early-out): exact host-side count;
     // shadow queries are counted on the device (warps leave early once their filters are zero)
     c->host_tests[0] = use_bvh ? 0ull : rays_nearest * (unsigned long long)c->ds.n_tri;   // LBVH: counted on the device
-    c->host_tests[1] = rays_nearest * (unsigned long long)c->ds.n_quad;
+    c->host_tests[1] = use_bvh ? 0ull : rays_nearest * (unsigned long long)c->ds.n_quad;   // LBVH: counted on the device
     c->host_tests[2] = rays_nearest * (unsigned long long)c->ds.n_plane;
     return RTB200_OK;
 }

@@ -50,7 +50,7 @@ def test_soup_queries_equal_brute_force(rt, renderer, port, synth):
     ps = synth.soup(6000, 16, 2, seed=11)
     renderer.set_scene(ps)
     info = renderer.build_bvh()
-    assert info["triangles"] == 6000 and info["nodes"] == 5999
+    assert info["triangles"] == 6000 and info["nodes"] == 6000 + 16 - 1     # the 16 ellipsoids are tree primitives too
     rng = np.random.default_rng(4)
     n = 65536
     org, d = _camera_rays(ps, rng, n)
@@ -170,3 +170,98 @@ def test_stacked_transparent_occluders_keep_scan_order(rt, renderer, synth):
     f_v = renderer.trace_shadow(pts, lights, flags=rt.F_USE_BVH)
     assert bits_equal(f_b, f_v)
     assert ((f_b > 0) & (f_b < 0.7)).all()       # all six layers filtered the light
+
+
+def _quadric_scene(rt, synth, rng, n_ell, n_cyl, n_tris, scale=1.0):
+    """Ellipsoids / spheres of very different sizes (tree primitives), axis-aligned cylinders and one
+    rotated ellipsoid (side list), optional triangles, ground plane; a quarter of the materials transparent."""
+    base = synth.soup(max(n_tris, 1), 0, 2, seed=int(rng.integers(1 << 30)))
+    ctr = rng.uniform(-300, 300, (n_ell, 3)) * scale
+    ctr[:, 1] = rng.uniform(0, 250, n_ell) * scale
+    rad = np.exp(rng.uniform(np.log(0.5), np.log(60.0), (n_ell, 3))) * scale
+    rad[: n_ell // 3] = rad[: n_ell // 3, :1]                              # a third are spheres
+    quads = [synth._ellipsoid(ctr[i], rad[i]) for i in range(n_ell)]
+    for _ in range(n_cyl):                                                  # x^2 + z^2 = r^2 around (cx, cz): unbounded in y
+        cx, cz, r = rng.uniform(-300, 300) * scale, rng.uniform(-300, 300) * scale, rng.uniform(3, 20) * scale
+        quads.append(np.array([1, 0, 1, 0, 0, 0, -2 * cx, 0, -2 * cz, cx * cx + cz * cz - r * r], F))
+    rot = synth._ellipsoid(np.array([40.0, 90.0, -30.0]) * scale, np.array([30.0, 12.0, 20.0]) * scale)
+    rot[5] = 0.25 * rot[0]                                                  # an xy term: not axis-aligned any more
+    quads.append(rot)
+    quads = np.stack(quads).astype(F)
+    Q = len(quads)
+    tri = base["tri_points"][:n_tris] * scale
+    T = len(tri)
+    mats = np.zeros((32, 10), F)
+    mats[:, 0:3] = rng.uniform(0.2, 1.0, (32, 3)); mats[:, 3], mats[:, 4], mats[:, 5], mats[:, 6] = 0.2, 0.8, 0.3, 12.0
+    mats[:8, 8], mats[:8, 9] = rng.uniform(0.4, 0.9, 8), 1.3               # transparent: coloured shadow filters
+    slots = rng.permutation(T + Q + 1)
+    arrays = {"tri_points": tri.astype(F), "tri_normal": synth.face_normals(tri.astype(F)) if T else np.zeros((0, 3), F),
+              "tri_material": rng.integers(0, 32, T).astype(np.int32), "tri_order": np.sort(slots[:T]).astype(np.int32),
+              "quad_coef": quads, "quad_material": rng.integers(0, 32, Q).astype(np.int32),
+              "quad_order": np.sort(slots[T:T + Q]).astype(np.int32),
+              "plane_coef": np.array([[0, 1, 0, 45.0 * scale]], F), "plane_material": np.array([20], np.int32),
+              "plane_order": slots[T + Q:].astype(np.int32), "materials": mats,
+              "lights": np.array([[100 * scale, 600 * scale, 200 * scale, 1, 1, 1, 0.6], [-300 * scale, 500 * scale, -100 * scale, 1, 0.9, 0.8, 0.5]], F)}
+    return rt.PackedScene(arrays, base.frame), ctr, rad
+
+
+def _grazing_rays(rng, ctr, rad, n, far):
+    """Rays aimed at the silhouette of sphere-like quadrics (closest approach = radius * (1 +- 1e-5..1e-2))."""
+    k = rng.integers(0, len(ctr), n)
+    c, r = ctr[k], rad[k, 0]
+    org = c + rng.normal(size=(n, 3)) * far
+    to_c = c - org
+    to_c /= np.linalg.norm(to_c, axis=1, keepdims=True)
+    side = np.cross(to_c, rng.normal(size=(n, 3)))
+    side /= np.linalg.norm(side, axis=1, keepdims=True)
+    eps = rng.choice([-1e-2, -1e-4, -1e-5, 1e-5, 1e-4, 1e-2], n)
+    tgt = c + side * (r * (1 + eps))[:, None]
+    d = tgt - org
+    return org.astype(F), (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(F)
+
+
+@pytest.mark.parametrize("n_tris,scale,far", [(0, 1.0, 400.0), (3000, 1.0, 400.0), (500, 0.02, 30.0), (0, 1.0, 20000.0)])
+def test_bounded_quadrics_in_tree_equal_linear_scan(rt, renderer, synth, n_tris, scale, far):
+    """ellipsoids / spheres as LBVH primitives (inflated boxes) must give the linear
+    scan's winners and filters bit for bit -- random rays, rays grazing the silhouettes, origins far
+    outside the scene (refit for a larger R), tiny scenes, quadric-only scenes."""
+    rng = np.random.default_rng(1000 + n_tris)
+    ps, ctr, rad = _quadric_scene(rt, synth, rng, 300, 6, n_tris, scale)
+    renderer.set_scene(ps)
+    info = renderer.build_bvh()
+    assert info["nodes"] == n_tris + 300 - 1                                # cylinders and the rotated one stay outside
+    n = 60000
+    org1, d1 = _camera_rays(ps, rng, n // 2, jitter=200.0 * scale, lo=tuple(-350 * scale for _ in range(3)), hi=tuple(350 * scale for _ in range(3)))
+    org2, d2 = _grazing_rays(rng, ctr[:100], rad[:100], n // 2, far * scale if far < 1000 else far)
+    org, d = np.concatenate([org1, org2]), np.concatenate([d1, d2])
+    pts = (ctr[rng.integers(0, len(ctr), n)] + rng.normal(size=(n, 3)) * 40 * scale).astype(F)
+    lights = np.tile(ps["lights"][0, 0:3], (n, 1)).astype(F)
+    idx, filt = _compare_queries(rt, renderer, ps, org, d, pts, lights)
+    T = n_tris
+    hit_quadric = np.isin(idx, ps["quad_order"])
+    assert hit_quadric.mean() > 0.1 and ((filt > 0) & (filt < 1)).any()
+    fr_b = rt.make_frame(ps.frame, 160, 90, max_bounces=2, flags=rt.F_FORCE_STREAM)
+    fr_v = rt.make_frame(ps.frame, 160, 90, max_bounces=2, flags=rt.F_USE_BVH)
+    a, a8, st_a = renderer.render(fr_b)
+    b, b8, st_b = renderer.render(fr_v)
+    assert bits_equal(a, b) and np.array_equal(a8, b8)
+    if far < 1000:        # (boxes refitted for origins 20000 away are inflated until little is culled: still exact)
+        assert st_b.tests_quadric < st_a.tests_quadric / 2                  # the tree really culls them
+
+
+def test_quadrics_can_be_kept_out_of_the_tree(rt, renderer, synth):
+    import os
+    rng = np.random.default_rng(9)
+    ps, _, _ = _quadric_scene(rt, synth, rng, 50, 2, 200)
+    renderer.set_scene(ps)
+    os.environ["RTB200_BVH_NO_QUADRICS"] = "1"
+    try:
+        info = renderer.build_bvh()
+    finally:
+        del os.environ["RTB200_BVH_NO_QUADRICS"]
+    assert info["nodes"] == 199
+    fr = rt.make_frame(ps.frame, 96, 54, max_bounces=2, flags=rt.F_USE_BVH)
+    a, a8, _ = renderer.render(fr)
+    renderer.build_bvh()
+    b, b8, _ = renderer.render(fr)
+    assert bits_equal(a, b) and np.array_equal(a8, b8)
