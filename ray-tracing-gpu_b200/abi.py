@@ -97,6 +97,9 @@ class PackedScene:
         return (len(self.a["tri_order"]), len(self.a["quad_order"]), len(self.a["plane_order"]), len(self.a["lights"]))
 
     def c_struct(self):
+        """The `rtb200_scene` view of the arrays (pointers into them; built once, the arrays are never rebound)."""
+        if getattr(self, "_c_struct", None) is not None:
+            return self._c_struct
         a = self.a
         s = Scene()
         s.n_triangles, s.n_quadrics, s.n_planes, s.n_lights = self.counts
@@ -109,6 +112,7 @@ class PackedScene:
             setattr(s, k, a[k].ctypes.data_as(_ip))
         s.materials = a["materials"].ctypes.data_as(C.POINTER(Material))
         s.lights = a["lights"].ctypes.data_as(C.POINTER(Light))
+        self._c_struct = s
         return s
 
     def nbytes(self):

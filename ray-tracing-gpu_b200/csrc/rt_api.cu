@@ -718,8 +718,13 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
     int rows_per_chunk = (int)((MAX_CHUNK_SAMPLES / (unsigned)fp.LW) / (16u * k)) * 16 * k;
     if (rows_per_chunk < 16 * k) rows_per_chunk = 16 * k;
     if (rows_per_chunk > local_LH) rows_per_chunk = ((local_LH + 16 * k - 1) / (16 * k)) * 16 * k;
-    if (ctx->host_f32 || ctx->host_rgba8) {
-        // overlapped read-back: about 8 chunks per frame, never smaller than 64 pixel rows
+    // overlapped read-back (host pointers given).  The copy engine is the slower side (config 2: 12 pixels/ns
+    // over PCIe against 24 rendered), so what counts is how soon the FIRST copy starts and how few copies there
+    // are: frames that are one kernel per chunk use a doubling schedule -- 64 rows, 128, 256, ... --, frames
+    // with a level loop per chunk about 8 equal chunks, never smaller than 64 pixel rows.
+    const bool overlap = ctx->host_f32 || ctx->host_rgba8;
+    const bool doubling = overlap && children == 0;
+    if (overlap && !doubling) {
         int want = (((local_rows + 7) / 8 + 15) / 16) * 16;
         if (want < 64) want = 64;
         if (want * k < rows_per_chunk) rows_per_chunk = want * k;
@@ -748,8 +753,9 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
     unsigned max_level_seen = 0, chunks = 0;
     std::vector<unsigned> seen_rays(1, 0);
 
-    for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunks) {
-        const int rows = std::min(rows_per_chunk, local_LH - ly0);
+    int step_rows = doubling ? std::min(64 * k, rows_per_chunk) : rows_per_chunk;
+    for (int ly0 = 0, rows = 0; ly0 < local_LH; ly0 += rows, ++chunks, step_rows = doubling ? std::min(2 * step_rows, rows_per_chunk) : step_rows) {
+        rows = std::min(step_rows, local_LH - ly0);
         if (children > 0) CU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, ctx->stream));
         std::vector<int> n_rays, n_links;
         n_rays.push_back(rows * fp.LW);
@@ -788,7 +794,7 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
             p.direct = direct ? 1 : 0;
             p.cull = (fr->flags & RTB200_F_EXACT_FP) ? 0 : 1;
             p.fb_f32 = ctx->out_f32_dev; p.fb_rgba8 = ctx->out_rgba8_dev;
-            if (direct && ctx->peer_cur && ly0 + rows_per_chunk >= local_LH) {
+            if (direct && ctx->peer_cur && ly0 + rows >= local_LH) {
                 // the frame's last producing kernel carries the completion signal to rank 0 itself
                 const PeerFrame* pf = static_cast<const PeerFrame*>(ctx->peer_cur);
                 if (pf->flag) { p.peer_flag = pf->flag; p.peer_done = pf->done; p.peer_seq = pf->seq; ctx->peer_signalled = true; }
