@@ -437,6 +437,17 @@ int comm_peer_begin(rtb200_ctx* c, int W, int H, bool want_f32, bool ack_previou
     return RTB200_OK;
 }
 
+// ranks > 0 that asked comm_peer_begin not to wait (wait_in_kernel) and then do not use a kernel for it
+int comm_peer_wait_ack(rtb200_ctx* c, const PeerFrame& pf, cudaStream_t s)
+{
+    if (!pf.ack) return RTB200_OK;
+    if (stream_wait_value32()(s, (unsigned long long)(uintptr_t)pf.ack, pf.ack_min, 0u /* GEQ, cyclic */) != 0) {
+        c->last_error = "cuStreamWaitValue32 (ack) failed";
+        return RTB200_E_CUDA;
+    }
+    return RTB200_OK;
+}
+
 int comm_peer_signal(rtb200_ctx* c, const PeerFrame& pf, cudaStream_t s)
 {
     if (!pf.flag) return RTB200_OK;

@@ -158,6 +158,7 @@ struct PeerFrame {
 // ack_previous (rank 0): tell the peers that the frame before this one is consumed.  wait_in_kernel (ranks > 0): the
 // caller's first kernel waits for the acknowledgement itself (LevelParams::peer_ack) instead of the stream.
 int  comm_peer_begin(rtb200_ctx* c, int W, int H, bool want_f32, bool ack_previous, bool wait_in_kernel, PeerFrame* pf, cudaStream_t s);
+int  comm_peer_wait_ack(rtb200_ctx* c, const PeerFrame& pf, cudaStream_t s);  // ranks > 0: the stream waits for pf.ack >= pf.ack_min
 int  comm_peer_signal(rtb200_ctx* c, const PeerFrame& pf, cudaStream_t s);   // ranks > 0, when no kernel signalled by itself
 int  comm_peer_wait(rtb200_ctx* c, const PeerFrame& pf, cudaStream_t s);     // rank 0: s waits for every peer's word
 int  comm_peer_ack(rtb200_ctx* c, unsigned int seq, cudaStream_t s);         // rank 0: frames <= seq are consumed

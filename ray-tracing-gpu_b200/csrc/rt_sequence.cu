@@ -10,14 +10,17 @@
 //   * with a host destination the RGBA8 frames alternate between two device buffers and travel to
 //     the host on the copy stream while the next frame renders (PCIe and the SMs overlap);
 //   * several GPUs (peer frame, rt_comm.cu): every rank enqueues its kernels without waiting on the
-//     host; each kernel stores into rank 0's frame half and signals by itself, rank 0's COPY stream
-//     waits for the peers' words, copies the frame out and acknowledges, so neither the signalling nor
-//     the read-back is on any rank's kernel-to-kernel path (peers run at most two frames ahead);
+//     host; a peer's side stream pushes each finished frame into rank 0's frame half with the copy
+//     engine (one 2-D copy of its bands) and writes the completion word, rank 0's side stream waits
+//     for the peers' words, copies the frame out and acknowledges, so neither the transfer nor the
+//     signalling nor the read-back is on any rank's kernel-to-kernel path (peers run at most two
+//     frames ahead);
 //   * per-frame counters live in per-frame slots and come back in one copy at the end.
 // Anything else (secondary rays, supersampling, streamed / LBVH paths, NCCL-gather fallback) is
 // rendered frame by frame through rtb200_render -- same results, no pipelining.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -94,9 +97,17 @@ extern "C" int rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frame
     const size_t lpx = (size_t)std::max(local_rows, 1) * fp0.W;
     if ((e = ctx->seq_stats.ensure(stat_bytes * (size_t)n_frames)) != cudaSuccess) return set_cuda_error(ctx, e, "sequence counters");
     if ((e = ctx->seq_host.ensure(stat_bytes * (size_t)n_frames)) != cudaSuccess) return set_cuda_error(ctx, e, "sequence counters (host)");
+    // Several GPUs, how a peer's rows reach rank 0 in a pipelined path.  "copy" (default): the kernel writes a local
+    // compact frame and the copy engine pushes it on the side stream while the next frame renders -- ONE 2-D copy, a
+    // band of rows is one contiguous piece on both sides -- followed by the completion word.  "store"
+    // (RTB200_PEER_PUSH=store, and what synchronous rtb200_render calls do): the kernel writes its rows over NVLink
+    // itself, 32 bytes at a time; rank 0 then takes in at most ~400 GB/s, which 8 GPUs on config 2 exceed
+    // (0.145 ms per frame against 0.093 with the copy engine's large packets; 4 GPUs 0.090 / 0.083; 2 GPUs 0.090 / 0.086).
+    bool push_copy = multi && ctx->rank != 0;
+    if (const char* pp = getenv("RTB200_PEER_PUSH")) push_copy = push_copy && pp[0] != 's';
     uchar4* target[2] = {nullptr, nullptr};
-    if (multi) { /* the frame halves of rank 0, chosen per frame by comm_peer_begin */ }
-    else if (out_rgba8) {
+    if (multi && !push_copy) { /* the frame halves of rank 0, chosen per frame by comm_peer_begin */ }
+    else if (out_rgba8 || push_copy) {
         for (int b = 0; b < 2; ++b) {
             if ((e = ctx->seq_fb[b].ensure(lpx * 4)) != cudaSuccess) return set_cuda_error(ctx, e, "sequence frame buffer");
             target[b] = ctx->seq_fb[b].as<uchar4>();
@@ -119,11 +130,12 @@ extern "C" int rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frame
             if (prc != RTB200_OK || !pf.rgba8) return prc != RTB200_OK ? prc : seq_fail(ctx, RTB200_E_STATE, "peer frame lost inside a sequence");
         }
         const int b = multi ? (int)(pf.seq & 1u) : (i & 1);
+        const bool push = push_copy && pf.flag;
         const bool consumer = out_rgba8 && (!multi || ctx->rank == 0);
         FrameParams fp;
         fill_frame_params(&frames[i], ctx->n_ranks, ctx->rank, fp);
         fp.secondary = 0;
-        fp.fb_global = multi ? 1 : 0;
+        fp.fb_global = (multi && !push) ? 1 : 0;
         LevelParams p;
         memset(&p, 0, sizeof p);
         p.f = fp;
@@ -134,14 +146,34 @@ extern "C" int rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frame
         p.direct = 1;
         p.cull = (frames[i].flags & RTB200_F_EXACT_FP) ? 0 : 1;
         p.fb_f32 = nullptr;                                   // a sequence delivers RGBA8 only
-        p.fb_rgba8 = multi ? static_cast<uchar4*>(pf.rgba8) : target[b];
-        if (multi && pf.flag && local_rows > 0) {             // wait for the half, store, signal: all in the one kernel
+        p.fb_rgba8 = (multi && !push) ? static_cast<uchar4*>(pf.rgba8) : target[b];
+        if (multi && pf.flag && local_rows > 0 && !push) {    // wait for the half, store, signal: all in the one kernel
             p.peer_flag = pf.flag; p.peer_done = pf.done; p.peer_seq = pf.seq;
             p.peer_ack = pf.ack; p.peer_ack_min = pf.ack_min;
         }
-        if (consumer && i >= 2) QCU(cudaStreamWaitEvent(ctx->stream, copied[b], 0));   // buffer b is free again
+        if ((consumer || push) && i >= 2) QCU(cudaStreamWaitEvent(ctx->stream, copied[b], 0));   // buffer b is free again
         if (local_rows > 0) QCU(launch_resident_level(p, exact, ctx->sm_count, ctx->stream));
-        else if (multi && pf.flag) { const int rc = comm_peer_signal(ctx, pf, ctx->stream); if (rc != RTB200_OK) return rc; }
+        else if (multi && pf.flag && !push) { const int rc = comm_peer_signal(ctx, pf, ctx->stream); if (rc != RTB200_OK) return rc; }
+        if (push) {
+            // side stream: wait for the kernel and for rank 0 to have let go of the half, push the bands, signal
+            QCU(cudaEventRecord(done[b], ctx->stream));
+            QCU(cudaStreamWaitEvent(ctx->copy_stream, done[b], 0));
+            int rc = comm_peer_wait_ack(ctx, pf, ctx->copy_stream);
+            if (rc != RTB200_OK) return rc;
+            const size_t row_bytes = 4 * (size_t)fp0.W, band_bytes = (size_t)band * row_bytes;
+            const int n_full = local_rows / band, tail = local_rows - n_full * band;
+            unsigned char* dst = static_cast<unsigned char*>(pf.rgba8);
+            const unsigned char* src = reinterpret_cast<const unsigned char*>(target[b]);
+            if (n_full > 0)
+                QCU(cudaMemcpy2DAsync(dst + (size_t)ctx->rank * band_bytes, (size_t)ctx->n_ranks * band_bytes, src, band_bytes,
+                                      band_bytes, (size_t)n_full, cudaMemcpyDeviceToDevice, ctx->copy_stream));
+            if (tail > 0)
+                QCU(cudaMemcpyAsync(dst + ((size_t)n_full * ctx->n_ranks + ctx->rank) * band_bytes, src + (size_t)n_full * band_bytes,
+                                    (size_t)tail * row_bytes, cudaMemcpyDeviceToDevice, ctx->copy_stream));
+            rc = comm_peer_signal(ctx, pf, ctx->copy_stream);
+            if (rc != RTB200_OK) return rc;
+            QCU(cudaEventRecord(copied[b], ctx->copy_stream));
+        }
         if (consumer || (multi && ctx->rank == 0)) {
             // side stream: (several GPUs: wait for the peers' words,) copy the frame out, acknowledge
             QCU(cudaEventRecord(done[b], ctx->stream));
