@@ -166,8 +166,13 @@ const char* rtb200_error_string(int status);
 const char* rtb200_last_error(const rtb200_ctx* ctx);
 
 /* --- scene -------------------------------------------------------------------------------- */
-/* Validates, packs to the device layout and uploads (one pinned staging buffer, one async copy). */
+/* Validates (see rtb200_validate_scene), packs to the device layout and uploads: small scenes are packed by the
+ * host into one pinned staging buffer (one async copy), large meshes are uploaded raw and packed by a kernel. */
 int  rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* scene);
+/* The checks rtb200_set_scene applies, without a context or a GPU: counts, null arrays, material indices,
+ * and the three order arrays (each strictly increasing, together a permutation of 0..N-1 = the insertion
+ * indices of CScene::m_Surfaces, Scene.cpp:107).  *why (may be NULL) receives a static string. */
+int  rtb200_validate_scene(const rtb200_scene* scene, const char** why);
 /* Optional: GPU-built LBVH over the triangles of the current scene (Morton codes, radix sort,
  * Karras hierarchy, bottom-up refit).  Planes and quadrics stay in the brute-force side list. */
 int  rtb200_build_bvh(rtb200_ctx* ctx);

@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "librtb200.so")
 
 EXPORTS = [
     "rtb200_abi_version", "rtb200_create", "rtb200_destroy", "rtb200_error_string", "rtb200_last_error",
-    "rtb200_set_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_render_sequence", "rtb200_read_frame",
+    "rtb200_set_scene", "rtb200_validate_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_render_sequence", "rtb200_read_frame",
     "rtb200_trace_nearest", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init", "rtb200_band_map",
     "rtb200_host_alloc", "rtb200_host_free", "rtb200_measure_fp32_peak", "rtb200_device_info",
     "rtb200_timer_mark", "rtb200_timer_elapsed",
@@ -67,10 +67,19 @@ def lib():
         L.rtb200_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.rtb200_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_char_p, C.c_int]
         L.rtb200_band_map.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.POINTER(C.c_int)]
+        L.rtb200_validate_scene.argtypes = [vp, C.POINTER(C.c_char_p)]
         L.rtb200_timer_mark.argtypes = [vp, C.c_int]
         L.rtb200_timer_elapsed.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_double)]
         _lib = L
     return _lib
+
+
+def validate_scene(ps):
+    """rtb200_validate_scene on a PackedScene: (ok, reason).  Needs no GPU."""
+    why = C.c_char_p()
+    s = ps.c_struct()
+    rc = lib().rtb200_validate_scene(C.byref(s), C.byref(why))
+    return rc == 0, (why.value or b"").decode()
 
 
 def band_map(height, band_rows, n_ranks, rank):

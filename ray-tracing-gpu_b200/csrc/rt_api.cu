@@ -237,6 +237,29 @@ static const char* validate_orders(const rtb200_scene* s, long long N)
     return nullptr;
 }
 
+// Everything rtb200_set_scene refuses, as text (null = the scene is acceptable).  Pure host code.
+static const char* scene_problem(const rtb200_scene* s)
+{
+    if (!s) return "null scene";
+    const int T = s->n_triangles, Q = s->n_quadrics, P = s->n_planes, L = s->n_lights, M = s->n_materials;
+    if (T < 0 || Q < 0 || P < 0 || L < 0 || M < 0) return "negative count";
+    const long long N = (long long)T + Q + P;
+    if (N > 0x7fffff00ll) return "too many surfaces";
+    if ((T && (!s->tri_points || !s->tri_normal || !s->tri_material || !s->tri_order)) ||
+        (Q && (!s->quad_coef || !s->quad_material || !s->quad_order)) ||
+        (P && (!s->plane_coef || !s->plane_material || !s->plane_order)) ||
+        (M && !s->materials) || (L && !s->lights) || (N && !M))
+        return "null array with non-zero count";
+    return validate_orders(s, N);
+}
+
+extern "C" int rtb200_validate_scene(const rtb200_scene* scene, const char** why)
+{
+    const char* w = scene_problem(scene);
+    if (why) *why = w ? w : "";
+    return w ? RTB200_E_ARG : RTB200_OK;
+}
+
 // memcpy of a large array into the pinned staging buffer on a few threads (one core moves ~10 GB/s)
 static void parallel_copy(void* dst, const void* src, size_t bytes)
 {
@@ -256,15 +279,9 @@ static void parallel_copy(void* dst, const void* src, size_t bytes)
 extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
 {
     if (!ctx || !s) return RTB200_E_ARG;
+    if (const char* why = scene_problem(s)) return fail(ctx, RTB200_E_ARG, why);
     const int T = s->n_triangles, Q = s->n_quadrics, P = s->n_planes, L = s->n_lights, M = s->n_materials;
-    if (T < 0 || Q < 0 || P < 0 || L < 0 || M < 0) return fail(ctx, RTB200_E_ARG, "negative count");
     const long long N = (long long)T + Q + P;
-    if (N > 0x7fffff00ll) return fail(ctx, RTB200_E_ARG, "too many surfaces");
-    if ((T && (!s->tri_points || !s->tri_normal || !s->tri_material || !s->tri_order)) ||
-        (Q && (!s->quad_coef || !s->quad_material || !s->quad_order)) ||
-        (P && (!s->plane_coef || !s->plane_material || !s->plane_order)) ||
-        (M && !s->materials) || (L && !s->lights) || (N && !M))
-        return fail(ctx, RTB200_E_ARG, "null array with non-zero count");
     CU(cudaSetDevice(ctx->device));
     bvh_invalidate(ctx);                         // an LBVH belongs to the scene it was built from
     ++ctx->scene_serial;
@@ -292,7 +309,6 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
     int pack_min = 2048;
     if (const char* pm = getenv("RTB200_PACK_ON_DEVICE_MIN")) pack_min = atoi(pm);
     if (T >= pack_min && T > 0) {
-        if (const char* why = validate_orders(s, N)) return fail(ctx, RTB200_E_ARG, why);
         // staging: [materials + lights][quad + plane records][quad centred forms][raw triangle arrays]
         const size_t ml_bytes = (size_t)rl.bytes - (size_t)rl.off_mat;
         const size_t qp_bytes = sizeof(QuadRec) * (size_t)Q + sizeof(PlaneRec) * (size_t)P;
@@ -386,22 +402,12 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
 
     // ---- unified list: slot = insertion order ------------------------------------------------
     SurfRec* surf = reinterpret_cast<SurfRec*>(h);
-    std::vector<unsigned char> seen((size_t)N, 0);
-    auto claim = [&](int order, int mat, int prev) -> bool {
-        if (order < 0 || order >= N || seen[(size_t)order] || order <= prev) return false;
-        if (mat < 0 || mat >= M) return false;
-        seen[(size_t)order] = 1;
-        return true;
-    };
     TriRec* tri = reinterpret_cast<TriRec*>(h + off_tri);
     float4* trn = reinterpret_cast<float4*>(h + off_trn);
-    int prev = -1;
     for (int i = 0; i < T; ++i) {
         const float* p = s->tri_points + 9 * (size_t)i;
         const float* n = s->tri_normal + 3 * (size_t)i;
         const int ord = s->tri_order[i], mat = s->tri_material[i];
-        if (!claim(ord, mat, prev)) return fail(ctx, RTB200_E_ARG, "tri_order/tri_material invalid");
-        prev = ord;
         // edges: the same binary32 subtractions CTriangle::Intersection performs per test
         const float e1x = p[3] - p[0], e1y = p[4] - p[1], e1z = p[5] - p[2];
         const float e2x = p[6] - p[0], e2y = p[7] - p[1], e2z = p[8] - p[2];
@@ -417,12 +423,9 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
     }
     for (int i = T; i < Tpad; ++i) tri[i].a.w = i2f(0x7fffffff);   // zero edges: det = 0, never hit
     QuadRec* quad = reinterpret_cast<QuadRec*>(h + off_quad);
-    prev = -1;
     for (int i = 0; i < Q; ++i) {
         const float* c = s->quad_coef + 10 * (size_t)i;
         const int ord = s->quad_order[i], mat = s->quad_material[i];
-        if (!claim(ord, mat, prev)) return fail(ctx, RTB200_E_ARG, "quad_order/quad_material invalid");
-        prev = ord;
         SurfRec& r = surf[ord];
         r.r0 = make_float4(c[0], c[1], c[2], i2f(SURF_QUADRIC));
         r.r1 = make_float4(c[3], c[4], c[5], i2f(mat));
@@ -435,12 +438,9 @@ extern "C" int rtb200_set_scene(rtb200_ctx* ctx, const rtb200_scene* s)
     ctx->h_quad_r3.resize((size_t)Q);
     for (int i = 0; i < Q; ++i) ctx->h_quad_r3[(size_t)i] = surf[s->quad_order[i]].r3;
     PlaneRec* plane = reinterpret_cast<PlaneRec*>(h + off_plane);
-    prev = -1;
     for (int i = 0; i < P; ++i) {
         const float* c = s->plane_coef + 4 * (size_t)i;
         const int ord = s->plane_order[i], mat = s->plane_material[i];
-        if (!claim(ord, mat, prev)) return fail(ctx, RTB200_E_ARG, "plane_order/plane_material invalid");
-        prev = ord;
         SurfRec& r = surf[ord];
         r.r0 = make_float4(c[0], c[1], c[2], i2f(SURF_PLANE));
         r.r1 = make_float4(c[3], 0.f, 0.f, i2f(mat));
