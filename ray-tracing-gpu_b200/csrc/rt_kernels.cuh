@@ -34,6 +34,7 @@ struct LevelParams {
     unsigned long long* stats;     // [RT_STAT_SLOTS][ST_COUNT]
     // direct resolve (level 0, spp 1, no secondary rays): the level kernel writes the frame itself
     int     cull;                  // warp-vote culling of bounded quadrics / triangles (0 with RTB200_F_EXACT_FP)
+    int     pre_table;             // set by the launcher: shared memory holds room for the primary-ray culling table
     int     direct;
     float*  fb_f32;                // [local rows][W][3]
     uchar4* fb_rgba8;              // [local rows][W]

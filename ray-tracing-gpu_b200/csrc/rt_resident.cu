@@ -28,6 +28,9 @@ struct SceneView {                 // resident blob seen through shared (or glob
     const LightRec* light;
     int n_surf, n_light;
     bool cull;                     // warp-vote culling allowed (off with RTB200_F_EXACT_FP)
+    // primary rays all start at the camera: the origin-dependent half of quadric_miss, once per CTA and surface
+    const float4* pre_qo;          // q * (c - cam) | e = (c - cam).q.(c - cam)      (null: not available)
+    const float*  pre_lim;         // rhs * 1.05 + 2e-5 * M(cam)
 };
 
 // Conservative "this ray cannot hit the quadric" test for quadrics rtb200_set_scene could write in
@@ -53,6 +56,24 @@ RT_DEV bool quadric_miss(V3 o, V3 d, float4 r0, float K, float4 r3)
     return a > 1.0e-20f && (fmaf(a, e, -b * b) > a * lim || (b < 0.f && e > lim));
 }
 
+// the same test with the origin-dependent terms taken from the per-CTA table (primary rays)
+RT_DEV void quadric_miss_origin_terms(V3 o, float4 r0, float K, float4 r3, float4& qo_e, float& lim)
+{
+    const V3 q = mk3(r0.x, r0.y, r0.z);
+    const V3 oc = mk3(r3.x - o.x, r3.y - o.y, r3.z - o.z);
+    const V3 qo = mk3(q.x * oc.x, q.y * oc.y, q.z * oc.z);
+    const float M = fmaf(q.x * o.x, o.x, fmaf(q.y * o.y, o.y, fmaf(q.z * o.z, o.z, r3.w + K)));
+    qo_e = make_float4(qo.x, qo.y, qo.z, dot3<false>(qo, oc));
+    lim = fmaf(r3.w, 1.05f, 2.0e-5f * M);
+}
+RT_DEV bool quadric_miss_pre(V3 d, float4 r0, float4 qo_e, float lim)
+{
+    const V3 qd = mk3(r0.x * d.x, r0.y * d.y, r0.z * d.z);
+    const float a = dot3<false>(qd, d);
+    const float b = fmaf(qo_e.z, d.z, fmaf(qo_e.y, d.y, qo_e.x * d.x));
+    return a > 1.0e-20f && (fmaf(a, qo_e.w, -b * b) > a * lim || (b < 0.f && qo_e.w > lim));
+}
+
 // distance of surface record `k` along (o,d); quadrics also report the A==0 branch
 //
 // Culling with warp votes (k, hence the type, is uniform over the warp): a centred-form quadric
@@ -60,7 +81,7 @@ RT_DEV bool quadric_miss(V3 o, V3 d, float4 r0, float K, float4 r3)
 // det/u filter of rt_cull.cuh for, is skipped by the whole warp -- the reference sequence below
 // only runs where its result can be a hit, so every value that is kept is still the reference's.
 template <bool E> RT_DEV float surface_t(const SurfRec* __restrict__ s, int k, V3 o, V3 d, bool active, bool cull,
-                                         int& type, bool& linear)
+                                         int& type, bool& linear, const float4* pre_qo = nullptr, const float* pre_lim = nullptr)
 {
     const float4 r0 = s[k].r0, r1 = s[k].r1, r2 = s[k].r2;
     type = __float_as_int(r0.w);
@@ -72,7 +93,10 @@ template <bool E> RT_DEV float surface_t(const SurfRec* __restrict__ s, int k, V
     if (type == SURF_QUADRIC) {
         if (cull) {
             const float4 r3 = s[k].r3;                 // centred form (c, rhs); rhs <= 0: not cullable
-            if (r3.w > 0.f && !__any_sync(0xffffffffu, active && !quadric_miss(o, d, r0, r2.w, r3))) return -1.0f;
+            if (r3.w > 0.f) {
+                const bool may = pre_qo ? !quadric_miss_pre(d, r0, pre_qo[k], pre_lim[k]) : !quadric_miss(o, d, r0, r2.w, r3);
+                if (!__any_sync(0xffffffffu, active && may)) return -1.0f;
+            }
         }
         Quadric q = { r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r2.x, r2.y, r2.z, r2.w };
         return quadric_t<E>(o, d, q, linear);
@@ -81,12 +105,14 @@ template <bool E> RT_DEV float surface_t(const SurfRec* __restrict__ s, int k, V
 }
 
 // nearest hit: the loop of Scene.cpp:1710-1715 (strict <, so the first surface wins a tie)
-template <bool E> RT_DEV void nearest_hit(const SceneView& sv, bool active, V3 o, V3 d, float& best_t, int& best_k, bool& best_lin)
+template <bool E> RT_DEV void nearest_hit(const SceneView& sv, bool active, V3 o, V3 d, float& best_t, int& best_k, bool& best_lin,
+                                          bool from_camera = false)
 {
     best_t = -1.0f; best_k = -1; best_lin = false;
+    const float4* pre_qo = from_camera ? sv.pre_qo : nullptr;
     for (int k = 0; k < sv.n_surf; ++k) {
         int type; bool lin;
-        float t = surface_t<E>(sv.surf, k, o, d, active, sv.cull, type, lin);
+        float t = surface_t<E>(sv.surf, k, o, d, active, sv.cull, type, lin, pre_qo, sv.pre_lim);
         if (t > RT_EPS && (t < best_t || best_t < 0.f)) { best_t = t; best_k = k; best_lin = lin; }
     }
 }
@@ -210,8 +236,26 @@ k_resident_level(const __grid_constant__ LevelParams p)
     sv.mat   = reinterpret_cast<const MatRec*>(smem + p.rl.off_mat);
     sv.light = reinterpret_cast<const LightRec*>(smem + p.rl.off_light);
     sv.n_surf = p.rl.n_surf; sv.n_light = p.rl.n_light; sv.cull = p.cull != 0;
+    sv.pre_qo = nullptr; sv.pre_lim = nullptr;
+    if (PRIMARY && p.pre_table && sv.cull) {
+        // every primary ray starts at the camera: the origin-dependent terms of the quadric vote, once per CTA
+        float4* tq = reinterpret_cast<float4*>(smem + ((p.rl.bytes + 15) & ~15));
+        float*  tl = reinterpret_cast<float*>(tq + sv.n_surf);
+        const V3 cam = mk3(f.cam_pos[0], f.cam_pos[1], f.cam_pos[2]);
+        for (int k = tid; k < sv.n_surf; k += RES_THREADS) {
+            const float4 r0 = sv.surf[k].r0, r3 = sv.surf[k].r3;
+            float4 qe = make_float4(0.f, 0.f, 0.f, 0.f); float lim = 0.f;
+            if (__float_as_int(r0.w) == SURF_QUADRIC && r3.w > 0.f) quadric_miss_origin_terms(cam, r0, sv.surf[k].r2.w, r3, qe, lim);
+            tq[k] = qe; tl[k] = lim;
+        }
+        __syncthreads();
+        sv.pre_qo = tq; sv.pre_lim = tl;
+    }
     unsigned int n_shadow = 0, n_tests = 0, n_refl_st = 0, n_refr_st = 0, n_nan = 0;
 
+    // tile walk without a division per tile: (tx, ty) advance by the grid stride
+    const int step_x = (int)(gridDim.x % (unsigned)tiles_x), step_y = (int)(gridDim.x / (unsigned)tiles_x);
+    int tile_x = PRIMARY ? (int)(blockIdx.x % (unsigned)tiles_x) : 0, tile_y = PRIMARY ? (int)(blockIdx.x / (unsigned)tiles_x) : 0;
     for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
     // ---- this thread's ray ------------------------------------------------------------------
     V3 o, d;
@@ -220,7 +264,9 @@ k_resident_level(const __grid_constant__ LevelParams p)
     int  self;                              // index of this ray in its level's colour buffer
     int  pix_x = 0, pix_y = 0;
     if (PRIMARY) {
-        const int tx = blk % tiles_x, ty = blk / tiles_x;
+        const int tx = tile_x, ty = tile_y;
+        tile_x += step_x; tile_y += step_y;
+        if (tile_x >= tiles_x) { tile_x -= tiles_x; ++tile_y; }
         const int lx = (tx << 4) + ((warp & 1) << 3) + (lane & 7);
         const int cy = (ty << 4) + ((warp >> 1) << 2) + (lane >> 3);   // row inside the chunk
         const int ly = p.chunk_ly0 + cy;                                 // local lattice row
@@ -238,7 +284,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
 
     // ---- nearest hit (Scene.cpp:1705-1720) -----------------------------------------------
     float t; int k; bool lin;
-    nearest_hit<E>(sv, valid, o, d, t, k, lin);
+    nearest_hit<E>(sv, valid, o, d, t, k, lin, PRIMARY);
     const bool hit = valid && k >= 0;
 
     float cr = f.background[0], cg = f.background[1], cb = f.background[2];
@@ -440,7 +486,7 @@ __global__ void __launch_bounds__(128) k_query_nearest(DeviceScene s, int n, con
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = i < n;
-    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light; sv.cull = cull;
+    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light; sv.cull = cull; sv.pre_qo = nullptr; sv.pre_lim = nullptr;
     V3 o = valid ? ld3(o3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
     V3 d = valid ? ld3(d3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
     float t; int k; bool lin;
@@ -456,7 +502,7 @@ __global__ void __launch_bounds__(128) k_query_shadow(DeviceScene s, int n, cons
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool valid = i < n;
-    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light; sv.cull = cull;
+    SceneView sv; sv.surf = s.surf; sv.mat = s.mat; sv.light = s.light; sv.n_surf = s.rl.n_surf; sv.n_light = s.rl.n_light; sv.cull = cull; sv.pre_qo = nullptr; sv.pre_lim = nullptr;
     V3 P = valid ? ld3(p3 + 3 * (size_t)i) : mk3(0.f, 0.f, 0.f);
     V3 L = valid ? ld3(l3 + 3 * (size_t)i) : mk3(1.f, 0.f, 0.f);
     V3 Ld = sub3<E>(L, P);
@@ -472,6 +518,8 @@ __global__ void __launch_bounds__(128) k_query_shadow(DeviceScene s, int n, cons
 // launchers
 // ---------------------------------------------------------------------------------------
 size_t resident_smem_bytes(const ResidentLayout& rl) { return (size_t)rl.bytes; }
+// blob + the per-CTA table of primary-ray culling terms (20 bytes per surface)
+static size_t resident_smem_with_table(const ResidentLayout& rl) { return (((size_t)rl.bytes + 15) & ~(size_t)15) + 20 * (size_t)rl.n_surf + 16; }
 
 cudaError_t resident_prepare(size_t max_smem_bytes)
 {
@@ -499,9 +547,12 @@ static cudaError_t launch_chain(void (*kernel)(P), dim3 grid, unsigned block, si
     return cudaLaunchKernelEx(&cfg, kernel, p);
 }
 
-cudaError_t launch_resident_level(const LevelParams& p, bool exact, int sm_count, cudaStream_t st)
+cudaError_t launch_resident_level(const LevelParams& p_in, bool exact, int sm_count, cudaStream_t st)
 {
-    const size_t smem = resident_smem_bytes(p.rl);
+    LevelParams p = p_in;
+    // the table rides along while the scene is small (it must not cost a resident CTA)
+    p.pre_table = (p.level == 0 && p.rl.bytes <= 16 * 1024) ? 1 : 0;
+    const size_t smem = p.pre_table ? resident_smem_with_table(p.rl) : resident_smem_bytes(p.rl);
     if (g_resident_ctas_per_sm <= 0) {
         int n = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_resident_level<true, true>, RES_THREADS, smem) != cudaSuccess || n <= 0) n = 2;
