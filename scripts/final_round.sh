@@ -5,6 +5,8 @@
 TAG=${1:-r1f}
 OUT=gpurun_out
 set -x
+timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -5 > $OUT/${TAG}_tests.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/${TAG}_smoke.log 2>&1
 timeout 400 python bench.py > $OUT/${TAG}_c2.json 2> $OUT/${TAG}_c2.err || exit 1
 timeout 300 python bench.py --impl reference > $OUT/${TAG}_c2_reference.json 2> $OUT/${TAG}_c2_reference.err
 timeout 400 python bench.py --workload c3 > $OUT/${TAG}_c3.json 2> $OUT/${TAG}_c3.err

@@ -120,7 +120,7 @@ def test_coplanar_duplicates_lowest_order_wins(rt, renderer, synth):
     assert all(first_copy[int(perm[i] % 1500)] == int(i) for i in hit[:5000])
 
 
-@pytest.mark.parametrize("n_tris", [1, 3, 4, 5, 9])
+@pytest.mark.parametrize("n_tris", [1, 3, 4, 5, 8, 9, 17])
 def test_tiny_scenes(rt, renderer, synth, n_tris):
     ps = synth.soup(n_tris, 2, 1, seed=40 + n_tris, radius=120.0)
     renderer.set_scene(ps)
@@ -245,7 +245,8 @@ def test_bounded_quadrics_in_tree_equal_linear_scan(rt, renderer, synth, n_tris,
     a, a8, st_a = renderer.render(fr_b)
     b, b8, st_b = renderer.render(fr_v)
     assert bits_equal(a, b) and np.array_equal(a8, b8)
-    if far < 1000:        # (boxes refitted for origins 20000 away are inflated until little is culled: still exact)
+    if far < 1000 and scale == 1.0:   # (origins 20000 away, or a camera 10^5 radii away from a tiny scene: the boxes
+                                      #  are inflated until little is culled -- still exact)
         assert st_b.tests_quadric < st_a.tests_quadric / 2                  # the tree really culls them
 
 
