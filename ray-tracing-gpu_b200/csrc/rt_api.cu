@@ -120,7 +120,7 @@ void rtb200_destroy(rtb200_ctx* ctx)
     ctx->scene_buf.release(); ctx->stage.release(); ctx->raw_buf.release();
     ctx->c0.release(); ctx->fb_f32.release(); ctx->fb_rgba8.release(); ctx->stats.release(); ctx->counters.release();
     ctx->full_f32.release(); ctx->full_rgba8.release(); ctx->h_small.release();
-    ctx->seq_fb[0].release(); ctx->seq_fb[1].release(); ctx->seq_stats.release(); ctx->seq_host.release(); ctx->h_levels.release();
+    ctx->seq_fb[0].release(); ctx->seq_fb[1].release(); ctx->seq_stats.release(); ctx->seq_host.release(); ctx->h_levels.release(); ctx->tail_dev.release(); ctx->tail_host.release();
     for (auto& l : ctx->levels) { l.od0.release(); l.od1.release(); l.colour.release(); l.links.release(); }
     ctx->q_in0.release(); ctx->q_in1.release(); ctx->q_out0.release(); ctx->q_out1.release(); ctx->q_out2.release();
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -607,6 +607,32 @@ static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const 
         if ((e = cur.links.ensure(sizeof(int4) * cap[(size_t)l])) != cudaSuccess) return set_cuda_error(ctx, e, "links");
     }
 
+    // Deep levels that held only a few hundred rays last time are walked by ONE single-CTA launch (tail mode of the
+    // level kernel, rt_resident.cu) instead of one launch each: tail_from = first such level, 0 = none.
+    int tail_from = 0;
+    if (known && !getenv("RTB200_NO_TAIL_LEVELS")) {
+        auto rays_at = [&](int l) { return (size_t)l < g.rays.size() ? g.rays[(size_t)l] : 0u; };   // beyond the history: empty
+        int t = last + 1;
+        while (t - 1 >= 2 && rays_at(t - 1) <= 512u) --t;
+        if (last - t + 1 >= 2 && last - t + 1 <= RT_TAIL_FOLD_MAX) tail_from = t;
+    }
+    if (tail_from) {
+        const size_t nt = (size_t)(last - tail_from + 1);
+        if ((e = ctx->tail_dev.ensure(sizeof(TailLevel) * nt)) != cudaSuccess) return set_cuda_error(ctx, e, "tail table");
+        if ((e = ctx->tail_host.ensure(sizeof(TailLevel) * nt)) != cudaSuccess) return set_cuda_error(ctx, e, "tail table (host)");
+        TailLevel* tv = ctx->tail_host.as<TailLevel>();
+        for (int l = tail_from; l <= last; ++l) {
+            TailLevel& v = tv[l - tail_from];
+            LevelBuf& cur = ctx->levels[(size_t)l];
+            LevelBuf& nxt = ctx->levels[(size_t)l + 1];
+            v.in_od0 = cur.od0.as<float4>(); v.in_od1 = cur.od1.as<float4>(); v.in_colour = cur.colour.as<float4>();
+            v.out_od0 = nxt.od0.as<float4>(); v.out_od1 = nxt.od1.as<float4>(); v.links = cur.links.as<int4>();
+            v.level = l; v.in_cap = (int)cap[(size_t)l]; v.spawn = l < max_b ? 1 : 0;
+            v.out_cap = (l == last) ? 0u : (unsigned)cap[(size_t)l + 1];
+        }
+        CU(cudaMemcpyAsync(ctx->tail_dev.p, tv, sizeof(TailLevel) * nt, cudaMemcpyHostToDevice, ctx->stream));
+    }
+
     // levels, folds and the resolve of a chunk form one chain of dependent launches: each kernel lets the
     // next one start its prologue early and waits for its predecessor itself (RTB200_NO_PDL=1: plain launches)
     const bool pdl = getenv("RTB200_NO_PDL") == nullptr;
@@ -615,11 +641,13 @@ static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const 
         const int rows = std::min(rows_per_chunk, local_LH - ly0);
         CU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, ctx->stream));
         for (int level = 0; level <= last; ++level) {
+            const bool tail_launch = tail_from && level == tail_from;
             const bool spawn = level < max_b;
             LevelBuf& cur = ctx->levels[(size_t)level];
             LevelBuf& nxt = ctx->levels[(size_t)level + 1];
             LevelParams p;
             memset(&p, 0, sizeof p);
+            if (tail_launch) { p.tail = ctx->tail_dev.as<TailLevel>(); p.tail_count = last - tail_from + 1; }
             p.f = fp;
             if (!spawn) p.f.secondary = 0;
             p.blob = ctx->ds.blob; p.rl = ctx->ds.rl;
@@ -646,9 +674,30 @@ static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const 
             CU(launch_resident_level(p, exact, ctx->sm_count, ctx->stream));
             if (timed) CU(cudaEventRecord(ctx->ev[3], ctx->stream));
             ++*launches;
+            if (tail_launch) break;                             // that launch walked every remaining level
         }
-        for (int l = std::min(last, max_b - 1); l >= 0; --l) {          // bottom-up fold of the levels that spawned
-            if (l == last) continue;                                     // (a probe level has no children to fold)
+        // bottom-up fold of the levels that spawned.  The deep levels (small queues) first, all of them in ONE
+        // single-CTA launch; then one grid per large level.
+        int fold_top = std::min(last, max_b - 1);
+        if (fold_top == last) --fold_top;                                // (a probe level has no children to fold)
+        int tail_first = fold_top + 1;
+        while (tail_first - 1 >= 1 && cap[(size_t)tail_first - 1] <= 16384 && fold_top - (tail_first - 1) < RT_TAIL_FOLD_MAX) --tail_first;
+        if (tail_first <= fold_top && fold_top - tail_first >= 1 && !getenv("RTB200_NO_TAIL_FOLD")) {
+            TailFoldParams tf;
+            memset(&tf, 0, sizeof tf);
+            tf.first = tail_first; tf.last = fold_top;
+            for (int l = tail_first; l <= fold_top; ++l) {
+                tf.links[l - tail_first] = ctx->levels[(size_t)l].links.as<int4>();
+                tf.colour[l - tail_first] = ctx->levels[(size_t)l].colour.as<float4>();
+                tf.cap[l - tail_first] = (int)cap[(size_t)l];
+            }
+            tf.colour[fold_top - tail_first + 1] = ctx->levels[(size_t)fold_top + 1].colour.as<float4>();
+            tf.counters = d_cnt; tf.mat = ctx->ds.mat; tf.pdl = pdl ? 2 : 0;
+            CU(launch_tail_fold(tf, exact, ctx->stream));
+            ++*launches;
+            fold_top = tail_first - 1;
+        }
+        for (int l = fold_top; l >= 0; --l) {
             CombineParams c;
             memset(&c, 0, sizeof c);
             c.links = ctx->levels[(size_t)l].links.as<int4>();

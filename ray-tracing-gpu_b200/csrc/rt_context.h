@@ -107,6 +107,8 @@ struct rtb200_ctx {
     unsigned long long scene_serial = 0;   // bumped by rtb200_set_scene
     unsigned long long level_fallbacks = 0;   // frames redone through the synchronous level loop (a queue guess was too small)
     rtb::PinnedBuf h_levels;               // per-chunk copies of the level counters
+    rtb::DevBuf tail_dev;                  // table of the deep levels one tail-mode launch walks
+    rtb::PinnedBuf tail_host;
     rtb::DevBuf seq_fb[2], seq_stats;  // rtb200_render_sequence: double-buffered RGBA8 frames, per-frame counters
     rtb::PinnedBuf seq_host;
     int last_W = 0, last_H = 0, last_local_rows = 0;

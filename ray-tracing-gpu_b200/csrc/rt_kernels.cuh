@@ -12,6 +12,17 @@ enum {                             // per-slot counter index
 };
 
 // One wavefront level of the scene-resident fused path (trace + shade + shadow + spawn).
+struct TailLevel {                 // one deep level of a tail-mode launch (see LevelParams::tail)
+    const float4* in_od0;
+    const float4* in_od1;
+    float4* in_colour;
+    float4* out_od0;
+    float4* out_od1;
+    int4*   links;
+    int     level, in_cap, spawn;   // spawn: 0 = the deepest allowed level
+    unsigned int out_cap;           // 0 = a probe: may only report that it wanted children
+};
+
 struct LevelParams {
     FrameParams f;
     const unsigned char* blob;     // resident blob (global)
@@ -46,6 +57,11 @@ struct LevelParams {
     int   out_guarded;                  // 1: appends are checked against out_cap
     unsigned int out_cap;
     unsigned int* overflow;
+    // tail mode (level >= 1 kernels, ONE CTA): the launch walks tail_count consecutive deep levels itself, a block
+    // barrier between them, taking each level's queues from this table in global memory -- a few hundred rays per
+    // level are not worth a launch each (render_resident_async)
+    const struct TailLevel* tail;
+    int   tail_count;
     // programmatic dependent launch: 1 = this kernel is part of a chain enqueued in one go; it lets its
     // successor start early (the successor's prologue overlaps this kernel's tail) and waits for its
     // predecessor before touching anything the predecessor wrote.  2 = same, and the launch itself carries
@@ -71,6 +87,19 @@ struct CombineParams {
     int   parent_is_level0;
     const unsigned int* n_links_dev;    // non-null: the link count lives on the device (n_links = capacity)
     int   pdl;                          // see LevelParams::pdl
+};
+
+// fold of SEVERAL deep levels by one CTA (render_resident_async): levels last, last - 1, ..., first (first >= 1),
+// a block barrier between them.  Deep levels hold a few hundred links; one launch instead of one per level.
+#define RT_TAIL_FOLD_MAX 32
+struct TailFoldParams {
+    int first, last;
+    const int4*  links[RT_TAIL_FOLD_MAX];      // [l - first]
+    float4*      colour[RT_TAIL_FOLD_MAX + 1]; // [l - first] parents of level l, [l - first + 1] their children
+    int          cap[RT_TAIL_FOLD_MAX];
+    const unsigned int* counters;              // [2 * l + 1] = links at level l
+    const MatRec* mat;
+    int pdl;
 };
 
 struct ResolveParams {
@@ -104,6 +133,7 @@ size_t resident_smem_bytes(const ResidentLayout& rl);
 cudaError_t resident_prepare(size_t max_smem_bytes);
 cudaError_t launch_resident_level(const LevelParams& p, bool exact, int sm_count, cudaStream_t st);
 cudaError_t launch_combine(const CombineParams& p, bool exact, cudaStream_t st);
+cudaError_t launch_tail_fold(const TailFoldParams& p, bool exact, cudaStream_t st);
 cudaError_t launch_resolve(const ResolveParams& p, cudaStream_t st);
 
 // ray-level queries over the unified list in global memory (rt_resident.cu)

@@ -217,8 +217,9 @@ k_resident_level(const __grid_constant__ LevelParams p)
         tma_load_1d(smem, p.blob, (uint32_t)p.rl.bytes, &bar);
     }
     if (p.pdl) pdl_wait();                  // everything below may read what the previous kernel wrote
+    const bool tail_mode = !PRIMARY && p.tail != nullptr;
     int in_count = p.in_count;
-    if (!PRIMARY && p.in_count_dev) {       // written by the level before this one, no host in between
+    if (!PRIMARY && p.in_count_dev && !tail_mode) {   // written by the level before this one, no host in between
         const unsigned int n = *p.in_count_dev;
         in_count = (int)(n < (unsigned int)p.in_cap ? n : (unsigned int)p.in_cap);
         if ((int)blockIdx.x * RES_THREADS >= in_count) {                   // whole CTA: nothing to do
@@ -253,10 +254,37 @@ k_resident_level(const __grid_constant__ LevelParams p)
     }
     unsigned int n_shadow = 0, n_tests = 0, n_refl_st = 0, n_refr_st = 0, n_nan = 0;
 
+    // the level this launch works on -- in tail mode one after the other, from the table
+    const float4* in_od0 = p.in_od0;
+    const float4* in_od1 = p.in_od1;
+    float4* in_colour = p.in_colour;
+    float4* out_od0 = p.out_od0;
+    float4* out_od1 = p.out_od1;
+    int4*   links = p.links;
+    unsigned int* out_count = p.out_count;
+    unsigned int* link_count = p.link_count;
+    int  level = p.level, out_guarded = p.out_guarded;
+    unsigned int out_cap = p.out_cap;
+    bool may_spawn = f.secondary != 0;
+    const int n_levels = tail_mode ? p.tail_count : 1;
+    for (int tl = 0; tl < n_levels; ++tl) {
+    int n_blocks_l = n_blocks;
+    if (tail_mode) {
+        const TailLevel tv = p.tail[tl];
+        in_od0 = tv.in_od0; in_od1 = tv.in_od1; in_colour = tv.in_colour;
+        out_od0 = tv.out_od0; out_od1 = tv.out_od1; links = tv.links;
+        level = tv.level; out_guarded = 1; out_cap = tv.out_cap; may_spawn = tv.spawn != 0;
+        out_count = p.out_count + 2 * tl; link_count = p.link_count + 2 * tl;       // counters of consecutive levels
+        const unsigned int n = __ldcg(p.in_count_dev + 2 * tl);                     // written by the level before
+        in_count = (int)(n < (unsigned int)tv.in_cap ? n : (unsigned int)tv.in_cap);
+        if (in_count == 0) break;                                                   // (the whole CTA reads the same value)
+        n_blocks_l = (in_count + RES_THREADS - 1) / RES_THREADS;
+    }
+
     // tile walk without a division per tile: (tx, ty) advance by the grid stride
     const int step_x = (int)(gridDim.x % (unsigned)tiles_x), step_y = (int)(gridDim.x / (unsigned)tiles_x);
     int tile_x = PRIMARY ? (int)(blockIdx.x % (unsigned)tiles_x) : 0, tile_y = PRIMARY ? (int)(blockIdx.x / (unsigned)tiles_x) : 0;
-    for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+    for (int blk = blockIdx.x; blk < n_blocks_l; blk += gridDim.x) {
     // ---- this thread's ray ------------------------------------------------------------------
     V3 o, d;
     float energy = 1.0f, ior = 1.0f;
@@ -277,8 +305,8 @@ k_resident_level(const __grid_constant__ LevelParams p)
     } else {
         self = blk * RES_THREADS + tid;
         valid = self < in_count;
-        const float4 a = valid ? p.in_od0[self] : make_float4(0.f, 0.f, 0.f, 0.f);
-        const float4 b = valid ? p.in_od1[self] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 a = valid ? in_od0[self] : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 b = valid ? in_od1[self] : make_float4(0.f, 0.f, 0.f, 0.f);
         o = f4_xyz(a); d = f4_xyz(b); energy = a.w; ior = b.w;
     }
 
@@ -341,7 +369,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
             }
         }
         // ---- secondary rays (Scene.cpp:1779-1823) ---------------------------------------------
-        if (hit && f.secondary && p.level < f.max_bounces) {
+        if (hit && may_spawn && level < f.max_bounces) {
             e_refl = FP<E>::mul(kr, energy);
             e_refr = FP<E>::mul(kt, energy);
             want_refl = e_refl > f.min_energy;
@@ -361,7 +389,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
                 c[0] = cr; c[1] = cg; c[2] = cb;
             }
         } else {
-            p.in_colour[self] = make_float4(cr, cg, cb, 0.f);
+            in_colour[self] = make_float4(cr, cg, cb, 0.f);
         }
     }
 
@@ -373,8 +401,8 @@ k_resident_level(const __grid_constant__ LevelParams p)
         const unsigned int m_any = m_refl | m_refr;
         unsigned int base = 0, lbase = 0;
         if (lane == 0) {
-            base  = atomicAdd(p.out_count, n_refl + n_refr);
-            lbase = atomicAdd(p.link_count, (unsigned int)__popc(m_any));
+            base  = atomicAdd(out_count, n_refl + n_refr);
+            lbase = atomicAdd(link_count, (unsigned int)__popc(m_any));
         }
         base  = __shfl_sync(0xffffffffu, base, 0);
         lbase = __shfl_sync(0xffffffffu, lbase, 0);
@@ -382,13 +410,13 @@ k_resident_level(const __grid_constant__ LevelParams p)
         int s_refl = -1, s_refr = -1;
         // guessed capacity exhausted: nothing is written, the link carries no children (so that the
         // fold stays in bounds) and the host is told to redo the frame with exact capacities
-        const bool room = !p.out_guarded || base + n_refl + n_refr <= p.out_cap;
+        const bool room = !out_guarded || base + n_refl + n_refr <= out_cap;
         if (!room && lane == 0) *p.overflow = 1u;
         if (room && want_refl) {
             s_refl = (int)(base + __popc(m_refl & below));
             const V3 rd = reflect3<E>(d, N);
-            p.out_od0[s_refl] = make_float4(P.x, P.y, P.z, e_refl);
-            p.out_od1[s_refl] = make_float4(rd.x, rd.y, rd.z, 0.0f);          // CRayon default ior, Rayon.cpp:16
+            out_od0[s_refl] = make_float4(P.x, P.y, P.z, e_refl);
+            out_od1[s_refl] = make_float4(rd.x, rd.y, rd.z, 0.0f);            // CRayon default ior, Rayon.cpp:16
             ++n_refl_st;
         }
         if (room && want_refr) {
@@ -397,14 +425,16 @@ k_resident_level(const __grid_constant__ LevelParams p)
             if (ior == mior) { nior = f.scene_ior; ratio = FP<E>::div(mior, f.scene_ior); n2 = neg3(N); }
             else             { nior = mior;        ratio = FP<E>::div(f.scene_ior, mior); }
             const V3 rd = refract3<E>(d, n2, ratio);
-            p.out_od0[s_refr] = make_float4(P.x, P.y, P.z, e_refr);
-            p.out_od1[s_refr] = make_float4(rd.x, rd.y, rd.z, nior);
+            out_od0[s_refr] = make_float4(P.x, P.y, P.z, e_refr);
+            out_od1[s_refr] = make_float4(rd.x, rd.y, rd.z, nior);
             ++n_refr_st;
         }
         if (want_refl || want_refr)
-            p.links[lbase + __popc(m_any & below)] = make_int4(self, s_refl, s_refr, mat);
+            links[lbase + __popc(m_any & below)] = make_int4(self, s_refl, s_refr, mat);
     }
     }   // tiles of this CTA
+    if (tail_mode) __syncthreads();         // the next level reads what this one appended (same CTA: visible after the barrier)
+    }   // levels of a tail-mode launch
 
     // ---- statistics ---------------------------------------------------------------------------
     warp_stats(p.stats, n_shadow, n_refl_st, n_refr_st, n_tests, n_nan);
@@ -439,6 +469,38 @@ __global__ void __launch_bounds__(256) k_combine(const CombineParams p)
     }
     if (p.parent_is_level0) { float* c = p.parent_c0 + 3 * (size_t)lk.x; c[0] = r; c[1] = g; c[2] = b; }
     else p.parent_colour[lk.x] = make_float4(r, g, b, 0.f);
+    }
+}
+
+// the same fold for a run of deep (small) levels, by ONE CTA: level l's parents are level l - 1's children,
+// so a block barrier separates the levels (global writes of a block are visible to it after the barrier)
+template <bool E>
+__global__ void __launch_bounds__(1024) k_tail_fold(const __grid_constant__ TailFoldParams p)
+{
+    if (p.pdl) { pdl_launch_dependents(); pdl_wait(); }
+    for (int l = p.last; l >= p.first; --l) {
+        const int s = l - p.first;
+        const unsigned int nd = p.counters[2 * l + 1];
+        const int n = (int)(nd < (unsigned int)p.cap[s] ? nd : (unsigned int)p.cap[s]);
+        const int4* __restrict__ links = p.links[s];
+        float4* parent = p.colour[s];
+        const float4* child = p.colour[s + 1];
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const int4 lk = links[i];
+            const float kr = p.mat[lk.w].m1.w, kt = p.mat[lk.w].m2.x;
+            const float4 c0 = parent[lk.x];
+            float r = c0.x, g = c0.y, b = c0.z;
+            if (lk.y >= 0) {
+                const float4 c = child[lk.y];
+                r = FP<E>::madd(c.x, kr, r); g = FP<E>::madd(c.y, kr, g); b = FP<E>::madd(c.z, kr, b);
+            }
+            if (lk.z >= 0) {
+                const float4 c = child[lk.z];
+                r = FP<E>::madd(c.x, kt, r); g = FP<E>::madd(c.y, kt, g); b = FP<E>::madd(c.z, kt, b);
+            }
+            parent[lk.x] = make_float4(r, g, b, 0.f);
+        }
+        __syncthreads();
     }
 }
 
@@ -566,7 +628,7 @@ cudaError_t launch_resident_level(const LevelParams& p_in, bool exact, int sm_co
         return launch_chain(exact ? k_resident_level<true, true> : k_resident_level<false, true>, grid, RES_THREADS, smem, st, pdl, p);
     }
     const int n_max = p.in_count_dev ? p.in_cap : p.in_count;
-    const dim3 grid((unsigned)std::min((n_max + RES_THREADS - 1) / RES_THREADS, max_ctas));
+    const dim3 grid(p.tail ? 1u : (unsigned)std::min((n_max + RES_THREADS - 1) / RES_THREADS, max_ctas));
     return launch_chain(exact ? k_resident_level<true, false> : k_resident_level<false, false>, grid, RES_THREADS, smem, st, pdl, p);
 }
 
@@ -576,6 +638,11 @@ cudaError_t launch_combine(const CombineParams& p, bool exact, cudaStream_t st)
     const unsigned want = (unsigned)((p.n_links + 255) / 256);
     const dim3 grid(p.n_links_dev ? std::min(want, 1184u) : want);
     return launch_chain(exact ? k_combine<true> : k_combine<false>, grid, 256, 0, st, p.pdl == 2, p);
+}
+
+cudaError_t launch_tail_fold(const TailFoldParams& p, bool exact, cudaStream_t st)
+{
+    return launch_chain(exact ? k_tail_fold<true> : k_tail_fold<false>, dim3(1), 1024, 0, st, p.pdl == 2, p);
 }
 
 cudaError_t launch_resolve(const ResolveParams& p, cudaStream_t st)
