@@ -1,12 +1,16 @@
 // rt_cli.cpp -- headless command line of the renderer: the reference's `exe scene.dat -x W -y H`
 // (Main.cpp:51-124) without GLUT/GLEW: the frame goes to a PPM file instead of a window.
 //   rt_cli scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--fused] [--exact] [--bvh]
-//          [--frames n] [--out image.ppm] [--obj mesh.obj]
+//          [--frames n] [--out image.ppm] [--obj mesh.obj] [--orbit n]
+// --orbit n: a camera path of n frames on a circle around the point looked at, as one pipelined
+// submission (CScene::LancerTrajectoire); with --out f.ppm the frames go to f_000.ppm, f_001.ppm, ...
 // Unlike Main.cpp:79 there is no power-of-two / multiple-of-16 restriction on W and H.
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <string>
+#include <vector>
 
 #include "Scene.h"
 #include "Var.h"
@@ -17,10 +21,10 @@ using namespace Scene;
 int main(int argc, char** argv)
 {
     if (argc < 2) {
-        std::cerr << "usage: " << argv[0] << " scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--fused] [--exact] [--bvh] [--frames n] [--out f.ppm] [--obj mesh.obj]" << std::endl;
+        std::cerr << "usage: " << argv[0] << " scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--fused] [--exact] [--bvh] [--frames n] [--out f.ppm] [--obj mesh.obj] [--orbit n]" << std::endl;
         return EXIT_FAILURE;
     }
-    int W = CVar::g_LargeurFenetre, H = CVar::g_HauteurFenetre, depth = -1, spp = 1, frames = 1;
+    int W = CVar::g_LargeurFenetre, H = CVar::g_HauteurFenetre, depth = -1, spp = 1, frames = 1, orbit = 0;
     unsigned int flags = 0;
     const char* out = nullptr;
     const char* obj = nullptr;
@@ -35,6 +39,7 @@ int main(int argc, char** argv)
         else if (!strcmp(argv[i], "--spp")) spp = atoi(next("--spp"));
         else if (!strcmp(argv[i], "--device")) CVar::g_Peripherique = atoi(next("--device"));
         else if (!strcmp(argv[i], "--frames")) frames = atoi(next("--frames"));
+        else if (!strcmp(argv[i], "--orbit")) orbit = atoi(next("--orbit"));
         else if (!strcmp(argv[i], "--out")) out = next("--out");
         else if (!strcmp(argv[i], "--obj")) obj = next("--obj");
         else if (!strcmp(argv[i], "--fused")) flags |= RTB200_F_FUSED_FP;
@@ -65,6 +70,33 @@ int main(int argc, char** argv)
     CVar::g_ComputeShader = new CNuanceurCalculProg(CVar::g_ComputeShaderPath, true);
 
     std::cout << "[ETAT]: Lancer de rayons..." << std::endl;
+    if (orbit > 0) {
+        const std::vector<CVecteur3> positions = scene->OrbiteCamera(orbit);
+        std::vector<unsigned char> images(out ? (size_t)orbit * W * H * 4 : 0);
+        const auto t0 = std::chrono::steady_clock::now();
+        const double ms = scene->LancerTrajectoire(positions, out ? images.data() : nullptr);
+        const auto t1 = std::chrono::steady_clock::now();
+        double rays = 0.0;
+        for (const rtb200_stats& st : scene->ObtenirStatistiquesTrajectoire())
+            rays += (double)(st.rays_primary + st.rays_shadow + st.rays_reflect + st.rays_refract);
+        std::cout << "[ETAT]: Trajectoire de " << orbit << " images terminee --> " << std::chrono::duration<double>(t1 - t0).count() << " secondes"
+                  << " (GPU " << ms << " ms, " << ms / orbit << " ms/image, " << rays / (ms * 1e3) << " Mrays/s)" << std::endl;
+        if (out) {
+            std::string base(out);
+            const size_t dot = base.rfind(".ppm");
+            if (dot != std::string::npos && dot + 4 == base.size()) base.erase(dot);
+            for (int f = 0; f < orbit; ++f) {
+                char suffixe[32];
+                snprintf(suffixe, sizeof suffixe, "_%03d.ppm", f);
+                const std::string nom = base + suffixe;
+                if (!CScene::EcrirePPM(nom.c_str(), images.data() + (size_t)f * W * H * 4, W, H)) { std::cerr << "[ERREUR]: cannot write " << nom << std::endl; return EXIT_FAILURE; }
+            }
+            std::cout << "[ETAT]: " << orbit << " images ecrites dans " << base << "_NNN.ppm" << std::endl;
+        }
+        CScene::LibererInstance();
+        delete CVar::g_ComputeShader;
+        return EXIT_SUCCESS;
+    }
     for (int f = 0; f < frames; ++f) {
         const auto t0 = std::chrono::steady_clock::now();
         scene->LancerRayons();

@@ -318,8 +318,12 @@ void CScene::Preparer()
         g.color[0] = c.r; g.color[1] = c.g; g.color[2] = c.b; g.intensity = l->GetIntensity();
         e.lights.push_back(g);
     }
-    // ---- frame block: replaces the "General" UBO (Scene.cpp:704-783) and Scene.cpp:676-679 -------
-    rtb200_frame& f = e.cadre;
+    RemplirCadre(e.cadre);
+}
+
+// ---- frame block: replaces the "General" UBO (Scene.cpp:704-783) and Scene.cpp:676-679 -----------
+void CScene::RemplirCadre(rtb200_frame& f) const
+{
     memset(&f, 0, sizeof f);
     f.width = m_ResLargeur; f.height = m_ResHauteur; f.spp_grid = m_GrilleSpp;
     f.max_bounces = m_NbRebondsMax; f.min_energy = m_EnergieMinRayon; f.scene_ior = m_IndiceRefractionScene;
@@ -363,16 +367,86 @@ void CScene::LancerRayons()
     }
 }
 
+// A camera path as ONE submission (rtb200_render_sequence): the reference draws a single frame per
+// process (Main.cpp:181); with the scene resident on the device a fly-through costs one kernel per frame.
+// positions[i] replaces the camera position of frame i; the point looked at, the up vector and the focal
+// length stay, and every camera goes through InitialiserCamera like the one of the scene file.
+double CScene::LancerTrajectoire(const std::vector<CVecteur3>& positions, unsigned char* images)
+{
+    Preparer();
+    if (positions.empty()) return 0.0;
+    if (!CVar::g_ComputerShadersON) {
+        std::cerr << "[ERREUR]: CVar::g_ComputerShadersON == false: this build has no CPU renderer." << std::endl;
+        exit(EXIT_FAILURE);
+    }
+    if (!CVar::g_ComputeShader) CVar::g_ComputeShader = new CNuanceurCalculProg(CVar::g_ComputeShaderPath, true);
+    CVar::g_ComputeShader->activer();
+    rtb200_ctx* ctx = CVar::g_ComputeShader->contexte();
+    std::vector<rtb200_frame> cadres(positions.size());
+    for (size_t i = 0; i < positions.size(); ++i) cadres[i] = CadreDepuis(positions[i]);
+    m_StatsTrajectoire.assign(positions.size(), rtb200_stats{});
+    const rtb200_scene vue = m_Emballee.vue();
+    int rc = rtb200_set_scene(ctx, &vue);
+    if (rc == RTB200_OK && (m_Drapeaux & RTB200_F_USE_BVH)) rc = rtb200_build_bvh(ctx);
+    if (rc == RTB200_OK) rc = rtb200_render_sequence(ctx, cadres.data(), (int)cadres.size(), images, m_StatsTrajectoire.data());
+    if (rc == RTB200_OK) {                               // the last frame is also the scene's current image (RGBA8:
+        const size_t octets = (size_t)m_ResLargeur * m_ResHauteur * 4;     // a sequence delivers no float frame)
+        m_ImageRGBA8.resize(octets);
+        if (images) memcpy(m_ImageRGBA8.data(), images + (positions.size() - 1) * octets, octets);
+        else rc = rtb200_read_frame(ctx, nullptr, m_ImageRGBA8.data());
+    }
+    if (rc != RTB200_OK) {
+        std::cerr << "[ERREUR]: rendu CUDA : " << rtb200_error_string(rc) << " -- " << rtb200_last_error(ctx) << std::endl;
+        exit(EXIT_FAILURE);
+    }
+    m_Stats = m_StatsTrajectoire.back();
+    double ms = 0.0;
+    for (const rtb200_stats& st : m_StatsTrajectoire) ms += st.ms_render;
+    return ms;
+}
+
+// The frame block of the scene's camera moved to `position` (the scene's own camera is left as it was).
+rtb200_frame CScene::CadreDepuis(const CVecteur3& position)
+{
+    const CVecteur3 depart = m_Camera.Position;
+    m_Camera.Position = position;
+    InitialiserCamera();
+    rtb200_frame f;
+    RemplirCadre(f);
+    m_Camera.Position = depart;
+    InitialiserCamera();
+    return f;
+}
+
+// n camera positions on a circle around the vertical axis through the point looked at, starting at
+// the scene's own camera (frame 0 is the frame LancerRayons draws).
+std::vector<CVecteur3> CScene::OrbiteCamera(const int n) const
+{
+    std::vector<CVecteur3> pos;
+    const CVecteur3 d = m_Camera.Position - m_Camera.PointVise;
+    for (int i = 0; i < n; ++i) {
+        const REAL a = RENDRE_REEL(2.0 * PI) * i / n, c = std::cos(a), s = std::sin(a);
+        pos.push_back(i == 0 ? m_Camera.Position
+                             : m_Camera.PointVise + CVecteur3(c * d.x + s * d.z, d.y, -s * d.x + c * d.z));
+    }
+    return pos;
+}
+
 bool CScene::EcrireImagePPM(const char* fichier) const
 {
     if (m_ImageRGBA8.empty()) return false;
+    return EcrirePPM(fichier, m_ImageRGBA8.data(), m_ResLargeur, m_ResHauteur);
+}
+
+bool CScene::EcrirePPM(const char* fichier, const unsigned char* rgba8, int largeur, int hauteur)
+{
     FILE* f = fopen(fichier, "wb");
     if (!f) return false;
-    fprintf(f, "P6\n%d %d\n255\n", m_ResLargeur, m_ResHauteur);
-    std::vector<unsigned char> row((size_t)m_ResLargeur * 3);
-    for (int y = m_ResHauteur - 1; y >= 0; --y) {       // buffer row 0 is the bottom scanline
-        const unsigned char* src = m_ImageRGBA8.data() + (size_t)y * m_ResLargeur * 4;
-        for (int x = 0; x < m_ResLargeur; ++x) { row[3 * x] = src[4 * x]; row[3 * x + 1] = src[4 * x + 1]; row[3 * x + 2] = src[4 * x + 2]; }
+    fprintf(f, "P6\n%d %d\n255\n", largeur, hauteur);
+    std::vector<unsigned char> row((size_t)largeur * 3);
+    for (int y = hauteur - 1; y >= 0; --y) {             // buffer row 0 is the bottom scanline
+        const unsigned char* src = rgba8 + (size_t)y * largeur * 4;
+        for (int x = 0; x < largeur; ++x) { row[3 * x] = src[4 * x]; row[3 * x + 1] = src[4 * x + 1]; row[3 * x + 2] = src[4 * x + 2]; }
         fwrite(row.data(), 1, row.size(), f);
     }
     fclose(f);
@@ -449,6 +523,36 @@ int rtscene_camera(const float* pos, const float* look, const float* up, int W, 
     s->AjusterResolution(W, H);
     *out = s->ObtenirSceneEmballee().cadre;
     CScene::LibererInstance();
+    return 0;
+}
+
+// CScene::LancerTrajectoire over CScene::OrbiteCamera(n): n frames (n * W*H*4 bytes) and the camera
+// blocks they were drawn with (so that a test can render the same frames one by one).
+int rtscene_orbit(int W, int H, unsigned int flags, int n, unsigned char* out_rgba8, rtb200_frame* out_frames, rtb200_stats* st)
+{
+    CScene* s = CScene::ObtenirInstance();
+    s->AjusterResolution(W, H);
+    s->AjusterSurechantillonnage(1);
+    s->AjusterDrapeauxRendu(flags);
+    CVar::g_ComputerShadersON = true;
+    s->Preparer();
+    const std::vector<CVecteur3> pos = s->OrbiteCamera(n);
+    s->LancerTrajectoire(pos, out_rgba8);
+    for (int i = 0; i < n; ++i) {
+        if (st) st[i] = s->ObtenirStatistiquesTrajectoire()[i];
+        if (out_frames) out_frames[i] = s->CadreDepuis(pos[i]);
+    }
+    return 0;
+}
+
+// The camera blocks alone (no device needed): what LancerTrajectoire would submit for OrbiteCamera(n).
+int rtscene_orbit_frames(int W, int H, int n, rtb200_frame* out_frames)
+{
+    CScene* s = CScene::ObtenirInstance();
+    s->AjusterResolution(W, H);
+    s->Preparer();
+    const std::vector<CVecteur3> pos = s->OrbiteCamera(n);
+    for (int i = 0; i < n; ++i) out_frames[i] = s->CadreDepuis(pos[i]);
     return 0;
 }
 

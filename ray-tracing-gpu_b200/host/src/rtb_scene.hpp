@@ -108,6 +108,14 @@ public:
     void Preparer();
     const SceneEmballee& ObtenirSceneEmballee();
     bool EcrireImagePPM(const char* fichier) const;   // P6, rows flipped so that the top scanline comes first
+    // Camera path in one pipelined submission (rtb200_render_sequence): frame i is drawn from positions[i]
+    // with the scene's look-at point and up vector.  `images` (n * W*H*4 bytes, may be NULL) receives every
+    // frame; the last one is also left in ObtenirImageRGBA8 / ObtenirInfoPixel.  Returns the GPU time (ms).
+    double LancerTrajectoire(const std::vector<CVecteur3>& positions, unsigned char* images);
+    rtb200_frame CadreDepuis(const CVecteur3& position);      // frame block of the camera moved to `position`
+    std::vector<CVecteur3> OrbiteCamera(const int n) const;   // n positions on a circle around the look-at point
+    const std::vector<rtb200_stats>& ObtenirStatistiquesTrajectoire() const { return m_StatsTrajectoire; }
+    static bool EcrirePPM(const char* fichier, const unsigned char* rgba8, int largeur, int hauteur);
 
 private:
     CScene();
@@ -137,6 +145,8 @@ private:
     bool m_Prepare = false;
     SceneEmballee m_Emballee;
     rtb200_stats m_Stats{};
+    std::vector<rtb200_stats> m_StatsTrajectoire;
+    void RemplirCadre(rtb200_frame& cadre) const;
 };
 
 } // namespace Scene

@@ -23,6 +23,8 @@ def lib():
         L.rtscene_pack.argtypes = [C.c_int, C.c_int, C.POINTER(abi.Scene), C.POINTER(abi.Frame)]
         L.rtscene_render.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint, C.c_void_p, C.c_void_p, C.POINTER(abi.Stats)]
         L.rtscene_add_obj.argtypes = [C.c_char_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p]
+        L.rtscene_orbit.argtypes = [C.c_int, C.c_int, C.c_uint, C.c_int, C.c_void_p, C.POINTER(abi.Frame), C.POINTER(abi.Stats)]
+        L.rtscene_orbit_frames.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(abi.Frame)]
         L.rtscene_free.restype = None
         L.rtscene_camera.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(abi.Frame)]
         _lib = L
@@ -71,6 +73,23 @@ def render_loaded(W, H, spp_grid=1, flags=0):
     st = abi.Stats()
     L.rtscene_render(W, H, spp_grid, flags, f.ctypes.data, q.ctypes.data, C.byref(st))
     return f, q, st
+
+
+def orbit_frames(W, H, n):
+    """Camera blocks of CScene::OrbiteCamera(n) for the loaded scene (host only, no device)."""
+    frames = (abi.Frame * n)()
+    lib().rtscene_orbit_frames(W, H, n, frames)
+    return list(frames)
+
+
+def orbit_loaded(W, H, n, flags=0):
+    """CScene::LancerTrajectoire over CScene::OrbiteCamera(n): (n, H, W, 4) RGBA8 frames, the camera
+    blocks they were drawn with and the per-frame statistics."""
+    q = np.empty((n, H, W, 4), np.uint8)
+    frames = (abi.Frame * n)()
+    st = (abi.Stats * n)()
+    lib().rtscene_orbit(W, H, flags, n, q.ctypes.data, frames, st)
+    return q, list(frames), list(st)
 
 
 def add_obj(path, rgb=(0.8, 0.8, 0.8), reflect=0.0, scale=1.0, translate=(0.0, 0.0, 0.0)):

@@ -170,3 +170,72 @@ def test_obj_mesh_renders_through_lbvh_like_the_oracle(rt, host, port, tmp_path)
     port.lib.rto_render(C.byref(s), C.byref(fr), want, port.max_threads)
     assert np.allclose(f, want, rtol=0, atol=4e-6)
     assert (np.abs(f - want) > 0).mean() < 0.01
+
+
+def _vec(a):
+    return np.array(a[:], np.float32)
+
+
+def test_orbit_camera_blocks(rt, host):
+    """CScene::OrbiteCamera / CadreDepuis: frame 0 is the scene's own camera bit for bit, every other
+    camera keeps height, distance to the point looked at and field of view, and its basis is the one
+    InitialiserCamera derives (orthonormal, N pointing from the look-at point to the camera)."""
+    path = os.path.join(GOLDEN, "scenes", "scene7.dat")
+    ps, own = host.load_and_pack(path, 96, 64)
+    frames = host.orbit_frames(96, 64, 8)
+    assert bytes(frames[0]) == bytes(own)
+    p0 = _vec(own.cam_pos).astype(np.float64)
+    # the point looked at lies on the line p0 - t * N
+    n0 = _vec(own.cam_n).astype(np.float64)
+    for k, f in enumerate(frames):
+        u, v, n = (_vec(x).astype(np.float64) for x in (f.cam_u, f.cam_v, f.cam_n))
+        for a in (u, v, n):
+            assert abs(np.dot(a, a) - 1.0) < 1e-5
+        assert abs(np.dot(u, v)) < 1e-5 and abs(np.dot(u, n)) < 1e-5 and abs(np.dot(v, n)) < 1e-5
+        assert np.allclose(np.cross(v, n), u, atol=1e-5)
+        assert f.half_h == pytest.approx(own.half_h, rel=1e-5) and f.half_w == pytest.approx(own.half_w, rel=1e-5)
+        assert (f.width, f.height, f.max_bounces) == (96, 64, own.max_bounces)
+        assert _vec(f.cam_pos)[1] == pytest.approx(p0[1], abs=1e-3)       # the circle is horizontal
+        assert abs(n[1] - n0[1]) < 1e-5                                    # same elevation angle
+    assert len({tuple(_vec(f.cam_pos)) for f in frames}) == 8
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,flags_name", [(1, None), (4, None), (7, None), (4, "F_USE_BVH")])
+def test_camera_path_equals_single_frames(rt, host, renderer, n, flags_name):
+    """CScene::LancerTrajectoire (one pipelined rtb200_render_sequence: depth 0 keeps the fast path;
+    depth 4 / LBVH take the frame-by-frame form) == the same cameras rendered one by one."""
+    flags = getattr(rt, flags_name) if flags_name else 0
+    path = os.path.join(GOLDEN, "scenes", f"scene{n}.dat")
+    for depth in (0, 4):
+        ps, _ = host.load_and_pack(path, 160, 120, depth)
+        q, frames, stats = host.orbit_loaded(160, 120, 6, flags)
+        renderer.set_scene(ps)
+        if flags:
+            renderer.build_bvh()
+        for i, fr in enumerate(frames):
+            assert fr.flags == flags and fr.max_bounces == depth
+            _, want8, st = renderer.render(fr)
+            assert np.array_equal(q[i], want8), (depth, i)
+            assert stats[i].rays_primary == 160 * 120 and stats[i].rays_shadow == st.rays_shadow
+        assert not np.array_equal(q[0], q[3])                             # the camera did move
+
+
+@pytest.mark.gpu
+def test_cli_orbit_writes_numbered_ppm(rt, host, renderer, tmp_path):
+    out = tmp_path / "fly.ppm"
+    path = os.path.join(GOLDEN, "scenes", "scene1.dat")
+    r = subprocess.run([host.CLI_PATH, path, "-x", "96", "-y", "64", "--depth", "0", "--orbit", "3", "--out", str(out)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    ps, _ = host.load_and_pack(path, 96, 64, 0)
+    frames = host.orbit_frames(96, 64, 3)
+    renderer.set_scene(ps)
+    head = b"P6\n96 64\n255\n"
+    for i, fr in enumerate(frames):
+        data = (tmp_path / f"fly_{i:03d}.ppm").read_bytes()
+        assert data.startswith(head)
+        img = np.frombuffer(data[len(head):], np.uint8).reshape(64, 96, 3)[::-1]
+        _, want8, _ = renderer.render(fr)
+        assert np.array_equal(img, want8[..., :3]), i
+    assert not (tmp_path / "fly_003.ppm").exists() and not out.exists()
