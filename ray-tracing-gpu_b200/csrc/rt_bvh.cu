@@ -263,7 +263,7 @@ __global__ void k_bvh_refit(const TriRec* __restrict__ tri, int n, BvhNode* node
 // ---------------------------------------------------------------------------------------
 // traversal
 // ---------------------------------------------------------------------------------------
-struct RayBox { float ix, iy, iz, ox, oy, oz; };           // 1/d and o/d
+struct RayBox { float ix, iy, iz, nx, ny, nz; };           // 1/d and -(o/d)
 
 RT_DEV float safe_rcp(float d)
 {
@@ -274,19 +274,23 @@ RT_DEV RayBox make_raybox(V3 o, V3 d)
 {
     RayBox r;
     r.ix = safe_rcp(d.x); r.iy = safe_rcp(d.y); r.iz = safe_rcp(d.z);
-    r.ox = o.x * r.ix; r.oy = o.y * r.iy; r.oz = o.z * r.iz;
+    r.nx = -(o.x * r.ix); r.ny = -(o.y * r.iy); r.nz = -(o.z * r.iz);
+#ifndef BVH_REMAT
+    // keep the three products in registers: without this ptxas recomputes them at every node
+    asm volatile("" : "+f"(r.nx), "+f"(r.ny), "+f"(r.nz));
+#endif
     return r;
 }
 
-// entry distance of the (already padded) box, or -1 when the ray misses it inside [0, limit]
-RT_DEV float slab(const RayBox& r, float lx, float ly, float lz, float hx, float hy, float hz, float limit)
+// does the ray meet the (already padded) box inside [0, limit]?  tn = entry distance
+RT_DEV bool slab(const RayBox& r, float lx, float ly, float lz, float hx, float hy, float hz, float limit, float& tn)
 {
-    const float ax = fmaf(lx, r.ix, -r.ox), bx = fmaf(hx, r.ix, -r.ox);
-    const float ay = fmaf(ly, r.iy, -r.oy), by = fmaf(hy, r.iy, -r.oy);
-    const float az = fmaf(lz, r.iz, -r.oz), bz = fmaf(hz, r.iz, -r.oz);
-    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float ax = fmaf(lx, r.ix, r.nx), bx = fmaf(hx, r.ix, r.nx);
+    const float ay = fmaf(ly, r.iy, r.ny), by = fmaf(hy, r.iy, r.ny);
+    const float az = fmaf(lz, r.iz, r.nz), bz = fmaf(hz, r.iz, r.nz);
+    tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), limit));
-    return tn <= tf * (1.0f + 2.0f * BVH_SLACK) ? tn : -1.0f;
+    return tn <= tf * (1.0f + 2.0f * BVH_SLACK);
 }
 
 // One triangle of a leaf.  MODE 0 / 2: the conservative fused filter of rt_cull.cuh in ONE pass
@@ -313,45 +317,53 @@ RT_DEV float triangle_leaf(V3 o, V3 d, V3 p0, V3 e1, V3 e2, float tmax)
 // Generic "while-while" traversal: the inner loop walks internal nodes only, so the lanes of a
 // warp leave it together and run the leaf code converged.  `Leaf` is called as
 // leaf(first, count, limit) and returns the new distance limit (negative = stop the traversal).
-template <class Leaf>
+// SHRINK: the limit can come down during the walk (nearest hit), so postponed subtrees carry their
+// entry distance and are dropped when they lie beyond it; an occlusion query (fixed limit) keeps
+// references only.  The bottom stack entry is a sentinel, so a pop never tests for an empty stack.
+#define BVH_DONE INT_MIN              // not a leaf reference: first + count <= n < 2^28 (bvh_build)
+
+template <bool SHRINK, class Leaf>
 RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& leaf, unsigned& n_nodes, unsigned& overflow)
 {
     const RayBox rb = make_raybox(o, d);
-    int   stack_ref[BVH_STACK];
-    float stack_tn[BVH_STACK];
-    int sp = 0;
+    const BvhNode* __restrict__ nodes = s.bvh_nodes;
+    int   stack_ref[BVH_STACK + 1];
+    float stack_tn[SHRINK ? BVH_STACK + 1 : 1];
+    stack_ref[0] = BVH_DONE;
+    stack_tn[0] = -1.0f;
+    int sp = 1;
     int ref = s.bvh_root;
-    bool alive = true;
-    // pop the next subtree that can still matter
-    auto pop = [&]() {
-        for (;;) {
-            if (sp == 0) { alive = false; ref = -1; return; }
-            --sp;
-            if (stack_tn[sp] <= limit * (1.0f + 2.0f * BVH_SLACK)) { ref = stack_ref[sp]; return; }
-        }
-    };
-    while (alive) {
+    for (;;) {
         while (ref >= 0) {                                   // ---- internal nodes
-            const BvhNode* __restrict__ nd = s.bvh_nodes + ref;
+            const BvhNode* __restrict__ nd = nodes + ref;
             const float4 b0 = __ldg(&nd->b0), b1 = __ldg(&nd->b1), b2 = __ldg(&nd->b2);
-            const int4 c = __ldg(&nd->c);
+            const int2 c = __ldg(reinterpret_cast<const int2*>(&nd->c));
             ++n_nodes;
-            const float t0 = slab(rb, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit);
-            const float t1 = slab(rb, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit);
-            if (t0 >= 0.f && t1 >= 0.f) {
+            float t0, t1;
+            const bool h0 = slab(rb, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0);
+            const bool h1 = slab(rb, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1);
+            if (h0 && h1) {
                 const bool swap = t1 < t0;
-                if (sp < BVH_STACK) { stack_ref[sp] = swap ? c.x : c.y; stack_tn[sp] = swap ? t0 : t1; ++sp; }
-                else overflow = 1;
+                if (sp <= BVH_STACK) {
+                    stack_ref[sp] = swap ? c.x : c.y;
+                    if (SHRINK) stack_tn[sp] = swap ? t0 : t1;
+                    ++sp;
+                } else overflow = 1;
                 ref = swap ? c.y : c.x;
-            } else if (t0 >= 0.f) ref = c.x;
-            else if (t1 >= 0.f) ref = c.y;
-            else { pop(); if (!alive) break; }
+            } else if (h0 || h1) ref = h0 ? c.x : c.y;
+            else if (SHRINK) {                               // next postponed subtree that can still matter
+                do { --sp; } while (stack_tn[sp] > limit * (1.0f + 2.0f * BVH_SLACK));
+                ref = stack_ref[sp];
+            } else ref = stack_ref[--sp];
         }
-        if (!alive) break;
+        if (ref == BVH_DONE) return;
         const int code = ~ref;                               // ---- leaf
         limit = leaf(code & ((1 << BVH_LEAF_SHIFT) - 1), (code >> BVH_LEAF_SHIFT) + 1, limit);
         if (limit < 0.f) return;
-        pop();
+        if (SHRINK) {
+            do { --sp; } while (stack_tn[sp] > limit * (1.0f + 2.0f * BVH_SLACK));
+            ref = stack_ref[sp];
+        } else ref = stack_ref[--sp];
     }
 }
 
@@ -383,7 +395,7 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
         int best_id = -1;
         if (s.bvh_n_prims > 0) {
             const TriRec* __restrict__ tri = s.bvh_tri;
-            bvh_traverse(s, o, d, 3.0e38f, [&](int first, int count, float limit) -> float {
+            bvh_traverse<true>(s, o, d, 3.0e38f, [&](int first, int count, float limit) -> float {
                 for (int k = 0; k < count; ++k) {
                     const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
                     float tt;
@@ -461,7 +473,7 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
         int n_list = 0;
         if (s.bvh_n_prims > 0) {
             const TriRec* __restrict__ tri = s.bvh_tri;
-            bvh_traverse(s, o, d, dist, [&](int first, int count, float limit) -> float {
+            bvh_traverse<false>(s, o, d, dist, [&](int first, int count, float limit) -> float {
                 n_tests += (unsigned)count;
                 for (int k = 0; k < count; ++k) {
                     const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
@@ -707,11 +719,17 @@ int bvh_build(rtb200_ctx* c)
             (e = b->parent.ensure(4 * nn)) != cudaSuccess || (e = b->leaf_parent.ensure(4 * nn)) != cudaSuccess ||
             (e = b->gamma.ensure(4 * nn)) != cudaSuccess || (e = b->flags.ensure(4 * nn)) != cudaSuccess)
             return set_cuda_error(c, e, "bvh buffers");
+        // Morton cells are CUBES (one scale for the three axes, the largest extent): with a scale per axis a
+        // flat scene (a terrain: 2000 x 120 x 2000) is cut into horizontal sheets at every third level, and
+        // rays cross those sheets all the time (config 4: 27 -> 18 nodes per ray with cubes).
+        // RTB200_BVH_ANISO=1 restores the per-axis scale for A/B measurements.
         Bounds6 bb;
+        const bool aniso = getenv("RTB200_BVH_ANISO") != nullptr;
+        const float ext_max = std::max(b->hi[0] - b->lo[0], std::max(b->hi[1] - b->lo[1], b->hi[2] - b->lo[2]));
         for (int k = 0; k < 3; ++k) {
             bb.lo[k] = b->lo[k];
-            const float ext = b->hi[k] - b->lo[k];
-            bb.inv[k] = ext > 0.f ? 1.0f / ext : 0.0f;
+            const float ext = aniso ? b->hi[k] - b->lo[k] : ext_max;
+            bb.inv[k] = ext > 0.f && std::isfinite(ext) ? 1.0f / ext : 0.0f;
         }
         const int blocks = (n + 255) / 256;
         k_bvh_morton<<<blocks, 256, 0, c->stream>>>(c->ds.tri, T, tq, n, bb, b->keys.as<unsigned long long>(), b->idx.as<unsigned int>());
