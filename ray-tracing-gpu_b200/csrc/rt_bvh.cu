@@ -435,12 +435,10 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
         p.hit[slot] = make_float2(best_t, __int_as_float(best_id));
     }
     // statistics: one atomic per warp and counter
-    for (int off = 16; off > 0; off >>= 1) {
-        n_nodes += __shfl_xor_sync(FULL_MASK, n_nodes, off);
-        n_tests += __shfl_xor_sync(FULL_MASK, n_tests, off);
-        n_qtests += __shfl_xor_sync(FULL_MASK, n_qtests, off);
-        overflow |= __shfl_xor_sync(FULL_MASK, overflow, off);
-    }
+    n_nodes = __reduce_add_sync(FULL_MASK, n_nodes);         // one REDUX each instead of five shuffle rounds
+    n_tests = __reduce_add_sync(FULL_MASK, n_tests);
+    n_qtests = __reduce_add_sync(FULL_MASK, n_qtests);
+    overflow = __reduce_or_sync(FULL_MASK, overflow);
     if (lane == 0 && p.stats) {
         unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
         if (n_nodes) atomicAdd(&st[ST_BVH_NODES], (unsigned long long)n_nodes);
@@ -539,13 +537,11 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
         }
         p.filter[i] = make_float4(fr, fg, fb, 0.f);
     }
-    for (int off = 16; off > 0; off >>= 1) {
-        n_nodes += __shfl_xor_sync(FULL_MASK, n_nodes, off);
-        n_tests += __shfl_xor_sync(FULL_MASK, n_tests, off);
-        n_side_q += __shfl_xor_sync(FULL_MASK, n_side_q, off);
-        n_side_p += __shfl_xor_sync(FULL_MASK, n_side_p, off);
-        overflow |= __shfl_xor_sync(FULL_MASK, overflow, off);
-    }
+    n_nodes = __reduce_add_sync(FULL_MASK, n_nodes);
+    n_tests = __reduce_add_sync(FULL_MASK, n_tests);
+    n_side_q = __reduce_add_sync(FULL_MASK, n_side_q);
+    n_side_p = __reduce_add_sync(FULL_MASK, n_side_p);
+    overflow = __reduce_or_sync(FULL_MASK, overflow);
     if (lane == 0 && p.stats) {
         unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
         if (n_nodes) atomicAdd(&st[ST_BVH_NODES_SHADOW], (unsigned long long)n_nodes);

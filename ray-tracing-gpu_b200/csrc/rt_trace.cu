@@ -395,12 +395,52 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
             const V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
             n_face += dot3<E>(Ld, N) > 0.f ? 1 : 0;
         }
+    // ---- queue slots: ONE atomic per counter and CTA ------------------------------------------------
+    // (one per warp made a quarter of a million atomics on a single address per 4K frame: the kernel spent
+    // a third of its time waiting for them, ncu source page of config 4)
+    bool want_refl = false, want_refr = false;
+    float e_refl = 0.f, e_refr = 0.f;
+    if (hit && p.f.secondary && p.level < p.f.max_bounces) {
+        e_refl = FP<E>::mul(kr, energy); e_refr = FP<E>::mul(kt, energy);
+        want_refl = e_refl > p.f.min_energy; want_refr = e_refr > p.f.min_energy;
+    }
+    const unsigned int m_refl = __ballot_sync(FULL_MASK, want_refl), m_refr = __ballot_sync(FULL_MASK, want_refr);
+    const unsigned int n_refl = __popc(m_refl), n_refr = __popc(m_refr), m_any = m_refl | m_refr;
     int incl = n_face;
     for (int off = 1; off < 32; off <<= 1) { const int v = __shfl_up_sync(FULL_MASK, incl, off); if (lane >= off) incl += v; }
-    unsigned int base = 0;
     const int total = __shfl_sync(FULL_MASK, incl, 31);
-    if (lane == 31 && total > 0) base = atomicAdd(p.sq_count, (unsigned int)total);
-    base = __shfl_sync(FULL_MASK, base, 31);
+    __shared__ uint4 s_cnt[8];                               // per warp: queries, reflected, refracted, links
+    __shared__ uint4 s_base[8];
+    const int warp = threadIdx.x >> 5;
+    if (lane == 0) s_cnt[warp] = make_uint4((unsigned int)total, n_refl, n_refr, (unsigned int)__popc(m_any));
+    __syncthreads();
+    if (warp == 0) {
+        const uint4 c = lane < 8 ? s_cnt[lane] : make_uint4(0u, 0u, 0u, 0u);
+        const unsigned int kids = c.y + c.z;
+        unsigned int iq = c.x, ik = kids, il = c.w;           // inclusive scans over the 8 warps
+        for (int off = 1; off < 8; off <<= 1) {
+            const unsigned int vq = __shfl_up_sync(FULL_MASK, iq, off), vk = __shfl_up_sync(FULL_MASK, ik, off), vl = __shfl_up_sync(FULL_MASK, il, off);
+            if (lane >= off) { iq += vq; ik += vk; il += vl; }
+        }
+        const unsigned int tq = __shfl_sync(FULL_MASK, iq, 7), tk = __shfl_sync(FULL_MASK, ik, 7), tl = __shfl_sync(FULL_MASK, il, 7);
+        const unsigned int t_refl = __reduce_add_sync(FULL_MASK, c.y), t_refr = __reduce_add_sync(FULL_MASK, c.z);
+        unsigned int bq = 0, bk = 0, bl = 0;
+        if (lane == 0) {
+            if (tq) bq = atomicAdd(p.sq_count, tq);
+            if (tk) {
+                bk = atomicAdd(p.out_count, tk);
+                bl = atomicAdd(p.link_count, tl);
+                unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+                if (t_refl) atomicAdd(&st[ST_REFLECT], (unsigned long long)t_refl);
+                if (t_refr) atomicAdd(&st[ST_REFRACT], (unsigned long long)t_refr);
+            }
+        }
+        bq = __shfl_sync(FULL_MASK, bq, 0); bk = __shfl_sync(FULL_MASK, bk, 0); bl = __shfl_sync(FULL_MASK, bl, 0);
+        if (lane < 8) s_base[lane] = make_uint4(bq + iq - c.x, bk + ik - kids, bl + il - c.w, 0u);
+    }
+    __syncthreads();
+    const uint4 wb = s_base[warp];
+    const unsigned int base = wb.x;
     int q = (int)base + incl - n_face;
     if (valid) {
         p.q_base[i] = q;
@@ -419,24 +459,8 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
             }
         }
     // ---- children --------------------------------------------------------------------------------
-    bool want_refl = false, want_refr = false;
-    float e_refl = 0.f, e_refr = 0.f;
-    if (hit && p.f.secondary && p.level < p.f.max_bounces) {
-        e_refl = FP<E>::mul(kr, energy); e_refr = FP<E>::mul(kt, energy);
-        want_refl = e_refl > p.f.min_energy; want_refr = e_refr > p.f.min_energy;
-    }
-    const unsigned int m_refl = __ballot_sync(FULL_MASK, want_refl), m_refr = __ballot_sync(FULL_MASK, want_refr);
-    if (m_refl | m_refr) {
-        const unsigned int n_refl = __popc(m_refl), n_refr = __popc(m_refr), m_any = m_refl | m_refr;
-        unsigned int cbase = 0, lbase = 0;
-        if (lane == 0) {
-            cbase = atomicAdd(p.out_count, n_refl + n_refr);
-            lbase = atomicAdd(p.link_count, (unsigned int)__popc(m_any));
-            unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
-            if (n_refl) atomicAdd(&st[ST_REFLECT], (unsigned long long)n_refl);
-            if (n_refr) atomicAdd(&st[ST_REFRACT], (unsigned long long)n_refr);
-        }
-        cbase = __shfl_sync(FULL_MASK, cbase, 0); lbase = __shfl_sync(FULL_MASK, lbase, 0);
+    if (m_any) {
+        const unsigned int cbase = wb.y, lbase = wb.z;
         const unsigned int below = (1u << lane) - 1u;
         int s_refl = -1, s_refr = -1;
         if (want_refl) {
