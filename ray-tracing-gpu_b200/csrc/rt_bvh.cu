@@ -453,7 +453,7 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
 // (0 * finite = 0), so the traversal may stop there; transparent occluders are collected and
 // multiplied in insertion order, the order of the linear scan.
 template <int MODE, bool QUADS>
-__global__ void __launch_bounds__(BVH_THREADS)
+__global__ void __launch_bounds__(BVH_THREADS, 9)          // 56 registers: 9 CTAs per SM (64 registers: +6 % time)
 k_bvh_shadow(const __grid_constant__ ShadowParams p)
 {
     const DeviceScene& s = p.s;
@@ -461,9 +461,9 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
     const int i = blockIdx.x * BVH_THREADS + threadIdx.x;
     unsigned n_nodes = 0, n_tests = 0, overflow = 0, n_side_q = 0, n_side_p = 0;
     if (i < p.n_queries) {
-        const float4 a = p.sq0[i], b = p.sq1[i];
-        const V3 o = f4_xyz(a), d = f4_xyz(b);
-        const float dist = a.w;
+        V3 o, d;
+        float dist;
+        shadow_query<(MODE != 2)>(p, i, o, d, dist);
         const float tlim = fmaf(dist, CULL_TREL, CULL_TABS);
         float fr = 1.0f, fg = 1.0f, fb = 1.0f;
         bool zero = false;

@@ -29,7 +29,7 @@ using namespace rtb;
 namespace rtb {
 
 struct StreamBufs {                // per-context scratch of the streamed path (lives in the ctx levels + these)
-    DevBuf hit, hitP, hitN, q_base, sq0, sq1, filter;
+    DevBuf hit, hitP, hitN, q_base, sq0, sq1, sq_src, filter;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // per-stage stopwatch
 };
 
@@ -43,7 +43,7 @@ void stream_release(rtb200_ctx* c)
 {
     if (!c->stream_scratch) return;
     StreamBufs* b = static_cast<StreamBufs*>(c->stream_scratch);
-    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->filter.release();
+    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->filter.release();
     for (auto& e : b->ev) if (e) cudaEventDestroy(e);
     delete b;
     c->stream_scratch = nullptr;
@@ -110,7 +110,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             const size_t n = (size_t)n_in;
             if ((e = sb->hit.ensure(sizeof(float2) * n)) != cudaSuccess || (e = sb->hitP.ensure(sizeof(float4) * n)) != cudaSuccess ||
                 (e = sb->hitN.ensure(sizeof(float4) * n)) != cudaSuccess || (e = sb->q_base.ensure(sizeof(int) * n)) != cudaSuccess ||
-                (e = sb->sq0.ensure(sizeof(float4) * n * std::max(L, 1))) != cudaSuccess || (e = sb->sq1.ensure(sizeof(float4) * n * std::max(L, 1))) != cudaSuccess ||
+                (e = sb->sq_src.ensure(sizeof(int2) * n * std::max(L, 1))) != cudaSuccess ||
                 (e = sb->filter.ensure(sizeof(float4) * n * std::max(L, 1))) != cudaSuccess)
                 return set_cuda_error(c, e, "stream scratch");
             if (level > 0 && (e = cur.colour.ensure(sizeof(float4) * n)) != cudaSuccess) return set_cuda_error(c, e, "colour");
@@ -145,7 +145,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             sa.chunk_ly0 = ly0; sa.chunk_rows = rows; sa.local_LH = local_LH;
             sa.in_od0 = tp.in_od0; sa.in_od1 = tp.in_od1; sa.n_rays = n_in; sa.hit = tp.hit;
             sa.hitP = sb->hitP.as<float4>(); sa.hitN = sb->hitN.as<float4>(); sa.q_base = sb->q_base.as<int>();
-            sa.sq0 = sb->sq0.as<float4>(); sa.sq1 = sb->sq1.as<float4>();
+            sa.sq_src = sb->sq_src.as<int2>();
             sa.out_od0 = nxt.od0.as<float4>(); sa.out_od1 = nxt.od1.as<float4>();
             sa.out_count = d_cnt + 4 * level; sa.link_count = d_cnt + 4 * level + 1; sa.sq_count = d_cnt + 4 * level + 2;
             sa.links = cur.links.as<int4>();
@@ -170,7 +170,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             if (n_sq > 0) {
                 ShadowParams sp;
                 memset(&sp, 0, sizeof sp);
-                sp.s = c->ds; sp.sq0 = sa.sq0; sp.sq1 = sa.sq1; sp.n_queries = n_sq;
+                sp.s = c->ds; sp.sq_src = sa.sq_src; sp.hitP = sa.hitP; sp.n_queries = n_sq;
                 sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode;
                 if (use_bvh) SCU(launch_bvh_shadow(sp, c->stream));
                 else         SCU(launch_trace_shadow(sp, c->sm_count, c->stream));

@@ -40,8 +40,8 @@ struct ShadeAParams {
     float4* hitP;                  // P.xyz | t
     float4* hitN;                  // N.xyz | order (int bits, -1 = miss)
     int*    q_base;                // first shadow query of the ray
-    float4* sq0;                   // P.xyz | dist
-    float4* sq1;                   // L.xyz (normalised) | 0
+    int2*   sq_src;                // shadow query = (ray of this level, light): the shadow kernels derive P, dist
+                                   // and direction from hitP and the light (8 B per query instead of 32)
     unsigned int* sq_count;
     float4* out_od0;
     float4* out_od1;
@@ -54,8 +54,10 @@ struct ShadeAParams {
 
 struct ShadowParams {
     DeviceScene s;
-    const float4* sq0;
-    const float4* sq1;
+    const float4* sq0;             // explicit queries (rtb200_trace_shadow): P.xyz | dist
+    const float4* sq1;             //                                         L.xyz (normalised) | 0
+    const int2*   sq_src;          // or, inside a frame: (ray, light) pairs over hitP (shade-A), sq0 / sq1 unused
+    const float4* hitP;
     int   n_queries;
     float4* filter;                // r g b | 0 per query
     unsigned long long* stats;
@@ -78,6 +80,23 @@ struct ShadeBParams {
     float4* colour;                // level >= 1 colours
     int   exact;
 };
+
+// One shadow query: origin, unit direction towards the light, distance to it.  The derived form repeats
+// the arithmetic shade-A / shade-B use for the same pair (Scene.cpp:1847-1848), in the same rounding mode.
+template <bool E>
+RT_DEV void shadow_query(const ShadowParams& p, int i, V3& o, V3& d, float& dist)
+{
+    if (p.sq_src) {
+        const int2 src = p.sq_src[i];
+        o = f4_xyz(p.hitP[src.x]);
+        V3 Ld = sub3<E>(f4_xyz(p.s.light[src.y].l0), o);
+        dist = norm3<E>(Ld);
+        d = scale3<E>(Ld, FP<E>::rcp(dist));
+    } else {
+        const float4 a = p.sq0[i], b = p.sq1[i];
+        o = f4_xyz(a); d = f4_xyz(b); dist = a.w;
+    }
+}
 
 cudaError_t launch_trace_nearest(const TraceParams& p, int sm_count, cudaStream_t st);
 cudaError_t launch_shade_a(const ShadeAParams& p, cudaStream_t st);

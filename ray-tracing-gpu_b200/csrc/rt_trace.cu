@@ -225,10 +225,9 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
             const bool valid = i < p.n_queries;
             slot[r] = valid ? i : -1;
             n_valid += valid ? 1 : 0;
-            const float4 a = valid ? p.sq0[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-            const float4 b = valid ? p.sq1[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-            o[r] = f4_xyz(a); d[r] = f4_xyz(b); dist[r] = a.w;
-            tlim[r] = fmaf(a.w, CULL_TREL, CULL_TABS);
+            o[r] = d[r] = mk3(0.f, 0.f, 0.f); dist[r] = 0.f;
+            if (valid) shadow_query<(MODE != 2)>(p, i, o[r], d[r], dist[r]);
+            tlim[r] = fmaf(dist[r], CULL_TREL, CULL_TABS);
             fr[r] = fg[r] = fb[r] = 1.0f;
             if (!valid) { fr[r] = fg[r] = fb[r] = 0.0f; }        // counts as finished
         }
@@ -449,14 +448,8 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
     }
     if (hit)
         for (int l = 0; l < s.rl.n_light; ++l) {
-            V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
-            if (dot3<E>(Ld, N) > 0.f) {
-                const float dist = norm3<E>(Ld);             // Scene.cpp:1847-1848
-                Ld = scale3<E>(Ld, FP<E>::rcp(dist));
-                p.sq0[q] = make_float4(P.x, P.y, P.z, dist);
-                p.sq1[q] = make_float4(Ld.x, Ld.y, Ld.z, 0.f);
-                ++q;
-            }
+            const V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
+            if (dot3<E>(Ld, N) > 0.f) p.sq_src[q++] = make_int2(i, l);    // direction and distance: shadow_query()
         }
     // ---- children --------------------------------------------------------------------------------
     if (m_any) {
