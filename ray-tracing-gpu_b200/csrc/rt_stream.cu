@@ -55,6 +55,16 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     StreamBufs* sb = stream_bufs(c);
     const int mode = (fr->flags & RTB200_F_FUSED_FP) ? 2 : ((fr->flags & RTB200_F_EXACT_FP) ? 1 : 0);
     const bool use_bvh = (fr->flags & RTB200_F_USE_BVH) != 0;
+    // warp <-> shadow query mapping of the LBVH kernel: by light when >= 64 lattice samples start on the average
+    // primitive and the light count lets a stride of 8 separate the lights (RTB200_SHADOW_BY_LIGHT=0/1 forces it)
+    bool shadow_by_light = false;
+    if (use_bvh) {
+        const int L = c->ds.rl.n_light;
+        const double prims = (double)std::max(c->ds.bvh_n_prims, 1);
+        const double samples = (double)fr->width * fr->height * std::max(fr->spp_grid, 1) * std::max(fr->spp_grid, 1);
+        shadow_by_light = L > 1 && (8 % L == 0 || L % 8 == 0) && samples / prims >= 64.0;
+        if (const char* e = getenv("RTB200_SHADOW_BY_LIGHT")) shadow_by_light = atoi(e) != 0;
+    }
     if (use_bvh) {                               // boxes must be padded for rays that start at the camera
         const int rc = bvh_prepare(c, fr->cam_pos, 1);
         if (rc != RTB200_OK) return rc;
@@ -171,6 +181,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 ShadowParams sp;
                 memset(&sp, 0, sizeof sp);
                 sp.s = c->ds; sp.sq_src = sa.sq_src; sp.hitP = sa.hitP; sp.n_queries = n_sq;
+                sp.by_light = shadow_by_light ? 1 : 0;
                 sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode;
                 if (use_bvh) SCU(launch_bvh_shadow(sp, c->stream));
                 else         SCU(launch_trace_shadow(sp, c->sm_count, c->stream));

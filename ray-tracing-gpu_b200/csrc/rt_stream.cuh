@@ -58,6 +58,7 @@ struct ShadowParams {
     const float4* sq1;             //                                         L.xyz (normalised) | 0
     const int2*   sq_src;          // or, inside a frame: (ray, light) pairs over hitP (shade-A), sq0 / sq1 unused
     const float4* hitP;
+    int   by_light;                // LBVH: lanes of a warp share the light rather than the hit (see k_bvh_shadow)
     int   n_queries;
     float4* filter;                // r g b | 0 per query
     unsigned long long* stats;
