@@ -151,6 +151,8 @@ typedef struct rtb200_stats {
     uint64_t level_loop_redone;    /* 1: the frame's levels were first enqueued without host round trips,   */
                                    /* a guessed queue capacity proved too small and the frame was redone    */
                                    /* with exact capacities (same pixels, slower)                           */
+    uint64_t tests_triangle_executed; /* streamed path: (ray, triangle) tests actually entered after the warp-level */
+                                   /* bundle culling (tests_triangle counts what the reference's scan performs)   */
 } rtb200_stats;
 
 typedef struct rtb200_ctx rtb200_ctx;

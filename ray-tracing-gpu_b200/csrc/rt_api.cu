@@ -1061,6 +1061,7 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     } else {
         st.shadow_tests_triangle = sum[ST_TEST_TRI_SHADOW];
         st.shadow_bvh_nodes = sum[ST_BVH_NODES_SHADOW];
+        st.tests_triangle_executed = sum[ST_TEST_TRI_EXEC];
         st.tests_triangle = sum[ST_TEST_TRI] + sum[ST_TEST_TRI_SHADOW] + ctx->host_tests[0];
         st.tests_quadric = sum[ST_TEST_QUAD] + ctx->host_tests[1];
         st.tests_plane = sum[ST_TEST_PLANE] + ctx->host_tests[2];

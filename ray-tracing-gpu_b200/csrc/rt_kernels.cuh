@@ -7,7 +7,7 @@ namespace rtb {
 #define RT_STAT_SLOTS 64           // counters are spread over 64 slots to keep atomics apart
 enum {                             // per-slot counter index
     ST_SHADOW = 0, ST_REFLECT, ST_REFRACT, ST_NAN, ST_TEST_TRI, ST_TEST_QUAD, ST_TEST_PLANE, ST_BVH_NODES,
-    ST_BVH_OVERFLOW, ST_TEST_TRI_SHADOW, ST_BVH_NODES_SHADOW,
+    ST_BVH_OVERFLOW, ST_TEST_TRI_SHADOW, ST_BVH_NODES_SHADOW, ST_TEST_TRI_EXEC,
     ST_COUNT
 };
 

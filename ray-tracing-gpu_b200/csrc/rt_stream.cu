@@ -9,6 +9,7 @@
 // The host reads three counters per level (children, links, shadow queries) to size the next
 // launches exactly; nothing else crosses the bus during a frame.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -32,6 +33,13 @@ struct StreamBufs {                // per-context scratch of the streamed path (
     DevBuf hit, hitP, hitN, q_base, sq0, sq1, sq_src, filter;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // per-stage stopwatch
 };
+
+// warp-bundle culling of the tiled kernels (rt_trace.cu); RTB200_NO_BUNDLE_CULL=1 turns it off for A/B runs
+static int bundle_cull_enabled()
+{
+    const char* e = getenv("RTB200_NO_BUNDLE_CULL");
+    return (e && atoi(e) != 0) ? 0 : 1;
+}
 
 static StreamBufs* stream_bufs(rtb200_ctx* c)
 {
@@ -136,7 +144,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             tp.f = fp; tp.s = c->ds; tp.primary = (level == 0);
             tp.chunk_ly0 = ly0; tp.chunk_rows = rows; tp.local_LH = local_LH;
             tp.in_od0 = cur.od0.as<float4>(); tp.in_od1 = cur.od1.as<float4>();
-            tp.n_rays = n_in; tp.hit = sb->hit.as<float2>(); tp.mode = mode;
+            tp.n_rays = n_in; tp.hit = sb->hit.as<float2>(); tp.mode = mode; tp.cull_bundles = bundle_cull_enabled();
             const bool timed = !timed_first && level == 0;
             if (timed) SCU(cudaEventRecord(ev_a, c->stream));
             SCU(cudaEventRecord(E[0], c->stream));
@@ -182,7 +190,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 memset(&sp, 0, sizeof sp);
                 sp.s = c->ds; sp.sq_src = sa.sq_src; sp.hitP = sa.hitP; sp.n_queries = n_sq;
                 sp.by_light = shadow_by_light ? 1 : 0;
-                sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode;
+                sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode; sp.cull_bundles = bundle_cull_enabled();
                 if (use_bvh) SCU(launch_bvh_shadow(sp, c->stream));
                 else         SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
                 ++*launches;
@@ -257,7 +265,7 @@ int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
     TraceParams tp;
     memset(&tp, 0, sizeof tp);
     tp.s = c->ds; tp.primary = 0; tp.in_od0 = sb->sq0.as<float4>(); tp.in_od1 = sb->sq1.as<float4>();
-    tp.n_rays = n; tp.hit = sb->hit.as<float2>(); tp.mode = mode;
+    tp.n_rays = n; tp.hit = sb->hit.as<float2>(); tp.mode = mode; tp.cull_bundles = bundle_cull_enabled();
     if (flags & RTB200_F_USE_BVH) SCU(launch_bvh_nearest(tp, c->stream));
     else                          SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
     SCU(launch_query_finish_nearest(c->ds, n, tp.in_od0, tp.in_od1, tp.hit, c->q_out0.as<int>(), c->q_out1.as<float>(),

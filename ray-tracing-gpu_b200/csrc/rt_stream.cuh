@@ -9,7 +9,7 @@ namespace rtb {
 #define ST_BLOCK_RAYS (ST_THREADS * ST_RPT)
 #define ST_TILE      256           // triangles per shared-memory tile (12 KB)
 #define ST_STAGES    2
-#define ST_SIDE_MAX  16384         // bytes of quadric + plane records kept in shared memory
+#define ST_SIDE_MAX  8192          // bytes of quadric + plane records kept in shared memory (170 quadrics)
 
 // nearest hit of every ray of one wavefront level against ALL surfaces (tiled brute force)
 struct TraceParams {
@@ -25,6 +25,7 @@ struct TraceParams {
                                    // 1: no filter, reference sequence for every test (EXACT_FP)
                                    // 2: filter + fused survivors (FUSED_FP)
     unsigned long long* stats;     // LBVH kernels: nodes visited / triangle tests (may be null)
+    int   cull_bundles;            // tiled kernels: cull whole triangles per warp against the cone of its rays
 };
 
 // shade-A: hit point, normal, shadow queries of the facing lights, children
@@ -63,6 +64,7 @@ struct ShadowParams {
     float4* filter;                // r g b | 0 per query
     unsigned long long* stats;
     int   mode;
+    int   cull_bundles;            // tiled kernel: per-light cones of the warp's queries (needs sq_src)
 };
 
 // shade-B: ambient + per-light diffuse/Phong with the shadow filters, in light order

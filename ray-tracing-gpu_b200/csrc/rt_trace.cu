@@ -26,8 +26,238 @@ namespace rtb {
 struct TraceSmem {
     TriRec tile[ST_STAGES][ST_TILE];                 // 24 KB
     unsigned char side[ST_SIDE_MAX];                 // quadric + plane records (when they fit)
+    float4 sphere[ST_TILE];                          // bounding spheres of the current tile: centre | radius ...
+    float  sphere_w[ST_TILE];                        // ... and |e1| |e2| (warp-bundle culling)
     uint64_t full[ST_STAGES];
 };
+
+// ---------------------------------------------------------------------------------------
+// Warp bundles: whole triangles are culled per WARP before any per-ray arithmetic.
+//
+// The 128 rays of a warp (32 lanes x 4) are bounded by a cone -- apex, unit axis, half angle -- that
+// contains every point a ray of the warp can report a hit at:
+//   * nearest hit: origins within rho of their mean m, directions within theta of their mean u
+//     => all rays lie in the cone of half angle theta around u whose apex sits rho / sin(theta)
+//     behind m (the ball of origins is inscribed in it); primary rays: rho = 0, apex = camera;
+//   * shadow queries of one light: the segments hit point -> light lie in the cone with the LIGHT
+//     as apex around the mean direction light -> hit points, and within `far` = the largest distance.
+// In a round of the tile loop lane j takes triangle j of a group of 32, builds its bounding sphere
+// (centroid, largest vertex distance), inflates it and tests it against the cone(s); the ballot of
+// the survivors is the list of triangles the warp then tests ray by ray with the unchanged filter +
+// reference-sequence code.  A culled triangle is one no ray of the warp can be reported to hit, so
+// every kept value is still the reference's (same contract as the LBVH):
+// CTriangle::Intersection accepts hits up to delta ~ c 2^-24 |S| |e1| |e2| |d| / |det| outside the
+// geometric triangle, |det| >= EPSILON (Triangle.cpp:142), hence the same pad as the LBVH boxes,
+//     pad = PADC 2^-24 / EPSILON  D |e1| |e2| max|d|,   D >= |origin - p0|, floor 32 ulp of D,
+// on top of explicit slack for the rounding of the test itself.  Incoherent warps (theta >= 44 deg,
+// directions in opposite half spaces, non-finite rays) do not cull at all.  Off in RTB200_F_EXACT_FP.
+// ---------------------------------------------------------------------------------------
+#define BUNDLE_PADK  (1.0f * 5.9604645e-8f / RT_EPS)
+#define BUNDLE_MAX_LIGHTS 8
+#define BUNDLE_SPLIT_SIN 0.02f    // a light's cone wider than this (1.1 degrees) is split in two
+
+struct Bundle {
+    float ax, ay, az;              // apex
+    float ux, uy, uz;              // unit axis
+    float sin_t, cos2;             // widened half angle
+    float far;                     // hits lie within `far` of the apex (3e38: unbounded)
+    float dadd;                    // |origin - x| <= |x - apex| + dadd for every origin of the bundle
+    float padk;                    // BUNDLE_PADK * max(1, max |d|)
+    float slack;                   // rounding of apex and centres: 4e-7 * |coordinates|
+    int   state;                   // 0: no rays, 1: cone valid, 2: wide (cannot cull)
+};
+
+RT_DEV float warp_sum(float v)
+{
+    #pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(FULL_MASK, v, off);
+    return v;
+}
+RT_DEV float warp_max_nonneg(float v)          // v >= 0, not NaN: binary32 orders like uint32
+{
+    return __uint_as_float(__reduce_max_sync(FULL_MASK, __float_as_uint(v)));
+}
+RT_DEV bool finite3(V3 a) { return fabsf(a.x) <= 3.0e38f && fabsf(a.y) <= 3.0e38f && fabsf(a.z) <= 3.0e38f; }
+
+// bounding sphere of a triangle record: centroid, largest vertex distance, |e1| |e2|
+RT_DEV void triangle_sphere(V3 p0, V3 e1, V3 e2, V3& c, float& r, float& w)
+{
+    const V3 a0 = mk3((e1.x + e2.x) * (-1.0f / 3.0f), (e1.y + e2.y) * (-1.0f / 3.0f), (e1.z + e2.z) * (-1.0f / 3.0f));   // p0 - c
+    c = mk3(p0.x - a0.x, p0.y - a0.y, p0.z - a0.z);
+    const V3 a1 = mk3(a0.x + e1.x, a0.y + e1.y, a0.z + e1.z), a2 = mk3(a0.x + e2.x, a0.y + e2.y, a0.z + e2.z);
+    const float r2 = fmaxf(dot3<false>(a0, a0), fmaxf(dot3<false>(a1, a1), dot3<false>(a2, a2)));
+    r = sqrtf(r2) * 1.00001f;
+    w = sqrtf(dot3<false>(e1, e1) * dot3<false>(e2, e2)) * 1.00001f;
+}
+
+// true: no point within the inflated sphere lies in the bundle's cone (and range)
+RT_DEV bool bundle_culls(const Bundle& b, V3 c, float r, float w)
+{
+    const float vx = c.x - b.ax, vy = c.y - b.ay, vz = c.z - b.az;
+    const float s = fmaf(vx, b.ux, fmaf(vy, b.uy, vz * b.uz));
+    const float vv = fmaf(vx, vx, fmaf(vy, vy, vz * vz));
+    const float dist = vv * rsqrtf(fmaxf(vv, 1.0e-30f)) * 1.00001f;
+    const float D = dist + b.dadd + r;
+    const float pad = fmaxf(b.padk * D * w, 3.8e-6f * D);
+    const float rp = fmaf(r + pad, 1.0001f, 1.0e-5f + b.slack);
+    // distance of the centre to the cone's boundary line in the (axis, perpendicular) half plane
+    const float cx = fmaf(vy, b.uz, -vz * b.uy), cy = fmaf(vz, b.ux, -vx * b.uz), cz = fmaf(vx, b.uy, -vy * b.ux);
+    const float perp2 = fmaf(cx, cx, fmaf(cy, cy, cz * cz));
+    const float h = fmaf(s, b.sin_t, rp) + 2.0e-6f * dist;
+    bool cull = h < 0.f || perp2 * b.cos2 > h * h;
+    const float fr = b.far + rp;
+    cull = cull || vv > fr * fr;
+    return cull;
+}
+
+// the same for a cone whose apex is a light (moderate distances: the perpendicular distance comes from
+// |v|^2 - s^2, its cancellation error is covered by an explicit slack)
+RT_DEV bool light_cone_culls(const Bundle& b, float4 sph, float w)
+{
+    const float vx = sph.x - b.ax, vy = sph.y - b.ay, vz = sph.z - b.az;
+    const float s = fmaf(vx, b.ux, fmaf(vy, b.uy, vz * b.uz));
+    const float vv = fmaf(vx, vx, fmaf(vy, vy, vz * vz));
+    const float dist = vv * rsqrtf(fmaxf(vv, 1.0e-30f)) * 1.00001f;
+    const float D = dist + b.dadd + sph.w;
+    const float pad = fmaxf(b.padk * D * w, 3.8e-6f * D);
+    const float rp = fmaf(sph.w + pad, 1.0001f, 1.0e-5f + b.slack);
+    const float perp2 = fmaf(-s, s, vv) - 4.0e-6f * vv;           // |axis| = 1 within 3e-7, products rounded
+    const float h = fmaf(s, b.sin_t, rp);
+    const float fr = b.far + rp;
+    return h < 0.f || perp2 * b.cos2 > h * h || vv > fr * fr;
+}
+
+// cone of a set of rays held 4 per lane; `use[r]`: the ray takes part
+RT_DEV Bundle bundle_of_rays(const V3* o, const V3* d, const bool* use)
+{
+    Bundle b;
+    b.ax = b.ay = b.az = 0.f; b.ux = b.uy = b.uz = 0.f; b.sin_t = 0.f; b.cos2 = 1.f;
+    b.far = 3.0e38f; b.dadd = 0.f; b.padk = BUNDLE_PADK; b.slack = 0.f; b.state = 2;
+    float so[3] = {0.f, 0.f, 0.f}, sd[3] = {0.f, 0.f, 0.f}, n = 0.f, dmax2 = 0.f;
+    V3 dn[ST_RPT];
+    bool fin = true;
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r) {
+        dn[r] = mk3(0.f, 0.f, 0.f);
+        if (use[r]) {
+            const float l2 = dot3<false>(d[r], d[r]);
+            const bool ok = finite3(o[r]) && finite3(d[r]) && l2 > 1.0e-20f && l2 < 1.0e20f;
+            fin = fin && ok;
+            if (ok) {
+                const float il = rsqrtf(l2);
+                dn[r] = mk3(d[r].x * il, d[r].y * il, d[r].z * il);
+                so[0] += o[r].x; so[1] += o[r].y; so[2] += o[r].z;
+                sd[0] += dn[r].x; sd[1] += dn[r].y; sd[2] += dn[r].z;
+                dmax2 = fmaxf(dmax2, l2);
+                n += 1.0f;
+            }
+        }
+    }
+    n = warp_sum(n);
+    fin = __all_sync(FULL_MASK, fin);
+    if (n == 0.f && fin) { b.state = 0; return b; }
+    if (!fin) return b;
+    #pragma unroll
+    for (int k = 0; k < 3; ++k) { so[k] = warp_sum(so[k]); sd[k] = warp_sum(sd[k]); }
+    dmax2 = warp_max_nonneg(dmax2);
+    const float inv_n = 1.0f / n;
+    const V3 m = mk3(so[0] * inv_n, so[1] * inv_n, so[2] * inv_n);
+    const float len2 = fmaf(sd[0], sd[0], fmaf(sd[1], sd[1], sd[2] * sd[2]));
+    if (!(len2 > 0.25f * n * n)) return b;                      // mean direction shorter than 0.5: incoherent
+    const float il = 1.0f / sqrtf(len2);
+    const V3 u = mk3(sd[0] * il, sd[1] * il, sd[2] * il);
+    float rho2 = 0.f, sin2 = 0.f;
+    bool fwd = true;
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r)
+        if (use[r]) {
+            const V3 q = mk3(o[r].x - m.x, o[r].y - m.y, o[r].z - m.z);
+            rho2 = fmaxf(rho2, dot3<false>(q, q));
+            const V3 x = cross3<false>(u, dn[r]);
+            sin2 = fmaxf(sin2, dot3<false>(x, x));
+            fwd = fwd && dot3<false>(u, dn[r]) > 0.5f;
+        }
+    rho2 = warp_max_nonneg(rho2); sin2 = warp_max_nonneg(sin2);
+    fwd = __all_sync(FULL_MASK, fwd);
+    if (!fwd) return b;
+    const float sin_e = fmaxf(fmaf(sqrtf(sin2), 1.0001f, 2.0e-6f), 1.0e-4f);
+    if (!(sin_e < 0.7f)) return b;
+    const float m1 = fabsf(m.x) + fabsf(m.y) + fabsf(m.z);
+    const float rho_e = fmaf(sqrtf(rho2), 1.0001f, 2.0e-6f * m1 + 1.0e-6f);
+    const float shift = rho_e / sin_e * 1.00001f;
+    b.ax = m.x - u.x * shift; b.ay = m.y - u.y * shift; b.az = m.z - u.z * shift;
+    b.ux = u.x; b.uy = u.y; b.uz = u.z;
+    b.sin_t = sin_e; b.cos2 = 1.0f - sin_e * sin_e;
+    b.slack = 4.0e-7f * (m1 + shift);
+    b.dadd = (shift + rho_e) * 1.0001f + b.slack;
+    b.padk = BUNDLE_PADK * fmaxf(1.0f, sqrtf(dmax2) * 1.00001f);
+    b.state = 1;
+    return b;
+}
+
+// direction (one of 4 per lane) of the member with the largest key >= 0 over the warp; unspecified without members
+RT_DEV V3 warp_pick(const V3* v, const float* key, const bool* in)
+{
+    float best = -1.0f;
+    V3 mine = mk3(0.f, 0.f, 0.f);
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r)
+        if (in[r] && key[r] > best) { best = key[r]; mine = v[r]; }
+    const float kb = fmaxf(best, 0.f);
+    const float m = warp_max_nonneg(kb);
+    const unsigned int who = __ballot_sync(FULL_MASK, best >= 0.f && kb == m);
+    const int src = who ? __ffs((int)who) - 1 : 0;
+    return mk3(__shfl_sync(FULL_MASK, mine.x, src), __shfl_sync(FULL_MASK, mine.y, src), __shfl_sync(FULL_MASK, mine.z, src));
+}
+
+// cone of the shadow queries of light `l` held 4 per lane (apex = the light); d = unit directions TOWARDS the light
+RT_DEV Bundle bundle_of_light(V3 L, const V3* d, const float* dist, const bool* in)
+{
+    Bundle b;
+    b.ax = L.x; b.ay = L.y; b.az = L.z; b.ux = b.uy = b.uz = 0.f; b.sin_t = 0.f; b.cos2 = 1.f;
+    b.far = 3.0e38f; b.dadd = 0.f; b.padk = BUNDLE_PADK * 1.0001f; b.state = 2;
+    b.slack = 4.0e-7f * (fabsf(L.x) + fabsf(L.y) + fabsf(L.z));
+    float sd[3] = {0.f, 0.f, 0.f}, n = 0.f, far = 0.f;
+    bool fin = true;
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r)
+        if (in[r]) {
+            const bool ok = finite3(d[r]) && dist[r] >= 0.f && dist[r] <= 3.0e38f;
+            fin = fin && ok;
+            if (ok) { sd[0] -= d[r].x; sd[1] -= d[r].y; sd[2] -= d[r].z; far = fmaxf(far, dist[r]); n += 1.0f; }
+        }
+    n = warp_sum(n);
+    fin = __all_sync(FULL_MASK, fin) && finite3(L);
+    if (n == 0.f && fin) { b.state = 0; return b; }
+    if (!fin) return b;
+    #pragma unroll
+    for (int k = 0; k < 3; ++k) sd[k] = warp_sum(sd[k]);
+    far = warp_max_nonneg(far);
+    const float len2 = fmaf(sd[0], sd[0], fmaf(sd[1], sd[1], sd[2] * sd[2]));
+    if (!(len2 > 0.25f * n * n)) return b;
+    const float il = 1.0f / sqrtf(len2);
+    const V3 u = mk3(sd[0] * il, sd[1] * il, sd[2] * il);
+    float sin2 = 0.f;
+    bool fwd = true;
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r)
+        if (in[r]) {
+            const V3 x = cross3<false>(u, d[r]);
+            sin2 = fmaxf(sin2, dot3<false>(x, x));
+            fwd = fwd && -dot3<false>(u, d[r]) > 0.5f;
+        }
+    sin2 = warp_max_nonneg(sin2);
+    fwd = __all_sync(FULL_MASK, fwd);
+    if (!fwd) return b;
+    const float sin_e = fmaf(sqrtf(sin2), 1.0002f, 4.0e-6f);       // |d| = 1 within a few ulp (normalised by the query)
+    if (!(sin_e < 0.7f)) return b;
+    b.ux = u.x; b.uy = u.y; b.uz = u.z;
+    b.sin_t = sin_e; b.cos2 = 1.0f - sin_e * sin_e;
+    b.far = fmaf(far, 1.0001f, 1.0e-4f);
+    b.dadd = b.far + b.slack;
+    b.state = 1;
+    return b;
+}
 
 // ---------------------------------------------------------------------------------------
 // Nearest hit.  One CTA = 1024 rays.  PRIMARY: the rays are a 32x32 tile of the sample lattice
@@ -61,6 +291,8 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
     const int tiles_x = (p.f.LW + 31) >> 5;
     const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + 31) >> 5) : (p.n_rays + ST_BLOCK_RAYS - 1) / ST_BLOCK_RAYS;
     uint32_t phase_bits = 0;                         // parity of each stage's barrier
+    unsigned int n_exec = 0;                         // triangles this warp tested ray by ray (survivors of the bundle cull)
+    unsigned long long exec_rays = 0;                // ... times the rays it held
 
     for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
         // ---- this thread's 4 rays ------------------------------------------------------------
@@ -79,7 +311,7 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
                 slot[r] = valid ? cy * p.f.LW + lx : -1;
                 primary_ray<(MODE != 2)>(p.f, valid ? lx : 0, valid ? global_lattice_row(p.f, ly) : 0, o[r], d[r]);
             } else {
-                const int i = blk * ST_BLOCK_RAYS + r * ST_THREADS + tid;
+                const int i = blk * ST_BLOCK_RAYS + warp * (32 * ST_RPT) + r * 32 + lane;   // a warp = 128 consecutive rays
                 valid = i < p.n_rays;
                 slot[r] = valid ? i : -1;
                 const float4 a = valid ? p.in_od0[i] : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -88,6 +320,15 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
             }
             if (!valid) d[r] = mk3(0.f, 0.f, 0.f);     // zero direction: det = 0, nothing can hit
             best_t[r] = -1.0f; best_id[r] = -1; tlim[r] = 3.0e38f;
+        }
+        // the cone that holds the warp's 128 rays (see "warp bundles" above)
+        Bundle bun;
+        bun.state = 2;
+        if (MODE != 1 && p.cull_bundles) {
+            bool use[ST_RPT];
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) use[r] = slot[r] >= 0;
+            bun = bundle_of_rays(o, d, use);
         }
 
         // ---- triangles: double-buffered TMA tiles ---------------------------------------------
@@ -105,18 +346,29 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
             mbar_wait(&sm.full[st], (phase_bits >> st) & 1u);
             phase_bits ^= (1u << st);
             const TriRec* __restrict__ tile = sm.tile[st];
+            if (MODE != 1 && p.cull_bundles) {       // bounding sphere of triangle `tid`, once per CTA and tile
+                V3 c; float rad, w;
+                triangle_sphere(f4_xyz(tile[tid].a), f4_xyz(tile[tid].b), f4_xyz(tile[tid].c), c, rad, w);
+                sm.sphere[tid] = make_float4(c.x, c.y, c.z, rad); sm.sphere_w[tid] = w;
+                __syncthreads();
+            }
 
-            #pragma unroll 2
-            for (int j = 0; j < ST_TILE; ++j) {
-                const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
-                const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
-                if (MODE == 1) {                     // no filter: the reference sequence for every test
+            if (MODE == 1) {                         // no filter: the reference sequence for every test
+                #pragma unroll 2
+                for (int j = 0; j < ST_TILE; ++j) {
+                    const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
+                    const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
                     #pragma unroll
                     for (int r = 0; r < ST_RPT; ++r) {
                         const float tt = triangle_t<true>(o[r], d[r], p0, e1, e2);
                         if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f)) { best_t[r] = tt; best_id[r] = __float_as_int(ra.w); }
                     }
-                } else {
+                }
+            } else {
+                // filter + reference-rounded survivors for triangle j of the tile, all 4 rays of the thread
+                auto test_triangle = [&](int j) {
+                    const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
+                    const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
                     bool cand[ST_RPT];
                     bool any = false;
                     #pragma unroll
@@ -139,6 +391,25 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
                                 }
                             }
                         }
+                    }
+                };
+                if (bun.state == 2) {                // no usable cone (or culling off): the plain scan of the tile
+                    n_exec += (unsigned int)min(ST_TILE, s.n_tri - t * ST_TILE);
+                    #pragma unroll 2
+                    for (int j = 0; j < ST_TILE; ++j) test_triangle(j);
+                } else
+                for (int j0 = 0; j0 < ST_TILE; j0 += 32) {
+                    unsigned int keep_mask;
+                    {                                // lane j looks at triangle j0 + j for the whole warp
+                        const float4 sph = sm.sphere[j0 + lane];
+                        const float w = sm.sphere_w[j0 + lane];
+                        const bool keep = w > 0.f && bun.state == 1 && !bundle_culls(bun, mk3(sph.x, sph.y, sph.z), sph.w, w);
+                        keep_mask = __ballot_sync(FULL_MASK, keep);
+                    }
+                    n_exec += (unsigned int)__popc(keep_mask);
+                    while (keep_mask) {
+                        test_triangle(j0 + __ffs((int)keep_mask) - 1);
+                        keep_mask &= keep_mask - 1u;
                     }
                 }
             }
@@ -168,7 +439,13 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
         }
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r)
-            if (slot[r] >= 0) p.hit[slot[r]] = make_float2(best_t[r], __int_as_float(best_id[r]));
+            if (slot[r] >= 0) { p.hit[slot[r]] = make_float2(best_t[r], __int_as_float(best_id[r])); exec_rays += n_exec; }
+        n_exec = 0;
+    }
+    if (MODE != 1 && p.stats) {                      // per-ray triangle tests actually entered
+        #pragma unroll
+        for (int off = 16; off > 0; off >>= 1) exec_rays += __shfl_xor_sync(FULL_MASK, exec_rays, off);
+        if (lane == 0 && exec_rays) atomicAdd(&p.stats[(size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + ST_TEST_TRI_EXEC], exec_rays);
     }
 }
 
@@ -191,8 +468,11 @@ __global__ void __launch_bounds__(ST_THREADS, 2)
 k_trace_shadow(const __grid_constant__ ShadowParams p)
 {
     __shared__ __align__(128) TraceSmem sm;
-    const int tid = threadIdx.x;
+    __shared__ Bundle cones[ST_THREADS / 32][2 * BUNDLE_MAX_LIGHTS];  // per warp and light: one cone, or two after a split
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const DeviceScene& s = p.s;
+    // per-light cones need the (ray, light) form of the queries and at most 8 lights; otherwise nothing is culled
+    const int n_cones = (MODE != 1 && p.cull_bundles && p.sq_src && s.rl.n_light <= BUNDLE_MAX_LIGHTS) ? s.rl.n_light : 0;
     const int n_tiles = s.n_tri_padded / ST_TILE;
     const int side_bytes = (int)(sizeof(QuadRec) * s.n_quad + sizeof(PlaneRec) * s.n_plane);
     const bool side_in_smem = side_bytes <= ST_SIDE_MAX;
@@ -212,18 +492,19 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
 
     const int n_blocks = (p.n_queries + ST_BLOCK_RAYS - 1) / ST_BLOCK_RAYS;
     uint32_t phase_bits = 0;
-    unsigned long long tests_tri = 0, tests_side_q = 0, tests_side_p = 0;
+    unsigned long long tests_tri = 0, tests_side_q = 0, tests_side_p = 0, exec_rays = 0;
 
     for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
         V3 o[ST_RPT], d[ST_RPT];
         float dist[ST_RPT], tlim[ST_RPT], fr[ST_RPT], fg[ST_RPT], fb[ST_RPT];
-        int slot[ST_RPT];
+        int slot[ST_RPT], lid[ST_RPT];
         int n_valid = 0;
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) {
-            const int i = blk * ST_BLOCK_RAYS + r * ST_THREADS + tid;
+            const int i = blk * ST_BLOCK_RAYS + warp * (32 * ST_RPT) + r * 32 + lane;   // a warp = 128 consecutive queries
             const bool valid = i < p.n_queries;
             slot[r] = valid ? i : -1;
+            lid[r] = (valid && n_cones) ? p.sq_src[i].y : -1;
             n_valid += valid ? 1 : 0;
             o[r] = d[r] = mk3(0.f, 0.f, 0.f); dist[r] = 0.f;
             if (valid) shadow_query<(MODE != 2)>(p, i, o[r], d[r], dist[r]);
@@ -232,6 +513,41 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
             if (!valid) { fr[r] = fg[r] = fb[r] = 0.0f; }        // counts as finished
         }
         bool warp_done = false;
+        bool can_cull = n_cones > 0;
+        for (int l = 0; l < n_cones; ++l) {          // the warp's cone(s) per light (uniform values, kept in shared memory)
+            const V3 L = f4_xyz(s.light[l].l0);
+            bool in[ST_RPT];
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) in[r] = lid[r] == l;
+            Bundle b = bundle_of_light(L, d, dist, in), b2;
+            b2 = b; b2.state = 0;
+            if (b.state == 2 || (b.state == 1 && b.sin_t > BUNDLE_SPLIT_SIN)) {
+                // the hit points of a warp often lie on two surfaces at different depths (a silhouette runs through
+                // its 32 pixels): two cones around the two most distant directions are far tighter than one
+                V3 nd[ST_RPT];
+                float key[ST_RPT];
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) { nd[r] = mk3(-d[r].x, -d[r].y, -d[r].z); key[r] = 1.0f; }
+                const V3 seed = warp_pick(nd, key, in);
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) key[r] = fmaxf(1.0f - dot3<false>(nd[r], seed), 0.f);
+                const V3 pa = warp_pick(nd, key, in);
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) key[r] = fmaxf(1.0f - dot3<false>(nd[r], pa), 0.f);
+                const V3 pb = warp_pick(nd, key, in);
+                bool in_a[ST_RPT], in_b[ST_RPT];
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) {
+                    const bool near_a = dot3<false>(nd[r], pa) >= dot3<false>(nd[r], pb);
+                    in_a[r] = in[r] && near_a; in_b[r] = in[r] && !near_a;
+                }
+                const Bundle ba = bundle_of_light(L, d, dist, in_a), bb = bundle_of_light(L, d, dist, in_b);
+                if (ba.state != 2 && bb.state != 2) { b = ba; b2 = bb; }
+            }
+            if (lane == 0) { cones[warp][2 * l] = b; cones[warp][2 * l + 1] = b2; }
+            can_cull = can_cull && b.state != 2;     // one light without a usable cone: every triangle has to be tested
+        }
+        __syncwarp();
 
         if (tid == 0 && n_tiles > 0) {
             mbar_arrive_expect_tx(&sm.full[0], (uint32_t)sizeof(TriRec) * ST_TILE);
@@ -247,21 +563,31 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
             mbar_wait(&sm.full[st], (phase_bits >> st) & 1u);
             phase_bits ^= (1u << st);
             const TriRec* __restrict__ tile = sm.tile[st];
+            if (n_cones) {                           // bounding sphere of triangle `tid`, once per CTA and tile
+                V3 c; float rad, w;
+                triangle_sphere(f4_xyz(tile[tid].a), f4_xyz(tile[tid].b), f4_xyz(tile[tid].c), c, rad, w);
+                sm.sphere[tid] = make_float4(c.x, c.y, c.z, rad); sm.sphere_w[tid] = w;
+                __syncthreads();
+            }
 
             if (!warp_done) {
                 const int real = min(ST_TILE, s.n_tri - t * ST_TILE);
                 tests_tri += (unsigned long long)n_valid * (unsigned long long)real;
-                #pragma unroll 2
-                for (int j = 0; j < ST_TILE; ++j) {
-                    const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
-                    const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
-                    if (MODE == 1) {
+                if (MODE == 1) {
+                    #pragma unroll 2
+                    for (int j = 0; j < ST_TILE; ++j) {
+                        const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
+                        const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
                         #pragma unroll
                         for (int r = 0; r < ST_RPT; ++r) {
                             const float tt = triangle_t<true>(o[r], d[r], p0, e1, e2);
                             if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(rb.w), fr[r], fg[r], fb[r]);
                         }
-                    } else {
+                    }
+                } else {
+                    auto test_triangle = [&](int j) {
+                        const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
+                        const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
                         bool cand[ST_RPT];
                         bool any = false;
                         #pragma unroll
@@ -281,6 +607,29 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
                                     if (tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(rb.w), fr[r], fg[r], fb[r]);
                                 }
                             }
+                        }
+                    };
+                    if (!can_cull) {                 // the plain scan of the tile
+                        exec_rays += (unsigned long long)n_valid * (unsigned long long)real;
+                        #pragma unroll 2
+                        for (int j = 0; j < ST_TILE; ++j) test_triangle(j);
+                    } else
+                    for (int j0 = 0; j0 < ST_TILE; j0 += 32) {
+                        unsigned int keep_mask;
+                        {                            // lane j looks at triangle j0 + j for the whole warp
+                            const float4 sph = sm.sphere[j0 + lane];
+                            const float w = sm.sphere_w[j0 + lane];
+                            bool keep = false;
+                            for (int l = 0; l < 2 * n_cones; ++l) {
+                                const Bundle& b = cones[warp][l];
+                                if (b.state == 1 && !light_cone_culls(b, sph, w)) keep = true;
+                            }
+                            keep_mask = __ballot_sync(FULL_MASK, keep && w > 0.f);
+                        }
+                        exec_rays += (unsigned long long)(__popc(keep_mask) * n_valid);
+                        while (keep_mask) {
+                            test_triangle(j0 + __ffs((int)keep_mask) - 1);
+                            keep_mask &= keep_mask - 1u;
                         }
                     }
                 }
@@ -325,10 +674,12 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
         tests_tri += __shfl_xor_sync(FULL_MASK, tests_tri, off);
         tests_side_q += __shfl_xor_sync(FULL_MASK, tests_side_q, off);
         tests_side_p += __shfl_xor_sync(FULL_MASK, tests_side_p, off);
+        exec_rays += __shfl_xor_sync(FULL_MASK, exec_rays, off);
     }
     if ((tid & 31) == 0) {
         unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
         if (tests_tri) atomicAdd(&st[ST_TEST_TRI_SHADOW], tests_tri);
+        if (exec_rays) atomicAdd(&st[ST_TEST_TRI_EXEC], exec_rays);
         if (tests_side_q) atomicAdd(&st[ST_TEST_QUAD], tests_side_q);
         if (tests_side_p) atomicAdd(&st[ST_TEST_PLANE], tests_side_p);
     }
