@@ -17,7 +17,10 @@
 
 namespace rtb {
 
-#define RES_THREADS 256
+#ifndef RES_THREADS
+#define RES_THREADS 256            // 256: 16x16 lattice tile per CTA (8 warps of 8x4), 128: 16x8
+#endif
+#define RES_TILE_H (RES_THREADS / 16)
 #ifndef RES_MIN_CTAS
 #define RES_MIN_CTAS 3            // 4 (<= 64 registers) was measured slower: spills, 86.0 vs 83.4 us on config 2
 #endif
@@ -229,7 +232,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
     }
     const FrameParams& f = p.f;
     const int tiles_x = (f.LW + 15) >> 4;
-    const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + 15) >> 4) : (in_count + RES_THREADS - 1) / RES_THREADS;
+    const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + RES_TILE_H - 1) / RES_TILE_H) : (in_count + RES_THREADS - 1) / RES_THREADS;
     if (p.peer_ack) peer_frame_wait_ack(p.peer_ack, p.peer_ack_min);      // several GPUs: the frame half is free
     mbar_wait(&bar, 0);
     SceneView sv;
@@ -296,7 +299,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
         tile_x += step_x; tile_y += step_y;
         if (tile_x >= tiles_x) { tile_x -= tiles_x; ++tile_y; }
         const int lx = (tx << 4) + ((warp & 1) << 3) + (lane & 7);
-        const int cy = (ty << 4) + ((warp >> 1) << 2) + (lane >> 3);   // row inside the chunk
+        const int cy = ty * RES_TILE_H + ((warp >> 1) << 2) + (lane >> 3);   // row inside the chunk
         const int ly = p.chunk_ly0 + cy;                                 // local lattice row
         valid = lx < f.LW && cy < p.chunk_rows && ly < p.local_LH;
         self = cy * f.LW + lx;
@@ -623,7 +626,7 @@ cudaError_t launch_resident_level(const LevelParams& p_in, bool exact, int sm_co
     const int max_ctas = g_resident_ctas_per_sm * sm_count;
     const bool pdl = p.pdl == 2;
     if (p.level == 0) {
-        const int tiles_x = (p.f.LW + 15) / 16, tiles_y = (p.chunk_rows + 15) / 16;
+        const int tiles_x = (p.f.LW + 15) / 16, tiles_y = (p.chunk_rows + RES_TILE_H - 1) / RES_TILE_H;
         const dim3 grid((unsigned)std::min(tiles_x * tiles_y, max_ctas));
         return launch_chain(exact ? k_resident_level<true, true> : k_resident_level<false, true>, grid, RES_THREADS, smem, st, pdl, p);
     }

@@ -99,3 +99,79 @@ def test_heightfield_and_supersampling_streamed(rt, renderer, port, synth):
     want, _ = port.render(ps, fr, threads=port.max_threads)
     assert np.allclose(got, want, rtol=0, atol=4e-6)
     assert st.rays_primary == 96 * 64 * 4
+
+
+# ---- warp-bundle culling (rt_trace.cu): whole triangles skipped per warp must change no bit -----------------
+def _frames_equal_exact(rt, renderer, ps, W, H, depth, spp=1):
+    a, a8, sa = renderer.render(rt.make_frame(ps.frame, W, H, max_bounces=depth, spp_grid=spp, flags=rt.F_FORCE_STREAM))
+    b, b8, sb = renderer.render(rt.make_frame(ps.frame, W, H, max_bounces=depth, spp_grid=spp, flags=rt.F_FORCE_STREAM | rt.F_EXACT_FP))
+    assert (sa.rays_shadow, sa.rays_reflect, sa.rays_refract) == (sb.rays_shadow, sb.rays_reflect, sb.rays_refract)
+    assert bits_equal(a, b) and np.array_equal(a8, b8)
+    return sa
+
+
+def test_bundle_culling_large_and_far_scenes(rt, renderer, synth):
+    """Triangles 10x larger than config 3's (the pad grows with |e1||e2|), the same soup 50 000 units away from the
+    world origin (rounding of apex and centres), a height field seen from inside (rays in every direction)."""
+    big = synth.soup(800, 8, 3, seed=41, radius=140.0)
+    renderer.set_scene(big)
+    st = _frames_equal_exact(rt, renderer, big, 384, 216, 3)
+    assert 0 < st.tests_triangle_executed < st.tests_triangle
+    far = synth.soup(1500, 8, 2, seed=42)
+    shift = np.array([50000.0, -20000.0, 30000.0], np.float32)
+    arr = {k: np.array(far[k]) for k in far.a}
+    arr["tri_points"] = (arr["tri_points"].reshape(-1, 3, 3) + shift).reshape(-1, 9).astype(np.float32)
+    arr["lights"][:, 0:3] += shift
+    q = arr["quad_coef"].astype(np.float64)          # re-centre the ellipsoids: x -> x - shift
+    ctr = -q[:, 6:9] / (2 * q[:, 0:3]) + shift
+    rhs = (q[:, 0:3] * (ctr - shift) ** 2).sum(1) - q[:, 9]
+    q[:, 6:9] = -2 * q[:, 0:3] * ctr
+    q[:, 9] = (q[:, 0:3] * ctr * ctr).sum(1) - rhs
+    arr["quad_coef"] = q.astype(np.float32)
+    arr["plane_coef"][:, 3] -= arr["plane_coef"][:, 0:3] @ shift
+    frame = dict(far.frame)
+    frame["cam_pos"] = (np.asarray(frame["cam_pos"], np.float32) + shift).astype(np.float32)
+    moved = rt.PackedScene(arr, frame)
+    renderer.set_scene(moved)
+    _frames_equal_exact(rt, renderer, moved, 320, 180, 2)
+    hf = synth.heightfield(6000, 300.0, 4, seed=43, camera=((0.0, 40.0, 0.0), (200.0, 0.0, 150.0), (0.0, 1.0, 0.0)))
+    renderer.set_scene(hf)
+    _frames_equal_exact(rt, renderer, hf, 320, 180, 3, spp=2)
+
+
+def test_bundle_culling_ray_queries(rt, renderer, synth):
+    """Coherent bundles through the ray-level entry: a common origin and a narrow fan (cones of a fraction of a
+    degree), directions that are not unit vectors, parallel rays from spread origins, NaN / zero rays in between."""
+    ps = synth.soup(4000, 16, 2, seed=44)
+    renderer.set_scene(ps)
+    rng = np.random.default_rng(6)
+    n = 16384
+    cam = np.asarray(ps.frame["cam_pos"], np.float32)
+    tgt = (np.array([30.0, 120.0, -50.0]) + rng.uniform(-25, 25, (n, 3))).astype(np.float32)
+    tgt = tgt[np.argsort(tgt[:, 0] // 4 * 1000 + tgt[:, 1] // 4)]            # neighbours in the list are neighbours in space
+    d = tgt - cam
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    o = np.tile(cam, (n, 1))
+    cases = {"fan": (o, d), "scaled": (o, (d * rng.choice([0.25, 1.0, 3.0], (n, 1))).astype(np.float32))}
+    op = (tgt + np.array([0, 0, 900.0], np.float32)).astype(np.float32)
+    cases["parallel"] = (op, np.tile(np.array([0.0, 0.0, -1.0], np.float32), (n, 1)))
+    bad_o, bad_d = o.copy(), d.copy()
+    bad_d[5::97] = 0.0
+    bad_d[11::89, 1] = np.nan
+    bad_o[13::101, 0] = np.inf
+    cases["bad"] = (bad_o, bad_d)
+    for name, (oo, dd) in cases.items():
+        i0, t0, n0 = renderer.trace_nearest(oo, dd, flags=rt.F_FORCE_STREAM)
+        i1, t1, n1 = renderer.trace_nearest(oo, dd, flags=rt.F_FORCE_STREAM | rt.F_EXACT_FP)
+        assert np.array_equal(i0, i1), name
+        assert bits_equal(t0, t1) and bits_equal(n0, n1), name
+    assert (i0 >= 0).any()
+
+
+def test_bundle_culling_many_lights(rt, renderer, synth):
+    """More than 8 lights: the shadow kernel keeps no cones and scans; 8 lights: the largest cone table."""
+    for n_lights in (8, 11):
+        ps = synth.heightfield(3000, 250.0, n_lights, seed=45)
+        renderer.set_scene(ps)
+        st = _frames_equal_exact(rt, renderer, ps, 256, 144, 2)
+        assert st.rays_shadow > 0
