@@ -142,7 +142,9 @@ template <bool E> RT_DEV int shadow_filter(const SceneView& sv, bool need, V3 P,
     for (; k < sv.n_surf; ++k) {
         int type; bool lin;
         float t = surface_t<E>(sv.surf, k, P, Ldir, need, sv.cull, type, lin);
-        if (need && t > RT_EPS && t < dist) {
+        const bool occluded = need && t > RT_EPS && t < dist;
+        if (!__any_sync(0xffffffffu, occluded)) continue;     // no filter changed: the exit test below cannot change either
+        if (occluded) {
             const int m = __float_as_int(sv.surf[k].r1.w);
             const float4 m0 = sv.mat[m].m0;
             const float kt = sv.mat[m].m2.x;
@@ -187,7 +189,7 @@ RT_DEV uchar4 quantise_rgba8(float r, float g, float b, unsigned int& nans)
         float w = v[c];
         if (w != w) { ++nans; w = 0.f; }
         w = fminf(fmaxf(w, 0.f), 1.f);
-        q[c] = (unsigned char)floorf(__fadd_rn(__fmul_rn(w, 255.0f), 0.5f));
+        q[c] = (unsigned char)__float2uint_rd(__fadd_rn(__fmul_rn(w, 255.0f), 0.5f));   // floor of a value in [0.5, 255.5]
     }
     return make_uchar4(q[0], q[1], q[2], 255);
 }
