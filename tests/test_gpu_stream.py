@@ -175,3 +175,62 @@ def test_bundle_culling_many_lights(rt, renderer, synth):
         renderer.set_scene(ps)
         st = _frames_equal_exact(rt, renderer, ps, 256, 144, 2)
         assert st.rays_shadow > 0
+
+
+def test_bundle_culling_rays_at_triangle_borders(rt, renderer, synth):
+    """The adversarial case for a conservative cull: tight bundles (128 consecutive rays aimed at ONE or two
+    triangles) whose rays pass exactly over edges and vertices, or miss them by 1e-6 .. 1e-2 of an edge length --
+    where CTriangle::Intersection accepts or rejects by rounding.  Common origin (a cone from a point) and parallel
+    rays from spread origins (apex far behind).
+      * warp-bundle culling against the plain scan (RTB200_NO_BUNDLE_CULL=1): bit for bit, no exception;
+      * the default mode against the filter-free exact mode: the per-ray filter of rt_cull.cuh has FIXED margins
+        (DESIGN.md 5.2), so rays aimed at the border of a triangle seen edge-on (|det| < 2e-3 |e1||e2|, where the
+        reference's own u, v carry errors of several per cent) may differ -- they are counted, must be few and must
+        all be of that kind."""
+    ps = synth.soup(1500, 0, 1, seed=46, radius=20.0)
+    renderer.set_scene(ps)
+    rng = np.random.default_rng(8)
+    tp = ps["tri_points"].reshape(-1, 3, 3).astype(np.float64)
+    T, per = len(tp), 64
+    tri = np.repeat(np.arange(T), per)
+    # barycentric targets on the border: vertices, edge points, and small steps across the border
+    kind = rng.integers(0, 3, T * per)
+    a = rng.uniform(0, 1, T * per)
+    u = np.where(kind == 0, a, np.where(kind == 1, 0.0, a))
+    v = np.where(kind == 0, 0.0, np.where(kind == 1, a, 1.0 - a))
+    vert = rng.uniform(0, 1, T * per) < 0.15
+    u = np.where(vert, rng.integers(0, 2, T * per), u).astype(np.float64)
+    v = np.where(vert, np.where(u == 1.0, 0.0, rng.integers(0, 2, T * per)), v).astype(np.float64)
+    step = rng.choice([0.0, 1e-6, -1e-6, 1e-4, -1e-4, 1e-2, -1e-2], T * per)
+    u, v = u + step * rng.uniform(-1, 1, T * per), v + step * rng.uniform(-1, 1, T * per)
+    p0, e1, e2 = tp[tri, 0], tp[tri, 1] - tp[tri, 0], tp[tri, 2] - tp[tri, 0]
+    tgt = p0 + u[:, None] * e1 + v[:, None] * e2
+    cam = np.asarray(ps.frame["cam_pos"], np.float64)
+    d = tgt - cam
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    cases = {"from the camera": (np.tile(cam, (len(tgt), 1)), d)}
+    axis = np.array([0.3, -0.2, -0.93]); axis /= np.linalg.norm(axis)
+    cases["parallel"] = (tgt - 700.0 * axis, np.tile(axis, (len(tgt), 1)))
+    w = np.linalg.norm(e1, axis=1) * np.linalg.norm(e2, axis=1)
+    n_hit = n_filter = 0
+    try:
+        for name, (o, dd) in cases.items():
+            o32, d32 = o.astype(np.float32), dd.astype(np.float32)
+            pts = (o + dd * 1400.0).astype(np.float32)
+            os.environ["RTB200_NO_BUNDLE_CULL"] = "0"
+            i0, t0, n0 = renderer.trace_nearest(o32, d32, flags=rt.F_FORCE_STREAM)
+            f0 = renderer.trace_shadow(pts, o32, flags=rt.F_FORCE_STREAM)
+            os.environ["RTB200_NO_BUNDLE_CULL"] = "1"
+            ip, tpl, npl = renderer.trace_nearest(o32, d32, flags=rt.F_FORCE_STREAM)
+            fp = renderer.trace_shadow(pts, o32, flags=rt.F_FORCE_STREAM)
+            assert np.array_equal(i0, ip) and bits_equal(t0, tpl) and bits_equal(n0, npl) and bits_equal(f0, fp), name
+            i1, t1, _ = renderer.trace_nearest(o32, d32, flags=rt.F_FORCE_STREAM | rt.F_EXACT_FP)
+            bad = np.flatnonzero((i0 != i1) | (t0.view(np.uint32) != t1.view(np.uint32)))
+            det = np.abs(np.einsum("ij,ij->i", e1, np.cross(d32.astype(np.float64), e2)))
+            assert (det[bad] < 2e-3 * w[bad]).all(), (name, bad[:5].tolist())
+            n_filter += len(bad)
+            n_hit += int((i0 >= 0).sum())
+    finally:
+        os.environ["RTB200_NO_BUNDLE_CULL"] = "0"
+    print(f"border rays: {n_hit} hits of {2 * T * per}, {n_filter} answers differ from the exact mode (edge-on triangles)")
+    assert n_hit > T * per and n_filter <= 2 * T * per // 1000
