@@ -293,25 +293,16 @@ RT_DEV bool slab(const RayBox& r, float lx, float ly, float lz, float hx, float 
     return tn <= tf * (1.0f + 2.0f * BVH_SLACK);
 }
 
-// One triangle of a leaf.  MODE 0 / 2: the conservative fused filter of rt_cull.cuh in ONE pass
-// (det, u, v, t with margins), survivors re-evaluated in the reference's rounding sequence (MODE 0)
-// or fused (MODE 2); MODE 1 (RTB200_F_EXACT_FP): the reference sequence for every test.
+// One triangle of a leaf.  MODE 0 / 2: the conservative fused filter of rt_cull.cuh (phase 1: det, u; phase 2:
+// v, t -- numerator space, error-scaled margins), survivors re-evaluated in the reference's rounding sequence
+// (MODE 0) or fused (MODE 2); MODE 1 (RTB200_F_EXACT_FP): the reference sequence for every test.
 template <int MODE>
 RT_DEV float triangle_leaf(V3 o, V3 d, V3 p0, V3 e1, V3 e2, float tmax)
 {
     if (MODE == 1) return triangle_t<true>(o, d, p0, e1, e2);
-    const V3 P = cross3<false>(d, e2);
-    const float det = dot3<false>(e1, P);
-    if (!(fabsf(det) >= CULL_DET)) return -1.0f;
-    const float rd = rcp_approx(det);
-    const V3 S = sub3<false>(o, p0);
-    const float u = dot3<false>(S, P) * rd;
-    if (!(fabsf(u - 0.5f) <= 0.5f + CULL_UV)) return -1.0f;
-    const V3 Q = cross3<false>(S, e1);
-    const float v = dot3<false>(d, Q) * rd;
-    const float t = dot3<false>(e2, Q) * rd;
-    if (!(v >= -CULL_UV && u + v <= 1.0f + CULL_UV && t > RT_EPS * 0.99f && t < tmax)) return -1.0f;
-    return MODE == 2 ? triangle_t<false>(o, d, p0, e1, e2) : triangle_t<true>(o, d, p0, e1, e2);
+    const TriMargins mg = tri_margins(e1, e2, max_abs3(d));
+    if (!triangle_phase1(o, d, p0, e1, e2, mg)) return -1.0f;
+    return triangle_survivor<MODE>(o, d, p0, e1, e2, tmax, mg);
 }
 
 // Generic "while-while" traversal: the inner loop walks internal nodes only, so the lanes of a

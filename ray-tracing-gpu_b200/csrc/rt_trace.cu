@@ -321,6 +321,9 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
             if (!valid) d[r] = mk3(0.f, 0.f, 0.f);     // zero direction: det = 0, nothing can hit
             best_t[r] = -1.0f; best_id[r] = -1; tlim[r] = 3.0e38f;
         }
+        float dmax = 0.f;                             // largest |direction component| of this thread's rays (filter margins)
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r) dmax = fmaxf(dmax, max_abs3(d[r]));
         // the cone that holds the warp's 128 rays (see "warp bundles" above)
         Bundle bun;
         bun.state = 2;
@@ -369,22 +372,19 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
                 auto test_triangle = [&](int j) {
                     const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
                     const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
+                    const TriMargins mg = tri_margins(e1, e2, dmax);
                     bool cand[ST_RPT];
                     bool any = false;
                     #pragma unroll
                     for (int r = 0; r < ST_RPT; ++r) {       // phase 1: det and u, fused, no division
-                        const V3 P = cross3<false>(d[r], e2);
-                        const float det = dot3<false>(e1, P);
-                        const V3 S = sub3<false>(o[r], p0);
-                        const float u = dot3<false>(S, P) * rcp_approx(det);
-                        cand[r] = fabsf(det) >= CULL_DET && fabsf(u - 0.5f) <= 0.5f + CULL_UV;
+                        cand[r] = triangle_phase1(o[r], d[r], p0, e1, e2, mg);    // branch-free: the 4 rays interleave
                         any |= cand[r];
                     }
                     if (__any_sync(FULL_MASK, any)) {
                         #pragma unroll
                         for (int r = 0; r < ST_RPT; ++r) {
-                            if (cand[r]) {
-                                const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, tlim[r]);
+                            if (cand[r] && slot[r] >= 0) {
+                                const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, tlim[r], mg);
                                 if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f)) {
                                     best_t[r] = tt; best_id[r] = __float_as_int(ra.w);
                                     tlim[r] = fmaf(tt, CULL_TREL, CULL_TABS);
@@ -513,6 +513,9 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
             if (!valid) { fr[r] = fg[r] = fb[r] = 0.0f; }        // counts as finished
         }
         bool warp_done = false;
+        float dmax = 0.f;                             // largest |direction component| of this thread's queries (filter margins)
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r) dmax = fmaxf(dmax, max_abs3(d[r]));
         bool can_cull = n_cones > 0;
         for (int l = 0; l < n_cones; ++l) {          // the warp's cone(s) per light (uniform values, kept in shared memory)
             const V3 L = f4_xyz(s.light[l].l0);
@@ -588,22 +591,19 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
                     auto test_triangle = [&](int j) {
                         const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
                         const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
+                        const TriMargins mg = tri_margins(e1, e2, dmax);
                         bool cand[ST_RPT];
                         bool any = false;
                         #pragma unroll
                         for (int r = 0; r < ST_RPT; ++r) {
-                            const V3 P = cross3<false>(d[r], e2);
-                            const float det = dot3<false>(e1, P);
-                            const V3 S = sub3<false>(o[r], p0);
-                            const float u = dot3<false>(S, P) * rcp_approx(det);
-                            cand[r] = fabsf(det) >= CULL_DET && fabsf(u - 0.5f) <= 0.5f + CULL_UV;
+                            cand[r] = triangle_phase1(o[r], d[r], p0, e1, e2, mg);    // branch-free: the 4 rays interleave
                             any |= cand[r];
                         }
                         if (__any_sync(FULL_MASK, any)) {
                             #pragma unroll
                             for (int r = 0; r < ST_RPT; ++r) {
                                 if (cand[r] && slot[r] >= 0) {
-                                    const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, tlim[r]);
+                                    const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, tlim[r], mg);
                                     if (tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(rb.w), fr[r], fg[r], fb[r]);
                                 }
                             }
