@@ -8,12 +8,13 @@
 //   * a persistent CTA holds 1024 rays (256 threads x 4 rays in registers) so one staged
 //     triangle serves 4 rays per thread (ILP) and 1024 rays per CTA (arithmetic intensity
 //     ~ 1000 x 46 flop per 48 B: HBM/L2 are irrelevant, the FMA pipe is the roof);
-//   * per (ray, triangle) a two-phase CULLING FILTER in fused arithmetic: phase 1 computes
-//     det and u only (one MUFU.RCP, no division) and a warp vote skips the rest of the test
-//     when no lane of the warp can hit; phase 2 finishes v and t for the survivors of phase 1.
-//     The filter is conservative (margins far above the rounding differences); only rays that
-//     pass it run the reference's own rounding sequence (triangle_t<true>), so the accepted
-//     distances are bit-identical to the CPU renderer.
+//   * per (ray, triangle) a two-phase CULLING FILTER in fused arithmetic (rt_cull.cuh): phase 1 computes
+//     det and S.P only -- no division, compared in numerator space -- and a warp vote skips the rest of the
+//     test when no lane of the warp can be accepted; phase 2 finishes v and t for the survivors of phase 1.
+//     The filter is conservative by construction (margins that bound the fused / reference difference of every
+//     numerator); only rays that pass it run the reference's own rounding sequence (triangle_t<true>), so the
+//     accepted distances are bit-identical to the CPU renderer.
+//   * whole triangles are culled per warp against the cone of its 128 rays ("warp bundles" below).
 //   * shadow queries leave at warp granularity once every ray of the warp holds a zero filter.
 #include "rt_stream.cuh"
 #include "rt_cull.cuh"
