@@ -30,7 +30,7 @@ using namespace rtb;
 namespace rtb {
 
 struct StreamBufs {                // per-context scratch of the streamed path (lives in the ctx levels + these)
-    DevBuf hit, hitP, hitN, q_base, sq0, sq1, sq_src, filter;
+    DevBuf hit, hitP, hitN, q_base, sq0, sq1, sq_src, sq_dst, filter;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // per-stage stopwatch
 };
 
@@ -39,6 +39,14 @@ static int bundle_cull_enabled()
 {
     const char* e = getenv("RTB200_NO_BUNDLE_CULL");
     return (e && atoi(e) != 0) ? 0 : 1;
+}
+
+// queue order of the tiled path (see render_streamed); off by default in this round: measured once, not yet through
+// the whole GPU suite
+static bool query_grouping_enabled()
+{
+    const char* e = getenv("RTB200_QUERY_GROUPING");
+    return e && atoi(e) != 0;
 }
 
 static StreamBufs* stream_bufs(rtb200_ctx* c)
@@ -51,7 +59,7 @@ void stream_release(rtb200_ctx* c)
 {
     if (!c->stream_scratch) return;
     StreamBufs* b = static_cast<StreamBufs*>(c->stream_scratch);
-    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->filter.release();
+    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->sq_dst.release(); b->filter.release();
     for (auto& e : b->ev) if (e) cudaEventDestroy(e);
     delete b;
     c->stream_scratch = nullptr;
@@ -73,6 +81,10 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
         shadow_by_light = L > 1 && (8 % L == 0 || L % 8 == 0) && samples / prims >= 64.0;
         if (const char* e = getenv("RTB200_SHADOW_BY_LIGHT")) shadow_by_light = atoi(e) != 0;
     }
+    // tiled kernels: level-0 rays by 16x16 patches and each CTA's shadow queries light by light, so that a warp of the
+    // trace kernels holds a compact bundle (RTB200_QUERY_GROUPING=1; changes the ORDER of the queues, no value)
+    const bool tile_rays = !use_bvh && query_grouping_enabled();
+    const bool group_queries = tile_rays && c->ds.rl.n_light >= 1 && c->ds.rl.n_light <= 8;
     if (use_bvh) {                               // boxes must be padded for rays that start at the camera
         const int rc = bvh_prepare(c, fr->cam_pos, 1);
         if (rc != RTB200_OK) return rc;
@@ -129,6 +141,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             if ((e = sb->hit.ensure(sizeof(float2) * n)) != cudaSuccess || (e = sb->hitP.ensure(sizeof(float4) * n)) != cudaSuccess ||
                 (e = sb->hitN.ensure(sizeof(float4) * n)) != cudaSuccess || (e = sb->q_base.ensure(sizeof(int) * n)) != cudaSuccess ||
                 (e = sb->sq_src.ensure(sizeof(int2) * n * std::max(L, 1))) != cudaSuccess ||
+                (group_queries && (e = sb->sq_dst.ensure(sizeof(int) * n * std::max(L, 1))) != cudaSuccess) ||
                 (e = sb->filter.ensure(sizeof(float4) * n * std::max(L, 1))) != cudaSuccess)
                 return set_cuda_error(c, e, "stream scratch");
             if (level > 0 && (e = cur.colour.ensure(sizeof(float4) * n)) != cudaSuccess) return set_cuda_error(c, e, "colour");
@@ -164,6 +177,8 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             sa.in_od0 = tp.in_od0; sa.in_od1 = tp.in_od1; sa.n_rays = n_in; sa.hit = tp.hit;
             sa.hitP = sb->hitP.as<float4>(); sa.hitN = sb->hitN.as<float4>(); sa.q_base = sb->q_base.as<int>();
             sa.sq_src = sb->sq_src.as<int2>();
+            sa.tile_rays = tile_rays ? 1 : 0;
+            sa.sq_dst = group_queries ? sb->sq_dst.as<int>() : nullptr;
             sa.out_od0 = nxt.od0.as<float4>(); sa.out_od1 = nxt.od1.as<float4>();
             sa.out_count = d_cnt + 4 * level; sa.link_count = d_cnt + 4 * level + 1; sa.sq_count = d_cnt + 4 * level + 2;
             sa.links = cur.links.as<int4>();
@@ -189,6 +204,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 ShadowParams sp;
                 memset(&sp, 0, sizeof sp);
                 sp.s = c->ds; sp.sq_src = sa.sq_src; sp.hitP = sa.hitP; sp.n_queries = n_sq;
+                sp.sq_dst = sa.sq_dst;
                 sp.by_light = shadow_by_light ? 1 : 0;
                 sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode; sp.cull_bundles = bundle_cull_enabled();
                 if (use_bvh) SCU(launch_bvh_shadow(sp, c->stream));

@@ -51,6 +51,10 @@ struct ShadeAParams {
     unsigned int* link_count;
     unsigned long long* stats;
     int   exact;                   // rounding of everything that is kept (1 unless FUSED_FP)
+    int   tile_rays;               // level 0: a CTA takes 16x16 lattice samples instead of 256 consecutive ones
+    int*  sq_dst;                  // null: queries in (ray, light) order, filter slot = query slot.  Otherwise the
+                                   // CTA's queries are queued light by light (<= 8 lights) and sq_dst[query] is the
+                                   // filter slot shade-B reads (q_base[ray] + rank of the light among the facing ones)
 };
 
 struct ShadowParams {
@@ -58,6 +62,7 @@ struct ShadowParams {
     const float4* sq0;             // explicit queries (rtb200_trace_shadow): P.xyz | dist
     const float4* sq1;             //                                         L.xyz (normalised) | 0
     const int2*   sq_src;          // or, inside a frame: (ray, light) pairs over hitP (shade-A), sq0 / sq1 unused
+    const int*    sq_dst;          // filter slot of every query (null: the query's own index)
     const float4* hitP;
     int   by_light;                // LBVH: lanes of a warp share the light rather than the hit (see k_bvh_shadow)
     int   n_queries;

@@ -667,7 +667,7 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
         }
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r)
-            if (slot[r] >= 0) p.filter[slot[r]] = make_float4(fr[r], fg[r], fb[r], 0.f);
+            if (slot[r] >= 0) p.filter[p.sq_dst ? p.sq_dst[slot[r]] : slot[r]] = make_float4(fr[r], fg[r], fb[r], 0.f);
     }
 
     // ---- statistics: tests entered (per thread -> warp -> one atomic per warp) ----------------
@@ -708,9 +708,18 @@ RT_DEV void level_ray(const FrameParams& f, int level, int chunk_ly0, int i, con
 template <bool E>
 __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAParams p)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31;
-    const bool valid = i < p.n_rays;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = i < p.n_rays;
+    if (p.tile_rays && p.level == 0) {
+        // 16x16 samples per CTA: the hit points of a warp's queries and the origins of its children lie in a compact
+        // patch, so the cones the tiled kernels cull with are narrow in both directions (a scanline is narrow in one)
+        const int tiles_x = (p.f.LW + 15) >> 4;
+        const int x = (blockIdx.x % tiles_x) * 16 + (threadIdx.x & 15), y = (blockIdx.x / tiles_x) * 16 + (threadIdx.x >> 4);
+        valid = x < p.f.LW && y < p.chunk_rows;
+        i = y * p.f.LW + x;
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool grouped = p.sq_dst != nullptr;
     const DeviceScene& s = p.s;
     V3 o = mk3(0.f, 0.f, 0.f), d = o, P = o, N = o;
     float energy = 0.f, ior = 0.f, t = -1.f;
@@ -741,10 +750,13 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
     }
     // ---- shadow queries ---------------------------------------------------------------------
     int n_face = 0;
+    unsigned int face_bits = 0;                              // bit l: light l faces the stored normal
     if (hit)
         for (int l = 0; l < s.rl.n_light; ++l) {
             const V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
-            n_face += dot3<E>(Ld, N) > 0.f ? 1 : 0;
+            const bool facing = dot3<E>(Ld, N) > 0.f;
+            n_face += facing ? 1 : 0;
+            face_bits |= facing ? (1u << (l & 31)) : 0u;
         }
     // ---- queue slots: ONE atomic per counter and CTA ------------------------------------------------
     // (one per warp made a quarter of a million atomics on a single address per 4K frame: the kernel spent
@@ -762,8 +774,14 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
     const int total = __shfl_sync(FULL_MASK, incl, 31);
     __shared__ uint4 s_cnt[8];                               // per warp: queries, reflected, refracted, links
     __shared__ uint4 s_base[8];
-    const int warp = threadIdx.x >> 5;
+    __shared__ unsigned short s_lcnt[BUNDLE_MAX_LIGHTS * 8]; // grouped queues: facing rays per (light, warp) ...
+    __shared__ unsigned short s_loff[BUNDLE_MAX_LIGHTS * 8]; // ... and their exclusive scan in that order
     if (lane == 0) s_cnt[warp] = make_uint4((unsigned int)total, n_refl, n_refr, (unsigned int)__popc(m_any));
+    if (grouped)
+        for (int l = 0; l < BUNDLE_MAX_LIGHTS; ++l) {
+            const unsigned int m = __ballot_sync(FULL_MASK, (face_bits >> l) & 1u);
+            if (lane == 0) s_lcnt[l * 8 + warp] = (unsigned short)__popc(m);
+        }
     __syncthreads();
     if (warp == 0) {
         const uint4 c = lane < 8 ? s_cnt[lane] : make_uint4(0u, 0u, 0u, 0u);
@@ -787,7 +805,14 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
             }
         }
         bq = __shfl_sync(FULL_MASK, bq, 0); bk = __shfl_sync(FULL_MASK, bk, 0); bl = __shfl_sync(FULL_MASK, bl, 0);
-        if (lane < 8) s_base[lane] = make_uint4(bq + iq - c.x, bk + ik - kids, bl + il - c.w, 0u);
+        if (lane < 8) s_base[lane] = make_uint4(bq + iq - c.x, bk + ik - kids, bl + il - c.w, bq);
+        if (grouped) {                                        // 64 (light, warp) counts, two per lane
+            const unsigned int v0 = s_lcnt[2 * lane], v1 = s_lcnt[2 * lane + 1];
+            unsigned int inc = v0 + v1;
+            for (int off = 1; off < 32; off <<= 1) { const unsigned int v = __shfl_up_sync(FULL_MASK, inc, off); if (lane >= off) inc += v; }
+            const unsigned int ex = inc - (v0 + v1);
+            s_loff[2 * lane] = (unsigned short)ex; s_loff[2 * lane + 1] = (unsigned short)(ex + v0);
+        }
     }
     __syncthreads();
     const uint4 wb = s_base[warp];
@@ -798,7 +823,20 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
         p.hitP[i] = make_float4(P.x, P.y, P.z, t);
         p.hitN[i] = make_float4(N.x, N.y, N.z, __int_as_float(id));
     }
-    if (hit)
+    if (grouped) {
+        // the CTA's queries light by light: a warp of the shadow kernel then holds (up to) 128 hit points of ONE
+        // light -- one narrow cone to cull with, and every kept triangle is one its 128 queries may really need
+        const unsigned int below = (1u << lane) - 1u;
+        for (int l = 0; l < s.rl.n_light; ++l) {
+            const bool facing = (face_bits >> l) & 1u;
+            const unsigned int m = __ballot_sync(FULL_MASK, facing);
+            if (facing) {
+                const int k = (int)(wb.w + s_loff[l * 8 + warp] + __popc(m & below));
+                p.sq_src[k] = make_int2(i, l);
+                p.sq_dst[k] = q++;
+            }
+        }
+    } else if (hit)
         for (int l = 0; l < s.rl.n_light; ++l) {
             const V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
             if (dot3<E>(Ld, N) > 0.f) p.sq_src[q++] = make_int2(i, l);    // direction and distance: shadow_query()
@@ -995,7 +1033,8 @@ cudaError_t launch_trace_shadow(const ShadowParams& p, int sm_count, cudaStream_
 cudaError_t launch_shade_a(const ShadeAParams& p, cudaStream_t st)
 {
     if (p.n_rays <= 0) return cudaSuccess;
-    const int blocks = (p.n_rays + 255) / 256;
+    int blocks = (p.n_rays + 255) / 256;
+    if (p.tile_rays && p.level == 0) blocks = ((p.f.LW + 15) / 16) * ((p.chunk_rows + 15) / 16);
     if (p.exact) k_shade_a<true><<<blocks, 256, 0, st>>>(p);
     else         k_shade_a<false><<<blocks, 256, 0, st>>>(p);
     return cudaGetLastError();
