@@ -139,6 +139,26 @@ def test_bundle_culling_large_and_far_scenes(rt, renderer, synth):
     _frames_equal_exact(rt, renderer, hf, 320, 180, 3, spp=2)
 
 
+def test_query_grouping_changes_no_bit(rt, renderer, synth, monkeypatch):
+    """Queue order of the tiled path (rt_stream.cu: level-0 rays by 16x16 patches, each CTA's shadow queries light by
+    light; RTB200_QUERY_GROUPING=0 restores ray order): a permutation of the queues, so frames, bytes and ray counts
+    are equal -- ragged 16x16 patches (251 x 131 at 2x2 samples), three levels with both kinds of children, 8 lights."""
+    cases = ((synth.soup(600, 24, 3, seed=2024, radius=45.0), 251, 131, 3, 2),
+             (synth.heightfield(3000, 250.0, 8, seed=45), 250, 150, 2, 1))
+    for n, (ps, W, H, depth, spp) in enumerate(cases):
+        renderer.set_scene(ps)
+        fr = rt.make_frame(ps.frame, W, H, max_bounces=depth, spp_grid=spp, flags=rt.F_FORCE_STREAM)
+        monkeypatch.setenv("RTB200_QUERY_GROUPING", "0")
+        a, a8, sa = renderer.render(fr)
+        monkeypatch.delenv("RTB200_QUERY_GROUPING")
+        b, b8, sb = renderer.render(fr)
+        assert bits_equal(a, b) and np.array_equal(a8, b8)
+        assert (sa.rays_shadow, sa.rays_reflect, sa.rays_refract) == (sb.rays_shadow, sb.rays_reflect, sb.rays_refract)
+        assert sa.rays_shadow > 0
+        if n == 0:          # measured on this scene: 7.5e7 -> 3.8e7 executed tests (profiles/r1_c3_ab_query_grouping.log)
+            assert sb.tests_triangle_executed < sa.tests_triangle_executed
+
+
 def test_bundle_culling_ray_queries(rt, renderer, synth):
     """Coherent bundles through the ray-level entry: a common origin and a narrow fan (cones of a fraction of a
     degree), directions that are not unit vectors, parallel rays from spread origins, NaN / zero rays in between."""
