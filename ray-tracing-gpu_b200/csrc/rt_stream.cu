@@ -35,10 +35,13 @@ struct StreamBufs {                // per-context scratch of the streamed path (
 };
 
 // warp-bundle culling of the tiled kernels (rt_trace.cu); RTB200_NO_BUNDLE_CULL=1 turns it off for A/B runs
+// RTB200_NEAREST_CONES=4 (not yet measured on a GPU, off by default): warps of secondary rays may hold up to 4 cones
 static int bundle_cull_enabled()
 {
     const char* e = getenv("RTB200_NO_BUNDLE_CULL");
-    return (e && atoi(e) != 0) ? 0 : 1;
+    if (e && atoi(e) != 0) return 0;
+    const char* m = getenv("RTB200_NEAREST_CONES");
+    return (m && atoi(m) > 1) ? 2 : 1;
 }
 
 // queue order of the tiled path (see render_streamed); RTB200_QUERY_GROUPING=0 restores the ray order for A/B runs
@@ -83,8 +86,10 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     // tiled kernels: level-0 rays by 16x16 patches and each CTA's shadow queries light by light, so that a warp of the
     // trace kernels holds a compact bundle (changes the ORDER of the queues, no value: frames stay bit-identical;
     // config 3: shadow stage 112 -> 60 ms, profiles/r1_c3_ab_query_grouping.log)
-    const bool tile_rays = !use_bvh && query_grouping_enabled();
-    const bool group_queries = tile_rays && c->ds.rl.n_light >= 1 && c->ds.rl.n_light <= 8;
+    // (LBVH: only the patches, opt-in with RTB200_BVH_TILE_RAYS=1 until measured -- its shadow kernel has a warp
+    // mapping of its own that relies on the queries of a ray being contiguous)
+    const bool tile_rays = query_grouping_enabled() && (!use_bvh || getenv("RTB200_BVH_TILE_RAYS") != nullptr);
+    const bool group_queries = tile_rays && !use_bvh && c->ds.rl.n_light >= 1 && c->ds.rl.n_light <= 8;
     if (use_bvh) {                               // boxes must be padded for rays that start at the camera
         const int rc = bvh_prepare(c, fr->cam_pos, 1);
         if (rc != RTB200_OK) return rc;

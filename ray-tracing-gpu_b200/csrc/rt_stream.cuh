@@ -26,6 +26,7 @@ struct TraceParams {
                                    // 2: filter + fused survivors (FUSED_FP)
     unsigned long long* stats;     // LBVH kernels: nodes visited / triangle tests (may be null)
     int   cull_bundles;            // tiled kernels: cull whole triangles per warp against the cone of its rays
+                                   // (0: off, 1: one cone per warp, > 1: secondary rays may split into up to 4)
 };
 
 // shade-A: hit point, normal, shadow queries of the facing lights, children

@@ -211,6 +211,26 @@ RT_DEV V3 warp_pick(const V3* v, const float* key, const bool* in)
     return mk3(__shfl_sync(FULL_MASK, mine.x, src), __shfl_sync(FULL_MASK, mine.y, src), __shfl_sync(FULL_MASK, mine.z, src));
 }
 
+// members `in` (unit directions dn, 4 per lane) split around their two most distant directions
+RT_DEV void split_members(const V3* dn, const bool* in, bool* in_a, bool* in_b)
+{
+    float key[ST_RPT];
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r) key[r] = 1.0f;
+    const V3 seed = warp_pick(dn, key, in);
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r) key[r] = fmaxf(1.0f - dot3<false>(dn[r], seed), 0.f);
+    const V3 pa = warp_pick(dn, key, in);
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r) key[r] = fmaxf(1.0f - dot3<false>(dn[r], pa), 0.f);
+    const V3 pb = warp_pick(dn, key, in);
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r) {
+        const bool near_a = dot3<false>(dn[r], pa) >= dot3<false>(dn[r], pb);
+        in_a[r] = in[r] && near_a; in_b[r] = in[r] && !near_a;
+    }
+}
+
 // cone of the shadow queries of light `l` held 4 per lane (apex = the light); d = unit directions TOWARDS the light
 RT_DEV Bundle bundle_of_light(V3 L, const V3* d, const float* dist, const bool* in)
 {
@@ -265,11 +285,16 @@ RT_DEV Bundle bundle_of_light(V3 L, const V3* d, const float* dist, const bool* 
 // (warp = 16x8 pixels, thread = a 2x2 quad) generated on the fly; otherwise 1024 consecutive
 // queue entries.
 // ---------------------------------------------------------------------------------------
-template <int MODE, bool PRIMARY>
+// MULTI (secondary rays, RTB200_NEAREST_CONES=4): a warp whose single cone is wide -- 128 consecutive children left
+// several surfaces in several directions -- splits its rays twice around their most distant directions and culls with
+// up to 4 cones (scripts/sim_secondary_grouping.py: level-1 rays of config 3, 44 % -> 0.3 % of the tests entered).
+#define BUNDLE_NEAREST_CONES 4
+template <int MODE, bool PRIMARY, bool MULTI>
 __global__ void __launch_bounds__(ST_THREADS, 2)
 k_trace_nearest(const __grid_constant__ TraceParams p)
 {
     __shared__ __align__(128) TraceSmem sm;
+    __shared__ Bundle ncones[MULTI ? ST_THREADS / 32 : 1][BUNDLE_NEAREST_CONES];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const DeviceScene& s = p.s;
     const int n_tiles = s.n_tri_padded / ST_TILE;
@@ -328,11 +353,35 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
         // the cone that holds the warp's 128 rays (see "warp bundles" above)
         Bundle bun;
         bun.state = 2;
+        bool multi = false;                           // MULTI: cull with ncones[warp][0..3] instead of `bun`
         if (MODE != 1 && p.cull_bundles) {
             bool use[ST_RPT];
             #pragma unroll
             for (int r = 0; r < ST_RPT; ++r) use[r] = slot[r] >= 0;
             bun = bundle_of_rays(o, d, use);
+            if (MULTI && (bun.state == 2 || (bun.state == 1 && bun.sin_t > BUNDLE_SPLIT_SIN))) {
+                V3 dn[ST_RPT];
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) {
+                    const float l2 = dot3<false>(d[r], d[r]);
+                    const float il = (l2 > 1.0e-20f && l2 < 1.0e20f) ? rsqrtf(l2) : 0.f;
+                    dn[r] = mk3(d[r].x * il, d[r].y * il, d[r].z * il);
+                }
+                bool ga[ST_RPT], gb[ST_RPT], g[BUNDLE_NEAREST_CONES][ST_RPT];
+                split_members(dn, use, ga, gb);
+                split_members(dn, ga, g[0], g[1]);
+                split_members(dn, gb, g[2], g[3]);
+                bool usable = true;
+                #pragma unroll
+                for (int k = 0; k < BUNDLE_NEAREST_CONES; ++k) {
+                    const Bundle b = bundle_of_rays(o, d, g[k]);     // state 0: an empty part
+                    usable = usable && b.state != 2;
+                    if (lane == 0) ncones[MULTI ? warp : 0][k] = b;
+                }
+                multi = usable;
+                if (usable) bun.state = 1;               // leave the plain scan; the cones are in shared memory
+                __syncwarp();
+            }
         }
 
         // ---- triangles: double-buffered TMA tiles ---------------------------------------------
@@ -404,7 +453,17 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
                     {                                // lane j looks at triangle j0 + j for the whole warp
                         const float4 sph = sm.sphere[j0 + lane];
                         const float w = sm.sphere_w[j0 + lane];
-                        const bool keep = w > 0.f && bun.state == 1 && !bundle_culls(bun, mk3(sph.x, sph.y, sph.z), sph.w, w);
+                        bool keep;
+                        if (MULTI && multi) {
+                            keep = false;
+                            #pragma unroll
+                            for (int k = 0; k < BUNDLE_NEAREST_CONES; ++k) {
+                                const Bundle& b = ncones[MULTI ? warp : 0][k];
+                                if (b.state == 1 && !bundle_culls(b, mk3(sph.x, sph.y, sph.z), sph.w, w)) keep = true;
+                            }
+                            keep = keep && w > 0.f;
+                        } else
+                            keep = w > 0.f && bun.state == 1 && !bundle_culls(bun, mk3(sph.x, sph.y, sph.z), sph.w, w);
                         keep_mask = __ballot_sync(FULL_MASK, keep);
                     }
                     n_exec += (unsigned int)__popc(keep_mask);
@@ -999,7 +1058,8 @@ cudaError_t launch_query_unpack_filter(int n, const float4* filter, float* out3,
 template <int MODE, bool PRIMARY>
 static cudaError_t launch_nearest_t(const TraceParams& p, int blocks, cudaStream_t st)
 {
-    k_trace_nearest<MODE, PRIMARY><<<blocks, ST_THREADS, 0, st>>>(p);
+    if (!PRIMARY && MODE != 1 && p.cull_bundles > 1) k_trace_nearest<MODE, false, (MODE != 1)><<<blocks, ST_THREADS, 0, st>>>(p);
+    else k_trace_nearest<MODE, PRIMARY, false><<<blocks, ST_THREADS, 0, st>>>(p);
     return cudaGetLastError();
 }
 
