@@ -300,10 +300,14 @@ def run_gpu(args):
     # (two extra frames on every rank, outside the timed region)
     brute = None
     if st.path == 1:
+        prev = os.environ.get("RTB200_NO_BUNDLE_CULL")
         os.environ["RTB200_NO_BUNDLE_CULL"] = "1"
         r.render(fr, want_f32=False, want_rgba8=False)
         _, _, sb = r.render(fr, want_f32=False, want_rgba8=False)
-        os.environ["RTB200_NO_BUNDLE_CULL"] = "0"
+        if prev is None:
+            os.environ.pop("RTB200_NO_BUNDLE_CULL")
+        else:
+            os.environ["RTB200_NO_BUNDLE_CULL"] = prev
         brute = {"kernel_ms": sb.ms_primary_kernel, "frame_ms": sb.ms_render + sb.ms_gather,
                  "stage_ms": {"trace_nearest": sb.ms_trace_nearest, "trace_shadow": sb.ms_trace_shadow, "shade": sb.ms_shade}}
         barrier()
@@ -417,7 +421,8 @@ def run_gpu(args):
                    "parallelism": (f"interleaved 16-row image bands x{world}, scene replicated; the producing kernels store into rank 0's frame "
                                    "over NVLink and signal completion themselves (peer frame), NCCL gather as fallback") if world > 1 else
                                   "one GPU (image bands x1)",
-                   "arithmetic": "reference rounding sequence (bit-exact mode)"},
+                   "arithmetic": "reference rounding sequence (bit-exact mode)",
+                   "switches": {k: v for k, v in os.environ.items() if k.startswith("RTB200_")}},
         "rays_per_frame": rays_total, "ms_per_frame": ms_max, "device_ms_per_frame": dev_max,
         "ms_per_frame_synchronous_calls": sync_loop_ms,
         "stage_ms_per_frame": {"trace_nearest": stage[0] / steps, "trace_shadow": stage[1] / steps, "shade": stage[2] / steps},

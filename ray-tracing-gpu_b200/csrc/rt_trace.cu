@@ -14,7 +14,8 @@
 //     The filter is conservative by construction (margins that bound the fused / reference difference of every
 //     numerator); only rays that pass it run the reference's own rounding sequence (triangle_t<true>), so the
 //     accepted distances are bit-identical to the CPU renderer.
-//   * whole triangles are culled per warp against the cone of its 128 rays ("warp bundles" below).
+//   * whole triangles are culled per warp against the cone of its 128 rays ("warp bundles" below); shade-A
+//     queues rays by 16x16 patches and shadow queries light by light so that those 128 rays are a compact bundle.
 //   * shadow queries leave at warp granularity once every ray of the warp holds a zero filter.
 #include "rt_stream.cuh"
 #include "rt_cull.cuh"
@@ -748,7 +749,8 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
 // ---------------------------------------------------------------------------------------
 // shade-A: per ray -- hit point and normal (as CIntersection would carry them), one shadow
 // query per light facing the stored normal (Scene.cpp:1751-1759), reflected / refracted
-// children (Scene.cpp:1779-1823).  Queries of one ray are contiguous, in light order.
+// children (Scene.cpp:1779-1823).  Filter slots of one ray are contiguous, in light order (q_base); the queries
+// themselves are queued in that order too, or -- sq_dst given -- light by light within the CTA.
 // ---------------------------------------------------------------------------------------
 template <bool E>
 RT_DEV void level_ray(const FrameParams& f, int level, int chunk_ly0, int i, const float4* od0, const float4* od1,
