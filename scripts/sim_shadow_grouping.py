@@ -1,12 +1,12 @@
 """CPU estimate (numpy, no GPU, no oracle): how many (shadow query, triangle) tests the per-light cones of
 k_trace_shadow (rt_trace.cu) leave, as a function of HOW the queries are grouped into warps of 128.
 
-Today (k_shade_a): the queries of one ray are contiguous, in light order, and the rays of a level-0 CTA are 256
-consecutive pixels of a scanline; a warp of the shadow kernel therefore holds ~32 scanline pixels x 4 lights, keeps a
+Before (k_shade_a, RTB200_QUERY_GROUPING=0): the queries of one ray are contiguous, in light order, and the rays of a level-0 CTA are 256
+consecutive pixels of a scanline; a warp of the shadow kernel then holds ~32 scanline pixels x 4 lights, keeps a
 triangle if ANY light's cone needs it, and runs the kept triangle for all 128 queries.  Alternatives counted here:
   rows+lights : the CTA's queries ordered by light first (a warp = up to 128 scanline pixels of ONE light)
   tiles       : CTA = 16x16 pixels, queries in ray order (a warp = 16x2 pixels x 4 lights)
-  tiles+lights: CTA = 16x16 pixels, ordered by light first (a warp = 16x8 pixels of ONE light)
+  tiles+lights: CTA = 16x16 pixels, ordered by light first (a warp = 16x8 pixels of ONE light) -- the default now
 Scene / camera: BASELINE config 3 (synth.soup(10000, 64, 4, seed=1234), 3840x2160), crops of 256x128 pixels.
 The cone maths is the numpy restatement tests/test_bundle_cull_math.py checks (including the two-cone split).
 
@@ -149,7 +149,7 @@ def main():
         dirs = (Ld / np.where(dist > 0, dist, 1)[..., None]).astype(F)
         px, py = xs.ravel() - x0, ys.ravel() - y0
         orders = {}
-        for name, tiles, by_light in (("rows (today)", False, False), ("rows+lights", False, True), ("tiles", True, False), ("tiles+lights", True, True)):
+        for name, tiles, by_light in (("rows (before)", False, False), ("rows+lights", False, True), ("tiles", True, False), ("tiles+lights", True, True)):
             cta = (py // 16) * (cw // 16) + px // 16 if tiles else py * (cw // 256) + px // 256
             inner = (py % 16) * 16 + px % 16 if tiles else px % 256
             ri, li = np.nonzero(face)                                            # queries in (ray, light) order
@@ -163,9 +163,9 @@ def main():
             print(f"    {name:14s} executed {ex / plain:7.4f} of the plain scan")
             a = tot.setdefault(name, [0, 0]); a[0] += ex; a[1] += plain
     print("all crops:")
-    base = tot["rows (today)"][0]
+    base = tot["rows (before)"][0]
     for name, (ex, plain) in tot.items():
-        print(f"    {name:14s} executed {ex / plain:7.4f} of the plain scan   ({base / ex:4.2f}x fewer than today)")
+        print(f"    {name:14s} executed {ex / plain:7.4f} of the plain scan   ({base / ex:4.2f}x fewer than before)")
 
 
 if __name__ == "__main__":
