@@ -1,5 +1,7 @@
+"""Debugging aid (test infrastructure: it uses the oracle as the checker): where a streamed-path frame differs from
+the oracle port.  usage: python tests/tools/debug_mismatch.py"""
 import os, sys, numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 from __graft_entry__ import load_package
 from oracle.portbind import PortOracle
 rt = load_package(); port = PortOracle(rt.abi); r = rt.Renderer(0)
