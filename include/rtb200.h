@@ -69,8 +69,13 @@ enum {
     RTB200_F_FORCE_RESIDENT = 1u << 4,/* always use the scene-resident fused kernel (fails if too large)  */
     RTB200_F_FUSED_FP     = 1u << 5,  /* contract every a*b+c into one FMA (fastest; NOT the reference's   */
                                       /* rounding: decisions on acne / edge pixels may flip) */
-    RTB200_F_GATHER_F32   = 1u << 6   /* multi-GPU: also gather the float RGB frame (default: RGBA8 only)   */
+    RTB200_F_GATHER_F32   = 1u << 6,  /* multi-GPU: also gather the float RGB frame (default: RGBA8 only)   */
+    RTB200_F_HOST_BANDS   = 1u << 7   /* several ranks: the host pointers of rtb200_render are the FULL frame on */
+                                      /* EVERY rank (one buffer shared by the ranks: threads of a process, or a  */
+                                      /* shared-memory segment between processes) and each rank copies its own    */
+                                      /* bands into it over its own PCIe link; nothing is gathered on the device  */
 };
+#define RTB200_MAX_BOUNCES 4096       /* rtb200_frame.max_bounces above this is refused (reference default: 20)  */
 
 /* Material block of ISurface (ISurface.h:24-41; defaults ISurface.cpp:15-25). 10 floats. */
 typedef struct rtb200_material {
@@ -222,6 +227,13 @@ int  rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* point3, const floa
 int  rtb200_comm_unique_id(uint8_t id[RTB200_UNIQUE_ID_BYTES]);
 int  rtb200_comm_init(rtb200_ctx* ctx, int rank, int n_ranks, const uint8_t id[RTB200_UNIQUE_ID_BYTES]);
 
+/* Sharding WITHOUT a communicator: the context renders only the bands of `rank` among `n_ranks` (same band
+ * layout); nothing is exchanged between contexts.  With RTB200_F_HOST_BANDS every context writes its bands
+ * into the caller's full host frame -- one process driving g GPUs from g threads needs nothing else
+ * (rt_cli --gpus g); without the flag the host pointers receive the rank's compact rows.  Replaces the
+ * single-process `device_ids[]` form of SURVEY.md 8b. */
+int  rtb200_set_sharding(rtb200_ctx* ctx, int rank, int n_ranks);
+
 /* The band layout rtb200_render uses with a communicator (pure host arithmetic, callable without a
  * GPU): rank `rank` renders *n_local rows and stores them compactly; out_global_rows[i] (capacity
  * >= *n_local, may be NULL) is the image row of its local row i.  band_rows 0 = default 16. */
@@ -233,9 +245,20 @@ int  rtb200_band_map(int height, int band_rows, int n_ranks, int rank,
  * rtb200_set_scene / rtb200_render are true async DMA). */
 int  rtb200_host_alloc(size_t bytes, void** out);
 void rtb200_host_free(void* p);
+/* Page-locks memory the caller already owns (e.g. a shared-memory segment holding the frame of several
+ * processes, RTB200_F_HOST_BANDS) for the lifetime of the registration. */
+int  rtb200_host_register(void* p, size_t bytes);
+int  rtb200_host_unregister(void* p);
 /* FP32 FMA peak of the context's GPU measured with a register-resident FFMA chain on every SM
  * (the denominator of the roofline fraction).  Returns TFLOP/s and the SM clock it saw. */
 int  rtb200_measure_fp32_peak(rtb200_ctx* ctx, double* tflops, double* sm_mhz);
+/* The same measurement with its parts, so that the figure can be recomputed: detail[0] TFLOP/s,
+ * [1] FFMA instructions per thread, [2] threads per block, [3] blocks, [4] elapsed ms of the best
+ * launch (CUDA events), [5] median SM cycles (clock64) and [6] nanoseconds (globaltimer) one block
+ * spent in the chain, [7] SM clock = cycles / ns in MHz, [8] FFMA issued per clock and SM
+ * (hardware limit 128), [9] SM count.  TFLOP/s = 2 x [1] x [2] x [3] / [4].  n >= 10. */
+#define RTB200_PEAK_DETAIL_COUNT 10
+int  rtb200_fp32_peak_detail(rtb200_ctx* ctx, double* detail, int n);
 /* Device properties the benchmark reports. */
 int  rtb200_device_info(rtb200_ctx* ctx, int* sm_count, int* l2_bytes, char* name, int name_len);
 /* Device-side stopwatch over SEVERAL calls (benchmarks time K frames as one region): records a

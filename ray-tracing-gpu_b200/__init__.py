@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 from . import abi
-from .abi import (F_EXACT_FP, F_FORCE_RESIDENT, F_FORCE_STREAM, F_FUSED_FP, F_GATHER_F32, F_NO_SECONDARY, F_USE_BVH,  # noqa: F401
+from .abi import (F_EXACT_FP, F_FORCE_RESIDENT, F_FORCE_STREAM, F_FUSED_FP, F_GATHER_F32, F_HOST_BANDS, F_NO_SECONDARY, F_USE_BVH,  # noqa: F401
                   Frame, PackedScene, Stats, make_frame)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -22,7 +22,7 @@ EXPORTS = [
     "rtb200_abi_version", "rtb200_create", "rtb200_destroy", "rtb200_error_string", "rtb200_last_error",
     "rtb200_set_scene", "rtb200_validate_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_render_sequence", "rtb200_read_frame",
     "rtb200_trace_nearest", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init", "rtb200_band_map",
-    "rtb200_host_alloc", "rtb200_host_free", "rtb200_measure_fp32_peak", "rtb200_device_info",
+    "rtb200_host_alloc", "rtb200_host_free", "rtb200_host_register", "rtb200_host_unregister", "rtb200_set_sharding", "rtb200_measure_fp32_peak", "rtb200_fp32_peak_detail", "rtb200_device_info",
     "rtb200_timer_mark", "rtb200_timer_elapsed",
 ]
 
@@ -64,7 +64,11 @@ def lib():
         L.rtb200_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
         L.rtb200_host_free.argtypes = [vp]
         L.rtb200_host_free.restype = None
+        L.rtb200_host_register.argtypes = [vp, C.c_size_t]
+        L.rtb200_host_unregister.argtypes = [vp]
+        L.rtb200_set_sharding.argtypes = [vp, C.c_int, C.c_int]
         L.rtb200_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.rtb200_fp32_peak_detail.argtypes = [vp, C.POINTER(C.c_double), C.c_int]
         L.rtb200_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_char_p, C.c_int]
         L.rtb200_band_map.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.POINTER(C.c_int)]
         L.rtb200_validate_scene.argtypes = [vp, C.POINTER(C.c_char_p)]
@@ -163,6 +167,14 @@ class Renderer:
         self._check(self.L.rtb200_measure_fp32_peak(self.h, C.byref(tf), C.byref(mhz)))
         return tf.value, mhz.value
 
+    def fp32_peak_detail(self):
+        """The FFMA-chain measurement with its parts (rtb200_fp32_peak_detail)."""
+        d = (C.c_double * 10)()
+        self._check(self.L.rtb200_fp32_peak_detail(self.h, d, 10))
+        keys = ("tflops", "ffma_per_thread", "threads_per_block", "blocks", "elapsed_ms", "block_cycles_median",
+                "block_ns_median", "sm_mhz_from_clock64_over_globaltimer", "ffma_per_clock_per_sm", "sm_count")
+        return dict(zip(keys, [float(v) for v in d]))
+
     def timer_mark(self, slot):
         self._check(self.L.rtb200_timer_mark(self.h, slot))
 
@@ -234,6 +246,16 @@ class Renderer:
         return out
 
     # multi-GPU ----------------------------------------------------------------------------
+    def set_sharding(self, rank, n_ranks):
+        """Band sharding without a communicator (rtb200_set_sharding)."""
+        self._check(self.L.rtb200_set_sharding(self.h, rank, n_ranks))
+
+    def host_register(self, arr):
+        self._check(self.L.rtb200_host_register(arr.ctypes.data, arr.nbytes))
+
+    def host_unregister(self, arr):
+        self._check(self.L.rtb200_host_unregister(arr.ctypes.data))
+
     def comm_unique_id(self):
         buf = (C.c_ubyte * abi.UNIQUE_ID_BYTES)()
         rc = self.L.rtb200_comm_unique_id(buf)

@@ -17,6 +17,7 @@ F_FORCE_STREAM = 1 << 3
 F_FORCE_RESIDENT = 1 << 4
 F_FUSED_FP = 1 << 5
 F_GATHER_F32 = 1 << 6
+F_HOST_BANDS = 1 << 7
 
 _fp = C.POINTER(C.c_float)
 _ip = C.POINTER(C.c_int32)

@@ -141,6 +141,30 @@ int rtb200_host_alloc(size_t bytes, void** out)
 
 void rtb200_host_free(void* p) { if (p) cudaFreeHost(p); }
 
+int rtb200_host_register(void* p, size_t bytes)
+{
+    if (!p || !bytes) return RTB200_E_ARG;
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return e == cudaErrorMemoryAllocation ? RTB200_E_OOM : RTB200_E_CUDA; }
+    return RTB200_OK;
+}
+
+int rtb200_host_unregister(void* p)
+{
+    if (!p) return RTB200_E_ARG;
+    if (cudaHostUnregister(p) != cudaSuccess) { (void)cudaGetLastError(); return RTB200_E_CUDA; }
+    return RTB200_OK;
+}
+
+int rtb200_set_sharding(rtb200_ctx* ctx, int rank, int n_ranks)
+{
+    if (!ctx || n_ranks < 1 || rank < 0 || rank >= n_ranks) return RTB200_E_ARG;
+    if (ctx->comm) return fail(ctx, RTB200_E_STATE, "rtb200_set_sharding on a context that has a communicator");
+    ctx->rank = rank; ctx->n_ranks = n_ranks;
+    ctx->level_guess.valid = false;
+    return RTB200_OK;
+}
+
 int rtb200_device_info(rtb200_ctx* ctx, int* sm_count, int* l2_bytes, char* name, int name_len)
 {
     if (!ctx) return RTB200_E_ARG;
@@ -180,6 +204,20 @@ int rtb200_measure_fp32_peak(rtb200_ctx* ctx, double* tflops, double* sm_mhz)
     ctx->peak_mhz = tf * 1e12 / (2.0 * 128.0 * ctx->sm_count) / 1e6;
     if (tflops) *tflops = tf;
     if (sm_mhz) *sm_mhz = ctx->peak_mhz;
+    return RTB200_OK;
+}
+
+int rtb200_fp32_peak_detail(rtb200_ctx* ctx, double* detail, int n)
+{
+    if (!ctx || !detail || n < RTB200_PEAK_DETAIL_COUNT) return RTB200_E_ARG;
+    CU(cudaSetDevice(ctx->device));
+    double tf = 0.0, d[8] = {0};
+    CU(run_fp32_peak(ctx->sm_count, &tf, ctx->stream, d));
+    ctx->peak_tflops = tf;
+    ctx->peak_mhz = tf * 1e12 / (2.0 * 128.0 * ctx->sm_count) / 1e6;
+    detail[0] = tf;
+    for (int i = 0; i < 8; ++i) detail[1 + i] = d[i];
+    detail[9] = (double)ctx->sm_count;
     return RTB200_OK;
 }
 
@@ -533,6 +571,43 @@ void fill_frame_params(const rtb200_frame* fr, int n_ranks, int rank, FrameParam
 // local frame.  The copy stream waits for that kernel only, so the transfer of chunk i runs under
 // the rendering of chunk i + 1 (PCIe and the SMs work at the same time).
 namespace rtb {
+// Local pixel rows [py0, py0 + prows) of this rank's compact frame -> the caller's host buffers, on stream `s`.
+// Plain case: the host buffers hold the same compact rows.  host_bands (several ranks, RTB200_F_HOST_BANDS): the host
+// buffers are the FULL frame and local band b (band_rows rows) is image band b * n_ranks + rank -- a 2-D copy whose
+// "row" is one whole band (contiguous on both sides), pitch = n_ranks bands on the host side.
+static cudaError_t copy_rows_out(rtb200_ctx* ctx, int W, int py0, int prows, cudaStream_t s)
+{
+    if (prows <= 0) return cudaSuccess;
+    cudaError_t e = cudaSuccess;
+    for (int which = 0; which < 2 && e == cudaSuccess; ++which) {
+        unsigned char* host = which == 0 ? reinterpret_cast<unsigned char*>(ctx->host_f32) : ctx->host_rgba8;
+        if (!host) continue;
+        const unsigned char* dev = which == 0 ? ctx->fb_f32.as<unsigned char>() : ctx->fb_rgba8.as<unsigned char>();
+        const size_t row_bytes = (size_t)W * (which == 0 ? 3 * sizeof(float) : 4);
+        if (!ctx->host_bands) {
+            e = cudaMemcpyAsync(host + row_bytes * py0, dev + row_bytes * py0, row_bytes * prows, cudaMemcpyDeviceToHost, s);
+            continue;
+        }
+        const int band = ctx->host_band_rows, n = ctx->n_ranks, r = ctx->rank;
+        int y = py0;
+        const int end = py0 + prows;
+        if (y % band) {                                     // (chunks start on band boundaries; belt and braces)
+            const int cnt = std::min(end - y, band - y % band);
+            e = cudaMemcpyAsync(host + row_bytes * band_global_row(band, n, r, y), dev + row_bytes * y, row_bytes * cnt, cudaMemcpyDeviceToHost, s);
+            y += cnt;
+        }
+        const int full = (end - y) / band;
+        if (full > 0 && e == cudaSuccess) {
+            e = cudaMemcpy2DAsync(host + row_bytes * band_global_row(band, n, r, y), row_bytes * band * n, dev + row_bytes * y, row_bytes * band,
+                                  row_bytes * band, (size_t)full, cudaMemcpyDeviceToHost, s);
+            y += full * band;
+        }
+        if (y < end && e == cudaSuccess)                    // the image's last, partial band
+            e = cudaMemcpyAsync(host + row_bytes * band_global_row(band, n, r, y), dev + row_bytes * y, row_bytes * (end - y), cudaMemcpyDeviceToHost, s);
+    }
+    return e;
+}
+
 int chunk_copy_out(rtb200_ctx* ctx, int W, int py0, int prows)
 {
     if ((!ctx->host_f32 && !ctx->host_rgba8) || prows <= 0) return RTB200_OK;
@@ -540,11 +615,7 @@ int chunk_copy_out(rtb200_ctx* ctx, int W, int py0, int prows)
     CU(cudaEventRecord(done, ctx->stream));
     CU(cudaStreamWaitEvent(ctx->copy_stream, done, 0));
     if (ctx->copy_chunks == 0) CU(cudaEventRecord(ctx->copy_ev[2], ctx->copy_stream));
-    const size_t off = (size_t)py0 * W, n = (size_t)prows * W;
-    if (ctx->host_f32)
-        CU(cudaMemcpyAsync(ctx->host_f32 + 3 * off, ctx->fb_f32.as<float>() + 3 * off, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->copy_stream));
-    if (ctx->host_rgba8)
-        CU(cudaMemcpyAsync(ctx->host_rgba8 + 4 * off, ctx->fb_rgba8.as<unsigned char>() + 4 * off, n * 4, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    CU(copy_rows_out(ctx, W, py0, prows, ctx->copy_stream));
     ++ctx->copy_chunks;
     return RTB200_OK;
 }
@@ -569,7 +640,10 @@ static int render_resident_async(rtb200_ctx* ctx, const rtb200_frame* fr, const 
     const bool known = g.valid && g.scene_serial == ctx->scene_serial && g.W == fp.W && g.H == fp.H && g.k == k &&
                        g.max_bounces == max_b && g.children == children && g.rows_per_chunk == rows_per_chunk &&
                        g.local_rows == local_rows;
-    int last = max_b;                                       // deepest level that gets a kernel
+    // deepest level that gets a kernel.  Unknown frame: probe a bounded depth (a level costs queues of >= 64 K entries
+    // and one launch per chunk even when the ray tree died long before); a tree that is deeper raises the overflow
+    // flag at the probe level and the frame is redone by the synchronous loop, which records the real depth.
+    int last = std::min(max_b, 8);
     if (known) {
         int used = 0;
         for (size_t l = 1; l < g.rays.size(); ++l) if (g.rays[l]) used = (int)l;
@@ -922,10 +996,17 @@ static int read_back(rtb200_ctx* ctx, float* out_f32, uint8_t* out_rgba8, double
     const size_t rows = full ? (size_t)ctx->last_H : (size_t)ctx->last_local_rows;
     const size_t px = rows * (size_t)ctx->last_W;
     CU(cudaEventRecord(ctx->ev[2], ctx->stream));
-    if (out_f32)
-        CU(cudaMemcpyAsync(out_f32, full ? static_cast<void*>(ctx->full_f32.as<unsigned char>() + ctx->full_off32) : ctx->fb_f32.p, px * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
-    if (out_rgba8)
-        CU(cudaMemcpyAsync(out_rgba8, full ? static_cast<void*>(ctx->full_rgba8.as<unsigned char>() + ctx->full_off8) : ctx->fb_rgba8.p, px * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->host_bands && !full) {                          // this rank's bands into the caller's full frame
+        ctx->host_f32 = out_f32; ctx->host_rgba8 = out_rgba8;
+        const cudaError_t e = copy_rows_out(ctx, ctx->last_W, 0, ctx->last_local_rows, ctx->stream);
+        ctx->host_f32 = nullptr; ctx->host_rgba8 = nullptr;
+        if (e != cudaSuccess) return set_cuda_error(ctx, e, "band read-back");
+    } else {
+        if (out_f32)
+            CU(cudaMemcpyAsync(out_f32, full ? static_cast<void*>(ctx->full_f32.as<unsigned char>() + ctx->full_off32) : ctx->fb_f32.p, px * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        if (out_rgba8)
+            CU(cudaMemcpyAsync(out_rgba8, full ? static_cast<void*>(ctx->full_rgba8.as<unsigned char>() + ctx->full_off8) : ctx->fb_rgba8.p, px * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    }
     CU(cudaEventRecord(ctx->ev[3], ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     float t = 0.f;
@@ -940,6 +1021,7 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     if (!ctx->have_scene) return fail(ctx, RTB200_E_STATE, "rtb200_render before rtb200_set_scene");
     if (fr->width <= 0 || fr->height <= 0 || fr->spp_grid < 0 || fr->spp_grid > 64) return fail(ctx, RTB200_E_ARG, "bad frame size");
     if ((long long)fr->width * std::max(fr->spp_grid, 1) > (1 << 20)) return fail(ctx, RTB200_E_ARG, "frame too wide");
+    if (fr->max_bounces > RTB200_MAX_BOUNCES) return fail(ctx, RTB200_E_ARG, "max_bounces above RTB200_MAX_BOUNCES");
     CU(cudaSetDevice(ctx->device));
     const bool exact = (fr->flags & RTB200_F_FUSED_FP) == 0;     // reference rounding unless fused is requested
     FrameParams fp;
@@ -963,13 +1045,18 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     // where the pixels go: the local band buffers, or -- several GPUs with peer access -- straight
     // into rank 0's full frame over NVLink (the producing kernels do the "gather" themselves)
     ctx->out_f32_dev = ctx->fb_f32.as<float>(); ctx->out_rgba8_dev = ctx->fb_rgba8.as<uchar4>();
-    const bool multi = ctx->comm && ctx->n_ranks > 1;
+    // RTB200_F_HOST_BANDS: every rank writes its own bands into the caller's FULL host frame (no gather on the device)
+    const bool host_bands = ctx->n_ranks > 1 && (fr->flags & RTB200_F_HOST_BANDS) != 0;
+    ctx->host_bands = host_bands; ctx->host_band_rows = band;
+    const bool multi = ctx->comm && ctx->n_ranks > 1 && !host_bands;
+    // (a float host pointer without RTB200_F_GATHER_F32 is simply not served on several GPUs: the decision must not
+    // depend on one rank's arguments, or the ranks would disagree about taking part in the frame)
     const bool gather_f32 = (fr->flags & RTB200_F_GATHER_F32) != 0;
+    if (multi && !gather_f32) out_f32 = nullptr;
     bool peer = false;
     PeerFrame pf;
     ctx->peer_cur = nullptr; ctx->peer_signalled = false;
     if (multi) {
-        if (ctx->rank == 0 && out_f32 && !gather_f32) return fail(ctx, RTB200_E_ARG, "float output on several GPUs needs RTB200_F_GATHER_F32");
         // rank 0 entering this frame has consumed the previous one: it tells the peers so (ack)
         const int prc = comm_peer_begin(ctx, fp.W, fp.H, gather_f32, true, false, &pf, ctx->stream);
         if (prc != RTB200_OK) return prc;
@@ -991,7 +1078,7 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     }
 
     // one GPU and host pointers given: read finished row chunks back while the next ones render
-    const bool overlap = !multi && (out_f32 || out_rgba8) && (size_t)fp.W * fp.H >= (256u << 10);
+    const bool overlap = !multi && (out_f32 || out_rgba8) && (size_t)fp.W * fp.H >= (256u << 10);   // (host bands: overlapped too)
     ctx->host_f32 = overlap ? out_f32 : nullptr;
     ctx->host_rgba8 = overlap ? out_rgba8 : nullptr;
     ctx->copy_chunks = 0;
@@ -1052,6 +1139,7 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     if (st.path == 0) st.rays_shadow = sum[ST_SHADOW];
     st.rays_reflect = sum[ST_REFLECT]; st.rays_refract = sum[ST_REFRACT];
     st.nan_pixels = sum[ST_NAN];
+    if (sum[ST_PEER_TIMEOUT]) return fail(ctx, RTB200_E_NCCL, "peer frame: rank 0 did not acknowledge the previous frame within 2 s; this frame may be torn");
     if (st.path == 0) {
         // resident kernels count surface tests in one counter; split by the scene's type mix
         const double n = std::max(1, ctx->ds.rl.n_surf);
@@ -1082,7 +1170,8 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
         CU(cudaEventElapsedTime(&t, ctx->copy_ev[2], ctx->copy_ev[3]));
         st.ms_d2h = t;                                          // mostly hidden under the rendering
     } else if (ctx->rank == 0 || !ctx->last_gathered) {
-        const bool want = (ctx->n_ranks <= 1) || ctx->rank == 0;
+        // every rank when it owns what it reads (host bands, or sharding without a communicator); else rank 0 only
+        const bool want = (ctx->n_ranks <= 1) || ctx->rank == 0 || ctx->host_bands || !ctx->comm;
         if (want) {
             rc = read_back(ctx, out_f32, out_rgba8, &st.ms_d2h);
             if (rc != RTB200_OK) return rc;
@@ -1103,6 +1192,24 @@ extern "C" int rtb200_read_frame(rtb200_ctx* ctx, float* out_f32, uint8_t* out_r
 // ---------------------------------------------------------------------------------------
 // Ray-level queries
 // ---------------------------------------------------------------------------------------
+// After a query through the streamed / LBVH kernels: the device counters they wrote.  A traversal whose stack
+// overflowed is an error here exactly as in rtb200_render (the hit would be wrong, silently).
+static int query_counters_check(rtb200_ctx* ctx)
+{
+    const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
+    cudaError_t e;
+    if ((e = ctx->h_small.ensure(8192)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
+    unsigned long long* h_st = reinterpret_cast<unsigned long long*>(ctx->h_small.as<unsigned char>() + 1024);
+    CU(cudaMemcpyAsync(h_st, ctx->stats.p, stat_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemsetAsync(ctx->stats.p, 0, stat_bytes, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    ctx->stats_clean = true;
+    unsigned long long overflow = 0;
+    for (int s = 0; s < RT_STAT_SLOTS; ++s) overflow += h_st[s * ST_COUNT + ST_BVH_OVERFLOW];
+    if (overflow) return fail(ctx, RTB200_E_CAPACITY, "LBVH traversal stack overflow");
+    return RTB200_OK;
+}
+
 extern "C" int rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* o3, const float* d3, uint32_t flags,
                                     int32_t* out_order, float* out_t, float* out_n3)
 {
@@ -1130,6 +1237,7 @@ extern "C" int rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* o3, con
     CU(cudaMemcpyAsync(out_t, ctx->q_out1.p, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemcpyAsync(out_n3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    if (q_stream) return query_counters_check(ctx);
     return RTB200_OK;
 }
 
@@ -1155,6 +1263,7 @@ extern "C" int rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* p3, cons
                            (flags & RTB200_F_FUSED_FP) == 0, (flags & RTB200_F_EXACT_FP) == 0, ctx->stream));
     CU(cudaMemcpyAsync(out3, ctx->q_out2.p, b3, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    if (q_stream) return query_counters_check(ctx);
     return RTB200_OK;
 }
 

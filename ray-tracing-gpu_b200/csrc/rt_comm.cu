@@ -107,6 +107,8 @@ int comm_unique_id(uint8_t* id)
     return RTB200_OK;
 }
 
+static int all_min(rtb200_ctx* c, int v, int* out);
+
 int comm_init(rtb200_ctx* c, int rank, int n_ranks, const uint8_t* id)
 {
     comm_destroy(c);
@@ -122,6 +124,12 @@ int comm_init(rtb200_ctx* c, int rank, int n_ranks, const uint8_t* id)
     if (r != ncclSuccess) { delete cm; return nccl_fail(c, r, "ncclCommInitRank"); }
     cudaEventCreate(&cm->e0); cudaEventCreate(&cm->e1);
     c->comm = cm; c->rank = rank; c->n_ranks = n_ranks;
+    // RTB200_NO_P2P is read ONCE, here, and agreed on by all ranks: every later branch of the frame path must depend
+    // on replicated state only (a rank that alone skipped the peer frame would desynchronise the frame counter)
+    int agreed = 1;
+    const int rc = all_min(c, getenv("RTB200_NO_P2P") ? 0 : 1, &agreed);
+    if (rc != RTB200_OK) return rc;
+    if (!agreed) { cm->p2p_tried = true; cm->p2p = false; }
     return RTB200_OK;
 }
 
@@ -406,7 +414,6 @@ int comm_peer_begin(rtb200_ctx* c, int W, int H, bool want_f32, bool ack_previou
     *pf = PeerFrame();
     if (!nccl_api() || !cm) return RTB200_E_STATE;
     if (cm->p2p_tried && !cm->p2p) return RTB200_OK;
-    if (getenv("RTB200_NO_P2P")) { cm->p2p_tried = true; cm->p2p = false; return RTB200_OK; }
     const size_t need8 = 4 * (size_t)W * H, need32 = want_f32 ? sizeof(float) * 3 * (size_t)W * H : 0;
     if (!(cm->p2p && need8 <= cm->stride8 && need32 <= cm->stride32)) {
         const int rc = peer_establish(c, std::max(need8, cm->stride8), want_f32 ? std::max(need32, cm->stride32) : cm->stride32);

@@ -96,6 +96,8 @@ struct rtb200_ctx {
     float*   host_f32 = nullptr;      // non-null during a render that overlaps its read-back
     uint8_t* host_rgba8 = nullptr;
     int      copy_chunks = 0;         // chunks already handed to the copy stream in this frame
+    bool     host_bands = false;      // RTB200_F_HOST_BANDS frame: the host pointers are the FULL frame, this rank writes its bands
+    int      host_band_rows = 16;
     // level loop without host round trips (resident path with secondary rays): what the last frame
     // of this shape needed per level, the guess the next one is sized by
     struct LevelGuess {

@@ -8,6 +8,9 @@ namespace rtb {
 enum {                             // per-slot counter index
     ST_SHADOW = 0, ST_REFLECT, ST_REFRACT, ST_NAN, ST_TEST_TRI, ST_TEST_QUAD, ST_TEST_PLANE, ST_BVH_NODES,
     ST_BVH_OVERFLOW, ST_TEST_TRI_SHADOW, ST_BVH_NODES_SHADOW, ST_TEST_TRI_EXEC,
+    ST_PEER_TIMEOUT,               // CTAs that gave up waiting for rank 0's acknowledgement (peer frame): the frame may be torn
+    ST_SHADOW_FIXUP,               // shadow queries whose filter product was redone in insertion order (rt_cullscan.cu)
+    ST_BVH_OUT_OF_RADIUS,          // LBVH rays that started beyond the radius the boxes are padded for (took the widened walk)
     ST_COUNT
 };
 
@@ -143,6 +146,6 @@ cudaError_t launch_query_shadow(const DeviceScene& s, int n, const float* p3, co
                                 float* out3, bool exact, bool cull, cudaStream_t st);
 
 // FFMA peak micro-benchmark (rt_peak.cu): returns FFMA-chain flop count and elapsed ms
-cudaError_t run_fp32_peak(int sm_count, double* tflops, cudaStream_t st);
+cudaError_t run_fp32_peak(int sm_count, double* tflops, cudaStream_t st, double* detail = nullptr);
 
 } // namespace rtb

@@ -10,6 +10,9 @@
 // recursion; every level runs on a compacted queue so warps never diverge on depth.
 #include <algorithm>
 #include <cstring>
+#include <map>
+#include <mutex>
+#include <utility>
 
 #include "rt_kernels.cuh"
 #include "rt_cull.cuh"
@@ -235,7 +238,7 @@ k_resident_level(const __grid_constant__ LevelParams p)
     const FrameParams& f = p.f;
     const int tiles_x = (f.LW + 15) >> 4;
     const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + RES_TILE_H - 1) / RES_TILE_H) : (in_count + RES_THREADS - 1) / RES_THREADS;
-    if (p.peer_ack) peer_frame_wait_ack(p.peer_ack, p.peer_ack_min);      // several GPUs: the frame half is free
+    if (p.peer_ack) peer_frame_wait_ack(p.peer_ack, p.peer_ack_min, p.stats ? p.stats + ST_PEER_TIMEOUT : nullptr);      // several GPUs: the frame half is free
     mbar_wait(&bar, 0);
     SceneView sv;
     sv.surf  = reinterpret_cast<const SurfRec*>(smem);
@@ -599,7 +602,28 @@ cudaError_t resident_prepare(size_t max_smem_bytes)
     return cudaSuccess;
 }
 
-static int g_resident_ctas_per_sm = 0;          // occupancy of the level kernel (queried once)
+// occupancy of the level kernels, cached per (instantiation, dynamic shared-memory bytes): it depends on the scene
+// blob size and differs between the primary and the secondary instantiation.  (A property of the kernel image and of
+// sm_100 alone, so one small process-wide table serves every context; guarded for multi-threaded callers.)
+static int resident_ctas_per_sm(int inst, size_t smem)
+{
+    static std::mutex mu;
+    static std::map<std::pair<int, size_t>, int> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find({inst, smem});
+    if (it != cache.end()) return it->second;
+    int n = 0;
+    cudaError_t e;
+    switch (inst) {
+    case 0:  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_resident_level<true, true>, RES_THREADS, smem); break;
+    case 1:  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_resident_level<false, true>, RES_THREADS, smem); break;
+    case 2:  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_resident_level<true, false>, RES_THREADS, smem); break;
+    default: e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_resident_level<false, false>, RES_THREADS, smem); break;
+    }
+    if (e != cudaSuccess || n <= 0) { (void)cudaGetLastError(); n = 1; }
+    cache[{inst, smem}] = n;
+    return n;
+}
 
 // plain launch, or (pdl) one that may start before the kernel ahead of it in the stream has finished
 template <class P>
@@ -620,12 +644,7 @@ cudaError_t launch_resident_level(const LevelParams& p_in, bool exact, int sm_co
     // the table rides along while the scene is small (it must not cost a resident CTA)
     p.pre_table = (p.level == 0 && p.rl.bytes <= 16 * 1024) ? 1 : 0;
     const size_t smem = p.pre_table ? resident_smem_with_table(p.rl) : resident_smem_bytes(p.rl);
-    if (g_resident_ctas_per_sm <= 0) {
-        int n = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_resident_level<true, true>, RES_THREADS, smem) != cudaSuccess || n <= 0) n = 2;
-        g_resident_ctas_per_sm = n;
-    }
-    const int max_ctas = g_resident_ctas_per_sm * sm_count;
+    const int max_ctas = resident_ctas_per_sm((exact ? 0 : 1) + (p.level == 0 ? 0 : 2), smem) * sm_count;
     const bool pdl = p.pdl == 2;
     if (p.level == 0) {
         const int tiles_x = (p.f.LW + 15) / 16, tiles_y = (p.chunk_rows + RES_TILE_H - 1) / RES_TILE_H;

@@ -146,8 +146,9 @@ __device__ __forceinline__ void peer_frame_signal(unsigned int* done, unsigned i
 
 // Peer frame: thread 0 of a CTA waits until rank 0's acknowledgement word (LOCAL memory, written by
 // rank 0 over NVLink) has reached `want` (cyclic compare).  Normally true on the first load.  Gives
-// up after 2 s of GPU time: a torn frame on a broken peer beats a hung GPU.  Followed by a barrier.
-__device__ __forceinline__ void peer_frame_wait_ack(const unsigned int* ack, unsigned int want)
+// up after 2 s of GPU time (a hung GPU is worse than a failed call) and says so in *timeouts: the host turns a
+// non-zero count into RTB200_E_NCCL -- the frame may be torn and must not be used.  Followed by a barrier.
+__device__ __forceinline__ void peer_frame_wait_ack(const unsigned int* ack, unsigned int want, unsigned long long* timeouts)
 {
     if (threadIdx.x == 0 && threadIdx.y == 0) {
         unsigned long long t0 = 0;
@@ -158,7 +159,7 @@ __device__ __forceinline__ void peer_frame_wait_ack(const unsigned int* ack, uns
             unsigned long long now;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
             if (t0 == 0) t0 = now;
-            else if (now - t0 > 2000000000ull) break;
+            else if (now - t0 > 2000000000ull) { if (timeouts) atomicAdd(timeouts, 1ull); break; }
             __nanosleep(200);
         }
     }

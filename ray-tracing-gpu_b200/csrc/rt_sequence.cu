@@ -199,6 +199,12 @@ extern "C" int rtb200_render_sequence(rtb200_ctx* ctx, const rtb200_frame* frame
     ctx->last_W = fp0.W; ctx->last_H = fp0.H; ctx->last_local_rows = local_rows;
     ctx->last_gathered = multi && ctx->rank == 0;
     if (out_rgba8) ctx->last_W = 0;                           // the frames went to the host; nothing to read back later
+    {   // a CTA that gave up waiting for rank 0's acknowledgement: the sequence may hold torn frames
+        const unsigned long long* h = ctx->seq_host.as<unsigned long long>();
+        unsigned long long timeouts = 0;
+        for (size_t i = 0; i < (size_t)n_frames * RT_STAT_SLOTS; ++i) timeouts += h[i * ST_COUNT + ST_PEER_TIMEOUT];
+        if (timeouts) { ctx->last_error = "peer frame: rank 0 did not acknowledge within 2 s; frames of this sequence may be torn"; return RTB200_E_NCCL; }
+    }
     if (stats) {
         const unsigned long long* h = ctx->seq_host.as<unsigned long long>();
         const double n_surf = std::max(1, ctx->ds.rl.n_surf);

@@ -282,11 +282,16 @@ int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
     cudaError_t e;
     if ((e = sb->sq0.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess || (e = sb->sq1.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess ||
         (e = sb->hit.ensure(sizeof(float2) * (size_t)n)) != cudaSuccess) return set_cuda_error(c, e, "query scratch");
+    const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
+    if ((e = c->stats.ensure(stat_bytes)) != cudaSuccess) return set_cuda_error(c, e, "stats");
+    if (!c->stats_clean) SCU(cudaMemsetAsync(c->stats.p, 0, stat_bytes, c->stream));
+    c->stats_clean = false;                      // the traversal reports a stack overflow through the frame counters
     SCU(launch_query_pack_rays(n, c->q_in0.as<float>(), c->q_in1.as<float>(), sb->sq0.as<float4>(), sb->sq1.as<float4>(), c->stream));
     TraceParams tp;
     memset(&tp, 0, sizeof tp);
     tp.s = c->ds; tp.primary = 0; tp.in_od0 = sb->sq0.as<float4>(); tp.in_od1 = sb->sq1.as<float4>();
     tp.n_rays = n; tp.hit = sb->hit.as<float2>(); tp.mode = mode; tp.cull_bundles = bundle_cull_enabled();
+    tp.stats = c->stats.as<unsigned long long>();
     if (flags & RTB200_F_USE_BVH) SCU(launch_bvh_nearest(tp, c->stream));
     else                          SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
     SCU(launch_query_finish_nearest(c->ds, n, tp.in_od0, tp.in_od1, tp.hit, c->q_out0.as<int>(), c->q_out1.as<float>(),
@@ -304,6 +309,7 @@ int stream_query_shadow(rtb200_ctx* c, int n, uint32_t flags)
         (e = sb->filter.ensure(sizeof(float4) * (size_t)n)) != cudaSuccess) return set_cuda_error(c, e, "query scratch");
     const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
     if ((e = c->stats.ensure(stat_bytes)) != cudaSuccess) return set_cuda_error(c, e, "stats");
+    if (!c->stats_clean) SCU(cudaMemsetAsync(c->stats.p, 0, stat_bytes, c->stream));
     c->stats_clean = false;                      // the query kernels add to the frame counters
     SCU(launch_query_pack_shadow(n, c->q_in0.as<float>(), c->q_in1.as<float>(), sb->sq0.as<float4>(), sb->sq1.as<float4>(), mode != 2, c->stream));
     ShadowParams sp;
