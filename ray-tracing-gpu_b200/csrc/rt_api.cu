@@ -870,7 +870,7 @@ static int render_resident(rtb200_ctx* ctx, const rtb200_frame* fr, const FrameP
     if ((e = ctx->c0.ensure(sizeof(float) * 3 * (size_t)rows_per_chunk * fp.LW)) != cudaSuccess) return set_cuda_error(ctx, e, "c0");
     const size_t n_counters = 2 * ((size_t)std::max(fr->max_bounces, 0) + 2);
     if ((e = ctx->counters.ensure(sizeof(unsigned) * n_counters)) != cudaSuccess) return set_cuda_error(ctx, e, "counters");
-    if ((e = ctx->h_small.ensure(8192)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
+    if ((e = ctx->h_small.ensure(16384)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
     unsigned* h_cnt = ctx->h_small.as<unsigned>();
     unsigned* d_cnt = ctx->counters.as<unsigned>();
     unsigned max_level_seen = 0, chunks = 0;
@@ -1038,7 +1038,7 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
     if ((e = ctx->fb_rgba8.ensure(lpx * 4)) != cudaSuccess) return set_cuda_error(ctx, e, "fb_rgba8");
     const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
     if ((e = ctx->stats.ensure(stat_bytes)) != cudaSuccess) return set_cuda_error(ctx, e, "stats");
-    if ((e = ctx->h_small.ensure(8192)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
+    if ((e = ctx->h_small.ensure(16384)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
     if (!ctx->stats_clean) CU(cudaMemsetAsync(ctx->stats.p, 0, stat_bytes, ctx->stream));
     ctx->stats_clean = false;
 
@@ -1198,7 +1198,7 @@ static int query_counters_check(rtb200_ctx* ctx)
 {
     const size_t stat_bytes = sizeof(unsigned long long) * RT_STAT_SLOTS * ST_COUNT;
     cudaError_t e;
-    if ((e = ctx->h_small.ensure(8192)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
+    if ((e = ctx->h_small.ensure(16384)) != cudaSuccess) return set_cuda_error(ctx, e, "pinned small");
     unsigned long long* h_st = reinterpret_cast<unsigned long long*>(ctx->h_small.as<unsigned char>() + 1024);
     CU(cudaMemcpyAsync(h_st, ctx->stats.p, stat_bytes, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaMemsetAsync(ctx->stats.p, 0, stat_bytes, ctx->stream));

@@ -211,7 +211,7 @@ int comm_gather_frame(rtb200_ctx* c, int W, int H, int band, bool want_f32, bool
         // rank_row_off lives in the tail of the stats buffer's pinned mirror -> use a small device copy
         DevBuf& cnt = c->counters;
         if ((e = cnt.ensure(sizeof(long long) * ((size_t)n + 1) + 64)) != cudaSuccess) return set_cuda_error(c, e, "offsets");
-        long long* h_off = reinterpret_cast<long long*>(c->h_small.as<unsigned char>() + 6144);
+        long long* h_off = reinterpret_cast<long long*>(c->h_small.as<unsigned char>() + 12288);
         memcpy(h_off, off.data(), sizeof(long long) * ((size_t)n + 1));
         if ((e = cudaMemcpyAsync(cnt.p, h_off, sizeof(long long) * ((size_t)n + 1), cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) return set_cuda_error(c, e, "offsets copy");
         dim3 grid((unsigned)std::min((W + 255) / 256, 64), (unsigned)H);
