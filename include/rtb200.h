@@ -158,6 +158,10 @@ typedef struct rtb200_stats {
                                    /* with exact capacities (same pixels, slower)                           */
     uint64_t tests_triangle_executed; /* streamed path: (ray, triangle) tests actually entered after the warp-level */
                                    /* bundle culling (tests_triangle counts what the reference's scan performs)   */
+    uint64_t shadow_fixups;        /* streamed path: shadow queries whose filter product (>= 3 transparent occluders */
+                                   /* met out of insertion order) was redone in the order of Scene.cpp:1856          */
+    uint64_t bvh_out_of_radius;    /* LBVH: rays that started farther from the mesh than the radius its boxes are    */
+                                   /* padded for and were walked with a pad widened for their own origin             */
 } rtb200_stats;
 
 typedef struct rtb200_ctx rtb200_ctx;

@@ -64,7 +64,8 @@ class Stats(C.Structure):
                 ("ms_trace_nearest", C.c_double), ("ms_trace_shadow", C.c_double),
                 ("ms_shade", C.c_double), ("ms_primary_kernel", C.c_double),
                 ("shadow_tests_triangle", C.c_uint64), ("shadow_bvh_nodes", C.c_uint64),
-                ("level_loop_redone", C.c_uint64), ("tests_triangle_executed", C.c_uint64)]
+                ("level_loop_redone", C.c_uint64), ("tests_triangle_executed", C.c_uint64),
+                ("shadow_fixups", C.c_uint64), ("bvh_out_of_radius", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -116,6 +116,7 @@ void rtb200_destroy(rtb200_ctx* ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     comm_destroy(ctx);
     stream_release(ctx);
+    cull_release(ctx);
     bvh_release(ctx);
     ctx->scene_buf.release(); ctx->stage.release(); ctx->raw_buf.release();
     ctx->c0.release(); ctx->fb_f32.release(); ctx->fb_rgba8.release(); ctx->stats.release(); ctx->counters.release();
@@ -1150,6 +1151,8 @@ extern "C" int rtb200_render(rtb200_ctx* ctx, const rtb200_frame* fr, float* out
         st.shadow_tests_triangle = sum[ST_TEST_TRI_SHADOW];
         st.shadow_bvh_nodes = sum[ST_BVH_NODES_SHADOW];
         st.tests_triangle_executed = sum[ST_TEST_TRI_EXEC];
+        st.shadow_fixups = sum[ST_SHADOW_FIXUP];
+        st.bvh_out_of_radius = sum[ST_BVH_OUT_OF_RADIUS];
         st.tests_triangle = sum[ST_TEST_TRI] + sum[ST_TEST_TRI_SHADOW] + ctx->host_tests[0];
         st.tests_quadric = sum[ST_TEST_QUAD] + ctx->host_tests[1];
         st.tests_plane = sum[ST_TEST_PLANE] + ctx->host_tests[2];

@@ -128,6 +128,7 @@ struct rtb200_ctx {
     // streamed path scratch (rt_stream.cu) and host-side test counts of the last frame
     void* stream_scratch = nullptr;
     void* bvh_state = nullptr;        // rt_bvh.cu
+    void* cull_state = nullptr;       // rt_cullscan.cu: Morton-sorted triangles + sphere hierarchy of the current scene
     unsigned long long host_tests[3] = {0, 0, 0};
 
     // peak cache
@@ -142,6 +143,9 @@ int  chunk_copy_out(rtb200_ctx* c, int W, int py0, int prows);              // r
 int  render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp, int local_rows,
                      bool exact, rtb200_stats* st, uint32_t* launches);     // rt_stream.cu
 void stream_release(rtb200_ctx* c);
+struct CullScene;
+int  cull_prepare(rtb200_ctx* c, CullScene* out);                            // rt_cullscan.cu
+void cull_release(rtb200_ctx* c);
 int  stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags);            // inputs q_in0/q_in1, outputs q_out0..2 (device)
 int  stream_query_shadow(rtb200_ctx* c, int n, uint32_t flags);
 // rt_comm.cu

@@ -1,0 +1,834 @@
+// rt_cullscan.cu -- the culled scan: the default kernels of the streamed path (large scenes, brute-force semantics).
+//
+// The reference tests every ray against every surface (Scene.cpp:1710-1715, :1850-1858).  The plain tiled kernels of
+// rt_trace.cu do exactly that at 2/3 of the FP32 peak; this file gets the SAME answers -- every kept value is still
+// produced by the reference's rounding sequence -- without entering most of those tests:
+//   * once per scene (cull_prepare, all on the device): the triangles are sorted by the Morton code of their centroid
+//     and a 32-ary hierarchy of bounding spheres is laid over the sorted array -- level 0 one sphere per triangle,
+//     level l one sphere per block of 32 level-(l-1) entries (no pointers: entry i of level l covers entries
+//     32 i .. 32 i + 31 of level l - 1);
+//   * a WARP holds 128 rays (4 per lane) and the cone(s) that contain them (rt_bundle.cuh: primary rays one cone from
+//     the camera, secondary rays up to four, shadow queries up to two per light with the light as apex).  It walks
+//     the hierarchy top-down: in a round lane j tests entry j of a block against the cones, the ballot of the
+//     survivors is the list of blocks to descend into -- one coalesced 512-byte load and ~50 instructions per lane
+//     decide 32 spheres;
+//   * the triangles that survive level 0 are queued per warp (shared memory) and then tested ray by ray with the
+//     two-phase filter + reference sequence of rt_cull.cuh, four rays per lane interleaved, the next triangle's
+//     record prefetched while the current one is tested;
+//   * warps never meet: no CTA barrier anywhere (the tile loop of rt_trace.cu met at two barriers per 256 triangles
+//     with survivor counts that differed by orders of magnitude: ncu, profiles/r1_c3_shadow_culled_ncu_full.txt);
+//     they take tasks of 128 rays from an atomic counter, so a slow bundle delays nobody;
+//   * quadrics of centred form (spheres, ellipsoids) are culled per warp the same way, lane j looking at quadric j.
+// A sphere that is culled contains no point at which any ray of the bundle can be REPORTED to hit the triangle by
+// CTriangle::Intersection -- the contract and the pad of rt_bundle.cuh; a block's sphere contains the inflated spheres
+// of everything below it (cull_prepare), so culling a block culls only what its members' own tests would cull.
+// Shadow filters: Scene.cpp:1856 multiplies in insertion order; the walk meets the occluders in Morton order.  Up to
+// two factors commute exactly; a query with three or more occluders met out of order and a non-zero product is redone
+// by k_shadow_fixup in insertion order (counted in rtb200_stats.shadow_fixups).
+#include <cfloat>
+#include <climits>
+
+#include <cub/cub.cuh>
+
+#include "rt_context.h"
+#include "rt_cullscan.cuh"
+#include "rt_bundle.cuh"
+
+namespace rtb {
+
+#define CS_THREADS    128
+#define CS_WARPS      (CS_THREADS / 32)
+#define CS_QCAP       160          // per-warp queue of surviving triangles; drained when fewer than 32 slots are free
+#define CS_MAX_CONES  16           // shadow: 8 lights x 2; nearest: 4
+#define CS_NEAREST_CONES 4
+#ifndef CS_MIN_CTAS
+#define CS_MIN_CTAS   4
+#endif
+
+// offsets of the levels inside the one array that holds them all: [level 3][level 2][level 1][level 0]
+RT_DEV int cs_level_offset(int n3, int level)
+{
+    return level == 0 ? 1057 * n3 : (level == 1 ? 33 * n3 : (level == 2 ? n3 : 0));
+}
+
+struct CsWarpSmem {
+    Bundle cones[CS_MAX_CONES];
+    int    queue[CS_QCAP];
+};
+
+template <bool LIGHT>
+RT_DEV bool cs_keep(const Bundle* cones, int n_c, bool keep_all, float4 sph, float w)
+{
+    bool keep = keep_all;
+    for (int k = 0; k < n_c; ++k) {
+        const Bundle& b = cones[k];
+        const bool culled = LIGHT ? light_cone_culls(b, sph, w) : bundle_culls(b, mk3(sph.x, sph.y, sph.z), sph.w, w);
+        keep = keep || !culled;
+    }
+    return keep && w > 0.f;
+}
+
+// Top-down walk of the sphere hierarchy with the warp's cones.  sink(first, mask): bit j of mask = triangle first + j
+// survived level 0; returns true to stop the walk (a shadow warp whose filters are all zero).
+template <int L, bool LIGHT, class Sink>
+RT_DEV bool cs_level(const CullScene& cs, const Bundle* cones, int n_c, bool keep_all, int lane, int block, Sink& sink)
+{
+    const int i = cs_level_offset(cs.n3, L) + block * 32 + lane;
+    bool keep = false;
+    if (L < CS_LEVELS - 1 || block * 32 + lane < cs.n3)       // (the top level holds n3 entries, not a multiple of 32)
+        keep = cs_keep<LIGHT>(cones, n_c, keep_all, __ldg(cs.sph + i), __ldg(cs.w + i));
+    unsigned int m = __ballot_sync(FULL_MASK, keep);
+    if constexpr (L == 0) {
+        return m ? sink(block * 32, m) : false;
+    } else {
+        while (m) {
+            const int child = block * 32 + __ffs((int)m) - 1;
+            m &= m - 1u;
+            if (cs_level<L - 1, LIGHT>(cs, cones, n_c, keep_all, lane, child, sink)) return true;
+        }
+        return false;
+    }
+}
+
+template <bool LIGHT, class Sink>
+RT_DEV void cs_walk(const CullScene& cs, const Bundle* cones, int n_c, bool keep_all, int lane, Sink&& sink)
+{
+    for (int b = 0; b < cs.top_blocks; ++b)
+        if (cs_level<CS_LEVELS - 1, LIGHT>(cs, cones, n_c, keep_all, lane, b, sink)) return;
+}
+
+// quadrics of centred form  sum q_i (x_i - c_i)^2 = rhs, q_i > 0 (r3 = c | rhs, rhs > 0): bounding sphere of the region
+// outside of which the reference's discriminant cannot come out positive for any origin within D of the centre
+// (the margin of quadric_miss, rt_resident.cu / DESIGN.md 5.3: rhs * 1.05 + 2e-5 * M, M = sum q_i (o_i^2 + c_i^2) with
+// |o_i| <= |c_i| + D).  Returns false when the quadric has no such sphere (cylinders, cones, rotated ones: always kept).
+RT_DEV bool cs_quadric_sphere(float4 q0, float4 r3, float D, float& radius)
+{
+    if (!(r3.w > 0.f) || !(q0.x > 0.f) || !(q0.y > 0.f) || !(q0.z > 0.f)) return false;
+    const float fx = fabsf(r3.x) + D, fy = fabsf(r3.y) + D, fz = fabsf(r3.z) + D;
+    const float M = q0.x * (fx * fx + r3.x * r3.x) + q0.y * (fy * fy + r3.y * r3.y) + q0.z * (fz * fz + r3.z * r3.z);
+    const float lim = fmaf(r3.w, 1.05f, 2.0e-5f * M * 1.001f);
+    const float qmin = fminf(q0.x, fminf(q0.y, q0.z));
+    radius = sqrtf(lim / qmin) * 1.0001f;
+    return radius <= 3.0e37f;
+}
+
+template <bool LIGHT>
+RT_DEV bool cs_keep_quadric(const Bundle* cones, int n_c, bool keep_all, float4 q0, float4 r3)
+{
+    if (keep_all) return true;
+    bool keep = false;
+    for (int k = 0; k < n_c; ++k) {
+        const Bundle& b = cones[k];
+        const float vx = r3.x - b.ax, vy = r3.y - b.ay, vz = r3.z - b.az;
+        const float D = sqrtf(fmaf(vx, vx, fmaf(vy, vy, vz * vz))) * 1.0001f + b.dadd;      // every origin lies within D of the centre
+        float radius;
+        if (!cs_quadric_sphere(q0, r3, D, radius)) return true;
+        const float4 sph = make_float4(r3.x, r3.y, r3.z, radius);
+        const bool culled = LIGHT ? light_cone_culls(b, sph, 0.f) : bundle_culls(b, mk3(sph.x, sph.y, sph.z), sph.w, 0.f);
+        keep = keep || !culled;
+    }
+    return keep;
+}
+
+// the cones of a warp's 128 nearest-hit rays: one, or -- when that one is wide -- up to four after two splits around the
+// most distant directions.  Returns the number of cones written (0 with keep_all = true: nothing can be culled).
+RT_DEV int cs_nearest_cones(const V3* o, const V3* d, const bool* use, Bundle* cones, int lane, bool& keep_all)
+{
+    keep_all = false;
+    Bundle one = bundle_of_rays(o, d, use);
+    if (one.state == 0) return 0;                               // no rays at all
+    if (one.state == 1 && !(one.sin_t > BUNDLE_SPLIT_SIN)) {
+        if (lane == 0) cones[0] = one;
+        __syncwarp();
+        return 1;
+    }
+    V3 dn[ST_RPT];
+    #pragma unroll
+    for (int r = 0; r < ST_RPT; ++r) {
+        const float l2 = dot3<false>(d[r], d[r]);
+        const float il = (l2 > 1.0e-20f && l2 < 1.0e20f) ? rsqrtf(l2) : 0.f;
+        dn[r] = mk3(d[r].x * il, d[r].y * il, d[r].z * il);
+    }
+    bool ga[ST_RPT], gb[ST_RPT], g[CS_NEAREST_CONES][ST_RPT];
+    split_members(dn, use, ga, gb);
+    split_members(dn, ga, g[0], g[1]);
+    split_members(dn, gb, g[2], g[3]);
+    int n = 0;
+    bool usable = true;
+    #pragma unroll
+    for (int k = 0; k < CS_NEAREST_CONES; ++k) {
+        const Bundle b = bundle_of_rays(o, d, g[k]);            // state 0: an empty part
+        usable = usable && b.state != 2;
+        if (b.state == 1) { if (lane == 0) cones[n] = b; ++n; }
+    }
+    if (!usable) {
+        if (one.state == 1) { if (lane == 0) cones[0] = one; __syncwarp(); return 1; }
+        keep_all = true;
+        return 0;
+    }
+    __syncwarp();
+    return n;
+}
+
+// ---------------------------------------------------------------------------------------
+// Nearest hit (Scene.cpp:1705-1720).  One warp task = 128 rays: PRIMARY a 16 x 8 block of the sample lattice
+// (thread = a 2 x 2 quad, rays generated on the fly), otherwise 128 consecutive queue entries.
+// ---------------------------------------------------------------------------------------
+template <int MODE, bool PRIMARY>
+__global__ void __launch_bounds__(CS_THREADS, CS_MIN_CTAS)
+k_cull_nearest(const __grid_constant__ CullTraceParams cp)
+{
+    __shared__ CsWarpSmem sm[CS_WARPS];
+    const TraceParams& p = cp.t;
+    const CullScene& cs = cp.cs;
+    const DeviceScene& s = p.s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    CsWarpSmem& ws = sm[warp];
+    const int tiles_x = (p.f.LW + 15) >> 4;
+    const int n_tasks = PRIMARY ? tiles_x * ((p.chunk_rows + 7) >> 3) : (p.n_rays + 127) >> 7;
+    unsigned long long exec_rays = 0;
+
+    for (;;) {
+        int task = 0;
+        if (lane == 0) task = (int)atomicAdd(cp.task_counter, 1u);
+        task = __shfl_sync(FULL_MASK, task, 0);
+        if (task >= n_tasks) break;
+
+        V3 o[ST_RPT], d[ST_RPT];
+        float best_t[ST_RPT], tlim[ST_RPT];
+        int best_id[ST_RPT], slot[ST_RPT];
+        bool use[ST_RPT];
+        int n_valid = 0;
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r) {
+            bool valid;
+            if (PRIMARY) {
+                const int tx = task % tiles_x, ty = task / tiles_x;
+                const int lx = (tx << 4) + ((lane & 7) << 1) + (r & 1);
+                const int cy = (ty << 3) + ((lane >> 3) << 1) + (r >> 1);
+                const int ly = p.chunk_ly0 + cy;
+                valid = lx < p.f.LW && cy < p.chunk_rows && ly < p.local_LH;
+                slot[r] = valid ? cy * p.f.LW + lx : -1;
+                primary_ray<(MODE != 2)>(p.f, valid ? lx : 0, valid ? global_lattice_row(p.f, ly) : 0, o[r], d[r]);
+            } else {
+                const int i = (task << 7) + r * 32 + lane;
+                valid = i < p.n_rays;
+                slot[r] = valid ? i : -1;
+                const float4 a = valid ? p.in_od0[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 b = valid ? p.in_od1[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+                o[r] = f4_xyz(a); d[r] = f4_xyz(b);
+            }
+            if (!valid) d[r] = mk3(0.f, 0.f, 0.f);     // zero direction: det = 0, nothing can hit
+            best_t[r] = -1.0f; best_id[r] = -1; tlim[r] = 3.0e38f;
+            use[r] = valid;
+            n_valid += valid ? 1 : 0;
+        }
+        float dmax = 0.f;                             // largest |direction component| of this thread's rays (filter margins)
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r) dmax = fmaxf(dmax, max_abs3(d[r]));
+        bool keep_all;
+        const int n_c = cs_nearest_cones(o, d, use, ws.cones, lane, keep_all);
+        n_valid = __reduce_add_sync(FULL_MASK, n_valid);
+
+        // ---- triangles ------------------------------------------------------------------------
+        auto test_triangle = [&](const float4 ra, const float4 rb, const float4 rc) {
+            const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
+            const TriMargins mg = tri_margins(e1, e2, dmax);
+            bool cand[ST_RPT];
+            bool any = false;
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) {
+                cand[r] = triangle_phase1(o[r], d[r], p0, e1, e2, mg);
+                any |= cand[r];
+            }
+            if (__any_sync(FULL_MASK, any)) {
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) {
+                    if (cand[r] && slot[r] >= 0) {
+                        const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, tlim[r], mg);
+                        const int ord = __float_as_int(ra.w);
+                        // Morton order is not insertion order: equal distances go to the lower order (Scene.cpp:1713)
+                        if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f || (tt == best_t[r] && ord < best_id[r]))) {
+                            best_t[r] = tt; best_id[r] = ord;
+                            tlim[r] = fmaf(tt, CULL_TREL, CULL_TABS);
+                        }
+                    }
+                }
+            }
+        };
+        int qn = 0;
+        auto drain = [&]() {
+            __syncwarp();
+            if (qn > 0) {
+                const TriRec* t0 = cs.tri + ws.queue[0];
+                float4 ra = __ldg(&t0->a), rb = __ldg(&t0->b), rc = __ldg(&t0->c);
+                for (int e = 0; e < qn; ++e) {
+                    const TriRec* tn = cs.tri + ws.queue[min(e + 1, qn - 1)];
+                    const float4 na = __ldg(&tn->a), nb = __ldg(&tn->b), nc = __ldg(&tn->c);
+                    test_triangle(ra, rb, rc);
+                    ra = na; rb = nb; rc = nc;
+                }
+            }
+            exec_rays += (unsigned long long)qn * (unsigned long long)n_valid;
+            qn = 0;
+            __syncwarp();
+        };
+        if (n_c > 0 || keep_all) {
+            cs_walk<false>(cs, ws.cones, n_c, keep_all, lane, [&](int first, unsigned int mask) {
+                if ((mask >> lane) & 1u) ws.queue[qn + __popc(mask & ((1u << lane) - 1u))] = first + lane;
+                qn += __popc(mask);
+                if (qn > CS_QCAP - 32) drain();
+                return false;
+            });
+            drain();
+        }
+
+        // ---- quadrics (lane j looks at quadric j for the warp) and planes; ties go to the lower insertion order ----
+        for (int q0i = 0; q0i < s.n_quad; q0i += 32) {
+            const int qi = q0i + lane;
+            bool keep = false;
+            if (qi < s.n_quad && n_valid > 0) {
+                const float4 q0 = s.quad[qi].q0;
+                keep = cs_keep_quadric<false>(ws.cones, n_c, keep_all || n_c == 0, q0, s.surf[__float_as_int(q0.w)].r3);
+            }
+            unsigned int mask = __ballot_sync(FULL_MASK, keep);
+            while (mask) {
+                const int q = q0i + __ffs((int)mask) - 1;
+                mask &= mask - 1u;
+                const float4 q0 = s.quad[q].q0, q1 = s.quad[q].q1, q2 = s.quad[q].q2;
+                const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+                const int ord = __float_as_int(q0.w);
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) {
+                    bool lin;
+                    const float tt = MODE == 2 ? quadric_t<false>(o[r], d[r], Q, lin) : quadric_t<true>(o[r], d[r], Q, lin);
+                    if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f || (tt == best_t[r] && ord < best_id[r]))) { best_t[r] = tt; best_id[r] = ord; }
+                }
+            }
+        }
+        for (int q = 0; q < s.n_plane; ++q) {
+            const float4 nc = s.plane[q].nc;
+            const int ord = s.plane[q].order;
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) {
+                const float tt = MODE == 2 ? plane_t<false>(o[r], d[r], f4_xyz(nc), nc.w) : plane_t<true>(o[r], d[r], f4_xyz(nc), nc.w);
+                if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f || (tt == best_t[r] && ord < best_id[r]))) { best_t[r] = tt; best_id[r] = ord; }
+            }
+        }
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r)
+            if (slot[r] >= 0) p.hit[slot[r]] = make_float2(best_t[r], __int_as_float(best_id[r]));
+    }
+    if (p.stats && lane == 0 && exec_rays)
+        atomicAdd(&p.stats[(size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + ST_TEST_TRI_EXEC], exec_rays);
+}
+
+// ---------------------------------------------------------------------------------------
+// Shadow filter (Scene.cpp:1842-1861): product of colour * kt over every surface hit strictly between EPSILON
+// and the light.  One warp task = 128 consecutive (ray, light) queries of the queue shade-A wrote light by light.
+// ---------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(CS_THREADS, CS_MIN_CTAS)
+k_cull_shadow(const __grid_constant__ CullShadowParams cp)
+{
+    __shared__ CsWarpSmem sm[CS_WARPS];
+    // per ray, rarely touched: largest insertion order among its occluders so far | occluders (saturating) and "met out of order"
+    __shared__ int s_ord[ST_RPT][CS_THREADS];
+    __shared__ unsigned char s_occ[ST_RPT][CS_THREADS];
+    const ShadowParams& p = cp.s;
+    const CullScene& cs = cp.cs;
+    const DeviceScene& s = p.s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    CsWarpSmem& ws = sm[warp];
+    const int n_lights = s.rl.n_light;
+    const int n_tasks = (p.n_queries + 127) >> 7;
+    unsigned long long tests_tri = 0, tests_side_q = 0, tests_side_p = 0, exec_rays = 0, fixups = 0;
+
+    for (;;) {
+        int task = 0;
+        if (lane == 0) task = (int)atomicAdd(cp.task_counter, 1u);
+        task = __shfl_sync(FULL_MASK, task, 0);
+        if (task >= n_tasks) break;
+
+        V3 o[ST_RPT], d[ST_RPT];
+        float dist[ST_RPT], fr[ST_RPT], fg[ST_RPT], fb[ST_RPT];
+        int slot[ST_RPT], lid[ST_RPT];
+        int n_valid = 0;
+        unsigned int light_bits = 0;
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r) {
+            const int i = (task << 7) + r * 32 + lane;
+            const bool valid = i < p.n_queries;
+            slot[r] = valid ? i : -1;
+            lid[r] = valid ? p.sq_src[i].y : -1;
+            n_valid += valid ? 1 : 0;
+            o[r] = d[r] = mk3(0.f, 0.f, 0.f); dist[r] = 0.f;
+            if (valid) { shadow_query<(MODE != 2)>(p, i, o[r], d[r], dist[r]); light_bits |= 1u << (lid[r] & 31); }
+            fr[r] = fg[r] = fb[r] = valid ? 1.0f : 0.0f;             // an invalid slot counts as finished
+            s_ord[r][tid] = -1; s_occ[r][tid] = 0;
+        }
+        n_valid = __reduce_add_sync(FULL_MASK, n_valid);
+        light_bits = __reduce_or_sync(FULL_MASK, light_bits);
+        float dmax = 0.f;
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r) dmax = fmaxf(dmax, max_abs3(d[r]));
+
+        // ---- the warp's cone(s) per light present: one, or two around the two most distant directions ----------
+        int n_c = 0;
+        bool keep_all = n_lights > 32;
+        for (int l = 0; l < n_lights && !keep_all; ++l) {
+            if (!((light_bits >> l) & 1u)) continue;
+            const V3 L = f4_xyz(s.light[l].l0);
+            bool in[ST_RPT];
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) in[r] = lid[r] == l;
+            Bundle b = bundle_of_light(L, d, dist, in), b2;
+            b2 = b; b2.state = 0;
+            if (b.state == 2 || (b.state == 1 && b.sin_t > BUNDLE_SPLIT_SIN)) {
+                V3 nd[ST_RPT];
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) nd[r] = neg3(d[r]);
+                bool in_a[ST_RPT], in_b[ST_RPT];
+                split_members(nd, in, in_a, in_b);
+                const Bundle ba = bundle_of_light(L, d, dist, in_a), bb = bundle_of_light(L, d, dist, in_b);
+                if (ba.state != 2 && bb.state != 2) { b = ba; b2 = bb; }
+            }
+            if (b.state == 2 || n_c + 2 > CS_MAX_CONES) { keep_all = true; break; }     // no usable cone: every triangle is tested
+            if (b.state == 1) { if (lane == 0) ws.cones[n_c] = b; ++n_c; }
+            if (b2.state == 1) { if (lane == 0) ws.cones[n_c] = b2; ++n_c; }
+        }
+        if (keep_all) n_c = 0;
+        __syncwarp();
+
+        auto occluder = [&](int r, int ord, int mat) {
+            const float4 m0 = s.mat[mat].m0;
+            const float kt = s.mat[mat].m2.x;
+            fr[r] = __fmul_rn(fr[r], __fmul_rn(m0.x, kt));
+            fg[r] = __fmul_rn(fg[r], __fmul_rn(m0.y, kt));
+            fb[r] = __fmul_rn(fb[r], __fmul_rn(m0.z, kt));
+            const int prev = s_ord[r][tid];
+            unsigned int st = s_occ[r][tid];
+            if (ord < prev) st |= 4u;
+            if ((st & 3u) < 3u) ++st;
+            s_occ[r][tid] = (unsigned char)st;
+            s_ord[r][tid] = max(prev, ord);
+        };
+        auto test_triangle = [&](const float4 ra, const float4 rb, const float4 rc) {
+            const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
+            const TriMargins mg = tri_margins(e1, e2, dmax);
+            bool cand[ST_RPT];
+            bool any = false;
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) {
+                cand[r] = triangle_phase1(o[r], d[r], p0, e1, e2, mg);
+                any |= cand[r];
+            }
+            if (__any_sync(FULL_MASK, any)) {
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) {
+                    if (cand[r] && slot[r] >= 0) {
+                        const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, fmaf(dist[r], CULL_TREL, CULL_TABS), mg);
+                        if (tt > RT_EPS && tt < dist[r]) occluder(r, __float_as_int(ra.w), __float_as_int(rb.w));
+                    }
+                }
+            }
+        };
+        auto all_zero = [&]() {
+            bool done = true;
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) done = done && (fr[r] == 0.f && fg[r] == 0.f && fb[r] == 0.f);
+            return __all_sync(FULL_MASK, done);                       // 0 * finite stays 0: the warp may stop testing
+        };
+        int qn = 0;
+        bool warp_done = false;
+        auto drain = [&]() {
+            __syncwarp();
+            if (qn > 0) {
+                const TriRec* t0 = cs.tri + ws.queue[0];
+                float4 ra = __ldg(&t0->a), rb = __ldg(&t0->b), rc = __ldg(&t0->c);
+                for (int e = 0; e < qn; ++e) {
+                    const TriRec* tn = cs.tri + ws.queue[min(e + 1, qn - 1)];
+                    const float4 na = __ldg(&tn->a), nb = __ldg(&tn->b), nc = __ldg(&tn->c);
+                    test_triangle(ra, rb, rc);
+                    ra = na; rb = nb; rc = nc;
+                }
+            }
+            exec_rays += (unsigned long long)qn * (unsigned long long)n_valid;
+            qn = 0;
+            __syncwarp();
+            warp_done = all_zero();
+        };
+        tests_tri += (unsigned long long)n_valid * (unsigned long long)cs.n_tri;
+        if (n_valid > 0) {
+            cs_walk<true>(cs, ws.cones, n_c, keep_all, lane, [&](int first, unsigned int mask) {
+                if ((mask >> lane) & 1u) ws.queue[qn + __popc(mask & ((1u << lane) - 1u))] = first + lane;
+                qn += __popc(mask);
+                if (qn > CS_QCAP - 32) drain();
+                return warp_done;
+            });
+            if (!warp_done) drain();
+        }
+
+        if (!warp_done) {
+            tests_side_q += (unsigned long long)n_valid * (unsigned long long)s.n_quad;
+            tests_side_p += (unsigned long long)n_valid * (unsigned long long)s.n_plane;
+            for (int q0i = 0; q0i < s.n_quad; q0i += 32) {
+                const int qi = q0i + lane;
+                bool keep = false;
+                if (qi < s.n_quad && n_valid > 0) {
+                    const float4 q0 = s.quad[qi].q0;
+                    keep = cs_keep_quadric<true>(ws.cones, n_c, keep_all || n_c == 0, q0, s.surf[__float_as_int(q0.w)].r3);
+                }
+                unsigned int mask = __ballot_sync(FULL_MASK, keep);
+                while (mask) {
+                    const int q = q0i + __ffs((int)mask) - 1;
+                    mask &= mask - 1u;
+                    const float4 q0 = s.quad[q].q0, q1 = s.quad[q].q1, q2 = s.quad[q].q2;
+                    const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+                    #pragma unroll
+                    for (int r = 0; r < ST_RPT; ++r) {
+                        bool lin;
+                        const float tt = MODE == 2 ? quadric_t<false>(o[r], d[r], Q, lin) : quadric_t<true>(o[r], d[r], Q, lin);
+                        if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) occluder(r, __float_as_int(q0.w), __float_as_int(q1.w));
+                    }
+                }
+            }
+            for (int q = 0; q < s.n_plane; ++q) {
+                const float4 nc = s.plane[q].nc;
+                const int m = s.plane[q].material, ord = s.plane[q].order;
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) {
+                    const float tt = MODE == 2 ? plane_t<false>(o[r], d[r], f4_xyz(nc), nc.w) : plane_t<true>(o[r], d[r], f4_xyz(nc), nc.w);
+                    if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) occluder(r, ord, m);
+                }
+            }
+        }
+        #pragma unroll
+        for (int r = 0; r < ST_RPT; ++r)
+            if (slot[r] >= 0) {
+                p.filter[p.sq_dst ? p.sq_dst[slot[r]] : slot[r]] = make_float4(fr[r], fg[r], fb[r], 0.f);
+                // three or more factors multiplied in another order than Scene.cpp:1856's: redo this query in order
+                const unsigned int st = s_occ[r][tid];
+                if ((st & 4u) && (st & 3u) >= 3u && (fr[r] != 0.f || fg[r] != 0.f || fb[r] != 0.f)) {
+                    const unsigned int k = atomicAdd(cp.fix_count, 1u);
+                    if ((int)k < cp.fix_cap) cp.fix_list[k] = slot[r];
+                    ++fixups;
+                }
+            }
+    }
+
+    for (int off = 16; off > 0; off >>= 1) {
+        tests_tri += __shfl_xor_sync(FULL_MASK, tests_tri, off);
+        tests_side_q += __shfl_xor_sync(FULL_MASK, tests_side_q, off);
+        tests_side_p += __shfl_xor_sync(FULL_MASK, tests_side_p, off);
+        fixups += __shfl_xor_sync(FULL_MASK, fixups, off);
+    }
+    if (lane == 0) {
+        // (tests_* were accumulated per warp, not per lane: undo the 32-fold sum of the uniform values)
+        unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+        if (tests_tri) atomicAdd(&st[ST_TEST_TRI_SHADOW], tests_tri >> 5);
+        if (exec_rays) atomicAdd(&st[ST_TEST_TRI_EXEC], exec_rays);
+        if (tests_side_q) atomicAdd(&st[ST_TEST_QUAD], tests_side_q >> 5);
+        if (tests_side_p) atomicAdd(&st[ST_TEST_PLANE], tests_side_p >> 5);
+        if (fixups) atomicAdd(&st[ST_SHADOW_FIXUP], fixups);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// The rare query whose product order matters: one warp per query walks the unified list (slot = insertion order,
+// Scene.cpp:107) 32 surfaces at a time; the occluders of a round are multiplied in slot order.
+// ---------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(128) k_shadow_fixup(const __grid_constant__ CullShadowParams cp)
+{
+    const ShadowParams& p = cp.s;
+    const DeviceScene& s = p.s;
+    const int lane = threadIdx.x & 31;
+    const int n = min((int)*cp.fix_count, cp.fix_cap);
+    const int n_surf = s.rl.n_surf;
+    for (int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n; w += gridDim.x * (blockDim.x >> 5)) {
+        const int qi = cp.fix_list[w];
+        V3 o, d;
+        float dist;
+        shadow_query<(MODE != 2)>(p, qi, o, d, dist);
+        float fr = 1.0f, fg = 1.0f, fb = 1.0f;
+        for (int k0 = 0; k0 < n_surf; k0 += 32) {
+            const int k = k0 + lane;
+            bool hit = false;
+            int mat = 0;
+            if (k < n_surf) {
+                const float4 r0 = s.surf[k].r0, r1 = s.surf[k].r1, r2 = s.surf[k].r2;
+                const int type = __float_as_int(r0.w);
+                mat = __float_as_int(r1.w);
+                float tt;
+                if (type == SURF_TRIANGLE) tt = MODE == 2 ? triangle_t<false>(o, d, f4_xyz(r0), f4_xyz(r1), f4_xyz(r2)) : triangle_t<true>(o, d, f4_xyz(r0), f4_xyz(r1), f4_xyz(r2));
+                else if (type == SURF_PLANE) tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(r0), r1.x) : plane_t<true>(o, d, f4_xyz(r0), r1.x);
+                else {
+                    const Quadric Q = { r0.x, r0.y, r0.z, r1.x, r1.y, r1.z, r2.x, r2.y, r2.z, r2.w };
+                    bool lin;
+                    tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+                }
+                hit = tt > RT_EPS && tt < dist;
+            }
+            unsigned int mask = __ballot_sync(FULL_MASK, hit);
+            while (mask) {
+                const int src = __ffs((int)mask) - 1;
+                mask &= mask - 1u;
+                const int m = __shfl_sync(FULL_MASK, mat, src);
+                const float4 m0 = s.mat[m].m0;
+                const float kt = s.mat[m].m2.x;
+                fr = __fmul_rn(fr, __fmul_rn(m0.x, kt));
+                fg = __fmul_rn(fg, __fmul_rn(m0.y, kt));
+                fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+            }
+        }
+        if (lane == 0) p.filter[p.sq_dst ? p.sq_dst[qi] : qi] = make_float4(fr, fg, fb, 0.f);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------
+static int cs_grid(int n_tasks, int sm_count)
+{
+    const int ctas = (n_tasks + CS_WARPS - 1) / CS_WARPS;
+    return ctas < CS_MIN_CTAS * sm_count ? ctas : CS_MIN_CTAS * sm_count;
+}
+
+cudaError_t launch_cull_nearest(const CullTraceParams& p, int sm_count, cudaStream_t st)
+{
+    const int tiles_x = (p.t.f.LW + 15) / 16;
+    const int n_tasks = p.t.primary ? tiles_x * ((p.t.chunk_rows + 7) / 8) : (p.t.n_rays + 127) / 128;
+    if (n_tasks <= 0) return cudaSuccess;
+    const int blocks = cs_grid(n_tasks, sm_count);
+    if (p.t.primary) {
+        if (p.t.mode == 2) k_cull_nearest<2, true><<<blocks, CS_THREADS, 0, st>>>(p);
+        else               k_cull_nearest<0, true><<<blocks, CS_THREADS, 0, st>>>(p);
+    } else {
+        if (p.t.mode == 2) k_cull_nearest<2, false><<<blocks, CS_THREADS, 0, st>>>(p);
+        else               k_cull_nearest<0, false><<<blocks, CS_THREADS, 0, st>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_cull_shadow(const CullShadowParams& p, int sm_count, cudaStream_t st)
+{
+    const int n_tasks = (p.s.n_queries + 127) / 128;
+    if (n_tasks <= 0) return cudaSuccess;
+    const int blocks = cs_grid(n_tasks, sm_count);
+    if (p.s.mode == 2) k_cull_shadow<2><<<blocks, CS_THREADS, 0, st>>>(p);
+    else               k_cull_shadow<0><<<blocks, CS_THREADS, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_shadow_fixup(const CullShadowParams& p, int sm_count, cudaStream_t st)
+{
+    if (p.s.mode == 2) k_shadow_fixup<2><<<sm_count, 128, 0, st>>>(p);
+    else               k_shadow_fixup<0><<<sm_count, 128, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// cull_prepare: Morton sort + sphere hierarchy, on the device, once per scene (cached until rtb200_set_scene)
+// ---------------------------------------------------------------------------------------
+RT_DEV int cs_float_order(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+static inline float cs_order_float(int i) { const int b = i >= 0 ? i : i ^ 0x7fffffff; float f; memcpy(&f, &b, 4); return f; }
+
+__global__ void k_cs_bounds(const TriRec* __restrict__ tri, int n, int* __restrict__ bounds)
+{
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = tri[i].a, b = tri[i].b, c = tri[i].c;
+        const float ctr[3] = {a.x + (b.x + c.x) * (1.0f / 3.0f), a.y + (b.y + c.y) * (1.0f / 3.0f), a.z + (b.z + c.z) * (1.0f / 3.0f)};
+        #pragma unroll
+        for (int k = 0; k < 3; ++k) if (fabsf(ctr[k]) <= 3.0e38f) { lo[k] = fminf(lo[k], ctr[k]); hi[k] = fmaxf(hi[k], ctr[k]); }
+    }
+    #pragma unroll
+    for (int k = 0; k < 3; ++k)
+        for (int off = 16; off > 0; off >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(FULL_MASK, lo[k], off));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(FULL_MASK, hi[k], off));
+        }
+    if ((threadIdx.x & 31) == 0) {
+        #pragma unroll
+        for (int k = 0; k < 3; ++k) { atomicMin(&bounds[k], cs_float_order(lo[k])); atomicMax(&bounds[3 + k], cs_float_order(hi[k])); }
+    }
+}
+
+RT_DEV unsigned int cs_expand10(unsigned int v)
+{
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+// 30-bit Morton code of the centroid in CUBIC cells (one scale for the three axes: a flat scene is not cut into sheets)
+__global__ void k_cs_keys(const TriRec* __restrict__ tri, int n, float lx, float ly, float lz, float inv, unsigned int* __restrict__ keys, int* __restrict__ idx)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = tri[i].a, b = tri[i].b, c = tri[i].c;
+    const float cx = a.x + (b.x + c.x) * (1.0f / 3.0f), cy = a.y + (b.y + c.y) * (1.0f / 3.0f), cz = a.z + (b.z + c.z) * (1.0f / 3.0f);
+    const float fx = fminf(fmaxf((cx - lx) * inv, 0.f), 1023.f), fy = fminf(fmaxf((cy - ly) * inv, 0.f), 1023.f), fz = fminf(fmaxf((cz - lz) * inv, 0.f), 1023.f);
+    const unsigned int ix = fx == fx ? (unsigned int)fx : 0u, iy = fy == fy ? (unsigned int)fy : 0u, iz = fz == fz ? (unsigned int)fz : 0u;
+    keys[i] = (cs_expand10(ix) << 2) | (cs_expand10(iy) << 1) | cs_expand10(iz);
+    idx[i] = i;
+}
+
+// sorted triangle array + level 0 (one thread per slot of the padded array)
+__global__ void k_cs_gather(const TriRec* __restrict__ tri, const int* __restrict__ idx, int n, int n0, TriRec* __restrict__ out,
+                            float4* __restrict__ sph0, float* __restrict__ w0)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n0) return;
+    if (i >= n) {
+        TriRec z;
+        z.a = make_float4(0.f, 0.f, 0.f, __int_as_float(0x7fffffff)); z.b = make_float4(0.f, 0.f, 0.f, 0.f); z.c = z.b;
+        out[i] = z; sph0[i] = make_float4(0.f, 0.f, 0.f, 0.f); w0[i] = 0.f;
+        return;
+    }
+    const TriRec r = tri[idx[i]];
+    out[i] = r;
+    V3 c; float rad, w;
+    triangle_sphere(f4_xyz(r.a), f4_xyz(r.b), f4_xyz(r.c), c, rad, w);
+    const bool ok = fabsf(c.x) <= 3.0e38f && fabsf(c.y) <= 3.0e38f && fabsf(c.z) <= 3.0e38f && rad <= 3.0e38f && w <= 3.0e38f;
+    // a triangle with non-finite numbers keeps a sphere nothing can cull; w must stay > 0 for every real triangle
+    sph0[i] = ok ? make_float4(c.x, c.y, c.z, rad) : make_float4(0.f, 0.f, 0.f, 3.0e38f);
+    w0[i] = ok ? fmaxf(w, 1.0e-30f) : 3.0e38f;
+}
+
+// level l from level l - 1: sphere around the mean centre of the non-empty children that contains their spheres
+__global__ void k_cs_group(const float4* __restrict__ sph_in, const float* __restrict__ w_in, int n_out, float4* __restrict__ sph_out, float* __restrict__ w_out)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_out) return;
+    float cx = 0.f, cy = 0.f, cz = 0.f, wmax = 0.f;
+    int cnt = 0;
+    bool huge = false;
+    for (int j = 0; j < 32; ++j) {
+        const float w = w_in[g * 32 + j];
+        if (!(w > 0.f)) continue;
+        const float4 s = sph_in[g * 32 + j];
+        if (s.w > 1.0e37f) { huge = true; }
+        cx += s.x; cy += s.y; cz += s.z; ++cnt; wmax = fmaxf(wmax, w);
+    }
+    if (cnt == 0) { sph_out[g] = make_float4(0.f, 0.f, 0.f, 0.f); w_out[g] = 0.f; return; }
+    const float inv = 1.0f / (float)cnt;
+    cx *= inv; cy *= inv; cz *= inv;
+    float R = 0.f;
+    for (int j = 0; j < 32; ++j) {
+        const float w = w_in[g * 32 + j];
+        if (!(w > 0.f)) continue;
+        const float4 s = sph_in[g * 32 + j];
+        const float dx = s.x - cx, dy = s.y - cy, dz = s.z - cz;
+        R = fmaxf(R, sqrtf(dx * dx + dy * dy + dz * dz) * 1.00001f + s.w);
+    }
+    const float m1 = fabsf(cx) + fabsf(cy) + fabsf(cz);
+    R = R * 1.00001f + 4.0e-7f * m1;
+    if (huge || !(R <= 3.0e38f) || !(m1 <= 3.0e38f)) { cx = cy = cz = 0.f; R = 3.0e38f; }
+    sph_out[g] = make_float4(cx, cy, cz, R);
+    w_out[g] = wmax;
+}
+
+struct CullState {
+    DevBuf tri, sph, w, keys, keys2, idx, idx2, tmp, bounds;
+    PinnedBuf h_bounds;
+    unsigned long long serial = ~0ull;       // scene the hierarchy was built for
+    CullScene cs{};
+    double build_ms = 0.0;
+};
+
+static CullState* cull_state(rtb200_ctx* c)
+{
+    if (!c->cull_state) c->cull_state = new CullState();
+    return static_cast<CullState*>(c->cull_state);
+}
+
+void cull_release(rtb200_ctx* c)
+{
+    if (!c->cull_state) return;
+    CullState* b = static_cast<CullState*>(c->cull_state);
+    b->tri.release(); b->sph.release(); b->w.release(); b->keys.release(); b->keys2.release();
+    b->idx.release(); b->idx2.release(); b->tmp.release(); b->bounds.release(); b->h_bounds.release();
+    delete b;
+    c->cull_state = nullptr;
+}
+
+#define KCU(call)                                                       \
+    do {                                                                \
+        cudaError_t e__ = (call);                                       \
+        if (e__ != cudaSuccess) return set_cuda_error(c, e__, #call);   \
+    } while (0)
+
+int cull_prepare(rtb200_ctx* c, CullScene* out)
+{
+    CullState* b = cull_state(c);
+    if (b->serial == c->scene_serial) { *out = b->cs; return RTB200_OK; }
+    const int T = c->ds.n_tri;
+    const int n3 = std::max(1, (T + 32767) / 32768);
+    const int n[CS_LEVELS] = {32768 * n3, 1024 * n3, 32 * n3, n3};
+    const size_t total = (size_t)n3 * (1057 + 32768);
+    cudaStream_t st = c->stream;
+    cudaEvent_t e0 = c->ev[6], e1 = c->ev[7];
+    KCU(b->tri.ensure(sizeof(TriRec) * (size_t)n[0]));
+    KCU(b->sph.ensure(sizeof(float4) * total));
+    KCU(b->w.ensure(sizeof(float) * total));
+    KCU(b->bounds.ensure(64));
+    KCU(b->h_bounds.ensure(64));
+    KCU(cudaEventRecord(e0, st));
+    int valid[CS_LEVELS];
+    valid[0] = T;
+    for (int l = 1; l < CS_LEVELS; ++l) valid[l] = (valid[l - 1] + 31) / 32;
+    float4* sph = b->sph.as<float4>();
+    float* w = b->w.as<float>();
+    const int off[CS_LEVELS] = {1057 * n3, 33 * n3, n3, 0};
+    KCU(cudaMemsetAsync(w, 0, sizeof(float) * total, st));
+    KCU(cudaMemsetAsync(sph, 0, sizeof(float4) * (size_t)off[0], st));
+    if (T > 0) {
+        KCU(b->keys.ensure(sizeof(unsigned int) * (size_t)T)); KCU(b->keys2.ensure(sizeof(unsigned int) * (size_t)T));
+        KCU(b->idx.ensure(sizeof(int) * (size_t)T)); KCU(b->idx2.ensure(sizeof(int) * (size_t)T));
+        int* h = b->h_bounds.as<int>();
+        for (int k = 0; k < 3; ++k) { h[k] = INT_MAX; h[3 + k] = INT_MIN; }
+        KCU(cudaMemcpyAsync(b->bounds.p, h, 24, cudaMemcpyHostToDevice, st));
+        k_cs_bounds<<<std::min((T + 255) / 256, 1184), 256, 0, st>>>(c->ds.tri, T, b->bounds.as<int>());
+        KCU(cudaGetLastError());
+        KCU(cudaMemcpyAsync(h, b->bounds.p, 24, cudaMemcpyDeviceToHost, st));
+        KCU(cudaStreamSynchronize(st));
+        float lo[3], ext = 0.f;
+        for (int k = 0; k < 3; ++k) {
+            lo[k] = cs_order_float(h[k]);
+            const float hi = cs_order_float(h[3 + k]);
+            if (!(lo[k] <= hi)) { lo[k] = 0.f; continue; }          // no finite centroid on this axis
+            ext = std::max(ext, hi - lo[k]);
+        }
+        const float inv = ext > 0.f ? 1023.999f / ext : 0.f;
+        k_cs_keys<<<(T + 255) / 256, 256, 0, st>>>(c->ds.tri, T, lo[0], lo[1], lo[2], inv, b->keys.as<unsigned int>(), b->idx.as<int>());
+        KCU(cudaGetLastError());
+        size_t tmp_bytes = 0;
+        KCU(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, b->keys.as<unsigned int>(), b->keys2.as<unsigned int>(), b->idx.as<int>(), b->idx2.as<int>(), T, 0, 30, st));
+        KCU(b->tmp.ensure(tmp_bytes));
+        KCU(cub::DeviceRadixSort::SortPairs(b->tmp.p, tmp_bytes, b->keys.as<unsigned int>(), b->keys2.as<unsigned int>(), b->idx.as<int>(), b->idx2.as<int>(), T, 0, 30, st));
+    }
+    k_cs_gather<<<(n[0] + 255) / 256, 256, 0, st>>>(c->ds.tri, b->idx2.as<int>(), T, n[0], b->tri.as<TriRec>(), sph + off[0], w + off[0]);
+    KCU(cudaGetLastError());
+    for (int l = 1; l < CS_LEVELS; ++l) {
+        if (valid[l] <= 0) break;
+        k_cs_group<<<(valid[l] + 127) / 128, 128, 0, st>>>(sph + off[l - 1], w + off[l - 1], valid[l], sph + off[l], w + off[l]);
+        KCU(cudaGetLastError());
+    }
+    KCU(cudaEventRecord(e1, st));
+    KCU(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) b->build_ms = ms;
+    CullScene& cs = b->cs;
+    cs.tri = b->tri.as<TriRec>(); cs.sph = sph; cs.w = w;
+    cs.n3 = n3; cs.n_tri = T;
+    cs.top_blocks = (n3 + 31) / 32;
+    b->serial = c->scene_serial;
+    *out = cs;
+    return RTB200_OK;
+}
+
+} // namespace rtb

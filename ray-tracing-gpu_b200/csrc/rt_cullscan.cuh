@@ -1,0 +1,42 @@
+// rt_cullscan.cuh -- the culled scan of the streamed path: every warp walks a 32-ary hierarchy of bounding spheres
+// over the Morton-sorted triangles with the cone(s) of its 128 rays and runs the filter + reference sequence only on
+// the triangles that survive (rt_cullscan.cu).  Same answers as the plain tiled scan of rt_trace.cu, bit for bit.
+#pragma once
+#include "rt_stream.cuh"
+
+namespace rtb {
+
+#define CS_LEVELS 4
+
+// Level 0: one bounding sphere per triangle (Morton order); level l >= 1: one sphere per block of 32 level-(l-1)
+// entries, 3 levels above the triangles.  n(l-1) == 32 n(l): the arrays are padded from the top with empty entries
+// (w == 0, never kept), n(3) = n3 = ceil(T / 32768).  All levels live in ONE array: [level 3][level 2][level 1][level 0].
+struct CullScene {
+    const TriRec* tri;               // triangles in Morton order, 32768 * n3 records (padding: zero edges)
+    const float4* sph;               // centre | radius
+    const float*  w;                 // |e1| |e2| bound of the triangle / the largest below the block; 0 = empty
+    int n3;
+    int top_blocks;                  // rounds of 32 at level 3 (1 up to a million triangles)
+    int n_tri;                       // real triangles
+};
+
+struct CullTraceParams {
+    TraceParams t;
+    CullScene   cs;
+    unsigned int* task_counter;      // zeroed before the launch: warps take tasks of 128 rays from it
+};
+
+struct CullShadowParams {
+    ShadowParams s;
+    CullScene    cs;
+    unsigned int* task_counter;
+    int*          fix_list;          // queries whose filter product has to be redone in insertion order (rare) ...
+    unsigned int* fix_count;         // ... how many, and the room there is
+    int           fix_cap;
+};
+
+cudaError_t launch_cull_nearest(const CullTraceParams& p, int sm_count, cudaStream_t st);
+cudaError_t launch_cull_shadow(const CullShadowParams& p, int sm_count, cudaStream_t st);
+cudaError_t launch_shadow_fixup(const CullShadowParams& p, int sm_count, cudaStream_t st);
+
+} // namespace rtb

@@ -16,6 +16,7 @@
 #include "rt_context.h"
 #include "rt_stream.cuh"
 #include "rt_bvh.cuh"
+#include "rt_cullscan.cuh"
 
 using namespace rtb;
 
@@ -31,6 +32,7 @@ namespace rtb {
 
 struct StreamBufs {                // per-context scratch of the streamed path (lives in the ctx levels + these)
     DevBuf hit, hitP, hitN, q_base, sq0, sq1, sq_src, sq_dst, filter;
+    DevBuf tasks, fix;             // culled scan: task / fix-up counters (3 words per level), fix-up list
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // per-stage stopwatch
 };
 
@@ -42,6 +44,15 @@ static int bundle_cull_enabled()
     if (e && atoi(e) != 0) return 0;
     const char* m = getenv("RTB200_NEAREST_CONES");
     return (m && atoi(m) > 1) ? 2 : 1;
+}
+
+// The culled scan (rt_cullscan.cu) is the default for everything the plain tiled kernels would cull per warp;
+// RTB200_CULLSCAN=0 keeps the tiled kernels with their per-tile warp-bundle culling (round 1) for A/B runs.
+static bool cullscan_enabled()
+{
+    if (bundle_cull_enabled() == 0) return false;
+    const char* e = getenv("RTB200_CULLSCAN");
+    return !(e && atoi(e) == 0);
 }
 
 // queue order of the tiled path (see render_streamed); RTB200_QUERY_GROUPING=0 restores the ray order for A/B runs
@@ -61,7 +72,7 @@ void stream_release(rtb200_ctx* c)
 {
     if (!c->stream_scratch) return;
     StreamBufs* b = static_cast<StreamBufs*>(c->stream_scratch);
-    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->sq_dst.release(); b->filter.release();
+    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->sq_dst.release(); b->filter.release(); b->tasks.release(); b->fix.release();
     for (auto& e : b->ev) if (e) cudaEventDestroy(e);
     delete b;
     c->stream_scratch = nullptr;
@@ -94,6 +105,14 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
         const int rc = bvh_prepare(c, fr->cam_pos, 1);
         if (rc != RTB200_OK) return rc;
     }
+    // culled scan: Morton-sorted triangles + sphere hierarchy of this scene (built once per rtb200_set_scene)
+    const bool cullscan = !use_bvh && mode != 1 && cullscan_enabled();
+    CullScene cull;
+    memset(&cull, 0, sizeof cull);
+    if (cullscan) {
+        const int rc = cull_prepare(c, &cull);
+        if (rc != RTB200_OK) return rc;
+    }
     const int k = fp.k;
     const int local_LH = local_rows * k;
     const int L = c->ds.rl.n_light;
@@ -111,6 +130,9 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     if ((e = c->counters.ensure(sizeof(unsigned) * n_counters)) != cudaSuccess) return set_cuda_error(c, e, "counters");
     unsigned* h_cnt = c->h_small.as<unsigned>();
     unsigned* d_cnt = c->counters.as<unsigned>();
+    const size_t n_tasks_words = 3 * ((size_t)std::max(fr->max_bounces, 0) + 2);
+    if (cullscan && (e = sb->tasks.ensure(sizeof(unsigned) * n_tasks_words)) != cudaSuccess) return set_cuda_error(c, e, "task counters");
+    unsigned* d_tasks = sb->tasks.as<unsigned>();
     unsigned max_level_seen = 0, chunks = 0;
     unsigned long long rays_nearest = 0;
     cudaEvent_t ev_a = c->ev[2], ev_b = c->ev[3];
@@ -132,6 +154,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunks) {
         const int rows = std::min(rows_per_chunk, local_LH - ly0);
         SCU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, c->stream));
+        if (cullscan) SCU(cudaMemsetAsync(d_tasks, 0, sizeof(unsigned) * n_tasks_words, c->stream));
         std::vector<int> n_rays, n_links;
         n_rays.push_back(rows * fp.LW);
         int level = 0;
@@ -168,6 +191,11 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             SCU(cudaEventRecord(E[0], c->stream));
             tp.stats = c->stats.as<unsigned long long>();
             if (use_bvh) SCU(launch_bvh_nearest(tp, c->stream));
+            else if (cullscan) {
+                CullTraceParams ctp;
+                ctp.t = tp; ctp.cs = cull; ctp.task_counter = d_tasks + 3 * level;
+                SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
+            }
             else         SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
             SCU(cudaEventRecord(E[1], c->stream));
             if (timed) { SCU(cudaEventRecord(ev_b, c->stream)); timed_first = true; }
@@ -213,6 +241,15 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 sp.by_light = shadow_by_light ? 1 : 0;
                 sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode; sp.cull_bundles = bundle_cull_enabled();
                 if (use_bvh) SCU(launch_bvh_shadow(sp, c->stream));
+                else if (cullscan && group_queries) {
+                    if ((e = sb->fix.ensure(sizeof(int) * (size_t)n_sq)) != cudaSuccess) return set_cuda_error(c, e, "fix-up list");
+                    CullShadowParams csp;
+                    csp.s = sp; csp.cs = cull; csp.task_counter = d_tasks + 3 * level + 1;
+                    csp.fix_count = d_tasks + 3 * level + 2; csp.fix_list = sb->fix.as<int>(); csp.fix_cap = n_sq;
+                    SCU(launch_cull_shadow(csp, c->sm_count, c->stream));
+                    SCU(launch_shadow_fixup(csp, c->sm_count, c->stream));     // queries whose product order matters (rare; reads the count itself)
+                    ++*launches;
+                }
                 else         SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
                 ++*launches;
             }
@@ -293,6 +330,16 @@ int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
     tp.n_rays = n; tp.hit = sb->hit.as<float2>(); tp.mode = mode; tp.cull_bundles = bundle_cull_enabled();
     tp.stats = c->stats.as<unsigned long long>();
     if (flags & RTB200_F_USE_BVH) SCU(launch_bvh_nearest(tp, c->stream));
+    else if (mode != 1 && cullscan_enabled()) {
+        CullTraceParams ctp;
+        ctp.t = tp;
+        const int rc = cull_prepare(c, &ctp.cs);
+        if (rc != RTB200_OK) return rc;
+        if ((e = sb->tasks.ensure(64)) != cudaSuccess) return set_cuda_error(c, e, "task counters");
+        SCU(cudaMemsetAsync(sb->tasks.p, 0, 4, c->stream));
+        ctp.task_counter = sb->tasks.as<unsigned>();
+        SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
+    }
     else                          SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
     SCU(launch_query_finish_nearest(c->ds, n, tp.in_od0, tp.in_od1, tp.hit, c->q_out0.as<int>(), c->q_out1.as<float>(),
                                     c->q_out2.as<float>(), mode != 2, c->stream));
