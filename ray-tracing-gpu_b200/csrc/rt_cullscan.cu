@@ -68,33 +68,50 @@ RT_DEV bool cs_keep(const Bundle* cones, int n_c, bool keep_all, float4 sph, flo
     return keep && w > 0.f;
 }
 
-// Top-down walk of the sphere hierarchy with the warp's cones.  sink(first, mask): bit j of mask = triangle first + j
-// survived level 0; returns true to stop the walk (a shadow warp whose filters are all zero).
-template <int L, bool LIGHT, class Sink>
-RT_DEV bool cs_level(const CullScene& cs, const Bundle* cones, int n_c, bool keep_all, int lane, int block, Sink& sink)
-{
-    const int i = cs_level_offset(cs.n3, L) + block * 32 + lane;
-    bool keep = false;
-    if (L < CS_LEVELS - 1 || block * 32 + lane < cs.n3)       // (the top level holds n3 entries, not a multiple of 32)
-        keep = cs_keep<LIGHT>(cones, n_c, keep_all, __ldg(cs.sph + i), __ldg(cs.w + i));
-    unsigned int m = __ballot_sync(FULL_MASK, keep);
-    if constexpr (L == 0) {
-        return m ? sink(block * 32, m) : false;
-    } else {
-        while (m) {
-            const int child = block * 32 + __ffs((int)m) - 1;
-            m &= m - 1u;
-            if (cs_level<L - 1, LIGHT>(cs, cones, n_c, keep_all, lane, child, sink)) return true;
-        }
-        return false;
-    }
-}
+// Top-down walk of the sphere hierarchy with the warp's cones, RESUMABLE: cs_fill appends the triangles that survive
+// level 0 to the warp's queue until fewer than 32 slots are free (returns false: drain the queue and call again) or
+// the hierarchy is exhausted (returns true).  The walk's state -- per level the mask of blocks still to descend into
+// and the index of their first entry -- is warp-uniform and lives in registers.  One copy of the cone test, one copy
+// of the drain in the caller: the first version inlined both per level and per call site, 105 KB of SASS, and the
+// warps stalled on instruction fetch more than on anything else (ncu: no_instruction 3.4 warps per issue).
+struct CsWalk {
+    int lvl, top_b, qn;              // lvl: level whose mask is being consumed (CS_LEVELS = fetch the next top block)
+    unsigned int m1, m2, m3;
+    int b1, b2, b3;
+};
+RT_DEV void cs_walk_init(CsWalk& w) { w.lvl = CS_LEVELS; w.top_b = 0; w.qn = 0; w.m1 = w.m2 = w.m3 = 0u; w.b1 = w.b2 = w.b3 = 0; }
 
-template <bool LIGHT, class Sink>
-RT_DEV void cs_walk(const CullScene& cs, const Bundle* cones, int n_c, bool keep_all, int lane, Sink&& sink)
+template <bool LIGHT>
+RT_DEV bool cs_fill(const CullScene& cs, CsWarpSmem& ws, int n_c, bool keep_all, int lane, CsWalk& w)
 {
-    for (int b = 0; b < cs.top_blocks; ++b)
-        if (cs_level<CS_LEVELS - 1, LIGHT>(cs, cones, n_c, keep_all, lane, b, sink)) return;
+    for (;;) {
+        int level, block;                                   // the block of 32 entries to test now
+        if (w.lvl == CS_LEVELS) {
+            if (w.top_b >= cs.top_blocks) return true;
+            level = CS_LEVELS - 1; block = w.top_b++;
+        } else {
+            const unsigned int m = w.lvl == 1 ? w.m1 : (w.lvl == 2 ? w.m2 : w.m3);
+            if (m == 0u) { ++w.lvl; continue; }
+            const int base = w.lvl == 1 ? w.b1 : (w.lvl == 2 ? w.b2 : w.b3);
+            block = base + __ffs((int)m) - 1;
+            const unsigned int rest = m & (m - 1u);
+            if (w.lvl == 1) w.m1 = rest; else if (w.lvl == 2) w.m2 = rest; else w.m3 = rest;
+            level = w.lvl - 1;
+        }
+        const int i = cs_level_offset(cs.n3, level) + block * 32 + lane;
+        bool keep = false;
+        if (level < CS_LEVELS - 1 || block * 32 + lane < cs.n3)       // (the top level holds n3 entries, not a multiple of 32)
+            keep = cs_keep<LIGHT>(ws.cones, n_c, keep_all, __ldg(cs.sph + i), __ldg(cs.w + i));
+        const unsigned int mm = __ballot_sync(FULL_MASK, keep);
+        if (level == 0) {
+            if (keep) ws.queue[w.qn + __popc(mm & ((1u << lane) - 1u))] = block * 32 + lane;
+            w.qn += __popc(mm);
+            if (w.qn > CS_QCAP - 32) return false;
+        } else {
+            if (level == 1) { w.m1 = mm; w.b1 = block * 32; } else if (level == 2) { w.m2 = mm; w.b2 = block * 32; } else { w.m3 = mm; w.b3 = block * 32; }
+            w.lvl = level;
+        }
+    }
 }
 
 // quadrics of centred form  sum q_i (x_i - c_i)^2 = rhs, q_i > 0 (r3 = c | rhs, rhs > 0): bounding sphere of the region
@@ -132,36 +149,56 @@ RT_DEV bool cs_keep_quadric(const Bundle* cones, int n_c, bool keep_all, float4 
 
 // the cones of a warp's 128 nearest-hit rays: one, or -- when that one is wide -- up to four after two splits around the
 // most distant directions.  Returns the number of cones written (0 with keep_all = true: nothing can be culled).
+// (Loops that are NOT unrolled on purpose: every copy of bundle_of_rays / split_members is ~300 instructions, and the
+// first version of this function was two thirds of the kernel's 128 KB of SASS.)
 RT_DEV int cs_nearest_cones(const V3* o, const V3* d, const bool* use, Bundle* cones, int lane, bool& keep_all)
 {
     keep_all = false;
-    Bundle one = bundle_of_rays(o, d, use);
-    if (one.state == 0) return 0;                               // no rays at all
-    if (one.state == 1 && !(one.sin_t > BUNDLE_SPLIT_SIN)) {
-        if (lane == 0) cones[0] = one;
-        __syncwarp();
-        return 1;
-    }
-    V3 dn[ST_RPT];
+    int grp[ST_RPT];                                            // group of each ray after the splits (2 bits)
     #pragma unroll
-    for (int r = 0; r < ST_RPT; ++r) {
-        const float l2 = dot3<false>(d[r], d[r]);
-        const float il = (l2 > 1.0e-20f && l2 < 1.0e20f) ? rsqrtf(l2) : 0.f;
-        dn[r] = mk3(d[r].x * il, d[r].y * il, d[r].z * il);
-    }
-    bool ga[ST_RPT], gb[ST_RPT], g[CS_NEAREST_CONES][ST_RPT];
-    split_members(dn, use, ga, gb);
-    split_members(dn, ga, g[0], g[1]);
-    split_members(dn, gb, g[2], g[3]);
+    for (int r = 0; r < ST_RPT; ++r) grp[r] = 0;
+    Bundle one;
     int n = 0;
-    bool usable = true;
-    #pragma unroll
-    for (int k = 0; k < CS_NEAREST_CONES; ++k) {
-        const Bundle b = bundle_of_rays(o, d, g[k]);            // state 0: an empty part
-        usable = usable && b.state != 2;
-        if (b.state == 1) { if (lane == 0) cones[n] = b; ++n; }
+    bool usable = true, split = false;
+    #pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        // pass 0: the cone of all rays; pass 1 (only when that one is wide): the cones of the four groups
+        const int n_groups = pass == 0 ? 1 : CS_NEAREST_CONES;
+        #pragma unroll 1
+        for (int k = 0; k < n_groups; ++k) {
+            bool in[ST_RPT];
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) in[r] = use[r] && (pass == 0 || grp[r] == k);
+            const Bundle b = bundle_of_rays(o, d, in);
+            if (pass == 0) one = b;
+            else {
+                usable = usable && b.state != 2;
+                if (b.state == 1) { if (lane == 0) cones[n] = b; ++n; }
+            }
+        }
+        if (pass == 0) {
+            if (one.state == 0) return 0;                       // no rays at all
+            if (one.state == 1 && !(one.sin_t > BUNDLE_SPLIT_SIN)) break;
+            split = true;
+            V3 dn[ST_RPT];
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r) {
+                const float l2 = dot3<false>(d[r], d[r]);
+                const float il = (l2 > 1.0e-20f && l2 < 1.0e20f) ? rsqrtf(l2) : 0.f;
+                dn[r] = mk3(d[r].x * il, d[r].y * il, d[r].z * il);
+            }
+            #pragma unroll 1
+            for (int it = 0; it < 3; ++it) {                    // all rays in two, then each half in two
+                bool in[ST_RPT], in_a[ST_RPT], in_b[ST_RPT];
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) in[r] = use[r] && (it == 0 || (grp[r] & 1) == it - 1);
+                split_members(dn, in, in_a, in_b);
+                #pragma unroll
+                for (int r = 0; r < ST_RPT; ++r) if (in_b[r]) grp[r] |= (it == 0 ? 1 : 2);
+            }
+        }
     }
-    if (!usable) {
+    if (!split || !usable) {
         if (one.state == 1) { if (lane == 0) cones[0] = one; __syncwarp(); return 1; }
         keep_all = true;
         return 0;
@@ -211,8 +248,9 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 slot[r] = valid ? cy * p.f.LW + lx : -1;
                 primary_ray<(MODE != 2)>(p.f, valid ? lx : 0, valid ? global_lattice_row(p.f, ly) : 0, o[r], d[r]);
             } else {
-                const int i = (task << 7) + r * 32 + lane;
-                valid = i < p.n_rays;
+                const int i0 = (task << 7) + r * 32 + lane;
+                valid = i0 < p.n_rays;
+                const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
                 slot[r] = valid ? i : -1;
                 const float4 a = valid ? p.in_od0[i] : make_float4(0.f, 0.f, 0.f, 0.f);
                 const float4 b = valid ? p.in_od1[i] : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -256,31 +294,29 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 }
             }
         };
-        int qn = 0;
-        auto drain = [&]() {
-            __syncwarp();
-            if (qn > 0) {
-                const TriRec* t0 = cs.tri + ws.queue[0];
-                float4 ra = __ldg(&t0->a), rb = __ldg(&t0->b), rc = __ldg(&t0->c);
-                for (int e = 0; e < qn; ++e) {
-                    const TriRec* tn = cs.tri + ws.queue[min(e + 1, qn - 1)];
-                    const float4 na = __ldg(&tn->a), nb = __ldg(&tn->b), nc = __ldg(&tn->c);
-                    test_triangle(ra, rb, rc);
-                    ra = na; rb = nb; rc = nc;
-                }
-            }
-            exec_rays += (unsigned long long)qn * (unsigned long long)n_valid;
-            qn = 0;
-            __syncwarp();
-        };
         if (n_c > 0 || keep_all) {
-            cs_walk<false>(cs, ws.cones, n_c, keep_all, lane, [&](int first, unsigned int mask) {
-                if ((mask >> lane) & 1u) ws.queue[qn + __popc(mask & ((1u << lane) - 1u))] = first + lane;
-                qn += __popc(mask);
-                if (qn > CS_QCAP - 32) drain();
-                return false;
-            });
-            drain();
+            CsWalk wk;
+            cs_walk_init(wk);
+            bool finished;
+            do {
+                finished = cs_fill<false>(cs, ws, n_c, keep_all, lane, wk);
+                __syncwarp();
+                const int qn = wk.qn;
+                if (qn > 0) {
+                    const TriRec* t0 = cs.tri + ws.queue[0];
+                    float4 ra = __ldg(&t0->a), rb = __ldg(&t0->b), rc = __ldg(&t0->c);
+                    #pragma unroll 1
+                    for (int e = 0; e < qn; ++e) {
+                        const TriRec* tn = cs.tri + ws.queue[min(e + 1, qn - 1)];
+                        const float4 na = __ldg(&tn->a), nb = __ldg(&tn->b), nc = __ldg(&tn->c);
+                        test_triangle(ra, rb, rc);
+                        ra = na; rb = nb; rc = nc;
+                    }
+                }
+                exec_rays += (unsigned long long)qn * (unsigned long long)n_valid;
+                wk.qn = 0;
+                __syncwarp();
+            } while (!finished);
         }
 
         // ---- quadrics (lane j looks at quadric j for the warp) and planes; ties go to the lower insertion order ----
@@ -357,8 +393,9 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
         unsigned int light_bits = 0;
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) {
-            const int i = (task << 7) + r * 32 + lane;
-            const bool valid = i < p.n_queries;
+            const int i0 = (task << 7) + r * 32 + lane;
+            const bool valid = i0 < p.n_queries;
+            const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
             slot[r] = valid ? i : -1;
             lid[r] = valid ? p.sq_src[i].y : -1;
             n_valid += valid ? 1 : 0;
@@ -390,8 +427,16 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
                 for (int r = 0; r < ST_RPT; ++r) nd[r] = neg3(d[r]);
                 bool in_a[ST_RPT], in_b[ST_RPT];
                 split_members(nd, in, in_a, in_b);
-                const Bundle ba = bundle_of_light(L, d, dist, in_a), bb = bundle_of_light(L, d, dist, in_b);
-                if (ba.state != 2 && bb.state != 2) { b = ba; b2 = bb; }
+                Bundle half[2];
+                #pragma unroll 1
+                for (int h = 0; h < 2; ++h) {
+                    bool ih[ST_RPT];
+                    #pragma unroll
+                    for (int r = 0; r < ST_RPT; ++r) ih[r] = h == 0 ? in_a[r] : in_b[r];
+                    const Bundle t = bundle_of_light(L, d, dist, ih);
+                    if (h == 0) half[0] = t; else half[1] = t;
+                }
+                if (half[0].state != 2 && half[1].state != 2) { b = half[0]; b2 = half[1]; }
             }
             if (b.state == 2 || n_c + 2 > CS_MAX_CONES) { keep_all = true; break; }     // no usable cone: every triangle is tested
             if (b.state == 1) { if (lane == 0) ws.cones[n_c] = b; ++n_c; }
@@ -439,34 +484,32 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
             for (int r = 0; r < ST_RPT; ++r) done = done && (fr[r] == 0.f && fg[r] == 0.f && fb[r] == 0.f);
             return __all_sync(FULL_MASK, done);                       // 0 * finite stays 0: the warp may stop testing
         };
-        int qn = 0;
         bool warp_done = false;
-        auto drain = [&]() {
-            __syncwarp();
-            if (qn > 0) {
-                const TriRec* t0 = cs.tri + ws.queue[0];
-                float4 ra = __ldg(&t0->a), rb = __ldg(&t0->b), rc = __ldg(&t0->c);
-                for (int e = 0; e < qn; ++e) {
-                    const TriRec* tn = cs.tri + ws.queue[min(e + 1, qn - 1)];
-                    const float4 na = __ldg(&tn->a), nb = __ldg(&tn->b), nc = __ldg(&tn->c);
-                    test_triangle(ra, rb, rc);
-                    ra = na; rb = nb; rc = nc;
-                }
-            }
-            exec_rays += (unsigned long long)qn * (unsigned long long)n_valid;
-            qn = 0;
-            __syncwarp();
-            warp_done = all_zero();
-        };
         tests_tri += (unsigned long long)n_valid * (unsigned long long)cs.n_tri;
         if (n_valid > 0) {
-            cs_walk<true>(cs, ws.cones, n_c, keep_all, lane, [&](int first, unsigned int mask) {
-                if ((mask >> lane) & 1u) ws.queue[qn + __popc(mask & ((1u << lane) - 1u))] = first + lane;
-                qn += __popc(mask);
-                if (qn > CS_QCAP - 32) drain();
-                return warp_done;
-            });
-            if (!warp_done) drain();
+            CsWalk wk;
+            cs_walk_init(wk);
+            bool finished;
+            do {
+                finished = cs_fill<true>(cs, ws, n_c, keep_all, lane, wk);
+                __syncwarp();
+                const int qn = wk.qn;
+                if (qn > 0) {
+                    const TriRec* t0 = cs.tri + ws.queue[0];
+                    float4 ra = __ldg(&t0->a), rb = __ldg(&t0->b), rc = __ldg(&t0->c);
+                    #pragma unroll 1
+                    for (int e = 0; e < qn; ++e) {
+                        const TriRec* tn = cs.tri + ws.queue[min(e + 1, qn - 1)];
+                        const float4 na = __ldg(&tn->a), nb = __ldg(&tn->b), nc = __ldg(&tn->c);
+                        test_triangle(ra, rb, rc);
+                        ra = na; rb = nb; rc = nc;
+                    }
+                }
+                exec_rays += (unsigned long long)qn * (unsigned long long)n_valid;
+                wk.qn = 0;
+                __syncwarp();
+                warp_done = all_zero();
+            } while (!finished && !warp_done);
         }
 
         if (!warp_done) {
@@ -509,9 +552,9 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
                 p.filter[p.sq_dst ? p.sq_dst[slot[r]] : slot[r]] = make_float4(fr[r], fg[r], fb[r], 0.f);
                 // three or more factors multiplied in another order than Scene.cpp:1856's: redo this query in order
                 const unsigned int st = s_occ[r][tid];
-                if ((st & 4u) && (st & 3u) >= 3u && (fr[r] != 0.f || fg[r] != 0.f || fb[r] != 0.f)) {
-                    const unsigned int k = atomicAdd(cp.fix_count, 1u);
-                    if ((int)k < cp.fix_cap) cp.fix_list[k] = slot[r];
+                if ((st & 4u) && (st & 3u) >= 3u && (fr[r] != 0.f || fg[r] != 0.f || fb[r] != 0.f) && p.fix_count) {
+                    const unsigned int k = atomicAdd(p.fix_count, 1u);
+                    if ((int)k < p.fix_cap) p.fix_list[k] = slot[r];
                     ++fixups;
                 }
             }
@@ -544,10 +587,10 @@ __global__ void __launch_bounds__(128) k_shadow_fixup(const __grid_constant__ Cu
     const ShadowParams& p = cp.s;
     const DeviceScene& s = p.s;
     const int lane = threadIdx.x & 31;
-    const int n = min((int)*cp.fix_count, cp.fix_cap);
+    const int n = min((int)*p.fix_count, p.fix_cap);
     const int n_surf = s.rl.n_surf;
     for (int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n; w += gridDim.x * (blockDim.x >> 5)) {
-        const int qi = cp.fix_list[w];
+        const int qi = p.fix_list[w];
         V3 o, d;
         float dist;
         shadow_query<(MODE != 2)>(p, qi, o, d, dist);
@@ -628,6 +671,16 @@ cudaError_t launch_shadow_fixup(const CullShadowParams& p, int sm_count, cudaStr
     return cudaGetLastError();
 }
 
+cudaError_t cull_sort_pairs(DevBuf* tmp, const unsigned int* keys_in, unsigned int* keys_out, const int* idx_in, int* idx_out,
+                            int n, int bits, cudaStream_t st)
+{
+    size_t bytes = 0;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(nullptr, bytes, keys_in, keys_out, idx_in, idx_out, n, 0, bits, st);
+    if (e != cudaSuccess) return e;
+    if ((e = tmp->ensure(bytes)) != cudaSuccess) return e;
+    return cub::DeviceRadixSort::SortPairs(tmp->p, bytes, keys_in, keys_out, idx_in, idx_out, n, 0, bits, st);
+}
+
 // ---------------------------------------------------------------------------------------
 // cull_prepare: Morton sort + sphere hierarchy, on the device, once per scene (cached until rtb200_set_scene)
 // ---------------------------------------------------------------------------------------
@@ -655,15 +708,6 @@ __global__ void k_cs_bounds(const TriRec* __restrict__ tri, int n, int* __restri
     }
 }
 
-RT_DEV unsigned int cs_expand10(unsigned int v)
-{
-    v = (v * 0x00010001u) & 0xFF0000FFu;
-    v = (v * 0x00000101u) & 0x0F00F00Fu;
-    v = (v * 0x00000011u) & 0xC30C30C3u;
-    v = (v * 0x00000005u) & 0x49249249u;
-    return v;
-}
-
 // 30-bit Morton code of the centroid in CUBIC cells (one scale for the three axes: a flat scene is not cut into sheets)
 __global__ void k_cs_keys(const TriRec* __restrict__ tri, int n, float lx, float ly, float lz, float inv, unsigned int* __restrict__ keys, int* __restrict__ idx)
 {
@@ -671,9 +715,7 @@ __global__ void k_cs_keys(const TriRec* __restrict__ tri, int n, float lx, float
     if (i >= n) return;
     const float4 a = tri[i].a, b = tri[i].b, c = tri[i].c;
     const float cx = a.x + (b.x + c.x) * (1.0f / 3.0f), cy = a.y + (b.y + c.y) * (1.0f / 3.0f), cz = a.z + (b.z + c.z) * (1.0f / 3.0f);
-    const float fx = fminf(fmaxf((cx - lx) * inv, 0.f), 1023.f), fy = fminf(fmaxf((cy - ly) * inv, 0.f), 1023.f), fz = fminf(fmaxf((cz - lz) * inv, 0.f), 1023.f);
-    const unsigned int ix = fx == fx ? (unsigned int)fx : 0u, iy = fy == fy ? (unsigned int)fy : 0u, iz = fz == fz ? (unsigned int)fz : 0u;
-    keys[i] = (cs_expand10(ix) << 2) | (cs_expand10(iy) << 1) | cs_expand10(iz);
+    keys[i] = morton30(cx, cy, cz, lx, ly, lz, inv);
     idx[i] = i;
 }
 
@@ -738,6 +780,7 @@ struct CullState {
     unsigned long long serial = ~0ull;       // scene the hierarchy was built for
     CullScene cs{};
     double build_ms = 0.0;
+    float lo[3] = {0.f, 0.f, 0.f}, ext = 0.f;  // centroid bounds of the triangles (origin and size of the Morton grid)
 };
 
 static CullState* cull_state(rtb200_ctx* c)
@@ -797,6 +840,7 @@ int cull_prepare(rtb200_ctx* c, CullScene* out)
         KCU(cudaMemcpyAsync(h, b->bounds.p, 24, cudaMemcpyDeviceToHost, st));
         KCU(cudaStreamSynchronize(st));
         float lo[3], ext = 0.f;
+        b->ext = 0.f;
         for (int k = 0; k < 3; ++k) {
             lo[k] = cs_order_float(h[k]);
             const float hi = cs_order_float(h[3 + k]);
@@ -804,6 +848,8 @@ int cull_prepare(rtb200_ctx* c, CullScene* out)
             ext = std::max(ext, hi - lo[k]);
         }
         const float inv = ext > 0.f ? 1023.999f / ext : 0.f;
+        b->ext = ext;
+        for (int k = 0; k < 3; ++k) b->lo[k] = lo[k];
         k_cs_keys<<<(T + 255) / 256, 256, 0, st>>>(c->ds.tri, T, lo[0], lo[1], lo[2], inv, b->keys.as<unsigned int>(), b->idx.as<int>());
         KCU(cudaGetLastError());
         size_t tmp_bytes = 0;
@@ -825,6 +871,14 @@ int cull_prepare(rtb200_ctx* c, CullScene* out)
     CullScene& cs = b->cs;
     cs.tri = b->tri.as<TriRec>(); cs.sph = sph; cs.w = w;
     cs.n3 = n3; cs.n_tri = T;
+    // sort keys of secondary rays / queries: the cells of the triangles' Morton grid, the box widened 4 x around its
+    // centre (reflections reach the ground plane far outside the mesh; what lies farther is clamped to the border cells)
+    for (int k = 0; k < 3; ++k) cs.key_lo[k] = 0.f;
+    cs.key_inv = 0.f;
+    if (T > 0 && b->ext > 0.f) {
+        for (int k = 0; k < 3; ++k) cs.key_lo[k] = b->lo[k] - 1.5f * b->ext;
+        cs.key_inv = 1023.999f / (4.0f * b->ext);
+    }
     cs.top_blocks = (n3 + 31) / 32;
     b->serial = c->scene_serial;
     *out = cs;

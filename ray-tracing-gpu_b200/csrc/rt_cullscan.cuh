@@ -18,25 +18,30 @@ struct CullScene {
     int n3;
     int top_blocks;                  // rounds of 32 at level 3 (1 up to a million triangles)
     int n_tri;                       // real triangles
+    float key_lo[3], key_inv;        // grid of the sort keys of secondary rays / queries (ShadeAParams::child_key)
 };
 
 struct CullTraceParams {
     TraceParams t;
     CullScene   cs;
     unsigned int* task_counter;      // zeroed before the launch: warps take tasks of 128 rays from it
+    const int*    perm;              // null, or: the i-th ray of the launch is queue entry perm[i] (rays sorted by the
+                                     // surface they leave, see ShadeAParams::child_key)
 };
 
 struct CullShadowParams {
     ShadowParams s;
     CullScene    cs;
     unsigned int* task_counter;
-    int*          fix_list;          // queries whose filter product has to be redone in insertion order (rare) ...
-    unsigned int* fix_count;         // ... how many, and the room there is
-    int           fix_cap;
-};
+    const int*    perm;              // null, or: the i-th query of the launch is queue entry perm[i] (sorted by light, place)
+};                                   // (fix-up list: ShadowParams::fix_list / fix_count / fix_cap)
 
 cudaError_t launch_cull_nearest(const CullTraceParams& p, int sm_count, cudaStream_t st);
 cudaError_t launch_cull_shadow(const CullShadowParams& p, int sm_count, cudaStream_t st);
 cudaError_t launch_shadow_fixup(const CullShadowParams& p, int sm_count, cudaStream_t st);
+// stable sort of n (key, index) pairs on the low `bits` bits of the key (cub radix sort); *tmp grows as needed
+struct DevBuf;
+cudaError_t cull_sort_pairs(DevBuf* tmp, const unsigned int* keys_in, unsigned int* keys_out, const int* idx_in, int* idx_out,
+                            int n, int bits, cudaStream_t st);
 
 } // namespace rtb

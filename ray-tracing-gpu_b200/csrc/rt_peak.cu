@@ -14,10 +14,14 @@ namespace rtb {
 
 // `clk` (may be null): per block, SM cycles (clock64) and nanoseconds (globaltimer) thread 0 spent in the chain --
 // the clock the chain really ran at and the FFMA issue rate per SM can be recomputed from them
-__global__ void __launch_bounds__(PEAK_THREADS) k_ffma_chain(float* sink, float a, float b, unsigned long long* clk)
+__global__ void __launch_bounds__(PEAK_THREADS, 4) k_ffma_chain(float* sink, float a, float b, unsigned long long* clk)
 {
-    unsigned long long c0 = 0, t0 = 0;
-    if (threadIdx.x == 0) { c0 = (unsigned long long)clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0)); }
+    __shared__ unsigned long long s_start[2];       // (kept out of the registers: 4 blocks x 512 threads need <= 32 per thread)
+    if (threadIdx.x == 0) {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        s_start[0] = (unsigned long long)clock64(); s_start[1] = t0;
+    }
     float x[PEAK_CHAINS];
     #pragma unroll
     for (int i = 0; i < PEAK_CHAINS; ++i) x[i] = (float)(threadIdx.x + i) * 1e-3f;
@@ -36,8 +40,8 @@ __global__ void __launch_bounds__(PEAK_THREADS) k_ffma_chain(float* sink, float 
         unsigned long long t1;
         const unsigned long long c1 = (unsigned long long)clock64();
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        clk[2 * blockIdx.x] = c1 - c0 + (s == 123.456f ? 1ull : 0ull);     // (depends on the chains: not hoisted above them)
-        clk[2 * blockIdx.x + 1] = t1 - t0;
+        clk[2 * blockIdx.x] = c1 - s_start[0] + (s == 123.456f ? 1ull : 0ull);     // (depends on the chains: not hoisted above them)
+        clk[2 * blockIdx.x + 1] = t1 - s_start[1];
     }
 }
 

@@ -33,21 +33,18 @@ namespace rtb {
 struct StreamBufs {                // per-context scratch of the streamed path (lives in the ctx levels + these)
     DevBuf hit, hitP, hitN, q_base, sq0, sq1, sq_src, sq_dst, filter;
     DevBuf tasks, fix;             // culled scan: task / fix-up counters (3 words per level), fix-up list
+    DevBuf ckey, cidx, ckey2, cperm, qkey, qidx, qkey2, qperm, sort_tmp;   // culled scan: (key, index) pairs of the children / queries of a level and their sorted forms
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // per-stage stopwatch
 };
 
-// warp-bundle culling of the tiled kernels (rt_trace.cu); RTB200_NO_BUNDLE_CULL=1 turns it off for A/B runs
-// RTB200_NEAREST_CONES=4 (not yet measured on a GPU, off by default): warps of secondary rays may hold up to 4 cones
+// RTB200_NO_BUNDLE_CULL=1: no culling of whole triangles per warp -- the plain tiled scan (the roofline measurement)
 static int bundle_cull_enabled()
 {
     const char* e = getenv("RTB200_NO_BUNDLE_CULL");
-    if (e && atoi(e) != 0) return 0;
-    const char* m = getenv("RTB200_NEAREST_CONES");
-    return (m && atoi(m) > 1) ? 2 : 1;
+    return (e && atoi(e) != 0) ? 0 : 1;
 }
 
-// The culled scan (rt_cullscan.cu) is the default for everything the plain tiled kernels would cull per warp;
-// RTB200_CULLSCAN=0 keeps the tiled kernels with their per-tile warp-bundle culling (round 1) for A/B runs.
+// The culled scan (rt_cullscan.cu) is the default; RTB200_CULLSCAN=0 (like RTB200_NO_BUNDLE_CULL=1) runs the plain tiled scan.
 static bool cullscan_enabled()
 {
     if (bundle_cull_enabled() == 0) return false;
@@ -73,6 +70,7 @@ void stream_release(rtb200_ctx* c)
     if (!c->stream_scratch) return;
     StreamBufs* b = static_cast<StreamBufs*>(c->stream_scratch);
     b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->sq_dst.release(); b->filter.release(); b->tasks.release(); b->fix.release();
+    b->ckey.release(); b->cidx.release(); b->ckey2.release(); b->cperm.release(); b->qkey.release(); b->qidx.release(); b->qkey2.release(); b->qperm.release(); b->sort_tmp.release();
     for (auto& e : b->ev) if (e) cudaEventDestroy(e);
     delete b;
     c->stream_scratch = nullptr;
@@ -113,6 +111,14 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
         const int rc = cull_prepare(c, &cull);
         if (rc != RTB200_OK) return rc;
     }
+    // levels >= 1 of the culled scan: rays sorted by the surface they leave, queries by (light, surface of the hit point)
+    // -- such groups are compact bundles, queue neighbours are not (RTB200_SORT_SECONDARY=0: queue order, for A/B runs)
+    bool sort_secondary = cullscan;
+    if (const char* e = getenv("RTB200_SORT_SECONDARY")) sort_secondary = sort_secondary && atoi(e) != 0;
+    if (cull.key_inv <= 0.f) sort_secondary = false;
+    int light_bits = 0;
+    while ((1 << light_bits) < std::max(c->ds.rl.n_light, 1)) ++light_bits;
+    bool rays_sorted = false;                   // the rays of the level about to be traced have a permutation in sb->cperm
     const int k = fp.k;
     const int local_LH = local_rows * k;
     const int L = c->ds.rl.n_light;
@@ -131,7 +137,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     unsigned* h_cnt = c->h_small.as<unsigned>();
     unsigned* d_cnt = c->counters.as<unsigned>();
     const size_t n_tasks_words = 3 * ((size_t)std::max(fr->max_bounces, 0) + 2);
-    if (cullscan && (e = sb->tasks.ensure(sizeof(unsigned) * n_tasks_words)) != cudaSuccess) return set_cuda_error(c, e, "task counters");
+    if ((e = sb->tasks.ensure(sizeof(unsigned) * n_tasks_words)) != cudaSuccess) return set_cuda_error(c, e, "task counters");
     unsigned* d_tasks = sb->tasks.as<unsigned>();
     unsigned max_level_seen = 0, chunks = 0;
     unsigned long long rays_nearest = 0;
@@ -154,7 +160,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     for (int ly0 = 0; ly0 < local_LH; ly0 += rows_per_chunk, ++chunks) {
         const int rows = std::min(rows_per_chunk, local_LH - ly0);
         SCU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned) * n_counters, c->stream));
-        if (cullscan) SCU(cudaMemsetAsync(d_tasks, 0, sizeof(unsigned) * n_tasks_words, c->stream));
+        SCU(cudaMemsetAsync(d_tasks, 0, sizeof(unsigned) * n_tasks_words, c->stream));
         std::vector<int> n_rays, n_links;
         n_rays.push_back(rows * fp.LW);
         int level = 0;
@@ -194,6 +200,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             else if (cullscan) {
                 CullTraceParams ctp;
                 ctp.t = tp; ctp.cs = cull; ctp.task_counter = d_tasks + 3 * level;
+                ctp.perm = (level > 0 && rays_sorted) ? sb->cperm.as<int>() : nullptr;
                 SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
             }
             else         SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
@@ -217,6 +224,22 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             sa.links = cur.links.as<int4>();
             sa.stats = c->stats.as<unsigned long long>();
             sa.exact = exact ? 1 : 0;
+            const bool sort_children = sort_secondary && spawn;
+            const bool sort_queries = sort_secondary && level > 0 && group_queries;
+            if (sort_children) {
+                const size_t cap = n * children;
+                if ((e = sb->ckey.ensure(4 * cap)) != cudaSuccess || (e = sb->cidx.ensure(4 * cap)) != cudaSuccess ||
+                    (e = sb->ckey2.ensure(4 * cap)) != cudaSuccess || (e = sb->cperm.ensure(4 * cap)) != cudaSuccess) return set_cuda_error(c, e, "sort buffers");
+                sa.child_key = sb->ckey.as<unsigned int>(); sa.child_idx = sb->cidx.as<int>();
+            }
+            if (sort_queries) {
+                const size_t cap = n * std::max(L, 1);
+                if ((e = sb->qkey.ensure(4 * cap)) != cudaSuccess || (e = sb->qidx.ensure(4 * cap)) != cudaSuccess ||
+                    (e = sb->qkey2.ensure(4 * cap)) != cudaSuccess || (e = sb->qperm.ensure(4 * cap)) != cudaSuccess) return set_cuda_error(c, e, "sort buffers");
+                sa.sq_key = sb->qkey.as<unsigned int>(); sa.sq_idx = sb->qidx.as<int>();
+            }
+            for (int a = 0; a < 3; ++a) sa.key_lo[a] = cull.key_lo[a];
+            sa.key_inv = cull.key_inv;
             SCU(launch_shade_a(sa, c->stream));
             SCU(cudaEventRecord(E[2], c->stream));
             ++*launches;
@@ -231,6 +254,19 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             }
             const int n_children = (int)h_cnt[0], n_lk = (int)h_cnt[1], n_sq = (int)h_cnt[2];
             st->rays_shadow += (uint64_t)n_sq;
+            rays_sorted = false;
+            if (sort_children && n_children > 256) {           // the next level's rays, by the surface they leave
+                SCU(cull_sort_pairs(&sb->sort_tmp, sb->ckey.as<unsigned int>(), sb->ckey2.as<unsigned int>(), sb->cidx.as<int>(), sb->cperm.as<int>(),
+                                    n_children, 30, c->stream));
+                rays_sorted = true;
+                *launches += 3;
+            }
+            const bool queries_sorted = sort_queries && n_sq > 256;
+            if (queries_sorted) {
+                SCU(cull_sort_pairs(&sb->sort_tmp, sb->qkey.as<unsigned int>(), sb->qkey2.as<unsigned int>(), sb->qidx.as<int>(), sb->qperm.as<int>(),
+                                    n_sq, 27 + light_bits, c->stream));
+                *launches += 3;
+            }
             // ---- shadow filters --------------------------------------------------------------
             SCU(cudaEventRecord(E[3], c->stream));
             if (n_sq > 0) {
@@ -241,16 +277,19 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 sp.by_light = shadow_by_light ? 1 : 0;
                 sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode; sp.cull_bundles = bundle_cull_enabled();
                 if (use_bvh) SCU(launch_bvh_shadow(sp, c->stream));
-                else if (cullscan && group_queries) {
+                else {
+                    // tiled / culled scan: queries whose product order matters go on a list and are redone in insertion order
                     if ((e = sb->fix.ensure(sizeof(int) * (size_t)n_sq)) != cudaSuccess) return set_cuda_error(c, e, "fix-up list");
+                    unsigned* tk = sb->tasks.as<unsigned>() + 3 * level;
+                    sp.fix_count = tk + 2; sp.fix_list = sb->fix.as<int>(); sp.fix_cap = n_sq;
                     CullShadowParams csp;
-                    csp.s = sp; csp.cs = cull; csp.task_counter = d_tasks + 3 * level + 1;
-                    csp.fix_count = d_tasks + 3 * level + 2; csp.fix_list = sb->fix.as<int>(); csp.fix_cap = n_sq;
-                    SCU(launch_cull_shadow(csp, c->sm_count, c->stream));
-                    SCU(launch_shadow_fixup(csp, c->sm_count, c->stream));     // queries whose product order matters (rare; reads the count itself)
+                    csp.s = sp; csp.cs = cull; csp.task_counter = tk + 1;
+                    csp.perm = queries_sorted ? sb->qperm.as<int>() : nullptr;
+                    if (cullscan && group_queries) SCU(launch_cull_shadow(csp, c->sm_count, c->stream));
+                    else                           SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+                    SCU(launch_shadow_fixup(csp, c->sm_count, c->stream));     // (reads the count itself; nearly always 0)
                     ++*launches;
                 }
-                else         SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
                 ++*launches;
             }
             SCU(cudaEventRecord(E[4], c->stream));
@@ -338,6 +377,7 @@ int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
         if ((e = sb->tasks.ensure(64)) != cudaSuccess) return set_cuda_error(c, e, "task counters");
         SCU(cudaMemsetAsync(sb->tasks.p, 0, 4, c->stream));
         ctp.task_counter = sb->tasks.as<unsigned>();
+        ctp.perm = nullptr;
         SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
     }
     else                          SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
@@ -364,7 +404,16 @@ int stream_query_shadow(rtb200_ctx* c, int n, uint32_t flags)
     sp.s = c->ds; sp.sq0 = sb->sq0.as<float4>(); sp.sq1 = sb->sq1.as<float4>(); sp.n_queries = n;
     sp.filter = sb->filter.as<float4>(); sp.stats = c->stats.as<unsigned long long>(); sp.mode = mode;
     if (flags & RTB200_F_USE_BVH) SCU(launch_bvh_shadow(sp, c->stream));
-    else                          SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+    else {
+        if ((e = sb->fix.ensure(sizeof(int) * (size_t)n)) != cudaSuccess || (e = sb->tasks.ensure(64)) != cudaSuccess) return set_cuda_error(c, e, "fix-up list");
+        SCU(cudaMemsetAsync(sb->tasks.p, 0, 12, c->stream));
+        sp.fix_count = sb->tasks.as<unsigned>() + 2; sp.fix_list = sb->fix.as<int>(); sp.fix_cap = n;
+        SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+        CullShadowParams csp;
+        memset(&csp, 0, sizeof csp);
+        csp.s = sp;
+        SCU(launch_shadow_fixup(csp, c->sm_count, c->stream));
+    }
     SCU(launch_query_unpack_filter(n, sp.filter, c->q_out2.as<float>(), c->stream));
     return RTB200_OK;
 }

@@ -25,8 +25,7 @@ struct TraceParams {
                                    // 1: no filter, reference sequence for every test (EXACT_FP)
                                    // 2: filter + fused survivors (FUSED_FP)
     unsigned long long* stats;     // LBVH kernels: nodes visited / triangle tests (may be null)
-    int   cull_bundles;            // tiled kernels: cull whole triangles per warp against the cone of its rays
-                                   // (0: off, 1: one cone per warp, > 1: secondary rays may split into up to 4)
+    int   cull_bundles;            // (culled scan only)
 };
 
 // shade-A: hit point, normal, shadow queries of the facing lights, children
@@ -53,6 +52,14 @@ struct ShadeAParams {
     unsigned long long* stats;
     int   exact;                   // rounding of everything that is kept (1 unless FUSED_FP)
     int   tile_rays;               // level 0: a CTA takes 16x16 lattice samples instead of 256 consecutive ones
+    // culled scan, levels >= 1 (rt_stream.cu): sort keys.  Rays that start close to each other and shadow queries
+    // that go from neighbouring points to the same light are compact bundles whatever their queue positions are;
+    // the host sorts (key, index) pairs and hands the trace kernels the permutation.  All four may be null.
+    unsigned int* child_key;       // per child slot: 30-bit Morton code of its origin (cells of key_inv^-1 from key_lo)
+    int*          child_idx;       // per child slot: the slot itself (values of the pair sort)
+    unsigned int* sq_key;          // per shadow query: light << 27 | 27-bit Morton code of the hit point
+    int*          sq_idx;
+    float         key_lo[3], key_inv;
     int*  sq_dst;                  // null: queries in (ray, light) order, filter slot = query slot.  Otherwise the
                                    // CTA's queries are queued light by light (<= 8 lights) and sq_dst[query] is the
                                    // filter slot shade-B reads (q_base[ray] + rank of the light among the facing ones)
@@ -70,7 +77,10 @@ struct ShadowParams {
     float4* filter;                // r g b | 0 per query
     unsigned long long* stats;
     int   mode;
-    int   cull_bundles;            // tiled kernel: per-light cones of the warp's queries (needs sq_src)
+    int   cull_bundles;            // (culled scan only)
+    int*          fix_list;        // queries whose filter product has to be redone in insertion order (rare) ...
+    unsigned int* fix_count;       // ... how many (null: nothing is recorded), and the room there is
+    int           fix_cap;
 };
 
 // shade-B: ambient + per-light diffuse/Phong with the shadow filters, in light order
@@ -105,6 +115,22 @@ RT_DEV void shadow_query(const ShadowParams& p, int i, V3& o, V3& d, float& dist
         const float4 a = p.sq0[i], b = p.sq1[i];
         o = f4_xyz(a); d = f4_xyz(b); dist = a.w;
     }
+}
+
+RT_DEV unsigned int expand10(unsigned int v)         // bit i of a 10-bit value -> bit 3 i
+{
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+// 30-bit Morton code of a point in cubic cells (clamped to the 1024^3 grid; NaN -> cell 0)
+RT_DEV unsigned int morton30(float x, float y, float z, float lx, float ly, float lz, float inv)
+{
+    const float fx = fminf(fmaxf((x - lx) * inv, 0.f), 1023.f), fy = fminf(fmaxf((y - ly) * inv, 0.f), 1023.f), fz = fminf(fmaxf((z - lz) * inv, 0.f), 1023.f);
+    const unsigned int ix = fx == fx ? (unsigned int)fx : 0u, iy = fy == fy ? (unsigned int)fy : 0u, iz = fz == fz ? (unsigned int)fz : 0u;
+    return (expand10(ix) << 2) | (expand10(iy) << 1) | expand10(iz);
 }
 
 cudaError_t launch_trace_nearest(const TraceParams& p, int sm_count, cudaStream_t st);

@@ -1,4 +1,5 @@
-// rt_trace.cu -- the brute-force intersection kernels of the streamed path (large scenes).
+// rt_trace.cu -- the PLAIN brute-force intersection kernels of the streamed path (large scenes) and the shading
+// stages of its wavefront.
 //
 // Every ray of a wavefront level is tested against EVERY surface (this is the reference's
 // algorithm: Scene.cpp:1710-1715 and :1850-1858 are linear scans).  What makes it fast:
@@ -14,9 +15,11 @@
 //     The filter is conservative by construction (margins that bound the fused / reference difference of every
 //     numerator); only rays that pass it run the reference's own rounding sequence (triangle_t<true>), so the
 //     accepted distances are bit-identical to the CPU renderer.
-//   * whole triangles are culled per warp against the cone of its 128 rays ("warp bundles" below); shade-A
-//     queues rays by 16x16 patches and shadow queries light by light so that those 128 rays are a compact bundle.
 //   * shadow queries leave at warp granularity once every ray of the warp holds a zero filter.
+// These kernels are the roofline kernels (bench.py times them with RTB200_NO_BUNDLE_CULL=1), the RTB200_F_EXACT_FP
+// path, and what explicit shadow queries and scenes with more than 8 lights run through.  The DEFAULT path of a frame
+// is the culled scan of rt_cullscan.cu, which skips whole triangles per warp (round 1 did that inside these tile
+// loops, meeting at two CTA barriers per tile: 91 ms for config 3 against 47 ms now) and returns the same bits.
 #include "rt_stream.cuh"
 #include "rt_cull.cuh"
 #include "rt_bundle.cuh"
@@ -29,8 +32,6 @@ namespace rtb {
 struct TraceSmem {
     TriRec tile[ST_STAGES][ST_TILE];                 // 24 KB
     unsigned char side[ST_SIDE_MAX];                 // quadric + plane records (when they fit)
-    float4 sphere[ST_TILE];                          // bounding spheres of the current tile: centre | radius ...
-    float  sphere_w[ST_TILE];                        // ... and |e1| |e2| (warp-bundle culling)
     uint64_t full[ST_STAGES];
 };
 
@@ -39,16 +40,11 @@ struct TraceSmem {
 // (warp = 16x8 pixels, thread = a 2x2 quad) generated on the fly; otherwise 1024 consecutive
 // queue entries.
 // ---------------------------------------------------------------------------------------
-// MULTI (secondary rays, RTB200_NEAREST_CONES=4): a warp whose single cone is wide -- 128 consecutive children left
-// several surfaces in several directions -- splits its rays twice around their most distant directions and culls with
-// up to 4 cones (scripts/sim_secondary_grouping.py: level-1 rays of config 3, 44 % -> 0.3 % of the tests entered).
-#define BUNDLE_NEAREST_CONES 4
-template <int MODE, bool PRIMARY, bool MULTI>
+template <int MODE, bool PRIMARY>
 __global__ void __launch_bounds__(ST_THREADS, 2)
 k_trace_nearest(const __grid_constant__ TraceParams p)
 {
     __shared__ __align__(128) TraceSmem sm;
-    __shared__ Bundle ncones[MULTI ? ST_THREADS / 32 : 1][BUNDLE_NEAREST_CONES];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const DeviceScene& s = p.s;
     const int n_tiles = s.n_tri_padded / ST_TILE;
@@ -71,9 +67,7 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
     const int tiles_x = (p.f.LW + 31) >> 5;
     const int n_blocks = PRIMARY ? tiles_x * ((p.chunk_rows + 31) >> 5) : (p.n_rays + ST_BLOCK_RAYS - 1) / ST_BLOCK_RAYS;
     uint32_t phase_bits = 0;                         // parity of each stage's barrier
-    unsigned int n_exec = 0;                         // triangles this warp tested ray by ray (survivors of the bundle cull)
-    unsigned long long exec_rays = 0;                // ... times the rays it held
-
+    unsigned long long exec_rays = 0;                // (ray, triangle) tests entered
     for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
         // ---- this thread's 4 rays ------------------------------------------------------------
         V3 o[ST_RPT], d[ST_RPT];
@@ -104,40 +98,6 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
         float dmax = 0.f;                             // largest |direction component| of this thread's rays (filter margins)
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) dmax = fmaxf(dmax, max_abs3(d[r]));
-        // the cone that holds the warp's 128 rays (see "warp bundles" above)
-        Bundle bun;
-        bun.state = 2;
-        bool multi = false;                           // MULTI: cull with ncones[warp][0..3] instead of `bun`
-        if (MODE != 1 && p.cull_bundles) {
-            bool use[ST_RPT];
-            #pragma unroll
-            for (int r = 0; r < ST_RPT; ++r) use[r] = slot[r] >= 0;
-            bun = bundle_of_rays(o, d, use);
-            if (MULTI && (bun.state == 2 || (bun.state == 1 && bun.sin_t > BUNDLE_SPLIT_SIN))) {
-                V3 dn[ST_RPT];
-                #pragma unroll
-                for (int r = 0; r < ST_RPT; ++r) {
-                    const float l2 = dot3<false>(d[r], d[r]);
-                    const float il = (l2 > 1.0e-20f && l2 < 1.0e20f) ? rsqrtf(l2) : 0.f;
-                    dn[r] = mk3(d[r].x * il, d[r].y * il, d[r].z * il);
-                }
-                bool ga[ST_RPT], gb[ST_RPT], g[BUNDLE_NEAREST_CONES][ST_RPT];
-                split_members(dn, use, ga, gb);
-                split_members(dn, ga, g[0], g[1]);
-                split_members(dn, gb, g[2], g[3]);
-                bool usable = true;
-                #pragma unroll
-                for (int k = 0; k < BUNDLE_NEAREST_CONES; ++k) {
-                    const Bundle b = bundle_of_rays(o, d, g[k]);     // state 0: an empty part
-                    usable = usable && b.state != 2;
-                    if (lane == 0) ncones[MULTI ? warp : 0][k] = b;
-                }
-                multi = usable;
-                if (usable) bun.state = 1;               // leave the plain scan; the cones are in shared memory
-                __syncwarp();
-            }
-        }
-
         // ---- triangles: double-buffered TMA tiles ---------------------------------------------
         if (tid == 0 && n_tiles > 0) {
             mbar_arrive_expect_tx(&sm.full[0], (uint32_t)sizeof(TriRec) * ST_TILE);
@@ -153,13 +113,6 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
             mbar_wait(&sm.full[st], (phase_bits >> st) & 1u);
             phase_bits ^= (1u << st);
             const TriRec* __restrict__ tile = sm.tile[st];
-            if (MODE != 1 && p.cull_bundles) {       // bounding sphere of triangle `tid`, once per CTA and tile
-                V3 c; float rad, w;
-                triangle_sphere(f4_xyz(tile[tid].a), f4_xyz(tile[tid].b), f4_xyz(tile[tid].c), c, rad, w);
-                sm.sphere[tid] = make_float4(c.x, c.y, c.z, rad); sm.sphere_w[tid] = w;
-                __syncthreads();
-            }
-
             if (MODE == 1) {                         // no filter: the reference sequence for every test
                 #pragma unroll 2
                 for (int j = 0; j < ST_TILE; ++j) {
@@ -197,35 +150,8 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
                         }
                     }
                 };
-                if (bun.state == 2) {                // no usable cone (or culling off): the plain scan of the tile
-                    n_exec += (unsigned int)min(ST_TILE, s.n_tri - t * ST_TILE);
-                    #pragma unroll 2
-                    for (int j = 0; j < ST_TILE; ++j) test_triangle(j);
-                } else
-                for (int j0 = 0; j0 < ST_TILE; j0 += 32) {
-                    unsigned int keep_mask;
-                    {                                // lane j looks at triangle j0 + j for the whole warp
-                        const float4 sph = sm.sphere[j0 + lane];
-                        const float w = sm.sphere_w[j0 + lane];
-                        bool keep;
-                        if (MULTI && multi) {
-                            keep = false;
-                            #pragma unroll
-                            for (int k = 0; k < BUNDLE_NEAREST_CONES; ++k) {
-                                const Bundle& b = ncones[MULTI ? warp : 0][k];
-                                if (b.state == 1 && !bundle_culls(b, mk3(sph.x, sph.y, sph.z), sph.w, w)) keep = true;
-                            }
-                            keep = keep && w > 0.f;
-                        } else
-                            keep = w > 0.f && bun.state == 1 && !bundle_culls(bun, mk3(sph.x, sph.y, sph.z), sph.w, w);
-                        keep_mask = __ballot_sync(FULL_MASK, keep);
-                    }
-                    n_exec += (unsigned int)__popc(keep_mask);
-                    while (keep_mask) {
-                        test_triangle(j0 + __ffs((int)keep_mask) - 1);
-                        keep_mask &= keep_mask - 1u;
-                    }
-                }
+                #pragma unroll 2
+                for (int j = 0; j < ST_TILE; ++j) test_triangle(j);
             }
             __syncthreads();                         // everyone is done with this stage
         }
@@ -253,10 +179,9 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
         }
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r)
-            if (slot[r] >= 0) { p.hit[slot[r]] = make_float2(best_t[r], __int_as_float(best_id[r])); exec_rays += n_exec; }
-        n_exec = 0;
+            if (slot[r] >= 0) { p.hit[slot[r]] = make_float2(best_t[r], __int_as_float(best_id[r])); exec_rays += (unsigned long long)s.n_tri; }
     }
-    if (MODE != 1 && p.stats) {                      // per-ray triangle tests actually entered
+    if (MODE != 1 && p.stats) {                      // per-ray triangle tests entered: all of them
         #pragma unroll
         for (int off = 16; off > 0; off >>= 1) exec_rays += __shfl_xor_sync(FULL_MASK, exec_rays, off);
         if (lane == 0 && exec_rays) atomicAdd(&p.stats[(size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + ST_TEST_TRI_EXEC], exec_rays);
@@ -266,30 +191,24 @@ k_trace_nearest(const __grid_constant__ TraceParams p)
 // ---------------------------------------------------------------------------------------
 // Shadow filter (Scene.cpp:1842-1861): product of colour*kt over every surface hit strictly
 // between EPSILON and the light.  One CTA = 1024 consecutive shadow queries.
+// The scan meets the occluders type by type (triangles, quadrics, planes), the reference in insertion order
+// (Scene.cpp:1856).  Up to two factors commute exactly; a query that met three or more, not in increasing insertion
+// order, with a non-zero product goes on the fix-up list and is redone in order by k_shadow_fixup (rt_cullscan.cu).
 // ---------------------------------------------------------------------------------------
-template <int MODE>
-RT_DEV void filter_mul(const MatRec* __restrict__ mat, int m, float& fr, float& fg, float& fb)
-{
-    const float4 m0 = mat[m].m0;
-    const float kt = mat[m].m2.x;
-    fr = __fmul_rn(fr, __fmul_rn(m0.x, kt));
-    fg = __fmul_rn(fg, __fmul_rn(m0.y, kt));
-    fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
-}
+#define OCC_ORDER_LIMIT (1 << 29)      // per-ray state word: (largest order + 1) << 3 | met out of order << 2 | occluders (saturating at 3)
 
 template <int MODE>
 __global__ void __launch_bounds__(ST_THREADS, 2)
 k_trace_shadow(const __grid_constant__ ShadowParams p)
 {
     __shared__ __align__(128) TraceSmem sm;
-    __shared__ Bundle cones[ST_THREADS / 32][2 * BUNDLE_MAX_LIGHTS];  // per warp and light: one cone, or two after a split
+    __shared__ unsigned int s_occ[ST_RPT][ST_THREADS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const DeviceScene& s = p.s;
-    // per-light cones need the (ray, light) form of the queries and at most 8 lights; otherwise nothing is culled
-    const int n_cones = (MODE != 1 && p.cull_bundles && p.sq_src && s.rl.n_light <= BUNDLE_MAX_LIGHTS) ? s.rl.n_light : 0;
     const int n_tiles = s.n_tri_padded / ST_TILE;
     const int side_bytes = (int)(sizeof(QuadRec) * s.n_quad + sizeof(PlaneRec) * s.n_plane);
     const bool side_in_smem = side_bytes <= ST_SIDE_MAX;
+    const bool track = s.rl.n_surf < OCC_ORDER_LIMIT;      // (beyond: every query with >= 3 occluders is redone)
 
     if (tid == 0) {
         for (int i = 0; i < ST_STAGES; ++i) mbar_init(&sm.full[i], 1);
@@ -306,65 +225,43 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
 
     const int n_blocks = (p.n_queries + ST_BLOCK_RAYS - 1) / ST_BLOCK_RAYS;
     uint32_t phase_bits = 0;
-    unsigned long long tests_tri = 0, tests_side_q = 0, tests_side_p = 0, exec_rays = 0;
+    unsigned long long tests_tri = 0, tests_side_q = 0, tests_side_p = 0, fixups = 0;
 
     for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
         V3 o[ST_RPT], d[ST_RPT];
         float dist[ST_RPT], tlim[ST_RPT], fr[ST_RPT], fg[ST_RPT], fb[ST_RPT];
-        int slot[ST_RPT], lid[ST_RPT];
+        int slot[ST_RPT];
         int n_valid = 0;
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) {
             const int i = blk * ST_BLOCK_RAYS + warp * (32 * ST_RPT) + r * 32 + lane;   // a warp = 128 consecutive queries
             const bool valid = i < p.n_queries;
             slot[r] = valid ? i : -1;
-            lid[r] = (valid && n_cones) ? p.sq_src[i].y : -1;
             n_valid += valid ? 1 : 0;
             o[r] = d[r] = mk3(0.f, 0.f, 0.f); dist[r] = 0.f;
             if (valid) shadow_query<(MODE != 2)>(p, i, o[r], d[r], dist[r]);
             tlim[r] = fmaf(dist[r], CULL_TREL, CULL_TABS);
             fr[r] = fg[r] = fb[r] = 1.0f;
             if (!valid) { fr[r] = fg[r] = fb[r] = 0.0f; }        // counts as finished
+            s_occ[r][tid] = 0u;
         }
         bool warp_done = false;
         float dmax = 0.f;                             // largest |direction component| of this thread's queries (filter margins)
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) dmax = fmaxf(dmax, max_abs3(d[r]));
-        bool can_cull = n_cones > 0;
-        for (int l = 0; l < n_cones; ++l) {          // the warp's cone(s) per light (uniform values, kept in shared memory)
-            const V3 L = f4_xyz(s.light[l].l0);
-            bool in[ST_RPT];
-            #pragma unroll
-            for (int r = 0; r < ST_RPT; ++r) in[r] = lid[r] == l;
-            Bundle b = bundle_of_light(L, d, dist, in), b2;
-            b2 = b; b2.state = 0;
-            if (b.state == 2 || (b.state == 1 && b.sin_t > BUNDLE_SPLIT_SIN)) {
-                // the hit points of a warp often lie on two surfaces at different depths (a silhouette runs through
-                // its 32 pixels): two cones around the two most distant directions are far tighter than one
-                V3 nd[ST_RPT];
-                float key[ST_RPT];
-                #pragma unroll
-                for (int r = 0; r < ST_RPT; ++r) { nd[r] = mk3(-d[r].x, -d[r].y, -d[r].z); key[r] = 1.0f; }
-                const V3 seed = warp_pick(nd, key, in);
-                #pragma unroll
-                for (int r = 0; r < ST_RPT; ++r) key[r] = fmaxf(1.0f - dot3<false>(nd[r], seed), 0.f);
-                const V3 pa = warp_pick(nd, key, in);
-                #pragma unroll
-                for (int r = 0; r < ST_RPT; ++r) key[r] = fmaxf(1.0f - dot3<false>(nd[r], pa), 0.f);
-                const V3 pb = warp_pick(nd, key, in);
-                bool in_a[ST_RPT], in_b[ST_RPT];
-                #pragma unroll
-                for (int r = 0; r < ST_RPT; ++r) {
-                    const bool near_a = dot3<false>(nd[r], pa) >= dot3<false>(nd[r], pb);
-                    in_a[r] = in[r] && near_a; in_b[r] = in[r] && !near_a;
-                }
-                const Bundle ba = bundle_of_light(L, d, dist, in_a), bb = bundle_of_light(L, d, dist, in_b);
-                if (ba.state != 2 && bb.state != 2) { b = ba; b2 = bb; }
-            }
-            if (lane == 0) { cones[warp][2 * l] = b; cones[warp][2 * l + 1] = b2; }
-            can_cull = can_cull && b.state != 2;     // one light without a usable cone: every triangle has to be tested
-        }
-        __syncwarp();
+        auto occluder = [&](int r, int ord, int mat) {
+            const float4 m0 = s.mat[mat].m0;
+            const float kt = s.mat[mat].m2.x;
+            fr[r] = __fmul_rn(fr[r], __fmul_rn(m0.x, kt));
+            fg[r] = __fmul_rn(fg[r], __fmul_rn(m0.y, kt));
+            fb[r] = __fmul_rn(fb[r], __fmul_rn(m0.z, kt));
+            unsigned int st = s_occ[r][tid];
+            const unsigned int key = (unsigned int)(ord + 1);
+            unsigned int flags = st & 7u;
+            if (!track || key < (st >> 3)) flags |= 4u;
+            if ((flags & 3u) < 3u) ++flags;
+            s_occ[r][tid] = (max(st >> 3, track ? key : 0u) << 3) | flags;
+        };
 
         if (tid == 0 && n_tiles > 0) {
             mbar_arrive_expect_tx(&sm.full[0], (uint32_t)sizeof(TriRec) * ST_TILE);
@@ -380,12 +277,6 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
             mbar_wait(&sm.full[st], (phase_bits >> st) & 1u);
             phase_bits ^= (1u << st);
             const TriRec* __restrict__ tile = sm.tile[st];
-            if (n_cones) {                           // bounding sphere of triangle `tid`, once per CTA and tile
-                V3 c; float rad, w;
-                triangle_sphere(f4_xyz(tile[tid].a), f4_xyz(tile[tid].b), f4_xyz(tile[tid].c), c, rad, w);
-                sm.sphere[tid] = make_float4(c.x, c.y, c.z, rad); sm.sphere_w[tid] = w;
-                __syncthreads();
-            }
 
             if (!warp_done) {
                 const int real = min(ST_TILE, s.n_tri - t * ST_TILE);
@@ -398,11 +289,12 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
                         #pragma unroll
                         for (int r = 0; r < ST_RPT; ++r) {
                             const float tt = triangle_t<true>(o[r], d[r], p0, e1, e2);
-                            if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(rb.w), fr[r], fg[r], fb[r]);
+                            if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) occluder(r, __float_as_int(ra.w), __float_as_int(rb.w));
                         }
                     }
                 } else {
-                    auto test_triangle = [&](int j) {
+                    #pragma unroll 2
+                    for (int j = 0; j < ST_TILE; ++j) {
                         const float4 ra = tile[j].a, rb = tile[j].b, rc = tile[j].c;
                         const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
                         const TriMargins mg = tri_margins(e1, e2, dmax);
@@ -418,32 +310,9 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
                             for (int r = 0; r < ST_RPT; ++r) {
                                 if (cand[r] && slot[r] >= 0) {
                                     const float tt = triangle_survivor<MODE>(o[r], d[r], p0, e1, e2, tlim[r], mg);
-                                    if (tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(rb.w), fr[r], fg[r], fb[r]);
+                                    if (tt > RT_EPS && tt < dist[r]) occluder(r, __float_as_int(ra.w), __float_as_int(rb.w));
                                 }
                             }
-                        }
-                    };
-                    if (!can_cull) {                 // the plain scan of the tile
-                        exec_rays += (unsigned long long)n_valid * (unsigned long long)real;
-                        #pragma unroll 2
-                        for (int j = 0; j < ST_TILE; ++j) test_triangle(j);
-                    } else
-                    for (int j0 = 0; j0 < ST_TILE; j0 += 32) {
-                        unsigned int keep_mask;
-                        {                            // lane j looks at triangle j0 + j for the whole warp
-                            const float4 sph = sm.sphere[j0 + lane];
-                            const float w = sm.sphere_w[j0 + lane];
-                            bool keep = false;
-                            for (int l = 0; l < 2 * n_cones; ++l) {
-                                const Bundle& b = cones[warp][l];
-                                if (b.state == 1 && !light_cone_culls(b, sph, w)) keep = true;
-                            }
-                            keep_mask = __ballot_sync(FULL_MASK, keep && w > 0.f);
-                        }
-                        exec_rays += (unsigned long long)(__popc(keep_mask) * n_valid);
-                        while (keep_mask) {
-                            test_triangle(j0 + __ffs((int)keep_mask) - 1);
-                            keep_mask &= keep_mask - 1u;
                         }
                     }
                 }
@@ -465,22 +334,30 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
                 for (int r = 0; r < ST_RPT; ++r) {
                     bool lin;
                     const float tt = MODE == 2 ? quadric_t<false>(o[r], d[r], Q, lin) : quadric_t<true>(o[r], d[r], Q, lin);
-                    if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, __float_as_int(q1.w), fr[r], fg[r], fb[r]);
+                    if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) occluder(r, __float_as_int(q0.w), __float_as_int(q1.w));
                 }
             }
             for (int q = 0; q < s.n_plane; ++q) {
                 const float4 nc = planes[q].nc;
-                const int m = planes[q].material;
+                const int m = planes[q].material, ord = planes[q].order;
                 #pragma unroll
                 for (int r = 0; r < ST_RPT; ++r) {
                     const float tt = MODE == 2 ? plane_t<false>(o[r], d[r], f4_xyz(nc), nc.w) : plane_t<true>(o[r], d[r], f4_xyz(nc), nc.w);
-                    if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) filter_mul<MODE>(s.mat, m, fr[r], fg[r], fb[r]);
+                    if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) occluder(r, ord, m);
                 }
             }
         }
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r)
-            if (slot[r] >= 0) p.filter[p.sq_dst ? p.sq_dst[slot[r]] : slot[r]] = make_float4(fr[r], fg[r], fb[r], 0.f);
+            if (slot[r] >= 0) {
+                p.filter[p.sq_dst ? p.sq_dst[slot[r]] : slot[r]] = make_float4(fr[r], fg[r], fb[r], 0.f);
+                const unsigned int st = s_occ[r][tid];
+                if ((st & 4u) && (st & 3u) >= 3u && (fr[r] != 0.f || fg[r] != 0.f || fb[r] != 0.f) && p.fix_count) {
+                    const unsigned int k = atomicAdd(p.fix_count, 1u);
+                    if ((int)k < p.fix_cap) p.fix_list[k] = slot[r];
+                    ++fixups;
+                }
+            }
     }
 
     // ---- statistics: tests entered (per thread -> warp -> one atomic per warp) ----------------
@@ -488,14 +365,14 @@ k_trace_shadow(const __grid_constant__ ShadowParams p)
         tests_tri += __shfl_xor_sync(FULL_MASK, tests_tri, off);
         tests_side_q += __shfl_xor_sync(FULL_MASK, tests_side_q, off);
         tests_side_p += __shfl_xor_sync(FULL_MASK, tests_side_p, off);
-        exec_rays += __shfl_xor_sync(FULL_MASK, exec_rays, off);
+        fixups += __shfl_xor_sync(FULL_MASK, fixups, off);
     }
     if ((tid & 31) == 0) {
         unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
-        if (tests_tri) atomicAdd(&st[ST_TEST_TRI_SHADOW], tests_tri);
-        if (exec_rays) atomicAdd(&st[ST_TEST_TRI_EXEC], exec_rays);
+        if (tests_tri) { atomicAdd(&st[ST_TEST_TRI_SHADOW], tests_tri); atomicAdd(&st[ST_TEST_TRI_EXEC], tests_tri); }
         if (tests_side_q) atomicAdd(&st[ST_TEST_QUAD], tests_side_q);
         if (tests_side_p) atomicAdd(&st[ST_TEST_PLANE], tests_side_p);
+        if (fixups) atomicAdd(&st[ST_SHADOW_FIXUP], fixups);
     }
 }
 
@@ -648,12 +525,16 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
                 const int k = (int)(wb.w + s_loff[l * 8 + warp] + __popc(m & below));
                 p.sq_src[k] = make_int2(i, l);
                 p.sq_dst[k] = q++;
+                if (p.sq_key) { p.sq_key[k] = ((unsigned int)l << 27) | (morton30(P.x, P.y, P.z, p.key_lo[0], p.key_lo[1], p.key_lo[2], p.key_inv) >> 3); p.sq_idx[k] = k; }
             }
         }
     } else if (hit)
         for (int l = 0; l < s.rl.n_light; ++l) {
             const V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
-            if (dot3<E>(Ld, N) > 0.f) p.sq_src[q++] = make_int2(i, l);    // direction and distance: shadow_query()
+            if (dot3<E>(Ld, N) > 0.f) {                                   // direction and distance: shadow_query()
+                if (p.sq_key) { p.sq_key[q] = ((unsigned int)l << 27) | (morton30(P.x, P.y, P.z, p.key_lo[0], p.key_lo[1], p.key_lo[2], p.key_inv) >> 3); p.sq_idx[q] = q; }
+                p.sq_src[q++] = make_int2(i, l);
+            }
         }
     // ---- children --------------------------------------------------------------------------------
     if (m_any) {
@@ -665,6 +546,7 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
             const V3 rd = reflect3<E>(d, N);
             p.out_od0[s_refl] = make_float4(P.x, P.y, P.z, e_refl);
             p.out_od1[s_refl] = make_float4(rd.x, rd.y, rd.z, 0.0f);
+            if (p.child_key) { p.child_key[s_refl] = morton30(P.x, P.y, P.z, p.key_lo[0], p.key_lo[1], p.key_lo[2], p.key_inv); p.child_idx[s_refl] = s_refl; }
         }
         if (want_refr) {
             s_refr = (int)(cbase + n_refl + __popc(m_refr & below));
@@ -674,6 +556,7 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
             const V3 rd = refract3<E>(d, n2, ratio);
             p.out_od0[s_refr] = make_float4(P.x, P.y, P.z, e_refr);
             p.out_od1[s_refr] = make_float4(rd.x, rd.y, rd.z, nior);
+            if (p.child_key) { p.child_key[s_refr] = morton30(P.x, P.y, P.z, p.key_lo[0], p.key_lo[1], p.key_lo[2], p.key_inv); p.child_idx[s_refr] = s_refr; }
         }
         if (want_refl || want_refr) p.links[lbase + __popc(m_any & below)] = make_int4(i, s_refl, s_refr, mat);
     }
@@ -813,8 +696,7 @@ cudaError_t launch_query_unpack_filter(int n, const float4* filter, float* out3,
 template <int MODE, bool PRIMARY>
 static cudaError_t launch_nearest_t(const TraceParams& p, int blocks, cudaStream_t st)
 {
-    if (!PRIMARY && MODE != 1 && p.cull_bundles > 1) k_trace_nearest<MODE, false, (MODE != 1)><<<blocks, ST_THREADS, 0, st>>>(p);
-    else k_trace_nearest<MODE, PRIMARY, false><<<blocks, ST_THREADS, 0, st>>>(p);
+    k_trace_nearest<MODE, PRIMARY><<<blocks, ST_THREADS, 0, st>>>(p);
     return cudaGetLastError();
 }
 

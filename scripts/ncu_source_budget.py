@@ -33,7 +33,7 @@ def main():
         if m:
             pending.append((os.path.basename(m.group(1)), int(m.group(2))))
             continue
-        m = re.match(r"\s+/\*([0-9a-f]{4})\*/\s+(.*?);", line)
+        m = re.match(r"\s+/\*([0-9a-f]{4,6})\*/\s+(.*?);", line)
         if m:
             if pending:
                 chain, pending = pending, []
