@@ -468,6 +468,9 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
         bool zero = false;
         int l_ord[BVH_SHADOW_LIST], l_mat[BVH_SHADOW_LIST];
         int n_list = 0;
+        // the product below is taken over the tree's occluders in insertion order, then the side list's: a query with
+        // three or more factors (two commute exactly) that were not met in increasing order is redone by k_shadow_fixup
+        bool ooo = false;
         if (s.bvh_n_prims > 0) {
             const TriRec* __restrict__ tri = s.bvh_tri;
             bvh_traverse<false>(s, o, d, dist, [&](int first, int count, float limit) -> float {
@@ -489,7 +492,7 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
                         const float cr = __fmul_rn(m0.x, kt), cg = __fmul_rn(m0.y, kt), cb = __fmul_rn(m0.z, kt);
                         if (cr == 0.f && cg == 0.f && cb == 0.f) { zero = true; return -1.0f; }
                         if (n_list < BVH_SHADOW_LIST) { l_ord[n_list] = __float_as_int(ra.w); l_mat[n_list] = m; ++n_list; }
-                        else { fr = __fmul_rn(fr, cr); fg = __fmul_rn(fg, cg); fb = __fmul_rn(fb, cb); }   // > 8 transparent layers: unordered
+                        else { fr = __fmul_rn(fr, cr); fg = __fmul_rn(fg, cg); fb = __fmul_rn(fb, cb); ooo = true; }   // > 8 transparent layers: redone in order (fix-up list)
                     }
                 }
                 return limit;
@@ -509,6 +512,7 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
                 fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
             }
         }
+        int n_occ = n_list + (ooo ? 1 : 0), max_ord = n_list ? l_ord[n_list - 1] : -1;
         if (!(fr == 0.f && fg == 0.f && fb == 0.f)) {
             n_side_q += (unsigned)s.bvh_n_quad; n_side_p = (unsigned)s.n_plane;
             for (int q = 0; q < s.bvh_n_quad; ++q) {
@@ -517,7 +521,8 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
                 bool lin;
                 const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
                 if (tt > RT_EPS && tt < dist) {
-                    const int m = __float_as_int(q1.w);
+                    const int m = __float_as_int(q1.w), ord = __float_as_int(q0.w);
+                    ooo = ooo || ord < max_ord; max_ord = max(max_ord, ord); ++n_occ;
                     const float4 m0 = __ldg(&s.mat[m].m0);
                     const float kt = __ldg(&s.mat[m].m2).x;
                     fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
@@ -527,7 +532,8 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
                 const float4 nc = __ldg(&s.plane[q].nc);
                 const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
                 if (tt > RT_EPS && tt < dist) {
-                    const int m = s.plane[q].material;
+                    const int m = s.plane[q].material, ord = s.plane[q].order;
+                    ooo = ooo || ord < max_ord; max_ord = max(max_ord, ord); ++n_occ;
                     const float4 m0 = __ldg(&s.mat[m].m0);
                     const float kt = __ldg(&s.mat[m].m2).x;
                     fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
@@ -535,6 +541,11 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
             }
         }
         p.filter[i] = make_float4(fr, fg, fb, 0.f);
+        if (ooo && n_occ >= 3 && !(fr == 0.f && fg == 0.f && fb == 0.f) && p.fix_count) {
+            const unsigned int k = atomicAdd(p.fix_count, 1u);
+            if ((int)k < p.fix_cap) p.fix_list[k] = i;
+            atomicAdd(&p.stats[(size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + ST_SHADOW_FIXUP], 1ull);
+        }
     }
     n_nodes = __reduce_add_sync(FULL_MASK, n_nodes);
     n_tests = __reduce_add_sync(FULL_MASK, n_tests);

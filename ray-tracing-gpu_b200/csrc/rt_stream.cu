@@ -276,21 +276,20 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 sp.sq_dst = sa.sq_dst;
                 sp.by_light = shadow_by_light ? 1 : 0;
                 sp.filter = sb->filter.as<float4>(); sp.stats = sa.stats; sp.mode = mode; sp.cull_bundles = bundle_cull_enabled();
-                if (use_bvh) SCU(launch_bvh_shadow(sp, c->stream));
-                else {
-                    // tiled / culled scan: queries whose product order matters go on a list and are redone in insertion order
+                {
+                    // queries whose product order matters go on a list and are redone in insertion order (every path)
                     if ((e = sb->fix.ensure(sizeof(int) * (size_t)n_sq)) != cudaSuccess) return set_cuda_error(c, e, "fix-up list");
                     unsigned* tk = sb->tasks.as<unsigned>() + 3 * level;
                     sp.fix_count = tk + 2; sp.fix_list = sb->fix.as<int>(); sp.fix_cap = n_sq;
                     CullShadowParams csp;
                     csp.s = sp; csp.cs = cull; csp.task_counter = tk + 1;
                     csp.perm = queries_sorted ? sb->qperm.as<int>() : nullptr;
-                    if (cullscan && group_queries) SCU(launch_cull_shadow(csp, c->sm_count, c->stream));
-                    else                           SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+                    if (use_bvh)                        SCU(launch_bvh_shadow(sp, c->stream));
+                    else if (cullscan && group_queries) SCU(launch_cull_shadow(csp, c->sm_count, c->stream));
+                    else                                SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
                     SCU(launch_shadow_fixup(csp, c->sm_count, c->stream));     // (reads the count itself; nearly always 0)
-                    ++*launches;
                 }
-                ++*launches;
+                *launches += 2;
             }
             SCU(cudaEventRecord(E[4], c->stream));
             // ---- shade B -------------------------------------------------------------------------
@@ -403,12 +402,12 @@ int stream_query_shadow(rtb200_ctx* c, int n, uint32_t flags)
     memset(&sp, 0, sizeof sp);
     sp.s = c->ds; sp.sq0 = sb->sq0.as<float4>(); sp.sq1 = sb->sq1.as<float4>(); sp.n_queries = n;
     sp.filter = sb->filter.as<float4>(); sp.stats = c->stats.as<unsigned long long>(); sp.mode = mode;
-    if (flags & RTB200_F_USE_BVH) SCU(launch_bvh_shadow(sp, c->stream));
-    else {
+    {
         if ((e = sb->fix.ensure(sizeof(int) * (size_t)n)) != cudaSuccess || (e = sb->tasks.ensure(64)) != cudaSuccess) return set_cuda_error(c, e, "fix-up list");
         SCU(cudaMemsetAsync(sb->tasks.p, 0, 12, c->stream));
         sp.fix_count = sb->tasks.as<unsigned>() + 2; sp.fix_list = sb->fix.as<int>(); sp.fix_cap = n;
-        SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
+        if (flags & RTB200_F_USE_BVH) SCU(launch_bvh_shadow(sp, c->stream));
+        else                          SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
         CullShadowParams csp;
         memset(&csp, 0, sizeof csp);
         csp.s = sp;

@@ -70,10 +70,8 @@ def test_soup_ray_queries(rt, renderer, port, synth):
     lights = np.tile(ps["lights"][0, 0:3], (n, 1)).astype(np.float32)
     filt = renderer.trace_shadow(pts, lights, flags=rt.F_FORCE_STREAM)
     wf = port.shadow(ps, pts, lights, threads=port.max_threads)
-    # the product is taken type by type (triangles, quadrics, planes) instead of in insertion
-    # order: identical when at most one factor is not 0/1, otherwise within an ulp or two
-    assert np.allclose(filt, wf, rtol=3e-7, atol=0)
-    assert np.array_equal(filt == 0, wf == 0)
+    # the product is the reference's, in insertion order (Scene.cpp:1856): queries that met >= 3 occluders out of order are redone
+    assert bits_equal(filt, wf)
 
 
 def test_soup_fused_mode_within_tolerance(rt, renderer, port, synth):
@@ -251,3 +249,83 @@ def test_bundle_culling_rays_at_triangle_borders(rt, renderer, synth):
         os.environ["RTB200_NO_BUNDLE_CULL"] = "0"
     print(f"border rays: {n_hit} hits of {2 * T * per}, {n_filter} answers differ from the exact mode")
     assert n_hit > T * per and n_filter == 0
+
+
+def _layered_scene(rt, synth, rng, n_extra=400):
+    """Transparent layers of ALL THREE surface types between the ground and the light, inserted in shuffled order:
+    big horizontal triangles, flat ellipsoids and horizontal planes.  A shadow ray from below crosses up to nine of them,
+    so the filter product has many factors and Scene.cpp:1856 fixes their order (insertion order)."""
+    F = np.float32
+    layers = []                                   # (kind, geometry)
+    for i in range(3):
+        y = 12.0 * (i + 1)
+        layers.append(("tri", [-600, y, -600, 600, y, -600, 0, y, 800]))
+    for i in range(3):
+        c, a = np.array([0.0, 50.0 + 14.0 * i, 0.0]), np.array([500.0, 3.0, 500.0])
+        q = 1.0 / (a * a)
+        layers.append(("quad", [q[0], q[1], q[2], 0, 0, 0, *(-2.0 * c * q), float(np.sum(c * c * q) - 1.0)]))
+    for i in range(3):
+        layers.append(("plane", [0.0, 1.0, 0.0, -(100.0 + 9.0 * i)]))       # y = 100, 109, 118
+    order = rng.permutation(len(layers))
+    extra = synth.soup(n_extra, 0, 1, seed=3)["tri_points"].copy()
+    extra[:, 1::3] += 600.0                                                # a cloud far above everything (fills the tiles / the tree)
+    tri, tri_o, tri_m, quad, quad_o, quad_m, pl, pl_o, pl_m = [], [], [], [], [], [], [], [], []
+    for slot, li in enumerate(order):
+        kind, g = layers[li]
+        if kind == "tri":
+            tri.append(g); tri_o.append(slot); tri_m.append(li)
+        elif kind == "quad":
+            quad.append(g); quad_o.append(slot); quad_m.append(li)
+        else:
+            pl.append(g); pl_o.append(slot); pl_m.append(li)
+    n_l = len(layers)
+    ground_slot = n_l
+    pl.append([0.0, 1.0, 0.0, 45.0]); pl_o.append(ground_slot); pl_m.append(n_l)
+    tri = np.concatenate([np.asarray(tri, F).reshape(-1, 9), extra]).astype(F)
+    tri_o += list(range(n_l + 1, n_l + 1 + len(extra)))
+    tri_m += [n_l] * len(extra)
+    mats = np.zeros((n_l + 1, 10), F)
+    mats[:, 0:3] = rng.uniform(0.55, 0.99, (n_l + 1, 3))
+    mats[:, 3], mats[:, 4] = 0.2, 0.8
+    mats[:n_l, 8], mats[:n_l, 9] = rng.uniform(0.8, 0.99, n_l), 1.0       # transparent, straight through (ior 1)
+    arrays = {"tri_points": tri, "tri_normal": synth.face_normals(tri), "tri_material": np.asarray(tri_m, np.int32),
+              "tri_order": np.asarray(tri_o, np.int32),
+              "quad_coef": np.asarray(quad, F), "quad_material": np.asarray(quad_m, np.int32), "quad_order": np.asarray(quad_o, np.int32),
+              "plane_coef": np.asarray(pl, F), "plane_material": np.asarray(pl_m, np.int32), "plane_order": np.asarray(pl_o, np.int32),
+              "materials": mats, "lights": np.array([[0, 400, 0, 1, 1, 1, 1.0], [150, 380, -80, 1, 1, 1, 0.5]], F)}
+    base = synth.soup(10, 0, 1, seed=1)
+    frame = dict(base.frame)
+    return rt.PackedScene(arrays, frame)
+
+
+def test_shadow_product_in_insertion_order(rt, renderer, port, synth):
+    """Scene.cpp:1850-1858 multiplies the filter in m_Surfaces order.  Nine transparent layers of mixed types in shuffled
+    insertion order: every path (plain tiled scan, culled scan inside a frame, LBVH) must return the oracle's bits;
+    the paths that do not meet the occluders in insertion order redo such queries (rtb200_stats.shadow_fixups)."""
+    rng = np.random.default_rng(21)
+    ps = _layered_scene(rt, synth, rng)
+    renderer.set_scene(ps)
+    renderer.build_bvh()
+    n = 6000
+    pts = np.stack([rng.uniform(-120, 120, n), np.full(n, 1.0), rng.uniform(-120, 120, n)], axis=1).astype(np.float32)
+    lights = np.tile(ps["lights"][0, 0:3], (n, 1)).astype(np.float32)
+    want = port.shadow(ps, pts, lights, threads=port.max_threads)
+    assert ((want > 0) & (want < 0.9)).all()                       # every query is filtered by several layers
+    for flags in (rt.F_FORCE_STREAM, rt.F_FORCE_STREAM | rt.F_EXACT_FP, rt.F_USE_BVH, rt.F_FORCE_RESIDENT):
+        got = renderer.trace_shadow(pts, lights, flags=flags)
+        assert bits_equal(got, want), flags
+    # inside a frame: the camera looks down at the ground through all the layers
+    F = np.float32
+    hostbind = import_module("rtb200.hostbind")
+    frame = hostbind.camera_frame((0.0, 300.0, 10.0), (0.0, 0.0, 0.0), (0.0, 0.0, -1.0))
+    frame["background"] = np.zeros(3, F)
+    ps2 = rt.PackedScene(ps.a, frame)
+    renderer.set_scene(ps2)
+    renderer.build_bvh()
+    fr = rt.make_frame(ps2.frame, 192, 128, max_bounces=2, flags=rt.F_FORCE_STREAM)
+    wantf, _ = port.render(ps2, fr, threads=port.max_threads)
+    for flags in (rt.F_FORCE_STREAM, rt.F_USE_BVH, rt.F_FORCE_RESIDENT):
+        gotf, _, st = renderer.render(rt.make_frame(ps2.frame, 192, 128, max_bounces=2, flags=flags))
+        assert bits_equal(gotf, wantf), flags
+        if flags != rt.F_FORCE_RESIDENT:
+            assert st.shadow_fixups > 0
