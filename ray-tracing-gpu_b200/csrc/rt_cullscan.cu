@@ -54,6 +54,9 @@ RT_DEV int cs_level_offset(int n3, int level)
 struct CsWarpSmem {
     Bundle cones[CS_MAX_CONES];
     int    queue[CS_QCAP];
+    TriRec stage[32];              // the next 32 queued triangles, fetched by 32 lanes at once (one L2 latency per 32
+                                   // triangles instead of one per triangle: a lone warp scanning everything -- a bundle
+                                   // no cone fits -- was bound by exactly that latency)
 };
 
 template <bool LIGHT>
@@ -222,7 +225,8 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     CsWarpSmem& ws = sm[warp];
     const int tiles_x = (p.f.LW + 15) >> 4;
-    const int n_tasks = PRIMARY ? tiles_x * ((p.chunk_rows + 7) >> 3) : (p.n_rays + 127) >> 7;
+    const int shift = PRIMARY ? 7 : cp.task_shift, rpt = 1 << (shift - 5);       // rays per lane in this launch: 4 or 1
+    const int n_tasks = PRIMARY ? tiles_x * ((p.chunk_rows + 7) >> 3) : (p.n_rays + (1 << shift) - 1) >> shift;
     unsigned long long exec_rays = 0;
 
     for (;;) {
@@ -248,8 +252,8 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 slot[r] = valid ? cy * p.f.LW + lx : -1;
                 primary_ray<(MODE != 2)>(p.f, valid ? lx : 0, valid ? global_lattice_row(p.f, ly) : 0, o[r], d[r]);
             } else {
-                const int i0 = (task << 7) + r * 32 + lane;
-                valid = i0 < p.n_rays;
+                const int i0 = (task << shift) + r * 32 + lane;
+                valid = r < rpt && i0 < p.n_rays;
                 const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
                 slot[r] = valid ? i : -1;
                 const float4 a = valid ? p.in_od0[i] : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -302,16 +306,18 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 finished = cs_fill<false>(cs, ws, n_c, keep_all, lane, wk);
                 __syncwarp();
                 const int qn = wk.qn;
-                if (qn > 0) {
-                    const TriRec* t0 = cs.tri + ws.queue[0];
-                    float4 ra = __ldg(&t0->a), rb = __ldg(&t0->b), rc = __ldg(&t0->c);
-                    #pragma unroll 1
-                    for (int e = 0; e < qn; ++e) {
-                        const TriRec* tn = cs.tri + ws.queue[min(e + 1, qn - 1)];
-                        const float4 na = __ldg(&tn->a), nb = __ldg(&tn->b), nc = __ldg(&tn->c);
-                        test_triangle(ra, rb, rc);
-                        ra = na; rb = nb; rc = nc;
+                #pragma unroll 1
+                for (int e0 = 0; e0 < qn; e0 += 32) {
+                    const int cnt = min(32, qn - e0);
+                    if (lane < cnt) {
+                        const TriRec* t = cs.tri + ws.queue[e0 + lane];
+                        const float4 a = __ldg(&t->a), b = __ldg(&t->b), c = __ldg(&t->c);
+                        ws.stage[lane].a = a; ws.stage[lane].b = b; ws.stage[lane].c = c;
                     }
+                    __syncwarp();
+                    #pragma unroll 1
+                    for (int e = 0; e < cnt; ++e) test_triangle(ws.stage[e].a, ws.stage[e].b, ws.stage[e].c);
+                    __syncwarp();
                 }
                 exec_rays += (unsigned long long)qn * (unsigned long long)n_valid;
                 wk.qn = 0;
@@ -377,7 +383,8 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     CsWarpSmem& ws = sm[warp];
     const int n_lights = s.rl.n_light;
-    const int n_tasks = (p.n_queries + 127) >> 7;
+    const int shift = cp.task_shift, rpt = 1 << (shift - 5);
+    const int n_tasks = (p.n_queries + (1 << shift) - 1) >> shift;
     unsigned long long tests_tri = 0, tests_side_q = 0, tests_side_p = 0, exec_rays = 0, fixups = 0;
 
     for (;;) {
@@ -393,8 +400,8 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
         unsigned int light_bits = 0;
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) {
-            const int i0 = (task << 7) + r * 32 + lane;
-            const bool valid = i0 < p.n_queries;
+            const int i0 = (task << shift) + r * 32 + lane;
+            const bool valid = r < rpt && i0 < p.n_queries;
             const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
             slot[r] = valid ? i : -1;
             lid[r] = valid ? p.sq_src[i].y : -1;
@@ -494,16 +501,18 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
                 finished = cs_fill<true>(cs, ws, n_c, keep_all, lane, wk);
                 __syncwarp();
                 const int qn = wk.qn;
-                if (qn > 0) {
-                    const TriRec* t0 = cs.tri + ws.queue[0];
-                    float4 ra = __ldg(&t0->a), rb = __ldg(&t0->b), rc = __ldg(&t0->c);
-                    #pragma unroll 1
-                    for (int e = 0; e < qn; ++e) {
-                        const TriRec* tn = cs.tri + ws.queue[min(e + 1, qn - 1)];
-                        const float4 na = __ldg(&tn->a), nb = __ldg(&tn->b), nc = __ldg(&tn->c);
-                        test_triangle(ra, rb, rc);
-                        ra = na; rb = nb; rc = nc;
+                #pragma unroll 1
+                for (int e0 = 0; e0 < qn; e0 += 32) {
+                    const int cnt = min(32, qn - e0);
+                    if (lane < cnt) {
+                        const TriRec* t = cs.tri + ws.queue[e0 + lane];
+                        const float4 a = __ldg(&t->a), b = __ldg(&t->b), c = __ldg(&t->c);
+                        ws.stage[lane].a = a; ws.stage[lane].b = b; ws.stage[lane].c = c;
                     }
+                    __syncwarp();
+                    #pragma unroll 1
+                    for (int e = 0; e < cnt; ++e) test_triangle(ws.stage[e].a, ws.stage[e].b, ws.stage[e].c);
+                    __syncwarp();
                 }
                 exec_rays += (unsigned long long)qn * (unsigned long long)n_valid;
                 wk.qn = 0;
@@ -641,7 +650,8 @@ static int cs_grid(int n_tasks, int sm_count)
 cudaError_t launch_cull_nearest(const CullTraceParams& p, int sm_count, cudaStream_t st)
 {
     const int tiles_x = (p.t.f.LW + 15) / 16;
-    const int n_tasks = p.t.primary ? tiles_x * ((p.t.chunk_rows + 7) / 8) : (p.t.n_rays + 127) / 128;
+    const int per = 1 << p.task_shift;
+    const int n_tasks = p.t.primary ? tiles_x * ((p.t.chunk_rows + 7) / 8) : (p.t.n_rays + per - 1) / per;
     if (n_tasks <= 0) return cudaSuccess;
     const int blocks = cs_grid(n_tasks, sm_count);
     if (p.t.primary) {
@@ -656,7 +666,8 @@ cudaError_t launch_cull_nearest(const CullTraceParams& p, int sm_count, cudaStre
 
 cudaError_t launch_cull_shadow(const CullShadowParams& p, int sm_count, cudaStream_t st)
 {
-    const int n_tasks = (p.s.n_queries + 127) / 128;
+    const int per = 1 << p.task_shift;
+    const int n_tasks = (p.s.n_queries + per - 1) / per;
     if (n_tasks <= 0) return cudaSuccess;
     const int blocks = cs_grid(n_tasks, sm_count);
     if (p.s.mode == 2) k_cull_shadow<2><<<blocks, CS_THREADS, 0, st>>>(p);

@@ -25,6 +25,8 @@ struct CullTraceParams {
     TraceParams t;
     CullScene   cs;
     unsigned int* task_counter;      // zeroed before the launch: warps take tasks of 128 rays from it
+    int           task_shift;        // log2 of the rays per task: 7 (four per lane), or 5 (one per lane) for levels with few
+                                     // rays -- more tasks than warps, tighter cones, and a bundle nothing can cull costs 1/4
     const int*    perm;              // null, or: the i-th ray of the launch is queue entry perm[i] (rays sorted by the
                                      // surface they leave, see ShadeAParams::child_key)
 };
@@ -33,6 +35,7 @@ struct CullShadowParams {
     ShadowParams s;
     CullScene    cs;
     unsigned int* task_counter;
+    int           task_shift;        // as in CullTraceParams
     const int*    perm;              // null, or: the i-th query of the launch is queue entry perm[i] (sorted by light, place)
 };                                   // (fix-up list: ShadowParams::fix_list / fix_count / fix_cap)
 

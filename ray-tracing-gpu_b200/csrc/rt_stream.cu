@@ -118,6 +118,9 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     if (cull.key_inv <= 0.f) sort_secondary = false;
     int light_bits = 0;
     while ((1 << light_bits) < std::max(c->ds.rl.n_light, 1)) ++light_bits;
+    // a level with fewer rays than this is traced one ray per lane (tasks of 32): see CullTraceParams::task_shift
+    int small_level = c->sm_count * 16 * 128 * 3;
+    if (const char* e = getenv("RTB200_SMALL_LEVEL")) small_level = atoi(e);
     bool rays_sorted = false;                   // the rays of the level about to be traced have a permutation in sb->cperm
     const int k = fp.k;
     const int local_LH = local_rows * k;
@@ -201,6 +204,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 CullTraceParams ctp;
                 ctp.t = tp; ctp.cs = cull; ctp.task_counter = d_tasks + 3 * level;
                 ctp.perm = (level > 0 && rays_sorted) ? sb->cperm.as<int>() : nullptr;
+                ctp.task_shift = (level > 0 && n_in < small_level) ? 5 : 7;
                 SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
             }
             else         SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
@@ -284,6 +288,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                     CullShadowParams csp;
                     csp.s = sp; csp.cs = cull; csp.task_counter = tk + 1;
                     csp.perm = queries_sorted ? sb->qperm.as<int>() : nullptr;
+                    csp.task_shift = (level > 0 && n_sq < small_level) ? 5 : 7;
                     if (use_bvh)                        SCU(launch_bvh_shadow(sp, c->stream));
                     else if (cullscan && group_queries) SCU(launch_cull_shadow(csp, c->sm_count, c->stream));
                     else                                SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
@@ -376,7 +381,7 @@ int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
         if ((e = sb->tasks.ensure(64)) != cudaSuccess) return set_cuda_error(c, e, "task counters");
         SCU(cudaMemsetAsync(sb->tasks.p, 0, 4, c->stream));
         ctp.task_counter = sb->tasks.as<unsigned>();
-        ctp.perm = nullptr;
+        ctp.perm = nullptr; ctp.task_shift = 7;
         SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
     }
     else                          SCU(launch_trace_nearest(tp, c->sm_count, c->stream));

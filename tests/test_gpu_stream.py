@@ -259,7 +259,7 @@ def _layered_scene(rt, synth, rng, n_extra=400):
     layers = []                                   # (kind, geometry)
     for i in range(3):
         y = 12.0 * (i + 1)
-        layers.append(("tri", [-600, y, -600, 600, y, -600, 0, y, 800]))
+        layers.append(("tri", [-600, y, -600, 0, y, 800, 600, y, -600]))      # normal up: a ray coming down enters (a normal along the ray would send it back up)
     for i in range(3):
         c, a = np.array([0.0, 50.0 + 14.0 * i, 0.0]), np.array([500.0, 3.0, 500.0])
         q = 1.0 / (a * a)
@@ -287,7 +287,9 @@ def _layered_scene(rt, synth, rng, n_extra=400):
     mats = np.zeros((n_l + 1, 10), F)
     mats[:, 0:3] = rng.uniform(0.55, 0.99, (n_l + 1, 3))
     mats[:, 3], mats[:, 4] = 0.2, 0.8
-    mats[:n_l, 8], mats[:n_l, 9] = rng.uniform(0.8, 0.99, n_l), 1.0       # transparent, straight through (ior 1)
+    # transparent; every layer its own index of refraction: a ray whose ior EQUALS the surface's is treated as leaving
+    # (Scene.cpp:1800, normal flipped) and would turn back at these upward-facing layers
+    mats[:n_l, 8], mats[:n_l, 9] = rng.uniform(0.8, 0.99, n_l), 1.05 + 0.03 * np.arange(n_l)
     arrays = {"tri_points": tri, "tri_normal": synth.face_normals(tri), "tri_material": np.asarray(tri_m, np.int32),
               "tri_order": np.asarray(tri_o, np.int32),
               "quad_coef": np.asarray(quad, F), "quad_material": np.asarray(quad_m, np.int32), "quad_order": np.asarray(quad_o, np.int32),
@@ -322,10 +324,11 @@ def test_shadow_product_in_insertion_order(rt, renderer, port, synth):
     ps2 = rt.PackedScene(ps.a, frame)
     renderer.set_scene(ps2)
     renderer.build_bvh()
-    fr = rt.make_frame(ps2.frame, 192, 128, max_bounces=2, flags=rt.F_FORCE_STREAM)
+    fr = rt.make_frame(ps2.frame, 192, 128, max_bounces=12, flags=rt.F_FORCE_STREAM)     # deep enough to reach the ground
     wantf, _ = port.render(ps2, fr, threads=port.max_threads)
     for flags in (rt.F_FORCE_STREAM, rt.F_USE_BVH, rt.F_FORCE_RESIDENT):
-        gotf, _, st = renderer.render(rt.make_frame(ps2.frame, 192, 128, max_bounces=2, flags=flags))
+        gotf, _, st = renderer.render(rt.make_frame(ps2.frame, 192, 128, max_bounces=12, flags=flags))
+        assert st.depth_levels >= 9
         assert bits_equal(gotf, wantf), flags
         if flags != rt.F_FORCE_RESIDENT:
             assert st.shadow_fixups > 0
