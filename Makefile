@@ -41,7 +41,7 @@ $(LIBDIR)/librtb200_scene.so: $(filter-out $(HOST)/src/rt_cli.cpp,$(HOSTSRC)) $(
 $(LIBDIR)/rt_cli: $(HOST)/src/rt_cli.cpp $(LIBDIR)/librtb200_scene.so
 	$(HOSTCXX) $(HOSTFLAGS) -o $@ $(HOST)/src/rt_cli.cpp -L$(LIBDIR) -lrtb200_scene -lrtb200 -Wl,-rpath,'$$ORIGIN'
 
-oracle:
+oracle: lib
 	$(MAKE) -C $(ROOT)oracle all
 
 clean:

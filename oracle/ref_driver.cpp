@@ -104,7 +104,9 @@ extern "C" {
 
 const char* ref_flavour(void)
 {
-#ifdef REF_RECURSION_RESTORED
+#ifdef REF_GPU_BINDING
+    return "recursion-restored, GPU branch = librtb200 binding";
+#elif defined(REF_RECURSION_RESTORED)
     return "recursion-restored";
 #else
     return "as-shipped";
@@ -121,6 +123,20 @@ int ref_max_threads(void)
 }
 
 void ref_free_scene(void) { drop_scene(); }
+
+// Which branch of CScene::LancerRayons the next ref_render_full takes (Scene.cpp:692).  Only the libref_gpu.so flavour
+// has something behind the GPU branch (oracle/ref_gpu_binding.inc -> librtb200.so); in the other flavours that branch is
+// the reference's GL code, which cannot run here, so they refuse.  ref_new_scene / ref_load_scene reset it to the CPU branch.
+int ref_use_gpu_branch(int on)
+{
+#ifdef REF_GPU_BINDING
+    CVar::g_ComputerShadersON = on != 0;
+    return 0;
+#else
+    (void)on;
+    return -1;
+#endif
+}
 
 void ref_new_scene(void)
 {

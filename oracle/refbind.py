@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-FLAVOURS = {"shipped": "libref_shipped.so", "rec": "libref_rec.so", "rec_ndebug": "libref_rec_ndebug.so"}
+FLAVOURS = {"shipped": "libref_shipped.so", "rec": "libref_rec.so", "rec_ndebug": "libref_rec_ndebug.so",
+            "gpu": "libref_gpu.so"}      # gpu: the reference with the INTEGRATION.md binding behind g_ComputerShadersON
 
 _f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
 _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
@@ -53,6 +54,8 @@ class RefRenderer:
         L.ref_dump_camera.argtypes = [_f32p]
         L.ref_render_region.argtypes = [C.c_int] * 7 + [_f32p, C.c_int]
         L.ref_render_region.restype = C.c_double
+        L.ref_use_gpu_branch.argtypes = [C.c_int]
+        L.ref_use_gpu_branch.restype = C.c_int
         L.ref_trace_rays.argtypes = [C.c_int, _f32p, _f32p, _f32p, C.c_int]
         L.ref_nearest_hits.argtypes = [C.c_int, _f32p, _f32p, _i32p, _f32p, _f32p, C.c_int]
         L.ref_shadow_filters.argtypes = [C.c_int, _f32p, _f32p, _f32p, C.c_int]
@@ -113,6 +116,11 @@ class RefRenderer:
         lights = np.ascontiguousarray(ps["lights"], np.float32).reshape(-1, 7)
         for l in lights:
             self.lib.ref_add_light(np.ascontiguousarray(l[0:3]), np.ascontiguousarray(l[3:6]), float(l[6]))
+
+    def use_gpu_branch(self, on):
+        """CVar::g_ComputerShadersON for the next render_full (Scene.cpp:692); only the "gpu" flavour accepts it."""
+        if self.lib.ref_use_gpu_branch(1 if on else 0) != 0:
+            raise RuntimeError("this flavour has no GPU branch that can run here")
 
     # -- rendering ---------------------------------------------------------------------
     def render_full(self, W, H):

@@ -56,6 +56,8 @@ struct BvhState {
     bool   built = false;
     float  lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};   // vertex bounds of the triangles
     float  radius = 0.f;                           // R the boxes are padded for
+    float  wmax = 0.f;                             // largest |e1| |e2| of a triangle (far rays: rt_scene.cuh, DeviceScene::bvh_grow_tri)
+    float  kq = 0.f, cmax = 0.f;                   // bounded quadrics in the tree: max (sum q / min q), max |centre coordinate|
     float  padc = 1.0f;                            // PADC; RTB200_BVH_PADC overrides
     double build_ms = 0.0, refit_ms = 0.0;
     unsigned refits = 0;
@@ -101,7 +103,7 @@ RT_DEV void quadric_box(const float4& a, const float4& b, const float4& c, float
 
 __global__ void k_bvh_bounds(const TriRec* __restrict__ tri, int n_tri, const TriRec* __restrict__ tq, int n, int* __restrict__ bounds)
 {
-    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX}, wmax = 0.f;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const TriRec r = bvh_prim(tri, n_tri, tq, i);
         const float4 a = r.a, b = r.b, c = r.c;
@@ -119,7 +121,11 @@ __global__ void k_bvh_bounds(const TriRec* __restrict__ tri, int n_tri, const Tr
             lo[k] = fminf(lo[k], fminf(p[k], fminf(v1, v2)));
             hi[k] = fmaxf(hi[k], fmaxf(p[k], fmaxf(v1, v2)));
         }
+        const float w = sqrtf(b.x * b.x + b.y * b.y + b.z * b.z) * sqrtf(c.x * c.x + c.y * c.y + c.z * c.z);
+        if (w <= 3.0e38f) wmax = fmaxf(wmax, w);                // (the l1 * l2 of k_bvh_refit's pad)
     }
+    for (int off = 16; off > 0; off >>= 1) wmax = fmaxf(wmax, __shfl_xor_sync(FULL_MASK, wmax, off));
+    if ((threadIdx.x & 31) == 0) atomicMax(&bounds[6], __float_as_int(wmax));     // non-negative floats order like ints
     #pragma unroll
     for (int k = 0; k < 3; ++k)
         for (int off = 16; off > 0; off >>= 1) {
@@ -292,6 +298,40 @@ RT_DEV bool slab(const RayBox& r, float lx, float ly, float lz, float hx, float 
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), limit));
     return tn <= tf * (1.0f + 2.0f * BVH_SLACK);
 }
+// the same for the box grown by g on every side (gx = g |1/dx| ...: the slab distances move by that much)
+RT_DEV bool slab_grown(const RayBox& r, float gx, float gy, float gz, float lx, float ly, float lz, float hx, float hy, float hz, float limit, float& tn)
+{
+    const float ax = fmaf(lx, r.ix, r.nx), bx = fmaf(hx, r.ix, r.nx);
+    const float ay = fmaf(ly, r.iy, r.ny), by = fmaf(hy, r.iy, r.ny);
+    const float az = fmaf(lz, r.iz, r.nz), bz = fmaf(hz, r.iz, r.nz);
+    tn = fmaxf(fmaxf(fminf(ax, bx) - gx, fminf(ay, by) - gy), fmaxf(fminf(az, bz) - gz, 0.0f));
+    const float tf = fminf(fminf(fmaxf(ax, bx) + gx, fmaxf(ay, by) + gy), fminf(fmaxf(az, bz) + gz, limit));
+    return tn <= tf * (1.0f + 2.0f * BVH_SLACK);
+}
+
+// Far rays.  The boxes are padded for origins whose farthest corner of the primitives' bounds lies within bvh_radius
+// (bvh_refit: pad = PADC 2^-24 / EPSILON R |e1| |e2|, floor 32 ulp of R; quadrics inflated for R).  `reach` is that
+// distance for one origin; a ray with reach > R needs every pad scaled by reach / R: its walk grows every box by the
+// pad of the LARGEST triangle at its reach (>= what any box lacks), and by the growth of the quadrics' inflated boxes,
+//     sqrt(lim(D)/q) - sqrt(lim(R)/q) <= sqrt((lim(D) - lim(R)) / q_min),  lim(D) - lim(R) = 2e-5 (M(D) - M(R)),
+//     M(D) - M(R) = sum q_i ((|c_i| + D)^2 - (|c_i| + R)^2) <= (D - R)(2 c_max + D + R) sum q_i.
+RT_DEV float bvh_reach(const DeviceScene& s, V3 o)
+{
+    const float fx = fmaxf(fabsf(o.x - s.bvh_lo[0]), fabsf(o.x - s.bvh_hi[0]));
+    const float fy = fmaxf(fabsf(o.y - s.bvh_lo[1]), fabsf(o.y - s.bvh_hi[1]));
+    const float fz = fmaxf(fabsf(o.z - s.bvh_lo[2]), fabsf(o.z - s.bvh_hi[2]));
+    return sqrtf(fmaf(fx, fx, fmaf(fy, fy, fz * fz))) * 1.00001f;
+}
+RT_DEV bool bvh_is_far(const DeviceScene& s, V3 o) { return !(bvh_reach(s, o) <= s.bvh_radius); }
+RT_DEV float bvh_far_grow(const DeviceScene& s, float reach)
+{
+    float g = s.bvh_grow_tri * reach;
+    if (s.bvh_kq > 0.f) {
+        const float R = s.bvh_radius;
+        g = fmaxf(g, sqrtf(2.1e-5f * s.bvh_kq * fmaxf(reach - R, 0.f) * (2.0f * s.bvh_cmax + reach + R)) * 1.01f);
+    }
+    return g;
+}
 
 // One triangle of a leaf.  MODE 0 / 2: the conservative fused filter of rt_cull.cuh (phase 1: det, u; phase 2:
 // v, t -- numerator space, error-scaled margins), survivors re-evaluated in the reference's rounding sequence
@@ -313,10 +353,11 @@ RT_DEV float triangle_leaf(V3 o, V3 d, V3 p0, V3 e1, V3 e2, float tmax)
 // references only.  The bottom stack entry is a sentinel, so a pop never tests for an empty stack.
 #define BVH_DONE INT_MIN              // not a leaf reference: first + count <= n < 2^28 (bvh_build)
 
-template <bool SHRINK, class Leaf>
-RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& leaf, unsigned& n_nodes, unsigned& overflow)
+template <bool SHRINK, bool GROW = false, class Leaf>
+RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& leaf, unsigned& n_nodes, unsigned& overflow, float grow = 0.f)
 {
     const RayBox rb = make_raybox(o, d);
+    const float gx = GROW ? grow * fabsf(rb.ix) : 0.f, gy = GROW ? grow * fabsf(rb.iy) : 0.f, gz = GROW ? grow * fabsf(rb.iz) : 0.f;
     const BvhNode* __restrict__ nodes = s.bvh_nodes;
     int   stack_ref[BVH_STACK + 1];
     float stack_tn[SHRINK ? BVH_STACK + 1 : 1];
@@ -331,8 +372,8 @@ RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& l
             const int2 c = __ldg(reinterpret_cast<const int2*>(&nd->c));
             ++n_nodes;
             float t0, t1;
-            const bool h0 = slab(rb, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0);
-            const bool h1 = slab(rb, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1);
+            const bool h0 = GROW ? slab_grown(rb, gx, gy, gz, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0) : slab(rb, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0);
+            const bool h1 = GROW ? slab_grown(rb, gx, gy, gz, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1) : slab(rb, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1);
             if (h0 && h1) {
                 const bool swap = t1 < t0;
                 if (sp <= BVH_STACK) {
@@ -379,6 +420,10 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
     } else {
         const int i = blockIdx.x * BVH_THREADS + threadIdx.x;
         if (i < p.n_rays) { slot = i; o = f4_xyz(p.in_od0[i]); d = f4_xyz(p.in_od1[i]); }
+        if (slot >= 0 && p.far_count && s.bvh_n_prims > 0 && bvh_is_far(s, o)) {       // beyond the padded radius: k_bvh_far_nearest
+            const unsigned int k = atomicAdd(p.far_count, 1u);
+            if ((int)k < p.far_cap) { p.far_list[k] = slot; slot = -1; }
+        }
     }
     unsigned n_nodes = 0, n_tests = 0, n_qtests = 0, overflow = 0;
     if (slot >= 0) {
@@ -459,10 +504,17 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
         if (blk + 256 <= p.n_queries) i = blk | ((i & 31) << 3) | ((i >> 5) & 7);
     }
     unsigned n_nodes = 0, n_tests = 0, overflow = 0, n_side_q = 0, n_side_p = 0;
-    if (i < p.n_queries) {
-        V3 o, d;
-        float dist;
+    bool mine = i < p.n_queries;
+    V3 o = mk3(0.f, 0.f, 0.f), d = o;
+    float dist = 0.f;
+    if (mine) {
         shadow_query<(MODE != 2)>(p, i, o, d, dist);
+        if (p.far_count && s.bvh_n_prims > 0 && bvh_is_far(s, o)) {          // beyond the padded radius: k_bvh_far_shadow
+            const unsigned int k = atomicAdd(p.far_count, 1u);
+            if ((int)k < p.far_cap) { p.far_list[k] = i; mine = false; }
+        }
+    }
+    if (mine) {
         const float tlim = fmaf(dist, CULL_TREL, CULL_TABS);
         float fr = 1.0f, fg = 1.0f, fb = 1.0f;
         bool zero = false;
@@ -562,6 +614,143 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Far rays (see bvh_reach): few, so one plain kernel per kind -- the same leaf tests and winner rule, every box grown
+// by what this ray's own origin needs.  Shadow: the occluders are multiplied as they are met; three or more go to the
+// fix-up list like everywhere else (k_shadow_fixup redoes the product in insertion order).
+// ---------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(128) k_bvh_far_nearest(const __grid_constant__ TraceParams p)
+{
+    const DeviceScene& s = p.s;
+    const int n = min((int)*p.far_count, p.far_cap);
+    unsigned n_nodes = 0, overflow = 0, n_far = 0;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < n; w += gridDim.x * blockDim.x) {
+        const int slot = p.far_list[w];
+        const V3 o = f4_xyz(p.in_od0[slot]), d = f4_xyz(p.in_od1[slot]);
+        float best_t = -1.0f;
+        int best_id = -1;
+        ++n_far;
+        const TriRec* __restrict__ tri = s.bvh_tri;
+        bvh_traverse<true, true>(s, o, d, 3.0e38f, [&](int first, int count, float limit) -> float {
+            for (int k = 0; k < count; ++k) {
+                const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
+                float tt;
+                if (rec_is_quadric(rc)) {
+                    const Quadric Q = { ra.x, ra.y, ra.z, 0.f, 0.f, 0.f, rb.x, rb.y, rb.z, rc.x };
+                    bool lin;
+                    tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+                } else
+                    tt = triangle_leaf<MODE>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc), best_t < 0.f ? 3.0e38f : fmaf(best_t, CULL_TREL, CULL_TABS));
+                const int ord = __float_as_int(ra.w);
+                if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; limit = tt; }
+            }
+            return limit;
+        }, n_nodes, overflow, bvh_far_grow(s, bvh_reach(s, o)));
+        for (int q = 0; q < s.bvh_n_quad; ++q) {
+            const float4 q0 = __ldg(&s.bvh_quad[q].q0), q1 = __ldg(&s.bvh_quad[q].q1), q2 = __ldg(&s.bvh_quad[q].q2);
+            const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+            const int ord = __float_as_int(q0.w);
+            bool lin;
+            const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+            if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+        }
+        for (int q = 0; q < s.n_plane; ++q) {
+            const float4 nc = __ldg(&s.plane[q].nc);
+            const int ord = s.plane[q].order;
+            const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
+            if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+        }
+        p.hit[slot] = make_float2(best_t, __int_as_float(best_id));
+    }
+    if (p.stats && (n_far | overflow)) {
+        unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+        if (n_far) atomicAdd(&st[ST_BVH_OUT_OF_RADIUS], (unsigned long long)n_far);
+        if (n_nodes) atomicAdd(&st[ST_BVH_NODES], (unsigned long long)n_nodes);
+        if (overflow) atomicAdd(&st[ST_BVH_OVERFLOW], 1ull);
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(128) k_bvh_far_shadow(const __grid_constant__ ShadowParams p)
+{
+    const DeviceScene& s = p.s;
+    const int n = min((int)*p.far_count, p.far_cap);
+    unsigned n_nodes = 0, overflow = 0, n_far = 0;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < n; w += gridDim.x * blockDim.x) {
+        const int i = p.far_list[w];
+        V3 o, d;
+        float dist;
+        shadow_query<(MODE != 2)>(p, i, o, d, dist);
+        const float tlim = fmaf(dist, CULL_TREL, CULL_TABS);
+        float fr = 1.0f, fg = 1.0f, fb = 1.0f;
+        int n_occ = 0;
+        ++n_far;
+        auto occluder = [&](int m) {
+            const float4 m0 = __ldg(&s.mat[m].m0);
+            const float kt = __ldg(&s.mat[m].m2).x;
+            fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+            ++n_occ;
+        };
+        const TriRec* __restrict__ tri = s.bvh_tri;
+        bvh_traverse<false, true>(s, o, d, dist, [&](int first, int count, float limit) -> float {
+            for (int k = 0; k < count; ++k) {
+                const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
+                float tt;
+                if (rec_is_quadric(rc)) {
+                    const Quadric Q = { ra.x, ra.y, ra.z, 0.f, 0.f, 0.f, rb.x, rb.y, rb.z, rc.x };
+                    bool lin;
+                    tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+                } else tt = triangle_leaf<MODE>(o, d, f4_xyz(ra), f4_xyz(rb), f4_xyz(rc), tlim);
+                if (tt > RT_EPS && tt < dist) occluder(__float_as_int(rb.w));
+            }
+            return limit;
+        }, n_nodes, overflow, bvh_far_grow(s, bvh_reach(s, o)));
+        for (int q = 0; q < s.bvh_n_quad; ++q) {
+            const float4 q0 = __ldg(&s.bvh_quad[q].q0), q1 = __ldg(&s.bvh_quad[q].q1), q2 = __ldg(&s.bvh_quad[q].q2);
+            const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+            bool lin;
+            const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+            if (tt > RT_EPS && tt < dist) occluder(__float_as_int(q1.w));
+        }
+        for (int q = 0; q < s.n_plane; ++q) {
+            const float4 nc = __ldg(&s.plane[q].nc);
+            const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
+            if (tt > RT_EPS && tt < dist) occluder(s.plane[q].material);
+        }
+        p.filter[i] = make_float4(fr, fg, fb, 0.f);
+        if (n_occ >= 3 && !(fr == 0.f && fg == 0.f && fb == 0.f) && p.fix_count) {
+            const unsigned int k = atomicAdd(p.fix_count, 1u);
+            if ((int)k < p.fix_cap) p.fix_list[k] = i;
+            if (p.stats) atomicAdd(&p.stats[(size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + ST_SHADOW_FIXUP], 1ull);
+        }
+    }
+    if (p.stats && (n_far | overflow)) {
+        unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+        if (n_far) atomicAdd(&st[ST_BVH_OUT_OF_RADIUS], (unsigned long long)n_far);
+        if (n_nodes) atomicAdd(&st[ST_BVH_NODES_SHADOW], (unsigned long long)n_nodes);
+        if (overflow) atomicAdd(&st[ST_BVH_OVERFLOW], 1ull);
+    }
+}
+
+cudaError_t launch_bvh_far_nearest(const TraceParams& p, int sm_count, cudaStream_t st)
+{
+    if (!p.far_count || p.primary || p.s.bvh_n_prims <= 0) return cudaSuccess;
+    if (p.mode == 2)      k_bvh_far_nearest<2><<<sm_count * 2, 128, 0, st>>>(p);
+    else if (p.mode == 1) k_bvh_far_nearest<1><<<sm_count * 2, 128, 0, st>>>(p);
+    else                  k_bvh_far_nearest<0><<<sm_count * 2, 128, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bvh_far_shadow(const ShadowParams& p, int sm_count, cudaStream_t st)
+{
+    if (!p.far_count || p.s.bvh_n_prims <= 0) return cudaSuccess;
+    if (p.mode == 2)      k_bvh_far_shadow<2><<<sm_count * 2, 128, 0, st>>>(p);
+    else if (p.mode == 1) k_bvh_far_shadow<1><<<sm_count * 2, 128, 0, st>>>(p);
+    else                  k_bvh_far_shadow<0><<<sm_count * 2, 128, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
 template <bool QUADS>
 static void launch_nearest_t(const TraceParams& p, int blocks, cudaStream_t st)
 {
@@ -638,6 +827,10 @@ static int bvh_refit(rtb200_ctx* c, BvhState* b, float radius)
 {
     const int n = b->n_prims;
     b->radius = radius;
+    for (int k = 0; k < 3; ++k) { c->ds.bvh_lo[k] = b->lo[k]; c->ds.bvh_hi[k] = b->hi[k]; }
+    c->ds.bvh_radius = radius;
+    c->ds.bvh_grow_tri = std::max(b->padc * 5.9604645e-8f / RT_EPS * b->wmax, 32.0f * 1.1920929e-7f) * 1.01f;
+    c->ds.bvh_kq = b->kq; c->ds.bvh_cmax = b->cmax;
     if (n <= BVH_LEAF_MAX) return RTB200_OK;                  // a single leaf: no boxes at all
     // pad = PADC * 2^-24 / EPSILON * R * |e1| |e2|, floor 32 ulp of R (rounding of the slab test)
     const float pad_scale = b->padc * 5.9604645e-8f / RT_EPS * radius;
@@ -675,6 +868,7 @@ int bvh_build(rtb200_ctx* c)
     // ---- quadrics: bounded ones join the tree, the others stay in the linear side list -----------------------
     std::vector<TriRec> tree_q;
     std::vector<QuadRec> side_q;
+    float kq = 0.f, cmax = 0.f;
     const bool quads_in_tree = getenv("RTB200_BVH_NO_QUADRICS") == nullptr;
     for (size_t i = 0; i < c->h_quad.size(); ++i) {
         const QuadRec& q = c->h_quad[i];
@@ -685,8 +879,12 @@ int bvh_build(rtb200_ctx* c)
             r.b = make_float4(q.q2.x, q.q2.y, q.q2.z, q.q1.w);            // lx ly lz | material
             r.c = make_float4(q.q2.w, r3.w, 0.f, 1.0f);                   // K, rhs, -, tag
             tree_q.push_back(r);
+            const float qmin = std::min(q.q0.x, std::min(q.q0.y, q.q0.z));
+            kq = std::max(kq, (q.q0.x + q.q0.y + q.q0.z) / qmin);
+            for (int k = 0; k < 3; ++k) cmax = std::max(cmax, std::fabs((&q.q2.x)[k] / (2.0f * (&q.q0.x)[k])));
         } else side_q.push_back(q);
     }
+    b->kq = kq; b->cmax = cmax;
     const int Qb = (int)tree_q.size(), Qs = (int)side_q.size();
     const long long n_ll = (long long)T + Qb;
     if (n_ll >= (1ll << BVH_LEAF_SHIFT)) { c->last_error = "too many primitives for the LBVH leaf encoding"; return RTB200_E_ARG; }
@@ -706,16 +904,18 @@ int bvh_build(rtb200_ctx* c)
     if (n > 0) {
         if ((e = b->tri_sorted.ensure(sizeof(TriRec) * (size_t)n)) != cudaSuccess || (e = b->bounds.ensure(sizeof(int) * 8)) != cudaSuccess)
             return set_cuda_error(c, e, "bvh buffers");
-        int h_init[6] = {INT_MAX, INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MIN};
+        int h_init[7] = {INT_MAX, INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MIN, 0};
         BCU(cudaMemcpyAsync(b->bounds.p, h_init, sizeof h_init, cudaMemcpyHostToDevice, c->stream));
         k_bvh_bounds<<<std::min((n + 255) / 256, 4 * c->sm_count), 256, 0, c->stream>>>(c->ds.tri, T, tq, n, b->bounds.as<int>());
         BCU(cudaGetLastError());
-        int h_b[6];
+        int h_b[7];
         BCU(cudaMemcpyAsync(h_b, b->bounds.p, sizeof h_b, cudaMemcpyDeviceToHost, c->stream));
         BCU(cudaStreamSynchronize(c->stream));
         for (int k = 0; k < 3; ++k) { b->lo[k] = order_float(h_b[k]); b->hi[k] = order_float(h_b[3 + k]); }
+        memcpy(&b->wmax, &h_b[6], 4);
     } else {
         for (int k = 0; k < 3; ++k) b->lo[k] = b->hi[k] = 0.f;
+        b->wmax = 0.f;
     }
     if (n > BVH_LEAF_MAX) {
         const size_t nn = (size_t)n;

@@ -17,5 +17,9 @@ namespace rtb {
 
 cudaError_t launch_bvh_nearest(const TraceParams& p, cudaStream_t st);
 cudaError_t launch_bvh_shadow(const ShadowParams& p, cudaStream_t st);
+// the rays / queries the launches above put on their far lists (origins beyond the padded radius): same answers as the
+// linear scan for them too -- every box grown by the pad their own origin needs.  No-ops without a far list.
+cudaError_t launch_bvh_far_nearest(const TraceParams& p, int sm_count, cudaStream_t st);
+cudaError_t launch_bvh_far_shadow(const ShadowParams& p, int sm_count, cudaStream_t st);
 
 } // namespace rtb

@@ -59,6 +59,12 @@ struct DeviceScene {
     int             bvh_n_prims;    // triangles + bounded quadrics in the tree
     const QuadRec*  bvh_quad;       // quadrics the LBVH kernels still scan linearly (unbounded / rotated ones)
     int             bvh_n_quad;
+    // exactness beyond the padded radius (rt_bvh.cu, "far rays"): the boxes are padded for ray origins whose farthest
+    // corner of [bvh_lo, bvh_hi] is within bvh_radius; a ray that starts farther out (a reflection off the ground plane
+    // near the horizon) walks the tree with every box grown by the pad ITS origin needs
+    float bvh_lo[3], bvh_hi[3], bvh_radius;
+    float bvh_grow_tri;             // triangles: grow = bvh_grow_tri * reach (the pad of the largest |e1||e2|, per unit of reach)
+    float bvh_kq, bvh_cmax;         // bounded quadrics in the tree: grow = sqrt(2.1e-5 kq (reach - R)(2 cmax + reach + R))
 };
 
 // ---- per-frame constants ------------------------------------------------------------------

@@ -32,7 +32,7 @@ namespace rtb {
 
 struct StreamBufs {                // per-context scratch of the streamed path (lives in the ctx levels + these)
     DevBuf hit, hitP, hitN, q_base, sq0, sq1, sq_src, sq_dst, filter;
-    DevBuf tasks, fix;             // culled scan: task / fix-up counters (3 words per level), fix-up list
+    DevBuf tasks, fix, far;        // per-level counters (6 words per level), fix-up list, LBVH far-ray list
     DevBuf ckey, cidx, ckey2, cperm, qkey, qidx, qkey2, qperm, sort_tmp;   // culled scan: (key, index) pairs of the children / queries of a level and their sorted forms
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // per-stage stopwatch
 };
@@ -69,7 +69,7 @@ void stream_release(rtb200_ctx* c)
 {
     if (!c->stream_scratch) return;
     StreamBufs* b = static_cast<StreamBufs*>(c->stream_scratch);
-    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->sq_dst.release(); b->filter.release(); b->tasks.release(); b->fix.release();
+    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->sq_dst.release(); b->filter.release(); b->tasks.release(); b->fix.release(); b->far.release();
     b->ckey.release(); b->cidx.release(); b->ckey2.release(); b->cperm.release(); b->qkey.release(); b->qidx.release(); b->qkey2.release(); b->qperm.release(); b->sort_tmp.release();
     for (auto& e : b->ev) if (e) cudaEventDestroy(e);
     delete b;
@@ -139,7 +139,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     if ((e = c->counters.ensure(sizeof(unsigned) * n_counters)) != cudaSuccess) return set_cuda_error(c, e, "counters");
     unsigned* h_cnt = c->h_small.as<unsigned>();
     unsigned* d_cnt = c->counters.as<unsigned>();
-    const size_t n_tasks_words = 3 * ((size_t)std::max(fr->max_bounces, 0) + 2);
+    const size_t n_tasks_words = 6 * ((size_t)std::max(fr->max_bounces, 0) + 2);      // per level: nearest tasks, shadow tasks, fix-ups, far rays, far queries, -
     if ((e = sb->tasks.ensure(sizeof(unsigned) * n_tasks_words)) != cudaSuccess) return set_cuda_error(c, e, "task counters");
     unsigned* d_tasks = sb->tasks.as<unsigned>();
     unsigned max_level_seen = 0, chunks = 0;
@@ -199,10 +199,17 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             if (timed) SCU(cudaEventRecord(ev_a, c->stream));
             SCU(cudaEventRecord(E[0], c->stream));
             tp.stats = c->stats.as<unsigned long long>();
-            if (use_bvh) SCU(launch_bvh_nearest(tp, c->stream));
+            if (use_bvh) {
+                if (level > 0) {                   // secondary rays may start beyond the radius the boxes are padded for
+                    if ((e = sb->far.ensure(sizeof(int) * n)) != cudaSuccess) return set_cuda_error(c, e, "far list");
+                    tp.far_list = sb->far.as<int>(); tp.far_count = d_tasks + 6 * level + 3; tp.far_cap = n_in;
+                }
+                SCU(launch_bvh_nearest(tp, c->stream));
+                if (level > 0) { SCU(launch_bvh_far_nearest(tp, c->sm_count, c->stream)); ++*launches; }
+            }
             else if (cullscan) {
                 CullTraceParams ctp;
-                ctp.t = tp; ctp.cs = cull; ctp.task_counter = d_tasks + 3 * level;
+                ctp.t = tp; ctp.cs = cull; ctp.task_counter = d_tasks + 6 * level;
                 ctp.perm = (level > 0 && rays_sorted) ? sb->cperm.as<int>() : nullptr;
                 ctp.task_shift = (level > 0 && n_in < small_level) ? 5 : 7;
                 SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
@@ -283,13 +290,20 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 {
                     // queries whose product order matters go on a list and are redone in insertion order (every path)
                     if ((e = sb->fix.ensure(sizeof(int) * (size_t)n_sq)) != cudaSuccess) return set_cuda_error(c, e, "fix-up list");
-                    unsigned* tk = sb->tasks.as<unsigned>() + 3 * level;
+                    unsigned* tk = sb->tasks.as<unsigned>() + 6 * level;
                     sp.fix_count = tk + 2; sp.fix_list = sb->fix.as<int>(); sp.fix_cap = n_sq;
                     CullShadowParams csp;
                     csp.s = sp; csp.cs = cull; csp.task_counter = tk + 1;
                     csp.perm = queries_sorted ? sb->qperm.as<int>() : nullptr;
                     csp.task_shift = (level > 0 && n_sq < small_level) ? 5 : 7;
-                    if (use_bvh)                        SCU(launch_bvh_shadow(sp, c->stream));
+                    if (use_bvh) {
+                        if ((e = sb->far.ensure(sizeof(int) * (size_t)n_sq)) != cudaSuccess) return set_cuda_error(c, e, "far list");
+                        sp.far_list = sb->far.as<int>(); sp.far_count = tk + 4; sp.far_cap = n_sq;
+                        csp.s = sp;
+                        SCU(launch_bvh_shadow(sp, c->stream));
+                        SCU(launch_bvh_far_shadow(sp, c->sm_count, c->stream));
+                        ++*launches;
+                    }
                     else if (cullscan && group_queries) SCU(launch_cull_shadow(csp, c->sm_count, c->stream));
                     else                                SCU(launch_trace_shadow(sp, c->sm_count, c->stream));
                     SCU(launch_shadow_fixup(csp, c->sm_count, c->stream));     // (reads the count itself; nearly always 0)

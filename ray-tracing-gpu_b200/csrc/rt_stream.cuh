@@ -26,6 +26,9 @@ struct TraceParams {
                                    // 2: filter + fused survivors (FUSED_FP)
     unsigned long long* stats;     // LBVH kernels: nodes visited / triangle tests (may be null)
     int   cull_bundles;            // (culled scan only)
+    int*          far_list;        // LBVH, secondary rays: rays that start beyond the padded radius are listed here
+    unsigned int* far_count;       // (null: every ray takes the normal walk) and traced by k_bvh_far_nearest
+    int           far_cap;
 };
 
 // shade-A: hit point, normal, shadow queries of the facing lights, children
@@ -81,6 +84,9 @@ struct ShadowParams {
     int*          fix_list;        // queries whose filter product has to be redone in insertion order (rare) ...
     unsigned int* fix_count;       // ... how many (null: nothing is recorded), and the room there is
     int           fix_cap;
+    int*          far_list;        // LBVH: queries whose origin lies beyond the padded radius (see TraceParams::far_list)
+    unsigned int* far_count;
+    int           far_cap;
 };
 
 // shade-B: ambient + per-light diffuse/Phong with the shadow filters, in light order

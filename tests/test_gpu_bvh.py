@@ -266,3 +266,41 @@ def test_quadrics_can_be_kept_out_of_the_tree(rt, renderer, synth):
     renderer.build_bvh()
     b, b8, _ = renderer.render(fr)
     assert bits_equal(a, b) and np.array_equal(a8, b8)
+
+
+def test_rays_that_start_beyond_the_padded_radius(rt, renderer, port, synth):
+    """The boxes are padded for origins within R of the mesh (R covers the camera).  Rays that start FARTHER out -- the
+    reflections off a mirror wall 4000 units away, the shadow queries of ground points near the horizon -- take the walk
+    with boxes grown for their own origin (rt_bvh.cu, "far rays"; rtb200_stats.bvh_out_of_radius counts them): same
+    frame as the linear scan, same as the oracle."""
+    hf = synth.heightfield(20000, 300.0, 3, seed=17, p_mirror=0.2)
+    a = {k: np.array(hf[k]) for k in hf.a}
+    T = len(a["tri_order"])
+    mats = a["materials"]
+    ground = len(mats) - 1
+    mats[ground, 7] = 0.5                                               # the ground reflects
+    wall = np.array([[0.9, 0.9, 0.95, 0.1, 0.3, 0, 0, 0.9, 0, 0]], F)   # a mirror wall at x = -4000
+    a["materials"] = np.concatenate([mats, wall]).astype(F)
+    a["plane_coef"] = np.concatenate([a["plane_coef"], np.array([[1.0, 0.0, 0.0, 4000.0]], F)]).astype(F)
+    a["plane_material"] = np.concatenate([a["plane_material"], [len(mats)]]).astype(np.int32)
+    a["plane_order"] = np.concatenate([a["plane_order"], [T + 1]]).astype(np.int32)
+    hostbind = import_module("rtb200.hostbind")
+    frame = hostbind.camera_frame((-700.0, 160.0, 40.0), (-4000.0, 60.0, 0.0), (0.0, 1.0, 0.0))
+    frame["background"] = np.array([0.1, 0.2, 0.5], F)
+    ps = rt.PackedScene(a, frame)
+    renderer.set_scene(ps)
+    info = renderer.build_bvh()
+    W, H = 320, 200
+    fr_b = rt.make_frame(ps.frame, W, H, max_bounces=3, flags=rt.F_USE_BVH)
+    got, got8, st = renderer.render(fr_b)
+    assert st.path == 2 and st.bvh_out_of_radius > 1000, st.bvh_out_of_radius
+    assert st.rays_reflect > W * H // 2                                  # the wall fills the view: its reflections start 3300+ units out
+    ref, ref8, st_s = renderer.render(rt.make_frame(ps.frame, W, H, max_bounces=3, flags=rt.F_FORCE_STREAM))
+    assert (st.rays_shadow, st.rays_reflect) == (st_s.rays_shadow, st_s.rays_reflect)
+    assert bits_equal(got, ref) and np.array_equal(got8, ref8)
+    x0, y0, w, h = 120, 70, 64, 40                                       # the mirrored terrain is in the middle of the view
+    want, _ = port.render_region(ps, fr_b, x0, y0, w, h, threads=port.max_threads)
+    crop = got[y0:y0 + h, x0:x0 + w]
+    assert np.allclose(crop, want, rtol=0, atol=4e-6), float(np.abs(crop - want).max())
+    assert len(np.unique(want.reshape(-1, 3), axis=0)) > 200             # (a real picture, not one flat colour)
+    assert info["pad_radius"] < 3000.0                                   # the wall really lies beyond the padded radius
