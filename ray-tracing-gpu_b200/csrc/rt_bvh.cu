@@ -315,14 +315,6 @@ RT_DEV bool slab_grown(const RayBox& r, float gx, float gy, float gz, float lx, 
 // pad of the LARGEST triangle at its reach (>= what any box lacks), and by the growth of the quadrics' inflated boxes,
 //     sqrt(lim(D)/q) - sqrt(lim(R)/q) <= sqrt((lim(D) - lim(R)) / q_min),  lim(D) - lim(R) = 2e-5 (M(D) - M(R)),
 //     M(D) - M(R) = sum q_i ((|c_i| + D)^2 - (|c_i| + R)^2) <= (D - R)(2 c_max + D + R) sum q_i.
-RT_DEV float bvh_reach(const DeviceScene& s, V3 o)
-{
-    const float fx = fmaxf(fabsf(o.x - s.bvh_lo[0]), fabsf(o.x - s.bvh_hi[0]));
-    const float fy = fmaxf(fabsf(o.y - s.bvh_lo[1]), fabsf(o.y - s.bvh_hi[1]));
-    const float fz = fmaxf(fabsf(o.z - s.bvh_lo[2]), fabsf(o.z - s.bvh_hi[2]));
-    return sqrtf(fmaf(fx, fx, fmaf(fy, fy, fz * fz))) * 1.00001f;
-}
-RT_DEV bool bvh_is_far(const DeviceScene& s, V3 o) { return !(bvh_reach(s, o) <= s.bvh_radius); }
 RT_DEV float bvh_far_grow(const DeviceScene& s, float reach)
 {
     float g = s.bvh_grow_tri * reach;
@@ -508,8 +500,8 @@ k_bvh_shadow(const __grid_constant__ ShadowParams p)
     V3 o = mk3(0.f, 0.f, 0.f), d = o;
     float dist = 0.f;
     if (mine) {
-        shadow_query<(MODE != 2)>(p, i, o, d, dist);
-        if (p.far_count && s.bvh_n_prims > 0 && bvh_is_far(s, o)) {          // beyond the padded radius: k_bvh_far_shadow
+        const bool far = shadow_query<(MODE != 2)>(p, i, o, d, dist);
+        if (far && p.far_count) {                                             // beyond the padded radius (shade-A marked it): k_bvh_far_shadow
             const unsigned int k = atomicAdd(p.far_count, 1u);
             if ((int)k < p.far_cap) { p.far_list[k] = i; mine = false; }
         }

@@ -235,6 +235,7 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             sa.links = cur.links.as<int4>();
             sa.stats = c->stats.as<unsigned long long>();
             sa.exact = exact ? 1 : 0;
+            sa.mark_far = use_bvh ? 1 : 0;
             const bool sort_children = sort_secondary && spawn;
             const bool sort_queries = sort_secondary && level > 0 && group_queries;
             if (sort_children) {

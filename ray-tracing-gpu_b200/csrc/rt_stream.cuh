@@ -63,6 +63,7 @@ struct ShadeAParams {
     unsigned int* sq_key;          // per shadow query: light << 27 | 27-bit Morton code of the hit point
     int*          sq_idx;
     float         key_lo[3], key_inv;
+    int           mark_far;        // LBVH frames: set SQ_FAR_BIT on the queries of hit points beyond the padded radius
     int*  sq_dst;                  // null: queries in (ray, light) order, filter slot = query slot.  Otherwise the
                                    // CTA's queries are queued light by light (<= 8 lights) and sq_dst[query] is the
                                    // filter slot shade-B reads (q_base[ray] + rank of the light among the facing ones)
@@ -108,20 +109,35 @@ struct ShadeBParams {
 
 // One shadow query: origin, unit direction towards the light, distance to it.  The derived form repeats
 // the arithmetic shade-A / shade-B use for the same pair (Scene.cpp:1847-1848), in the same rounding mode.
+#define SQ_FAR_BIT 0x40000000      // in sq_src[].y next to the light index: the hit point lies beyond the radius the LBVH boxes
+                                   // are padded for (shade-A knows the point; the shadow kernel only tests the bit)
 template <bool E>
-RT_DEV void shadow_query(const ShadowParams& p, int i, V3& o, V3& d, float& dist)
+RT_DEV bool shadow_query(const ShadowParams& p, int i, V3& o, V3& d, float& dist)
 {
     if (p.sq_src) {
-        const int2 src = p.sq_src[i];
+        int2 src = p.sq_src[i];
+        const bool far = (src.y & SQ_FAR_BIT) != 0;
+        src.y &= ~SQ_FAR_BIT;
         o = f4_xyz(p.hitP[src.x]);
         V3 Ld = sub3<E>(f4_xyz(p.s.light[src.y].l0), o);
         dist = norm3<E>(Ld);
         d = scale3<E>(Ld, FP<E>::rcp(dist));
-    } else {
-        const float4 a = p.sq0[i], b = p.sq1[i];
-        o = f4_xyz(a); d = f4_xyz(b); dist = a.w;
+        return far;
     }
+    const float4 a = p.sq0[i], b = p.sq1[i];
+    o = f4_xyz(a); d = f4_xyz(b); dist = a.w;
+    return false;
 }
+
+// LBVH: distance from a ray origin to the farthest corner of the primitives' bounds -- what the padded boxes must cover
+RT_DEV float bvh_reach(const DeviceScene& s, V3 o)
+{
+    const float fx = fmaxf(fabsf(o.x - s.bvh_lo[0]), fabsf(o.x - s.bvh_hi[0]));
+    const float fy = fmaxf(fabsf(o.y - s.bvh_lo[1]), fabsf(o.y - s.bvh_hi[1]));
+    const float fz = fmaxf(fabsf(o.z - s.bvh_lo[2]), fabsf(o.z - s.bvh_hi[2]));
+    return sqrtf(fmaf(fx, fx, fmaf(fy, fy, fz * fz))) * 1.00001f;
+}
+RT_DEV bool bvh_is_far(const DeviceScene& s, V3 o) { return !(bvh_reach(s, o) <= s.bvh_radius); }
 
 RT_DEV unsigned int expand10(unsigned int v)         // bit i of a 10-bit value -> bit 3 i
 {

@@ -440,6 +440,7 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
         kr = m1.w; kt = m2.x; mior = m2.y;
     }
     // ---- shadow queries ---------------------------------------------------------------------
+    const int far_bit = (p.mark_far && hit && s.bvh_n_prims > 0 && bvh_is_far(s, P)) ? SQ_FAR_BIT : 0;
     int n_face = 0;
     unsigned int face_bits = 0;                              // bit l: light l faces the stored normal
     if (hit)
@@ -523,7 +524,7 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
             const unsigned int m = __ballot_sync(FULL_MASK, facing);
             if (facing) {
                 const int k = (int)(wb.w + s_loff[l * 8 + warp] + __popc(m & below));
-                p.sq_src[k] = make_int2(i, l);
+                p.sq_src[k] = make_int2(i, l | far_bit);
                 p.sq_dst[k] = q++;
                 if (p.sq_key) { p.sq_key[k] = ((unsigned int)l << 27) | (morton30(P.x, P.y, P.z, p.key_lo[0], p.key_lo[1], p.key_lo[2], p.key_inv) >> 3); p.sq_idx[k] = k; }
             }
@@ -533,7 +534,7 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
             const V3 Ld = sub3<E>(f4_xyz(s.light[l].l0), P);
             if (dot3<E>(Ld, N) > 0.f) {                                   // direction and distance: shadow_query()
                 if (p.sq_key) { p.sq_key[q] = ((unsigned int)l << 27) | (morton30(P.x, P.y, P.z, p.key_lo[0], p.key_lo[1], p.key_lo[2], p.key_inv) >> 3); p.sq_idx[q] = q; }
-                p.sq_src[q++] = make_int2(i, l);
+                p.sq_src[q++] = make_int2(i, l | far_bit);
             }
         }
     // ---- children --------------------------------------------------------------------------------
