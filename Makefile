@@ -44,8 +44,18 @@ $(LIBDIR)/rt_cli: $(HOST)/src/rt_cli.cpp $(LIBDIR)/librtb200_scene.so
 oracle: lib
 	$(MAKE) -C $(ROOT)oracle all
 
+# CHECKED build: every .cu with -DRTB200_CHECKED (device-side bounds checks, rt_math.cuh: RT_CHECK) into ab/checked/
+# (git-ignored, travels to the GPU box); run anything against it with RTB200_LIB=ab/checked/librtb200.so
+CHKDIR  := $(ROOT)ab/checked
+CHKOBJS := $(patsubst $(OBJDIR)/%.o,$(CHKDIR)/%.o,$(CUOBJS))
+$(CHKDIR)/%.o: $(CSRC)/%.cu $(CUHDRS)
+	@mkdir -p $(CHKDIR)
+	$(NVCC) $(NVFLAGS) -DRTB200_CHECKED -c $< -o $@
+checked: $(CHKOBJS)
+	$(NVCC) -shared -ccbin $(HOSTCXX) -o $(CHKDIR)/librtb200.so $^ -ldl
+
 clean:
 	rm -rf $(OBJDIR) $(LIBDIR)
 	$(MAKE) -C $(ROOT)oracle clean
 
-.PHONY: all lib host oracle clean
+.PHONY: all lib host oracle checked clean

@@ -16,7 +16,8 @@ from .abi import (F_EXACT_FP, F_FORCE_RESIDENT, F_FORCE_STREAM, F_FUSED_FP, F_GA
                   Frame, PackedScene, Stats, make_frame)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "librtb200.so")
+# RTB200_LIB: another build of the SAME library (e.g. ab/checked/librtb200.so, `make checked`) -- never a fallback
+LIB_PATH = os.path.abspath(os.environ["RTB200_LIB"]) if os.environ.get("RTB200_LIB") else os.path.join(_HERE, "lib", "librtb200.so")
 
 EXPORTS = [
     "rtb200_abi_version", "rtb200_create", "rtb200_destroy", "rtb200_error_string", "rtb200_last_error",

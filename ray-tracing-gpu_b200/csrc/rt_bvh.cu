@@ -382,6 +382,7 @@ RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& l
         }
         if (ref == BVH_DONE) return;
         const int code = ~ref;                               // ---- leaf
+        RT_CHECK((code & ((1 << BVH_LEAF_SHIFT) - 1)) + (code >> BVH_LEAF_SHIFT) + 1 <= s.bvh_n_prims && sp >= 1 && sp <= BVH_STACK + 1);
         limit = leaf(code & ((1 << BVH_LEAF_SHIFT) - 1), (code >> BVH_LEAF_SHIFT) + 1, limit);
         if (limit < 0.f) return;
         if (SHRINK) {
@@ -619,6 +620,7 @@ __global__ void __launch_bounds__(128) k_bvh_far_nearest(const __grid_constant__
     unsigned n_nodes = 0, overflow = 0, n_far = 0;
     for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < n; w += gridDim.x * blockDim.x) {
         const int slot = p.far_list[w];
+        RT_CHECK(slot >= 0 && slot < p.n_rays);
         const V3 o = f4_xyz(p.in_od0[slot]), d = f4_xyz(p.in_od1[slot]);
         float best_t = -1.0f;
         int best_id = -1;

@@ -102,11 +102,13 @@ RT_DEV bool cs_fill(const CullScene& cs, CsWarpSmem& ws, int n_c, bool keep_all,
             level = w.lvl - 1;
         }
         const int i = cs_level_offset(cs.n3, level) + block * 32 + lane;
+        RT_CHECK(level >= 0 && level < CS_LEVELS && block >= 0 && i >= 0 && i < cs.n3 * (1057 + 32768));
         bool keep = false;
         if (level < CS_LEVELS - 1 || block * 32 + lane < cs.n3)       // (the top level holds n3 entries, not a multiple of 32)
             keep = cs_keep<LIGHT>(ws.cones, n_c, keep_all, __ldg(cs.sph + i), __ldg(cs.w + i));
         const unsigned int mm = __ballot_sync(FULL_MASK, keep);
         if (level == 0) {
+            RT_CHECK(w.qn >= 0 && w.qn + 32 <= CS_QCAP);
             if (keep) ws.queue[w.qn + __popc(mm & ((1u << lane) - 1u))] = block * 32 + lane;
             w.qn += __popc(mm);
             if (w.qn > CS_QCAP - 32) return false;
@@ -255,6 +257,7 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 const int i0 = (task << shift) + r * 32 + lane;
                 valid = r < rpt && i0 < p.n_rays;
                 const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
+                RT_CHECK(!valid || (i >= 0 && i < p.n_rays));
                 slot[r] = valid ? i : -1;
                 const float4 a = valid ? p.in_od0[i] : make_float4(0.f, 0.f, 0.f, 0.f);
                 const float4 b = valid ? p.in_od1[i] : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -310,6 +313,7 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 for (int e0 = 0; e0 < qn; e0 += 32) {
                     const int cnt = min(32, qn - e0);
                     if (lane < cnt) {
+                        RT_CHECK(ws.queue[e0 + lane] >= 0 && ws.queue[e0 + lane] < 32768 * cs.n3);
                         const TriRec* t = cs.tri + ws.queue[e0 + lane];
                         const float4 a = __ldg(&t->a), b = __ldg(&t->b), c = __ldg(&t->c);
                         ws.stage[lane].a = a; ws.stage[lane].b = b; ws.stage[lane].c = c;
@@ -403,6 +407,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
             const int i0 = (task << shift) + r * 32 + lane;
             const bool valid = r < rpt && i0 < p.n_queries;
             const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
+            RT_CHECK(!valid || (i >= 0 && i < p.n_queries));
             slot[r] = valid ? i : -1;
             lid[r] = valid ? p.sq_src[i].y : -1;
             n_valid += valid ? 1 : 0;
@@ -446,6 +451,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
                 if (half[0].state != 2 && half[1].state != 2) { b = half[0]; b2 = half[1]; }
             }
             if (b.state == 2 || n_c + 2 > CS_MAX_CONES) { keep_all = true; break; }     // no usable cone: every triangle is tested
+            RT_CHECK(n_c + 2 <= CS_MAX_CONES);
             if (b.state == 1) { if (lane == 0) ws.cones[n_c] = b; ++n_c; }
             if (b2.state == 1) { if (lane == 0) ws.cones[n_c] = b2; ++n_c; }
         }
@@ -505,6 +511,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
                 for (int e0 = 0; e0 < qn; e0 += 32) {
                     const int cnt = min(32, qn - e0);
                     if (lane < cnt) {
+                        RT_CHECK(ws.queue[e0 + lane] >= 0 && ws.queue[e0 + lane] < 32768 * cs.n3);
                         const TriRec* t = cs.tri + ws.queue[e0 + lane];
                         const float4 a = __ldg(&t->a), b = __ldg(&t->b), c = __ldg(&t->c);
                         ws.stage[lane].a = a; ws.stage[lane].b = b; ws.stage[lane].c = c;
@@ -600,6 +607,7 @@ __global__ void __launch_bounds__(128) k_shadow_fixup(const __grid_constant__ Cu
     const int n_surf = s.rl.n_surf;
     for (int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n; w += gridDim.x * (blockDim.x >> 5)) {
         const int qi = p.fix_list[w];
+        RT_CHECK(qi >= 0 && qi < p.n_queries);
         V3 o, d;
         float dist;
         shadow_query<(MODE != 2)>(p, qi, o, d, dist);

@@ -12,12 +12,26 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace rtb {
 
 #define RT_EPS 1.0e-2f    // EPSILON, MathUtils.h:35: self-hit offset AND degenerate threshold
 
 #define RT_DEV __device__ __forceinline__
+
+// Device-side checks of the CHECKED build (make checked -> ab/checked/librtb200.so; compute-sanitizer is closed on the
+// GPU pool this was developed on, so the bounds the kernels rely on are asserted by the kernels themselves there):
+// a violated check prints where and traps, the call returns RTB200_E_CUDA.  Compiled out of the product library.
+#ifdef RTB200_CHECKED
+#define RT_CHECK(cond)                                                                                        \
+    do {                                                                                                      \
+        if (!(cond)) { printf("RT_CHECK failed: %s (%s:%d, block %d thread %d)\n", #cond, __FILE__, __LINE__, \
+                              (int)blockIdx.x, (int)threadIdx.x); __trap(); }                                 \
+    } while (0)
+#else
+#define RT_CHECK(cond) do { } while (0)
+#endif
 
 template <bool EXACT>
 struct FP {

@@ -524,6 +524,7 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
             const unsigned int m = __ballot_sync(FULL_MASK, facing);
             if (facing) {
                 const int k = (int)(wb.w + s_loff[l * 8 + warp] + __popc(m & below));
+                RT_CHECK(k >= 0 && k < p.n_rays * s.rl.n_light && q >= 0 && q < p.n_rays * s.rl.n_light);
                 p.sq_src[k] = make_int2(i, l | far_bit);
                 p.sq_dst[k] = q++;
                 if (p.sq_key) { p.sq_key[k] = ((unsigned int)l << 27) | (morton30(P.x, P.y, P.z, p.key_lo[0], p.key_lo[1], p.key_lo[2], p.key_inv) >> 3); p.sq_idx[k] = k; }
@@ -544,6 +545,7 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
         int s_refl = -1, s_refr = -1;
         if (want_refl) {
             s_refl = (int)(cbase + __popc(m_refl & below));
+            RT_CHECK(s_refl >= 0 && s_refl < 2 * p.n_rays);
             const V3 rd = reflect3<E>(d, N);
             p.out_od0[s_refl] = make_float4(P.x, P.y, P.z, e_refl);
             p.out_od1[s_refl] = make_float4(rd.x, rd.y, rd.z, 0.0f);
@@ -551,6 +553,7 @@ __global__ void __launch_bounds__(256) k_shade_a(const __grid_constant__ ShadeAP
         }
         if (want_refr) {
             s_refr = (int)(cbase + n_refl + __popc(m_refr & below));
+            RT_CHECK(s_refr >= 0 && s_refr < 2 * p.n_rays);
             V3 n2 = N; float ratio, nior;
             if (ior == mior) { nior = p.f.scene_ior; ratio = FP<E>::div(mior, p.f.scene_ior); n2 = neg3(N); }
             else             { nior = mior;          ratio = FP<E>::div(p.f.scene_ior, mior); }
