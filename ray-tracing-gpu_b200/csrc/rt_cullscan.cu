@@ -119,6 +119,174 @@ RT_DEV bool cs_fill(const CullScene& cs, CsWarpSmem& ws, int n_c, bool keep_all,
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Per-LANE walk -- for the bundles no cone fits (rays of a deep wavefront level: neighbours in space that fly apart in
+// every direction).  Walking the hierarchy with such a bundle keeps everything, i.e. a scan of all triangles by one
+// warp; instead every lane descends the same hierarchy with ITS OWN ray (cs_ray_misses: the cone tests of
+// rt_bundle.cuh for a cone of zero opening, same pad).  The lanes step in lock
+// step -- each tests the 32 entries of its own current block --, the triangles that survive level 0 are tested by that
+// lane alone.  ~50 blocks instead of 10 000 triangles per ray.
+// ---------------------------------------------------------------------------------------
+// One ray as the lanes see it: the half line from `o` along the unit vector `u`, hits within [0, far] of o.
+// LIGHT: o = the light, u = from the light towards the hit point, far = their distance (widened); the shadow ray's own
+// origin -- what the pad of a triangle scales with -- lies within dadd = far of o.
+struct LaneRay {
+    V3 o, u;
+    float far, dadd, padk, slack;
+    bool ok;                          // false: non-finite or degenerate ray -> the lane keeps everything
+};
+RT_DEV LaneRay cs_lane_ray(V3 o, V3 d)
+{
+    LaneRay r;
+    const float l2 = dot3<false>(d, d);
+    r.ok = finite3(o) && finite3(d) && l2 > 1.0e-20f && l2 < 1.0e20f;
+    const float il = r.ok ? rsqrtf(l2) : 0.f;
+    r.o = o; r.u = mk3(d.x * il, d.y * il, d.z * il);
+    r.far = 3.0e38f;
+    r.slack = 4.0e-7f * (fabsf(o.x) + fabsf(o.y) + fabsf(o.z)) + 1.0e-6f;
+    r.dadd = r.slack;
+    r.padk = BUNDLE_PADK * fmaxf(1.0f, sqrtf(l2) * 1.00001f);
+    return r;
+}
+RT_DEV LaneRay cs_lane_query(V3 L, V3 d, float dist)          // d = unit direction TOWARDS the light L
+{
+    LaneRay r;
+    r.ok = finite3(L) && finite3(d) && dist >= 0.f && dist <= 3.0e38f;
+    r.o = L; r.u = neg3(d);
+    r.far = fmaf(dist, 1.0001f, 1.0e-4f);
+    r.slack = 4.0e-7f * (fabsf(L.x) + fabsf(L.y) + fabsf(L.z)) + 1.0e-6f;
+    r.dadd = r.far + r.slack;
+    r.padk = BUNDLE_PADK * 1.0001f;
+    return r;
+}
+// true: no point of the INFLATED sphere (pad of rt_bundle.cuh for origins within |c - o| + dadd + radius) lies on the ray.
+// The tests of bundle_culls / light_cone_culls for a cone of zero opening: distance of the centre to the line against
+// the inflated radius (the cancellation of |v|^2 - s^2 and |u| = 1 +- 3e-7 are covered by 4e-6 |v|^2), sphere entirely
+// behind the origin, sphere entirely beyond the far end.
+RT_DEV bool cs_ray_misses(const LaneRay& r, float4 sph, float w)
+{
+    const float vx = sph.x - r.o.x, vy = sph.y - r.o.y, vz = sph.z - r.o.z;
+    const float s = fmaf(vx, r.u.x, fmaf(vy, r.u.y, vz * r.u.z));
+    const float vv = fmaf(vx, vx, fmaf(vy, vy, vz * vz));
+    const float dist = vv * rsqrtf(fmaxf(vv, 1.0e-30f)) * 1.00001f;
+    const float D = dist + r.dadd + sph.w;
+    const float pad = fmaxf(r.padk * D * w, 3.8e-6f * D);
+    const float rp = fmaf(sph.w + pad, 1.0001f, 1.0e-5f + r.slack + 2.0e-6f * dist);
+    const float perp2 = fmaf(-s, s, vv) - 4.0e-6f * vv;
+    return perp2 > rp * rp || s < -rp || s > r.far + rp;
+}
+
+// leaf(first, mask): the lane's ray may touch triangles first + j for the bits j of mask (called per lane, diverged)
+template <class Leaf>
+RT_DEV void cs_lane_walk(const CullScene& cs, const LaneRay& b, bool active, Leaf&& leaf)
+{
+    int lvl = CS_LEVELS, top_b = 0;
+    unsigned int m1 = 0u, m2 = 0u, m3 = 0u;
+    int b1 = 0, b2 = 0, b3 = 0;
+    bool busy = active;
+    while (__any_sync(FULL_MASK, busy)) {
+        // ---- which block does this lane test now? ------------------------------------------------
+        int level = -1, block = 0;
+        while (busy && level < 0) {
+            if (lvl == CS_LEVELS) {
+                if (top_b >= cs.top_blocks) { busy = false; break; }
+                level = CS_LEVELS - 1; block = top_b++;
+            } else {
+                const unsigned int m = lvl == 1 ? m1 : (lvl == 2 ? m2 : m3);
+                if (m == 0u) { ++lvl; continue; }
+                const int base = lvl == 1 ? b1 : (lvl == 2 ? b2 : b3);
+                block = base + __ffs((int)m) - 1;
+                const unsigned int rest = m & (m - 1u);
+                if (lvl == 1) m1 = rest; else if (lvl == 2) m2 = rest; else m3 = rest;
+                level = lvl - 1;
+            }
+        }
+        // ---- 32 entries of that block against this lane's ray (lock step over the warp) --------------
+        unsigned int mm = 0u;
+        if (level >= 0) {
+            const int i0 = cs_level_offset(cs.n3, level) + block * 32;
+            const int n_in = level == CS_LEVELS - 1 ? min(32, cs.n3 - block * 32) : 32;
+            #pragma unroll 4
+            for (int j = 0; j < 32; ++j) {
+                if (j < n_in) {
+                    const float4 sph = __ldg(cs.sph + i0 + j);
+                    const float w = __ldg(cs.w + i0 + j);
+                    const bool keep = w > 0.f && !(b.ok && cs_ray_misses(b, sph, w));
+                    mm |= keep ? (1u << j) : 0u;
+                }
+            }
+            if (level == 0) { if (mm) leaf(block * 32, mm); }
+            else {
+                if (level == 1) { m1 = mm; b1 = block * 32; } else if (level == 2) { m2 = mm; b2 = block * 32; } else { m3 = mm; b3 = block * 32; }
+                lvl = level;
+            }
+        }
+    }
+}
+
+
+// nearest hit of ONE ray per lane over the triangles (kept out of line: rare path, and the kernels are large enough)
+template <int MODE>
+__device__ __noinline__ int cs_lane_nearest(const CullScene& cs, V3 o, V3 d, bool active, float& best_t, int& best_id)
+{
+    const LaneRay b = cs_lane_ray(o, d);
+    float bt = best_t;
+    int bi = best_id, tests = 0;
+    const float dmax = max_abs3(d);
+    cs_lane_walk(cs, b, active, [&](int first, unsigned int mask) {
+        while (mask) {
+            const TriRec* t = cs.tri + first + __ffs((int)mask) - 1;
+            mask &= mask - 1u;
+            const float4 ra = __ldg(&t->a), rb = __ldg(&t->b), rc = __ldg(&t->c);
+            const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
+            const TriMargins mg = tri_margins(e1, e2, dmax);
+            ++tests;
+            if (!triangle_phase1(o, d, p0, e1, e2, mg)) continue;
+            const float tt = triangle_survivor<MODE>(o, d, p0, e1, e2, bt < 0.f ? 3.0e38f : fmaf(bt, CULL_TREL, CULL_TABS), mg);
+            const int ord = __float_as_int(ra.w);
+            if (tt > RT_EPS && (tt < bt || bt < 0.f || (tt == bt && ord < bi))) { bt = tt; bi = ord; }
+        }
+    });
+    best_t = bt; best_id = bi;
+    return tests;
+}
+
+// shadow filter of ONE query per lane over the triangles; occ / max_ord: the occluder bookkeeping of k_cull_shadow
+template <int MODE>
+__device__ __noinline__ int cs_lane_shadow(const CullScene& cs, const MatRec* __restrict__ mat, V3 L, V3 o, V3 d, float dist, bool active,
+                                           float& fr, float& fg, float& fb, unsigned int& occ, int& max_ord)
+{
+    const LaneRay b = cs_lane_query(L, d, dist);
+    float r_ = fr, g_ = fg, b_ = fb;
+    unsigned int st = occ;
+    int mo = max_ord, tests = 0;
+    const float dmax = max_abs3(d), tlim = fmaf(dist, CULL_TREL, CULL_TABS);
+    cs_lane_walk(cs, b, active, [&](int first, unsigned int mask) {
+        while (mask) {
+            const TriRec* t = cs.tri + first + __ffs((int)mask) - 1;
+            mask &= mask - 1u;
+            if (r_ == 0.f && g_ == 0.f && b_ == 0.f) return;             // 0 * finite stays 0
+            const float4 ra = __ldg(&t->a), rb = __ldg(&t->b), rc = __ldg(&t->c);
+            const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
+            const TriMargins mg = tri_margins(e1, e2, dmax);
+            ++tests;
+            if (!triangle_phase1(o, d, p0, e1, e2, mg)) continue;
+            const float tt = triangle_survivor<MODE>(o, d, p0, e1, e2, tlim, mg);
+            if (tt > RT_EPS && tt < dist) {
+                const int ord = __float_as_int(ra.w), m = __float_as_int(rb.w);
+                const float4 m0 = mat[m].m0;
+                const float kt = mat[m].m2.x;
+                r_ = __fmul_rn(r_, __fmul_rn(m0.x, kt)); g_ = __fmul_rn(g_, __fmul_rn(m0.y, kt)); b_ = __fmul_rn(b_, __fmul_rn(m0.z, kt));
+                if (ord < mo) st |= 4u;
+                if ((st & 3u) < 3u) ++st;
+                mo = max(mo, ord);
+            }
+        }
+    });
+    fr = r_; fg = g_; fb = b_; occ = st; max_ord = mo;
+    return tests;
+}
+
 // quadrics of centred form  sum q_i (x_i - c_i)^2 = rhs, q_i > 0 (r3 = c | rhs, rhs > 0): bounding sphere of the region
 // outside of which the reference's discriminant cannot come out positive for any origin within D of the centre
 // (the margin of quadric_miss, rt_resident.cu / DESIGN.md 5.3: rhs * 1.05 + 2e-5 * M, M = sum q_i (o_i^2 + c_i^2) with
@@ -216,7 +384,10 @@ RT_DEV int cs_nearest_cones(const V3* o, const V3* d, const bool* use, Bundle* c
 // Nearest hit (Scene.cpp:1705-1720).  One warp task = 128 rays: PRIMARY a 16 x 8 block of the sample lattice
 // (thread = a 2 x 2 quad, rays generated on the fly), otherwise 128 consecutive queue entries.
 // ---------------------------------------------------------------------------------------
-template <int MODE, bool PRIMARY>
+// LANE = false: the kernel proper; a task no cone fits is put on cp.lane_list instead of being traced.
+// LANE = true:  traces the tasks of that list lane by lane (cs_lane_nearest) -- its own kernel so that the rare path
+//               costs the common one neither registers nor instruction cache.
+template <int MODE, bool PRIMARY, bool LANE>
 __global__ void __launch_bounds__(CS_THREADS, CS_MIN_CTAS)
 k_cull_nearest(const __grid_constant__ CullTraceParams cp)
 {
@@ -233,9 +404,14 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
 
     for (;;) {
         int task = 0;
-        if (lane == 0) task = (int)atomicAdd(cp.task_counter, 1u);
+        if (lane == 0) task = (int)atomicAdd(LANE ? cp.lane_task_counter : cp.task_counter, 1u);
         task = __shfl_sync(FULL_MASK, task, 0);
-        if (task >= n_tasks) break;
+        int only_r = -1;                               // LANE: a listed task is split into its ray slots, one per warp
+        if (LANE) {
+            if (task >= (int)min(*cp.lane_count, (unsigned int)cp.lane_cap) * rpt) break;
+            only_r = task % rpt;
+            task = cp.lane_list[task / rpt];
+        } else if (task >= n_tasks) break;
 
         V3 o[ST_RPT], d[ST_RPT];
         float best_t[ST_RPT], tlim[ST_RPT];
@@ -250,12 +426,12 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 const int lx = (tx << 4) + ((lane & 7) << 1) + (r & 1);
                 const int cy = (ty << 3) + ((lane >> 3) << 1) + (r >> 1);
                 const int ly = p.chunk_ly0 + cy;
-                valid = lx < p.f.LW && cy < p.chunk_rows && ly < p.local_LH;
+                valid = lx < p.f.LW && cy < p.chunk_rows && ly < p.local_LH && (!LANE || r == only_r);
                 slot[r] = valid ? cy * p.f.LW + lx : -1;
                 primary_ray<(MODE != 2)>(p.f, valid ? lx : 0, valid ? global_lattice_row(p.f, ly) : 0, o[r], d[r]);
             } else {
                 const int i0 = (task << shift) + r * 32 + lane;
-                valid = r < rpt && i0 < p.n_rays;
+                valid = r < rpt && i0 < p.n_rays && (!LANE || r == only_r);
                 const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
                 RT_CHECK(!valid || (i >= 0 && i < p.n_rays));
                 slot[r] = valid ? i : -1;
@@ -271,9 +447,17 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
         float dmax = 0.f;                             // largest |direction component| of this thread's rays (filter margins)
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) dmax = fmaxf(dmax, max_abs3(d[r]));
-        bool keep_all;
-        const int n_c = cs_nearest_cones(o, d, use, ws.cones, lane, keep_all);
+        bool keep_all = true;
+        const int n_c = LANE ? 0 : cs_nearest_cones(o, d, use, ws.cones, lane, keep_all);
         n_valid = __reduce_add_sync(FULL_MASK, n_valid);
+        bool to_lanes = keep_all;                                          // no cone fits, or only wide ones: the lane kernel takes this task
+        for (int k = 0; k < n_c; ++k) to_lanes = to_lanes || ws.cones[k].sin_t > cp.lane_sin;
+        if (!LANE && to_lanes && n_valid > 0 && cp.lane_list) {
+            unsigned int k = 0;
+            if (lane == 0) k = atomicAdd(cp.lane_count, 1u);
+            k = __shfl_sync(FULL_MASK, k, 0);
+            if ((int)k < cp.lane_cap) { if (lane == 0) cp.lane_list[k] = task; continue; }
+        }
 
         // ---- triangles ------------------------------------------------------------------------
         auto test_triangle = [&](const float4 ra, const float4 rb, const float4 rc) {
@@ -301,7 +485,14 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 }
             }
         };
-        if (n_c > 0 || keep_all) {
+        if (LANE) {
+            // no cone fits these rays: every lane walks the hierarchy with its own rays, one after the other
+            int tests = 0;
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r)
+                if (r < rpt) tests += cs_lane_nearest<MODE>(cs, o[r], d[r], slot[r] >= 0, best_t[r], best_id[r]);
+            exec_rays += (unsigned long long)__reduce_add_sync(FULL_MASK, tests);
+        } else if (n_c > 0 || keep_all) {
             CsWalk wk;
             cs_walk_init(wk);
             bool finished;
@@ -373,7 +564,7 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
 // Shadow filter (Scene.cpp:1842-1861): product of colour * kt over every surface hit strictly between EPSILON
 // and the light.  One warp task = 128 consecutive (ray, light) queries of the queue shade-A wrote light by light.
 // ---------------------------------------------------------------------------------------
-template <int MODE>
+template <int MODE, bool LANE>           // LANE: see k_cull_nearest
 __global__ void __launch_bounds__(CS_THREADS, CS_MIN_CTAS)
 k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 {
@@ -393,9 +584,14 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 
     for (;;) {
         int task = 0;
-        if (lane == 0) task = (int)atomicAdd(cp.task_counter, 1u);
+        if (lane == 0) task = (int)atomicAdd(LANE ? cp.lane_task_counter : cp.task_counter, 1u);
         task = __shfl_sync(FULL_MASK, task, 0);
-        if (task >= n_tasks) break;
+        int only_r = -1;
+        if (LANE) {
+            if (task >= (int)min(*cp.lane_count, (unsigned int)cp.lane_cap) * rpt) break;
+            only_r = task % rpt;
+            task = cp.lane_list[task / rpt];
+        } else if (task >= n_tasks) break;
 
         V3 o[ST_RPT], d[ST_RPT];
         float dist[ST_RPT], fr[ST_RPT], fg[ST_RPT], fb[ST_RPT];
@@ -405,7 +601,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) {
             const int i0 = (task << shift) + r * 32 + lane;
-            const bool valid = r < rpt && i0 < p.n_queries;
+            const bool valid = r < rpt && i0 < p.n_queries && (!LANE || r == only_r);
             const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
             RT_CHECK(!valid || (i >= 0 && i < p.n_queries));
             slot[r] = valid ? i : -1;
@@ -424,7 +620,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 
         // ---- the warp's cone(s) per light present: one, or two around the two most distant directions ----------
         int n_c = 0;
-        bool keep_all = n_lights > 32;
+        bool keep_all = LANE || n_lights > 32;
         for (int l = 0; l < n_lights && !keep_all; ++l) {
             if (!((light_bits >> l) & 1u)) continue;
             const V3 L = f4_xyz(s.light[l].l0);
@@ -457,6 +653,14 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
         }
         if (keep_all) n_c = 0;
         __syncwarp();
+        bool to_lanes = keep_all;                                          // no cone fits, or only wide ones: the lane kernel takes this task
+        for (int k = 0; k < n_c; ++k) to_lanes = to_lanes || ws.cones[k].sin_t > cp.lane_sin;
+        if (!LANE && to_lanes && n_valid > 0 && cp.lane_list) {
+            unsigned int k = 0;
+            if (lane == 0) k = atomicAdd(cp.lane_count, 1u);
+            k = __shfl_sync(FULL_MASK, k, 0);
+            if ((int)k < cp.lane_cap) { if (lane == 0) cp.lane_list[k] = task; continue; }
+        }
 
         auto occluder = [&](int r, int ord, int mat) {
             const float4 m0 = s.mat[mat].m0;
@@ -499,7 +703,21 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
         };
         bool warp_done = false;
         tests_tri += (unsigned long long)n_valid * (unsigned long long)cs.n_tri;
-        if (n_valid > 0) {
+        if (LANE) {
+            // no cone fits these queries: every lane walks the hierarchy with its own queries, one after the other
+            int tests = 0;
+            #pragma unroll
+            for (int r = 0; r < ST_RPT; ++r)
+                if (r < rpt) {
+                    unsigned int occ = s_occ[r][tid];
+                    int mo = s_ord[r][tid];
+                    const V3 L = f4_xyz(s.light[max(lid[r], 0)].l0);
+                    tests += cs_lane_shadow<MODE>(cs, s.mat, L, o[r], d[r], dist[r], slot[r] >= 0, fr[r], fg[r], fb[r], occ, mo);
+                    s_occ[r][tid] = (unsigned char)occ; s_ord[r][tid] = mo;
+                }
+            exec_rays += (unsigned long long)__reduce_add_sync(FULL_MASK, tests);
+            warp_done = all_zero();
+        } else if (n_valid > 0) {
             CsWalk wk;
             cs_walk_init(wk);
             bool finished;
@@ -598,22 +816,27 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 // Scene.cpp:107) 32 surfaces at a time; the occluders of a round are multiplied in slot order.
 // ---------------------------------------------------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(128) k_shadow_fixup(const __grid_constant__ CullShadowParams cp)
+__global__ void __launch_bounds__(256) k_shadow_fixup(const __grid_constant__ CullShadowParams cp)
 {
+    // one CTA per listed query: the 8 warps test surfaces 256 at a time, the materials of the occluders of a round are
+    // gathered in slot order (a prefix sum over the 8 ballots) and thread 0 multiplies them in that order
+    __shared__ int s_mat[256];
+    __shared__ int s_cnt[8];
+    __shared__ float s_f[3];
     const ShadowParams& p = cp.s;
     const DeviceScene& s = p.s;
-    const int lane = threadIdx.x & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min((int)*p.fix_count, p.fix_cap);
     const int n_surf = s.rl.n_surf;
-    for (int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n; w += gridDim.x * (blockDim.x >> 5)) {
+    for (int w = blockIdx.x; w < n; w += gridDim.x) {
         const int qi = p.fix_list[w];
         RT_CHECK(qi >= 0 && qi < p.n_queries);
         V3 o, d;
         float dist;
         shadow_query<(MODE != 2)>(p, qi, o, d, dist);
-        float fr = 1.0f, fg = 1.0f, fb = 1.0f;
-        for (int k0 = 0; k0 < n_surf; k0 += 32) {
-            const int k = k0 + lane;
+        if (tid == 0) { s_f[0] = 1.0f; s_f[1] = 1.0f; s_f[2] = 1.0f; }
+        for (int k0 = 0; k0 < n_surf; k0 += 256) {
+            const int k = k0 + tid;
             bool hit = false;
             int mat = 0;
             if (k < n_surf) {
@@ -630,19 +853,27 @@ __global__ void __launch_bounds__(128) k_shadow_fixup(const __grid_constant__ Cu
                 }
                 hit = tt > RT_EPS && tt < dist;
             }
-            unsigned int mask = __ballot_sync(FULL_MASK, hit);
-            while (mask) {
-                const int src = __ffs((int)mask) - 1;
-                mask &= mask - 1u;
-                const int m = __shfl_sync(FULL_MASK, mat, src);
-                const float4 m0 = s.mat[m].m0;
-                const float kt = s.mat[m].m2.x;
-                fr = __fmul_rn(fr, __fmul_rn(m0.x, kt));
-                fg = __fmul_rn(fg, __fmul_rn(m0.y, kt));
-                fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+            const unsigned int mask = __ballot_sync(FULL_MASK, hit);
+            if (lane == 0) s_cnt[warp] = __popc(mask);
+            __syncthreads();
+            int base = 0, total = 0;
+            #pragma unroll
+            for (int q = 0; q < 8; ++q) { if (q < warp) base += s_cnt[q]; total += s_cnt[q]; }
+            if (hit) s_mat[base + __popc(mask & ((1u << lane) - 1u))] = mat;
+            __syncthreads();
+            if (tid == 0 && total > 0) {
+                float fr = s_f[0], fg = s_f[1], fb = s_f[2];
+                for (int e = 0; e < total; ++e) {
+                    const float4 m0 = s.mat[s_mat[e]].m0;
+                    const float kt = s.mat[s_mat[e]].m2.x;
+                    fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+                }
+                s_f[0] = fr; s_f[1] = fg; s_f[2] = fb;
             }
+            __syncthreads();
         }
-        if (lane == 0) p.filter[p.sq_dst ? p.sq_dst[qi] : qi] = make_float4(fr, fg, fb, 0.f);
+        if (tid == 0) p.filter[p.sq_dst ? p.sq_dst[qi] : qi] = make_float4(s_f[0], s_f[1], s_f[2], 0.f);
+        __syncthreads();
     }
 }
 
@@ -663,11 +894,22 @@ cudaError_t launch_cull_nearest(const CullTraceParams& p, int sm_count, cudaStre
     if (n_tasks <= 0) return cudaSuccess;
     const int blocks = cs_grid(n_tasks, sm_count);
     if (p.t.primary) {
-        if (p.t.mode == 2) k_cull_nearest<2, true><<<blocks, CS_THREADS, 0, st>>>(p);
-        else               k_cull_nearest<0, true><<<blocks, CS_THREADS, 0, st>>>(p);
+        if (p.t.mode == 2) k_cull_nearest<2, true, false><<<blocks, CS_THREADS, 0, st>>>(p);
+        else               k_cull_nearest<0, true, false><<<blocks, CS_THREADS, 0, st>>>(p);
     } else {
-        if (p.t.mode == 2) k_cull_nearest<2, false><<<blocks, CS_THREADS, 0, st>>>(p);
-        else               k_cull_nearest<0, false><<<blocks, CS_THREADS, 0, st>>>(p);
+        if (p.t.mode == 2) k_cull_nearest<2, false, false><<<blocks, CS_THREADS, 0, st>>>(p);
+        else               k_cull_nearest<0, false, false><<<blocks, CS_THREADS, 0, st>>>(p);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess || !p.lane_list) return e;
+    // the tasks no cone fitted (the count is read on the device; usually none, or the rays of the deep levels)
+    const int lane_blocks = cs_grid(n_tasks, sm_count);
+    if (p.t.primary) {
+        if (p.t.mode == 2) k_cull_nearest<2, true, true><<<lane_blocks, CS_THREADS, 0, st>>>(p);
+        else               k_cull_nearest<0, true, true><<<lane_blocks, CS_THREADS, 0, st>>>(p);
+    } else {
+        if (p.t.mode == 2) k_cull_nearest<2, false, true><<<lane_blocks, CS_THREADS, 0, st>>>(p);
+        else               k_cull_nearest<0, false, true><<<lane_blocks, CS_THREADS, 0, st>>>(p);
     }
     return cudaGetLastError();
 }
@@ -678,15 +920,19 @@ cudaError_t launch_cull_shadow(const CullShadowParams& p, int sm_count, cudaStre
     const int n_tasks = (p.s.n_queries + per - 1) / per;
     if (n_tasks <= 0) return cudaSuccess;
     const int blocks = cs_grid(n_tasks, sm_count);
-    if (p.s.mode == 2) k_cull_shadow<2><<<blocks, CS_THREADS, 0, st>>>(p);
-    else               k_cull_shadow<0><<<blocks, CS_THREADS, 0, st>>>(p);
+    if (p.s.mode == 2) k_cull_shadow<2, false><<<blocks, CS_THREADS, 0, st>>>(p);
+    else               k_cull_shadow<0, false><<<blocks, CS_THREADS, 0, st>>>(p);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess || !p.lane_list) return e;
+    if (p.s.mode == 2) k_cull_shadow<2, true><<<blocks, CS_THREADS, 0, st>>>(p);
+    else               k_cull_shadow<0, true><<<blocks, CS_THREADS, 0, st>>>(p);
     return cudaGetLastError();
 }
 
 cudaError_t launch_shadow_fixup(const CullShadowParams& p, int sm_count, cudaStream_t st)
 {
-    if (p.s.mode == 2) k_shadow_fixup<2><<<sm_count, 128, 0, st>>>(p);
-    else               k_shadow_fixup<0><<<sm_count, 128, 0, st>>>(p);
+    if (p.s.mode == 2) k_shadow_fixup<2><<<sm_count * 4, 256, 0, st>>>(p);
+    else               k_shadow_fixup<0><<<sm_count * 4, 256, 0, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -28,7 +28,12 @@ struct CullTraceParams {
     int           task_shift;        // log2 of the rays per task: 7 (four per lane), or 5 (one per lane) for levels with few
                                      // rays -- more tasks than warps, tighter cones, and a bundle nothing can cull costs 1/4
     const int*    perm;              // null, or: the i-th ray of the launch is queue entry perm[i] (rays sorted by the
-                                     // surface they leave, see ShadeAParams::child_key)
+                                     // place they start at, see ShadeAParams::child_key)
+    int*          lane_list;         // tasks no cone fits: listed by the kernel proper, traced lane by lane by a second
+    unsigned int* lane_count;        // launch (null: such tasks keep every triangle and scan them all)
+    unsigned int* lane_task_counter;
+    int           lane_cap;
+    float         lane_sin;          // a bundle with a cone wider than this (sine of the half angle) also goes to the lanes
 };
 
 struct CullShadowParams {
@@ -37,6 +42,11 @@ struct CullShadowParams {
     unsigned int* task_counter;
     int           task_shift;        // as in CullTraceParams
     const int*    perm;              // null, or: the i-th query of the launch is queue entry perm[i] (sorted by light, place)
+    int*          lane_list;         // as in CullTraceParams
+    unsigned int* lane_count;
+    unsigned int* lane_task_counter;
+    int           lane_cap;
+    float         lane_sin;          // a bundle with a cone wider than this (sine of the half angle) also goes to the lanes
 };                                   // (fix-up list: ShadowParams::fix_list / fix_count / fix_cap)
 
 cudaError_t launch_cull_nearest(const CullTraceParams& p, int sm_count, cudaStream_t st);

@@ -32,7 +32,7 @@ namespace rtb {
 
 struct StreamBufs {                // per-context scratch of the streamed path (lives in the ctx levels + these)
     DevBuf hit, hitP, hitN, q_base, sq0, sq1, sq_src, sq_dst, filter;
-    DevBuf tasks, fix, far;        // per-level counters (6 words per level), fix-up list, LBVH far-ray list
+    DevBuf tasks, fix, far, lane;  // per-level counters (12 words per level), fix-up list, LBVH far-ray list, lane-walk task list
     DevBuf ckey, cidx, ckey2, cperm, qkey, qidx, qkey2, qperm, sort_tmp;   // culled scan: (key, index) pairs of the children / queries of a level and their sorted forms
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // per-stage stopwatch
 };
@@ -69,7 +69,7 @@ void stream_release(rtb200_ctx* c)
 {
     if (!c->stream_scratch) return;
     StreamBufs* b = static_cast<StreamBufs*>(c->stream_scratch);
-    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->sq_dst.release(); b->filter.release(); b->tasks.release(); b->fix.release(); b->far.release();
+    b->hit.release(); b->hitP.release(); b->hitN.release(); b->q_base.release(); b->sq0.release(); b->sq1.release(); b->sq_src.release(); b->sq_dst.release(); b->filter.release(); b->tasks.release(); b->fix.release(); b->far.release(); b->lane.release();
     b->ckey.release(); b->cidx.release(); b->ckey2.release(); b->cperm.release(); b->qkey.release(); b->qidx.release(); b->qkey2.release(); b->qperm.release(); b->sort_tmp.release();
     for (auto& e : b->ev) if (e) cudaEventDestroy(e);
     delete b;
@@ -121,6 +121,11 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     // a level with fewer rays than this is traced one ray per lane (tasks of 32): see CullTraceParams::task_shift
     int small_level = c->sm_count * 16 * 128 * 3;
     if (const char* e = getenv("RTB200_SMALL_LEVEL")) small_level = atoi(e);
+    // cones wider than this are not worth a warp walk (CullTraceParams::lane_sin).  Measured on config 3 (sweep 1.0 ..
+    // 0.12, one call): nearest-hit rays 8.3 -> 5.6 ms at 0.12-0.2, shadow queries best at 0.5 (15.2 ms; 18.4 at 0.12)
+    float lane_sin = 0.15f, lane_sin_shadow = 0.5f;
+    if (const char* e = getenv("RTB200_LANE_SIN")) lane_sin = (float)atof(e);
+    if (const char* e = getenv("RTB200_LANE_SIN_SHADOW")) lane_sin_shadow = (float)atof(e);
     bool rays_sorted = false;                   // the rays of the level about to be traced have a permutation in sb->cperm
     const int k = fp.k;
     const int local_LH = local_rows * k;
@@ -139,7 +144,8 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     if ((e = c->counters.ensure(sizeof(unsigned) * n_counters)) != cudaSuccess) return set_cuda_error(c, e, "counters");
     unsigned* h_cnt = c->h_small.as<unsigned>();
     unsigned* d_cnt = c->counters.as<unsigned>();
-    const size_t n_tasks_words = 6 * ((size_t)std::max(fr->max_bounces, 0) + 2);      // per level: nearest tasks, shadow tasks, fix-ups, far rays, far queries, -
+    // per level: nearest tasks, shadow tasks, fix-ups, far rays, far queries, -, lane-walk tasks (nearest: count, counter; shadow: count, counter)
+    const size_t n_tasks_words = 12 * ((size_t)std::max(fr->max_bounces, 0) + 2);
     if ((e = sb->tasks.ensure(sizeof(unsigned) * n_tasks_words)) != cudaSuccess) return set_cuda_error(c, e, "task counters");
     unsigned* d_tasks = sb->tasks.as<unsigned>();
     unsigned max_level_seen = 0, chunks = 0;
@@ -202,16 +208,23 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
             if (use_bvh) {
                 if (level > 0) {                   // secondary rays may start beyond the radius the boxes are padded for
                     if ((e = sb->far.ensure(sizeof(int) * n)) != cudaSuccess) return set_cuda_error(c, e, "far list");
-                    tp.far_list = sb->far.as<int>(); tp.far_count = d_tasks + 6 * level + 3; tp.far_cap = n_in;
+                    tp.far_list = sb->far.as<int>(); tp.far_count = d_tasks + 12 * level + 3; tp.far_cap = n_in;
                 }
                 SCU(launch_bvh_nearest(tp, c->stream));
                 if (level > 0) { SCU(launch_bvh_far_nearest(tp, c->sm_count, c->stream)); ++*launches; }
             }
             else if (cullscan) {
                 CullTraceParams ctp;
-                ctp.t = tp; ctp.cs = cull; ctp.task_counter = d_tasks + 6 * level;
+                ctp.t = tp; ctp.cs = cull; ctp.task_counter = d_tasks + 12 * level;
                 ctp.perm = (level > 0 && rays_sorted) ? sb->cperm.as<int>() : nullptr;
                 ctp.task_shift = (level > 0 && n_in < small_level) ? 5 : 7;
+                {
+                    const int n_tasks = tp.primary ? ((fp.LW + 15) / 16) * ((rows + 7) / 8) : (n_in + (1 << ctp.task_shift) - 1) >> ctp.task_shift;
+                    if ((e = sb->lane.ensure(sizeof(int) * (size_t)std::max(n_tasks, 1))) != cudaSuccess) return set_cuda_error(c, e, "lane list");
+                    ctp.lane_list = sb->lane.as<int>(); ctp.lane_cap = n_tasks;
+                    ctp.lane_count = d_tasks + 12 * level + 6; ctp.lane_task_counter = d_tasks + 12 * level + 7; ctp.lane_sin = lane_sin;
+                    ++*launches;
+                }
                 SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
             }
             else         SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
@@ -291,12 +304,20 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
                 {
                     // queries whose product order matters go on a list and are redone in insertion order (every path)
                     if ((e = sb->fix.ensure(sizeof(int) * (size_t)n_sq)) != cudaSuccess) return set_cuda_error(c, e, "fix-up list");
-                    unsigned* tk = sb->tasks.as<unsigned>() + 6 * level;
+                    unsigned* tk = sb->tasks.as<unsigned>() + 12 * level;
                     sp.fix_count = tk + 2; sp.fix_list = sb->fix.as<int>(); sp.fix_cap = n_sq;
                     CullShadowParams csp;
                     csp.s = sp; csp.cs = cull; csp.task_counter = tk + 1;
                     csp.perm = queries_sorted ? sb->qperm.as<int>() : nullptr;
                     csp.task_shift = (level > 0 && n_sq < small_level) ? 5 : 7;
+                    csp.lane_list = nullptr; csp.lane_count = nullptr; csp.lane_task_counter = nullptr; csp.lane_cap = 0; csp.lane_sin = lane_sin_shadow;
+                    if (cullscan && group_queries) {
+                        const int n_tasks = (n_sq + (1 << csp.task_shift) - 1) >> csp.task_shift;
+                        if ((e = sb->lane.ensure(sizeof(int) * (size_t)std::max(n_tasks, 1))) != cudaSuccess) return set_cuda_error(c, e, "lane list");
+                        csp.lane_list = sb->lane.as<int>(); csp.lane_cap = n_tasks;
+                        csp.lane_count = tk + 8; csp.lane_task_counter = tk + 9;
+                        ++*launches;
+                    }
                     if (use_bvh) {
                         if ((e = sb->far.ensure(sizeof(int) * (size_t)n_sq)) != cudaSuccess) return set_cuda_error(c, e, "far list");
                         sp.far_list = sb->far.as<int>(); sp.far_count = tk + 4; sp.far_cap = n_sq;
@@ -397,6 +418,11 @@ int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
         SCU(cudaMemsetAsync(sb->tasks.p, 0, 4, c->stream));
         ctp.task_counter = sb->tasks.as<unsigned>();
         ctp.perm = nullptr; ctp.task_shift = 7;
+        const int n_tasks = (n + 127) / 128;
+        if ((e = sb->lane.ensure(sizeof(int) * (size_t)n_tasks)) != cudaSuccess) return set_cuda_error(c, e, "lane list");
+        SCU(cudaMemsetAsync(sb->tasks.p, 0, 16, c->stream));
+        ctp.lane_list = sb->lane.as<int>(); ctp.lane_cap = n_tasks;
+        ctp.lane_count = sb->tasks.as<unsigned>() + 1; ctp.lane_task_counter = sb->tasks.as<unsigned>() + 2; ctp.lane_sin = 0.15f;
         SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
     }
     else                          SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
