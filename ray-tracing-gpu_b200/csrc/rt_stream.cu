@@ -95,9 +95,10 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     // tiled kernels: level-0 rays by 16x16 patches and each CTA's shadow queries light by light, so that a warp of the
     // trace kernels holds a compact bundle (changes the ORDER of the queues, no value: frames stay bit-identical;
     // config 3: shadow stage 112 -> 60 ms, profiles/r1_c3_ab_query_grouping.log)
-    // (LBVH: only the patches, opt-in with RTB200_BVH_TILE_RAYS=1 until measured -- its shadow kernel has a warp
-    // mapping of its own that relies on the queries of a ray being contiguous)
-    const bool tile_rays = query_grouping_enabled() && (!use_bvh || getenv("RTB200_BVH_TILE_RAYS") != nullptr);
+    // (LBVH: only the patches -- its shadow kernel has a warp mapping of its own that relies on the queries of a ray
+    // being contiguous; measured in round 2: config 5 507 -> 480 ms, config 4 unchanged)
+    bool tile_rays = query_grouping_enabled();
+    if (use_bvh) if (const char* e = getenv("RTB200_BVH_TILE_RAYS")) tile_rays = tile_rays && atoi(e) != 0;   // (LBVH: the patches only; =0 for A/B runs)
     const bool group_queries = tile_rays && !use_bvh && c->ds.rl.n_light >= 1 && c->ds.rl.n_light <= 8;
     if (use_bvh) {                               // boxes must be padded for rays that start at the camera
         const int rc = bvh_prepare(c, fr->cam_pos, 1);
