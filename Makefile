@@ -12,7 +12,7 @@ HOSTCXX := /usr/bin/g++
 
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -ccbin $(HOSTCXX) \
            -Xcompiler -fPIC,-Wall,-Wno-unused-function -Xptxas -warn-spills
-CUOBJS  := $(addprefix $(OBJDIR)/,rt_api.o rt_resident.o rt_stream.o rt_trace.o rt_comm.o rt_peak.o rt_bvh.o rt_sequence.o rt_pack.o rt_cullscan.o)
+CUOBJS  := $(addprefix $(OBJDIR)/,rt_api.o rt_resident.o rt_stream.o rt_trace.o rt_comm.o rt_peak.o rt_bvh.o rt_sequence.o rt_pack.o rt_cullscan.o rt_noalloc.o)
 CUHDRS  := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) $(ROOT)include/rtb200.h
 
 all: lib host oracle

@@ -224,6 +224,20 @@ int  rtb200_trace_nearest(rtb200_ctx* ctx, int n, const float* origin3, const fl
 int  rtb200_trace_shadow(rtb200_ctx* ctx, int n, const float* point3, const float* light3,
                          uint32_t flags, float* out_filter3);
 
+/* rtb200_trace_nearest WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same results as rtb200_trace_nearest, but the device-side staging of the rays and
+ * of the answers lives in a static __device__ array inside the library (RTB200_STATIC_QUERY_MAX rays x 44 bytes =
+ * 2.75 MB, held by every GPU that loads the library until the process exits); the call makes no cudaMalloc / cudaFree
+ * and calls no allocating library routine.  Limits: n <= RTB200_STATIC_QUERY_MAX (more: RTB200_E_ARG, split the batch);
+ * only scenes that take the scene-resident query path (packed scene <= 64 KB, or RTB200_F_FORCE_RESIDENT; not
+ * RTB200_F_FORCE_STREAM / RTB200_F_USE_BVH, whose kernels keep scratch structures of their own: RTB200_E_ARG).
+ * All calls on one GPU share the array (it keeps the last call's contents; nothing in it needs clearing): calls that
+ * overlap on the same GPU -- two contexts on one device driven from two threads -- race and must be serialised. */
+#define RTB200_STATIC_QUERY_MAX 65536
+int  rtb200_trace_nearest_static(rtb200_ctx* ctx, int n, const float* origin3, const float* dir3,
+                                 uint32_t flags, int32_t* out_order, float* out_t, float* out_normal3);
+
 /* --- multi-GPU ---------------------------------------------------------------------------- */
 #define RTB200_UNIQUE_ID_BYTES 128
 /* Rank 0 obtains an id, distributes the bytes by any means (torch.distributed, a file, MPI),

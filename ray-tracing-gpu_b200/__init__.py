@@ -22,7 +22,7 @@ LIB_PATH = os.path.abspath(os.environ["RTB200_LIB"]) if os.environ.get("RTB200_L
 EXPORTS = [
     "rtb200_abi_version", "rtb200_create", "rtb200_destroy", "rtb200_error_string", "rtb200_last_error",
     "rtb200_set_scene", "rtb200_validate_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_render_sequence", "rtb200_read_frame",
-    "rtb200_trace_nearest", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init", "rtb200_band_map",
+    "rtb200_trace_nearest", "rtb200_trace_nearest_static", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init", "rtb200_band_map",
     "rtb200_host_alloc", "rtb200_host_free", "rtb200_host_register", "rtb200_host_unregister", "rtb200_set_sharding", "rtb200_measure_fp32_peak", "rtb200_fp32_peak_detail", "rtb200_device_info",
     "rtb200_timer_mark", "rtb200_timer_elapsed",
 ]
@@ -59,6 +59,7 @@ def lib():
         L.rtb200_read_frame.argtypes = [vp, vp, vp]
         L.rtb200_render_sequence.argtypes = [vp, vp, C.c_int, vp, vp]
         L.rtb200_trace_nearest.argtypes = [vp, C.c_int, vp, vp, C.c_uint32, vp, vp, vp]
+        L.rtb200_trace_nearest_static.argtypes = [vp, C.c_int, vp, vp, C.c_uint32, vp, vp, vp]
         L.rtb200_trace_shadow.argtypes = [vp, C.c_int, vp, vp, C.c_uint32, vp]
         L.rtb200_comm_unique_id.argtypes = [vp]
         L.rtb200_comm_init.argtypes = [vp, C.c_int, C.c_int, vp]
@@ -237,6 +238,18 @@ class Renderer:
         nrm = np.empty((n, 3), np.float32)
         self._check(self.L.rtb200_trace_nearest(self.h, n, org.ctypes.data, dirs.ctypes.data, flags,
                                                 idx.ctypes.data, t.ctypes.data, nrm.ctypes.data))
+        return idx, t, nrm
+
+    def trace_nearest_static(self, org, dirs, flags=0):
+        """rtb200_trace_nearest_static: the same query with its scratch in static device memory (no allocation)."""
+        org = np.ascontiguousarray(org, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        n = len(org)
+        idx = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        nrm = np.empty((n, 3), np.float32)
+        self._check(self.L.rtb200_trace_nearest_static(self.h, n, org.ctypes.data, dirs.ctypes.data, flags,
+                                                       idx.ctypes.data, t.ctypes.data, nrm.ctypes.data))
         return idx, t, nrm
 
     def trace_shadow(self, pts, lights, flags=0):
