@@ -31,7 +31,7 @@ $(LIBDIR)/librtb200.so: $(CUOBJS)
 # and the headless CLI that replaces Main.cpp's GLUT window.
 HOSTSRC := $(wildcard $(HOST)/src/*.cpp)
 HOSTHDR := $(wildcard $(HOST)/include/*.h) $(wildcard $(HOST)/src/*.hpp)
-HOSTFLAGS := -std=c++17 -O2 -ffp-contract=off -fPIC -Wall -I$(HOST)/include -I$(HOST)/src -I$(ROOT)include
+HOSTFLAGS := -std=c++17 -O2 -ffp-contract=off -fPIC -Wall -pthread -I$(HOST)/include -I$(HOST)/src -I$(ROOT)include
 
 host: $(LIBDIR)/librtb200_scene.so $(LIBDIR)/rt_cli
 

@@ -277,6 +277,8 @@ int  rtb200_measure_fp32_peak(rtb200_ctx* ctx, double* tflops, double* sm_mhz);
  * (hardware limit 128), [9] SM count.  TFLOP/s = 2 x [1] x [2] x [3] / [4].  n >= 10. */
 #define RTB200_PEAK_DETAIL_COUNT 10
 int  rtb200_fp32_peak_detail(rtb200_ctx* ctx, double* detail, int n);
+/* Number of CUDA devices this process sees (what rt_cli --gpus g spreads its contexts over). */
+int  rtb200_device_count(int* n);
 /* Device properties the benchmark reports. */
 int  rtb200_device_info(rtb200_ctx* ctx, int* sm_count, int* l2_bytes, char* name, int name_len);
 /* Device-side stopwatch over SEVERAL calls (benchmarks time K frames as one region): records a

@@ -23,7 +23,7 @@ EXPORTS = [
     "rtb200_abi_version", "rtb200_create", "rtb200_destroy", "rtb200_error_string", "rtb200_last_error",
     "rtb200_set_scene", "rtb200_validate_scene", "rtb200_build_bvh", "rtb200_bvh_info", "rtb200_render", "rtb200_render_sequence", "rtb200_read_frame",
     "rtb200_trace_nearest", "rtb200_trace_nearest_static", "rtb200_trace_shadow", "rtb200_comm_unique_id", "rtb200_comm_init", "rtb200_band_map",
-    "rtb200_host_alloc", "rtb200_host_free", "rtb200_host_register", "rtb200_host_unregister", "rtb200_set_sharding", "rtb200_measure_fp32_peak", "rtb200_fp32_peak_detail", "rtb200_device_info",
+    "rtb200_host_alloc", "rtb200_host_free", "rtb200_host_register", "rtb200_host_unregister", "rtb200_set_sharding", "rtb200_measure_fp32_peak", "rtb200_fp32_peak_detail", "rtb200_device_info", "rtb200_device_count",
     "rtb200_timer_mark", "rtb200_timer_elapsed",
 ]
 

@@ -132,6 +132,14 @@ void rtb200_destroy(rtb200_ctx* ctx)
     delete ctx;
 }
 
+int rtb200_device_count(int* n)
+{
+    if (!n) return RTB200_E_ARG;
+    *n = 0;
+    if (cudaGetDeviceCount(n) != cudaSuccess) { (void)cudaGetLastError(); *n = 0; return RTB200_E_CUDA; }
+    return RTB200_OK;
+}
+
 int rtb200_host_alloc(size_t bytes, void** out)
 {
     if (!out) return RTB200_E_ARG;

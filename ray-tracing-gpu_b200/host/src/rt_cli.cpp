@@ -1,7 +1,9 @@
 // rt_cli.cpp -- headless command line of the renderer: the reference's `exe scene.dat -x W -y H`
 // (Main.cpp:51-124) without GLUT/GLEW: the frame goes to a PPM file instead of a window.
-//   rt_cli scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--fused] [--exact] [--bvh]
+//   rt_cli scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--gpus g] [--fused] [--exact] [--bvh]
 //          [--frames n] [--out image.ppm] [--obj mesh.obj] [--orbit n]
+// --gpus g: one frame over g GPUs (one context + thread per GPU, interleaved 16-row bands, every GPU writes its bands
+// into the host frame itself); not combined with --orbit.
 // --orbit n: a camera path of n frames on a circle around the point looked at, as one pipelined
 // submission (CScene::LancerTrajectoire); with --out f.ppm the frames go to f_000.ppm, f_001.ppm, ...
 // Unlike Main.cpp:79 there is no power-of-two / multiple-of-16 restriction on W and H.
@@ -21,7 +23,7 @@ using namespace Scene;
 int main(int argc, char** argv)
 {
     if (argc < 2) {
-        std::cerr << "usage: " << argv[0] << " scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--fused] [--exact] [--bvh] [--frames n] [--out f.ppm] [--obj mesh.obj] [--orbit n]" << std::endl;
+        std::cerr << "usage: " << argv[0] << " scene.dat [-x W] [-y H] [--depth d] [--spp k] [--device n] [--gpus g] [--fused] [--exact] [--bvh] [--frames n] [--out f.ppm] [--obj mesh.obj] [--orbit n]" << std::endl;
         return EXIT_FAILURE;
     }
     int W = CVar::g_LargeurFenetre, H = CVar::g_HauteurFenetre, depth = -1, spp = 1, frames = 1, orbit = 0;
@@ -38,6 +40,7 @@ int main(int argc, char** argv)
         else if (!strcmp(argv[i], "--depth")) depth = atoi(next("--depth"));
         else if (!strcmp(argv[i], "--spp")) spp = atoi(next("--spp"));
         else if (!strcmp(argv[i], "--device")) CVar::g_Peripherique = atoi(next("--device"));
+        else if (!strcmp(argv[i], "--gpus")) CVar::g_NbPeripheriques = atoi(next("--gpus"));
         else if (!strcmp(argv[i], "--frames")) frames = atoi(next("--frames"));
         else if (!strcmp(argv[i], "--orbit")) orbit = atoi(next("--orbit"));
         else if (!strcmp(argv[i], "--out")) out = next("--out");
@@ -48,6 +51,9 @@ int main(int argc, char** argv)
         else { std::cerr << "[ERREUR]: unknown option " << argv[i] << std::endl; return EXIT_FAILURE; }
     }
     if (W <= 0 || H <= 0) { std::cerr << "[ERREUR]: bad resolution" << std::endl; return EXIT_FAILURE; }
+    if (CVar::g_NbPeripheriques < 1 || CVar::g_NbPeripheriques > 64 || (CVar::g_NbPeripheriques > 1 && orbit > 0)) {
+        std::cerr << "[ERREUR]: --gpus wants 1..64 and no --orbit" << std::endl; return EXIT_FAILURE;
+    }
 
     CVar::g_GestionnaireDeScene = CScene::ObtenirInstance();
     CScene* scene = CVar::g_GestionnaireDeScene;

@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
+#include <thread>
 
 using namespace Scene;
 
@@ -18,6 +19,7 @@ static char g_chemin_nuanceur[] = "shaders/rayTracing.glsl";
 char* CVar::g_ComputeShaderPath = g_chemin_nuanceur;
 CNuanceurCalculProg* CVar::g_ComputeShader = nullptr;
 int CVar::g_Peripherique = 0;
+int CVar::g_NbPeripheriques = 1;
 
 const REAL CScene::DIM_FILM_CAM = 0.024f;
 
@@ -355,6 +357,7 @@ void CScene::LancerRayons()
     CVar::g_ComputeShader->activer();
     rtb200_ctx* ctx = CVar::g_ComputeShader->contexte();
     const rtb200_scene vue = m_Emballee.vue();
+    if (CVar::g_NbPeripheriques > 1) { LancerRayonsMultiGPU(ctx, vue); return; }
     int rc = rtb200_set_scene(ctx, &vue);                // was: SceneData UBO glBufferData (Scene.cpp:1268)
     if (rc == RTB200_OK && (m_Drapeaux & RTB200_F_USE_BVH)) rc = rtb200_build_bvh(ctx);
     if (rc == RTB200_OK) {
@@ -364,6 +367,58 @@ void CScene::LancerRayons()
     if (rc != RTB200_OK) {
         std::cerr << "[ERREUR]: rendu CUDA : " << rtb200_error_string(rc) << " -- " << rtb200_last_error(ctx) << std::endl;
         exit(EXIT_FAILURE);
+    }
+}
+
+// One frame over g GPUs from ONE process (rt_cli --gpus g; SURVEY.md 8b's single-process form): one context and one host
+// thread per GPU, band sharding without a communicator (rtb200_set_sharding), scene replicated, and every context
+// writes its own interleaved 16-row bands straight into this scene's host frame (RTB200_F_HOST_BANDS) over its own
+// PCIe link.  Nothing is exchanged between the GPUs.  With fewer devices than g the contexts share devices (same
+// frame, no speed-up).  `premier` = the context CVar::g_ComputeShader owns (rank 0).
+void CScene::LancerRayonsMultiGPU(rtb200_ctx* premier, const rtb200_scene& vue)
+{
+    static std::vector<rtb200_ctx*> autres;              // ranks 1 .. g-1, kept for the life of the process
+    const int g = CVar::g_NbPeripheriques;
+    int n_dev = 0;
+    if (rtb200_device_count(&n_dev) != RTB200_OK || n_dev < 1) { std::cerr << "[ERREUR]: aucun peripherique CUDA" << std::endl; exit(EXIT_FAILURE); }
+    while ((int)autres.size() < g - 1) {
+        rtb200_ctx* c = nullptr;
+        const int dev = (CVar::g_Peripherique + (int)autres.size() + 1) % n_dev;
+        const int rc = rtb200_create(dev, &c);
+        if (rc != RTB200_OK) { std::cerr << "[ERREUR]: rtb200_create(" << dev << ") : " << rtb200_error_string(rc) << " -- " << rtb200_last_error(nullptr) << std::endl; exit(EXIT_FAILURE); }
+        autres.push_back(c);
+    }
+    m_ImageRGBA8.resize((size_t)m_ResLargeur * m_ResHauteur * 4);
+    rtb200_frame cadre = m_Emballee.cadre;
+    cadre.flags |= RTB200_F_HOST_BANDS;
+    std::vector<int> rcs((size_t)g, RTB200_OK);
+    std::vector<rtb200_stats> stats((size_t)g);
+    auto travail = [&](int rang) {
+        rtb200_ctx* c = rang == 0 ? premier : autres[(size_t)rang - 1];
+        int rc = rtb200_set_sharding(c, rang, g);
+        if (rc == RTB200_OK) rc = rtb200_set_scene(c, &vue);
+        if (rc == RTB200_OK && (m_Drapeaux & RTB200_F_USE_BVH)) rc = rtb200_build_bvh(c);
+        if (rc == RTB200_OK) rc = rtb200_render(c, &cadre, m_InfoPixel, m_ImageRGBA8.data(), &stats[(size_t)rang]);
+        rcs[(size_t)rang] = rc;
+    };
+    std::vector<std::thread> fils;
+    for (int r = 1; r < g; ++r) fils.emplace_back(travail, r);
+    travail(0);
+    for (std::thread& t : fils) t.join();
+    for (int r = 0; r < g; ++r)
+        if (rcs[(size_t)r] != RTB200_OK) {
+            rtb200_ctx* c = r == 0 ? premier : autres[(size_t)r - 1];
+            std::cerr << "[ERREUR]: rendu CUDA (GPU " << r << ") : " << rtb200_error_string(rcs[(size_t)r]) << " -- " << rtb200_last_error(c) << std::endl;
+            exit(EXIT_FAILURE);
+        }
+    m_Stats = stats[0];                                  // whole-frame counters: sums; times: the slowest GPU
+    for (int r = 1; r < g; ++r) {
+        const rtb200_stats& s = stats[(size_t)r];
+        m_Stats.ms_render = std::max(m_Stats.ms_render, s.ms_render);
+        m_Stats.rays_primary += s.rays_primary; m_Stats.rays_shadow += s.rays_shadow;
+        m_Stats.rays_reflect += s.rays_reflect; m_Stats.rays_refract += s.rays_refract;
+        m_Stats.tests_triangle += s.tests_triangle; m_Stats.tests_quadric += s.tests_quadric; m_Stats.tests_plane += s.tests_plane;
+        m_Stats.kernel_launches += s.kernel_launches; m_Stats.nan_pixels += s.nan_pixels;
     }
 }
 

@@ -100,6 +100,7 @@ public:
     const float* ObtenirInfoPixel() const { return m_InfoPixel; }                     // W*H*3 floats, row 0 = bottom
     const unsigned char* ObtenirImageRGBA8() const { return m_ImageRGBA8.data(); }    // W*H*4 bytes
     const rtb200_stats& ObtenirStatistiques() const { return m_Stats; }
+    void LancerRayonsMultiGPU(rtb200_ctx* premier, const rtb200_scene& vue);   // CVar::g_NbPeripheriques > 1 (rt_cli --gpus g)
     int ObtenirLargeur() const { return m_ResLargeur; }
     int ObtenirHauteur() const { return m_ResHauteur; }
     size_t NbSurfaces() const { return m_Surfaces.size(); }
@@ -162,4 +163,5 @@ public:
     static CNuanceurCalculProg* g_ComputeShader;
     static char* g_ComputeShaderPath;                  // kept; unused (no GLSL file is loaded)
     static int g_Peripherique;                         // addition: CUDA device index
+    static int g_NbPeripheriques;                      // addition: GPUs one frame is spread over (rt_cli --gpus g); 1 = the reference's single device
 };

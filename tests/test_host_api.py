@@ -107,6 +107,25 @@ def test_cli_renders_ppm(rt, host, tmp_path):
     assert np.array_equal(img, q)
 
 
+@pytest.mark.gpu
+def test_cli_gpus_option_assembles_the_same_image(rt, host, tmp_path):
+    """rt_cli --gpus g: one context + thread per GPU, band sharding without a communicator, every context writes its
+    bands into the host frame (RTB200_F_HOST_BANDS).  With fewer devices than g the contexts share devices: the image
+    must be the one --gpus 1 writes, byte for byte (ragged height: 250 rows = 15 bands of 16 + 10 rows)."""
+    scene = os.path.join(GOLDEN, "scenes", "scene9.dat")
+    imgs = []
+    for g in (1, 3, 8):
+        out = tmp_path / f"s9_{g}.ppm"
+        r = subprocess.run([host.CLI_PATH, scene, "-x", "333", "-y", "250", "--depth", "4", "--gpus", str(g), "--out", str(out)],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        imgs.append(out.read_bytes())
+    assert imgs[0].startswith(b"P6\n333 250\n255\n") and len(imgs[0]) > 333 * 250 * 3
+    assert imgs[1] == imgs[0] and imgs[2] == imgs[0]
+    r = subprocess.run([host.CLI_PATH, scene, "--gpus", "2", "--orbit", "3"], capture_output=True, text=True)
+    assert r.returncode != 0
+
+
 def _write_obj(path, nq=12, size=60.0, y0=5.0):
     """A bumpy nq x nq quad grid (two conventions of face records, one 4-gon per quad)."""
     xs = np.linspace(-size, size, nq + 1)
