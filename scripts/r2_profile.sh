@@ -10,7 +10,9 @@ cap() {  # tag workload kernel-regex skip
 }
 cap c3_plain_nearest c3 k_trace_nearest 0
 cap c3_cull_shadow c3 k_cull_shadow 0
-cap c3_cull_nearest_l1 c3 k_cull_nearest 1
+cap c3_cull_nearest_l1 c3 k_cull_nearest 2        # launches per frame: <primary>, <primary, lanes>, <level 1>, <level 1, lanes>, ...
+cap c3_cull_nearest_l1_lanes c3 k_cull_nearest 3
+cap c3_cull_shadow_lanes c3 k_cull_shadow 1
 cap c4_bvh_shadow c4 k_bvh_shadow 0
 cap c4_bvh_nearest c4 k_bvh_nearest 0
 cap c5_bvh_shadow c5 k_bvh_shadow 0
