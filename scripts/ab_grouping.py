@@ -1,8 +1,9 @@
 #!/usr/bin/env python
-"""A/B of the queue order of the tiled path (RTB200_QUERY_GROUPING, read per frame): level-0 rays by 16x16 patches
-and each CTA's shadow queries light by light -- and of RTB200_NEAREST_CONES=4 (warps of secondary rays cull with up to
-4 cones).  Frames must be bit-identical (only the ORDER of the queues / the set of culled triangles changes);
-prints frame / stage times and the share of (ray, triangle) tests executed.
+"""A/B of the switches of the streamed path, inside one process (all read per frame): the default culled scan, the
+same without the 16x16 patches / light-by-light queues (RTB200_QUERY_GROUPING=0), without the Morton sort of the
+levels >= 1 (RTB200_SORT_SECONDARY=0), and the plain tiled scan (RTB200_NO_BUNDLE_CULL=1).  Frames must be bit-identical
+(only the ORDER of the work / the set of culled triangles changes); prints frame / stage times and the share of
+(ray, triangle) tests entered.
 usage: python scripts/ab_grouping.py [quick]"""
 import os
 import sys
@@ -28,20 +29,22 @@ def main():
         r.set_scene(ps)
         fr = rt.make_frame(ps.frame, W, H, max_bounces=depth, spp_grid=spp, flags=rt.F_FORCE_STREAM)
         res = {}
-        for tag, env, cones in (("ray order", "0", "1"), ("grouped", "1", "1"), ("grouped, 4 cones", "1", "4")):
-            os.environ["RTB200_QUERY_GROUPING"] = env
-            os.environ["RTB200_NEAREST_CONES"] = cones      # secondary rays: up to 4 cones per warp (k_trace_nearest MULTI)
+        variants = (("default", {}), ("scanline queues", {"RTB200_QUERY_GROUPING": "0"}), ("levels >= 1 unsorted", {"RTB200_SORT_SECONDARY": "0"}),
+                    ("plain scan", {"RTB200_NO_BUNDLE_CULL": "1"}))
+        for tag, env in variants:
+            os.environ.update(env)
             r.render(fr, want_f32=False, want_rgba8=False)
             img, img8, st = r.render(fr)
+            for k in env:
+                os.environ.pop(k)
             res[tag] = (img, img8, st)
             print(f"{name} [{tag}]: {st.ms_render:.2f} ms (nearest {st.ms_trace_nearest:.2f}, shadow {st.ms_trace_shadow:.2f}, shade {st.ms_shade:.2f}), "
                   f"rays p/s/rl/rr {st.rays_primary}/{st.rays_shadow}/{st.rays_reflect}/{st.rays_refract}, "
-                  f"tests executed {st.tests_triangle_executed / max(st.tests_triangle, 1):.4f} of {st.tests_triangle:.3e}", flush=True)
-        os.environ.pop("RTB200_QUERY_GROUPING"); os.environ.pop("RTB200_NEAREST_CONES")
-        a = res["ray order"]
-        for tag in ("grouped", "grouped, 4 cones"):
+                  f"tests entered {st.tests_triangle_executed / max(st.tests_triangle, 1):.4f} of {st.tests_triangle:.3e}, fix-ups {st.shadow_fixups}", flush=True)
+        a = res["default"]
+        for tag, _ in variants[1:]:
             b = res[tag]
-            print(f"   ray order vs {tag}: differing floats =", int((a[0].view(np.uint32) != b[0].view(np.uint32)).sum()),
+            print(f"   default vs {tag}: differing floats =", int((a[0].view(np.uint32) != b[0].view(np.uint32)).sum()),
                   "| differing bytes =", int((a[1] != b[1]).sum()),
                   "| ray counts equal =", (a[2].rays_shadow, a[2].rays_reflect, a[2].rays_refract) == (b[2].rays_shadow, b[2].rays_reflect, b[2].rays_refract), flush=True)
     r.close()
