@@ -25,6 +25,7 @@
 // Shadow filters: Scene.cpp:1856 multiplies in insertion order; the walk meets the occluders in Morton order.  Up to
 // two factors commute exactly; a query with three or more occluders met out of order and a non-zero product is redone
 // by k_shadow_fixup in insertion order (counted in rtb200_stats.shadow_fixups).
+#include <algorithm>
 #include <cfloat>
 #include <climits>
 
@@ -384,10 +385,9 @@ RT_DEV int cs_nearest_cones(const V3* o, const V3* d, const bool* use, Bundle* c
 // Nearest hit (Scene.cpp:1705-1720).  One warp task = 128 rays: PRIMARY a 16 x 8 block of the sample lattice
 // (thread = a 2 x 2 quad, rays generated on the fly), otherwise 128 consecutive queue entries.
 // ---------------------------------------------------------------------------------------
-// LANE = false: the kernel proper; a task no cone fits is put on cp.lane_list instead of being traced.
-// LANE = true:  traces the tasks of that list lane by lane (cs_lane_nearest) -- its own kernel so that the rare path
-//               costs the common one neither registers nor instruction cache.
-template <int MODE, bool PRIMARY, bool LANE>
+// A task no (narrow) cone fits is put on cp.lane_list instead of being traced: k_lane_nearest traces those lane by lane
+// -- its own small kernel, so that the rare path costs this one neither registers nor instruction cache.
+template <int MODE, bool PRIMARY>
 __global__ void __launch_bounds__(CS_THREADS, CS_MIN_CTAS)
 k_cull_nearest(const __grid_constant__ CullTraceParams cp)
 {
@@ -404,14 +404,9 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
 
     for (;;) {
         int task = 0;
-        if (lane == 0) task = (int)atomicAdd(LANE ? cp.lane_task_counter : cp.task_counter, 1u);
+        if (lane == 0) task = (int)atomicAdd(cp.task_counter, 1u);
         task = __shfl_sync(FULL_MASK, task, 0);
-        int only_r = -1;                               // LANE: a listed task is split into its ray slots, one per warp
-        if (LANE) {
-            if (task >= (int)min(*cp.lane_count, (unsigned int)cp.lane_cap) * rpt) break;
-            only_r = task % rpt;
-            task = cp.lane_list[task / rpt];
-        } else if (task >= n_tasks) break;
+        if (task >= n_tasks) break;
 
         V3 o[ST_RPT], d[ST_RPT];
         float best_t[ST_RPT], tlim[ST_RPT];
@@ -426,12 +421,12 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 const int lx = (tx << 4) + ((lane & 7) << 1) + (r & 1);
                 const int cy = (ty << 3) + ((lane >> 3) << 1) + (r >> 1);
                 const int ly = p.chunk_ly0 + cy;
-                valid = lx < p.f.LW && cy < p.chunk_rows && ly < p.local_LH && (!LANE || r == only_r);
+                valid = lx < p.f.LW && cy < p.chunk_rows && ly < p.local_LH;
                 slot[r] = valid ? cy * p.f.LW + lx : -1;
                 primary_ray<(MODE != 2)>(p.f, valid ? lx : 0, valid ? global_lattice_row(p.f, ly) : 0, o[r], d[r]);
             } else {
                 const int i0 = (task << shift) + r * 32 + lane;
-                valid = r < rpt && i0 < p.n_rays && (!LANE || r == only_r);
+                valid = r < rpt && i0 < p.n_rays;
                 const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
                 RT_CHECK(!valid || (i >= 0 && i < p.n_rays));
                 slot[r] = valid ? i : -1;
@@ -448,11 +443,11 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) dmax = fmaxf(dmax, max_abs3(d[r]));
         bool keep_all = true;
-        const int n_c = LANE ? 0 : cs_nearest_cones(o, d, use, ws.cones, lane, keep_all);
+        const int n_c = cs_nearest_cones(o, d, use, ws.cones, lane, keep_all);
         n_valid = __reduce_add_sync(FULL_MASK, n_valid);
         bool to_lanes = keep_all;                                          // no cone fits, or only wide ones: the lane kernel takes this task
         for (int k = 0; k < n_c; ++k) to_lanes = to_lanes || ws.cones[k].sin_t > cp.lane_sin;
-        if (!LANE && to_lanes && n_valid > 0 && cp.lane_list) {
+        if (to_lanes && n_valid > 0 && cp.lane_list) {
             unsigned int k = 0;
             if (lane == 0) k = atomicAdd(cp.lane_count, 1u);
             k = __shfl_sync(FULL_MASK, k, 0);
@@ -485,14 +480,7 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 }
             }
         };
-        if (LANE) {
-            // no cone fits these rays: every lane walks the hierarchy with its own rays, one after the other
-            int tests = 0;
-            #pragma unroll
-            for (int r = 0; r < ST_RPT; ++r)
-                if (r < rpt) tests += cs_lane_nearest<MODE>(cs, o[r], d[r], slot[r] >= 0, best_t[r], best_id[r]);
-            exec_rays += (unsigned long long)__reduce_add_sync(FULL_MASK, tests);
-        } else if (n_c > 0 || keep_all) {
+        if (n_c > 0 || keep_all) {
             CsWalk wk;
             cs_walk_init(wk);
             bool finished;
@@ -564,7 +552,7 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
 // Shadow filter (Scene.cpp:1842-1861): product of colour * kt over every surface hit strictly between EPSILON
 // and the light.  One warp task = 128 consecutive (ray, light) queries of the queue shade-A wrote light by light.
 // ---------------------------------------------------------------------------------------
-template <int MODE, bool LANE>           // LANE: see k_cull_nearest
+template <int MODE>
 __global__ void __launch_bounds__(CS_THREADS, CS_MIN_CTAS)
 k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 {
@@ -584,14 +572,9 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 
     for (;;) {
         int task = 0;
-        if (lane == 0) task = (int)atomicAdd(LANE ? cp.lane_task_counter : cp.task_counter, 1u);
+        if (lane == 0) task = (int)atomicAdd(cp.task_counter, 1u);
         task = __shfl_sync(FULL_MASK, task, 0);
-        int only_r = -1;
-        if (LANE) {
-            if (task >= (int)min(*cp.lane_count, (unsigned int)cp.lane_cap) * rpt) break;
-            only_r = task % rpt;
-            task = cp.lane_list[task / rpt];
-        } else if (task >= n_tasks) break;
+        if (task >= n_tasks) break;
 
         V3 o[ST_RPT], d[ST_RPT];
         float dist[ST_RPT], fr[ST_RPT], fg[ST_RPT], fb[ST_RPT];
@@ -601,7 +584,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
         #pragma unroll
         for (int r = 0; r < ST_RPT; ++r) {
             const int i0 = (task << shift) + r * 32 + lane;
-            const bool valid = r < rpt && i0 < p.n_queries && (!LANE || r == only_r);
+            const bool valid = r < rpt && i0 < p.n_queries;
             const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
             RT_CHECK(!valid || (i >= 0 && i < p.n_queries));
             slot[r] = valid ? i : -1;
@@ -620,7 +603,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 
         // ---- the warp's cone(s) per light present: one, or two around the two most distant directions ----------
         int n_c = 0;
-        bool keep_all = LANE || n_lights > 32;
+        bool keep_all = n_lights > 32;
         for (int l = 0; l < n_lights && !keep_all; ++l) {
             if (!((light_bits >> l) & 1u)) continue;
             const V3 L = f4_xyz(s.light[l].l0);
@@ -655,7 +638,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
         __syncwarp();
         bool to_lanes = keep_all;                                          // no cone fits, or only wide ones: the lane kernel takes this task
         for (int k = 0; k < n_c; ++k) to_lanes = to_lanes || ws.cones[k].sin_t > cp.lane_sin;
-        if (!LANE && to_lanes && n_valid > 0 && cp.lane_list) {
+        if (to_lanes && n_valid > 0 && cp.lane_list) {
             unsigned int k = 0;
             if (lane == 0) k = atomicAdd(cp.lane_count, 1u);
             k = __shfl_sync(FULL_MASK, k, 0);
@@ -703,21 +686,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
         };
         bool warp_done = false;
         tests_tri += (unsigned long long)n_valid * (unsigned long long)cs.n_tri;
-        if (LANE) {
-            // no cone fits these queries: every lane walks the hierarchy with its own queries, one after the other
-            int tests = 0;
-            #pragma unroll
-            for (int r = 0; r < ST_RPT; ++r)
-                if (r < rpt) {
-                    unsigned int occ = s_occ[r][tid];
-                    int mo = s_ord[r][tid];
-                    const V3 L = f4_xyz(s.light[max(lid[r], 0)].l0);
-                    tests += cs_lane_shadow<MODE>(cs, s.mat, L, o[r], d[r], dist[r], slot[r] >= 0, fr[r], fg[r], fb[r], occ, mo);
-                    s_occ[r][tid] = (unsigned char)occ; s_ord[r][tid] = mo;
-                }
-            exec_rays += (unsigned long long)__reduce_add_sync(FULL_MASK, tests);
-            warp_done = all_zero();
-        } else if (n_valid > 0) {
+        if (n_valid > 0) {
             CsWalk wk;
             cs_walk_init(wk);
             bool finished;
@@ -812,6 +781,139 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 }
 
 // ---------------------------------------------------------------------------------------
+// The lane kernels: the tasks the kernels above listed (no narrow cone fits their rays), ONE ray / query per lane.
+// A listed task of 2^shift rays is split into its 32-ray slices, one per warp (dynamic).  Each lane walks the sphere
+// hierarchy with its own ray (cs_lane_nearest / cs_lane_shadow), then tests the quadrics (quadric_t rejects a miss
+// without a division) and the planes itself.  Small kernels on purpose: 64 registers, twice the resident warps of the
+// kernels above -- the walk of a lone ray waits on L2 more than it computes.
+// ---------------------------------------------------------------------------------------
+#define CS_LANE_MIN_CTAS 8
+
+template <int MODE>
+__global__ void __launch_bounds__(CS_THREADS, CS_LANE_MIN_CTAS)
+k_lane_nearest(const __grid_constant__ CullTraceParams cp)
+{
+    const TraceParams& p = cp.t;
+    const CullScene& cs = cp.cs;
+    const DeviceScene& s = p.s;
+    const int lane = threadIdx.x & 31;
+    const int shift = cp.task_shift, rpt = 1 << (shift - 5);
+    const int n_listed = (int)min(*cp.lane_count, (unsigned int)cp.lane_cap);
+    unsigned long long exec_rays = 0;
+    for (;;) {
+        int w = 0;
+        if (lane == 0) w = (int)atomicAdd(cp.lane_task_counter, 1u);
+        w = __shfl_sync(FULL_MASK, w, 0);
+        if (w >= n_listed * rpt) break;
+        const int i0 = (cp.lane_list[w / rpt] << shift) + (w % rpt) * 32 + lane;
+        const bool valid = i0 < p.n_rays;
+        const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
+        RT_CHECK(!valid || (i >= 0 && i < p.n_rays));
+        V3 o = mk3(0.f, 0.f, 0.f), d = o;
+        if (valid) { o = f4_xyz(p.in_od0[i]); d = f4_xyz(p.in_od1[i]); }
+        float best_t = -1.0f;
+        int best_id = -1;
+        const int tests = cs_lane_nearest<MODE>(cs, o, d, valid, best_t, best_id);
+        exec_rays += (unsigned long long)__reduce_add_sync(FULL_MASK, tests);
+        if (!valid) continue;
+        for (int q = 0; q < s.n_quad; ++q) {
+            const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
+            const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+            const int ord = __float_as_int(q0.w);
+            bool lin;
+            const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+            if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+        }
+        for (int q = 0; q < s.n_plane; ++q) {
+            const float4 nc = __ldg(&s.plane[q].nc);
+            const int ord = s.plane[q].order;
+            const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
+            if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+        }
+        p.hit[i] = make_float2(best_t, __int_as_float(best_id));
+    }
+    if (p.stats && lane == 0 && exec_rays)
+        atomicAdd(&p.stats[(size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + ST_TEST_TRI_EXEC], exec_rays);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(CS_THREADS, CS_LANE_MIN_CTAS)
+k_lane_shadow(const __grid_constant__ CullShadowParams cp)
+{
+    const ShadowParams& p = cp.s;
+    const CullScene& cs = cp.cs;
+    const DeviceScene& s = p.s;
+    const int lane = threadIdx.x & 31;
+    const int shift = cp.task_shift, rpt = 1 << (shift - 5);
+    const int n_listed = (int)min(*cp.lane_count, (unsigned int)cp.lane_cap);
+    unsigned long long exec_rays = 0, tests_tri = 0, tests_q = 0, tests_p = 0, fixups = 0;
+    for (;;) {
+        int w = 0;
+        if (lane == 0) w = (int)atomicAdd(cp.lane_task_counter, 1u);
+        w = __shfl_sync(FULL_MASK, w, 0);
+        if (w >= n_listed * rpt) break;
+        const int i0 = (cp.lane_list[w / rpt] << shift) + (w % rpt) * 32 + lane;
+        const bool valid = i0 < p.n_queries;
+        const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
+        RT_CHECK(!valid || (i >= 0 && i < p.n_queries));
+        V3 o = mk3(0.f, 0.f, 0.f), d = o;
+        float dist = 0.f;
+        int lid = 0;
+        if (valid) { shadow_query<(MODE != 2)>(p, i, o, d, dist); lid = p.sq_src[i].y & ~SQ_FAR_BIT; }
+        float fr = valid ? 1.0f : 0.0f, fg = fr, fb = fr;
+        unsigned int occ = 0;
+        int max_ord = -1;
+        const int tests = cs_lane_shadow<MODE>(cs, s.mat, f4_xyz(s.light[lid].l0), o, d, dist, valid, fr, fg, fb, occ, max_ord);
+        exec_rays += (unsigned long long)__reduce_add_sync(FULL_MASK, tests);
+        if (!valid) continue;
+        tests_tri += (unsigned long long)cs.n_tri;
+        auto occluder = [&](int ord, int mat) {
+            const float4 m0 = s.mat[mat].m0;
+            const float kt = s.mat[mat].m2.x;
+            fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+            if (ord < max_ord) occ |= 4u;
+            if ((occ & 3u) < 3u) ++occ;
+            max_ord = max(max_ord, ord);
+        };
+        if (!(fr == 0.f && fg == 0.f && fb == 0.f)) {
+            tests_q += (unsigned long long)s.n_quad; tests_p += (unsigned long long)s.n_plane;
+            for (int q = 0; q < s.n_quad; ++q) {
+                const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
+                const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+                bool lin;
+                const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+                if (tt > RT_EPS && tt < dist) occluder(__float_as_int(q0.w), __float_as_int(q1.w));
+            }
+            for (int q = 0; q < s.n_plane; ++q) {
+                const float4 nc = __ldg(&s.plane[q].nc);
+                const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
+                if (tt > RT_EPS && tt < dist) occluder(s.plane[q].order, s.plane[q].material);
+            }
+        }
+        p.filter[p.sq_dst ? p.sq_dst[i] : i] = make_float4(fr, fg, fb, 0.f);
+        if ((occ & 4u) && (occ & 3u) >= 3u && (fr != 0.f || fg != 0.f || fb != 0.f) && p.fix_count) {
+            const unsigned int k = atomicAdd(p.fix_count, 1u);
+            if ((int)k < p.fix_cap) p.fix_list[k] = i;
+            ++fixups;
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        tests_tri += __shfl_xor_sync(FULL_MASK, tests_tri, off);
+        tests_q += __shfl_xor_sync(FULL_MASK, tests_q, off);
+        tests_p += __shfl_xor_sync(FULL_MASK, tests_p, off);
+        fixups += __shfl_xor_sync(FULL_MASK, fixups, off);
+    }
+    if (lane == 0 && p.stats) {
+        unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
+        if (tests_tri) atomicAdd(&st[ST_TEST_TRI_SHADOW], tests_tri);
+        if (exec_rays) atomicAdd(&st[ST_TEST_TRI_EXEC], exec_rays);
+        if (tests_q) atomicAdd(&st[ST_TEST_QUAD], tests_q);
+        if (tests_p) atomicAdd(&st[ST_TEST_PLANE], tests_p);
+        if (fixups) atomicAdd(&st[ST_SHADOW_FIXUP], fixups);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // The rare query whose product order matters: one warp per query walks the unified list (slot = insertion order,
 // Scene.cpp:107) 32 surfaces at a time; the occluders of a round are multiplied in slot order.
 // ---------------------------------------------------------------------------------------
@@ -886,31 +988,35 @@ static int cs_grid(int n_tasks, int sm_count)
     return ctas < CS_MIN_CTAS * sm_count ? ctas : CS_MIN_CTAS * sm_count;
 }
 
-cudaError_t launch_cull_nearest(const CullTraceParams& p, int sm_count, cudaStream_t st)
+static int lane_grid(int n_tasks, int rpt, int sm_count)
 {
+    const long long warps = (long long)n_tasks * rpt;
+    const long long ctas = (warps + CS_WARPS - 1) / CS_WARPS;
+    return (int)std::min<long long>(ctas, (long long)CS_LANE_MIN_CTAS * sm_count);
+}
+
+cudaError_t launch_cull_nearest(const CullTraceParams& p_in, int sm_count, cudaStream_t st)
+{
+    CullTraceParams p = p_in;
+    if (p.t.primary) p.lane_list = nullptr;              // (primary rays always have the camera's cone; a degenerate camera scans)
     const int tiles_x = (p.t.f.LW + 15) / 16;
     const int per = 1 << p.task_shift;
     const int n_tasks = p.t.primary ? tiles_x * ((p.t.chunk_rows + 7) / 8) : (p.t.n_rays + per - 1) / per;
     if (n_tasks <= 0) return cudaSuccess;
     const int blocks = cs_grid(n_tasks, sm_count);
     if (p.t.primary) {
-        if (p.t.mode == 2) k_cull_nearest<2, true, false><<<blocks, CS_THREADS, 0, st>>>(p);
-        else               k_cull_nearest<0, true, false><<<blocks, CS_THREADS, 0, st>>>(p);
+        if (p.t.mode == 2) k_cull_nearest<2, true><<<blocks, CS_THREADS, 0, st>>>(p);
+        else               k_cull_nearest<0, true><<<blocks, CS_THREADS, 0, st>>>(p);
     } else {
-        if (p.t.mode == 2) k_cull_nearest<2, false, false><<<blocks, CS_THREADS, 0, st>>>(p);
-        else               k_cull_nearest<0, false, false><<<blocks, CS_THREADS, 0, st>>>(p);
+        if (p.t.mode == 2) k_cull_nearest<2, false><<<blocks, CS_THREADS, 0, st>>>(p);
+        else               k_cull_nearest<0, false><<<blocks, CS_THREADS, 0, st>>>(p);
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess || !p.lane_list) return e;
     // the tasks no cone fitted (the count is read on the device; usually none, or the rays of the deep levels)
-    const int lane_blocks = cs_grid(n_tasks, sm_count);
-    if (p.t.primary) {
-        if (p.t.mode == 2) k_cull_nearest<2, true, true><<<lane_blocks, CS_THREADS, 0, st>>>(p);
-        else               k_cull_nearest<0, true, true><<<lane_blocks, CS_THREADS, 0, st>>>(p);
-    } else {
-        if (p.t.mode == 2) k_cull_nearest<2, false, true><<<lane_blocks, CS_THREADS, 0, st>>>(p);
-        else               k_cull_nearest<0, false, true><<<lane_blocks, CS_THREADS, 0, st>>>(p);
-    }
+    const int lb = lane_grid(n_tasks, per / 32, sm_count);
+    if (p.t.mode == 2) k_lane_nearest<2><<<lb, CS_THREADS, 0, st>>>(p);
+    else               k_lane_nearest<0><<<lb, CS_THREADS, 0, st>>>(p);
     return cudaGetLastError();
 }
 
@@ -920,12 +1026,13 @@ cudaError_t launch_cull_shadow(const CullShadowParams& p, int sm_count, cudaStre
     const int n_tasks = (p.s.n_queries + per - 1) / per;
     if (n_tasks <= 0) return cudaSuccess;
     const int blocks = cs_grid(n_tasks, sm_count);
-    if (p.s.mode == 2) k_cull_shadow<2, false><<<blocks, CS_THREADS, 0, st>>>(p);
-    else               k_cull_shadow<0, false><<<blocks, CS_THREADS, 0, st>>>(p);
+    if (p.s.mode == 2) k_cull_shadow<2><<<blocks, CS_THREADS, 0, st>>>(p);
+    else               k_cull_shadow<0><<<blocks, CS_THREADS, 0, st>>>(p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess || !p.lane_list) return e;
-    if (p.s.mode == 2) k_cull_shadow<2, true><<<blocks, CS_THREADS, 0, st>>>(p);
-    else               k_cull_shadow<0, true><<<blocks, CS_THREADS, 0, st>>>(p);
+    const int lb = lane_grid(n_tasks, per / 32, sm_count);
+    if (p.s.mode == 2) k_lane_shadow<2><<<lb, CS_THREADS, 0, st>>>(p);
+    else               k_lane_shadow<0><<<lb, CS_THREADS, 0, st>>>(p);
     return cudaGetLastError();
 }
 

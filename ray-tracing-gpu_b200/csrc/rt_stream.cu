@@ -122,9 +122,10 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     // a level with fewer rays than this is traced one ray per lane (tasks of 32): see CullTraceParams::task_shift
     int small_level = c->sm_count * 16 * 128 * 3;
     if (const char* e = getenv("RTB200_SMALL_LEVEL")) small_level = atoi(e);
-    // cones wider than this are not worth a warp walk (CullTraceParams::lane_sin).  Measured on config 3 (sweep 1.0 ..
-    // 0.12, one call): nearest-hit rays 8.3 -> 5.6 ms at 0.12-0.2, shadow queries best at 0.5 (15.2 ms; 18.4 at 0.12)
-    float lane_sin = 0.15f, lane_sin_shadow = 0.5f;
+    // cones wider than this are not worth a warp walk (CullTraceParams::lane_sin).  Measured on config 3 (two sweeps inside
+    // one call each): flat between 0.05 and 0.15 for nearest-hit rays and between 0.2 and 0.5 for shadow queries
+    // (21.6 - 22.2 ms per frame), worse outside (shadow 0.12: 22.9 ms; everything to the warps: 25.3 ms)
+    float lane_sin = 0.1f, lane_sin_shadow = 0.25f;
     if (const char* e = getenv("RTB200_LANE_SIN")) lane_sin = (float)atof(e);
     if (const char* e = getenv("RTB200_LANE_SIN_SHADOW")) lane_sin_shadow = (float)atof(e);
     bool rays_sorted = false;                   // the rays of the level about to be traced have a permutation in sb->cperm
@@ -423,7 +424,7 @@ int stream_query_nearest(rtb200_ctx* c, int n, uint32_t flags)
         if ((e = sb->lane.ensure(sizeof(int) * (size_t)n_tasks)) != cudaSuccess) return set_cuda_error(c, e, "lane list");
         SCU(cudaMemsetAsync(sb->tasks.p, 0, 16, c->stream));
         ctp.lane_list = sb->lane.as<int>(); ctp.lane_cap = n_tasks;
-        ctp.lane_count = sb->tasks.as<unsigned>() + 1; ctp.lane_task_counter = sb->tasks.as<unsigned>() + 2; ctp.lane_sin = 0.15f;
+        ctp.lane_count = sb->tasks.as<unsigned>() + 1; ctp.lane_task_counter = sb->tasks.as<unsigned>() + 2; ctp.lane_sin = 0.1f;
         SCU(launch_cull_nearest(ctp, c->sm_count, c->stream));
     }
     else                          SCU(launch_trace_nearest(tp, c->sm_count, c->stream));
