@@ -128,7 +128,8 @@ class ClockSampler(threading.Thread):
     def stop(self, windows):
         if self.proc:
             self.proc.terminate()
-        self.join(timeout=2)
+        if self.is_alive():
+            self.join(timeout=2)
 
         def inside(t):
             return any(a - 0.03 <= t <= b + 0.03 for a, b in windows)

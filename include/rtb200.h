@@ -273,8 +273,8 @@ int  rtb200_measure_fp32_peak(rtb200_ctx* ctx, double* tflops, double* sm_mhz);
 /* The same measurement with its parts, so that the figure can be recomputed: detail[0] TFLOP/s,
  * [1] FFMA instructions per thread, [2] threads per block, [3] blocks, [4] elapsed ms of the best
  * launch (CUDA events), [5] median SM cycles (clock64) and [6] nanoseconds (globaltimer) one block
- * spent in the chain, [7] SM clock = cycles / ns in MHz, [8] FFMA issued per clock and SM
- * (hardware limit 128), [9] SM count.  TFLOP/s = 2 x [1] x [2] x [3] / [4].  n >= 10. */
+ * spent in the chain, [7] SM clock = cycles / ns in MHz, [8] FFMA issued per clock and SM over the whole launch
+ * = [1] x [2] x [3] / ([4] x [7] x [9]) (hardware limit 128), [9] SM count.  TFLOP/s = 2 x [1] x [2] x [3] / [4].  n >= 10. */
 #define RTB200_PEAK_DETAIL_COUNT 10
 int  rtb200_fp32_peak_detail(rtb200_ctx* ctx, double* detail, int n);
 /* Number of CUDA devices this process sees (what rt_cli --gpus g spreads its contexts over). */

@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(PEAK_THREADS, 4) k_ffma_chain(float* sink, flo
 
 // detail (may be null, 8 doubles): FFMA instructions per thread, threads per block, blocks, best elapsed ms (CUDA
 // events), median per-block SM cycles and nanoseconds of that launch, SM clock = cycles / ns (MHz), FFMA per clock
-// and SM = resident threads per SM x FFMA per thread / cycles (the hardware limit is 128)
+// and SM = all FFMA / (elapsed x that clock x SMs) (the hardware limit is 128)
 cudaError_t run_fp32_peak(int sm_count, double* tflops, cudaStream_t st, double* detail)
 {
     float* sink = nullptr;
@@ -84,7 +84,10 @@ cudaError_t run_fp32_peak(int sm_count, double* tflops, cudaStream_t st, double*
         const double ffma_per_thread = (double)PEAK_ITERS * 4.0 * PEAK_CHAINS;
         detail[0] = ffma_per_thread; detail[1] = PEAK_THREADS; detail[2] = blocks; detail[3] = best_ms;
         detail[4] = mc; detail[5] = mn; detail[6] = mn > 0 ? mc / mn * 1e3 : 0.0;
-        detail[7] = mc > 0 ? 4.0 * PEAK_THREADS * ffma_per_thread / mc : 0.0;
+        // FFMA issued per clock and SM over the WHOLE launch: all FFMA / (elapsed time x measured clock x SMs).  (Per block,
+        // 4 x 512 threads x FFMA / block cycles over-states it: the four blocks of an SM do not overlap for their whole life.)
+        const double clk_hz = detail[6] * 1.0e6;
+        detail[7] = (best_ms > 0.f && clk_hz > 0.0) ? ffma_per_thread * PEAK_THREADS * (double)blocks / (best_ms * 1.0e-3 * clk_hz * sm_count) : 0.0;
     }
     if (clk) cudaFree(clk);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
