@@ -10,13 +10,13 @@ cap() {  # tag workload kernel-regex skip
 }
 cap c3_plain_nearest c3 k_trace_nearest 0
 cap c3_cull_shadow c3 k_cull_shadow 0
-cap c3_cull_nearest_l1 c3 k_cull_nearest 2        # launches per frame: <primary>, <primary, lanes>, <level 1>, <level 1, lanes>, ...
-cap c3_cull_nearest_l1_lanes c3 k_cull_nearest 3
-cap c3_cull_shadow_lanes c3 k_cull_shadow 1
+cap c3_cull_nearest_l1 c3 k_cull_nearest 1        # launches per frame: <primary>, <level 1>, <level 2>, ...
+cap c3_lane_nearest_l1 c3 k_lane_nearest 0
+cap c3_lane_shadow_l0 c3 k_lane_shadow 0
 cap c4_bvh_shadow c4 k_bvh_shadow 0
 cap c4_bvh_nearest c4 k_bvh_nearest 0
 cap c5_bvh_shadow c5 k_bvh_shadow 0
 cap c2_resident c2 k_resident_level 0
-timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/${TAG}_c3_launches.csv \
+timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file $OUT/${TAG}_c3_launches.csv \
     python bench.py --workload c3 --steps 2 --warmup 1 --no-cpu --no-nested > $OUT/${TAG}_c3_launches.log 2>&1
 ls -la $OUT | tail -30
