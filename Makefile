@@ -54,8 +54,20 @@ $(CHKDIR)/%.o: $(CSRC)/%.cu $(CUHDRS)
 checked: $(CHKOBJS)
 	$(NVCC) -shared -ccbin $(HOSTCXX) -o $(CHKDIR)/librtb200.so $^ -ldl
 
+# ASan + UBSan build of the host scene API (parser, Pretraitement, SoA packer) and of the C oracle into ab/asan/; run the
+# CPU tests against them with
+#   RTB200_SCENE_LIB=ab/asan/librtb200_scene.so RTB200_ORACLE_LIB=ab/asan/librt_oracle.so \
+#   LD_PRELOAD="$$(gcc -print-file-name=libasan.so) $$(gcc -print-file-name=libubsan.so)" \
+#   ASAN_OPTIONS=detect_leaks=0:alloc_dealloc_mismatch=0:new_delete_type_mismatch=0 python -m pytest tests -m "not gpu"
+# (the two mismatch checks are off because the REFERENCE frees its new[] frame buffer with a scalar delete, Scene.cpp:528)
+asan: $(LIBDIR)/librtb200.so
+	@mkdir -p $(ROOT)ab/asan
+	$(HOSTCXX) $(HOSTFLAGS) -O1 -g -fno-omit-frame-pointer -fsanitize=address,undefined -shared -o $(ROOT)ab/asan/librtb200_scene.so \
+	    $(filter-out $(HOST)/src/rt_cli.cpp,$(HOSTSRC)) -L$(LIBDIR) -lrtb200 -Wl,-rpath,$(LIBDIR)
+	/usr/bin/gcc -std=gnu11 -O1 -g -fsanitize=address,undefined -ffp-contract=off -fPIC -fopenmp -shared -o $(ROOT)ab/asan/librt_oracle.so $(ROOT)oracle/rt_oracle.c -lm
+
 clean:
 	rm -rf $(OBJDIR) $(LIBDIR)
 	$(MAKE) -C $(ROOT)oracle clean
 
-.PHONY: all lib host oracle checked clean
+.PHONY: all lib host oracle checked asan clean

@@ -8,7 +8,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB = os.path.join(_HERE, "librt_oracle.so")
+_LIB = os.path.abspath(os.environ["RTB200_ORACLE_LIB"]) if os.environ.get("RTB200_ORACLE_LIB") else os.path.join(_HERE, "librt_oracle.so")
 
 _f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
 _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")

@@ -8,7 +8,8 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "librtb200_scene.so")
+# RTB200_SCENE_LIB: another build of the same library (e.g. the ASan / UBSan build, `make asan`)
+LIB_PATH = os.path.abspath(os.environ["RTB200_SCENE_LIB"]) if os.environ.get("RTB200_SCENE_LIB") else os.path.join(_HERE, "lib", "librtb200_scene.so")
 CLI_PATH = os.path.join(_HERE, "lib", "rt_cli")
 _lib = None
 
