@@ -298,6 +298,28 @@ RT_DEV bool slab(const RayBox& r, float lx, float ly, float lz, float hx, float 
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), limit));
     return tn <= tf * (1.0f + 2.0f * BVH_SLACK);
 }
+// The same test with the ray's OCTANT known at compile time (bit k of OCT set: direction component k is negative): which of
+// a box's two planes per axis is entered first is then a matter of naming registers, not of six FMNMX per box -- the
+// values of tn and tf are the ones slab() computes (fma is monotone: lo <= hi  =>  fma(lo, i, n) <= fma(hi, i, n) for
+// i >= 0), so the walk, its counters and the frame are unchanged.  12 instead of 18 instructions per box.
+template <int OCT>
+RT_DEV bool slab_oct(const RayBox& r, float lx, float ly, float lz, float hx, float hy, float hz, float limit, float& tn)
+{
+    const float ax = fmaf((OCT & 1) ? hx : lx, r.ix, r.nx), bx = fmaf((OCT & 1) ? lx : hx, r.ix, r.nx);
+    const float ay = fmaf((OCT & 2) ? hy : ly, r.iy, r.ny), by = fmaf((OCT & 2) ? ly : hy, r.iy, r.ny);
+    const float az = fmaf((OCT & 4) ? hz : lz, r.iz, r.nz), bz = fmaf((OCT & 4) ? lz : hz, r.iz, r.nz);
+    tn = fmaxf(fmaxf(ax, ay), fmaxf(az, 0.0f));
+    const float tf = fminf(fminf(bx, by), fminf(bz, limit));
+    return tn <= tf * (1.0f + 2.0f * BVH_SLACK);
+}
+// octant of a direction for slab_oct, or 8 (the generic test) when a component is so small that safe_rcp replaces its
+// reciprocal, or not finite -- there the products can overflow and only slab()'s min / max ignore the NaNs
+RT_DEV int ray_octant(V3 d)
+{
+    const bool ok = fabsf(d.x) > 1.0e-30f && fabsf(d.y) > 1.0e-30f && fabsf(d.z) > 1.0e-30f &&
+                    fabsf(d.x) < 1.0e30f && fabsf(d.y) < 1.0e30f && fabsf(d.z) < 1.0e30f;
+    return ok ? ((d.x < 0.f ? 1 : 0) | (d.y < 0.f ? 2 : 0) | (d.z < 0.f ? 4 : 0)) : 8;
+}
 // the same for the box grown by g on every side (gx = g |1/dx| ...: the slab distances move by that much)
 RT_DEV bool slab_grown(const RayBox& r, float gx, float gy, float gz, float lx, float ly, float lz, float hx, float hy, float hz, float limit, float& tn)
 {
@@ -345,7 +367,7 @@ RT_DEV float triangle_leaf(V3 o, V3 d, V3 p0, V3 e1, V3 e2, float tmax)
 // references only.  The bottom stack entry is a sentinel, so a pop never tests for an empty stack.
 #define BVH_DONE INT_MIN              // not a leaf reference: first + count <= n < 2^28 (bvh_build)
 
-template <bool SHRINK, bool GROW = false, class Leaf>
+template <bool SHRINK, bool GROW = false, int OCT = 8, class Leaf>
 RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& leaf, unsigned& n_nodes, unsigned& overflow, float grow = 0.f)
 {
     const RayBox rb = make_raybox(o, d);
@@ -364,8 +386,17 @@ RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& l
             const int2 c = __ldg(reinterpret_cast<const int2*>(&nd->c));
             ++n_nodes;
             float t0, t1;
-            const bool h0 = GROW ? slab_grown(rb, gx, gy, gz, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0) : slab(rb, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0);
-            const bool h1 = GROW ? slab_grown(rb, gx, gy, gz, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1) : slab(rb, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1);
+            bool h0, h1;
+            if (GROW) {
+                h0 = slab_grown(rb, gx, gy, gz, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0);
+                h1 = slab_grown(rb, gx, gy, gz, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1);
+            } else if (OCT < 8) {
+                h0 = slab_oct<OCT & 7>(rb, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0);
+                h1 = slab_oct<OCT & 7>(rb, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1);
+            } else {
+                h0 = slab(rb, b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, limit, t0);
+                h1 = slab(rb, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w, limit, t1);
+            }
             if (h0 && h1) {
                 const bool swap = t1 < t0;
                 if (sp <= BVH_STACK) {
@@ -389,6 +420,32 @@ RT_DEV void bvh_traverse(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& l
             do { --sp; } while (stack_tn[sp] > limit * (1.0f + 2.0f * BVH_SLACK));
             ref = stack_ref[sp];
         } else ref = stack_ref[--sp];
+    }
+}
+
+// the walk specialised for the ray's octant (nine copies of the loop; the lanes of a warp mostly share theirs).  Used by
+// the nearest-hit kernel (config 5: 100 -> 90 ms, config 4: 1.80 -> 1.69 ms); the occlusion kernel keeps the generic
+// walk -- measured with the variants: no gain (config 5 shadow 325 -> 324 ms) and + 5 % on config 4 (56 registers:
+// spills, and nine copies of its larger leaf code).
+template <bool SHRINK, class Leaf>
+RT_DEV void bvh_traverse_oct(const DeviceScene& s, V3 o, V3 d, float limit, Leaf&& leaf, unsigned& n_nodes, unsigned& overflow)
+{
+    // ... only when every lane that walks now shares the octant: a warp of mixed octants (the eight lights of one hit
+    // point in adjacent lanes) would serialise nine copies of the loop (measured: config 4 shadow 6.6 -> 14.1 ms).
+    // Any choice is correct -- the variants compute the same values -- so the vote only has to be cheap.
+    int oct = ray_octant(d);
+    const unsigned int active = __activemask();
+    if (!__all_sync(active, oct == __shfl_sync(active, oct, __ffs((int)active) - 1))) oct = 8;
+    switch (oct) {
+    case 0: bvh_traverse<SHRINK, false, 0>(s, o, d, limit, leaf, n_nodes, overflow); break;
+    case 1: bvh_traverse<SHRINK, false, 1>(s, o, d, limit, leaf, n_nodes, overflow); break;
+    case 2: bvh_traverse<SHRINK, false, 2>(s, o, d, limit, leaf, n_nodes, overflow); break;
+    case 3: bvh_traverse<SHRINK, false, 3>(s, o, d, limit, leaf, n_nodes, overflow); break;
+    case 4: bvh_traverse<SHRINK, false, 4>(s, o, d, limit, leaf, n_nodes, overflow); break;
+    case 5: bvh_traverse<SHRINK, false, 5>(s, o, d, limit, leaf, n_nodes, overflow); break;
+    case 6: bvh_traverse<SHRINK, false, 6>(s, o, d, limit, leaf, n_nodes, overflow); break;
+    case 7: bvh_traverse<SHRINK, false, 7>(s, o, d, limit, leaf, n_nodes, overflow); break;
+    default: bvh_traverse<SHRINK, false, 8>(s, o, d, limit, leaf, n_nodes, overflow); break;
     }
 }
 
@@ -424,7 +481,7 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
         int best_id = -1;
         if (s.bvh_n_prims > 0) {
             const TriRec* __restrict__ tri = s.bvh_tri;
-            bvh_traverse<true>(s, o, d, 3.0e38f, [&](int first, int count, float limit) -> float {
+            bvh_traverse_oct<true>(s, o, d, 3.0e38f, [&](int first, int count, float limit) -> float {
                 for (int k = 0; k < count; ++k) {
                     const float4 ra = __ldg(&tri[first + k].a), rb = __ldg(&tri[first + k].b), rc = __ldg(&tri[first + k].c);
                     float tt;
