@@ -539,7 +539,10 @@ k_bvh_nearest(const __grid_constant__ TraceParams p)
 // (0 * finite = 0), so the traversal may stop there; transparent occluders are collected and
 // multiplied in insertion order, the order of the linear scan.
 template <int MODE, bool QUADS>
-__global__ void __launch_bounds__(BVH_THREADS, 9)          // 56 registers: 9 CTAs per SM (64 registers: +6 % time)
+#ifndef BVH_SHADOW_CTAS
+#define BVH_SHADOW_CTAS 9
+#endif
+__global__ void __launch_bounds__(BVH_THREADS, BVH_SHADOW_CTAS)          // 56 registers: 9 CTAs per SM (64 registers: +6 % time)
 k_bvh_shadow(const __grid_constant__ ShadowParams p)
 {
     const DeviceScene& s = p.s;
