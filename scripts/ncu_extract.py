@@ -4,7 +4,8 @@
   profiles/r2_ncu_lbvh_counters.json  what binds the LBVH walk: issue active, active threads per instruction, stalls,
                                       L1 / L2 hit rates, L2 throughput (roofline of configs 4 / 5)
 and one text summary per capture (profiles/<tag>_<name>_ncu_full.txt).
-usage: python scripts/ncu_extract.py gpurun_out r2p"""
+usage: python scripts/ncu_extract.py gpurun_out r2p [output directory, default profiles/]
+(scripts/r2_profile.sh runs it ON the GPU box with gpurun_out/extracted as output: ten .ncu-rep files exceed what a call may bring back)"""
 import csv
 import json
 import os
@@ -55,11 +56,13 @@ def read(rep):
 
 def main():
     d, tag = sys.argv[1], sys.argv[2]
+    out_dir = sys.argv[3] if len(sys.argv) > 3 else os.path.join(ROOT, "profiles")
+    os.makedirs(out_dir, exist_ok=True)
     caps = {n[len(tag) + 1:-8]: os.path.join(d, n) for n in sorted(os.listdir(d)) if n.startswith(tag + "_") and n.endswith(".ncu-rep")}
     got = {}
     for name, rep in caps.items():
         got[name] = read(rep)
-        sys.argv = ["ncu_summary.py", rep, os.path.join(ROOT, "profiles", f"r2_{name}_ncu_full.txt")]
+        sys.argv = ["ncu_summary.py", rep, os.path.join(out_dir, f"r2_{name}_ncu_full.txt")]
         try:
             import io, contextlib
             with contextlib.redirect_stdout(io.StringIO()):
@@ -72,14 +75,14 @@ def main():
             g = got[name]
             traffic[wl] = {"dram_read_bytes": g["dram_read"], "dram_write_bytes": g["dram_write"], "kernel": g["kernel"],
                            "source": f"profiles/r2_{name}_ncu_full.txt (ncu --set full --clock-control none, one launch)"}
-    json.dump(traffic, open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json"), "w"), indent=1)
+    json.dump(traffic, open(os.path.join(out_dir, "r2_ncu_traffic.json"), "w"), indent=1)
     lb = {}
     for wl, name in (("c4", "c4_bvh_shadow"), ("c5", "c5_bvh_shadow")):
         if name in got:
             lb[wl] = dict(got[name], source=f"profiles/r2_{name}_ncu_full.txt")
     if "c4_bvh_nearest" in got:
         lb["c4_nearest"] = dict(got["c4_bvh_nearest"], source="profiles/r2_c4_bvh_nearest_ncu_full.txt")
-    json.dump(lb, open(os.path.join(ROOT, "profiles", "r2_ncu_lbvh_counters.json"), "w"), indent=1)
+    json.dump(lb, open(os.path.join(out_dir, "r2_ncu_lbvh_counters.json"), "w"), indent=1)
     for k, v in got.items():
         print(k, {a: (round(b, 3) if isinstance(b, float) else b) for a, b in v.items() if a not in ("kernel",)})
 

@@ -19,4 +19,7 @@ cap c5_bvh_shadow c5 k_bvh_shadow 0
 cap c2_resident c2 k_resident_level 0
 timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file $OUT/${TAG}_c3_launches.csv \
     python bench.py --workload c3 --steps 2 --warmup 1 --no-cpu --no-nested > $OUT/${TAG}_c3_launches.log 2>&1
+# ten .ncu-rep files are more than a call may bring back (64 MiB): summarise them here, keep two for source-level budgets
+python scripts/ncu_extract.py $OUT $TAG $OUT/extracted > $OUT/${TAG}_extract.log 2>&1
+for n in c3_plain_nearest c3_cull_nearest_l1 c3_lane_nearest_l1 c3_lane_shadow_l0 c4_bvh_shadow c4_bvh_nearest c2_resident; do rm -f $OUT/${TAG}_$n.ncu-rep; done
 ls -la $OUT | tail -30
