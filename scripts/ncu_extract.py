@@ -35,6 +35,10 @@ WANT = {
     "dram_write": "dram__bytes_write.sum",
     "l2_throughput_pct": "lts__throughput.avg.pct_of_peak_sustained_elapsed",
     "bank_conflicts_shared": "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+    "l1_data_pipe_pct": "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed",
+    "l1_wavefronts": "l1tex__data_pipe_lsu_wavefronts.sum",
+    "global_load_requests": "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum",
+    "global_load_sectors": "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum",
 }
 UNIT = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "ms": 1.0, "us": 1e-3, "ns": 1e-6, "s": 1e3}
 

@@ -16,7 +16,13 @@ KEYS = [
     "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
     "smsp__inst_executed_op_branch.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
     "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct", "dram__bytes_read.sum", "dram__bytes_write.sum",
-    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__cycles_elapsed.max", "sm__cycles_active.avg",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+    # the L1 data pipe: one wavefront = one cycle of it; a warp-wide LDG.128 returns 512 B to the registers = 4 wavefronts
+    # however few sectors it touched (what co-limits the LBVH walk)
+    "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed", "l1tex__lsu_writeback_active.avg.pct_of_peak_sustained_elapsed",
+    "l1tex__data_pipe_lsu_wavefronts.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum",
+    "sass__inst_executed_local_loads", "sass__inst_executed_local_stores",
+    "sm__cycles_elapsed.max", "sm__cycles_active.avg",
     "smsp__cycles_active.avg", "smsp__average_warp_latency_issue_stalled_math_pipe_throttle.ratio",
     "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
     "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
