@@ -108,7 +108,7 @@ template <bool LIGHT>
 RT_DEV bool cs_fill(const CullScene& cs, CsWarpSmem& ws, int n_c, bool keep_all, int lane, CsWalk& w)
 {
     constexpr bool PAIR = CS_PAIR && !LIGHT;
-    constexpr int ROUND = PAIR ? 64 : 32;                   // queue slots a round can fill; the queue is drained above 128 entries
+    [[maybe_unused]] constexpr int ROUND = PAIR ? 64 : 32;  // queue slots a round can fill; the queue is drained above 128 entries
     for (;;) {
         int level, block, block2 = -1;                      // the block(s) of 32 entries to test now
         if (w.lvl == CS_LEVELS) {
@@ -209,16 +209,36 @@ RT_DEV bool cs_ray_misses(const LaneRay& r, float4 sph, float w)
     return perp2 > rp * rp || s < -rp || s > r.far + rp;
 }
 
-// leaf(first, mask): the lane's ray may touch triangles first + j for the bits j of mask (called per lane, diverged)
-template <class Leaf>
-RT_DEV void cs_lane_walk(const CullScene& cs, const LaneRay& b, bool active, Leaf&& leaf)
+// A ray is walked by a GROUP of CS_LANE_G adjacent lanes (a warp holds 32 / CS_LANE_G rays): the lanes of a group
+// share the ray and the walk's state (every lane keeps a copy), each tests its share of a block's 32 spheres -- entry
+// k G + g for lane g, so that neighbours read neighbours -- and the union of their masks (log2 G shuffles) is the
+// block's mask.  The triangles that survive level 0 are dealt out by rank, every lane testing its own.  Why: with one
+// ray per lane a warp's walk is ~100 lock-step rounds of 32 dependent sphere tests + the leaf tests, 0.8 ms for ONE
+// slice of 32 rays whatever the level's size -- and a kernel cannot end before its slowest warp: the launch list of
+// config 3 showed the lane kernels of levels 1, 2 and 3 at 0.84 / 0.81 / 0.83 ms for 8 : 2.4 : 1 rays.
+#ifndef CS_LANE_G
+#define CS_LANE_G 8
+#endif
+static_assert(CS_LANE_G == 1 || CS_LANE_G == 2 || CS_LANE_G == 4 || CS_LANE_G == 8 || CS_LANE_G == 16, "group size");
+
+// leaf(first, mask): the group's ray may touch triangles first + j for the bits j of mask (called by every lane of the
+// group with the same arguments; the lanes diverge inside).  stop(): evaluated by every lane at the top of a round, the
+// group leaves the walk when any of its lanes says so.
+template <class Leaf, class Stop>
+RT_DEV void cs_lane_walk(const CullScene& cs, const LaneRay& b, bool active, int lane, Leaf&& leaf, Stop&& stop)
 {
+    constexpr int G = CS_LANE_G;
+    const int g = lane & (G - 1);
+    const unsigned int group_bits = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << (lane & ~(G - 1));
     int lvl = CS_LEVELS, top_b = 0;
     unsigned int m1 = 0u, m2 = 0u, m3 = 0u;
     int b1 = 0, b2 = 0, b3 = 0;
     bool busy = active;
-    while (__any_sync(FULL_MASK, busy)) {
-        // ---- which block does this lane test now? ------------------------------------------------
+    for (;;) {
+        const unsigned int stops = __ballot_sync(FULL_MASK, busy && stop());
+        if (stops & group_bits) busy = false;
+        if (!__any_sync(FULL_MASK, busy)) break;
+        // ---- which block does this group test now? -----------------------------------------------
         int level = -1, block = 0;
         while (busy && level < 0) {
             if (lvl == CS_LEVELS) {
@@ -234,13 +254,14 @@ RT_DEV void cs_lane_walk(const CullScene& cs, const LaneRay& b, bool active, Lea
                 level = lvl - 1;
             }
         }
-        // ---- 32 entries of that block against this lane's ray (lock step over the warp) --------------
+        // ---- the block's 32 entries against the group's ray, 32 / G per lane (lock step over the warp) ---
         unsigned int mm = 0u;
         if (level >= 0) {
             const int i0 = cs_level_offset(cs.n3, level) + block * 32;
             const int n_in = level == CS_LEVELS - 1 ? min(32, cs.n3 - block * 32) : 32;
             #pragma unroll 4
-            for (int j = 0; j < 32; ++j) {
+            for (int k = 0; k < 32 / G; ++k) {
+                const int j = k * G + g;
                 if (j < n_in) {
                     const float4 sph = __ldg(cs.sph + i0 + j);
                     const float w = __ldg(cs.w + i0 + j);
@@ -248,6 +269,10 @@ RT_DEV void cs_lane_walk(const CullScene& cs, const LaneRay& b, bool active, Lea
                     mm |= keep ? (1u << j) : 0u;
                 }
             }
+        }
+        #pragma unroll
+        for (int off = 1; off < G; off <<= 1) mm |= __shfl_xor_sync(FULL_MASK, mm, off);     // (every lane: groups without a block pass 0)
+        if (level >= 0) {
             if (level == 0) { if (mm) leaf(block * 32, mm); }
             else {
                 if (level == 1) { m1 = mm; b1 = block * 32; } else if (level == 2) { m2 = mm; b2 = block * 32; } else { m3 = mm; b3 = block * 32; }
@@ -256,17 +281,32 @@ RT_DEV void cs_lane_walk(const CullScene& cs, const LaneRay& b, bool active, Lea
         }
     }
 }
+// the bits of `mask` this lane of the group takes: every G-th one by rank
+RT_DEV unsigned int cs_lane_share(unsigned int mask, int g)
+{
+    constexpr int G = CS_LANE_G;
+    if (G == 1) return mask;
+    unsigned int mine = 0u;
+    for (int rank = 0; mask; ++rank) {
+        const unsigned int low = mask & (0u - mask);
+        if ((rank & (G - 1)) == g) mine |= low;
+        mask ^= low;
+    }
+    return mine;
+}
 
-
-// nearest hit of ONE ray per lane over the triangles (kept out of line: rare path, and the kernels are large enough)
+// nearest hit of ONE ray per group over the triangles: every lane returns the best of ITS share (the caller combines).
+// Kept out of line: rare path, and the kernels are large enough.
 template <int MODE>
-__device__ __noinline__ int cs_lane_nearest(const CullScene& cs, V3 o, V3 d, bool active, float& best_t, int& best_id)
+__device__ __noinline__ int cs_lane_nearest(const CullScene& cs, V3 o, V3 d, bool active, int lane, float& best_t, int& best_id)
 {
     const LaneRay b = cs_lane_ray(o, d);
+    const int g = lane & (CS_LANE_G - 1);
     float bt = best_t;
     int bi = best_id, tests = 0;
     const float dmax = max_abs3(d);
-    cs_lane_walk(cs, b, active, [&](int first, unsigned int mask) {
+    cs_lane_walk(cs, b, active, lane, [&](int first, unsigned int mask) {
+        mask = cs_lane_share(mask, g);
         while (mask) {
             const TriRec* t = cs.tri + first + __ffs((int)mask) - 1;
             mask &= mask - 1u;
@@ -279,22 +319,25 @@ __device__ __noinline__ int cs_lane_nearest(const CullScene& cs, V3 o, V3 d, boo
             const int ord = __float_as_int(ra.w);
             if (tt > RT_EPS && (tt < bt || bt < 0.f || (tt == bt && ord < bi))) { bt = tt; bi = ord; }
         }
-    });
+    }, []() { return false; });
     best_t = bt; best_id = bi;
     return tests;
 }
 
-// shadow filter of ONE query per lane over the triangles; occ / max_ord: the occluder bookkeeping of k_cull_shadow
+// shadow filter of ONE query per group over the triangles: every lane returns the product over the occluders of ITS
+// share and their number (saturating at 3); a lane that holds a zero product stops the group
 template <int MODE>
-__device__ __noinline__ int cs_lane_shadow(const CullScene& cs, const MatRec* __restrict__ mat, V3 L, V3 o, V3 d, float dist, bool active,
-                                           float& fr, float& fg, float& fb, unsigned int& occ, int& max_ord)
+__device__ __noinline__ int cs_lane_shadow(const CullScene& cs, const MatRec* __restrict__ mat, V3 L, V3 o, V3 d, float dist, bool active, int lane,
+                                           float& fr, float& fg, float& fb, unsigned int& occ)
 {
     const LaneRay b = cs_lane_query(L, d, dist);
+    const int g = lane & (CS_LANE_G - 1);
     float r_ = fr, g_ = fg, b_ = fb;
-    unsigned int st = occ;
-    int mo = max_ord, tests = 0;
+    unsigned int n_occ = occ;
+    int tests = 0;
     const float dmax = max_abs3(d), tlim = fmaf(dist, CULL_TREL, CULL_TABS);
-    cs_lane_walk(cs, b, active, [&](int first, unsigned int mask) {
+    cs_lane_walk(cs, b, active, lane, [&](int first, unsigned int mask) {
+        mask = cs_lane_share(mask, g);
         while (mask) {
             const TriRec* t = cs.tri + first + __ffs((int)mask) - 1;
             mask &= mask - 1u;
@@ -306,17 +349,15 @@ __device__ __noinline__ int cs_lane_shadow(const CullScene& cs, const MatRec* __
             if (!triangle_phase1(o, d, p0, e1, e2, mg)) continue;
             const float tt = triangle_survivor<MODE>(o, d, p0, e1, e2, tlim, mg);
             if (tt > RT_EPS && tt < dist) {
-                const int ord = __float_as_int(ra.w), m = __float_as_int(rb.w);
+                const int m = __float_as_int(rb.w);
                 const float4 m0 = mat[m].m0;
                 const float kt = mat[m].m2.x;
                 r_ = __fmul_rn(r_, __fmul_rn(m0.x, kt)); g_ = __fmul_rn(g_, __fmul_rn(m0.y, kt)); b_ = __fmul_rn(b_, __fmul_rn(m0.z, kt));
-                if (ord < mo) st |= 4u;
-                if ((st & 3u) < 3u) ++st;
-                mo = max(mo, ord);
+                if (n_occ < 3u) ++n_occ;
             }
         }
-    });
-    fr = r_; fg = g_; fb = b_; occ = st; max_ord = mo;
+    }, [&]() { return r_ == 0.f && g_ == 0.f && b_ == 0.f; });
+    fr = r_; fg = g_; fb = b_; occ = n_occ;
     return tests;
 }
 
@@ -813,31 +854,35 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
 }
 
 // ---------------------------------------------------------------------------------------
-// The lane kernels: the tasks the kernels above listed (no narrow cone fits their rays), ONE ray / query per lane.
-// A listed task of 2^shift rays is split into its 32-ray slices, one per warp (dynamic).  Each lane walks the sphere
-// hierarchy with its own ray (cs_lane_nearest / cs_lane_shadow), then tests the quadrics (quadric_t rejects a miss
-// without a division) and the planes itself.  Small kernels on purpose: 64 registers, twice the resident warps of the
-// kernels above -- the walk of a lone ray waits on L2 more than it computes.
+// The lane kernels: the tasks the kernels above listed (no narrow cone fits their rays), one ray / query per GROUP of
+// CS_LANE_G lanes (cs_lane_walk).  A listed task of 2^shift rays is split into pieces of 32 / G rays, one per warp
+// (dynamic).  Each group walks the sphere hierarchy with its ray, then its lanes share out the quadrics (quadric_t
+// rejects a miss without a division) and the planes, and combine: the nearest hit is the best of the lanes' bests
+// (ties to the lower insertion order, Scene.cpp:1713); a shadow filter is the product of the lanes' products -- up to two
+// factors commute exactly, a query with three or more occluders and a non-zero product is redone in insertion order by
+// k_shadow_fixup.  Small kernels on purpose: 64 registers, twice the resident warps of the kernels above.
 // ---------------------------------------------------------------------------------------
 #define CS_LANE_MIN_CTAS 8
+#define CS_LANE_RAYS (32 / CS_LANE_G)          // rays per warp
 
 template <int MODE>
 __global__ void __launch_bounds__(CS_THREADS, CS_LANE_MIN_CTAS)
 k_lane_nearest(const __grid_constant__ CullTraceParams cp)
 {
+    constexpr int G = CS_LANE_G;
     const TraceParams& p = cp.t;
     const CullScene& cs = cp.cs;
     const DeviceScene& s = p.s;
-    const int lane = threadIdx.x & 31;
-    const int shift = cp.task_shift, rpt = 1 << (shift - 5);
+    const int lane = threadIdx.x & 31, g = lane & (G - 1);
+    const int shift = cp.task_shift, pieces = (1 << shift) / CS_LANE_RAYS;       // pieces per listed task
     const int n_listed = (int)min(*cp.lane_count, (unsigned int)cp.lane_cap);
     unsigned long long exec_rays = 0;
     for (;;) {
         int w = 0;
         if (lane == 0) w = (int)atomicAdd(cp.lane_task_counter, 1u);
         w = __shfl_sync(FULL_MASK, w, 0);
-        if (w >= n_listed * rpt) break;
-        const int i0 = (cp.lane_list[w / rpt] << shift) + (w % rpt) * 32 + lane;
+        if (w >= n_listed * pieces) break;
+        const int i0 = (cp.lane_list[w / pieces] << shift) + (w % pieces) * CS_LANE_RAYS + lane / G;
         const bool valid = i0 < p.n_rays;
         const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
         RT_CHECK(!valid || (i >= 0 && i < p.n_rays));
@@ -845,24 +890,31 @@ k_lane_nearest(const __grid_constant__ CullTraceParams cp)
         if (valid) { o = f4_xyz(p.in_od0[i]); d = f4_xyz(p.in_od1[i]); }
         float best_t = -1.0f;
         int best_id = -1;
-        const int tests = cs_lane_nearest<MODE>(cs, o, d, valid, best_t, best_id);
+        const int tests = cs_lane_nearest<MODE>(cs, o, d, valid, lane, best_t, best_id);
         exec_rays += (unsigned long long)__reduce_add_sync(FULL_MASK, tests);
-        if (!valid) continue;
-        for (int q = 0; q < s.n_quad; ++q) {
-            const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
-            const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
-            const int ord = __float_as_int(q0.w);
-            bool lin;
-            const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
-            if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+        if (valid) {
+            for (int q = g; q < s.n_quad; q += G) {
+                const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
+                const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
+                const int ord = __float_as_int(q0.w);
+                bool lin;
+                const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
+                if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+            }
+            for (int q = g; q < s.n_plane; q += G) {
+                const float4 nc = __ldg(&s.plane[q].nc);
+                const int ord = s.plane[q].order;
+                const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
+                if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+            }
         }
-        for (int q = 0; q < s.n_plane; ++q) {
-            const float4 nc = __ldg(&s.plane[q].nc);
-            const int ord = s.plane[q].order;
-            const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
-            if (tt > RT_EPS && (tt < best_t || best_t < 0.f || (tt == best_t && ord < best_id))) { best_t = tt; best_id = ord; }
+        #pragma unroll
+        for (int off = 1; off < G; off <<= 1) {             // the group's best (every lane takes part: no divergence here)
+            const float ot = __shfl_xor_sync(FULL_MASK, best_t, off);
+            const int oi = __shfl_xor_sync(FULL_MASK, best_id, off);
+            if (ot > RT_EPS && (ot < best_t || best_t < 0.f || (ot == best_t && oi < best_id))) { best_t = ot; best_id = oi; }
         }
-        p.hit[i] = make_float2(best_t, __int_as_float(best_id));
+        if (valid && g == 0) p.hit[i] = make_float2(best_t, __int_as_float(best_id));
     }
     if (p.stats && lane == 0 && exec_rays)
         atomicAdd(&p.stats[(size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT + ST_TEST_TRI_EXEC], exec_rays);
@@ -872,19 +924,21 @@ template <int MODE>
 __global__ void __launch_bounds__(CS_THREADS, CS_LANE_MIN_CTAS)
 k_lane_shadow(const __grid_constant__ CullShadowParams cp)
 {
+    constexpr int G = CS_LANE_G;
     const ShadowParams& p = cp.s;
     const CullScene& cs = cp.cs;
     const DeviceScene& s = p.s;
-    const int lane = threadIdx.x & 31;
-    const int shift = cp.task_shift, rpt = 1 << (shift - 5);
+    const int lane = threadIdx.x & 31, g = lane & (G - 1);
+    const int shift = cp.task_shift, pieces = (1 << shift) / CS_LANE_RAYS;
     const int n_listed = (int)min(*cp.lane_count, (unsigned int)cp.lane_cap);
-    unsigned long long exec_rays = 0, tests_tri = 0, tests_q = 0, tests_p = 0, fixups = 0;
+    unsigned long long exec_rays = 0;
+    unsigned int n_queries = 0, tests_q = 0, tests_p = 0, fixups = 0;              // per lane; summed over the warp at the end
     for (;;) {
         int w = 0;
         if (lane == 0) w = (int)atomicAdd(cp.lane_task_counter, 1u);
         w = __shfl_sync(FULL_MASK, w, 0);
-        if (w >= n_listed * rpt) break;
-        const int i0 = (cp.lane_list[w / rpt] << shift) + (w % rpt) * 32 + lane;
+        if (w >= n_listed * pieces) break;
+        const int i0 = (cp.lane_list[w / pieces] << shift) + (w % pieces) * CS_LANE_RAYS + lane / G;
         const bool valid = i0 < p.n_queries;
         const int i = (valid && cp.perm) ? cp.perm[i0] : i0;
         RT_CHECK(!valid || (i >= 0 && i < p.n_queries));
@@ -893,55 +947,66 @@ k_lane_shadow(const __grid_constant__ CullShadowParams cp)
         int lid = 0;
         if (valid) { shadow_query<(MODE != 2)>(p, i, o, d, dist); lid = p.sq_src[i].y & ~SQ_FAR_BIT; }
         float fr = valid ? 1.0f : 0.0f, fg = fr, fb = fr;
-        unsigned int occ = 0;
-        int max_ord = -1;
-        const int tests = cs_lane_shadow<MODE>(cs, s.mat, f4_xyz(s.light[lid].l0), o, d, dist, valid, fr, fg, fb, occ, max_ord);
+        unsigned int occ = 0;                                                     // occluders in this lane's product, saturating at 3
+        const int tests = cs_lane_shadow<MODE>(cs, s.mat, f4_xyz(s.light[lid].l0), o, d, dist, valid, lane, fr, fg, fb, occ);
         exec_rays += (unsigned long long)__reduce_add_sync(FULL_MASK, tests);
-        if (!valid) continue;
-        tests_tri += (unsigned long long)cs.n_tri;
-        auto occluder = [&](int ord, int mat) {
-            const float4 m0 = s.mat[mat].m0;
-            const float kt = s.mat[mat].m2.x;
-            fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
-            if (ord < max_ord) occ |= 4u;
-            if ((occ & 3u) < 3u) ++occ;
-            max_ord = max(max_ord, ord);
-        };
-        if (!(fr == 0.f && fg == 0.f && fb == 0.f)) {
-            tests_q += (unsigned long long)s.n_quad; tests_p += (unsigned long long)s.n_plane;
-            for (int q = 0; q < s.n_quad; ++q) {
+        // is the group's product zero already?  (then nobody looks at the side lists)
+        bool zero = fr == 0.f && fg == 0.f && fb == 0.f;
+        #pragma unroll
+        for (int off = 1; off < G; off <<= 1) {
+            const int other = __shfl_xor_sync(FULL_MASK, (int)zero, off);          // (not inside the ||: every lane must shuffle)
+            zero = zero || other != 0;
+        }
+        if (valid && g == 0) ++n_queries;
+        if (valid && !zero) {
+            auto occluder = [&](int mat) {
+                const float4 m0 = s.mat[mat].m0;
+                const float kt = s.mat[mat].m2.x;
+                fr = __fmul_rn(fr, __fmul_rn(m0.x, kt)); fg = __fmul_rn(fg, __fmul_rn(m0.y, kt)); fb = __fmul_rn(fb, __fmul_rn(m0.z, kt));
+                if (occ < 3u) ++occ;
+            };
+            if (g == 0) { tests_q += (unsigned int)s.n_quad; tests_p += (unsigned int)s.n_plane; }
+            for (int q = g; q < s.n_quad; q += G) {
                 const float4 q0 = __ldg(&s.quad[q].q0), q1 = __ldg(&s.quad[q].q1), q2 = __ldg(&s.quad[q].q2);
                 const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
                 bool lin;
                 const float tt = MODE == 2 ? quadric_t<false>(o, d, Q, lin) : quadric_t<true>(o, d, Q, lin);
-                if (tt > RT_EPS && tt < dist) occluder(__float_as_int(q0.w), __float_as_int(q1.w));
+                if (tt > RT_EPS && tt < dist) occluder(__float_as_int(q1.w));
             }
-            for (int q = 0; q < s.n_plane; ++q) {
+            for (int q = g; q < s.n_plane; q += G) {
                 const float4 nc = __ldg(&s.plane[q].nc);
                 const float tt = MODE == 2 ? plane_t<false>(o, d, f4_xyz(nc), nc.w) : plane_t<true>(o, d, f4_xyz(nc), nc.w);
-                if (tt > RT_EPS && tt < dist) occluder(s.plane[q].order, s.plane[q].material);
+                if (tt > RT_EPS && tt < dist) occluder(s.plane[q].material);
             }
         }
-        p.filter[p.sq_dst ? p.sq_dst[i] : i] = make_float4(fr, fg, fb, 0.f);
-        if ((occ & 4u) && (occ & 3u) >= 3u && (fr != 0.f || fg != 0.f || fb != 0.f) && p.fix_count) {
-            const unsigned int k = atomicAdd(p.fix_count, 1u);
-            if ((int)k < p.fix_cap) p.fix_list[k] = i;
-            ++fixups;
+        // the group's product and number of occluders (1 * x = x exactly: the lanes without occluders do not disturb it)
+        #pragma unroll
+        for (int off = 1; off < G; off <<= 1) {
+            fr = __fmul_rn(fr, __shfl_xor_sync(FULL_MASK, fr, off));
+            fg = __fmul_rn(fg, __shfl_xor_sync(FULL_MASK, fg, off));
+            fb = __fmul_rn(fb, __shfl_xor_sync(FULL_MASK, fb, off));
+            occ = min(occ + __shfl_xor_sync(FULL_MASK, occ, off), 3u);
+        }
+        if (valid && g == 0) {
+            p.filter[p.sq_dst ? p.sq_dst[i] : i] = make_float4(fr, fg, fb, 0.f);
+            if (occ >= 3u && (fr != 0.f || fg != 0.f || fb != 0.f) && p.fix_count) {   // order of the factors unknown: redone in order
+                const unsigned int k = atomicAdd(p.fix_count, 1u);
+                if ((int)k < p.fix_cap) p.fix_list[k] = i;
+                ++fixups;
+            }
         }
     }
-    for (int off = 16; off > 0; off >>= 1) {
-        tests_tri += __shfl_xor_sync(FULL_MASK, tests_tri, off);
-        tests_q += __shfl_xor_sync(FULL_MASK, tests_q, off);
-        tests_p += __shfl_xor_sync(FULL_MASK, tests_p, off);
-        fixups += __shfl_xor_sync(FULL_MASK, fixups, off);
-    }
+    n_queries = __reduce_add_sync(FULL_MASK, n_queries);
+    tests_q = __reduce_add_sync(FULL_MASK, tests_q);
+    tests_p = __reduce_add_sync(FULL_MASK, tests_p);
+    fixups = __reduce_add_sync(FULL_MASK, fixups);
     if (lane == 0 && p.stats) {
         unsigned long long* st = p.stats + (size_t)(blockIdx.x % RT_STAT_SLOTS) * ST_COUNT;
-        if (tests_tri) atomicAdd(&st[ST_TEST_TRI_SHADOW], tests_tri);
+        if (n_queries) atomicAdd(&st[ST_TEST_TRI_SHADOW], (unsigned long long)n_queries * (unsigned long long)cs.n_tri);
         if (exec_rays) atomicAdd(&st[ST_TEST_TRI_EXEC], exec_rays);
-        if (tests_q) atomicAdd(&st[ST_TEST_QUAD], tests_q);
-        if (tests_p) atomicAdd(&st[ST_TEST_PLANE], tests_p);
-        if (fixups) atomicAdd(&st[ST_SHADOW_FIXUP], fixups);
+        if (tests_q) atomicAdd(&st[ST_TEST_QUAD], (unsigned long long)tests_q);
+        if (tests_p) atomicAdd(&st[ST_TEST_PLANE], (unsigned long long)tests_p);
+        if (fixups) atomicAdd(&st[ST_SHADOW_FIXUP], (unsigned long long)fixups);
     }
 }
 
@@ -1046,7 +1111,7 @@ cudaError_t launch_cull_nearest(const CullTraceParams& p_in, int sm_count, cudaS
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess || !p.lane_list) return e;
     // the tasks no cone fitted (the count is read on the device; usually none, or the rays of the deep levels)
-    const int lb = lane_grid(n_tasks, per / 32, sm_count);
+    const int lb = lane_grid(n_tasks, per / CS_LANE_RAYS, sm_count);
     if (p.t.mode == 2) k_lane_nearest<2><<<lb, CS_THREADS, 0, st>>>(p);
     else               k_lane_nearest<0><<<lb, CS_THREADS, 0, st>>>(p);
     return cudaGetLastError();
@@ -1062,7 +1127,7 @@ cudaError_t launch_cull_shadow(const CullShadowParams& p, int sm_count, cudaStre
     else               k_cull_shadow<0><<<blocks, CS_THREADS, 0, st>>>(p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess || !p.lane_list) return e;
-    const int lb = lane_grid(n_tasks, per / 32, sm_count);
+    const int lb = lane_grid(n_tasks, per / CS_LANE_RAYS, sm_count);
     if (p.s.mode == 2) k_lane_shadow<2><<<lb, CS_THREADS, 0, st>>>(p);
     else               k_lane_shadow<0><<<lb, CS_THREADS, 0, st>>>(p);
     return cudaGetLastError();
