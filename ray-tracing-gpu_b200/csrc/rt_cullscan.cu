@@ -532,11 +532,16 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
             const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
             const TriMargins mg = tri_margins(e1, e2, dmax);
             bool cand[ST_RPT];
-            bool any = false;
+            cand[0] = triangle_phase1(o[0], d[0], p0, e1, e2, mg);
+            bool any = cand[0];
             #pragma unroll
-            for (int r = 0; r < ST_RPT; ++r) {
-                cand[r] = triangle_phase1(o[r], d[r], p0, e1, e2, mg);
-                any |= cand[r];
+            for (int r = 1; r < ST_RPT; ++r) cand[r] = false;
+            if (rpt > 1) {                                  // (tasks of 32 rays -- the small levels -- fill slot 0 only)
+                #pragma unroll
+                for (int r = 1; r < ST_RPT; ++r) {
+                    cand[r] = triangle_phase1(o[r], d[r], p0, e1, e2, mg);
+                    any |= cand[r];
+                }
             }
             if (__any_sync(FULL_MASK, any)) {
                 #pragma unroll
@@ -598,6 +603,7 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
                 const int ord = __float_as_int(q0.w);
                 #pragma unroll
                 for (int r = 0; r < ST_RPT; ++r) {
+                    if (r >= rpt) break;                    // (small levels: slot 0 only)
                     bool lin;
                     const float tt = MODE == 2 ? quadric_t<false>(o[r], d[r], Q, lin) : quadric_t<true>(o[r], d[r], Q, lin);
                     if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f || (tt == best_t[r] && ord < best_id[r]))) { best_t[r] = tt; best_id[r] = ord; }
@@ -609,6 +615,7 @@ k_cull_nearest(const __grid_constant__ CullTraceParams cp)
             const int ord = s.plane[q].order;
             #pragma unroll
             for (int r = 0; r < ST_RPT; ++r) {
+                if (r >= rpt) break;
                 const float tt = MODE == 2 ? plane_t<false>(o[r], d[r], f4_xyz(nc), nc.w) : plane_t<true>(o[r], d[r], f4_xyz(nc), nc.w);
                 if (tt > RT_EPS && (tt < best_t[r] || best_t[r] < 0.f || (tt == best_t[r] && ord < best_id[r]))) { best_t[r] = tt; best_id[r] = ord; }
             }
@@ -735,11 +742,16 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
             const V3 p0 = f4_xyz(ra), e1 = f4_xyz(rb), e2 = f4_xyz(rc);
             const TriMargins mg = tri_margins(e1, e2, dmax);
             bool cand[ST_RPT];
-            bool any = false;
+            cand[0] = triangle_phase1(o[0], d[0], p0, e1, e2, mg);
+            bool any = cand[0];
             #pragma unroll
-            for (int r = 0; r < ST_RPT; ++r) {
-                cand[r] = triangle_phase1(o[r], d[r], p0, e1, e2, mg);
-                any |= cand[r];
+            for (int r = 1; r < ST_RPT; ++r) cand[r] = false;
+            if (rpt > 1) {                                  // (tasks of 32 queries -- the small levels -- fill slot 0 only)
+                #pragma unroll
+                for (int r = 1; r < ST_RPT; ++r) {
+                    cand[r] = triangle_phase1(o[r], d[r], p0, e1, e2, mg);
+                    any |= cand[r];
+                }
             }
             if (__any_sync(FULL_MASK, any)) {
                 #pragma unroll
@@ -806,6 +818,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
                     const Quadric Q = { q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, q2.x, q2.y, q2.z, q2.w };
                     #pragma unroll
                     for (int r = 0; r < ST_RPT; ++r) {
+                        if (r >= rpt) break;                // (small levels: slot 0 only)
                         bool lin;
                         const float tt = MODE == 2 ? quadric_t<false>(o[r], d[r], Q, lin) : quadric_t<true>(o[r], d[r], Q, lin);
                         if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) occluder(r, __float_as_int(q0.w), __float_as_int(q1.w));
@@ -817,6 +830,7 @@ k_cull_shadow(const __grid_constant__ CullShadowParams cp)
                 const int m = s.plane[q].material, ord = s.plane[q].order;
                 #pragma unroll
                 for (int r = 0; r < ST_RPT; ++r) {
+                    if (r >= rpt) break;
                     const float tt = MODE == 2 ? plane_t<false>(o[r], d[r], f4_xyz(nc), nc.w) : plane_t<true>(o[r], d[r], f4_xyz(nc), nc.w);
                     if (slot[r] >= 0 && tt > RT_EPS && tt < dist[r]) occluder(r, ord, m);
                 }
