@@ -332,3 +332,46 @@ def test_shadow_product_in_insertion_order(rt, renderer, port, synth):
         assert bits_equal(gotf, wantf), flags
         if flags != rt.F_FORCE_RESIDENT:
             assert st.shadow_fixups > 0
+
+
+def test_lane_group_kernels_alone_give_the_reference_frame(rt, renderer, synth, port, monkeypatch):
+    """RTB200_LANE_SIN = RTB200_LANE_SIN_SHADOW = 0: every bundle of the culled scan except the primary rays' goes to
+    the lane kernels (a ray walked by a group of 8 lanes, rt_cullscan.cu cs_lane_walk).  Nearest hits (best of the
+    lanes' bests), shadow products (product of the lanes' products; three or more factors -> fix-up list) and the
+    side lists shared out over the lanes must give the oracle's frame bit for bit -- on a soup with quadrics, mirrors
+    and glass, and on the layered scene whose shadow rays cross up to nine transparent surfaces of all three kinds."""
+    ps = synth.soup(3000, 16, 3, seed=11)
+    renderer.set_scene(ps)
+    fr = rt.make_frame(ps.frame, 240, 144, max_bounces=3, flags=rt.F_FORCE_STREAM)
+    want, _ = port.render(ps, fr, threads=port.max_threads)
+    c = port.ray_counts()
+    base, _, _ = renderer.render(fr)                                   # the thresholds as shipped
+    monkeypatch.setenv("RTB200_LANE_SIN", "0")
+    monkeypatch.setenv("RTB200_LANE_SIN_SHADOW", "0")
+    got, _, st = renderer.render(fr)
+    assert st.rays_reflect + st.rays_refract > 300 and st.rays_shadow > 10000
+    assert (st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract) == (c["primary"], c["shadow"], c["reflect"], c["refract"])
+    assert bits_equal(got, base)                                       # same device, same powf: bit for bit
+    assert np.allclose(got, want, rtol=0, atol=4e-6)                   # (powf of the specular term: host against device)
+    rng = np.random.default_rng(21)
+    pl = _layered_scene(rt, synth, rng)
+    hostbind = import_module("rtb200.hostbind")
+    frame = hostbind.camera_frame((0.0, 300.0, 10.0), (0.0, 0.0, 0.0), (0.0, 0.0, -1.0))
+    frame["background"] = np.zeros(3, np.float32)
+    ps2 = rt.PackedScene(pl.a, frame)
+    renderer.set_scene(ps2)
+    fr2 = rt.make_frame(ps2.frame, 160, 96, max_bounces=12, flags=rt.F_FORCE_STREAM)
+    want2, _ = port.render(ps2, fr2, threads=port.max_threads)
+    got2, _, st2 = renderer.render(fr2)
+    assert st2.depth_levels >= 9 and st2.shadow_fixups > 0
+    assert bits_equal(got2, want2)
+    # the ray-level query: 128 consecutive rays that fly apart in every direction -- no cone fits, the lane kernel takes them
+    renderer.set_scene(ps)
+    n = 20000
+    org = (np.asarray(ps.frame["cam_pos"], np.float32) * 0.3 + rng.uniform(-300, 300, (n, 3))).astype(np.float32)
+    d = rng.normal(size=(n, 3))
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    gi, gt, gn = renderer.trace_nearest(org, d, flags=rt.F_FORCE_STREAM)
+    wi, wt, wn = port.nearest(ps, org, d, threads=port.max_threads)
+    assert np.array_equal(gi, wi) and bits_equal(gt, wt) and bits_equal(gn, wn)
+    assert (wi >= 0).mean() > 0.2
