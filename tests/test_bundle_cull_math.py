@@ -215,3 +215,81 @@ def test_light_cones_never_cull_an_occluder():
     assert not (occ_f & away).any()
     tight = (b["sin_t"] < 0.05) & ~b["wide"]
     assert away[tight].mean() > 0.9
+
+
+# ---- the lane walk (rt_cullscan.cu: cs_lane_ray / cs_lane_query / cs_ray_misses): ONE ray against a sphere --------
+def lane_ray(o, d):
+    """nearest-hit ray: half line from o along d.  o, d: [B, 3]."""
+    l2 = dot(d, d)
+    u = (d * (F(1) / np.sqrt(l2))[:, None]).astype(F)
+    slack = (F(4e-7) * np.abs(o).sum(1, dtype=F) + F(1e-6)).astype(F)
+    return dict(o=o, u=u, far=np.full(len(o), F(3e38), F), dadd=slack, slack=slack,
+                padk=(PADK * np.maximum(F(1), np.sqrt(l2) * F(1.00001))).astype(F))
+
+
+def lane_query(L, d, dist):
+    """shadow query seen from the light: half line from L along -d, hits within `far` of L; the query's own origin --
+    what the pad scales with -- lies within dadd = far of L."""
+    far = (dist * F(1.0001) + F(1e-4)).astype(F)
+    slack = (F(4e-7) * np.abs(L).sum(1, dtype=F) + F(1e-6)).astype(F)
+    return dict(o=L, u=(-d).astype(F), far=far, dadd=(far + slack).astype(F), slack=slack, padk=np.full(len(L), PADK * F(1.0001), F))
+
+
+def ray_misses(r, c, rad, w):
+    """r: dict of [B]; c: [B, K, 3]; rad, w: [B, K].  True = the inflated sphere cannot hold a reported hit of the ray."""
+    v = (c - r["o"][:, None, :]).astype(F)
+    s = dot(v, r["u"][:, None, :])
+    vv = dot(v, v)
+    dist = (np.sqrt(vv) * F(1.00001)).astype(F)
+    D = (dist + r["dadd"][:, None] + rad).astype(F)
+    pad = np.maximum(r["padk"][:, None] * D * w, F(3.8e-6) * D).astype(F)
+    rp = ((rad + pad) * F(1.0001) + (F(1e-5) + r["slack"][:, None] + F(2e-6) * dist)).astype(F)
+    perp2 = (vv - s * s - F(4e-6) * vv).astype(F)
+    with np.errstate(over="ignore"):
+        return (perp2 > rp * rp) | (s < -rp) | (s > r["far"][:, None] + rp)
+
+
+def test_lane_walk_never_skips_an_accepted_triangle():
+    """One ray per group of lanes (the bundles no cone fits): a triangle the reference accepts the ray on -- placed with
+    the ray over its border, down to 1e-5 rad from edge-on, coordinates up to 5e4 -- is never behind a sphere test that
+    says "miss" (without the pad and the slacks the same attack finds ~3 700 violations in 240 000 placements); and the
+    test still rejects what lies off the ray."""
+    rng = np.random.default_rng(13)
+    B, K = 40000, 12
+    # ---- nearest-hit rays: any origin, any direction, |d| in {0.25, 1, 3}
+    o = rng.uniform(-1, 1, (B, 3)) * 10.0 ** rng.uniform(0, 4.7, (B, 1))
+    dlen = np.where(rng.uniform(0, 1, (B, 1)) < 0.1, rng.choice([0.25, 3.0], (B, 1)), 1.0)
+    d = unit(rng.normal(size=(B, 3))) * dlen
+    o1, d1 = f32(o)[:, None, :], f32(d)[:, None, :]
+    tmin, tmax = np.full((B, 1), 0.02) / dlen, np.full((B, 1), 3000.0) / dlen
+    rep = lambda a: np.repeat(a, 8, axis=1)                     # (the helper picks among >= 8 rays: eight copies of the one)
+    p0, e1, e2 = triangles_on_rays(rng, rep(o1), rep(d1), rep(tmin), rep(tmax), K)
+    hit = accepted_by_any_ray(o1, d1, p0, e1, e2)
+    c, rad, w = triangle_sphere(p0, e1, e2)
+    miss = ray_misses(lane_ray(o1[:, 0], d1[:, 0]), c, rad, w)
+    assert hit.mean() > 0.3                                    # (a lone ray over a border: accepted about half of the time)
+    assert not (hit & miss).any(), int((hit & miss).sum())
+    pf, f1, f2 = _far_triangles(rng, o, B, K)
+    cf, rf, wf = triangle_sphere(pf, f1, f2)
+    away = ray_misses(lane_ray(o1[:, 0], d1[:, 0]), cf, rf, wf)
+    assert not (accepted_by_any_ray(o1, d1, pf, f1, f2) & away).any()
+    assert away.mean() > 0.95
+    # ---- shadow queries: hit point -> light, Scene.cpp:1847-1848 in binary32
+    L = rng.uniform(-1, 1, (B, 3)) * 10.0 ** rng.uniform(1, 4.5, (B, 1))
+    pts = L + unit(rng.normal(size=(B, 3))) * 10.0 ** rng.uniform(0.5, 3.5, (B, 1))
+    pts, L32 = f32(pts), f32(L)
+    Ld = (L32 - pts).astype(F)
+    dist = np.sqrt(dot(Ld, Ld)).astype(F)
+    dq = (Ld * (F(1) / dist)[:, None]).astype(F)
+    p1, d1 = pts[:, None, :], dq[:, None, :]
+    p0, e1, e2 = triangles_on_rays(rng, rep(p1), rep(d1), np.full((B, 8), 0.02), rep(dist[:, None].astype(np.float64)), K)
+    occ = accepted_by_any_ray(p1, d1, p0, e1, e2, dist=dist[:, None])
+    c, rad, w = triangle_sphere(p0, e1, e2)
+    miss = ray_misses(lane_query(L32, dq, dist), c, rad, w)
+    assert occ.mean() > 0.3
+    assert not (occ & miss).any(), int((occ & miss).sum())
+    # beyond the light and behind the hit point nothing occludes, and the test knows
+    beyond = f32(L + unit(L - pts.astype(np.float64)) * rng.uniform(40, 400, (B, 1)))[:, None, :]
+    e = f32(rng.uniform(-1, 1, (B, 1, 3)) * 5.0)
+    cb, rb, wb = triangle_sphere(beyond, e, np.roll(e, 1, axis=2))
+    assert ray_misses(lane_query(L32, dq, dist), cb, rb, wb).mean() > 0.99
