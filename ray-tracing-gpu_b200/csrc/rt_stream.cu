@@ -26,7 +26,13 @@ using namespace rtb;
         if (e__ != cudaSuccess) return set_cuda_error(c, e__, #call);   \
     } while (0)
 
-#define STREAM_CHUNK_SAMPLES (8u << 20)
+// Samples traced per pass over the levels (a frame larger than this is rendered in row chunks; config 5: 32 per GPU).
+// Every chunk costs three host synchronisations and the tails of ~18 launches: config 5 took 500 / 483 / 474 ms per
+// frame with 8 / 16 / 32 M samples per chunk (same frame).  32 M samples hold ~8 GB of queues.  RTB200_CHUNK_SAMPLES
+// overrides it (tests render small frames in many chunks).
+#ifndef STREAM_CHUNK_SAMPLES
+#define STREAM_CHUNK_SAMPLES (32u << 20)
+#endif
 
 namespace rtb {
 
@@ -136,7 +142,9 @@ int render_streamed(rtb200_ctx* c, const rtb200_frame* fr, const FrameParams& fp
     if (fr->min_energy < 0.f) children = 2;
     if (!fp.secondary || fr->max_bounces <= 0) children = 0;
 
-    int rows_per_chunk = (int)((STREAM_CHUNK_SAMPLES / (unsigned)fp.LW) / (32u * k)) * 32 * k;
+    unsigned chunk_samples = STREAM_CHUNK_SAMPLES;
+    if (const char* e = getenv("RTB200_CHUNK_SAMPLES")) { const long v = atol(e); if (v > 0 && v <= (1l << 30)) chunk_samples = (unsigned)v; }
+    int rows_per_chunk = (int)((chunk_samples / (unsigned)fp.LW) / (32u * k)) * 32 * k;
     if (rows_per_chunk < 32 * k) rows_per_chunk = 32 * k;
     if (rows_per_chunk > local_LH) rows_per_chunk = ((local_LH + 32 * k - 1) / (32 * k)) * 32 * k;
 

@@ -375,3 +375,24 @@ def test_lane_group_kernels_alone_give_the_reference_frame(rt, renderer, synth, 
     wi, wt, wn = port.nearest(ps, org, d, threads=port.max_threads)
     assert np.array_equal(gi, wi) and bits_equal(gt, wt) and bits_equal(gn, wn)
     assert (wi >= 0).mean() > 0.2
+
+
+def test_row_chunks_change_nothing(rt, renderer, synth, monkeypatch):
+    """RTB200_CHUNK_SAMPLES: the streamed and LBVH paths render a frame larger than the chunk size in row chunks (own
+    queues, counters and read-back per chunk).  A supersampled, ragged frame cut into many chunks must equal the frame
+    rendered in one piece, bit for bit, floats and RGBA8."""
+    soup = synth.soup(1200, 8, 3, seed=4)
+    hf = synth.heightfield(6000, 300.0, 3, seed=9)
+    for ps, flags, spp in ((soup, rt.F_FORCE_STREAM, 1), (soup, rt.F_FORCE_STREAM, 2), (hf, rt.F_USE_BVH, 2)):
+        renderer.set_scene(ps)
+        if flags & rt.F_USE_BVH:
+            renderer.build_bvh()
+        fr = rt.make_frame(ps.frame, 333, 301, max_bounces=3, spp_grid=spp, flags=flags)
+        monkeypatch.delenv("RTB200_CHUNK_SAMPLES", raising=False)
+        want, want8, st1 = renderer.render(fr)
+        assert st1.chunks == 1
+        monkeypatch.setenv("RTB200_CHUNK_SAMPLES", "30000")
+        got, got8, st = renderer.render(fr)
+        assert st.chunks >= 4
+        assert bits_equal(got, want) and np.array_equal(got8, want8)
+        assert (st.rays_primary, st.rays_shadow, st.rays_reflect, st.rays_refract) == (st1.rays_primary, st1.rays_shadow, st1.rays_reflect, st1.rays_refract)
