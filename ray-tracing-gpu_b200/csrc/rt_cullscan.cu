@@ -153,12 +153,11 @@ RT_DEV bool cs_fill(const CullScene& cs, CsWarpSmem& ws, int n_c, bool keep_all,
 }
 
 // ---------------------------------------------------------------------------------------
-// Per-LANE walk -- for the bundles no cone fits (rays of a deep wavefront level: neighbours in space that fly apart in
+// Per-RAY walk -- for the bundles no cone fits (rays of a deep wavefront level: neighbours in space that fly apart in
 // every direction).  Walking the hierarchy with such a bundle keeps everything, i.e. a scan of all triangles by one
-// warp; instead every lane descends the same hierarchy with ITS OWN ray (cs_ray_misses: the cone tests of
-// rt_bundle.cuh for a cone of zero opening, same pad).  The lanes step in lock
-// step -- each tests the 32 entries of its own current block --, the triangles that survive level 0 are tested by that
-// lane alone.  ~50 blocks instead of 10 000 triangles per ray.
+// warp; instead every ray descends the same hierarchy ALONE (cs_ray_misses: the cone tests of rt_bundle.cuh for a cone
+// of zero opening, same pad), carried by a group of lanes (cs_lane_walk below).  The groups of a warp step in lock
+// step -- each over the 32 entries of its own current block.  ~50 blocks instead of 10 000 triangles per ray.
 // ---------------------------------------------------------------------------------------
 // One ray as the lanes see it: the half line from `o` along the unit vector `u`, hits within [0, far] of o.
 // LIGHT: o = the light, u = from the light towards the hit point, far = their distance (widened); the shadow ray's own
@@ -458,7 +457,7 @@ RT_DEV int cs_nearest_cones(const V3* o, const V3* d, const bool* use, Bundle* c
 // Nearest hit (Scene.cpp:1705-1720).  One warp task = 128 rays: PRIMARY a 16 x 8 block of the sample lattice
 // (thread = a 2 x 2 quad, rays generated on the fly), otherwise 128 consecutive queue entries.
 // ---------------------------------------------------------------------------------------
-// A task no (narrow) cone fits is put on cp.lane_list instead of being traced: k_lane_nearest traces those lane by lane
+// A task no (narrow) cone fits is put on cp.lane_list instead of being traced: k_lane_nearest traces those ray by ray
 // -- its own small kernel, so that the rare path costs this one neither registers nor instruction cache.
 template <int MODE, bool PRIMARY>
 __global__ void __launch_bounds__(CS_THREADS, CS_MIN_CTAS)

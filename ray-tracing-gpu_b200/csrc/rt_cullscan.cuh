@@ -29,7 +29,7 @@ struct CullTraceParams {
                                      // rays -- more tasks than warps, tighter cones, and a bundle nothing can cull costs 1/4
     const int*    perm;              // null, or: the i-th ray of the launch is queue entry perm[i] (rays sorted by the
                                      // place they start at, see ShadeAParams::child_key)
-    int*          lane_list;         // tasks no cone fits: listed by the kernel proper, traced lane by lane by a second
+    int*          lane_list;         // tasks no cone fits: listed by the kernel proper, traced ray by ray (8 lanes each) by a second
     unsigned int* lane_count;        // launch (null: such tasks keep every triangle and scan them all)
     unsigned int* lane_task_counter;
     int           lane_cap;
